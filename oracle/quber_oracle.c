@@ -1,0 +1,453 @@
+/*
+ * quber_oracle.c — CPU restatement of QuBER's maskrefiner inference hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under quber_b200/ may import, link or
+ * execute this file; only tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs use it, and there only as the checker
+ * or the timed CPU baseline, never as the product.
+ *
+ * Every function cites the reference file:line (relative to /root/reference)
+ * whose arithmetic it restates.  Parity pinning: tests/golden/ holds outputs
+ * of the reference's own Python (imported from /root/reference by
+ * oracle/gen_golden.py) and tests/test_oracle_golden.py checks this file
+ * against them.  Two sub-steps are pinned only to a tolerance, not bit-exact,
+ * and say so where they are defined: the x4 bilinear up-sampling (PyTorch's
+ * CPU and CUDA kernels themselves differ by 1 ulp) and the float score
+ * reductions.
+ *
+ * Build: make -C oracle   (plain gcc, -ffp-contract=off so that every fused
+ * multiply-add below is an explicit fmaf()).
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define ORACLE_API __attribute__((visibility("default")))
+
+/* ------------------------------------------------------------------------- */
+/* A1: initial-mask encode — maskrefiner/predictor.py:304-357                 */
+/*     (Gaussian table: predictor.py:246-251)                                 */
+/* ------------------------------------------------------------------------- */
+
+/* predictor.py:246-251: g = exp(-((x-x0)^2 + (y-y0)^2) / (2 sigma^2)), float64,
+ * size 6*sigma+3, centre 3*sigma+1.  The heat-map it is pasted into is float32
+ * (predictor.py:304), so only the float32 rounding of g is observable. */
+ORACLE_API void oracle_gaussian_table(int sigma, float *g /* [(6s+3)^2] */) {
+    const int size = 6 * sigma + 3;
+    const double c0 = 3 * sigma + 1;
+    for (int y = 0; y < size; ++y)
+        for (int x = 0; x < size; ++x) {
+            const double dx = (double)x - c0, dy = (double)y - c0;
+            g[y * size + x] = (float)exp(-(dx * dx + dy * dy) / (double)(2 * sigma * sigma));
+        }
+}
+
+/* Python round() / np.round on a float64: half to even (predictor.py:324). */
+static long round_half_even(double v) { return (long)nearbyint(v); }
+
+/* predictor.py:304-357.  masks: [K,H,W] uint8, any non-zero value is "inside".
+ * out: [3,H,W] float32 = (centre heat-map, offset_y / H, offset_x / W).
+ * centres_yx (optional, [K,2] float64) receives the float64 centroids, NaN for
+ * empty masks (which the reference skips, predictor.py:314-316). */
+ORACLE_API void oracle_encode_initial_masks(const uint8_t *masks, int K, int H, int W, int sigma,
+                                            float *out, double *centres_yx) {
+    const size_t HW = (size_t)H * W;
+    const int gs = 6 * sigma + 3;
+    float *g = (float *)malloc(sizeof(float) * gs * gs);
+    oracle_gaussian_table(sigma, g);
+    memset(out, 0, sizeof(float) * 3 * HW);
+    float *center = out, *off_y = out + HW, *off_x = out + 2 * HW;
+    for (int k = 0; k < K; ++k) {
+        const uint8_t *m = masks + (size_t)k * HW;
+        /* np.where + np.mean (predictor.py:313,320): integer index sums are exact in
+         * float64, the mean is one correctly rounded division. */
+        uint64_t sy = 0, sx = 0, n = 0;
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x)
+                if (m[(size_t)y * W + x]) { sy += y; sx += x; ++n; }
+        if (centres_yx) { centres_yx[2 * k] = NAN; centres_yx[2 * k + 1] = NAN; }
+        if (n == 0) continue;
+        const double cy = (double)sy / (double)n, cx = (double)sx / (double)n;
+        if (centres_yx) { centres_yx[2 * k] = cy; centres_yx[2 * k + 1] = cx; }
+        const long y0 = round_half_even(cy), x0 = round_half_even(cx);        /* :324 */
+        const long ulx = x0 - 3 * sigma - 1, uly = y0 - 3 * sigma - 1;        /* :327 */
+        const long brx = x0 + 3 * sigma + 2, bry = y0 + 3 * sigma + 2;        /* :329 */
+        const long cx0 = ulx > 0 ? ulx : 0, cx1 = brx < W ? brx : W;           /* :336 */
+        const long cy0 = uly > 0 ? uly : 0, cy1 = bry < H ? bry : H;           /* :337 */
+        for (long y = cy0; y < cy1; ++y)
+            for (long x = cx0; x < cx1; ++x) {                                 /* :338-341 */
+                const float gv = g[(y - uly) * gs + (x - ulx)];
+                float *c = &center[(size_t)y * W + x];
+                if (gv > *c) *c = gv;
+            }
+        /* :345-346 — float64 arithmetic, float32 store; later masks overwrite. */
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x)
+                if (m[(size_t)y * W + x]) {
+                    off_y[(size_t)y * W + x] = (float)((cy - (double)(float)y) / (double)H);
+                    off_x[(size_t)y * W + x] = (float)((cx - (double)(float)x) / (double)W);
+                }
+    }
+    free(g);
+}
+
+/* ------------------------------------------------------------------------- */
+/* A13: boundary extraction — explicit_error_estimation/util.py:62-99          */
+/*      quadruple maps — tools/ours/panoptic2eee.py:110-123                    */
+/* ------------------------------------------------------------------------- */
+
+/* util.py:72-90: dilation = max(1, round(ratio * sqrt(h^2+w^2))) (Python round,
+ * half-even on float64). */
+ORACLE_API int oracle_boundary_dilation(int H, int W, double ratio) {
+    const double diag = sqrt((double)H * H + (double)W * W);
+    long d = round_half_even(ratio * diag);
+    return d < 1 ? 1 : (int)d;
+}
+
+/* util.py:72-90 literally: 1-px zero border, `d` iterations of 3x3 erosion
+ * (cv2.erode: pixels outside the padded image do not constrain the minimum),
+ * crop, `mask - eroded` in uint8.  Deliberately the slow iterated form, so the
+ * "(2d+1)^2 zero-padded min-filter" shortcut the CUDA kernel takes is checked
+ * against the literal recipe. */
+ORACLE_API void oracle_mask_to_boundary(const uint8_t *mask, int H, int W, int d, uint8_t *out) {
+    const int PH = H + 2, PW = W + 2;
+    uint8_t *a = (uint8_t *)calloc((size_t)PH * PW, 1), *b = (uint8_t *)malloc((size_t)PH * PW);
+    for (int y = 0; y < H; ++y) memcpy(a + (size_t)(y + 1) * PW + 1, mask + (size_t)y * W, W);
+    for (int it = 0; it < d; ++it) {
+        for (int y = 0; y < PH; ++y)
+            for (int x = 0; x < PW; ++x) {
+                uint8_t mn = 255;
+                for (int dy = -1; dy <= 1; ++dy)
+                    for (int dx = -1; dx <= 1; ++dx) {
+                        const int yy = y + dy, xx = x + dx;
+                        if (yy < 0 || yy >= PH || xx < 0 || xx >= PW) continue;
+                        const uint8_t v = a[(size_t)yy * PW + xx];
+                        if (v < mn) mn = v;
+                    }
+                b[(size_t)y * PW + x] = mn;
+            }
+        uint8_t *t = a; a = b; b = t;
+    }
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            out[(size_t)y * W + x] = (uint8_t)(mask[(size_t)y * W + x] - a[(size_t)(y + 1) * PW + x + 1]);
+    free(a); free(b);
+}
+
+/* util.py:62-68: uint8 running sum (wraps mod 256 exactly like numpy), then > 0. */
+ORACLE_API void oracle_masks_to_fg_mask(const uint8_t *masks, int K, int H, int W, uint8_t *fg) {
+    const size_t HW = (size_t)H * W;
+    memset(fg, 0, HW);
+    for (int k = 0; k < K; ++k)
+        for (size_t i = 0; i < HW; ++i) fg[i] = (uint8_t)(fg[i] + masks[(size_t)k * HW + i]);
+    for (size_t i = 0; i < HW; ++i) fg[i] = fg[i] > 0;
+}
+
+/* util.py:92-99: union (uint8 running sum > 0) of the per-mask boundaries.
+ * per_instance (optional) receives each mask's boundary [K,H,W]. */
+ORACLE_API void oracle_masks_to_boundary(const uint8_t *masks, int K, int H, int W, int d,
+                                         uint8_t *per_instance, uint8_t *boundary) {
+    const size_t HW = (size_t)H * W;
+    uint8_t *tmp = (uint8_t *)malloc(HW);
+    memset(boundary, 0, HW);
+    for (int k = 0; k < K; ++k) {
+        uint8_t *dst = per_instance ? per_instance + (size_t)k * HW : tmp;
+        oracle_mask_to_boundary(masks + (size_t)k * HW, H, W, d, dst);
+        for (size_t i = 0; i < HW; ++i) boundary[i] = (uint8_t)(boundary[i] + dst[i]);
+    }
+    for (size_t i = 0; i < HW; ++i) boundary[i] = boundary[i] > 0;
+    free(tmp);
+}
+
+/* panoptic2eee.py:110-123: out[0..3] = TP, TN, FP, FN of (gt, pred) binary maps
+ * (channel order TP,TN,FP,FN as model.py:210-213 stacks them). */
+ORACLE_API void oracle_quadruple_maps(const uint8_t *gt, const uint8_t *pred, size_t n, uint8_t *out) {
+    for (size_t i = 0; i < n; ++i) {
+        const int g = gt[i] != 0, p = pred[i] != 0;
+        out[i] = g && p;
+        out[n + i] = !g && !p;
+        out[2 * n + i] = !g && p;
+        out[3 * n + i] = g && !p;
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* A6: x-scale bilinear up-sampling — model.py:689-708                         */
+/* ------------------------------------------------------------------------- */
+
+/* F.interpolate(scale_factor=s, mode="bilinear", align_corners=False), written
+ * as PyTorch's CUDA kernel writes it (aten UpSampleBilinear2d.cu: source index
+ * max(r*(dst+0.5)-0.5, 0) with r = 1/s, lambdas, then
+ * h0*(w0*a + w1*b) + h1*(w0*c + w1*d)) with every product and sum rounded
+ * separately.  PINNED TO TOLERANCE ONLY: PyTorch's own CPU and CUDA kernels
+ * differ from each other by 1 ulp, so the golden test bounds the difference
+ * (<= 4 ulp) instead of demanding equality.  `mul` post-scales (offset * 4,
+ * model.py:698). */
+static inline float up_sample_at(const float *src, int h, int w, float rh, float rw, int oy, int ox) {
+    float sy = rh * ((float)oy + 0.5f) - 0.5f; if (sy < 0.f) sy = 0.f;
+    float sx = rw * ((float)ox + 0.5f) - 0.5f; if (sx < 0.f) sx = 0.f;
+    const int y1 = (int)sy, x1 = (int)sx;
+    const int yp = (y1 < h - 1) ? 1 : 0, xp = (x1 < w - 1) ? 1 : 0;
+    const float ly = sy - (float)y1, lx = sx - (float)x1;
+    const float hy = 1.f - ly, hx = 1.f - lx;
+    const float a = src[(size_t)y1 * w + x1], b = src[(size_t)y1 * w + x1 + xp];
+    const float c = src[(size_t)(y1 + yp) * w + x1], d = src[(size_t)(y1 + yp) * w + x1 + xp];
+    const float top = hx * a + lx * b, bot = hx * c + lx * d;
+    return hy * top + ly * bot;
+}
+
+ORACLE_API void oracle_upsample_bilinear(const float *src, int C, int h, int w, int scale, float mul,
+                                         float *dst /* [C, h*scale, w*scale] */) {
+    const int H = h * scale, W = w * scale;
+    const float r = 1.0f / (float)scale;
+    for (int c = 0; c < C; ++c)
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                float v = up_sample_at(src + (size_t)c * h * w, h, w, r, r, y, x);
+                if (mul != 1.0f) v *= mul;
+                dst[((size_t)c * H + y) * W + x] = v;
+            }
+}
+
+/* ------------------------------------------------------------------------- */
+/* A8: find_instance_center — post_processing.py:9-41                          */
+/* ------------------------------------------------------------------------- */
+
+static int cmp_float_desc(const void *a, const void *b) {
+    const float x = *(const float *)a, y = *(const float *)b;
+    return (x < y) - (x > y);
+}
+
+/* Returns the number of centres written to out_yx ([cap,2] int32, raster order
+ * like torch.nonzero).  top_k <= 0 means None. */
+ORACLE_API int oracle_find_instance_center(const float *heat, int H, int W, float threshold,
+                                           int nms_kernel, int top_k, int32_t *out_yx, int cap) {
+    const size_t HW = (size_t)H * W;
+    float *t = (float *)malloc(sizeof(float) * HW), *kept = (float *)malloc(sizeof(float) * HW);
+    /* :22 F.threshold(x, thr, -1): x > thr ? x : -1 */
+    for (size_t i = 0; i < HW; ++i) t[i] = heat[i] > threshold ? heat[i] : -1.0f;
+    /* :25-29 max_pool2d(kernel, stride 1, pad (k-1)/2, implicit -inf padding); keep equal */
+    const int p = (nms_kernel - 1) / 2;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            float mx = -INFINITY;
+            for (int dy = -p; dy <= nms_kernel - 1 - p; ++dy)
+                for (int dx = -p; dx <= nms_kernel - 1 - p; ++dx) {
+                    const int yy = y + dy, xx = x + dx;
+                    if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+                    const float v = t[(size_t)yy * W + xx];
+                    if (v > mx) mx = v;
+                }
+            const float v = t[(size_t)y * W + x];
+            kept[(size_t)y * W + x] = (v != mx) ? -1.0f : v;
+        }
+    float cut = 0.0f; /* :37 `> 0` when top_k is None */
+    if (top_k > 0) {
+        /* :40-41 kth largest of the whole (filler-including) map, clamped at 0, strict > */
+        float *s = (float *)malloc(sizeof(float) * HW);
+        memcpy(s, kept, sizeof(float) * HW);
+        qsort(s, HW, sizeof(float), cmp_float_desc);
+        const float kth = s[(size_t)top_k - 1 < HW ? (size_t)top_k - 1 : HW - 1];
+        cut = kth < 0.f ? 0.f : kth;
+        free(s);
+    }
+    int n = 0;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            if (kept[(size_t)y * W + x] > cut) {
+                if (n < cap) { out_yx[2 * n] = y; out_yx[2 * n + 1] = x; }
+                ++n;
+            }
+    free(t); free(kept);
+    return n;
+}
+
+/* ------------------------------------------------------------------------- */
+/* A9: group_pixels — post_processing.py:44-76                                 */
+/* ------------------------------------------------------------------------- */
+
+/* Distance as torch's CPU vector_norm evaluates it for a length-2 reduction
+ * (checked bit-for-bit in this container on 7e5 samples): acc = dy*dy, then
+ * acc = fma(dx, dx, acc), then sqrt.  argmin keeps the first minimum. */
+ORACLE_API void oracle_group_pixels(const int32_t *centres_yx, int K, const float *offsets /* [2,H,W] */,
+                                    int H, int W, int32_t *ins_id /* [H,W], values 1..K */) {
+    const size_t HW = (size_t)H * W;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            const size_t i = (size_t)y * W + x;
+            const float ly = (float)y + offsets[i], lx = (float)x + offsets[HW + i];   /* :66 */
+            int best = 0; float bd = INFINITY;
+            for (int k = 0; k < K; ++k) {
+                const float dy = (float)centres_yx[2 * k] - ly, dx = (float)centres_yx[2 * k + 1] - lx;
+                const float dist = sqrtf(fmaf(dx, dx, dy * dy));                          /* :71 */
+                if (dist < bd) { bd = dist; best = k; }                                   /* :75 */
+            }
+            ins_id[i] = best + 1;
+        }
+}
+
+/* model.py:292 `r.sigmoid().round()`: 1 iff float32 sigmoid(x) > 0.5.  Measured
+ * on torch 2.11 CPU (vector and scalar paths, exhaustive over [5e-8, 2e-7]):
+ * the first float that rounds to 1 is 0x33c00001, i.e. x > 1.5 * 2^-24. */
+#define FG_LOGIT_CUT 8.940696716308594e-08f
+ORACLE_API int oracle_fg_from_logit(float x) { return x > FG_LOGIT_CUT; }
+
+/* ------------------------------------------------------------------------- */
+/* A8-A12 composed: get_panoptic_segmentation (post_processing.py:165-221),    */
+/* merge_semantic_and_instance (:110-162), instance extraction                 */
+/* (model.py:313-356), error-map decode (eval/eval_utils.py:308-328)           */
+/* ------------------------------------------------------------------------- */
+
+typedef struct {
+    int32_t n_centres;    /* K' after NMS/top-k */
+    int32_t n_instances;  /* K'' surviving labels (panoptic != void) */
+} oracle_post_counts;
+
+/*
+ * Inputs are full-resolution float maps (the reference's r, c, o, b after
+ * sem_seg_postprocess, model.py:266-289):
+ *   fg_logit [H,W], centre [H,W], offset [2,H,W], eee [C,H,W] (may be NULL, C in 2..4).
+ * Outputs (caller-allocated):
+ *   panoptic [H,W] float32: void_label (-1) / 1000 / 1001...     (merge, :129-160)
+ *   labels   [cap] int32: surviving panoptic labels ascending     (model.py:322)
+ *   masks    [cap,H,W] uint8 0/1                                  (model.py:331-334)
+ *   scores   [cap] float32 = mean(sigmoid(fg)[mask]) * c[int(cy), int(cx)]  (:340-350)
+ *   boxes    [cap,4] float32 = x_min, y_min, x_max+1, y_max+1     (BitMasks.get_bounding_boxes)
+ *   onehot   [C,H,W] uint8: argmax over eee channels, first max wins (eval_utils.py:311-313)
+ *   centres_yx [top_k,2] int32
+ * thing_ids for the uoais-sim metadata is dict_values([0])
+ * (register_uoais_sim_panoptic.py:189-193), so background (class 0) is
+ * "thing" and skipped at :153-156 while class 1 with ins_seg == 0 is pasted as
+ * stuff label 1*label_divisor when its area >= stuff_area — reachable exactly
+ * when no centre was found (ins_seg all zero).
+ */
+ORACLE_API int oracle_post_process(const float *fg_logit, const float *centre, const float *offset,
+                                   const float *eee, int C, int H, int W, float threshold,
+                                   int nms_kernel, int top_k, int min_area, int stuff_area,
+                                   int label_divisor, float void_label, int cap, float *panoptic,
+                                   int32_t *labels, uint8_t *masks, float *scores, float *boxes,
+                                   uint8_t *onehot, int32_t *centres_yx, oracle_post_counts *counts) {
+    const size_t HW = (size_t)H * W;
+    int32_t *ctr = (int32_t *)malloc(sizeof(int32_t) * 2 * HW);
+    const int K = oracle_find_instance_center(centre, H, W, threshold, nms_kernel, top_k, ctr, (int)HW);
+    if (centres_yx) memcpy(centres_yx, ctr, sizeof(int32_t) * 2 * (size_t)(K < top_k || top_k <= 0 ? K : top_k));
+    int32_t *ins = (int32_t *)calloc(HW, sizeof(int32_t));
+    uint8_t *fg = (uint8_t *)malloc(HW);
+    for (size_t i = 0; i < HW; ++i) fg[i] = (uint8_t)oracle_fg_from_logit(fg_logit[i]);
+    if (K > 0) {                                             /* post_processing.py:103-107 */
+        oracle_group_pixels(ctr, K, offset, H, W, ins);
+        for (size_t i = 0; i < HW; ++i) ins[i] = fg[i] ? ins[i] : 0;
+    }
+    for (size_t i = 0; i < HW; ++i) panoptic[i] = void_label;   /* :129 */
+    /* :137-150: ids ascending; area filter 512 (hard-coded in the reference as 512) */
+    int64_t *area = (int64_t *)calloc((size_t)K + 1, sizeof(int64_t));
+    for (size_t i = 0; i < HW; ++i) if (ins[i] > 0) area[ins[i]]++;
+    int32_t *newid = (int32_t *)calloc((size_t)K + 1, sizeof(int32_t));
+    int running = 0;
+    for (int id = 1; id <= K; ++id) {
+        if (area[id] == 0) continue;          /* :143-144 */
+        if (area[id] < min_area) continue;    /* :145-146 */
+        newid[id] = ++running;                /* class is always 1 inside is_thing */
+    }
+    for (size_t i = 0; i < HW; ++i)
+        if (ins[i] > 0 && newid[ins[i]] > 0) panoptic[i] = (float)(1 * label_divisor + newid[ins[i]]);
+    /* :152-160 stuff paste: class 0 is in thing_ids -> skipped; class 1 where ins_seg == 0 */
+    {
+        int64_t a = 0;
+        for (size_t i = 0; i < HW; ++i) a += (fg[i] && ins[i] == 0);
+        if (a > 0 && a >= stuff_area)
+            for (size_t i = 0; i < HW; ++i)
+                if (fg[i] && ins[i] == 0) panoptic[i] = (float)(1 * label_divisor);
+    }
+    /* model.py:322-354: np.unique ascending, skip -1 */
+    int n_inst = 0;
+    {
+        /* labels present: label_divisor (stuff) and label_divisor + 1..running */
+        int has_stuff = 0;
+        for (size_t i = 0; i < HW && !has_stuff; ++i) has_stuff = panoptic[i] == (float)label_divisor;
+        for (int l = has_stuff ? 0 : 1; l <= running; ++l) {
+            const float lab = (float)(label_divisor + l);
+            if (void_label == lab) continue;
+            if (n_inst < cap) {
+                uint8_t *m = masks ? masks + (size_t)n_inst * HW : NULL;
+                double ssum = 0.0; uint64_t sy = 0, sx = 0, n = 0;
+                int x0 = W, y0 = H, x1 = -1, y1 = -1;
+                for (int y = 0; y < H; ++y)
+                    for (int x = 0; x < W; ++x) {
+                        const size_t i = (size_t)y * W + x;
+                        const int in = panoptic[i] == lab;
+                        if (m) m[i] = (uint8_t)in;
+                        if (!in) continue;
+                        ssum += (double)(1.0f / (1.0f + expf(-fg_logit[i])));   /* :319,341 */
+                        sy += y; sx += x; ++n;
+                        if (x < x0) x0 = x; if (x > x1) x1 = x;
+                        if (y < y0) y0 = y; if (y > y1) y1 = y;
+                    }
+                labels[n_inst] = label_divisor + l;
+                /* :343-348 centroid of the mask, int() truncation */
+                const int cy = (int)((double)sy / (double)n), cx = (int)((double)sx / (double)n);
+                const float sem = (float)(ssum / (double)n);
+                if (scores) scores[n_inst] = sem * centre[(size_t)cy * W + cx];   /* :350 */
+                if (boxes) {
+                    boxes[4 * n_inst + 0] = (float)x0; boxes[4 * n_inst + 1] = (float)y0;
+                    boxes[4 * n_inst + 2] = (float)(x1 + 1); boxes[4 * n_inst + 3] = (float)(y1 + 1);
+                }
+            }
+            ++n_inst;
+        }
+    }
+    /* eval_utils.py:311-313: argmax(0) -> stack of (== i) */
+    if (eee && onehot)
+        for (size_t i = 0; i < HW; ++i) {
+            int best = 0; float bv = eee[i];
+            for (int c = 1; c < C; ++c) if (eee[(size_t)c * HW + i] > bv) { bv = eee[(size_t)c * HW + i]; best = c; }
+            for (int c = 0; c < C; ++c) onehot[(size_t)c * HW + i] = (uint8_t)(c == best);
+        }
+    if (counts) { counts->n_centres = K; counts->n_instances = n_inst; }
+    free(ctr); free(ins); free(fg); free(area); free(newid);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------- */
+/* A14: MSDeformAttn forward                                                  */
+/*   OPS/src/cuda/ms_deform_im2col_cuda.cuh:38-89 (bilinear), :242-304 (loop)  */
+/*   CPU twin OPS/functions/ms_deform_attn_func.py:52-72                       */
+/* ------------------------------------------------------------------------- */
+
+#define MSDA_IMPL(NAME, T)                                                                          \
+    ORACLE_API void NAME(const T *value, const int64_t *shapes, const int64_t *starts, const T *loc,    \
+                         const T *attn, int B, int S, int M, int D, int L, int Q, int P, T *out) {  \
+        for (int b = 0; b < B; ++b)                                                                 \
+            for (int q = 0; q < Q; ++q)                                                             \
+                for (int m = 0; m < M; ++m) {                                                       \
+                    const size_t qm = ((size_t)b * Q + q) * M + m;                                  \
+                    for (int c = 0; c < D; ++c) {                                                   \
+                        T col = 0;                                                                  \
+                        for (int l = 0; l < L; ++l) {                                               \
+                            const int h = (int)shapes[2 * l], w = (int)shapes[2 * l + 1];           \
+                            const T *v = value + ((size_t)b * S + (size_t)starts[l]) * M * D;       \
+                            for (int p = 0; p < P; ++p) {                                           \
+                                const size_t lp = (qm * L + l) * P + p;                             \
+                                const T lw = loc[2 * lp], lh = loc[2 * lp + 1], a = attn[lp];       \
+                                const T him = lh * h - (T)0.5, wim = lw * w - (T)0.5; /* cuh:290 */ \
+                                if (!(him > -1 && wim > -1 && him < h && wim < w)) continue;        \
+                                const int hl = (int)floor(him), wl = (int)floor(wim);               \
+                                const int hh_ = hl + 1, wh_ = wl + 1;                               \
+                                const T lhh = him - hl, lww = wim - wl, hh = 1 - lhh, hw = 1 - lww; \
+                                T v1 = 0, v2 = 0, v3 = 0, v4 = 0;                                   \
+                                if (hl >= 0 && wl >= 0) v1 = v[((size_t)hl * w + wl) * M * D + m * D + c];         \
+                                if (hl >= 0 && wh_ <= w - 1) v2 = v[((size_t)hl * w + wh_) * M * D + m * D + c];   \
+                                if (hh_ <= h - 1 && wl >= 0) v3 = v[((size_t)hh_ * w + wl) * M * D + m * D + c];   \
+                                if (hh_ <= h - 1 && wh_ <= w - 1) v4 = v[((size_t)hh_ * w + wh_) * M * D + m * D + c]; \
+                                const T w1 = hh * hw, w2 = hh * lww, w3 = lhh * hw, w4 = lhh * lww;  \
+                                col += (w1 * v1 + w2 * v2 + w3 * v3 + w4 * v4) * a;                  \
+                            }                                                                       \
+                        }                                                                           \
+                        out[qm * D + c] = col;                                                      \
+                    }                                                                               \
+                }                                                                                   \
+    }
+
+MSDA_IMPL(oracle_msda_forward_f32, float)
+MSDA_IMPL(oracle_msda_forward_f64, double)
