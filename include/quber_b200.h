@@ -1,0 +1,170 @@
+/*
+ * quber_b200.h — C ABI of libquber_b200.so: the B200 (sm_100a) implementation of
+ * QuBER's maskrefiner inference hot path.
+ *
+ * Conventions (all entry points):
+ *   - plain C, no C++/torch types; every pointer marked "dev" is a CUDA device
+ *     pointer owned by the caller, "host" a host pointer; nothing is allocated
+ *     or freed inside the library; scratch comes from the caller through a
+ *     `*_workspace_bytes` query;
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it,
+ *     re-entrant, hold no global state and are CUDA-graph capturable (no host
+ *     synchronisation, no host read-back);
+ *   - return value: QUBER_OK or a negative QUBER_E_* code (never an exception).
+ *     The reference reports the same conditions through ATen asserts
+ *     (OPS/src/cuda/ms_deform_attn_cuda.cu:33-57) or Python ValueError
+ *     (maskrefiner/modeling/mask_refiner/post_processing.py:199-204); the Python
+ *     shim in quber_b200/_lib.py maps the codes back to those exception types.
+ *
+ * Reference paths are relative to the QuBER checkout; OPS =
+ * ext_modules/UnseenObjectsWithMeanShift/MSMFormer/meanshiftformer/modeling/pixel_decoder/ops.
+ * The reference has no C ABI of its own (its native surface is a pybind/ATen
+ * module, OPS/src/vision.cpp:18-21); each entry point below names the reference
+ * interface it stands in for.
+ */
+#ifndef QUBER_B200_H
+#define QUBER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QUBER_ABI_VERSION 1
+
+enum {
+    QUBER_OK = 0,
+    QUBER_E_INVALID = -1,    /* bad argument (null pointer, non-positive size, unsupported value) */
+    QUBER_E_WORKSPACE = -2,  /* workspace pointer null / too small */
+    QUBER_E_CUDA = -3,       /* a CUDA runtime call or kernel launch failed */
+    QUBER_E_ALIGN = -4,      /* pointer not aligned as documented */
+    QUBER_E_UNSUPPORTED = -5 /* shape outside what the kernels implement (documented per call) */
+};
+
+/* Library / ABI version (QUBER_ABI_VERSION it was built with). */
+int quber_version(void);
+/* Static string for a QUBER_* code. */
+const char *quber_error_string(int code);
+/* cudaGetLastError-style text of the last CUDA failure seen by this thread (static buffer). */
+const char *quber_last_cuda_error(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * K0  initial-mask encode — replaces the NumPy loop of MaskRefinerPredictor.predict
+ *     (maskrefiner/predictor.py:304-357; twin: PerturbedInputGenerator.__call__,
+ *     maskrefiner/data/dataset_mappers/target_generator.py:229-276).
+ *   masks  dev [B,K,H,W] uint8, non-zero = inside;  K <= 254
+ *   gauss  dev [(6*sigma+3)^2] float32 — quber_gaussian_table() fills a host copy
+ *   out    dev [B,3,H,W] float32 = (centre heat-map, offset_y/H, offset_x/W)
+ *   Later masks overwrite earlier ones in the offset planes, empty masks are skipped, centroid
+ *   arithmetic is float64 exactly as in the reference.  W must be a multiple of 16 and `masks`
+ *   16-byte aligned (QUBER_E_ALIGN otherwise).
+ * ------------------------------------------------------------------------------------------- */
+void quber_gaussian_table(int sigma, float *host_table);
+size_t quber_encode_workspace_bytes(int B, int K, int H, int W);
+int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int sigma,
+                               const float *gauss, float *out, void *workspace, size_t workspace_bytes,
+                               void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K2  boundary extraction by erosion — replaces mask_to_boundary / masks_to_boundary /
+ *     masks_to_fg_mask (explicit_error_estimation/util.py:62-99; duplicates
+ *     tools/ours/panoptic2eee.py:23-59).
+ *   masks         dev [B,K,H,W] uint8 (any values; erosion is a true uint8 min filter)
+ *   d             erosion iterations = quber_boundary_dilation(H, W, ratio); 1 <= d <= 64
+ *   per_instance  dev [B,K,H,W] uint8 or NULL: mask - erode_d(mask)      (util.py:72-90)
+ *   boundary      dev [B,H,W] uint8 or NULL: (uint8 sum over k of per-instance) > 0   (util.py:92-99)
+ *   fg            dev [B,H,W] uint8 or NULL: (uint8 sum over k of masks) > 0          (util.py:62-68)
+ *   W must be a multiple of 16 and the pointers 16-byte aligned.
+ * quber_quadruple_maps: TP/TN/FP/FN of two binary maps (tools/ours/panoptic2eee.py:110-123),
+ *   gt, pred dev [B,n] uint8 (non-zero = set) -> out dev [B,4,n] uint8 in (TP,TN,FP,FN) order
+ *   (maskrefiner/modeling/mask_refiner/model.py:210-213).
+ * ------------------------------------------------------------------------------------------- */
+int quber_boundary_dilation(int H, int W, double ratio);
+int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
+                        uint8_t *boundary, uint8_t *fg, void *stream);
+int quber_quadruple_maps(const uint8_t *gt, const uint8_t *pred, int B, size_t n, uint8_t *out, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K3/K4  post-processing — replaces, in ONE call and with no host round trip:
+ *     MaskRefinerInsEmbedHead.forward's x4 bilinear up-sampling (model.py:689-708),
+ *     `r.sigmoid().round()` (model.py:292), find_instance_center / group_pixels /
+ *     get_instance_segmentation / merge_semantic_and_instance / get_panoptic_segmentation
+ *     (maskrefiner/modeling/mask_refiner/post_processing.py:9-221), the per-instance loop of
+ *     MaskRefiner.forward (model.py:313-356) and the caller-side error-map decode
+ *     (eval/eval_utils.py:308-328).
+ * ------------------------------------------------------------------------------------------- */
+typedef struct quber_post_params {
+    int32_t B, H, W;        /* output (full) resolution */
+    int32_t scale;          /* 1: inputs are full-resolution maps (already up-sampled / post-processed
+                               by the caller); s>1: inputs are [.., H/s, W/s] head outputs and the
+                               kernels up-sample by s on the fly (bilinear, align_corners=False) */
+    float offset_mul;       /* multiplies the offset after up-sampling (model.py:698: 4.0 when scale=4) */
+    int32_t eee_channels;   /* 0 (no error head) or 2..4 */
+    float threshold;        /* MODEL.PANOPTIC_DEEPLAB.CENTER_THRESHOLD */
+    int32_t nms_kernel;     /* odd, <= 15 */
+    int32_t top_k;          /* 1..1024 */
+    int32_t min_area;       /* 512: post_processing.py:145 */
+    int32_t stuff_area;     /* MODEL.PANOPTIC_DEEPLAB.STUFF_AREA */
+    int32_t label_divisor;  /* metadata label_divisor (1000) */
+    float void_label;       /* -1 */
+    int32_t max_instances;  /* capacity (rows) of masks/labels/scores/boxes over the whole batch */
+    int32_t flags;          /* QUBER_POST_* bits */
+} quber_post_params;
+
+/* centers_yx / n_centers are INPUTS (group_pixels with caller-supplied centres, post_processing.py:44);
+ * the NMS / top-k kernels are skipped */
+#define QUBER_POST_GIVEN_CENTERS 1
+/* find_instance_center(top_k=None) (post_processing.py:36-37): every positive NMS survivor is a
+ * centre; top_k is then only the capacity of centers_yx (status bit 2 is set if it overflowed) */
+#define QUBER_POST_NO_TOPK 2
+
+typedef struct quber_post_io {
+    /* inputs, dev float32; low resolution [B,C,H/scale,W/scale] */
+    const float *foreground; /* [B,1,h,w] logits */
+    const float *center;     /* [B,1,h,w] */
+    const float *offset;     /* [B,2,h,w] (y,x) */
+    const float *eee;        /* [B,C,h,w] or NULL */
+    /* outputs, dev; any of the optional ones may be NULL */
+    float *sem_seg;          /* opt [B,1,H,W]  up-sampled foreground logits ("sem_seg") */
+    float *eee_full;         /* opt [B,C,H,W]  up-sampled error logits ("eee_boundary") */
+    uint8_t *eee_onehot;     /* opt [B,C,H,W]  argmax one-hot (TP,TN,FP,FN) */
+    float *panoptic;         /* opt [B,H,W]    void_label / label_divisor (+ running id) */
+    int32_t *label_map;      /* opt [B,H,W]    0 = void, j+1 = j-th instance of the image (collective payload) */
+    int32_t *ins_seg;        /* opt [B,H,W]    foreground * grouped centre id (get_instance_segmentation, :107) */
+    uint8_t *masks;          /* opt [max_instances,H,W] 0/1, images back to back (inst_offsets) */
+    int32_t *centers_yx;     /* req [B,top_k,2] */
+    int32_t *n_centers;      /* req [B] */
+    int32_t *inst_offsets;   /* req [B+1] exclusive prefix of instances per image */
+    int32_t *labels;         /* req [max_instances] panoptic label of each instance */
+    float *scores;           /* req [max_instances] */
+    float *boxes;            /* req [max_instances,4] x0,y0,x1,y1 */
+    int32_t *status;         /* req [1] bit 0: max_instances exceeded (extra instances dropped);
+                                        bit 1: more than top_k centres with QUBER_POST_NO_TOPK (extra dropped) */
+} quber_post_io;
+
+size_t quber_post_workspace_bytes(const quber_post_params *p);
+int quber_post_process(const quber_post_params *p, const quber_post_io *io, void *workspace,
+                       size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K1  MSDeformAttn forward — replaces MultiScaleDeformableAttention.ms_deform_attn_forward
+ *     (OPS/src/vision.cpp:18-21 -> OPS/src/cuda/ms_deform_attn_cuda.cu:25-85 ->
+ *     OPS/src/cuda/ms_deform_im2col_cuda.cuh:242-304).
+ *   value   dev [B,S,M,D]      float32 (dtype 0) or bfloat16 (dtype 1)
+ *   shapes  dev [L,2] int64 (H_l, W_l);  starts dev [L] int64  — int64 as in the reference API
+ *   loc     dev [B,Q,M,L,P,2]  float32 (x,y) in [0,1];  attn dev [B,Q,M,L,P] float32
+ *   out     dev [B,Q,M*D]      float32 (dtype 0) / bfloat16 (dtype 1)
+ *   L <= 8.  Vector path for D in {8,16,32,64} (16-byte aligned value/out), scalar path otherwise.
+ *   `im2col_step` of the reference API is accepted by the Python shim and ignored: the whole batch
+ *   is one launch.
+ * ------------------------------------------------------------------------------------------- */
+int quber_msda_forward(const void *value, const int64_t *shapes, const int64_t *starts, const float *loc,
+                       const float *attn, int B, int S, int M, int D, int L, int Q, int P, int dtype,
+                       void *out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QUBER_B200_H */

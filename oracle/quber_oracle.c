@@ -112,16 +112,28 @@ ORACLE_API int oracle_boundary_dilation(int H, int W, double ratio) {
  * against the literal recipe. */
 ORACLE_API void oracle_mask_to_boundary(const uint8_t *mask, int H, int W, int d, uint8_t *out) {
     const int PH = H + 2, PW = W + 2;
-    uint8_t *a = (uint8_t *)calloc((size_t)PH * PW, 1), *b = (uint8_t *)malloc((size_t)PH * PW);
+    /* Only the bounding box of the non-zero pixels can change: erosion of zeros is zero.  The
+     * iterations below are the literal 3x3 recipe, just not run over rows/columns that are all 0. */
+    int y0 = H, y1 = -1, x0 = W, x1 = -1;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x)
+            if (mask[(size_t)y * W + x]) {
+                if (y < y0) y0 = y; if (y > y1) y1 = y;
+                if (x < x0) x0 = x; if (x > x1) x1 = x;
+            }
+    if (y1 < 0) { memset(out, 0, (size_t)H * W); return; }
+    /* padded coordinates of the box (+1 for the border), clipped to the padded image */
+    const int by0 = y0 + 1, by1 = y1 + 1, bx0 = x0 + 1, bx1 = x1 + 1;
+    uint8_t *a = (uint8_t *)calloc((size_t)PH * PW, 1), *b = (uint8_t *)calloc((size_t)PH * PW, 1);
     for (int y = 0; y < H; ++y) memcpy(a + (size_t)(y + 1) * PW + 1, mask + (size_t)y * W, W);
     for (int it = 0; it < d; ++it) {
-        for (int y = 0; y < PH; ++y)
-            for (int x = 0; x < PW; ++x) {
+        for (int y = by0; y <= by1; ++y)
+            for (int x = bx0; x <= bx1; ++x) {
                 uint8_t mn = 255;
                 for (int dy = -1; dy <= 1; ++dy)
                     for (int dx = -1; dx <= 1; ++dx) {
                         const int yy = y + dy, xx = x + dx;
-                        if (yy < 0 || yy >= PH || xx < 0 || xx >= PW) continue;
+                        if (yy < 0 || yy >= PH || xx < 0 || xx >= PW) continue;   /* cv2.erode ignores outside */
                         const uint8_t v = a[(size_t)yy * PW + xx];
                         if (v < mn) mn = v;
                     }
@@ -418,33 +430,35 @@ ORACLE_API int oracle_post_process(const float *fg_logit, const float *centre, c
 #define MSDA_IMPL(NAME, T)                                                                          \
     ORACLE_API void NAME(const T *value, const int64_t *shapes, const int64_t *starts, const T *loc,    \
                          const T *attn, int B, int S, int M, int D, int L, int Q, int P, T *out) {  \
+        static const T zeros[1024] = {0};                                                           \
         for (int b = 0; b < B; ++b)                                                                 \
             for (int q = 0; q < Q; ++q)                                                             \
                 for (int m = 0; m < M; ++m) {                                                       \
                     const size_t qm = ((size_t)b * Q + q) * M + m;                                  \
-                    for (int c = 0; c < D; ++c) {                                                   \
-                        T col = 0;                                                                  \
-                        for (int l = 0; l < L; ++l) {                                               \
-                            const int h = (int)shapes[2 * l], w = (int)shapes[2 * l + 1];           \
-                            const T *v = value + ((size_t)b * S + (size_t)starts[l]) * M * D;       \
-                            for (int p = 0; p < P; ++p) {                                           \
-                                const size_t lp = (qm * L + l) * P + p;                             \
-                                const T lw = loc[2 * lp], lh = loc[2 * lp + 1], a = attn[lp];       \
-                                const T him = lh * h - (T)0.5, wim = lw * w - (T)0.5; /* cuh:290 */ \
-                                if (!(him > -1 && wim > -1 && him < h && wim < w)) continue;        \
-                                const int hl = (int)floor(him), wl = (int)floor(wim);               \
-                                const int hh_ = hl + 1, wh_ = wl + 1;                               \
-                                const T lhh = him - hl, lww = wim - wl, hh = 1 - lhh, hw = 1 - lww; \
-                                T v1 = 0, v2 = 0, v3 = 0, v4 = 0;                                   \
-                                if (hl >= 0 && wl >= 0) v1 = v[((size_t)hl * w + wl) * M * D + m * D + c];         \
-                                if (hl >= 0 && wh_ <= w - 1) v2 = v[((size_t)hl * w + wh_) * M * D + m * D + c];   \
-                                if (hh_ <= h - 1 && wl >= 0) v3 = v[((size_t)hh_ * w + wl) * M * D + m * D + c];   \
-                                if (hh_ <= h - 1 && wh_ <= w - 1) v4 = v[((size_t)hh_ * w + wh_) * M * D + m * D + c]; \
-                                const T w1 = hh * hw, w2 = hh * lww, w3 = lhh * hw, w4 = lhh * lww;  \
-                                col += (w1 * v1 + w2 * v2 + w3 * v3 + w4 * v4) * a;                  \
-                            }                                                                       \
+                    T *col = out + qm * D;                                                          \
+                    for (int c = 0; c < D; ++c) col[c] = 0;                                         \
+                    /* per channel the sum runs over (l, p) in the reference's order (cuh:279-301); \
+                     * the channel loop is innermost only so that gcc can vectorise it */          \
+                    for (int l = 0; l < L; ++l) {                                                   \
+                        const int h = (int)shapes[2 * l], w = (int)shapes[2 * l + 1];               \
+                        const T *v = value + ((size_t)b * S + (size_t)starts[l]) * M * D + m * D;   \
+                        for (int p = 0; p < P; ++p) {                                               \
+                            const size_t lp = (qm * L + l) * P + p;                                 \
+                            const T lw = loc[2 * lp], lh = loc[2 * lp + 1], a = attn[lp];           \
+                            const T him = lh * h - (T)0.5, wim = lw * w - (T)0.5; /* cuh:290 */     \
+                            if (!(him > -1 && wim > -1 && him < h && wim < w)) continue;            \
+                            const int hl = (int)floor(him), wl = (int)floor(wim);                   \
+                            const int hh_ = hl + 1, wh_ = wl + 1;                                   \
+                            const T lhh = him - hl, lww = wim - wl, hh = 1 - lhh, hw = 1 - lww;     \
+                            const T *p1 = zeros, *p2 = zeros, *p3 = zeros, *p4 = zeros;             \
+                            if (hl >= 0 && wl >= 0) p1 = v + ((size_t)hl * w + wl) * M * D;         \
+                            if (hl >= 0 && wh_ <= w - 1) p2 = v + ((size_t)hl * w + wh_) * M * D;   \
+                            if (hh_ <= h - 1 && wl >= 0) p3 = v + ((size_t)hh_ * w + wl) * M * D;   \
+                            if (hh_ <= h - 1 && wh_ <= w - 1) p4 = v + ((size_t)hh_ * w + wh_) * M * D; \
+                            const T w1 = hh * hw, w2 = hh * lww, w3 = lhh * hw, w4 = lhh * lww;      \
+                            for (int c = 0; c < D; ++c)                                             \
+                                col[c] += (w1 * p1[c] + w2 * p2[c] + w3 * p3[c] + w4 * p4[c]) * a;  \
                         }                                                                           \
-                        out[qm * D + c] = col;                                                      \
                     }                                                                               \
                 }                                                                                   \
     }

@@ -1,0 +1,209 @@
+// K2: per-instance boundary extraction by erosion + union / foreground maps + quadruple maps.
+//
+// Reference: explicit_error_estimation/util.py:62-99 (masks_to_fg_mask, mask_to_boundary,
+// masks_to_boundary), tools/ours/panoptic2eee.py:110-123 (TP/TN/FP/FN).
+//
+// `d` iterations of a 3x3 erosion on a 1-px zero-padded image equal ONE zero-padded
+// (2d+1)x(2d+1) uint8 min filter; that is what runs here, separably and four pixels per
+// instruction (__vminu4 on packed bytes) with window doubling:
+//     F_1 = x,  F_2p[i] = min(F_p[i], F_p[i+p]),  win_w[i] = min(F_p[i], F_p[i+w-p])  (p = 2^k <= w)
+// first along rows at byte granularity (__byte_perm realigns the shifted words), then along
+// columns on whole words.  One CTA owns one (image, tile) and walks all K mask planes, so the
+// union (`boundary`) and foreground (`fg`) sums live in registers and are written once.
+// A tile (+halo) whose bytes are all equal has no boundary: it is detected on load and skipped.
+#include "common.cuh"
+
+namespace quber {
+
+constexpr int B_TW = 128;           // tile width in pixels (32 packed words)
+constexpr int B_TWW = B_TW / 4;     // 32
+constexpr int B_TH = 64;            // tile height
+constexpr int B_THREADS = 256;
+constexpr int B_RPT = B_TH * B_TWW / B_THREADS;  // central words per thread (8)
+
+__device__ __forceinline__ uint32_t shift_bytes(uint32_t lo, uint32_t hi, int s) {
+    // bytes [s, s+4) of the little-endian 8-byte string lo:hi, s in 0..3
+    return __byte_perm(lo, hi, 0x3210 + 0x1111 * s);
+}
+
+__global__ void __launch_bounds__(B_THREADS)
+boundary_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, int d, uint8_t *__restrict__ per_instance,
+                uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg) {
+    extern __shared__ uint32_t smem[];
+    const int hw = (d + 3) >> 2;            // halo words per side
+    const int WS = B_TWW + 2 * hw;          // words per staged row
+    const int R = B_TH + 2 * d;             // staged rows
+    uint32_t *bufA = smem, *bufB = smem + (size_t)R * WS;
+    const int tid = threadIdx.x;
+    const int b = blockIdx.z;
+    const int ty0 = blockIdx.y * B_TH, tx0 = blockIdx.x * B_TW;
+    const int Ww = W >> 2;                  // words per image row
+    const size_t HW = (size_t)H * W;
+    const int w = 2 * d + 1;
+    int p_top = 1;
+    while (p_top * 2 <= w) p_top *= 2;
+    const int lead = 4 * hw - d;            // byte offset of (x - d) relative to staged byte 0 for central x = 4*hw
+
+    const int ci = tid & 31, cr0 = tid >> 5;   // central word column, first central row
+    uint32_t uni_acc[B_RPT], fg_acc[B_RPT];
+#pragma unroll
+    for (int j = 0; j < B_RPT; ++j) uni_acc[j] = fg_acc[j] = 0;
+
+    for (int k = 0; k < K; ++k) {
+        const uint32_t *plane = reinterpret_cast<const uint32_t *>(masks + ((size_t)b * K + k) * HW);
+        // ---- stage tile + halo (zero outside the image) ----
+        uint32_t diff = 0, first = 0;
+        {
+            const int gy = ty0 - d, gxw = (tx0 >> 2) - hw;
+            if (gy >= 0 && gxw >= 0) first = __ldg(plane + (size_t)gy * Ww + gxw);
+            first = (first & 0xffu) * 0x01010101u;
+        }
+        for (int idx = tid; idx < R * WS; idx += B_THREADS) {
+            const int r = idx / WS, i = idx - r * WS;
+            const int gy = ty0 - d + r, gxw = (tx0 >> 2) - hw + i;
+            uint32_t v = 0;
+            if (gy >= 0 && gy < H && gxw >= 0 && gxw < Ww) v = ld_stream_u1(plane + (size_t)gy * Ww + gxw);
+            bufA[idx] = v;
+            diff |= v ^ first;
+        }
+        uint32_t orig[B_RPT];
+        const int any = __syncthreads_or(diff != 0);
+        uint32_t er[B_RPT];
+        if (!any) {
+            // uniform tile + halo: eroded == mask everywhere -> boundary 0
+#pragma unroll
+            for (int j = 0; j < B_RPT; ++j) { orig[j] = first; er[j] = first; }
+        } else {
+#pragma unroll
+            for (int j = 0; j < B_RPT; ++j) orig[j] = bufA[(size_t)(cr0 + 8 * j + d) * WS + hw + ci];
+            // ---- horizontal pass: doubling on every staged row ----
+            uint32_t *src = bufA, *dst = bufB;
+            for (int p = 1; p < p_top; p <<= 1) {
+                const int sw = p >> 2, sb = p & 3;
+                for (int idx = tid; idx < R * WS; idx += B_THREADS) {
+                    const int r = idx / WS, i = idx - r * WS;
+                    const uint32_t *row = src + (size_t)r * WS;
+                    const int j0 = i + sw;
+                    const uint32_t lo = j0 < WS ? row[j0] : 0u, hi = j0 + 1 < WS ? row[j0 + 1] : 0u;
+                    dst[idx] = __vminu4(row[i], sb ? shift_bytes(lo, hi, sb) : lo);
+                }
+                __syncthreads();
+                uint32_t *t = src; src = dst; dst = t;
+            }
+            // combine: Hmin[x] = min(F_p[x-d], F_p[x+d+1-p]) for the central words; written compactly
+            // (B_TWW words per row) into dst
+            {
+                const int o1 = lead, o2 = lead + w - p_top;     // byte offsets relative to word (i - hw)*4 ... see below
+                for (int idx = tid; idx < R * B_TWW; idx += B_THREADS) {
+                    const int r = idx >> 5, i = idx & 31;
+                    const uint32_t *row = src + (size_t)r * WS;
+                    // central word i covers staged bytes [4*(hw+i), +4); window start byte = 4*(hw+i) - d = 4*i + lead
+                    const int a1 = 4 * i + o1, a2 = 4 * i + o2;
+                    const int w1 = a1 >> 2, s1 = a1 & 3, w2 = a2 >> 2, s2 = a2 & 3;
+                    const uint32_t v1 = shift_bytes(row[w1], w1 + 1 < WS ? row[w1 + 1] : 0u, s1);
+                    const uint32_t v2 = shift_bytes(row[w2], w2 + 1 < WS ? row[w2 + 1] : 0u, s2);
+                    dst[idx] = __vminu4(v1, v2);
+                }
+                __syncthreads();
+                uint32_t *t = src; src = dst; dst = t;
+            }
+            // ---- vertical pass on the compact [R][32] array ----
+            for (int p = 1; p < p_top; p <<= 1) {
+                for (int idx = tid; idx < R * B_TWW; idx += B_THREADS) {
+                    const int r = idx >> 5;
+                    const uint32_t other = (r + p < R) ? src[idx + p * B_TWW] : 0u;
+                    dst[idx] = __vminu4(src[idx], other);
+                }
+                __syncthreads();
+                uint32_t *t = src; src = dst; dst = t;
+            }
+#pragma unroll
+            for (int j = 0; j < B_RPT; ++j) {
+                const int r = cr0 + 8 * j;      // output row r <-> staged rows r .. r+2d
+                er[j] = __vminu4(src[r * B_TWW + ci], src[(r + w - p_top) * B_TWW + ci]);
+            }
+        }
+        // ---- write / accumulate ----
+#pragma unroll
+        for (int j = 0; j < B_RPT; ++j) {
+            const int gy = ty0 + cr0 + 8 * j, gxw = (tx0 >> 2) + ci;
+            const uint32_t bd = __vsub4(orig[j], er[j]);
+            uni_acc[j] = __vadd4(uni_acc[j], bd);
+            fg_acc[j] = __vadd4(fg_acc[j], orig[j]);
+            if (per_instance && gy < H && gxw < Ww)
+                st_stream_u1(per_instance + ((size_t)b * K + k) * HW + (size_t)gy * W + 4 * gxw, bd);
+        }
+        __syncthreads();   // staged buffers are reused by the next plane
+    }
+#pragma unroll
+    for (int j = 0; j < B_RPT; ++j) {
+        const int gy = ty0 + cr0 + 8 * j, gxw = (tx0 >> 2) + ci;
+        if (gy < H && gxw < Ww) {
+            const size_t o = (size_t)b * HW + (size_t)gy * W + 4 * gxw;
+            // per byte: (sum > 0) -> 1.  __vcmpne4 gives 0xff per non-zero byte.
+            if (boundary) st_stream_u1(boundary + o, __vcmpne4(uni_acc[j], 0u) & 0x01010101u);
+            if (fg) st_stream_u1(fg + o, __vcmpne4(fg_acc[j], 0u) & 0x01010101u);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+quadruple_kernel(const uint8_t *__restrict__ gt, const uint8_t *__restrict__ pred, size_t n, uint8_t *__restrict__ out) {
+    const int b = blockIdx.y;
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    if (i >= n) return;
+    const uint8_t *g = gt + (size_t)b * n + i, *p = pred + (size_t)b * n + i;
+    uint8_t *o = out + (size_t)b * 4 * n + i;
+    if (i + 16 <= n && ((n & 15) == 0)) {
+        const uint4 gv = ld_stream_u4(g), pv = ld_stream_u4(p);
+        uint4 tp, tn, fp, fn;
+#define QUAD(c)                                                   \
+        {                                                         \
+            const uint32_t G = __vcmpne4(gv.c, 0u), P = __vcmpne4(pv.c, 0u); \
+            tp.c = (G & P) & 0x01010101u; tn.c = (~G & ~P) & 0x01010101u;     \
+            fp.c = (~G & P) & 0x01010101u; fn.c = (G & ~P) & 0x01010101u;     \
+        }
+        QUAD(x) QUAD(y) QUAD(z) QUAD(w)
+#undef QUAD
+        st_stream_u4(o, tp); st_stream_u4(o + n, tn); st_stream_u4(o + 2 * n, fp); st_stream_u4(o + 3 * n, fn);
+    } else {
+        for (int j = 0; j < 16 && i + j < n; ++j) {
+            const bool G = g[j] != 0, P = p[j] != 0;
+            o[j] = G && P; o[n + j] = !G && !P; o[2 * n + j] = !G && P; o[3 * n + j] = G && !P;
+        }
+    }
+}
+
+}  // namespace quber
+
+extern "C" int quber_boundary_dilation(int H, int W, double ratio) {
+    // util.py:80-84: int(round(ratio * sqrt(h^2 + w^2))) (Python round: half to even), at least 1
+    const double diag = sqrt((double)H * H + (double)W * W);
+    const long dd = (long)nearbyint(ratio * diag);
+    return dd < 1 ? 1 : (int)dd;
+}
+
+extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
+                                   uint8_t *boundary, uint8_t *fg, void *stream) {
+    using namespace quber;
+    if (!masks || B <= 0 || K <= 0 || H <= 0 || W <= 0 || d < 1 || d > 64) return QUBER_E_INVALID;
+    if (!per_instance && !boundary && !fg) return QUBER_E_INVALID;
+    if (W % 16 != 0 || !aligned16(masks) || (per_instance && !aligned16(per_instance)) ||
+        (boundary && !aligned16(boundary)) || (fg && !aligned16(fg)))
+        return QUBER_E_ALIGN;
+    const int hw = (d + 3) >> 2, WS = B_TWW + 2 * hw, R = B_TH + 2 * d;
+    const size_t smem = 2 * (size_t)R * WS * sizeof(uint32_t);
+    QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid(cdiv(W, B_TW), cdiv(H, B_TH), B);
+    boundary_kernel<<<grid, B_THREADS, smem, (cudaStream_t)stream>>>(masks, K, H, W, d, per_instance, boundary, fg);
+    return check_launch("boundary_kernel");
+}
+
+extern "C" int quber_quadruple_maps(const uint8_t *gt, const uint8_t *pred, int B, size_t n, uint8_t *out, void *stream) {
+    using namespace quber;
+    if (!gt || !pred || !out || B <= 0 || n == 0) return QUBER_E_INVALID;
+    if ((n % 16 == 0) && (!aligned16(gt) || !aligned16(pred) || !aligned16(out))) return QUBER_E_ALIGN;
+    dim3 grid((unsigned)((n + 16 * 256 - 1) / (16 * 256)), B);
+    quadruple_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(gt, pred, n, out);
+    return check_launch("quadruple_kernel");
+}

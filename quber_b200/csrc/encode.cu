@@ -1,0 +1,180 @@
+// K0: initial-mask encode (centre heat-map + normalised offsets).
+//
+// Reference: maskrefiner/predictor.py:304-357 (MaskRefinerPredictor.predict), Gaussian table
+// predictor.py:246-251; twin maskrefiner/data/dataset_mappers/target_generator.py:229-276.
+//
+// Two passes, both one CTA per 16x128-pixel tile of one image:
+//   reduce: reads the K mask planes once (8 pixels / thread / plane, 64-bit streaming loads),
+//           accumulates per-mask (count, sum y, sum x) — integers, so the float64 centroid is the
+//           same correctly-rounded division numpy makes — and records per pixel the LAST mask that
+//           covers it (the reference's overwrite order).
+//   emit:   per pixel, offsets from that last mask's centroid in float64 (as numpy: float64
+//           arithmetic, float32 store) and the max over the clipped 63x63 Gaussian pastes.
+// HBM traffic = K*HW (masks) + HW (last-mask map, written then read) + 12*HW (output).
+#include <limits.h>
+#include <math.h>
+
+#include "common.cuh"
+
+namespace quber {
+
+constexpr int E_TW = 128, E_TH = 16, E_THREADS = 256;   // 8 px per thread
+constexpr uint8_t E_NONE = 0xff;
+
+struct EncSums { unsigned long long n, sy, sx; };
+
+__global__ void __launch_bounds__(E_THREADS)
+encode_reduce_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, EncSums *__restrict__ sums,
+                     uint8_t *__restrict__ lastk) {
+    extern __shared__ unsigned int acc[];   // [K][3]
+    const int tid = threadIdx.x, b = blockIdx.z;
+    for (int i = tid; i < 3 * K; i += E_THREADS) acc[i] = 0;
+    __syncthreads();
+    const int y = blockIdx.y * E_TH + (tid >> 4), x0 = blockIdx.x * E_TW + (tid & 15) * 8;
+    const bool inb = y < H && x0 < W;       // W % 16 == 0 -> the 8 pixels are all in or all out
+    const size_t HW = (size_t)H * W;
+    const size_t pix = (size_t)y * W + x0;
+    uint32_t last_lo = 0xffffffffu, last_hi = 0xffffffffu;   // packed per-pixel last k
+    const uint8_t *base = masks + (size_t)b * K * HW + pix;
+    for (int k = 0; k < K; ++k) {
+        uint2 v = make_uint2(0, 0);
+        if (inb) v = ld_stream_u2(base + (size_t)k * HW);
+        const bool nz = (v.x | v.y) != 0;
+        if (__any_sync(0xffffffffu, nz)) {
+            unsigned n = 0, sx = 0;
+            if (nz) {
+                const uint32_t mlo = __vcmpne4(v.x, 0u), mhi = __vcmpne4(v.y, 0u);   // 0xff per set byte
+                const uint32_t kk = (uint32_t)k * 0x01010101u;
+                last_lo = (last_lo & ~mlo) | (kk & mlo);
+                last_hi = (last_hi & ~mhi) | (kk & mhi);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const unsigned a = (mlo >> (8 * j)) & 1u, c = (mhi >> (8 * j)) & 1u;
+                    n += a + c;
+                    sx += a * (unsigned)(x0 + j) + c * (unsigned)(x0 + 4 + j);
+                }
+            }
+            unsigned sy = n * (unsigned)y;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                n += __shfl_xor_sync(0xffffffffu, n, o);
+                sy += __shfl_xor_sync(0xffffffffu, sy, o);
+                sx += __shfl_xor_sync(0xffffffffu, sx, o);
+            }
+            if ((tid & 31) == 0) {
+                atomicAdd(&acc[3 * k], n); atomicAdd(&acc[3 * k + 1], sy); atomicAdd(&acc[3 * k + 2], sx);
+            }
+        }
+    }
+    if (inb) st_stream_u2(lastk + (size_t)b * HW + pix, make_uint2(last_lo, last_hi));
+    __syncthreads();
+    for (int k = tid; k < K; k += E_THREADS)
+        if (acc[3 * k]) {
+            EncSums *s = sums + (size_t)b * K + k;
+            atomicAdd(&s->n, (unsigned long long)acc[3 * k]);
+            atomicAdd(&s->sy, (unsigned long long)acc[3 * k + 1]);
+            atomicAdd(&s->sx, (unsigned long long)acc[3 * k + 2]);
+        }
+}
+
+struct EncCentre { double cy, cx; int uly, ulx; };
+
+__global__ void __launch_bounds__(E_THREADS)
+encode_emit_kernel(const EncSums *__restrict__ sums, const uint8_t *__restrict__ lastk, int K, int H, int W, int sigma,
+                   const float *__restrict__ gauss, float *__restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    EncCentre *ctr = reinterpret_cast<EncCentre *>(smraw);            // [K]
+    int *list = reinterpret_cast<int *>(ctr + K);                     // [K] masks whose paste touches this tile
+    __shared__ int nlist;
+    const int tid = threadIdx.x, b = blockIdx.z;
+    const int gs = 6 * sigma + 3, half = 3 * sigma + 1;
+    const int ty0 = blockIdx.y * E_TH, tx0 = blockIdx.x * E_TW;
+    if (tid == 0) nlist = 0;
+    __syncthreads();
+    for (int k = tid; k < K; k += E_THREADS) {
+        const EncSums s = sums[(size_t)b * K + k];
+        EncCentre c;
+        c.cy = c.cx = 0.0; c.uly = c.ulx = INT_MIN / 2;
+        if (s.n) {
+            c.cy = (double)s.sy / (double)s.n;                       // np.mean of exact integer sums
+            c.cx = (double)s.sx / (double)s.n;
+            c.uly = __double2int_rn(c.cy) - half;                    // round(): half to even (predictor.py:324-327)
+            c.ulx = __double2int_rn(c.cx) - half;
+            if (c.uly < ty0 + E_TH && c.uly + gs > ty0 && c.ulx < tx0 + E_TW && c.ulx + gs > tx0)
+                list[atomicAdd(&nlist, 1)] = k;
+        }
+        ctr[k] = c;
+    }
+    __syncthreads();
+    const int y = ty0 + (tid >> 4), x0 = tx0 + (tid & 15) * 8;
+    if (y >= H || x0 >= W) return;
+    const size_t HW = (size_t)H * W, pix = (size_t)y * W + x0;
+    float cen[8], oy[8], ox[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) cen[j] = 0.f;
+    const int n = nlist;
+    for (int t = 0; t < n; ++t) {                                     // max is order-independent
+        const EncCentre c = ctr[list[t]];
+        const int gy = y - c.uly;
+        if ((unsigned)gy >= (unsigned)gs) continue;
+        const float *grow = gauss + gy * gs;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int gx = x0 + j - c.ulx;
+            if ((unsigned)gx < (unsigned)gs) cen[j] = fmaxf(cen[j], __ldg(grow + gx));
+        }
+    }
+    const uint2 lk = *reinterpret_cast<const uint2 *>(lastk + (size_t)b * HW + pix);
+    const double dH = (double)H, dW = (double)W;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const uint32_t k = ((j < 4 ? lk.x : lk.y) >> (8 * (j & 3))) & 0xffu;
+        if (k == E_NONE) { oy[j] = 0.f; ox[j] = 0.f; continue; }
+        const EncCentre c = ctr[k];
+        oy[j] = (float)((c.cy - (double)y) / dH);                    // predictor.py:345-346
+        ox[j] = (float)((c.cx - (double)(x0 + j)) / dW);
+    }
+    float *o = out + (size_t)b * 3 * HW + pix;
+    st_stream_f4(o, make_float4(cen[0], cen[1], cen[2], cen[3]));
+    st_stream_f4(o + 4, make_float4(cen[4], cen[5], cen[6], cen[7]));
+    st_stream_f4(o + HW, make_float4(oy[0], oy[1], oy[2], oy[3]));
+    st_stream_f4(o + HW + 4, make_float4(oy[4], oy[5], oy[6], oy[7]));
+    st_stream_f4(o + 2 * HW, make_float4(ox[0], ox[1], ox[2], ox[3]));
+    st_stream_f4(o + 2 * HW + 4, make_float4(ox[4], ox[5], ox[6], ox[7]));
+}
+
+}  // namespace quber
+
+extern "C" void quber_gaussian_table(int sigma, float *host_table) {
+    // predictor.py:246-251 (float64 exp, observed through a float32 heat-map)
+    const int size = 6 * sigma + 3;
+    const double c0 = 3 * sigma + 1;
+    for (int y = 0; y < size; ++y)
+        for (int x = 0; x < size; ++x) {
+            const double dx = (double)x - c0, dy = (double)y - c0;
+            host_table[y * size + x] = (float)exp(-(dx * dx + dy * dy) / (double)(2 * sigma * sigma));
+        }
+}
+
+extern "C" size_t quber_encode_workspace_bytes(int B, int K, int H, int W) {
+    if (B <= 0 || K <= 0 || H <= 0 || W <= 0) return 0;
+    return quber::align_up((size_t)B * K * sizeof(quber::EncSums), 256) + quber::align_up((size_t)B * H * W, 256);
+}
+
+extern "C" int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int sigma, const float *gauss,
+                                          float *out, void *workspace, size_t workspace_bytes, void *stream) {
+    using namespace quber;
+    if (!masks || !gauss || !out || B <= 0 || K <= 0 || K > 254 || H <= 0 || W <= 0 || sigma < 1) return QUBER_E_INVALID;
+    if (W % 16 != 0 || !aligned16(masks) || !aligned16(out)) return QUBER_E_ALIGN;
+    if (!workspace || workspace_bytes < quber_encode_workspace_bytes(B, K, H, W) || !aligned16(workspace)) return QUBER_E_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    EncSums *sums = reinterpret_cast<EncSums *>(workspace);
+    const size_t sums_bytes = align_up((size_t)B * K * sizeof(EncSums), 256);
+    uint8_t *lastk = reinterpret_cast<uint8_t *>(workspace) + sums_bytes;
+    QUBER_CUDA_TRY(cudaMemsetAsync(sums, 0, sums_bytes, st));
+    dim3 grid(cdiv(W, E_TW), cdiv(H, E_TH), B);
+    encode_reduce_kernel<<<grid, E_THREADS, 3 * K * sizeof(unsigned), st>>>(masks, K, H, W, sums, lastk);
+    if (int rc = check_launch("encode_reduce_kernel")) return rc;
+    encode_emit_kernel<<<grid, E_THREADS, K * (sizeof(EncCentre) + sizeof(int)), st>>>(sums, lastk, K, H, W, sigma, gauss, out);
+    return check_launch("encode_emit_kernel");
+}

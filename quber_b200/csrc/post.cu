@@ -1,0 +1,603 @@
+// K3/K4: centre NMS + top-k, then the fused decode / grouping / panoptic merge / instance pass.
+//
+// Reference (all of it replaced by quber_post_process, with no host round trip):
+//   maskrefiner/modeling/mask_refiner/model.py:689-708   x4 bilinear up-sampling of every head output
+//   model.py:292                                         r.sigmoid().round()
+//   maskrefiner/modeling/mask_refiner/post_processing.py:9-41    find_instance_center
+//   post_processing.py:44-76                                     group_pixels
+//   post_processing.py:79-162                                    get_instance_segmentation, merge_semantic_and_instance
+//   model.py:313-356                                     per-instance masks / scores / boxes
+//   eval/eval_utils.py:308-328                           error-map argmax -> one-hot
+//
+// Launch sequence on one stream (B images per launch, no host synchronisation):
+//   memset(zeroed workspace) -> center_nms -> center_select -> group -> relabel -> offsets -> emit -> finalize
+// The 1/4-resolution head outputs are the only float inputs read from HBM; the up-sampled maps are
+// recomputed where they are consumed (the bilinear formula is deterministic) and written once when
+// the caller asks for them (sem_seg, eee_full).
+#include "common.cuh"
+
+namespace quber {
+
+constexpr int P_TW = 128, P_TH = 16, P_THREADS = 256;   // pixel tile of group/emit: 8 px per thread
+constexpr int N_TW = 64, N_TH = 32;                     // pixel tile of the NMS kernel
+constexpr int SEL_THREADS = 1024;
+constexpr int SEL_SMEM_VALS = 4096;
+constexpr unsigned INS_STUFF = 0xffffu;                 // foreground pixel of an image without centres
+
+struct InstStat {                 // per (image, instance index); zero-initialised, integer atomics only
+    unsigned long long sig;       // sum of sigmoid(fg logit) in 2^-32 fixed point (deterministic)
+    unsigned long long sy, sx;
+    unsigned int cnt, maxx, maxnx, maxy, maxny, pad;
+};
+
+struct PostWs {
+    uint32_t *bitmask;   // [B,H,WB]
+    uint16_t *ins;       // [B,H,W]
+    uint32_t *area;      // [B,top_k+1]   (index 0: foreground pixels of a centre-less image)   zeroed
+    InstStat *stats;     // [B,top_k]                                                         zeroed
+    uint32_t *newid;     // [B,top_k+1]
+    int32_t *n_inst;     // [B]
+    int32_t *has_stuff;  // [B]
+    size_t zero_bytes;   // area + stats are contiguous
+    size_t total;
+};
+
+static PostWs carve(const quber_post_params &p, void *base) {
+    PostWs w;
+    const size_t B = p.B, H = p.H, W = p.W, WB = (W + 31) / 32, K1 = (size_t)p.top_k + 1;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
+    char *b = static_cast<char *>(base);
+    const size_t o_area = take(B * K1 * 4);
+    const size_t o_stats = take(B * (size_t)p.top_k * sizeof(InstStat));
+    w.zero_bytes = off;
+    const size_t o_bit = take(B * H * WB * 4);
+    const size_t o_ins = take(B * H * W * 2);
+    const size_t o_new = take(B * K1 * 4);
+    const size_t o_ni = take(B * 4);
+    const size_t o_hs = take(B * 4);
+    w.total = off;
+    w.area = reinterpret_cast<uint32_t *>(b + o_area);
+    w.stats = reinterpret_cast<InstStat *>(b + o_stats);
+    w.bitmask = reinterpret_cast<uint32_t *>(b + o_bit);
+    w.ins = reinterpret_cast<uint16_t *>(b + o_ins);
+    w.newid = reinterpret_cast<uint32_t *>(b + o_new);
+    w.n_inst = reinterpret_cast<int32_t *>(b + o_ni);
+    w.has_stuff = reinterpret_cast<int32_t *>(b + o_hs);
+    return w;
+}
+
+// ------------------------------------------------------------------------------------------------
+// find_instance_center, part 1: threshold + kxk max-pool NMS -> candidate bit mask.
+// post_processing.py:22-29.  Candidate <=> thresholded value equals its window maximum and is > 0
+// (only positive survivors can pass the final `> max(kth, 0)` test at :37/:41).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(P_THREADS)
+center_nms_kernel(const float *__restrict__ center, int H, int W, int scale, float threshold, int nms_kernel,
+                  uint32_t *__restrict__ bitmask) {
+    extern __shared__ float nsm[];
+    const int p = (nms_kernel - 1) / 2;
+    const int TWp = N_TW + nms_kernel - 1, THp = N_TH + nms_kernel - 1;
+    float *T = nsm, *RM = nsm + THp * TWp;        // RM: [THp][N_TW]
+    const UpSampler up(H, W, scale);
+    const int b = blockIdx.z, ty0 = blockIdx.y * N_TH, tx0 = blockIdx.x * N_TW;
+    const float *plane = center + (size_t)b * up.h * up.w;
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < THp * TWp; idx += P_THREADS) {
+        const int r = idx / TWp, c = idx - r * TWp;
+        const int gy = ty0 - p + r, gx = tx0 - p + c;
+        float t = -INFINITY;                         // max_pool2d pads with -inf
+        if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+            const float v = up.at(plane, gy, gx);
+            t = v > threshold ? v : -1.0f;          // F.threshold(x, thr, -1)
+        }
+        T[idx] = t;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < THp * N_TW; idx += P_THREADS) {
+        const int r = idx / N_TW, c = idx - r * N_TW;
+        float m = T[r * TWp + c];
+        for (int j = 1; j < nms_kernel; ++j) m = fmaxf(m, T[r * TWp + c + j]);
+        RM[idx] = m;
+    }
+    __syncthreads();
+    const int warp = tid >> 5, lane = tid & 31, WB = (W + 31) / 32;
+    for (int wi = warp; wi < N_TH * 2; wi += P_THREADS / 32) {
+        const int row = wi >> 1, half = wi & 1, xx = half * 32 + lane;
+        const int gy = ty0 + row, gx = tx0 + xx;
+        float m = RM[row * N_TW + xx];
+        for (int j = 1; j < nms_kernel; ++j) m = fmaxf(m, RM[(row + j) * N_TW + xx]);
+        const float v = T[(row + p) * TWp + xx + p];
+        const bool cand = gy < H && gx < W && v == m && v > 0.f;
+        const uint32_t word = __ballot_sync(0xffffffffu, cand);
+        const int wx = (tx0 >> 5) + half;
+        if (lane == 0 && gy < H && wx < WB) bitmask[((size_t)b * H + gy) * WB + wx] = word;
+    }
+}
+
+// block-wide exclusive scan of one int per thread (blockDim.x == SEL_THREADS); returns the block total via `total`
+__device__ __forceinline__ int block_excl_scan(int v, int *warp_tot, int &total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncthreads();                 // warp_tot may still be read from a previous call
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    int wbase = 0, tot = 0;
+    for (int i = 0; i < nw; ++i) {
+        const int t = warp_tot[i];
+        if (i < warp) wbase += t;
+        tot += t;
+    }
+    total = tot;
+    return wbase + inc - v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// find_instance_center, part 2: k-th largest candidate (radix select on the float bits), strict `>`,
+// raster-ordered emission.  post_processing.py:36-41.  One CTA per image.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(SEL_THREADS)
+center_select_kernel(const float *__restrict__ center, int H, int W, int scale, int top_k, int no_topk,
+                     const uint32_t *__restrict__ bitmask, int32_t *__restrict__ centers_yx, int32_t *__restrict__ n_centers,
+                     int32_t *__restrict__ overflow) {
+    __shared__ float vals[SEL_SMEM_VALS];
+    __shared__ int hist[256];
+    __shared__ int warp_tot[32];
+    __shared__ int s_n, s_fill, s_bin, s_remaining;
+    const UpSampler up(H, W, scale);
+    const int b = blockIdx.x, tid = threadIdx.x, WB = (W + 31) / 32, nwords = H * WB;
+    const float *plane = center + (size_t)b * up.h * up.w;
+    const uint32_t *bm = bitmask + (size_t)b * nwords;
+    if (tid == 0) { s_n = 0; s_fill = 0; }
+    __syncthreads();
+    int local = 0;
+    for (int i = tid; i < nwords; i += SEL_THREADS) local += __popc(bm[i]);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((tid & 31) == 0 && local) atomicAdd(&s_n, local);
+    __syncthreads();
+    const int n = s_n;
+    float cut = 0.f;                                  // `> 0` when fewer than top_k candidates (kth is a -1 filler, clamped)
+    if (n >= top_k && !no_topk) {
+        const bool in_smem = n <= SEL_SMEM_VALS;
+        if (in_smem) {
+            for (int i = tid; i < nwords; i += SEL_THREADS) {
+                uint32_t wbits = bm[i];
+                const int y = i / WB, xb = (i - y * WB) * 32;
+                while (wbits) {
+                    const int bit = __ffs(wbits) - 1;
+                    wbits &= wbits - 1;
+                    vals[atomicAdd(&s_fill, 1)] = up.at(plane, y, xb + bit);
+                }
+            }
+            __syncthreads();
+        }
+        uint32_t prefix = 0, pmask = 0;
+        if (tid == 0) s_remaining = top_k;
+        for (int pass = 0; pass < 4; ++pass) {
+            const int shift = 24 - 8 * pass;
+            for (int i = tid; i < 256; i += SEL_THREADS) hist[i] = 0;
+            __syncthreads();
+            if (in_smem) {
+                for (int i = tid; i < n; i += SEL_THREADS) {
+                    const uint32_t key = __float_as_uint(vals[i]);
+                    if ((key & pmask) == prefix) atomicAdd(&hist[(key >> shift) & 255], 1);
+                }
+            } else {
+                for (int i = tid; i < nwords; i += SEL_THREADS) {
+                    uint32_t wbits = bm[i];
+                    const int y = i / WB, xb = (i - y * WB) * 32;
+                    while (wbits) {
+                        const int bit = __ffs(wbits) - 1;
+                        wbits &= wbits - 1;
+                        const uint32_t key = __float_as_uint(up.at(plane, y, xb + bit));
+                        if ((key & pmask) == prefix) atomicAdd(&hist[(key >> shift) & 255], 1);
+                    }
+                }
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int cum = 0, rem = s_remaining, bin = 255;
+                for (; bin >= 0; --bin) {
+                    if (cum + hist[bin] >= rem) break;
+                    cum += hist[bin];
+                }
+                s_bin = bin < 0 ? 0 : bin;
+                s_remaining = rem - cum;
+            }
+            __syncthreads();
+            prefix |= (uint32_t)s_bin << shift;
+            pmask |= 255u << shift;
+        }
+        cut = __uint_as_float(prefix);                // the top_k-th largest score (> 0)
+    }
+    // raster-ordered emission of candidates with value > cut
+    int base = 0;
+    for (int i0 = 0; i0 < nwords; i0 += SEL_THREADS) {
+        const int i = i0 + tid;
+        uint32_t wbits = i < nwords ? bm[i] : 0u;
+        const int y = i / WB, xb = (i - y * WB) * 32;
+        if (cut > 0.f && wbits) {
+            uint32_t keep = 0, t = wbits;
+            while (t) {
+                const int bit = __ffs(t) - 1;
+                t &= t - 1;
+                if (up.at(plane, y, xb + bit) > cut) keep |= 1u << bit;
+            }
+            wbits = keep;
+        }
+        int total;
+        int pos = base + block_excl_scan(__popc(wbits), warp_tot, total);
+        while (wbits) {
+            const int bit = __ffs(wbits) - 1;
+            wbits &= wbits - 1;
+            if (pos < top_k) {
+                centers_yx[((size_t)b * top_k + pos) * 2] = y;
+                centers_yx[((size_t)b * top_k + pos) * 2 + 1] = xb + bit;
+            }
+            ++pos;
+        }
+        base += total;
+    }
+    if (tid == 0) {
+        n_centers[b] = base < top_k ? base : top_k;
+        if (base > top_k) atomicOr(overflow, 2);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused per-pixel pass 1: up-sample, foreground test, nearest-centre grouping, area histogram,
+// error-map up-sample + argmax one-hot.   model.py:689-708,292; post_processing.py:44-76,103-107;
+// eval/eval_utils.py:311-313.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(P_THREADS)
+group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ n_centers, uint16_t *__restrict__ ins,
+             uint32_t *__restrict__ area) {
+    extern __shared__ float gsm[];
+    float *cy = gsm, *cx = gsm + p.top_k;
+    unsigned int *hist = reinterpret_cast<unsigned int *>(gsm + 2 * p.top_k);   // [top_k+1]
+    const int b = blockIdx.z, tid = threadIdx.x, H = p.H, W = p.W;
+    const int n = n_centers[b];
+    for (int i = tid; i < n; i += P_THREADS) {
+        cy[i] = (float)io.centers_yx[((size_t)b * p.top_k + i) * 2];
+        cx[i] = (float)io.centers_yx[((size_t)b * p.top_k + i) * 2 + 1];
+    }
+    for (int i = tid; i <= p.top_k; i += P_THREADS) hist[i] = 0;
+    __syncthreads();
+    const UpSampler up(H, W, p.scale);
+    const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
+    const int y = blockIdx.y * P_TH + (tid >> 4), x0 = blockIdx.x * P_TW + (tid & 15) * 8;
+    const bool inb = y < H && x0 < W;
+    if (inb) {
+        const size_t pix = (size_t)y * W + x0;
+        const float *fgp = io.foreground + (size_t)b * hw;
+        const float *oyp = io.offset + (size_t)b * 2 * hw, *oxp = oyp + hw;
+        float sem[8];
+        unsigned id[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int x = x0 + j;
+            sem[j] = up.at(fgp, y, x);
+            id[j] = 0;
+            if (sem[j] > QUBER_FG_LOGIT_CUT) {                     // r.sigmoid().round() == 1
+                if (n == 0) { id[j] = INS_STUFF; continue; }
+                const float ly = __fadd_rn((float)y, __fmul_rn(up.at(oyp, y, x), p.offset_mul));
+                const float lx = __fadd_rn((float)x, __fmul_rn(up.at(oxp, y, x), p.offset_mul));
+                // argmin_k sqrt(fma(dx,dx,dy*dy)), first minimum wins (torch.norm + argmin).  sqrt is
+                // monotone, so it is evaluated only when the squared distance improves.
+                float dy = __fsub_rn(cy[0], ly), dx = __fsub_rn(cx[0], lx);
+                float best_d2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+                float best_s = __fsqrt_rn(best_d2);
+                int best = 0;
+                for (int k = 1; k < n; ++k) {
+                    dy = __fsub_rn(cy[k], ly); dx = __fsub_rn(cx[k], lx);
+                    const float d2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+                    if (d2 < best_d2) {
+                        const float s = __fsqrt_rn(d2);
+                        if (s < best_s) { best_s = s; best_d2 = d2; best = k; }
+                    }
+                }
+                id[j] = best + 1;
+            }
+        }
+        if (io.sem_seg) {
+            float *o = io.sem_seg + (size_t)b * HW + pix;
+            st_stream_f4(o, make_float4(sem[0], sem[1], sem[2], sem[3]));
+            st_stream_f4(o + 4, make_float4(sem[4], sem[5], sem[6], sem[7]));
+        }
+        st_stream_u4(ins + (size_t)b * HW + pix,
+                     make_uint4(id[0] | (id[1] << 16), id[2] | (id[3] << 16), id[4] | (id[5] << 16), id[6] | (id[7] << 16)));
+        if (io.ins_seg) {
+            int32_t *o = io.ins_seg + (size_t)b * HW + pix;
+            unsigned v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = id[j] == INS_STUFF ? 0u : id[j];
+            st_stream_u4(o, make_uint4(v[0], v[1], v[2], v[3]));
+            st_stream_u4(o + 4, make_uint4(v[4], v[5], v[6], v[7]));
+        }
+        // area histogram, run-length compressed per thread
+        unsigned cur = id[0], cnt = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (id[j] != cur) {
+                if (cur) atomicAdd(&hist[cur == INS_STUFF ? 0 : cur], cnt);
+                cur = id[j]; cnt = 0;
+            }
+            ++cnt;
+        }
+        if (cur) atomicAdd(&hist[cur == INS_STUFF ? 0 : cur], cnt);
+        // error maps
+        const int C = p.eee_channels;
+        if (C > 0 && io.eee && (io.eee_full || io.eee_onehot)) {
+            float bestv[8];
+            int bestc[8];
+            for (int c = 0; c < C; ++c) {
+                const float *ep = io.eee + ((size_t)b * C + c) * hw;
+                float v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    v[j] = up.at(ep, y, x0 + j);
+                    if (c == 0 || v[j] > bestv[j]) { bestv[j] = v[j]; bestc[j] = c; }   // first maximum wins
+                }
+                if (io.eee_full) {
+                    float *o = io.eee_full + ((size_t)b * C + c) * HW + pix;
+                    st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
+                    st_stream_f4(o + 4, make_float4(v[4], v[5], v[6], v[7]));
+                }
+            }
+            if (io.eee_onehot)
+                for (int c = 0; c < C; ++c) {
+                    uint32_t lo = 0, hi = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        lo |= (uint32_t)(bestc[j] == c) << (8 * j);
+                        hi |= (uint32_t)(bestc[4 + j] == c) << (8 * j);
+                    }
+                    st_stream_u2(io.eee_onehot + ((size_t)b * C + c) * HW + pix, make_uint2(lo, hi));
+                }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i <= n; i += P_THREADS)
+        if (hist[i]) atomicAdd(&area[(size_t)b * (p.top_k + 1) + i], hist[i]);
+}
+
+// merge_semantic_and_instance's id loop (post_processing.py:137-150): ids ascending, drop area < min_area,
+// running new id; stuff paste (:152-160) reachable only for a centre-less image.  One CTA per image.
+__global__ void __launch_bounds__(SEL_THREADS)
+relabel_kernel(quber_post_params p, const int32_t *__restrict__ n_centers, const uint32_t *__restrict__ area,
+               uint32_t *__restrict__ newid, int32_t *__restrict__ n_inst, int32_t *__restrict__ has_stuff) {
+    __shared__ int warp_tot[32];
+    const int b = blockIdx.x, tid = threadIdx.x, n = n_centers[b];
+    const uint32_t *a = area + (size_t)b * (p.top_k + 1);
+    uint32_t *nid = newid + (size_t)b * (p.top_k + 1);
+    int base = 0;
+    for (int i0 = 0; i0 < n; i0 += SEL_THREADS) {
+        const int id = i0 + tid + 1;
+        const int flag = (id <= n) && a[id] > 0 && (int)a[id] >= p.min_area;
+        int total;
+        const int ex = block_excl_scan(flag, warp_tot, total);
+        if (id <= n) nid[id] = flag ? base + ex + 1 : 0;
+        base += total;
+    }
+    if (tid == 0) {
+        nid[0] = 0;
+        int hs = 0;
+        if (n == 0) {
+            const uint32_t s = a[0];
+            hs = s > 0 && (long long)s >= (long long)p.stuff_area;
+        }
+        has_stuff[b] = hs;
+        n_inst[b] = hs ? 1 : base;
+    }
+}
+
+__global__ void __launch_bounds__(SEL_THREADS)
+offsets_kernel(int B, int max_instances, const int32_t *__restrict__ n_inst, int32_t *__restrict__ inst_offsets,
+               int32_t *__restrict__ status) {
+    __shared__ int warp_tot[32];
+    int base = 0;
+    for (int i0 = 0; i0 < B; i0 += SEL_THREADS) {
+        const int i = i0 + threadIdx.x;
+        const int v = i < B ? n_inst[i] : 0;
+        int total;
+        const int ex = block_excl_scan(v, warp_tot, total);
+        if (i < B) inst_offsets[i] = base + ex;
+        base += total;
+    }
+    if (threadIdx.x == 0) {
+        inst_offsets[B] = base;
+        if (base > max_instances) atomicOr(status, 1);
+    }
+}
+
+// Fused per-pixel pass 2: panoptic labels, compact per-instance masks, label map and the integer
+// statistics the scores / boxes are made of.  post_processing.py:129,150,160; model.py:318-353.
+__global__ void __launch_bounds__(P_THREADS)
+emit_kernel(quber_post_params p, quber_post_io io, const uint16_t *__restrict__ ins, const uint32_t *__restrict__ newid,
+            const int32_t *__restrict__ n_inst, const int32_t *__restrict__ has_stuff, InstStat *__restrict__ stats) {
+    extern __shared__ __align__(16) unsigned char esm[];
+    const int b = blockIdx.z, tid = threadIdx.x, H = p.H, W = p.W;
+    const int ninst = n_inst[b], hs = has_stuff[b], nc = io.n_centers[b];
+    InstStat *sst = reinterpret_cast<InstStat *>(esm);                         // [max(ninst,1)]
+    uint32_t *nid = reinterpret_cast<uint32_t *>(sst + (ninst > 0 ? ninst : 1)); // [nc+1]
+    for (int i = tid; i < ninst * (int)(sizeof(InstStat) / 4); i += P_THREADS) reinterpret_cast<uint32_t *>(sst)[i] = 0;
+    for (int i = tid; i <= nc; i += P_THREADS) nid[i] = newid[(size_t)b * (p.top_k + 1) + i];
+    __syncthreads();
+    const UpSampler up(H, W, p.scale);
+    const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
+    const int y = blockIdx.y * P_TH + (tid >> 4), x0 = blockIdx.x * P_TW + (tid & 15) * 8;
+    if (y < H && x0 < W) {
+        const size_t pix = (size_t)y * W + x0;
+        const uint4 raw = *reinterpret_cast<const uint4 *>(ins + (size_t)b * HW + pix);
+        const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
+        int idx[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const unsigned v = (rw[j >> 1] >> (16 * (j & 1))) & 0xffffu;
+            int t = -1;
+            if (v == INS_STUFF) t = hs ? 0 : -1;
+            else if (v) t = (int)nid[v] - 1;
+            idx[j] = t;
+        }
+        if (io.panoptic) {
+            float pv[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                pv[j] = idx[j] < 0 ? p.void_label : (float)(p.label_divisor + (hs ? 0 : idx[j] + 1));
+            float *o = io.panoptic + (size_t)b * HW + pix;
+            st_stream_f4(o, make_float4(pv[0], pv[1], pv[2], pv[3]));
+            st_stream_f4(o + 4, make_float4(pv[4], pv[5], pv[6], pv[7]));
+        }
+        if (io.label_map) {
+            int32_t *o = io.label_map + (size_t)b * HW + pix;
+            st_stream_u4(o, make_uint4(idx[0] + 1, idx[1] + 1, idx[2] + 1, idx[3] + 1));
+            st_stream_u4(o + 4, make_uint4(idx[4] + 1, idx[5] + 1, idx[6] + 1, idx[7] + 1));
+        }
+        if (io.masks) {
+            const int off = io.inst_offsets[b];
+            for (int i = 0; i < ninst; ++i) {
+                if (off + i >= p.max_instances) break;
+                uint32_t lo = 0, hi = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    lo |= (uint32_t)(idx[j] == i) << (8 * j);
+                    hi |= (uint32_t)(idx[4 + j] == i) << (8 * j);
+                }
+                st_stream_u2(io.masks + (size_t)(off + i) * HW + pix, make_uint2(lo, hi));
+            }
+        }
+        // statistics, run-length compressed per thread
+        const float *fgp = io.foreground + (size_t)b * hw;
+        int cur = -1;
+        unsigned cnt = 0, sx = 0, mnx = 0, mxx = 0;
+        unsigned long long sig = 0;
+        auto flush = [&]() {
+            if (cur < 0 || cnt == 0) return;
+            InstStat *s = sst + cur;
+            atomicAdd(&s->sig, sig);
+            atomicAdd(&s->sy, (unsigned long long)cnt * (unsigned)y);
+            atomicAdd(&s->sx, (unsigned long long)sx);
+            atomicAdd(&s->cnt, cnt);
+            atomicMax(&s->maxx, mxx);
+            atomicMax(&s->maxnx, (unsigned)(W - 1) - mnx);
+            atomicMax(&s->maxy, (unsigned)y);
+            atomicMax(&s->maxny, (unsigned)(H - 1 - y));
+        };
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (idx[j] != cur) { flush(); cur = idx[j]; cnt = 0; sx = 0; sig = 0; mnx = x0 + j; }
+            if (cur >= 0) {
+                const float x = up.at(fgp, y, x0 + j);
+                const float sg = __fdividef(1.0f, 1.0f + __expf(-x));       // model.py:319 sigmoid
+                sig += __float2ull_rn(sg * 4294967296.0f);
+                ++cnt; sx += x0 + j; mxx = x0 + j;
+            }
+        }
+        flush();
+    }
+    __syncthreads();
+    for (int i = tid; i < ninst; i += P_THREADS) {
+        const InstStat s = sst[i];
+        if (!s.cnt) continue;
+        InstStat *g = stats + (size_t)b * p.top_k + i;
+        atomicAdd(&g->sig, s.sig); atomicAdd(&g->sy, s.sy); atomicAdd(&g->sx, s.sx);
+        atomicAdd(&g->cnt, s.cnt);
+        atomicMax(&g->maxx, s.maxx); atomicMax(&g->maxnx, s.maxnx);
+        atomicMax(&g->maxy, s.maxy); atomicMax(&g->maxny, s.maxny);
+    }
+}
+
+// model.py:322-353: label, score = mean(sigmoid(fg)[mask]) * centre[int(cy), int(cx)], box.
+__global__ void __launch_bounds__(P_THREADS)
+finalize_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ n_inst,
+                const int32_t *__restrict__ has_stuff, const InstStat *__restrict__ stats) {
+    const int b = blockIdx.x;
+    const int ninst = n_inst[b], hs = has_stuff[b], off = io.inst_offsets[b];
+    const UpSampler up(p.H, p.W, p.scale);
+    const float *cplane = io.center + (size_t)b * up.h * up.w;
+    for (int i = threadIdx.x; i < ninst; i += blockDim.x) {
+        const int row = off + i;
+        if (row >= p.max_instances) break;
+        const InstStat s = stats[(size_t)b * p.top_k + i];
+        io.labels[row] = p.label_divisor + (hs ? 0 : i + 1);
+        const double cnt = (double)s.cnt;
+        const float sem = (float)((double)s.sig * (1.0 / 4294967296.0) / cnt);
+        const int cy = (int)((double)s.sy / cnt), cx = (int)((double)s.sx / cnt);
+        io.scores[row] = __fmul_rn(sem, up.at(cplane, cy, cx));
+        io.boxes[4 * row + 0] = (float)(p.W - 1 - (int)s.maxnx);
+        io.boxes[4 * row + 1] = (float)(p.H - 1 - (int)s.maxny);
+        io.boxes[4 * row + 2] = (float)(s.maxx + 1);
+        io.boxes[4 * row + 3] = (float)(s.maxy + 1);
+    }
+}
+
+}  // namespace quber
+
+static int post_validate(const quber_post_params *p) {
+    if (!p) return QUBER_E_INVALID;
+    if (p->B <= 0 || p->H <= 0 || p->W <= 0 || p->scale < 1 || p->top_k < 1 || p->top_k > 1024 ||
+        p->nms_kernel < 1 || p->nms_kernel > 15 || (p->nms_kernel & 1) == 0 || p->max_instances < 0 ||
+        (p->eee_channels != 0 && (p->eee_channels < 2 || p->eee_channels > 4)))
+        return QUBER_E_INVALID;
+    if (p->W % 8 != 0 || p->H % p->scale != 0 || p->W % p->scale != 0) return QUBER_E_UNSUPPORTED;
+    return QUBER_OK;
+}
+
+extern "C" size_t quber_post_workspace_bytes(const quber_post_params *p) {
+    if (post_validate(p) != QUBER_OK) return 0;
+    return quber::carve(*p, reinterpret_cast<void *>(4096)).total;
+}
+
+extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_io *iop, void *workspace,
+                                  size_t workspace_bytes, void *stream) {
+    using namespace quber;
+    if (int rc = post_validate(pp)) return rc;
+    if (!iop) return QUBER_E_INVALID;
+    const quber_post_params p = *pp;
+    const quber_post_io io = *iop;
+    if (!io.foreground || !io.center || !io.offset || !io.centers_yx || !io.n_centers || !io.inst_offsets || !io.labels ||
+        !io.scores || !io.boxes || !io.status)
+        return QUBER_E_INVALID;
+    if (p.eee_channels > 0 && !io.eee) return QUBER_E_INVALID;
+    const void *al[] = {io.sem_seg, io.eee_full, io.eee_onehot, io.panoptic, io.label_map, io.masks, io.ins_seg};
+    for (const void *q : al)
+        if (q && !aligned16(q)) return QUBER_E_ALIGN;
+    if (!workspace || !aligned16(workspace) || workspace_bytes < carve(p, reinterpret_cast<void *>(4096)).total) return QUBER_E_WORKSPACE;
+    const PostWs ws = carve(p, workspace);
+    cudaStream_t st = (cudaStream_t)stream;
+    QUBER_CUDA_TRY(cudaMemsetAsync(workspace, 0, ws.zero_bytes, st));
+    QUBER_CUDA_TRY(cudaMemsetAsync(io.status, 0, sizeof(int32_t), st));
+
+    if (!(p.flags & QUBER_POST_GIVEN_CENTERS)) {
+        const int TWp = N_TW + p.nms_kernel - 1, THp = N_TH + p.nms_kernel - 1;
+        const size_t smem = ((size_t)THp * TWp + (size_t)THp * N_TW) * sizeof(float);
+        dim3 grid(cdiv(p.W, N_TW), cdiv(p.H, N_TH), p.B);
+        center_nms_kernel<<<grid, P_THREADS, smem, st>>>(io.center, p.H, p.W, p.scale, p.threshold, p.nms_kernel, ws.bitmask);
+        if (int rc = check_launch("center_nms_kernel")) return rc;
+        center_select_kernel<<<p.B, SEL_THREADS, 0, st>>>(io.center, p.H, p.W, p.scale, p.top_k, (p.flags & QUBER_POST_NO_TOPK) != 0,
+                                                         ws.bitmask, io.centers_yx, io.n_centers, io.status);
+        if (int rc = check_launch("center_select_kernel")) return rc;
+    }
+    dim3 pgrid(cdiv(p.W, P_TW), cdiv(p.H, P_TH), p.B);
+    group_kernel<<<pgrid, P_THREADS, (3 * (size_t)p.top_k + 1) * 4, st>>>(p, io, io.n_centers, ws.ins, ws.area);
+    if (int rc = check_launch("group_kernel")) return rc;
+    relabel_kernel<<<p.B, SEL_THREADS, 0, st>>>(p, io.n_centers, ws.area, ws.newid, ws.n_inst, ws.has_stuff);
+    if (int rc = check_launch("relabel_kernel")) return rc;
+    offsets_kernel<<<1, SEL_THREADS, 0, st>>>(p.B, p.max_instances, ws.n_inst, io.inst_offsets, io.status);
+    if (int rc = check_launch("offsets_kernel")) return rc;
+    {
+        const size_t smem = (size_t)p.top_k * sizeof(InstStat) + ((size_t)p.top_k + 1) * 4 + sizeof(InstStat);
+        if (smem > 48 * 1024)
+            QUBER_CUDA_TRY(cudaFuncSetAttribute(emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        emit_kernel<<<pgrid, P_THREADS, smem, st>>>(p, io, ws.ins, ws.newid, ws.n_inst, ws.has_stuff, ws.stats);
+        if (int rc = check_launch("emit_kernel")) return rc;
+    }
+    finalize_kernel<<<p.B, P_THREADS, 0, st>>>(p, io, ws.n_inst, ws.has_stuff, ws.stats);
+    return check_launch("finalize_kernel");
+}

@@ -1,0 +1,239 @@
+"""Device-side operators: torch CUDA tensors in, torch CUDA tensors out, computed by the hand-written
+sm_100a kernels of libquber_b200.so through its C ABI (include/quber_b200.h).
+
+PyTorch is plumbing only here (device memory, the current stream); there is no PyTorch or CPU
+implementation of any of these ops in the product.  They are also registered as `torch.ops.quber.*`
+custom ops at the bottom of the file.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+_GAUSS = {}
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _need_cuda(t, name, dtype=None):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        # same condition the reference asserts with AT_ASSERTM("... must be a CUDA tensor"), ms_deform_attn_cuda.cu:39-43
+        raise ValueError(f"{name} must be a CUDA tensor")
+    if dtype is not None and t.dtype != dtype:
+        raise ValueError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} tensor has to be contiguous")   # ms_deform_attn_cuda.cu:33-37
+    return t
+
+
+def gaussian_table(sigma, device):
+    key = (sigma, str(device))
+    if key not in _GAUSS:
+        n = 6 * sigma + 3
+        host = np.empty((n, n), np.float32)
+        _lib.lib().quber_gaussian_table(sigma, host.ctypes.data_as(ctypes.c_void_p))
+        _GAUSS[key] = torch.from_numpy(host).to(device)
+    return _GAUSS[key]
+
+
+def boundary_dilation(H, W, ratio):
+    """explicit_error_estimation/util.py:80-84."""
+    return int(_lib.lib().quber_boundary_dilation(int(H), int(W), float(ratio)))
+
+
+def encode_initial_masks(masks, sigma=10):
+    """maskrefiner/predictor.py:304-357 for a batch: masks [B,K,H,W] uint8 -> [B,3,H,W] float32."""
+    _need_cuda(masks, "masks", torch.uint8)
+    B, K, H, W = masks.shape
+    L = _lib.lib()
+    out = torch.empty((B, 3, H, W), dtype=torch.float32, device=masks.device)
+    nbytes = L.quber_encode_workspace_bytes(B, K, H, W)
+    ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=masks.device)
+    g = gaussian_table(sigma, masks.device)
+    with torch.cuda.device(masks.device):
+        _lib.check(L.quber_encode_initial_masks(_ptr(masks), B, K, H, W, sigma, _ptr(g), _ptr(out), _ptr(ws), nbytes,
+                                                _stream()), "quber_encode_initial_masks")
+    return out
+
+
+def mask_boundary(masks, d, per_instance=True, union=True, fg=True):
+    """explicit_error_estimation/util.py:62-99 for a batch: masks [B,K,H,W] uint8 ->
+    (per-instance boundary [B,K,H,W] | None, union boundary [B,H,W] | None, fg [B,H,W] | None)."""
+    _need_cuda(masks, "masks", torch.uint8)
+    B, K, H, W = masks.shape
+    per = torch.empty_like(masks) if per_instance else None
+    uni = torch.empty((B, H, W), dtype=torch.uint8, device=masks.device) if union else None
+    fgm = torch.empty((B, H, W), dtype=torch.uint8, device=masks.device) if fg else None
+    with torch.cuda.device(masks.device):
+        _lib.check(_lib.lib().quber_mask_boundary(_ptr(masks), B, K, H, W, int(d), _ptr(per), _ptr(uni), _ptr(fgm),
+                                                  _stream()), "quber_mask_boundary")
+    return per, uni, fgm
+
+
+def quadruple_maps(gt, pred):
+    """tools/ours/panoptic2eee.py:110-123: gt, pred [B,...] uint8 -> [B,4,...] uint8 (TP,TN,FP,FN)."""
+    _need_cuda(gt, "gt", torch.uint8)
+    _need_cuda(pred, "pred", torch.uint8)
+    if gt.shape != pred.shape:
+        raise ValueError("gt and pred must have the same shape")
+    B = gt.shape[0]
+    n = gt[0].numel()
+    out = torch.empty((B, 4) + tuple(gt.shape[1:]), dtype=torch.uint8, device=gt.device)
+    with torch.cuda.device(gt.device):
+        _lib.check(_lib.lib().quber_quadruple_maps(_ptr(gt), _ptr(pred), B, n, _ptr(out), _stream()), "quber_quadruple_maps")
+    return out
+
+
+def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=None, threshold=0.3, nms_kernel=7,
+                 top_k=200, min_area=512, stuff_area=2048, label_divisor=1000, void_label=-1.0, max_instances=None,
+                 want=("sem_seg", "eee_full", "eee_onehot", "panoptic", "label_map", "masks"), centers=None,
+                 n_centers=None, no_topk=False):
+    """One fused call for model.py:689-708 + :260-356 + post_processing.py:9-221 + eval_utils.py:308-328.
+
+    foreground [B,1,h,w], center [B,1,h,w], offset [B,2,h,w], eee [B,C,h,w] float32 CUDA tensors at
+    1/scale resolution (scale=1: full-resolution maps).  Returns a dict of device tensors; nothing is
+    synchronised or copied to the host.
+    """
+    _need_cuda(foreground, "foreground", torch.float32)
+    _need_cuda(center, "center", torch.float32)
+    _need_cuda(offset, "offset", torch.float32)
+    if center.dim() != 4 or foreground.dim() != 4:
+        raise ValueError("Center prediction with un-supported dimension: {}.".format(center.dim()))   # post_processing.py:199
+    if offset.dim() != 4 or offset.shape[1] != 2:
+        raise ValueError("Offset prediction with un-supported dimension: {}.".format(offset.dim()))   # :203
+    dev = foreground.device
+    B, _, h, w = foreground.shape
+    H, W = h * scale, w * scale
+    C = 0
+    if eee is not None:
+        _need_cuda(eee, "eee", torch.float32)
+        C = eee.shape[1]
+    if offset_mul is None:
+        offset_mul = float(scale)          # model.py:698
+    if max_instances is None:
+        max_instances = B * min(top_k, 64)
+    flags = 0
+    p = _lib.PostParams(B, H, W, scale, offset_mul, C, threshold, nms_kernel, top_k, min_area, stuff_area, label_divisor,
+                        void_label, max_instances, 0)
+    out = {}
+    i32, f32, u8 = torch.int32, torch.float32, torch.uint8
+    mk = lambda name, shape, dt: out.setdefault(name, torch.empty(shape, dtype=dt, device=dev)) if name in want else None
+    sem = mk("sem_seg", (B, 1, H, W), f32)
+    eee_full = mk("eee_full", (B, C, H, W), f32) if C else None
+    onehot = mk("eee_onehot", (B, C, H, W), u8) if C else None
+    pan = mk("panoptic", (B, H, W), f32)
+    lmap = mk("label_map", (B, H, W), i32)
+    iseg = mk("ins_seg", (B, H, W), i32)
+    masks = mk("masks", (max(max_instances, 1), H, W), u8)
+    if centers is not None:
+        flags |= _lib.POST_GIVEN_CENTERS
+        out["centers_yx"] = _need_cuda(centers, "centers", i32)
+        out["n_centers"] = _need_cuda(n_centers, "n_centers", i32)
+        if tuple(centers.shape) != (B, top_k, 2):
+            raise ValueError("centers must be [B, top_k, 2] int32")
+    else:
+        out["centers_yx"] = torch.empty((B, top_k, 2), dtype=i32, device=dev)
+        out["n_centers"] = torch.empty((B,), dtype=i32, device=dev)
+    if no_topk:
+        flags |= _lib.POST_NO_TOPK
+    p.flags = flags
+    out["inst_offsets"] = torch.empty((B + 1,), dtype=i32, device=dev)
+    out["labels"] = torch.empty((max(max_instances, 1),), dtype=i32, device=dev)
+    out["scores"] = torch.empty((max(max_instances, 1),), dtype=f32, device=dev)
+    out["boxes"] = torch.empty((max(max_instances, 1), 4), dtype=f32, device=dev)
+    out["status"] = torch.empty((1,), dtype=i32, device=dev)
+    io = _lib.PostIO(*[None if t is None else t.data_ptr() for t in (
+        foreground, center, offset, eee, sem, eee_full, onehot, pan, lmap, iseg, masks, out["centers_yx"],
+        out["n_centers"], out["inst_offsets"], out["labels"], out["scores"], out["boxes"], out["status"])])
+    L = _lib.lib()
+    nbytes = L.quber_post_workspace_bytes(ctypes.byref(p))
+    if nbytes == 0:
+        _lib.check(L.quber_post_process(ctypes.byref(p), ctypes.byref(io), None, 0, _stream()), "quber_post_process")
+    ws = torch.empty(nbytes, dtype=u8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(L.quber_post_process(ctypes.byref(p), ctypes.byref(io), _ptr(ws), nbytes, _stream()), "quber_post_process")
+    out["max_instances"] = max_instances
+    return out
+
+
+def msda_forward(value, spatial_shapes, level_start_index, sampling_locations, attention_weights, im2col_step=None):
+    """MultiScaleDeformableAttention.ms_deform_attn_forward (OPS/src/vision.cpp:18-21).
+
+    value [B,S,M,D] float32 | bfloat16, spatial_shapes [L,2] int64, level_start_index [L] int64,
+    sampling_locations [B,Q,M,L,P,2] float32, attention_weights [B,Q,M,L,P] float32 -> [B,Q,M*D] (value dtype).
+    `im2col_step` is accepted for signature compatibility and ignored (the batch is one launch).
+    """
+    _need_cuda(value, "value")
+    _need_cuda(spatial_shapes, "spatial_shapes", torch.int64)
+    _need_cuda(level_start_index, "level_start_index", torch.int64)
+    _need_cuda(sampling_locations, "sampling_loc", torch.float32)
+    _need_cuda(attention_weights, "attn_weight", torch.float32)
+    if value.dtype == torch.float32:
+        dt = 0
+    elif value.dtype == torch.bfloat16:
+        dt = 1
+    else:
+        raise ValueError(f"value must be float32 or bfloat16, got {value.dtype}")
+    B, S, M, D = value.shape
+    _, Q, _, Lv, P, _ = sampling_locations.shape
+    out = torch.empty((B, Q, M * D), dtype=value.dtype, device=value.device)
+    with torch.cuda.device(value.device):
+        _lib.check(_lib.lib().quber_msda_forward(_ptr(value), _ptr(spatial_shapes), _ptr(level_start_index),
+                                                 _ptr(sampling_locations), _ptr(attention_weights), B, S, M, D, Lv, Q, P, dt,
+                                                 _ptr(out), _stream()), "quber_msda_forward")
+    return out
+
+
+# ---- torch.library registration: torch.ops.quber.* ----------------------------------------------
+def _register():
+    try:
+        from torch.library import custom_op
+    except Exception:        # pragma: no cover - very old torch
+        return
+
+    @custom_op("quber::msda_forward", mutates_args=(), device_types="cuda")
+    def _msda(value: torch.Tensor, spatial_shapes: torch.Tensor, level_start_index: torch.Tensor,
+              sampling_locations: torch.Tensor, attention_weights: torch.Tensor) -> torch.Tensor:
+        return msda_forward(value, spatial_shapes, level_start_index, sampling_locations, attention_weights)
+
+    @_msda.register_fake
+    def _(value, spatial_shapes, level_start_index, sampling_locations, attention_weights):
+        B, S, M, D = value.shape
+        return value.new_empty((B, sampling_locations.shape[1], M * D))
+
+    @custom_op("quber::encode_initial_masks", mutates_args=(), device_types="cuda")
+    def _enc(masks: torch.Tensor, sigma: int) -> torch.Tensor:
+        return encode_initial_masks(masks, sigma)
+
+    @_enc.register_fake
+    def _(masks, sigma):
+        B, K, H, W = masks.shape
+        return masks.new_empty((B, 3, H, W), dtype=torch.float32)
+
+    @custom_op("quber::mask_boundary", mutates_args=(), device_types="cuda")
+    def _bnd(masks: torch.Tensor, d: int) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+        return mask_boundary(masks, d)
+
+    @_bnd.register_fake
+    def _(masks, d):
+        B, K, H, W = masks.shape
+        return torch.empty_like(masks), masks.new_empty((B, H, W)), masks.new_empty((B, H, W))
+
+    @custom_op("quber::quadruple_maps", mutates_args=(), device_types="cuda")
+    def _quad(gt: torch.Tensor, pred: torch.Tensor) -> torch.Tensor:
+        return quadruple_maps(gt, pred)
+
+    @_quad.register_fake
+    def _(gt, pred):
+        return gt.new_empty((gt.shape[0], 4) + tuple(gt.shape[1:]))
+
+
+_register()

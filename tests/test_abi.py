@@ -1,0 +1,115 @@
+"""CPU-only: the C-ABI library loads and exports every symbol include/quber_b200.h declares; the
+ctypes structs mirror the header; host-only entry points (no GPU needed) agree with the oracle."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from quber_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header():
+    return open(os.path.join(ROOT, "include", "quber_b200.h")).read()
+
+
+def test_library_present_and_versioned():
+    assert os.path.exists(_lib.SO_PATH), "build it: python -c 'import __graft_entry__ as g; g.build()'"
+    assert _lib.lib().quber_version() == 1
+
+
+def test_every_declared_symbol_is_exported_and_bound():
+    h = re.sub(r"/\*.*?\*/", "", _header(), flags=re.S)
+    declared = set(re.findall(r"\b(quber_[a-z_0-9]+)\s*\(", h))
+    assert declared, "no declarations parsed"
+    raw = ctypes.CDLL(_lib.SO_PATH)
+    for name in declared:
+        assert hasattr(raw, name), f"{name} declared in the header but not exported"
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+
+
+def test_struct_layout_matches_header():
+    h = _header()
+    body = re.search(r"typedef struct quber_post_params \{(.*?)\} quber_post_params;", h, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if decl:
+            names += [n.strip() for n in decl.split(None, 1)[1].split(",")]
+    assert names == [f[0] for f in _lib.PostParams._fields_]
+    body = re.search(r"typedef struct quber_post_io \{(.*?)\} quber_post_io;", h, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = [re.findall(r"\*\s*([a-z_]+)$", d.strip())[0] for d in body.split(";") if d.strip()]
+    assert names == [f[0] for f in _lib.PostIO._fields_]
+
+
+def test_error_strings_and_exception_mapping():
+    L = _lib.lib()
+    assert L.quber_error_string(0) == b"ok"
+    for code in (-1, -2, -3, -4, -5):
+        assert L.quber_error_string(code)
+    with pytest.raises(ValueError):
+        _lib.check(_lib.E_INVALID, "x")
+    with pytest.raises(ValueError):
+        _lib.check(_lib.E_ALIGN, "x")
+    with pytest.raises(RuntimeError):
+        _lib.check(_lib.E_WORKSPACE, "x")
+
+
+def test_argument_validation_without_gpu():
+    """Argument checks run before any CUDA call, so they are testable on a CPU-only host."""
+    L = _lib.lib()
+    assert L.quber_encode_initial_masks(None, 1, 1, 16, 16, 10, None, None, None, 0, None) == _lib.E_INVALID
+    assert L.quber_mask_boundary(None, 1, 1, 16, 16, 8, None, None, None, None) == _lib.E_INVALID
+    assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 24, 8, ctypes.c_void_p(16), None, None, None) == _lib.E_ALIGN
+    assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 16, 0, ctypes.c_void_p(16), None, None, None) == _lib.E_INVALID
+    assert L.quber_msda_forward(None, None, None, None, None, 1, 1, 1, 1, 1, 1, 1, 0, None, None) == _lib.E_INVALID
+    p = _lib.PostParams(1, 480, 640, 4, 4.0, 4, 0.3, 8, 200, 512, 2048, 1000, -1.0, 8, 0)    # even nms kernel
+    assert L.quber_post_workspace_bytes(ctypes.byref(p)) == 0
+    p.nms_kernel = 7
+    assert L.quber_post_workspace_bytes(ctypes.byref(p)) > 480 * 640 * 2
+    assert L.quber_encode_workspace_bytes(2, 30, 480, 640) >= 2 * 480 * 640
+
+
+def test_host_helpers_match_oracle():
+    L = _lib.lib()
+    for (H, W, r) in [(480, 640, 0.01), (480, 640, 0.02), (750, 1333, 0.01), (10, 10, 0.01), (1080, 1920, 0.02)]:
+        assert L.quber_boundary_dilation(H, W, r) == oracle.boundary_dilation(H, W, r)
+    for sigma in (8, 10):
+        n = 6 * sigma + 3
+        t = np.empty((n, n), np.float32)
+        L.quber_gaussian_table(sigma, t.ctypes.data_as(ctypes.c_void_p))
+        np.testing.assert_array_equal(t, oracle.gaussian_table(sigma))
+
+
+def test_product_never_imports_oracle():
+    """The oracle is test infrastructure: nothing under quber_b200/ may reference it."""
+    pkg = os.path.join(ROOT, "quber_b200")
+    for dp, _, fns in os.walk(pkg):
+        for fn in fns:
+            if fn.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dp, fn)).read()
+                assert not re.search(r"^\s*(import|from)\s+oracle\b", src, re.M), f"{fn} imports oracle"
+                assert "libquber_oracle" not in src, fn
+
+
+def test_ops_fail_loudly_without_cuda():
+    import torch
+    from quber_b200 import ops
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(ValueError, match="CUDA tensor"):
+        ops.encode_initial_masks(torch.zeros(1, 1, 16, 16, dtype=torch.uint8))
+    with pytest.raises(ValueError, match="CUDA tensor"):
+        ops.msda_forward(torch.zeros(1, 4, 1, 8), torch.zeros(1, 2, dtype=torch.long), torch.zeros(1, dtype=torch.long),
+                         torch.zeros(1, 1, 1, 1, 1, 2), torch.zeros(1, 1, 1, 1, 1))
+    from quber_b200 import msda
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):     # OPS/src/ms_deform_attn.h:43
+        msda.ms_deform_attn_forward(torch.zeros(1, 4, 1, 8), torch.zeros(1, 2, dtype=torch.long),
+                                    torch.zeros(1, dtype=torch.long), torch.zeros(1, 1, 1, 1, 1, 2),
+                                    torch.zeros(1, 1, 1, 1, 1), 64)
