@@ -11,6 +11,9 @@
 // columns on whole words.  One CTA owns one (image, tile) and walks all K mask planes, so the
 // union (`boundary`) and foreground (`fg`) sums live in registers and are written once.
 // A tile (+halo) whose bytes are all equal has no boundary: it is detected on load and skipped.
+#include <cuda.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace quber {
@@ -27,7 +30,7 @@ __device__ __forceinline__ uint32_t shift_bytes(uint32_t lo, uint32_t hi, int s)
 }
 
 __global__ void __launch_bounds__(B_THREADS)
-boundary_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, int d, uint8_t *__restrict__ per_instance,
+boundary_ldg_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, int d, uint8_t *__restrict__ per_instance,
                 uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg) {
     extern __shared__ uint32_t smem[];
     const int hw = (d + 3) >> 2;            // halo words per side
@@ -147,6 +150,191 @@ boundary_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, int d, u
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// TMA version (default).  The (tile + halo) box of every mask plane is fetched by ONE
+// cp.async.bulk.tensor.3d per plane — out-of-image bytes arrive as zeros, which IS the erosion's
+// zero padding — double-buffered against the compute of the previous plane through two mbarriers,
+// and the per-instance result leaves through a TMA store (clipped at the image edge by the
+// hardware).  No thread issues a global load; the only per-thread global stores are the two
+// union maps at the end.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (int spin = 0; !done; ++spin) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (spin > (1 << 24)) __trap();       // a lost TMA must fail the launch, never hang the GPU
+    }
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, uint64_t *bar, int x, int y, int z) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y), "r"(z) : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, const void *src, int x, int y, int z) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(map), "r"(smem_u32(src)), "r"(x), "r"(y), "r"(z) : "memory");
+}
+__device__ __forceinline__ void tma_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void tma_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void tma_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__global__ void __launch_bounds__(B_THREADS)
+boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map, int K, int H, int W,
+                    int d, int has_per, uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg) {
+    extern __shared__ __align__(128) unsigned char sm_raw[];
+    __shared__ __align__(8) uint64_t full[2];
+    const int hw = ((d + 3) >> 2) + (((d + 3) >> 2) & 1);   // halo words per side, even -> inner box bytes % 16 == 0
+    const int WS = B_TWW + 2 * hw;                          // words per staged row
+    const int R = B_TH + 2 * d;                             // staged rows
+    const uint32_t stage_bytes = (uint32_t)R * WS * 4;
+    const uint32_t stage_stride = (stage_bytes + 127u) & ~127u;
+    auto S = [&](int i) { return reinterpret_cast<uint32_t *>(sm_raw + (size_t)(i & 1) * stage_stride); };
+    uint32_t *V1 = reinterpret_cast<uint32_t *>(sm_raw + 2 * stage_stride);                 // [R][32]
+    uint32_t *O0 = V1 + (((size_t)R * B_TWW + 31) & ~(size_t)31);                            // [64][32] x2, 128-B aligned
+    uint32_t *Z = O0 + 2 * B_TH * B_TWW;                                                    // zero tile
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.z;
+    const int ty0 = blockIdx.y * B_TH, tx0 = blockIdx.x * B_TW;
+    const int Ww = W >> 2;
+    const size_t HW = (size_t)H * W;
+    const int w = 2 * d + 1;
+    int p_top = 1;
+    while (p_top * 2 <= w) p_top *= 2;
+    const int lead = 4 * hw - d;
+
+    for (int i = tid; i < B_TH * B_TWW; i += B_THREADS) Z[i] = 0u;
+    if (tid == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    fence_proxy_async();         // Z was written by the generic proxy, TMA stores read it
+    __syncthreads();
+    if (tid == 0) {
+        mbar_expect_tx(&full[0], stage_bytes);
+        tma_load_3d(S(0), &in_map, &full[0], tx0 - 4 * hw, ty0 - d, b * K);
+    }
+
+    const int ci = tid & 31, cr0 = tid >> 5;
+    uint32_t uni_acc[B_RPT], fg_acc[B_RPT];
+#pragma unroll
+    for (int j = 0; j < B_RPT; ++j) uni_acc[j] = fg_acc[j] = 0;
+    int o_slot = 0;
+
+    for (int k = 0; k < K; ++k) {
+        uint32_t *cur = S(k);
+        if (tid == 0 && k + 1 < K) {          // prefetch the next plane; its buffer was released by the barrier that ended iteration k-1
+            fence_proxy_async();
+            mbar_expect_tx(&full[(k + 1) & 1], stage_bytes);
+            tma_load_3d(S(k + 1), &in_map, &full[(k + 1) & 1], tx0 - 4 * hw, ty0 - d, b * K + k + 1);
+        }
+        mbar_wait(&full[k & 1], (k >> 1) & 1);
+        // ---- uniformity scan (128-bit shared loads) ----
+        const uint32_t first = (cur[0] & 0xffu) * 0x01010101u;
+        uint32_t diff = 0;
+        {
+            const uint4 *c4 = reinterpret_cast<const uint4 *>(cur);
+            const int n4 = (R * WS) >> 2;                   // WS is even and R*WS*4 % 16 == 0
+            for (int i = tid; i < n4; i += B_THREADS) {
+                const uint4 v = c4[i];
+                diff |= (v.x ^ first) | (v.y ^ first) | (v.z ^ first) | (v.w ^ first);
+            }
+        }
+        const int any = __syncthreads_or(diff != 0);
+        uint32_t orig[B_RPT], er[B_RPT];
+        if (!any) {
+#pragma unroll
+            for (int j = 0; j < B_RPT; ++j) { orig[j] = first; er[j] = first; }
+            if (has_per && tid == 0) { tma_store_3d(&out_map, Z, tx0, ty0, b * K + k); tma_commit(); }
+        } else {
+#pragma unroll
+            for (int j = 0; j < B_RPT; ++j) orig[j] = cur[(size_t)(cr0 + 8 * j + d) * WS + hw + ci];
+            __syncthreads();                                 // every thread holds its originals before rows are overwritten
+            // ---- horizontal pass, in place, one warp per row (rows are independent: warp-level sync only) ----
+            for (int r = warp; r < R; r += B_THREADS / 32) {
+                uint32_t *row = cur + (size_t)r * WS;
+                const int i0 = lane, i1 = lane + 32;
+                for (int p = 1; p < p_top; p <<= 1) {
+                    const int sw = p >> 2, sb = p & 3;
+                    uint32_t n0, n1 = 0;
+                    {
+                        const int j0 = i0 + sw;
+                        const uint32_t lo = j0 < WS ? row[j0] : 0u, hi = j0 + 1 < WS ? row[j0 + 1] : 0u;
+                        n0 = __vminu4(row[i0], sb ? shift_bytes(lo, hi, sb) : lo);
+                    }
+                    if (i1 < WS) {
+                        const int j0 = i1 + sw;
+                        const uint32_t lo = j0 < WS ? row[j0] : 0u, hi = j0 + 1 < WS ? row[j0 + 1] : 0u;
+                        n1 = __vminu4(row[i1], sb ? shift_bytes(lo, hi, sb) : lo);
+                    }
+                    __syncwarp();
+                    row[i0] = n0;
+                    if (i1 < WS) row[i1] = n1;
+                    __syncwarp();
+                }
+                const int a1 = 4 * lane + lead, a2 = a1 + w - p_top;
+                const int w1 = a1 >> 2, s1 = a1 & 3, w2 = a2 >> 2, s2 = a2 & 3;
+                const uint32_t v1 = shift_bytes(row[w1], w1 + 1 < WS ? row[w1 + 1] : 0u, s1);
+                const uint32_t v2 = shift_bytes(row[w2], w2 + 1 < WS ? row[w2 + 1] : 0u, s2);
+                V1[r * B_TWW + lane] = __vminu4(v1, v2);
+            }
+            __syncthreads();
+            // ---- vertical pass: ping-pong V1 <-> (dead) staging buffer ----
+            uint32_t *src = V1, *dst = cur;
+            for (int p = 1; p < p_top; p <<= 1) {
+                for (int idx = tid; idx < R * B_TWW; idx += B_THREADS) {
+                    const int r = idx >> 5;
+                    const uint32_t other = (r + p < R) ? src[idx + p * B_TWW] : 0u;
+                    dst[idx] = __vminu4(src[idx], other);
+                }
+                __syncthreads();
+                uint32_t *t = src; src = dst; dst = t;
+            }
+#pragma unroll
+            for (int j = 0; j < B_RPT; ++j) {
+                const int r = cr0 + 8 * j;
+                er[j] = __vminu4(src[r * B_TWW + ci], src[(r + w - p_top) * B_TWW + ci]);
+            }
+            if (has_per) {
+                if (tid == 0) tma_wait_read<1>();            // the store that last used this O slot has read it
+                __syncthreads();
+                uint32_t *o = O0 + (size_t)o_slot * B_TH * B_TWW;
+#pragma unroll
+                for (int j = 0; j < B_RPT; ++j) o[(cr0 + 8 * j) * B_TWW + ci] = __vsub4(orig[j], er[j]);
+                fence_proxy_async();
+                __syncthreads();
+                if (tid == 0) { tma_store_3d(&out_map, o, tx0, ty0, b * K + k); tma_commit(); }
+                o_slot ^= 1;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < B_RPT; ++j) {
+            uni_acc[j] = __vadd4(uni_acc[j], __vsub4(orig[j], er[j]));
+            fg_acc[j] = __vadd4(fg_acc[j], orig[j]);
+        }
+        __syncthreads();   // releases `cur` (and the V buffers) for the prefetch issued at the top of the next iteration
+    }
+#pragma unroll
+    for (int j = 0; j < B_RPT; ++j) {
+        const int gy = ty0 + cr0 + 8 * j, gxw = (tx0 >> 2) + ci;
+        if (gy < H && gxw < Ww) {
+            const size_t o = (size_t)b * HW + (size_t)gy * W + 4 * gxw;
+            if (boundary) st_stream_u1(boundary + o, __vcmpne4(uni_acc[j], 0u) & 0x01010101u);
+            if (fg) st_stream_u1(fg + o, __vcmpne4(fg_acc[j], 0u) & 0x01010101u);
+        }
+    }
+    if (tid == 0) tma_wait_all();     // shared memory must outlive the bulk stores that read it
+}
+
 __global__ void __launch_bounds__(256)
 quadruple_kernel(const uint8_t *__restrict__ gt, const uint8_t *__restrict__ pred, size_t n, uint8_t *__restrict__ out) {
     const int b = blockIdx.y;
@@ -183,6 +371,37 @@ extern "C" int quber_boundary_dilation(int H, int W, double ratio) {
     return dd < 1 ? 1 : (int)dd;
 }
 
+namespace quber {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+// uint8 tensor [planes, H, W] viewed through a (box_w x box_h x 1) window; out-of-range bytes read as 0
+static bool make_map(CUtensorMap *m, const void *base, int planes, int H, int W, int box_w, int box_h) {
+    EncodeTiledFn enc = get_encode_tiled();
+    if (!enc) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)planes};
+    const cuuint64_t strides[2] = {(cuuint64_t)W, (cuuint64_t)W * H};
+    const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+}  // namespace quber
+
 extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
                                    uint8_t *boundary, uint8_t *fg, void *stream) {
     using namespace quber;
@@ -191,12 +410,29 @@ extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, in
     if (W % 16 != 0 || !aligned16(masks) || (per_instance && !aligned16(per_instance)) ||
         (boundary && !aligned16(boundary)) || (fg && !aligned16(fg)))
         return QUBER_E_ALIGN;
+    if (B > 65535) return QUBER_E_UNSUPPORTED;
+    dim3 grid(cdiv(W, B_TW), cdiv(H, B_TH), B);
+    const char *impl = getenv("QUBER_BOUNDARY_IMPL");      // "ldg": the plain-load kernel (kept for A/B checks)
+    if (!(impl && impl[0] == 'l')) {
+        const int hw = ((d + 3) >> 2) + (((d + 3) >> 2) & 1), WS = B_TWW + 2 * hw, R = B_TH + 2 * d;
+        CUtensorMap in_map, out_map;
+        if (!make_map(&in_map, masks, B * K, H, W, WS * 4, R) ||
+            !make_map(&out_map, per_instance ? per_instance : masks, B * K, H, W, B_TW, B_TH)) {
+            set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
+            return QUBER_E_CUDA;
+        }
+        const size_t stage = align_up((size_t)R * WS * 4, 128);
+        const size_t smem = 2 * stage + align_up((size_t)R * B_TWW * 4, 128) + 3 * (size_t)B_TH * B_TWW * 4 + 128;
+        QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        boundary_tma_kernel<<<grid, B_THREADS, smem, (cudaStream_t)stream>>>(in_map, out_map, K, H, W, d, per_instance != nullptr,
+                                                                            boundary, fg);
+        return check_launch("boundary_tma_kernel");
+    }
     const int hw = (d + 3) >> 2, WS = B_TWW + 2 * hw, R = B_TH + 2 * d;
     const size_t smem = 2 * (size_t)R * WS * sizeof(uint32_t);
-    QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid(cdiv(W, B_TW), cdiv(H, B_TH), B);
-    boundary_kernel<<<grid, B_THREADS, smem, (cudaStream_t)stream>>>(masks, K, H, W, d, per_instance, boundary, fg);
-    return check_launch("boundary_kernel");
+    QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_ldg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    boundary_ldg_kernel<<<grid, B_THREADS, smem, (cudaStream_t)stream>>>(masks, K, H, W, d, per_instance, boundary, fg);
+    return check_launch("boundary_ldg_kernel");
 }
 
 extern "C" int quber_quadruple_maps(const uint8_t *gt, const uint8_t *pred, int B, size_t n, uint8_t *out, void *stream) {

@@ -6,11 +6,11 @@
 // meanshiftformer/modeling/pixel_decoder/ops).
 //
 // The reference runs one thread per output scalar: 48 scalar gathers each and the sampling
-// locations re-read by all D channel threads.  Here D/4 lanes own one (query, head): every corner of
-// every tap is ONE 128-bit load per lane (a head's D floats are contiguous, value is [B,S,M,D]), the
-// (x, y, weight) triple of a tap is a broadcast load shared by the lane group, and a CTA works on
-// 32 CONSECUTIVE queries of ONE head so that overlapping bilinear footprints of neighbouring
-// queries hit in L1.  Accumulation order over (level, point) and the w1..w4 arithmetic are the
+// locations re-read (and the bilinear set-up recomputed) by all D channel threads.  Here D/4 lanes own
+// one (query, head): every corner of every tap is ONE 128-bit load per lane (a head's D floats are
+// contiguous, value is [B,S,M,D]), the set-up of a tap is done once and warp-shuffled to the group,
+// and a CTA works on 32 CONSECUTIVE queries of ONE head so that overlapping bilinear footprints of
+// neighbouring queries hit in L1.  Accumulation order over (level, point) and the w1..w4 arithmetic are the
 // reference's, so fp32 results agree with it to rounding.
 #include <cuda_bf16.h>
 
@@ -38,8 +38,15 @@ template <> struct Vec4<__nv_bfloat16> {
 };
 
 // D/4 lanes per (query, head); blockDim.x = 256; blockIdx = (query block, head, batch).
+//
+// Two phases per round of LPG taps.  SETUP: lane t of the group prepares tap (s0 + t) — loads its
+// (x, y, weight), does the floor / bounds / corner-weight arithmetic ONCE (the reference repeats it in
+// all D channel threads) and turns the four corners into clamped element offsets with zeroed weights
+// for corners outside the map (== the reference's `v = 0`, cuh:58-81, without predicated loads).
+// GATHER: the prepared tap is broadcast inside the group with width-LPG shuffles and every lane issues
+// four unconditional 128-bit loads and the reference's w1..w4 arithmetic on its four channels.
 template <int D, typename VT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
                     const float *__restrict__ loc, const float *__restrict__ attn, int S, int M, int L, int Q, int P,
                     VT *__restrict__ out) {
@@ -47,40 +54,64 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
     constexpr int GPB = 256 / LPG;          // (query, head) groups per CTA
     const int lane = threadIdx.x % LPG, grp = threadIdx.x / LPG;
     const int m = blockIdx.y, b = blockIdx.z;
-    const int q = blockIdx.x * GPB + grp;
-    if (q >= Q) return;
+    int q = blockIdx.x * GPB + grp;
+    const bool active = q < Q;
+    if (!active) q = Q - 1;                 // stay in the shuffles; nothing is stored
     const size_t qm = ((size_t)b * Q + q) * M + m;
-    const float *lp = loc + qm * L * P * 2;
-    const float *ap = attn + qm * L * P;
+    const int LP = L * P;
+    const float2 *lp = reinterpret_cast<const float2 *>(loc) + qm * LP;
+    const float *ap = attn + qm * LP;
     const int MD = M * D;
+    const VT *vb = value + (size_t)b * S * MD + m * D + lane * 4;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int l = 0; l < L; ++l) {
-        const int h = (int)__ldg(shapes + 2 * l), w = (int)__ldg(shapes + 2 * l + 1);
-        const VT *vbase = value + ((size_t)b * S + (size_t)__ldg(starts + l)) * MD + m * D + lane * 4;
-#pragma unroll 4
-        for (int pt = 0; pt < P; ++pt) {
-            const float2 xy = __ldg(reinterpret_cast<const float2 *>(lp) + l * P + pt);
-            const float a = __ldg(ap + l * P + pt);
-            const float him = xy.y * h - 0.5f, wim = xy.x * w - 0.5f;          // cuh:290-291
-            if (him > -1.f && wim > -1.f && him < (float)h && wim < (float)w) { // cuh:293
+    for (int s0 = 0; s0 < LP; s0 += LPG) {
+        // ---- setup: this lane's tap ----
+        const int tap = s0 + lane;
+        int o1 = 0, o3 = 0;
+        float w1 = 0.f, w2 = 0.f, w3 = 0.f, w4 = 0.f, a = 0.f;
+        if (tap < LP) {
+            int l = 0;
+            for (int i = 1; i < L; ++i) l += tap >= i * P;                       // tap / P without an integer division
+            const int h = (int)__ldg(shapes + 2 * l), w = (int)__ldg(shapes + 2 * l + 1);
+            const int start = (int)__ldg(starts + l);
+            const float2 xy = __ldg(lp + tap);
+            const float him = xy.y * h - 0.5f, wim = xy.x * w - 0.5f;            // cuh:290-291
+            if (him > -1.f && wim > -1.f && him < (float)h && wim < (float)w) {  // cuh:293
+                a = __ldg(ap + tap);
                 const int hl = (int)floorf(him), wl = (int)floorf(wim);
                 const float lh = him - hl, lw = wim - wl, hh = 1.f - lh, hw = 1.f - lw;
                 const bool y0 = hl >= 0, y1 = hl + 1 <= h - 1, x0 = wl >= 0, x1 = wl + 1 <= w - 1;
-                const VT *p00 = vbase + ((size_t)hl * w + wl) * MD;
-                float4 v1 = make_float4(0, 0, 0, 0), v2 = v1, v3 = v1, v4 = v1;
-                if (y0 && x0) v1 = Vec4<VT>::load(p00);
-                if (y0 && x1) v2 = Vec4<VT>::load(p00 + MD);
-                if (y1 && x0) v3 = Vec4<VT>::load(p00 + (size_t)w * MD);
-                if (y1 && x1) v4 = Vec4<VT>::load(p00 + (size_t)w * MD + MD);
-                const float w1 = hh * hw, w2 = hh * lw, w3 = lh * hw, w4 = lh * lw;   // cuh:85
-                acc.x += (w1 * v1.x + w2 * v2.x + w3 * v3.x + w4 * v4.x) * a;        // cuh:87,295
-                acc.y += (w1 * v1.y + w2 * v2.y + w3 * v3.y + w4 * v4.y) * a;
-                acc.z += (w1 * v1.z + w2 * v2.z + w3 * v3.z + w4 * v4.z) * a;
-                acc.w += (w1 * v1.w + w2 * v2.w + w3 * v3.w + w4 * v4.w) * a;
+                const int ry0 = max(hl, 0), ry1 = min(hl + 1, h - 1), cx0 = max(wl, 0);
+                o1 = ((start + ry0 * w + cx0) * MD) | (int)(x0 && x1);           // bit 0: the x+1 corner is a different pixel
+                o3 = (start + ry1 * w + cx0) * MD;
+                w1 = (y0 && x0) ? hh * hw : 0.f;                                 // cuh:85 (w1..w4), 0 where the reference reads v = 0
+                w2 = (y0 && x1) ? hh * lw : 0.f;
+                w3 = (y1 && x0) ? lh * hw : 0.f;
+                w4 = (y1 && x1) ? lh * lw : 0.f;
+            }
+        }
+        // ---- gather: all lanes of the group walk the prepared taps in the reference's (l, p) order ----
+        const int nt = min(LPG, LP - s0);
+#pragma unroll
+        for (int j = 0; j < LPG; ++j) {
+            if (j < nt) {
+                int bo1 = __shfl_sync(0xffffffffu, o1, j, LPG);
+                const int bo3 = __shfl_sync(0xffffffffu, o3, j, LPG);
+                const float b1 = __shfl_sync(0xffffffffu, w1, j, LPG), b2 = __shfl_sync(0xffffffffu, w2, j, LPG);
+                const float b3 = __shfl_sync(0xffffffffu, w3, j, LPG), b4 = __shfl_sync(0xffffffffu, w4, j, LPG);
+                const float ba = __shfl_sync(0xffffffffu, a, j, LPG);
+                const int dx = (bo1 & 1) ? MD : 0;
+                bo1 &= ~1;
+                const float4 v1 = Vec4<VT>::load(vb + bo1), v2 = Vec4<VT>::load(vb + bo1 + dx);
+                const float4 v3 = Vec4<VT>::load(vb + bo3), v4 = Vec4<VT>::load(vb + bo3 + dx);
+                acc.x += (b1 * v1.x + b2 * v2.x + b3 * v3.x + b4 * v4.x) * ba;   // cuh:87,295
+                acc.y += (b1 * v1.y + b2 * v2.y + b3 * v3.y + b4 * v4.y) * ba;
+                acc.z += (b1 * v1.z + b2 * v2.z + b3 * v3.z + b4 * v4.z) * ba;
+                acc.w += (b1 * v1.w + b2 * v2.w + b3 * v3.w + b4 * v4.w) * ba;
             }
         }
     }
-    Vec4<VT>::store(out + qm * D + lane * 4, acc);
+    if (active) Vec4<VT>::store(out + qm * D + lane * 4, acc);
 }
 
 // Any D (the reference's own mapping: one thread per output scalar), fp32 only.
