@@ -85,6 +85,10 @@ int quber_boundary_dilation(int H, int W, double ratio);
 int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
                         uint8_t *boundary, uint8_t *fg, void *stream);
 int quber_quadruple_maps(const uint8_t *gt, const uint8_t *pred, int B, size_t n, uint8_t *out, void *stream);
+/* Diagnostic, NOT on the hot path (synchronises the device): number of TMA tile loads that
+ * quber_mask_boundary gave up waiting for since the library was loaded (always 0 on a healthy
+ * device; a non-zero value means the outputs of that call are invalid), or -1 on a CUDA error. */
+int quber_tma_timeouts(void);
 
 /* ---------------------------------------------------------------------------------------------
  * K3/K4  post-processing — replaces, in ONE call and with no host round trip:

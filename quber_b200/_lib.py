@@ -42,6 +42,7 @@ SYMBOLS = {
     "quber_boundary_dilation": (c_i, [c_i, c_i, c_d]),
     "quber_mask_boundary": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp]),
     "quber_quadruple_maps": (c_i, [c_vp, c_vp, c_i, c_sz, c_vp, c_vp]),
+    "quber_tma_timeouts": (c_i, []),
     "quber_post_workspace_bytes": (c_sz, [ctypes.POINTER(PostParams)]),
     "quber_post_process": (c_i, [ctypes.POINTER(PostParams), ctypes.POINTER(PostIO), c_vp, c_sz, c_vp]),
     "quber_msda_forward": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),

@@ -154,10 +154,25 @@ boundary_ldg_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, int 
 // ------------------------------------------------------------------------------------------------
 // TMA version (default).  The (tile + halo) box of every mask plane is fetched by ONE
 // cp.async.bulk.tensor.3d per plane — out-of-image bytes arrive as zeros, which IS the erosion's
-// zero padding — double-buffered against the compute of the previous plane through two mbarriers,
-// and the per-instance result leaves through a TMA store (clipped at the image edge by the
-// hardware).  No thread issues a global load; the only per-thread global stores are the two
-// union maps at the end.
+// zero padding — two planes ahead of the compute through two mbarriers, and the per-instance
+// result leaves through a TMA store (clipped at the image edge by the hardware).  No thread issues
+// a global load; the only per-thread global stores are the two union maps at the end.
+//
+// Measured on B200 (scripts/tma_probe.cu): a tiled load faults (illegal instruction) unless the
+// innermost start coordinate is a multiple of 16 BYTES; negative / past-the-edge load coordinates
+// are fine (zero fill); a store must not start at a negative coordinate.  Hence the horizontal halo
+// is rounded up to 16 pixels (B_HX) and stores always start at the tile origin.
+//
+// Per plane a CTA takes one of three routes, decided from one pass over the staged bytes:
+//   empty   every byte 0                         -> nothing to erode; a zero tile is stored
+//   binary  every byte in {0, v} for a single v  -> the tile is packed to ONE BIT per pixel (16 pixels
+//           per 128-bit shared load), eroded with funnel shifts and ANDs on 32-pixel words, and expanded
+//           back to bytes only for the 128x64 central tile.  This is the route every real mask takes
+//           (the reference feeds 0/255 or 0/1 masks).
+//   bytes   anything else                        -> the exact uint8 min filter (window doubling on
+//           packed bytes, as in boundary_ldg_kernel), so arbitrary planes still match cv2 bit for bit.
+// The union maps are uint8 WRAPPING sums over the planes (util.py:96-98 sums uint8 arrays), kept as
+// packed byte accumulators in registers in every route.
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
@@ -166,13 +181,15 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+// false = timed out (a lost TMA must fail the call, never hang the GPU)
+__device__ __forceinline__ bool mbar_wait(uint64_t *bar, uint32_t parity) {
     uint32_t done = 0;
     for (int spin = 0; !done; ++spin) {
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-        if (spin > (1 << 24)) __trap();       // a lost TMA must fail the launch, never hang the GPU
+        if (spin > (1 << 22)) return false;
     }
+    return true;
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, uint64_t *bar, int x, int y, int z) {
@@ -187,109 +204,199 @@ __device__ __forceinline__ void tma_commit() { asm volatile("cp.async.bulk.commi
 template <int N> __device__ __forceinline__ void tma_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void tma_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
+// packed-byte helpers that stay cheap in SASS (sm_100 has no SIMD-in-word integer min/add: __vminu4 and
+// friends expand to LOP3/IADD sequences, which is why the binary route avoids them)
+__device__ __forceinline__ uint32_t add_bytes(uint32_t a, uint32_t b) {          // per-byte wrapping add
+    return ((a & 0x7f7f7f7fu) + (b & 0x7f7f7f7fu)) ^ ((a ^ b) & 0x80808080u);
+}
+__device__ __forceinline__ uint32_t nonzero_bytes01(uint32_t w) {                // 0x01 per non-zero byte
+    return ((((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u) >> 7;
+}
+__device__ __forceinline__ uint32_t nibble_to_bytes01(uint32_t n) {              // bit i of n -> 0x01 in byte i
+    return (n * 0x00204081u) & 0x01010101u;
+}
+
+// staged geometry shared by the kernel and the host launcher
+struct BGeom {
+    int hx, SW, WS, WS16, R, RW32;
+    uint32_t stage_bytes, stage_stride, v1_bytes, bits_bytes, hb_bytes;
+    size_t smem;
+    __host__ __device__ explicit BGeom(int d) {
+        hx = (d + 15) & ~15;                  // horizontal halo in pixels: TMA start coordinate % 16 == 0
+        SW = B_TW + 2 * hx;                   // staged row, bytes (multiple of 32)
+        WS = SW >> 2;
+        WS16 = SW >> 4;
+        R = B_TH + 2 * d;
+        RW32 = (SW >> 5) + 1;                 // bit-row words + one zero word read by the last funnel shift
+        stage_bytes = (uint32_t)R * SW;
+        stage_stride = (stage_bytes + 127u) & ~127u;
+        v1_bytes = ((uint32_t)R * B_TWW * 4 + 127u) & ~127u;
+        bits_bytes = ((uint32_t)R * RW32 * 4 + 127u) & ~127u;
+        hb_bytes = ((uint32_t)R * 4 * 4 + 127u) & ~127u;
+        smem = 2 * (size_t)stage_stride + v1_bytes + 3 * (size_t)B_TH * B_TWW * 4 + bits_bytes + hb_bytes + 128;
+    }
+};
+
+__device__ unsigned int g_tma_timeouts = 0;     // diagnostic: mbarrier waits that gave up (quber_tma_timeouts())
+
 __global__ void __launch_bounds__(B_THREADS)
 boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map, int K, int H, int W,
                     int d, int has_per, uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg) {
     extern __shared__ __align__(128) unsigned char sm_raw[];
     __shared__ __align__(8) uint64_t full[2];
-    const int hw = ((d + 3) >> 2) + (((d + 3) >> 2) & 1);   // halo words per side, even -> inner box bytes % 16 == 0
-    const int WS = B_TWW + 2 * hw;                          // words per staged row
-    const int R = B_TH + 2 * d;                             // staged rows
-    const uint32_t stage_bytes = (uint32_t)R * WS * 4;
-    const uint32_t stage_stride = (stage_bytes + 127u) & ~127u;
-    auto S = [&](int i) { return reinterpret_cast<uint32_t *>(sm_raw + (size_t)(i & 1) * stage_stride); };
-    uint32_t *V1 = reinterpret_cast<uint32_t *>(sm_raw + 2 * stage_stride);                 // [R][32]
-    uint32_t *O0 = V1 + (((size_t)R * B_TWW + 31) & ~(size_t)31);                            // [64][32] x2, 128-B aligned
-    uint32_t *Z = O0 + 2 * B_TH * B_TWW;                                                    // zero tile
+    __shared__ uint32_t red[6];                 // 3 rotating (OR, AND) slots of the per-plane byte census
+    __shared__ int s_abort;
+    const BGeom g(d);
+    const int hx = g.hx, WS = g.WS, WS16 = g.WS16, R = g.R, RW32 = g.RW32, hw = hx >> 2;
+    auto S = [&](int i) { return reinterpret_cast<uint32_t *>(sm_raw + (size_t)(i & 1) * g.stage_stride); };
+    uint32_t *V1 = reinterpret_cast<uint32_t *>(sm_raw + 2 * (size_t)g.stage_stride);       // [R][32]   (byte route)
+    uint32_t *O0 = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(V1) + g.v1_bytes);   // [64][32] x2
+    uint32_t *Z = O0 + 2 * B_TH * B_TWW;                                                   // zero tile
+    uint32_t *bits = Z + B_TH * B_TWW;                                                     // [R][RW32] one bit per staged pixel
+    uint32_t *Hb = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(bits) + g.bits_bytes);   // [R][4]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.z;
     const int ty0 = blockIdx.y * B_TH, tx0 = blockIdx.x * B_TW;
-    const int Ww = W >> 2;
     const size_t HW = (size_t)H * W;
     const int w = 2 * d + 1;
     int p_top = 1;
     while (p_top * 2 <= w) p_top *= 2;
-    const int lead = 4 * hw - d;
+    const int lead = hx - d;
 
     for (int i = tid; i < B_TH * B_TWW; i += B_THREADS) Z[i] = 0u;
+    for (int i = tid; i < R * RW32; i += B_THREADS) bits[i] = 0u;      // the pad word of every bit row stays 0
     if (tid == 0) {
         mbar_init(&full[0], 1);
         mbar_init(&full[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        red[0] = red[2] = red[4] = 0u;
+        red[1] = red[3] = red[5] = 0xffffffffu;
+        s_abort = 0;
     }
     fence_proxy_async();         // Z was written by the generic proxy, TMA stores read it
     __syncthreads();
+    auto issue = [&](int k) {    // thread 0 only: fetch plane k into stage k & 1
+        fence_proxy_async();
+        mbar_expect_tx(&full[k & 1], g.stage_bytes);
+        tma_load_3d(S(k), &in_map, &full[k & 1], tx0 - hx, ty0 - d, b * K + k);
+    };
     if (tid == 0) {
-        mbar_expect_tx(&full[0], stage_bytes);
-        tma_load_3d(S(0), &in_map, &full[0], tx0 - 4 * hw, ty0 - d, b * K);
+        issue(0);
+        if (K > 1) issue(1);
     }
 
-    const int ci = tid & 31, cr0 = tid >> 5;
-    uint32_t uni_acc[B_RPT], fg_acc[B_RPT];
+    const int row = tid >> 2, jw = tid & 3;     // this thread's 32 output pixels: tile row, 32-pixel column group
+    uint32_t uni_acc[8], fg_acc[8];
 #pragma unroll
-    for (int j = 0; j < B_RPT; ++j) uni_acc[j] = fg_acc[j] = 0;
+    for (int q = 0; q < 8; ++q) uni_acc[q] = fg_acc[q] = 0;
     int o_slot = 0;
 
     for (int k = 0; k < K; ++k) {
         uint32_t *cur = S(k);
-        if (tid == 0 && k + 1 < K) {          // prefetch the next plane; its buffer was released by the barrier that ended iteration k-1
-            fence_proxy_async();
-            mbar_expect_tx(&full[(k + 1) & 1], stage_bytes);
-            tma_load_3d(S(k + 1), &in_map, &full[(k + 1) & 1], tx0 - 4 * hw, ty0 - d, b * K + k + 1);
-        }
-        mbar_wait(&full[k & 1], (k >> 1) & 1);
-        // ---- uniformity scan (128-bit shared loads) ----
-        const uint32_t first = (cur[0] & 0xffu) * 0x01010101u;
-        uint32_t diff = 0;
+        if (!mbar_wait(&full[k & 1], (k >> 1) & 1)) { s_abort = 1; atomicAdd(&g_tma_timeouts, 1u); }
+        // ---- census + bit packing: one pass over the staged bytes, 16 pixels per shared load ----
+        const int slot = (k % 3) * 2;
         {
+            uint32_t o = 0u, a = 0xffffffffu;
             const uint4 *c4 = reinterpret_cast<const uint4 *>(cur);
-            const int n4 = (R * WS) >> 2;                   // WS is even and R*WS*4 % 16 == 0
-            for (int i = tid; i < n4; i += B_THREADS) {
-                const uint4 v = c4[i];
-                diff |= (v.x ^ first) | (v.y ^ first) | (v.z ^ first) | (v.w ^ first);
+            uint16_t *b16 = reinterpret_cast<uint16_t *>(bits);
+            const int n16 = R * WS16;
+            for (int idx = tid; idx < n16; idx += B_THREADS) {
+                const int r = idx / WS16, c = idx - r * WS16;
+                const uint4 x = c4[idx];
+                const uint32_t t0 = nonzero_bytes01(x.x), t1 = nonzero_bytes01(x.y), t2 = nonzero_bytes01(x.z), t3 = nonzero_bytes01(x.w);
+                o |= x.x | x.y | x.z | x.w;
+                a &= (x.x | ~(t0 * 255u)) & (x.y | ~(t1 * 255u)) & (x.z | ~(t2 * 255u)) & (x.w | ~(t3 * 255u));
+                const uint32_t pk = ((t0 * 0x01020408u) >> 24) | (((t1 * 0x01020408u) >> 24) << 4) |
+                                    (((t2 * 0x01020408u) >> 24) << 8) | (((t3 * 0x01020408u) >> 24) << 12);
+                b16[r * (2 * RW32) + c] = (uint16_t)pk;
+            }
+            o = __reduce_or_sync(0xffffffffu, o);
+            a = __reduce_and_sync(0xffffffffu, a);
+            if (lane == 0) {
+                if (o) atomicOr(&red[slot], o);
+                if (a != 0xffffffffu) atomicAnd(&red[slot + 1], a);
             }
         }
-        const int any = __syncthreads_or(diff != 0);
-        uint32_t orig[B_RPT], er[B_RPT];
-        if (!any) {
-#pragma unroll
-            for (int j = 0; j < B_RPT; ++j) { orig[j] = first; er[j] = first; }
+        __syncthreads();                                    // S1: census complete, every read of `cur` above is done
+        if (s_abort) break;
+        const uint32_t oc = red[slot], ac = red[slot + 1];
+        const uint32_t v = (oc | (oc >> 8) | (oc >> 16) | (oc >> 24)) & 0xffu;          // OR of all bytes
+        const uint32_t va = (ac & (ac >> 8) & (ac >> 16) & (ac >> 24)) & 0xffu;         // AND of the non-zero bytes
+        const bool empty = v == 0u, binary = v == va;
+        if (tid == 0) {
+            const int s2 = ((k + 2) % 3) * 2;               // next written two iterations from now, last read one ago
+            red[s2] = 0u;
+            red[s2 + 1] = 0xffffffffu;
+            if ((empty || binary) && k + 2 < K) issue(k + 2);   // the stage is dead already on these routes
+        }
+        if (empty) {
             if (has_per && tid == 0) { tma_store_3d(&out_map, Z, tx0, ty0, b * K + k); tma_commit(); }
-        } else {
+            continue;
+        }
+        uint32_t bdw[8], mw[8];
+        if (binary) {
+            // ---- horizontal erosion on bit rows: window [x-d, x+d] for the four central 32-pixel words ----
+            for (int it = tid; it < R * 4; it += B_THREADS) {
+                const uint32_t *row32 = bits + (it >> 2) * RW32;
+                const int s0 = hx + 32 * (it & 3) - d;
+                uint32_t e = 0xffffffffu;
+                for (int t = 0; t < w; ++t) {
+                    const int s = s0 + t;
+                    e &= __funnelshift_r(row32[s >> 5], row32[(s >> 5) + 1], s & 31);
+                }
+                Hb[it] = e;
+            }
+            if (has_per && tid == 0) tma_wait_read<1>();     // the store that last used this O slot has read it
+            __syncthreads();                                 // S2
+            uint32_t e = 0xffffffffu;
+            for (int t = 0; t < w; ++t) e &= Hb[(row + t) * 4 + jw];
+            const uint32_t *mrow = bits + (row + d) * RW32 + (hx >> 5) + jw;
+            const uint32_t m = __funnelshift_r(mrow[0], mrow[1], hx & 31);
+            const uint32_t bd = m & ~e;                      // mask - eroded, one bit per pixel
 #pragma unroll
-            for (int j = 0; j < B_RPT; ++j) orig[j] = cur[(size_t)(cr0 + 8 * j + d) * WS + hw + ci];
+            for (int q = 0; q < 8; ++q) {
+                bdw[q] = nibble_to_bytes01((bd >> (4 * q)) & 15u) * v;
+                mw[q] = nibble_to_bytes01((m >> (4 * q)) & 15u) * v;
+            }
+        } else {
+            // ---- exact uint8 min filter (window doubling on packed bytes) ----
+            {
+                const uint4 *src4 = reinterpret_cast<const uint4 *>(cur + (size_t)(row + d) * WS + hw + 8 * jw);
+                const uint4 a0 = src4[0], a1 = src4[1];
+                mw[0] = a0.x; mw[1] = a0.y; mw[2] = a0.z; mw[3] = a0.w; mw[4] = a1.x; mw[5] = a1.y; mw[6] = a1.z; mw[7] = a1.w;
+            }
             __syncthreads();                                 // every thread holds its originals before rows are overwritten
-            // ---- horizontal pass, in place, one warp per row (rows are independent: warp-level sync only) ----
-            for (int r = warp; r < R; r += B_THREADS / 32) {
-                uint32_t *row = cur + (size_t)r * WS;
+            for (int r = warp; r < R; r += B_THREADS / 32) {  // horizontal pass, in place, one warp per row
+                uint32_t *rowp = cur + (size_t)r * WS;
                 const int i0 = lane, i1 = lane + 32;
                 for (int p = 1; p < p_top; p <<= 1) {
                     const int sw = p >> 2, sb = p & 3;
                     uint32_t n0, n1 = 0;
                     {
                         const int j0 = i0 + sw;
-                        const uint32_t lo = j0 < WS ? row[j0] : 0u, hi = j0 + 1 < WS ? row[j0 + 1] : 0u;
-                        n0 = __vminu4(row[i0], sb ? shift_bytes(lo, hi, sb) : lo);
+                        const uint32_t lo = j0 < WS ? rowp[j0] : 0u, hi = j0 + 1 < WS ? rowp[j0 + 1] : 0u;
+                        n0 = __vminu4(rowp[i0], sb ? shift_bytes(lo, hi, sb) : lo);
                     }
                     if (i1 < WS) {
                         const int j0 = i1 + sw;
-                        const uint32_t lo = j0 < WS ? row[j0] : 0u, hi = j0 + 1 < WS ? row[j0 + 1] : 0u;
-                        n1 = __vminu4(row[i1], sb ? shift_bytes(lo, hi, sb) : lo);
+                        const uint32_t lo = j0 < WS ? rowp[j0] : 0u, hi = j0 + 1 < WS ? rowp[j0 + 1] : 0u;
+                        n1 = __vminu4(rowp[i1], sb ? shift_bytes(lo, hi, sb) : lo);
                     }
                     __syncwarp();
-                    row[i0] = n0;
-                    if (i1 < WS) row[i1] = n1;
+                    rowp[i0] = n0;
+                    if (i1 < WS) rowp[i1] = n1;
                     __syncwarp();
                 }
                 const int a1 = 4 * lane + lead, a2 = a1 + w - p_top;
                 const int w1 = a1 >> 2, s1 = a1 & 3, w2 = a2 >> 2, s2 = a2 & 3;
-                const uint32_t v1 = shift_bytes(row[w1], w1 + 1 < WS ? row[w1 + 1] : 0u, s1);
-                const uint32_t v2 = shift_bytes(row[w2], w2 + 1 < WS ? row[w2 + 1] : 0u, s2);
+                const uint32_t v1 = shift_bytes(rowp[w1], w1 + 1 < WS ? rowp[w1 + 1] : 0u, s1);
+                const uint32_t v2 = shift_bytes(rowp[w2], w2 + 1 < WS ? rowp[w2 + 1] : 0u, s2);
                 V1[r * B_TWW + lane] = __vminu4(v1, v2);
             }
+            if (has_per && tid == 0) tma_wait_read<1>();
             __syncthreads();
-            // ---- vertical pass: ping-pong V1 <-> (dead) staging buffer ----
-            uint32_t *src = V1, *dst = cur;
+            uint32_t *src = V1, *dst = cur;                  // vertical pass: ping-pong V1 <-> (dead) staging buffer
             for (int p = 1; p < p_top; p <<= 1) {
                 for (int idx = tid; idx < R * B_TWW; idx += B_THREADS) {
                     const int r = idx >> 5;
@@ -299,37 +406,46 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
                 __syncthreads();
                 uint32_t *t = src; src = dst; dst = t;
             }
+            const uint32_t *e0 = src + row * B_TWW + 8 * jw, *e1 = src + (row + w - p_top) * B_TWW + 8 * jw;
 #pragma unroll
-            for (int j = 0; j < B_RPT; ++j) {
-                const int r = cr0 + 8 * j;
-                er[j] = __vminu4(src[r * B_TWW + ci], src[(r + w - p_top) * B_TWW + ci]);
-            }
+            for (int q = 0; q < 8; ++q) bdw[q] = __vsub4(mw[q], __vminu4(e0[q], e1[q]));
+        }
+        // ---- common tail: wrapping uint8 sums for the union maps, per-instance tile out through TMA ----
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            uni_acc[q] = add_bytes(uni_acc[q], bdw[q]);
+            fg_acc[q] = add_bytes(fg_acc[q], mw[q]);
+        }
+        if (has_per) {
+            uint4 *o4 = reinterpret_cast<uint4 *>(O0 + (size_t)o_slot * B_TH * B_TWW + row * B_TWW + 8 * jw);
+            o4[0] = make_uint4(bdw[0], bdw[1], bdw[2], bdw[3]);
+            o4[1] = make_uint4(bdw[4], bdw[5], bdw[6], bdw[7]);
+            fence_proxy_async();
+        }
+        __syncthreads();                                     // S3: O tile complete; bits / Hb / V1 / cur are free again
+        if (tid == 0) {
             if (has_per) {
-                if (tid == 0) tma_wait_read<1>();            // the store that last used this O slot has read it
-                __syncthreads();
-                uint32_t *o = O0 + (size_t)o_slot * B_TH * B_TWW;
-#pragma unroll
-                for (int j = 0; j < B_RPT; ++j) o[(cr0 + 8 * j) * B_TWW + ci] = __vsub4(orig[j], er[j]);
-                fence_proxy_async();
-                __syncthreads();
-                if (tid == 0) { tma_store_3d(&out_map, o, tx0, ty0, b * K + k); tma_commit(); }
-                o_slot ^= 1;
+                tma_store_3d(&out_map, O0 + (size_t)o_slot * B_TH * B_TWW, tx0, ty0, b * K + k);
+                tma_commit();
             }
+            if (!binary && k + 2 < K) issue(k + 2);
         }
-#pragma unroll
-        for (int j = 0; j < B_RPT; ++j) {
-            uni_acc[j] = __vadd4(uni_acc[j], __vsub4(orig[j], er[j]));
-            fg_acc[j] = __vadd4(fg_acc[j], orig[j]);
-        }
-        __syncthreads();   // releases `cur` (and the V buffers) for the prefetch issued at the top of the next iteration
+        o_slot ^= 1;
     }
+    if (!s_abort) {
+        const int gy = ty0 + row, gx = tx0 + 32 * jw;
+        if (gy < H && gx < W) {                              // W % 16 == 0: each 16-pixel half is all in or all out
+            const size_t o = (size_t)b * HW + (size_t)gy * W + gx;
 #pragma unroll
-    for (int j = 0; j < B_RPT; ++j) {
-        const int gy = ty0 + cr0 + 8 * j, gxw = (tx0 >> 2) + ci;
-        if (gy < H && gxw < Ww) {
-            const size_t o = (size_t)b * HW + (size_t)gy * W + 4 * gxw;
-            if (boundary) st_stream_u1(boundary + o, __vcmpne4(uni_acc[j], 0u) & 0x01010101u);
-            if (fg) st_stream_u1(fg + o, __vcmpne4(fg_acc[j], 0u) & 0x01010101u);
+            for (int h = 0; h < 2; ++h) {
+                if (gx + 16 * h >= W) break;
+                if (boundary)
+                    st_stream_u4(boundary + o + 16 * h, make_uint4(nonzero_bytes01(uni_acc[4 * h]), nonzero_bytes01(uni_acc[4 * h + 1]),
+                                                                   nonzero_bytes01(uni_acc[4 * h + 2]), nonzero_bytes01(uni_acc[4 * h + 3])));
+                if (fg)
+                    st_stream_u4(fg + o + 16 * h, make_uint4(nonzero_bytes01(fg_acc[4 * h]), nonzero_bytes01(fg_acc[4 * h + 1]),
+                                                             nonzero_bytes01(fg_acc[4 * h + 2]), nonzero_bytes01(fg_acc[4 * h + 3])));
+            }
         }
     }
     if (tid == 0) tma_wait_all();     // shared memory must outlive the bulk stores that read it
@@ -414,18 +530,16 @@ extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, in
     dim3 grid(cdiv(W, B_TW), cdiv(H, B_TH), B);
     const char *impl = getenv("QUBER_BOUNDARY_IMPL");      // "ldg": the plain-load kernel (kept for A/B checks)
     if (!(impl && impl[0] == 'l')) {
-        const int hw = ((d + 3) >> 2) + (((d + 3) >> 2) & 1), WS = B_TWW + 2 * hw, R = B_TH + 2 * d;
+        const BGeom g(d);
         CUtensorMap in_map, out_map;
-        if (!make_map(&in_map, masks, B * K, H, W, WS * 4, R) ||
+        if (!make_map(&in_map, masks, B * K, H, W, g.SW, g.R) ||
             !make_map(&out_map, per_instance ? per_instance : masks, B * K, H, W, B_TW, B_TH)) {
             set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
             return QUBER_E_CUDA;
         }
-        const size_t stage = align_up((size_t)R * WS * 4, 128);
-        const size_t smem = 2 * stage + align_up((size_t)R * B_TWW * 4, 128) + 3 * (size_t)B_TH * B_TWW * 4 + 128;
-        QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        boundary_tma_kernel<<<grid, B_THREADS, smem, (cudaStream_t)stream>>>(in_map, out_map, K, H, W, d, per_instance != nullptr,
-                                                                            boundary, fg);
+        QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+        boundary_tma_kernel<<<grid, B_THREADS, g.smem, (cudaStream_t)stream>>>(in_map, out_map, K, H, W, d, per_instance != nullptr,
+                                                                              boundary, fg);
         return check_launch("boundary_tma_kernel");
     }
     const int hw = (d + 3) >> 2, WS = B_TWW + 2 * hw, R = B_TH + 2 * d;
@@ -433,6 +547,12 @@ extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, in
     QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_ldg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     boundary_ldg_kernel<<<grid, B_THREADS, smem, (cudaStream_t)stream>>>(masks, K, H, W, d, per_instance, boundary, fg);
     return check_launch("boundary_ldg_kernel");
+}
+
+extern "C" int quber_tma_timeouts(void) {
+    unsigned int n = 0;
+    if (cudaMemcpyFromSymbol(&n, quber::g_tma_timeouts, sizeof(n)) != cudaSuccess) return -1;
+    return (int)n;
 }
 
 extern "C" int quber_quadruple_maps(const uint8_t *gt, const uint8_t *pred, int B, size_t n, uint8_t *out, void *stream) {

@@ -76,6 +76,32 @@ def test_boundary_random_bytes_any_radius(d):
         np.testing.assert_array_equal(fg[b].cpu().numpy(), oracle.masks_to_fg_mask(m[b]))
 
 
+@pytest.mark.parametrize("d", [1, 7, 8, 16, 17, 33, 64])
+def test_boundary_binary_route_values_and_mixed_planes(d):
+    """Binary planes with different non-zero values (bit-packed route), overlapping so that the uint8
+    wrap-around of the union sums matters (128 + 128 == 0), mixed with a noise plane (byte route) and an
+    empty plane, on a frame whose size is not a multiple of the 128x64 tile."""
+    rng = np.random.default_rng(100 + d)
+    base = synth.ellipse_masks(6, 200, 272, seed=d, axes=(20, 80), margin=10, value=1)
+    vals = [255, 128, 128, 1, 7, 254]
+    m = np.zeros((2, 8, 200, 272), np.uint8)
+    for k in range(6):
+        m[0, k] = base[k] * vals[k]
+        m[1, k] = base[5 - k] * vals[k]
+    m[0, 2] = m[0, 1]                                                # identical 128-valued planes: sums wrap to 0
+    m[0, 6] = rng.integers(0, 256, (200, 272), dtype=np.uint8)       # noise plane between binary ones
+    m[1, 6, :, :] = 255                                              # full plane: only the image border erodes
+    per, uni, fg = ops.mask_boundary(cu(m), d)
+    for b in range(2):
+        p = np.stack([_oracle_boundary_d(x, d) for x in m[b]])
+        u = (p.sum(0, dtype=np.uint8) > 0).astype(np.uint8)
+        np.testing.assert_array_equal(per[b].cpu().numpy(), p)
+        np.testing.assert_array_equal(uni[b].cpu().numpy(), u)
+        np.testing.assert_array_equal(fg[b].cpu().numpy(), oracle.masks_to_fg_mask(m[b]))
+    from quber_b200 import _lib
+    assert _lib.lib().quber_tma_timeouts() == 0
+
+
 def _oracle_boundary_d(mask, d):
     import ctypes
     out = np.empty_like(mask)
