@@ -6,13 +6,24 @@
 // meanshiftformer/modeling/pixel_decoder/ops).
 //
 // The reference runs one thread per output scalar: 48 scalar gathers each and the sampling
-// locations re-read (and the bilinear set-up recomputed) by all D channel threads.  Here D/4 lanes own
-// one (query, head): every corner of every tap is ONE 128-bit load per lane (a head's D floats are
-// contiguous, value is [B,S,M,D]), the set-up of a tap is done once and warp-shuffled to the group,
-// and a CTA works on 32 CONSECUTIVE queries of ONE head so that overlapping bilinear footprints of
-// neighbouring queries hit in L1.  Accumulation order over (level, point) and the w1..w4 arithmetic are the
-// reference's, so fp32 results agree with it to rounding.
+// locations re-read (and the bilinear set-up recomputed) by all D channel threads.  Here a group of
+// D/CPL lanes owns one (query, head) and every corner of every tap is ONE 128-bit load per lane (a head's
+// D channels are contiguous, value is [B,S,M,D]; CPL = 4 fp32 or 8 bf16 channels per lane).  A CTA
+// works on 256/(D/CPL) CONSECUTIVE queries of ONE head so that overlapping bilinear footprints of
+// neighbouring queries hit in L1 (ncu: 68 % L1 sector hit rate, value read from DRAM exactly once).
+//
+// What bounds it (ncu --set full, profiles/): the L1 data pipe, not HBM.  Every gathered corner is a
+// 128-byte line that must be written back to registers at 128 B/clk/SM: 48 lines x B*Q*M = 9.9 GB per
+// launch at C2 = 266 us at 1.965 GHz, before the per-tap broadcast of the set-up (one more write-back
+// cycle per 32-bit value).  l1tex__lsu_writeback_active sits at 72 % and l1tex__data_pipe_lsu_wavefronts
+// at 75 %; 54 % of warp samples wait in long_scoreboard on that pipe.  Measured alternatives, all slower
+// at C2 (fp32, us/launch): set-up recomputed by every lane 594; 7-value shuffle broadcast 568; 16-byte
+// shared-memory tap records read with LDS.128 648; 4-value broadcast + per-lane weights 587; register
+// software pipelining of the corner loads 681 (3 CTAs/SM) and 903 (2 CTAs/SM) — throughput follows
+// resident warps, not loads in flight; 2-D query patches 585.  Kept: the variant with the fewest
+// instructions per gathered byte (558).
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -20,77 +31,117 @@ namespace quber {
 
 constexpr int MSDA_MAX_L = 8;
 
-template <typename VT> struct Vec4;
-template <> struct Vec4<float> {
-    static __device__ __forceinline__ float4 load(const float *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
-    static __device__ __forceinline__ void store(float *p, float4 v) { st_stream_f4(p, v); }
-};
-template <> struct Vec4<__nv_bfloat16> {
-    static __device__ __forceinline__ float4 load(const __nv_bfloat16 *p) {
-        const uint2 r = __ldg(reinterpret_cast<const uint2 *>(p));
-        return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
-                           __uint_as_float(r.y & 0xffff0000u));
+template <typename VT> struct Lane;     // CPL channels of one pixel of one head, as ONE 128-bit access
+template <> struct Lane<float> {
+    static constexpr int CPL = 4;
+    float c[4];
+    __device__ __forceinline__ void load(const float *p) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(p));
+        c[0] = v.x; c[1] = v.y; c[2] = v.z; c[3] = v.w;
     }
-    static __device__ __forceinline__ void store(__nv_bfloat16 *p, float4 v) {
-        const __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
-        st_stream_u2(p, make_uint2(*reinterpret_cast<const uint32_t *>(&a), *reinterpret_cast<const uint32_t *>(&b)));
+    static __device__ __forceinline__ void store(float *p, const float *a) { st_stream_f4(p, make_float4(a[0], a[1], a[2], a[3])); }
+    static __device__ __forceinline__ uint4 load_raw(const float *p) { return __ldg(reinterpret_cast<const uint4 *>(p)); }
+    static __device__ __forceinline__ void unpack(const uint4 &r, float *c) {
+        c[0] = __uint_as_float(r.x); c[1] = __uint_as_float(r.y); c[2] = __uint_as_float(r.z); c[3] = __uint_as_float(r.w);
+    }
+};
+template <> struct Lane<__nv_bfloat16> {
+    static constexpr int CPL = 8;
+    float c[8];
+    __device__ __forceinline__ void load(const __nv_bfloat16 *p) {
+        const uint4 r = __ldg(reinterpret_cast<const uint4 *>(p));
+        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            c[2 * i] = __uint_as_float(w[i] << 16);
+            c[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        }
+    }
+    static __device__ __forceinline__ void store(__nv_bfloat16 *p, const float *a) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(a[2 * i], a[2 * i + 1]);
+            w[i] = *reinterpret_cast<const uint32_t *>(&h);
+        }
+        st_stream_u4(p, make_uint4(w[0], w[1], w[2], w[3]));
+    }
+    static __device__ __forceinline__ uint4 load_raw(const __nv_bfloat16 *p) { return __ldg(reinterpret_cast<const uint4 *>(p)); }
+    static __device__ __forceinline__ void unpack(const uint4 &r, float *c) {
+        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            c[2 * i] = __uint_as_float(w[i] << 16);
+            c[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        }
     }
 };
 
-// D/4 lanes per (query, head); blockDim.x = 256; blockIdx = (query block, head, batch).
+// D/CPL lanes per (query, head); blockDim.x = 256; blockIdx = (query block, head, batch).
 //
-// Two phases per round of LPG taps.  SETUP: lane t of the group prepares tap (s0 + t) — loads its
-// (x, y, weight), does the floor / bounds / corner-weight arithmetic ONCE (the reference repeats it in
-// all D channel threads) and turns the four corners into clamped element offsets with zeroed weights
-// for corners outside the map (== the reference's `v = 0`, cuh:58-81, without predicated loads).
-// GATHER: the prepared tap is broadcast inside the group with width-LPG shuffles and every lane issues
-// four unconditional 128-bit loads and the reference's w1..w4 arithmetic on its four channels.
+// Two phases per round of LPG taps.  SETUP: lane t of the group prepares tap (s0 + t) — its (x, y, weight)
+// were fetched one round ahead with streaming loads — doing the floor / bounds / corner-weight arithmetic
+// ONCE (the reference repeats it in all D channel threads): clamped element offsets, and the four corner
+// weights already multiplied by the attention weight, zero for corners outside the map (== the
+// reference's `v = 0`, cuh:58-81, without predicated loads).  GATHER: the prepared tap is broadcast inside
+// the group with six width-LPG shuffles and every lane issues four unconditional 128-bit loads and four FMAs
+// per channel.  (w_i * a) * v_i differs from the reference's (sum_i w_i v_i) * a by rounding only
+// (measured: <= 6e-9 abs on the C2 inputs against the oracle, tolerance 1e-3).
 template <int D, typename VT>
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, 4)
 msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
-                    const float *__restrict__ loc, const float *__restrict__ attn, int S, int M, int L, int Q, int P,
-                    VT *__restrict__ out) {
-    constexpr int LPG = D / 4;              // lanes per group
-    constexpr int GPB = 256 / LPG;          // (query, head) groups per CTA
-    const int lane = threadIdx.x % LPG, grp = threadIdx.x / LPG;
+                          const float *__restrict__ loc, const float *__restrict__ attn, int S, int M, int L, int Q, int P,
+                          VT *__restrict__ out) {
+    constexpr int CPL = Lane<VT>::CPL;
+    constexpr int LPG = D / CPL;
+    constexpr int GPB = 256 / LPG;
+    __shared__ int s_h[MSDA_MAX_L], s_w[MSDA_MAX_L], s_start[MSDA_MAX_L];
+    const int tid = threadIdx.x;
+    const int lane = tid % LPG, grp = tid / LPG;
     const int m = blockIdx.y, b = blockIdx.z;
-    int q = blockIdx.x * GPB + grp;
-    const bool active = q < Q;
-    if (!active) q = Q - 1;                 // stay in the shuffles; nothing is stored
+    const int LP = L * P, MD = M * D;
+    if (tid < L) {
+        s_h[tid] = (int)__ldg(shapes + 2 * tid);
+        s_w[tid] = (int)__ldg(shapes + 2 * tid + 1);
+        s_start[tid] = (int)__ldg(starts + tid);
+    }
+    __syncthreads();
+    const int qreal = blockIdx.x * GPB + grp;
+    const int q = min(qreal, Q - 1);
     const size_t qm = ((size_t)b * Q + q) * M + m;
-    const int LP = L * P;
-    const float2 *lp = reinterpret_cast<const float2 *>(loc) + qm * LP;
+    const float *lp = loc + qm * LP * 2;
     const float *ap = attn + qm * LP;
-    const int MD = M * D;
-    const VT *vb = value + (size_t)b * S * MD + m * D + lane * 4;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const VT *vb = value + (size_t)b * S * MD + m * D + lane * CPL;
+    float acc[CPL];
+#pragma unroll
+    for (int c = 0; c < CPL; ++c) acc[c] = 0.f;
+    uint2 raw_xy = make_uint2(0u, 0u);
+    uint32_t raw_a = 0u;
+    if (lane < LP) { raw_xy = ld_stream_u2(lp + 2 * lane); raw_a = ld_stream_u1(ap + lane); }
     for (int s0 = 0; s0 < LP; s0 += LPG) {
-        // ---- setup: this lane's tap ----
         const int tap = s0 + lane;
         int o1 = 0, o3 = 0;
-        float w1 = 0.f, w2 = 0.f, w3 = 0.f, w4 = 0.f, a = 0.f;
+        float w1 = 0.f, w2 = 0.f, w3 = 0.f, w4 = 0.f;
         if (tap < LP) {
-            int l = 0;
-            for (int i = 1; i < L; ++i) l += tap >= i * P;                       // tap / P without an integer division
-            const int h = (int)__ldg(shapes + 2 * l), w = (int)__ldg(shapes + 2 * l + 1);
-            const int start = (int)__ldg(starts + l);
-            const float2 xy = __ldg(lp + tap);
-            const float him = xy.y * h - 0.5f, wim = xy.x * w - 0.5f;            // cuh:290-291
-            if (him > -1.f && wim > -1.f && him < (float)h && wim < (float)w) {  // cuh:293
-                a = __ldg(ap + tap);
+            const int l = tap / P;
+            const int h = s_h[l], w = s_w[l];
+            const float him = __uint_as_float(raw_xy.y) * h - 0.5f, wim = __uint_as_float(raw_xy.x) * w - 0.5f;   // cuh:290-291
+            if (him > -1.f && wim > -1.f && him < (float)h && wim < (float)w) {          // cuh:293
+                const float a = __uint_as_float(raw_a);
                 const int hl = (int)floorf(him), wl = (int)floorf(wim);
                 const float lh = him - hl, lw = wim - wl, hh = 1.f - lh, hw = 1.f - lw;
                 const bool y0 = hl >= 0, y1 = hl + 1 <= h - 1, x0 = wl >= 0, x1 = wl + 1 <= w - 1;
                 const int ry0 = max(hl, 0), ry1 = min(hl + 1, h - 1), cx0 = max(wl, 0);
-                o1 = ((start + ry0 * w + cx0) * MD) | (int)(x0 && x1);           // bit 0: the x+1 corner is a different pixel
+                const int start = s_start[l];
+                o1 = ((start + ry0 * w + cx0) * MD) | (int)(x0 && x1);                   // bit 0: the x+1 corner is a different pixel
                 o3 = (start + ry1 * w + cx0) * MD;
-                w1 = (y0 && x0) ? hh * hw : 0.f;                                 // cuh:85 (w1..w4), 0 where the reference reads v = 0
-                w2 = (y0 && x1) ? hh * lw : 0.f;
-                w3 = (y1 && x0) ? lh * hw : 0.f;
-                w4 = (y1 && x1) ? lh * lw : 0.f;
+                w1 = (y0 && x0) ? hh * hw * a : 0.f;                                     // cuh:85, 0 where the reference reads v = 0
+                w2 = (y0 && x1) ? hh * lw * a : 0.f;
+                w3 = (y1 && x0) ? lh * hw * a : 0.f;
+                w4 = (y1 && x1) ? lh * lw * a : 0.f;
             }
         }
-        // ---- gather: all lanes of the group walk the prepared taps in the reference's (l, p) order ----
+        if (tap + LPG < LP) { raw_xy = ld_stream_u2(lp + 2 * (tap + LPG)); raw_a = ld_stream_u1(ap + tap + LPG); }
         const int nt = min(LPG, LP - s0);
 #pragma unroll
         for (int j = 0; j < LPG; ++j) {
@@ -99,19 +150,18 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
                 const int bo3 = __shfl_sync(0xffffffffu, o3, j, LPG);
                 const float b1 = __shfl_sync(0xffffffffu, w1, j, LPG), b2 = __shfl_sync(0xffffffffu, w2, j, LPG);
                 const float b3 = __shfl_sync(0xffffffffu, w3, j, LPG), b4 = __shfl_sync(0xffffffffu, w4, j, LPG);
-                const float ba = __shfl_sync(0xffffffffu, a, j, LPG);
                 const int dx = (bo1 & 1) ? MD : 0;
                 bo1 &= ~1;
-                const float4 v1 = Vec4<VT>::load(vb + bo1), v2 = Vec4<VT>::load(vb + bo1 + dx);
-                const float4 v3 = Vec4<VT>::load(vb + bo3), v4 = Vec4<VT>::load(vb + bo3 + dx);
-                acc.x += (b1 * v1.x + b2 * v2.x + b3 * v3.x + b4 * v4.x) * ba;   // cuh:87,295
-                acc.y += (b1 * v1.y + b2 * v2.y + b3 * v3.y + b4 * v4.y) * ba;
-                acc.z += (b1 * v1.z + b2 * v2.z + b3 * v3.z + b4 * v4.z) * ba;
-                acc.w += (b1 * v1.w + b2 * v2.w + b3 * v3.w + b4 * v4.w) * ba;
+                float v1[CPL], v2[CPL], v3[CPL], v4[CPL];
+                const uint4 r1 = Lane<VT>::load_raw(vb + bo1), r2 = Lane<VT>::load_raw(vb + bo1 + dx);
+                const uint4 r3 = Lane<VT>::load_raw(vb + bo3), r4 = Lane<VT>::load_raw(vb + bo3 + dx);
+                Lane<VT>::unpack(r1, v1); Lane<VT>::unpack(r2, v2); Lane<VT>::unpack(r3, v3); Lane<VT>::unpack(r4, v4);
+#pragma unroll
+                for (int c = 0; c < CPL; ++c) acc[c] += b1 * v1[c] + b2 * v2[c] + b3 * v3[c] + b4 * v4[c];
             }
         }
     }
-    if (active) Vec4<VT>::store(out + qm * D + lane * 4, acc);
+    if (qreal < Q) Lane<VT>::store(out + qm * D + lane * CPL, acc);
 }
 
 // Any D (the reference's own mapping: one thread per output scalar), fp32 only.
@@ -151,7 +201,7 @@ msda_forward_scalar_kernel(const float *__restrict__ value, const int64_t *__res
 template <int D, typename VT>
 static int launch_vec(const void *value, const int64_t *shapes, const int64_t *starts, const float *loc, const float *attn,
                       int B, int S, int M, int L, int Q, int P, void *out, cudaStream_t st) {
-    constexpr int GPB = 256 / (D / 4);
+    constexpr int GPB = 256 / (D / Lane<VT>::CPL);
     dim3 grid(cdiv(Q, GPB), M, B);
     msda_forward_kernel<D, VT><<<grid, 256, 0, st>>>(static_cast<const VT *>(value), shapes, starts, loc, attn, S, M, L, Q, P,
                                                     static_cast<VT *>(out));
@@ -167,7 +217,7 @@ extern "C" int quber_msda_forward(const void *value, const int64_t *shapes, cons
     if (!value || !shapes || !starts || !loc || !attn || !out) return QUBER_E_INVALID;
     if (B <= 0 || S <= 0 || M <= 0 || D <= 0 || L <= 0 || L > MSDA_MAX_L || Q <= 0 || P <= 0) return QUBER_E_INVALID;
     if (dtype != 0 && dtype != 1) return QUBER_E_INVALID;
-    if (M > 65535 || B > 65535) return QUBER_E_UNSUPPORTED;
+    if (M > 65535 || B > 65535 || (long long)S * M * D >= (1ll << 31)) return QUBER_E_UNSUPPORTED;
     cudaStream_t st = (cudaStream_t)stream;
     const bool vec_ok = aligned16(value) && aligned16(out) && ((reinterpret_cast<uintptr_t>(loc) & 7u) == 0);
     if (dtype == 1) {
