@@ -168,6 +168,26 @@ int quber_msda_forward(const void *value, const int64_t *shapes, const int64_t *
                        const float *attn, int B, int S, int M, int D, int L, int Q, int P, int dtype,
                        void *out, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Dense projections on tcgen05 / TMEM:  C[M,N] = act(A[M,K] * W[N,K]^T + bias[N])
+ *     — the nn.Linear layers of MSDeformAttn (OPS/modules/ms_deform_attn.py:98-124: value_proj,
+ *     sampling_offsets, attention_weights, output_proj), the encoder FFN
+ *     (MSMF/modeling/pixel_decoder/msdeformattn.py:116-131) and, on channels-last activations, the 1x1
+ *     convolutions of FusionLayers / the RGB-D level fusion (maskrefiner/modeling/mask_refiner/model.py:430-452,
+ *     maskrefiner/modeling/backbone/resnet.py:473-485).  In the reference these are cuBLAS / cuDNN calls
+ *     made by PyTorch.
+ *   A     dev [M,K] row-major, row pitch lda elements;  W dev [N,K] row-major (PyTorch Linear weight), pitch ldw
+ *   in_dtype   1: bfloat16 (tcgen05 kind::f16)   2: float32 multiplied as TF32 (kind::tf32)
+ *   bias  dev [N] float32 or NULL;   act  0: none, 1: ReLU
+ *   C     dev [M,N] row-major, pitch ldc;  out_dtype 0: float32, 1: bfloat16.  Accumulation is fp32 in TMEM.
+ *   N % 8 == 0; A, W, C 16-byte aligned with row pitches that are multiples of 16 bytes
+ *   (QUBER_E_UNSUPPORTED / QUBER_E_ALIGN otherwise).  Any M; K needs no padding (TMA zero-fills the tail).
+ * quber_gemm_timeouts: diagnostic like quber_tma_timeouts (pipeline waits that gave up; 0 when healthy).
+ * ------------------------------------------------------------------------------------------- */
+int quber_gemm_bias_act(const void *A, const void *W, const float *bias, void *C, int M, int N, int K, int lda,
+                        int ldw, int ldc, int in_dtype, int out_dtype, int act, void *stream);
+int quber_gemm_timeouts(void);
+
 #ifdef __cplusplus
 }
 #endif

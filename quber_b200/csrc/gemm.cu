@@ -1,0 +1,274 @@
+// Dense projection GEMM on the 5th-generation tensor cores:  C[M,N] = act(A[M,K] * W[N,K]^T + bias[N]).
+//
+// This is the Linear / 1x1-convolution shape of the path: value_proj, sampling_offsets,
+// attention_weights, output_proj of MSDeformAttn (OPS/modules/ms_deform_attn.py:98-124), the encoder FFN
+// (MSMF/modeling/pixel_decoder/msdeformattn.py:116-131), and the 1x1 convolutions of FusionLayers /
+// the RGB-D level fusion in channels-last form (maskrefiner/modeling/mask_refiner/model.py:430-452,
+// maskrefiner/modeling/backbone/resnet.py:473-485).  PyTorch stores a Linear weight as [N,K] row-major,
+// i.e. BOTH operands are K-major — exactly what tcgen05.mma wants from shared memory.
+//
+// Structure (one 128 x BN output tile per CTA, 192 threads, 2-3 CTAs per SM so that one CTA's epilogue
+// overlaps another's main loop — with K = 256 the main loop is only four k-blocks and the GEMM is bound by
+// the HBM traffic of A and C, not by the tensor pipe):
+//   warp 0   one lane: TMA producer — A and W tiles (128B-swizzled, K-major) into a 3-stage ring, mbarrier
+//            complete_tx; rows / columns / k past the matrix edge arrive as zeros (TMA out-of-bounds fill)
+//   warp 1   allocates TMEM (BN fp32 columns x 128 lanes); one lane issues tcgen05.mma (cta_group::1,
+//            kind::f16 for bf16 or kind::tf32 for fp32 inputs, M = 128, N = BN, K = 32 bytes per instruction),
+//            tcgen05.commit frees the smem stage / signals the epilogue
+//   warps 2-5  epilogue: tcgen05.ld (32 lanes x 32 columns per instruction) -> + bias -> activation ->
+//            128-bit global stores (fp32 or bf16)
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace quber {
+
+constexpr int G_BM = 128;
+constexpr int G_STAGES = 3;
+constexpr int G_THREADS = 192;
+constexpr int G_KBYTES = 128;          // bytes of K per stage row = one 128B swizzle atom
+
+__device__ __forceinline__ uint32_t g_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void g_mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(g_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void g_mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(g_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ unsigned int g_gemm_timeouts = 0;
+// false = gave up (a lost TMA / MMA must fail the call, never hang the GPU)
+__device__ __forceinline__ bool g_mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (int spin = 0; !done; ++spin) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(g_smem_u32(bar)), "r"(parity) : "memory");
+        if (spin > (1 << 22)) { atomicAdd(&g_gemm_timeouts, 1u); return false; }
+    }
+    return true;
+}
+__device__ __forceinline__ void g_tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar, int x, int y) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(g_smem_u32(dst)), "l"(map), "r"(g_smem_u32(bar)), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(g_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate, int tf32) {
+    if (tf32)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// K-major operand tile, 128-byte rows, SWIZZLE_128B: 8-row atoms of 1024 bytes (SBO), LBO unused (= 1),
+// descriptor version 1 (Blackwell), layout type 2 (cute/arch/mma_sm100_desc.hpp: SmemDescriptor).
+__device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3fffu);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+template <int BN, bool TF32, typename OT>
+__global__ void __launch_bounds__(G_THREADS)
+gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                     const float *__restrict__ bias, OT *__restrict__ C, int M, int N, int K, int ldc, int act) {
+    extern __shared__ __align__(1024) unsigned char gsm_raw[];
+    // SWIZZLE_128B tiles must sit on 1024-byte boundaries of the SHARED address space
+    unsigned char *gsm = gsm_raw + ((1024u - (g_smem_u32(gsm_raw) & 1023u)) & 1023u);
+    __shared__ __align__(8) uint64_t full[G_STAGES], empty[G_STAGES], tmem_full;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ float bias_s[BN];
+    __shared__ int abort_s;
+    constexpr int A_BYTES = G_BM * G_KBYTES, W_BYTES = BN * G_KBYTES, STAGE = A_BYTES + W_BYTES;
+    constexpr int KELEMS = TF32 ? 32 : 64;              // elements of K per stage
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * G_BM, n0 = blockIdx.y * BN;
+    const int nkb = (K + KELEMS - 1) / KELEMS;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < G_STAGES; ++s) { g_mbar_init(&full[s], 1); g_mbar_init(&empty[s], 1); }
+        g_mbar_init(&tmem_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        abort_s = 0;
+    }
+    for (int i = threadIdx.x; i < BN; i += G_THREADS) bias_s[i] = (bias && n0 + i < N) ? __ldg(bias + n0 + i) : 0.f;
+    if (warp == 1) {                                     // TMEM: BN fp32 accumulator columns
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(g_smem_u32(&tmem_base_s)), "n"(BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_d = tmem_base_s;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % G_STAGES;
+                if (kb >= G_STAGES && !g_mbar_wait(&empty[s], ((kb / G_STAGES) - 1) & 1)) { abort_s = 1; break; }
+                unsigned char *sa = gsm + (size_t)s * STAGE, *sw = sa + A_BYTES;
+                g_mbar_expect_tx(&full[s], STAGE);
+                g_tma_load_2d(sa, &map_a, &full[s], kb * KELEMS, m0);
+                g_tma_load_2d(sw, &map_w, &full[s], kb * KELEMS, n0);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            // instruction descriptor (cute/arch/mma_sm100_desc.hpp: InstrDescriptor): D = F32, A/B = BF16 or TF32,
+            // both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+            const uint32_t fmt = TF32 ? 2u : 1u;
+            const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(G_BM >> 4) << 24);
+            bool ok = true;
+            for (int kb = 0; kb < nkb && ok; ++kb) {
+                const int s = kb % G_STAGES;
+                ok = g_mbar_wait(&full[s], (kb / G_STAGES) & 1);
+                if (!ok) { abort_s = 1; break; }
+                tc_fence_after();
+                const uint32_t sa = g_smem_u32(gsm + (size_t)s * STAGE), sw = sa + A_BYTES;
+                const uint64_t ad = umma_desc_k128(sa), wd = umma_desc_k128(sw);
+#pragma unroll
+                for (int k = 0; k < G_KBYTES / 32; ++k)          // 32 bytes of K per instruction: +2 in the 16-byte address field
+                    tc_mma(tmem_d, ad + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, TF32);
+                tc_commit(&empty[s]);                            // frees the stage when these MMAs have read it
+            }
+            tc_commit(&tmem_full);                               // accumulator complete (or abort: release the epilogue)
+        }
+    } else {
+        // ===== epilogue: warps 2..5 own TMEM lanes 32 * (warp % 4) .. +31 =====
+        const int q = warp & 3;
+        const int row = m0 + 32 * q + lane;
+        const bool ok = g_mbar_wait(&tmem_full, 0);
+        tc_fence_after();
+        if (ok && !abort_s) {
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t r[32];
+                const uint32_t taddr = tmem_d + ((uint32_t)(32 * q) << 16) + (uint32_t)c0;
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                      "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+                      "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+                      "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                    : "r"(taddr));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (row < M) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        float x = __uint_as_float(r[j]) + bias_s[c0 + j];
+                        if (act == 1) x = fmaxf(x, 0.f);
+                        v[j] = x;
+                    }
+                    OT *dst = C + (size_t)row * ldc + n0 + c0;
+                    if constexpr (sizeof(OT) == 4) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            if (n0 + c0 + j < N)                 // N % 8 == 0: a 4-column group is all in or all out
+                                st_stream_f4(reinterpret_cast<float *>(dst) + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8)
+                            if (n0 + c0 + j < N) {
+                                uint32_t w[4];
+#pragma unroll
+                                for (int t = 0; t < 4; ++t) {
+                                    const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * t], v[j + 2 * t + 1]);
+                                    w[t] = *reinterpret_cast<const uint32_t *>(&h);
+                                }
+                                st_stream_u4(reinterpret_cast<__nv_bfloat16 *>(dst) + j, make_uint4(w[0], w[1], w[2], w[3]));
+                            }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(BN) : "memory");
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn gemm_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+// row-major [rows, K] matrix with row pitch `ld` elements, viewed through (128 bytes of K) x box_rows boxes, 128B swizzle
+static bool gemm_map(CUtensorMap *m, const void *base, int rows, int K, int ld, int box_rows, bool tf32) {
+    EncodeTiledFn enc = gemm_encode_fn();
+    if (!enc) return false;
+    const int es = tf32 ? 4 : 2;
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * es};
+    const cuuint32_t box[2] = {(cuuint32_t)(G_KBYTES / es), (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides,
+               box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int BN, bool TF32, typename OT>
+static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const float *bias, void *C, int M, int N, int K, int ldc, int act,
+                       cudaStream_t st) {
+    const size_t smem = (size_t)G_STAGES * (G_BM + BN) * G_KBYTES + 1024;
+    QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_bias_act_kernel<BN, TF32, OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid(cdiv(M, G_BM), cdiv(N, BN));
+    gemm_bias_act_kernel<BN, TF32, OT><<<grid, G_THREADS, smem, st>>>(ma, mw, bias, static_cast<OT *>(C), M, N, K, ldc, act);
+    return check_launch("gemm_bias_act_kernel");
+}
+
+}  // namespace quber
+
+extern "C" int quber_gemm_timeouts(void) {
+    unsigned int n = 0;
+    if (cudaMemcpyFromSymbol(&n, quber::g_gemm_timeouts, sizeof(n)) != cudaSuccess) return -1;
+    return (int)n;
+}
+
+extern "C" int quber_gemm_bias_act(const void *A, const void *W, const float *bias, void *C, int M, int N, int K, int lda, int ldw,
+                                   int ldc, int in_dtype, int out_dtype, int act, void *stream) {
+    using namespace quber;
+    if (!A || !W || !C || M <= 0 || N <= 0 || K <= 0) return QUBER_E_INVALID;
+    if ((in_dtype != 1 && in_dtype != 2) || (out_dtype != 0 && out_dtype != 1) || (act != 0 && act != 1)) return QUBER_E_INVALID;
+    const bool tf32 = in_dtype == 2;
+    const int es = tf32 ? 4 : 2, os = out_dtype == 0 ? 4 : 2;
+    if (lda < K || ldw < K || ldc < N) return QUBER_E_INVALID;
+    if (N % 8 != 0) return QUBER_E_UNSUPPORTED;
+    if (!aligned16(A) || !aligned16(W) || !aligned16(C) || ((size_t)lda * es) % 16 || ((size_t)ldw * es) % 16 || ((size_t)ldc * os) % 16)
+        return QUBER_E_ALIGN;
+    const int BN = (N % 128 == 0 || N > 192) ? 128 : 64;
+    CUtensorMap ma, mw;
+    if (!gemm_map(&ma, A, M, K, lda, G_BM, tf32) || !gemm_map(&mw, W, N, K, ldw, BN, tf32)) {
+        set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
+        return QUBER_E_CUDA;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+#define QG(BN_, TF_, OT_) return gemm_launch<BN_, TF_, OT_>(ma, mw, bias, C, M, N, K, ldc, act, st)
+    if (BN == 128) {
+        if (tf32) { if (out_dtype == 0) QG(128, true, float); else QG(128, true, __nv_bfloat16); }
+        else      { if (out_dtype == 0) QG(128, false, float); else QG(128, false, __nv_bfloat16); }
+    } else {
+        if (tf32) { if (out_dtype == 0) QG(64, true, float); else QG(64, true, __nv_bfloat16); }
+        else      { if (out_dtype == 0) QG(64, false, float); else QG(64, false, __nv_bfloat16); }
+    }
+#undef QG
+}

@@ -192,6 +192,46 @@ def msda_forward(value, spatial_shapes, level_start_index, sampling_locations, a
     return out
 
 
+def gemm_bias_act(a, weight, bias=None, act="none", out_dtype=None):
+    """C = act(a @ weight.T + bias) on tcgen05 / TMEM (quber_gemm_bias_act) — the nn.Linear / 1x1-conv shape.
+
+    a [..., K] and weight [N, K] are both bfloat16 (tcgen05 kind::f16) or both float32 (multiplied as TF32);
+    bias [N] float32 or None; act "none" | "relu"; out_dtype float32 (default for float32 inputs) or bfloat16.
+    The last dimension of `a` must be contiguous; leading dimensions are flattened into rows.
+    """
+    _need_cuda(weight, "weight")
+    if not isinstance(a, torch.Tensor) or not a.is_cuda:
+        raise ValueError("a must be a CUDA tensor")
+    if a.dtype != weight.dtype or a.dtype not in (torch.bfloat16, torch.float32):
+        raise ValueError("a and weight must both be bfloat16 or both float32")
+    K = a.shape[-1]
+    N = weight.shape[0]
+    if weight.dim() != 2 or weight.shape[1] != K:
+        raise ValueError(f"weight must be [N, {K}], got {tuple(weight.shape)}")
+    a2 = a.reshape(-1, K)
+    if a2.stride(1) != 1:
+        a2 = a2.contiguous()
+    M = a2.shape[0]
+    if out_dtype is None:
+        out_dtype = a.dtype
+    if out_dtype not in (torch.float32, torch.bfloat16):
+        raise ValueError("out_dtype must be float32 or bfloat16")
+    if bias is not None:
+        _need_cuda(bias, "bias", torch.float32)
+        if bias.numel() != N:
+            raise ValueError("bias must have N elements")
+    if act not in ("none", "relu"):
+        raise ValueError("act must be 'none' or 'relu'")
+    out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    if M > 0:
+        with torch.cuda.device(a.device):
+            _lib.check(_lib.lib().quber_gemm_bias_act(_ptr(a2), _ptr(weight), _ptr(bias), _ptr(out), M, N, K, a2.stride(0),
+                                                      weight.stride(0), N, 1 if a.dtype == torch.bfloat16 else 2,
+                                                      0 if out_dtype == torch.float32 else 1, 1 if act == "relu" else 0,
+                                                      _stream()), "quber_gemm_bias_act")
+    return out.reshape(tuple(a.shape[:-1]) + (N,))
+
+
 # ---- torch.library registration: torch.ops.quber.* ----------------------------------------------
 def _register():
     try:
