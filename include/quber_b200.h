@@ -180,8 +180,8 @@ int quber_msda_forward(const void *value, const int64_t *shapes, const int64_t *
  *   in_dtype   1: bfloat16 (tcgen05 kind::f16)   2: float32 multiplied as TF32 (kind::tf32)
  *   bias  dev [N] float32 or NULL;   act  0: none, 1: ReLU
  *   C     dev [M,N] row-major, pitch ldc;  out_dtype 0: float32, 1: bfloat16.  Accumulation is fp32 in TMEM.
- *   N % 8 == 0; A, W, C 16-byte aligned with row pitches that are multiples of 16 bytes
- *   (QUBER_E_UNSUPPORTED / QUBER_E_ALIGN otherwise).  Any M; K needs no padding (TMA zero-fills the tail).
+ *   A, W, C 16-byte aligned with row pitches that are multiples of 16 bytes (QUBER_E_ALIGN otherwise).
+ *   Any M, N, K: tiles past a matrix edge are zero-filled on load and clipped on store by TMA.
  * quber_gemm_timeouts: diagnostic like quber_tma_timeouts (pipeline waits that gave up; 0 when healthy).
  * ------------------------------------------------------------------------------------------- */
 int quber_gemm_bias_act(const void *A, const void *W, const float *bias, void *C, int M, int N, int K, int lda,

@@ -16,7 +16,7 @@
 //            kind::f16 for bf16 or kind::tf32 for fp32 inputs, M = 128, N = BN, K = 32 bytes per instruction),
 //            tcgen05.commit frees the smem stage / signals the epilogue
 //   warps 2-5  epilogue: tcgen05.ld (32 lanes x 32 columns per instruction) -> + bias -> activation ->
-//            128-bit global stores (fp32 or bf16)
+//            128B-swizzled staging in the (now dead) pipeline stages -> TMA store of 32-row x 128-byte boxes
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -79,7 +79,7 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
 template <int BN, bool TF32, typename OT>
 __global__ void __launch_bounds__(G_THREADS)
 gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
-                     const float *__restrict__ bias, OT *__restrict__ C, int M, int N, int K, int ldc, int act) {
+                     const __grid_constant__ CUtensorMap map_c, const float *__restrict__ bias, int M, int N, int K, int act) {
     extern __shared__ __align__(1024) unsigned char gsm_raw[];
     // SWIZZLE_128B tiles must sit on 1024-byte boundaries of the SHARED address space
     unsigned char *gsm = gsm_raw + ((1024u - (g_smem_u32(gsm_raw) & 1023u)) & 1023u);
@@ -90,7 +90,7 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     constexpr int A_BYTES = G_BM * G_KBYTES, W_BYTES = BN * G_KBYTES, STAGE = A_BYTES + W_BYTES;
     constexpr int KELEMS = TF32 ? 32 : 64;              // elements of K per stage
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * G_BM, n0 = blockIdx.y * BN;
+    const int m0 = blockIdx.y * G_BM, n0 = blockIdx.x * BN;   // N tiles fastest: neighbours share the A tile in L2
     const int nkb = (K + KELEMS - 1) / KELEMS;
 
     if (threadIdx.x == 0) {
@@ -145,53 +145,72 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         }
     } else {
         // ===== epilogue: warps 2..5 own TMEM lanes 32 * (warp % 4) .. +31 =====
+        // Each warp stages its 32 rows x 128 bytes of output per chunk in shared memory (the pipeline stages are
+        // dead once tmem_full has fired), 128B-swizzled so that the 32 row-owning lanes hit distinct banks, and
+        // hands it to a TMA store: full 128-byte row segments leave the SM, rows / columns past the matrix
+        // edge are clipped by the hardware.  Two staging buffers per warp: the store of chunk c overlaps the
+        // TMEM read of chunk c + 1.
         const int q = warp & 3;
-        const int row = m0 + 32 * q + lane;
         const bool ok = g_mbar_wait(&tmem_full, 0);
         tc_fence_after();
         if (ok && !abort_s) {
+            constexpr int CW = 128 / (int)sizeof(OT);            // output columns per 128-byte chunk: 32 fp32 / 64 bf16
+            unsigned char *stg = gsm + (size_t)(warp - 2) * 2 * 4096;
+            const uint32_t sw = (uint32_t)(lane & 7);            // swizzle phase of this lane's staging row
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 32) {
-                uint32_t r[32];
-                const uint32_t taddr = tmem_d + ((uint32_t)(32 * q) << 16) + (uint32_t)c0;
-                asm volatile(
-                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                    : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-                      "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-                      "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-                      "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-                    : "r"(taddr));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (row < M) {
+            for (int c0 = 0, ci = 0; c0 < BN; c0 += CW, ++ci) {
+                unsigned char *buf = stg + (ci & 1) * 4096;
+                if (ci >= 2) {
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    __syncwarp();
+                }
+                unsigned char *myrow = buf + lane * 128;
+#pragma unroll
+                for (int h = 0; h < CW / 32; ++h) {
+                    uint32_t r[32];
+                    const uint32_t taddr = tmem_d + ((uint32_t)(32 * q) << 16) + (uint32_t)(c0 + 32 * h);
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+                          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+                          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                        : "r"(taddr));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        float x = __uint_as_float(r[j]) + bias_s[c0 + j];
+                        float x = __uint_as_float(r[j]) + bias_s[c0 + 32 * h + j];
                         if (act == 1) x = fmaxf(x, 0.f);
                         v[j] = x;
                     }
-                    OT *dst = C + (size_t)row * ldc + n0 + c0;
                     if constexpr (sizeof(OT) == 4) {
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4)
-                            if (n0 + c0 + j < N)                 // N % 8 == 0: a 4-column group is all in or all out
-                                st_stream_f4(reinterpret_cast<float *>(dst) + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
+                        for (int j = 0; j < 8; ++j)              // 16-byte chunk j of the row lands at chunk j ^ (row & 7)
+                            *reinterpret_cast<float4 *>(myrow + ((((uint32_t)j) ^ sw) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                     } else {
 #pragma unroll
-                        for (int j = 0; j < 32; j += 8)
-                            if (n0 + c0 + j < N) {
-                                uint32_t w[4];
+                        for (int j = 0; j < 4; ++j) {
+                            uint32_t w[4];
 #pragma unroll
-                                for (int t = 0; t < 4; ++t) {
-                                    const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * t], v[j + 2 * t + 1]);
-                                    w[t] = *reinterpret_cast<const uint32_t *>(&h);
-                                }
-                                st_stream_u4(reinterpret_cast<__nv_bfloat16 *>(dst) + j, make_uint4(w[0], w[1], w[2], w[3]));
+                            for (int t = 0; t < 4; ++t) {
+                                const __nv_bfloat162 hh = __floats2bfloat162_rn(v[8 * j + 2 * t], v[8 * j + 2 * t + 1]);
+                                w[t] = *reinterpret_cast<const uint32_t *>(&hh);
                             }
+                            *reinterpret_cast<uint4 *>(myrow + ((((uint32_t)(4 * h + j)) ^ sw) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                        }
                     }
                 }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0 && n0 + c0 < N) {
+                    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+                                 ::"l"(&map_c), "r"(g_smem_u32(buf)), "r"(n0 + c0), "r"(m0 + 32 * q) : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
             }
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // smem must outlive the stores that read it
         }
     }
     tc_fence_before();
@@ -213,26 +232,26 @@ static EncodeTiledFn gemm_encode_fn() {
     return fn;
 }
 // row-major [rows, K] matrix with row pitch `ld` elements, viewed through (128 bytes of K) x box_rows boxes, 128B swizzle
-static bool gemm_map(CUtensorMap *m, const void *base, int rows, int K, int ld, int box_rows, bool tf32) {
+static bool gemm_map(CUtensorMap *m, const void *base, int rows, int K, int ld, int box_rows, int es) {
     EncodeTiledFn enc = gemm_encode_fn();
     if (!enc) return false;
-    const int es = tf32 ? 4 : 2;
     const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
     const cuuint64_t strides[1] = {(cuuint64_t)ld * es};
     const cuuint32_t box[2] = {(cuuint32_t)(G_KBYTES / es), (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    return enc(m, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides,
+    return enc(m, es == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides,
                box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 template <int BN, bool TF32, typename OT>
-static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const float *bias, void *C, int M, int N, int K, int ldc, int act,
-                       cudaStream_t st) {
+static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUtensorMap &mc, const float *bias, int M, int N, int K,
+                       int act, cudaStream_t st) {
     const size_t smem = (size_t)G_STAGES * (G_BM + BN) * G_KBYTES + 1024;
     QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_bias_act_kernel<BN, TF32, OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid(cdiv(M, G_BM), cdiv(N, BN));
-    gemm_bias_act_kernel<BN, TF32, OT><<<grid, G_THREADS, smem, st>>>(ma, mw, bias, static_cast<OT *>(C), M, N, K, ldc, act);
+    if (cdiv(M, G_BM) > 65535) return QUBER_E_UNSUPPORTED;
+    dim3 grid(cdiv(N, BN), cdiv(M, G_BM));
+    gemm_bias_act_kernel<BN, TF32, OT><<<grid, G_THREADS, smem, st>>>(ma, mw, mc, bias, M, N, K, act);
     return check_launch("gemm_bias_act_kernel");
 }
 
@@ -252,17 +271,16 @@ extern "C" int quber_gemm_bias_act(const void *A, const void *W, const float *bi
     const bool tf32 = in_dtype == 2;
     const int es = tf32 ? 4 : 2, os = out_dtype == 0 ? 4 : 2;
     if (lda < K || ldw < K || ldc < N) return QUBER_E_INVALID;
-    if (N % 8 != 0) return QUBER_E_UNSUPPORTED;
     if (!aligned16(A) || !aligned16(W) || !aligned16(C) || ((size_t)lda * es) % 16 || ((size_t)ldw * es) % 16 || ((size_t)ldc * os) % 16)
         return QUBER_E_ALIGN;
     const int BN = (N % 128 == 0 || N > 192) ? 128 : 64;
-    CUtensorMap ma, mw;
-    if (!gemm_map(&ma, A, M, K, lda, G_BM, tf32) || !gemm_map(&mw, W, N, K, ldw, BN, tf32)) {
+    CUtensorMap ma, mw, mc;                 // C: 128-byte x 32-row boxes, one per epilogue warp and chunk
+    if (!gemm_map(&ma, A, M, K, lda, G_BM, es) || !gemm_map(&mw, W, N, K, ldw, BN, es) || !gemm_map(&mc, C, M, N, ldc, 32, os)) {
         set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
         return QUBER_E_CUDA;
     }
     cudaStream_t st = (cudaStream_t)stream;
-#define QG(BN_, TF_, OT_) return gemm_launch<BN_, TF_, OT_>(ma, mw, bias, C, M, N, K, ldc, act, st)
+#define QG(BN_, TF_, OT_) return gemm_launch<BN_, TF_, OT_>(ma, mw, mc, bias, M, N, K, act, st)
     if (BN == 128) {
         if (tf32) { if (out_dtype == 0) QG(128, true, float); else QG(128, true, __nv_bfloat16); }
         else      { if (out_dtype == 0) QG(128, false, float); else QG(128, false, __nv_bfloat16); }

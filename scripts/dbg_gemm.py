@@ -7,7 +7,7 @@ torch.manual_seed(0)
 def tf32(x):
     return (x.view(torch.int32) & ~0x1fff).view(torch.float32)
 cases = [(128, 128, 64), (128, 64, 64), (256, 128, 256), (300, 256, 256), (1000, 192, 256), (1000, 96, 256), (515, 1024, 256),
-         (515, 256, 1024), (201600, 256, 256), (77, 40, 168)]
+         (515, 256, 1024), (201600, 256, 256), (77, 40, 168), (1000, 4, 32), (333, 100, 72)]
 for dt in ("bf16", "tf32"):
     for (M, N, K) in cases:
         a = torch.randn(M, K, device="cuda"); w = torch.randn(N, K, device="cuda") / K ** 0.5; b = torch.randn(N, device="cuda")
@@ -17,9 +17,11 @@ for dt in ("bf16", "tf32"):
             a, w = tf32(a), tf32(w)
         ref = torch.relu(a.double() @ w.double().T + b.double()).float()
         out = ops.gemm_bias_act(a, w, b, act="relu", out_dtype=torch.float32)
+        ob = ops.gemm_bias_act(a, w, b, act="relu", out_dtype=torch.bfloat16) if N % 8 == 0 else None
         torch.cuda.synchronize()
         err = (out - ref).abs().max().item()
-        print(dt, (M, N, K), "max abs err", f"{err:.3e}", "timeouts", _lib.lib().quber_gemm_timeouts(), flush=True)
+        errb = (ob.float() - ref).abs().max().item() if ob is not None else -1
+        print(dt, (M, N, K), "max abs err", f"{err:.3e}", f"bf16 out {errb:.3e}", "timeouts", _lib.lib().quber_gemm_timeouts(), flush=True)
 # timing at the MSDA value_proj shape
 for dt in ("bf16", "tf32"):
     M, N, K = 201600, 256, 256

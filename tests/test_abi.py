@@ -69,6 +69,11 @@ def test_argument_validation_without_gpu():
     assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 24, 8, ctypes.c_void_p(16), None, None, None) == _lib.E_ALIGN
     assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 16, 0, ctypes.c_void_p(16), None, None, None) == _lib.E_INVALID
     assert L.quber_msda_forward(None, None, None, None, None, 1, 1, 1, 1, 1, 1, 1, 0, None, None) == _lib.E_INVALID
+    v16 = ctypes.c_void_p(16)
+    assert L.quber_gemm_bias_act(None, v16, None, v16, 128, 128, 64, 64, 64, 128, 1, 0, 0, None) == _lib.E_INVALID
+    assert L.quber_gemm_bias_act(v16, v16, None, v16, 128, 128, 64, 64, 64, 128, 3, 0, 0, None) == _lib.E_INVALID     # dtype
+    assert L.quber_gemm_bias_act(v16, v16, None, v16, 128, 128, 64, 32, 64, 128, 1, 0, 0, None) == _lib.E_INVALID     # lda < K
+    assert L.quber_gemm_bias_act(v16, v16, None, v16, 128, 128, 60, 60, 60, 128, 1, 0, 0, None) == _lib.E_ALIGN       # 120-byte pitch
     p = _lib.PostParams(1, 480, 640, 4, 4.0, 4, 0.3, 8, 200, 512, 2048, 1000, -1.0, 8, 0)    # even nms kernel
     assert L.quber_post_workspace_bytes(ctypes.byref(p)) == 0
     p.nms_kernel = 7

@@ -399,3 +399,50 @@ def test_msda_full_size_linearity_and_oracle_sample():
     assert float((outc[inner] - 0.5).abs().max()) < 1e-5
     ref = oracle.msda_forward(inp["value"][:1], inp["shapes"], inp["starts"], inp["loc"][:1, :500], inp["attn"][:1, :500])
     np.testing.assert_allclose(out[:1, :500].cpu().numpy(), ref, rtol=0, atol=1e-7)
+
+
+# ------------------------------------------------------------------ tcgen05 GEMM (Linear / 1x1 conv)
+def _tf32(x):
+    return (x.view(torch.int32) & ~0x1FFF).view(torch.float32)
+
+
+@pytest.mark.parametrize("shape", [(128, 128, 64), (300, 256, 256), (1000, 192, 256), (1000, 96, 256), (515, 1024, 256),
+                                   (515, 256, 1024), (77, 40, 168), (1000, 4, 32), (333, 100, 72), (6300, 256, 256)])
+@pytest.mark.parametrize("dt", ["bf16", "tf32"])
+def test_gemm_bias_act_matches_fp64_reference(shape, dt):
+    """C = relu(A W^T + b) against a float64 torch reference on inputs that are exactly representable in the
+    multiply precision (bf16, or fp32 with a 10-bit mantissa for TF32), so that only the fp32 accumulation
+    order differs: tolerance 1e-4 relative to the row scale (measured <= 2e-5)."""
+    from quber_b200 import _lib
+    M, N, K = shape
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(M, K, device=DEV, generator=g)
+    w = torch.randn(N, K, device=DEV, generator=g) / K ** 0.5
+    b = torch.randn(N, device=DEV, generator=g)
+    a, w = (a.bfloat16(), w.bfloat16()) if dt == "bf16" else (_tf32(a), _tf32(w))
+    ref = torch.relu(a.double() @ w.double().T + b.double())
+    out = ops.gemm_bias_act(a, w, b, act="relu", out_dtype=torch.float32)
+    assert out.shape == (M, N) and out.dtype == torch.float32
+    torch.testing.assert_close(out.double(), ref, rtol=0, atol=1e-4)
+    lin = ops.gemm_bias_act(a, w, None, act="none", out_dtype=torch.float32)
+    torch.testing.assert_close(lin.double(), a.double() @ w.double().T, rtol=0, atol=1e-4)
+    if N % 8 == 0:
+        ob = ops.gemm_bias_act(a, w, b, act="relu", out_dtype=torch.bfloat16)
+        torch.testing.assert_close(ob.double(), ref, rtol=2 ** -7, atol=1e-3)       # bf16 output rounding
+    assert _lib.lib().quber_gemm_timeouts() == 0
+
+
+def test_gemm_leading_dims_and_general_fp32_inputs():
+    """[B,S,K] activations (flattened rows), and arbitrary fp32 inputs multiplied as TF32: error bounded by the
+    10-bit mantissa (|err| <= 2^-10 * sum |a||w| per element)."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(3, 700, 256, device=DEV, generator=g)
+    w = torch.randn(192, 256, device=DEV, generator=g) / 16
+    b = torch.randn(192, device=DEV, generator=g)
+    y = ops.gemm_bias_act(x, w, b)
+    assert y.shape == (3, 700, 192)
+    ref = x.double() @ w.double().T + b.double()
+    bound = (x.abs().double() @ w.abs().double().T) * 2.0 ** -10
+    assert ((y.double() - ref).abs() <= bound + 1e-5).all()
+    with pytest.raises(ValueError):
+        ops.gemm_bias_act(x, w.bfloat16(), b)
