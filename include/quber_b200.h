@@ -169,6 +169,27 @@ int quber_msda_forward(const void *value, const int64_t *shapes, const int64_t *
                        void *out, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Network glue that is pure bandwidth (csrc/fusion.cu).
+ * quber_pack_input — replaces the input stage of MaskRefiner.forward
+ *     (maskrefiner/modeling/mask_refiner/model.py:137-153): (uint8 image - PIXEL_MEAN) / PIXEL_STD and the
+ *     channel concat with the encoded initial-mask offsets.
+ *   image dev [B,C,H,W] uint8; offsets dev [B,CO,H,W] float32 (NULL iff CO == 0); mean, stdv dev [C] float32
+ *   out dev [B,C+CO,H,W] float32.  H*W % 16 == 0, 16-byte aligned pointers.  Bit-exact with torch.
+ * quber_fuse_concat — replaces the softmax / sigmoid / torch.cat chain in front of a hierarchy stage
+ *     (model.py:745-759).  sources[i] dev [B,channels[i],h,w] float32, ops[i] 0: copy, 1: sigmoid,
+ *     2: softmax over that source's channels (<= QUBER_FUSE_MAX_SOFTMAX); host arrays of n_sources entries.
+ *   layout 0: out dev [B,sum(channels),h,w] float32 (what torch.cat returns)
+ *   layout 1 / 2: out dev [B*h*w, pitch] float32 / bfloat16 channels-last rows, columns >= sum(channels)
+ *     zero-filled — the A operand of quber_gemm_bias_act for the 1x1 convolution that follows (model.py:430-440)
+ * ------------------------------------------------------------------------------------------- */
+#define QUBER_FUSE_MAX_SOURCES 12
+#define QUBER_FUSE_MAX_SOFTMAX 8
+int quber_pack_input(const uint8_t *image, const float *offsets, const float *mean, const float *stdv, int B, int C,
+                     int CO, int H, int W, float *out, void *stream);
+int quber_fuse_concat(const float *const *sources, const int *channels, const int *ops, int n_sources, int B, int h,
+                      int w, int layout, int pitch, void *out, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Dense projections on tcgen05 / TMEM:  C[M,N] = act(A[M,K] * W[N,K]^T + bias[N])
  *     — the nn.Linear layers of MSDeformAttn (OPS/modules/ms_deform_attn.py:98-124: value_proj,
  *     sampling_offsets, attention_weights, output_proj), the encoder FFN

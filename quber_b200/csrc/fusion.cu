@@ -1,0 +1,172 @@
+// Elementwise glue of the network that is pure HBM bandwidth, fused into single passes:
+//
+//  quber_pack_input   — MaskRefiner.forward's input stage (maskrefiner/modeling/mask_refiner/model.py:137-153):
+//                       uint8 image -> float, (x - PIXEL_MEAN) / PIXEL_STD, channel-concat with the encoded
+//                       initial-mask offsets.  Three torch kernels + a cat in the reference; one pass here.
+//  quber_fuse_concat  — the "error-guided fusion" input of every hierarchy stage
+//                       (model.py:745-759): y' = cat(y, head features of the previous stage...,
+//                       softmax(eee logits) | sigmoid(other logits)...) along channels.  The reference
+//                       materialises every softmax / sigmoid and re-copies the growing tensor once per torch.cat
+//                       (about 2 x n_sources x the final size in traffic); here every source plane is read once
+//                       and the result written once, either as NCHW fp32 (drop-in for the torch.cat result) or
+//                       as channels-last rows [B*h*w, pitch] in fp32 / bf16, which is the A operand of
+//                       quber_gemm_bias_act for the 1x1 convolution that follows (model.py:430-440).
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace quber {
+
+// ---------------------------------------------------------------------------------------------- pack_input
+__global__ void __launch_bounds__(256)
+pack_input_kernel(const uint8_t *__restrict__ image, const float *__restrict__ offsets, const float *__restrict__ mean,
+                  const float *__restrict__ stdv, int C, int CO, size_t HW, float *__restrict__ out) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const size_t i = ((size_t)blockIdx.x * 256 + threadIdx.x) * 16;
+    if (i >= HW) return;
+    float *o = out + ((size_t)b * (C + CO) + c) * HW + i;
+    if (c < C) {
+        const float m = __ldg(mean + c), s = __ldg(stdv + c);
+        const uint4 v = ld_stream_u4(image + ((size_t)b * C + c) * HW + i);     // 16 pixels
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float4 r;
+            r.x = __fdiv_rn(__fsub_rn((float)(w[k] & 0xffu), m), s);
+            r.y = __fdiv_rn(__fsub_rn((float)((w[k] >> 8) & 0xffu), m), s);
+            r.z = __fdiv_rn(__fsub_rn((float)((w[k] >> 16) & 0xffu), m), s);
+            r.w = __fdiv_rn(__fsub_rn((float)(w[k] >> 24), m), s);
+            st_stream_f4(o + 4 * k, r);
+        }
+    } else {
+        const float *src = offsets + ((size_t)b * CO + (c - C)) * HW + i;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint4 v = ld_stream_u4(src + 4 * k);
+            st_stream_u4(o + 4 * k, v);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- fuse_concat
+constexpr int F_PIX = 64;            // pixels per CTA
+constexpr int F_THREADS = 256;
+
+struct FuseArgs {
+    const float *src[QUBER_FUSE_MAX_SOURCES];
+    int channels[QUBER_FUSE_MAX_SOURCES];
+    int op[QUBER_FUSE_MAX_SOURCES];
+    int n;
+};
+
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
+
+// layout 0: NCHW fp32;  1: channels-last fp32 rows;  2: channels-last bf16 rows (pitch elements per pixel, zero padded)
+template <int LAYOUT>
+__global__ void __launch_bounds__(F_THREADS)
+fuse_concat_kernel(FuseArgs a, int ctot, int pitch, size_t hw, void *__restrict__ out) {
+    extern __shared__ float tile[];                      // [F_PIX][pitch + 1] for the channels-last layouts
+    const int b = blockIdx.y;
+    const size_t p0 = (size_t)blockIdx.x * F_PIX;
+    const int p = threadIdx.x & (F_PIX - 1), cs = threadIdx.x / F_PIX;   // 4 channel lanes x 64 pixels
+    const bool inb = p0 + p < hw;
+    const int tp = pitch + 1;
+    int coff = 0;
+    for (int s = 0; s < a.n; ++s) {
+        const int C = a.channels[s];
+        const float *src = a.src[s] + (size_t)b * C * hw + p0 + p;
+        if (a.op[s] == 2) {
+            // softmax over the source's channels (model.py:756, eee logits: 2..4 channels), one pixel per thread
+            if (cs == 0) {
+                float v[QUBER_FUSE_MAX_SOFTMAX];
+                float mx = -INFINITY;
+#pragma unroll
+                for (int c = 0; c < QUBER_FUSE_MAX_SOFTMAX; ++c)
+                    if (c < C) { v[c] = inb ? __ldg(src + (size_t)c * hw) : 0.f; mx = fmaxf(mx, v[c]); }
+                float sum = 0.f;
+#pragma unroll
+                for (int c = 0; c < QUBER_FUSE_MAX_SOFTMAX; ++c)
+                    if (c < C) { v[c] = __expf(v[c] - mx); sum += v[c]; }
+                const float inv = 1.0f / sum;
+#pragma unroll
+                for (int c = 0; c < QUBER_FUSE_MAX_SOFTMAX; ++c)
+                    if (c < C) {
+                        const float r = v[c] * inv;
+                        if (LAYOUT == 0) { if (inb) static_cast<float *>(out)[((size_t)b * ctot + coff + c) * hw + p0 + p] = r; }
+                        else tile[p * tp + coff + c] = r;
+                    }
+            }
+        } else {
+            const bool sg = a.op[s] == 1;
+            for (int c = cs; c < C; c += F_THREADS / F_PIX) {
+                float r = inb ? __ldg(src + (size_t)c * hw) : 0.f;
+                if (sg) r = sigmoid_f(r);
+                if (LAYOUT == 0) { if (inb) static_cast<float *>(out)[((size_t)b * ctot + coff + c) * hw + p0 + p] = r; }
+                else tile[p * tp + coff + c] = r;
+            }
+        }
+        coff += C;
+    }
+    if (LAYOUT == 0) return;
+    for (int c = ctot + cs; c < pitch; c += F_THREADS / F_PIX) tile[p * tp + c] = 0.f;     // K padding for the GEMM
+    __syncthreads();
+    // the CTA's F_PIX rows are one contiguous block of F_PIX * pitch elements
+    const size_t row0 = (size_t)b * hw + p0;
+    const int nrow = (int)min((size_t)F_PIX, hw - p0);
+    for (int i = threadIdx.x; i < nrow * pitch; i += F_THREADS) {
+        const int r = i / pitch, c = i - r * pitch;
+        const float v = tile[r * tp + c];
+        if (LAYOUT == 1) static_cast<float *>(out)[row0 * pitch + i] = v;
+        else static_cast<__nv_bfloat16 *>(out)[row0 * pitch + i] = __float2bfloat16_rn(v);
+    }
+}
+
+}  // namespace quber
+
+extern "C" int quber_pack_input(const uint8_t *image, const float *offsets, const float *mean, const float *stdv, int B, int C,
+                                int CO, int H, int W, float *out, void *stream) {
+    using namespace quber;
+    if (!image || !mean || !stdv || !out || B <= 0 || C <= 0 || CO < 0 || H <= 0 || W <= 0) return QUBER_E_INVALID;
+    if (CO > 0 && !offsets) return QUBER_E_INVALID;
+    const size_t HW = (size_t)H * W;
+    if (HW % 16 != 0) return QUBER_E_UNSUPPORTED;
+    if (!aligned16(image) || !aligned16(out) || (offsets && !aligned16(offsets))) return QUBER_E_ALIGN;
+    if (B > 65535 || C + CO > 65535) return QUBER_E_UNSUPPORTED;
+    dim3 grid((unsigned)((HW / 16 + 255) / 256), C + CO, B);
+    pack_input_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(image, offsets, mean, stdv, C, CO, HW, out);
+    return check_launch("pack_input_kernel");
+}
+
+extern "C" int quber_fuse_concat(const float *const *sources, const int *channels, const int *ops, int n_sources, int B, int h,
+                                 int w, int layout, int pitch, void *out, void *stream) {
+    using namespace quber;
+    if (!sources || !channels || !ops || !out || n_sources <= 0 || n_sources > QUBER_FUSE_MAX_SOURCES || B <= 0 || h <= 0 || w <= 0)
+        return QUBER_E_INVALID;
+    if (layout < 0 || layout > 2) return QUBER_E_INVALID;
+    FuseArgs a;
+    a.n = n_sources;
+    int ctot = 0;
+    for (int s = 0; s < n_sources; ++s) {
+        if (!sources[s] || channels[s] <= 0 || ops[s] < 0 || ops[s] > 2) return QUBER_E_INVALID;
+        if (ops[s] == 2 && channels[s] > QUBER_FUSE_MAX_SOFTMAX) return QUBER_E_UNSUPPORTED;
+        a.src[s] = sources[s]; a.channels[s] = channels[s]; a.op[s] = ops[s];
+        ctot += channels[s];
+    }
+    if (layout == 0) pitch = ctot;
+    if (pitch < ctot) return QUBER_E_INVALID;
+    if (B > 65535) return QUBER_E_UNSUPPORTED;
+    const size_t hw = (size_t)h * w;
+    dim3 grid((unsigned)((hw + F_PIX - 1) / F_PIX), B);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t smem = layout == 0 ? 0 : (size_t)F_PIX * (pitch + 1) * sizeof(float);
+    if (layout == 0) {
+        fuse_concat_kernel<0><<<grid, F_THREADS, 0, st>>>(a, ctot, pitch, hw, out);
+    } else if (layout == 1) {
+        if (smem > 48 * 1024) QUBER_CUDA_TRY(cudaFuncSetAttribute(fuse_concat_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        fuse_concat_kernel<1><<<grid, F_THREADS, smem, st>>>(a, ctot, pitch, hw, out);
+    } else {
+        if (smem > 48 * 1024) QUBER_CUDA_TRY(cudaFuncSetAttribute(fuse_concat_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        fuse_concat_kernel<2><<<grid, F_THREADS, smem, st>>>(a, ctot, pitch, hw, out);
+    }
+    return check_launch("fuse_concat_kernel");
+}

@@ -1,0 +1,219 @@
+"""`MaskRefiner` meta-architecture — drop-in for maskrefiner/modeling/mask_refiner/model.py:74-358 (inference).
+
+Same constructor argument (a cfg with the reference's keys), same `forward(batched_inputs) -> list[dict]`
+contract and output keys ("sem_seg", "eee_boundary" / "eee_mask" when enabled, "panoptic_seg", and
+"instances" only when an instance survives — callers test `"instances" not in output`,
+eval/refiner_model.py:267).  What differs is what runs behind it:
+
+  reference                                               here
+  ------------------------------------------------------  ---------------------------------------------------
+  per image: .to(device), (x-mean)/std, ImageList, cat    ops.pack_input: one kernel for the whole batch (A2)
+  backbone / decoder / heads (cuDNN)                      network.py (cuDNN) + ops.fuse_concat / gemm_bias_act (A3-A5)
+  5 x F.interpolate(x4), sem_seg_postprocess, sigmoid,    ops.post_process: ONE launch sequence for the batch, no host
+  find_instance_center, group_pixels, merge, per-label    round trip (A6-A12); up-sampling is recomputed where it is
+  Python loop with .item() syncs, D2H of the map          consumed
+"""
+import torch
+from torch import nn
+
+from . import network, ops
+from .config import UOAIS_SIM_META
+
+
+class Boxes:
+    """detectron2.structures.Boxes, as far as consumers of `pred_boxes` use it."""
+
+    def __init__(self, tensor):
+        self.tensor = tensor
+
+    def __len__(self):
+        return self.tensor.shape[0]
+
+    def to(self, *a, **k):
+        return Boxes(self.tensor.to(*a, **k))
+
+
+class Instances:
+    """detectron2.structures.Instances, as far as the path's callers use it (attribute bag keyed by image size;
+    consumers read `.pred_masks`, eval/refiner_model.py:270-271)."""
+
+    def __init__(self, image_size, **fields):
+        self._image_size = image_size
+        self._fields = dict(fields)
+
+    @property
+    def image_size(self):
+        return self._image_size
+
+    def __getattr__(self, name):
+        f = self.__dict__.get("_fields", {})
+        if name in f:
+            return f[name]
+        raise AttributeError("Cannot find field '{}' in the given Instances!".format(name))
+
+    def __setattr__(self, name, val):
+        if name.startswith("_"):
+            super().__setattr__(name, val)
+        else:
+            self._fields[name] = val
+
+    def has(self, name):
+        return name in self._fields
+
+    def get_fields(self):
+        return self._fields
+
+    def __len__(self):
+        for v in self._fields.values():
+            return len(v)
+        raise NotImplementedError("Empty Instances does not support __len__!")
+
+    def to(self, *a, **k):
+        return Instances(self._image_size, **{n: (v.to(*a, **k) if hasattr(v, "to") else v) for n, v in self._fields.items()})
+
+
+class MaskRefiner(nn.Module):
+    def __init__(self, cfg, precision="fp32"):
+        """precision "fp32": every convolution / GEMM in fp32 (parity mode, config C2);
+        "bf16": channels-last bf16 autocast for the cuDNN part and tcgen05 bf16 GEMMs for the 1x1 of FusionLayers (C3)."""
+        super().__init__()
+        self.backbone = network.BACKBONE_REGISTRY[cfg.MODEL.BACKBONE.NAME](cfg, None)
+        shapes = {k: (self.backbone._out_feature_channels[k], self.backbone._out_feature_strides[k])
+                  for k in self.backbone._out_features}
+        self.offset_input_on = cfg.INPUT.OFFSET_INPUT_ON
+        self.depth_on = cfg.INPUT.DEPTH_ON
+        self.ins_embed_head = network.INS_EMBED_BRANCHES_REGISTRY[cfg.MODEL.INS_EMBED_HEAD.NAME](cfg, shapes)
+        self.register_buffer("pixel_mean", torch.tensor(cfg.MODEL.PIXEL_MEAN, dtype=torch.float32).view(-1, 1, 1), False)
+        self.register_buffer("pixel_std", torch.tensor(cfg.MODEL.PIXEL_STD, dtype=torch.float32).view(-1, 1, 1), False)
+        self.meta = UOAIS_SIM_META
+        p = cfg.MODEL.PANOPTIC_DEEPLAB
+        self.stuff_area, self.threshold, self.nms_kernel, self.top_k = p.STUFF_AREA, p.CENTER_THRESHOLD, p.NMS_KERNEL, p.TOP_K_INSTANCE
+        self.predict_instances = p.PREDICT_INSTANCES
+        self.size_divisibility = p.SIZE_DIVISIBILITY
+        self.benchmark_network_speed = p.BENCHMARK_NETWORK_SPEED
+        self.eee_mask_on = cfg.MODEL.INS_EMBED_HEAD.EEE_MASK_ON
+        self.eee_boundary_on = cfg.MODEL.INS_EMBED_HEAD.EEE_BOUNDARY_ON
+        self.error_type = cfg.MODEL.INS_EMBED_HEAD.ERROR_TYPE
+        self.common_stride = cfg.MODEL.INS_EMBED_HEAD.COMMON_STRIDE
+        self.max_instances_per_image = 64
+        self.set_precision(precision)
+
+    def set_precision(self, precision):
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
+        self.precision = precision
+        self.ins_embed_head.use_kernels = True
+        self.ins_embed_head.gemm_1x1 = precision == "bf16"
+
+    @property
+    def device(self):
+        return self.pixel_mean.device
+
+    # ---- A2: batch assembly --------------------------------------------------------------------------
+    def _pack(self, batched_inputs):
+        imgs = [x["image"] for x in batched_inputs]
+        sizes = [tuple(i.shape[-2:]) for i in imgs]
+        div = self.size_divisibility if self.size_divisibility > 0 else getattr(self.backbone, "size_divisibility", 0)
+        Hm, Wm = max(s[0] for s in sizes), max(s[1] for s in sizes)
+        if div > 1:
+            Hm, Wm = (Hm + div - 1) // div * div, (Wm + div - 1) // div * div
+        same = all(s == (Hm, Wm) for s in sizes)
+        dev = self.device
+        offs = [x["initial_pred_offset"] for x in batched_inputs] if self.offset_input_on else None
+        if dev.type == "cuda" and same and all(i.dtype == torch.uint8 for i in imgs) and (Hm * Wm) % 16 == 0:
+            image = torch.stack([i.to(dev, non_blocking=True) for i in imgs]).contiguous()
+            off = torch.stack([o.to(dev, non_blocking=True) for o in offs]).float().contiguous() if offs is not None else None
+            return ops.pack_input(image, off, self.pixel_mean, self.pixel_std), sizes
+        # ImageList.from_tensors semantics (pad right / bottom with 0 AFTER normalisation), model.py:137-153
+        out = []
+        for n, i in enumerate(imgs):
+            t = (i.to(dev) - self.pixel_mean) / self.pixel_std
+            if offs is not None:
+                t = torch.cat([t, offs[n].to(dev).float()], dim=0)
+            out.append(torch.nn.functional.pad(t, (0, Wm - t.shape[-1], 0, Hm - t.shape[-2])))
+        return torch.stack(out), sizes
+
+    # ---- A3-A5: network ------------------------------------------------------------------------------
+    def network_logits(self, x):
+        """[B,9,H,W] normalised input -> dict of 1/COMMON_STRIDE-resolution float32 logits (the head outputs
+        before model.py:688-708's up-sampling)."""
+        if self.precision == "bf16" and x.is_cuda:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                feats = self.backbone(x.contiguous(memory_format=torch.channels_last))
+                out = self.ins_embed_head.layers({k: v for k, v in feats.items()})
+        else:
+            feats = self.backbone(x)
+            out = self.ins_embed_head.layers(feats)
+        return {k: v.float().contiguous() for k, v in out.items()}
+
+    # ---- forward -------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def forward(self, batched_inputs):
+        x, sizes = self._pack(batched_inputs)
+        out = self.network_logits(x)
+        if self.benchmark_network_speed:
+            return []
+        if not x.is_cuda:
+            raise RuntimeError("quber_b200 has no CPU post-processing: MaskRefiner.forward needs a CUDA device "
+                               "(network_logits() runs anywhere)")
+        B = x.shape[0]
+        s = self.common_stride
+        heights = [bi.get("height", sz[0]) for bi, sz in zip(batched_inputs, sizes)]
+        widths = [bi.get("width", sz[1]) for bi, sz in zip(batched_inputs, sizes)]
+        eee = out.get("eee_boundary") if self.eee_boundary_on else None
+        identity = all(sz == (x.shape[2], x.shape[3]) and (h, w) == sz for sz, h, w in zip(sizes, heights, widths))
+        want = ("sem_seg", "panoptic", "masks") + (("eee_full",) if eee is not None else ())
+        kw = dict(threshold=self.threshold, nms_kernel=self.nms_kernel, top_k=self.top_k, stuff_area=self.stuff_area,
+                  label_divisor=self.meta["label_divisor"], want=want)
+        results = []
+        if identity and x.shape[3] % 8 == 0:
+            # sem_seg_postprocess is the identity: up-sample inside the fused kernels
+            r = ops.post_process(out["foreground"], out["center"], out["offset"], eee, scale=s,
+                                 max_instances=B * self.max_instances_per_image, **kw)
+            mfull = None
+            if self.eee_mask_on:
+                mfull = torch.nn.functional.interpolate(out["eee_mask"], scale_factor=s, mode="bilinear", align_corners=False)
+            for b in range(B):
+                results.append(self._result(r, b, b, heights[b], widths[b], None if mfull is None else mfull[b]))
+        else:
+            up = lambda t: torch.nn.functional.interpolate(t, scale_factor=s, mode="bilinear", align_corners=False)
+            full = {k: up(v) for k, v in out.items()}
+            full["offset"] = full["offset"] * s
+            for b in range(B):
+                pp = lambda t: network.sem_seg_postprocess(t[b], sizes[b], heights[b], widths[b])[None].contiguous()
+                e = pp(full["eee_boundary"]) if eee is not None else None
+                Wb = widths[b]
+                pad = (-Wb) % 8
+                padw = (lambda t: torch.nn.functional.pad(t, (0, pad), value=-1e4).contiguous()) if pad else (lambda t: t)
+                r = ops.post_process(padw(pp(full["foreground"])), padw(pp(full["center"])), padw(pp(full["offset"])),
+                                     None if e is None else padw(e), scale=1, max_instances=self.max_instances_per_image, **kw)
+                m = pp(full["eee_mask"])[0] if self.eee_mask_on else None
+                results.append(self._result(r, 0, b, heights[b], Wb, m, crop=Wb if pad else None))
+        return results
+
+    def _result(self, r, rb, b, height, width, eee_mask, crop=None):
+        cw = (lambda t: t[..., :crop]) if crop else (lambda t: t)
+        res = {"sem_seg": cw(r["sem_seg"][rb])}
+        if self.eee_boundary_on and "eee_full" in r:
+            res["eee_boundary"] = cw(r["eee_full"][rb])
+        if eee_mask is not None:
+            res["eee_mask"] = eee_mask
+        res["panoptic_seg"] = (cw(r["panoptic"][rb]), None)
+        if self.predict_instances:
+            o0, o1 = int(r["inst_offsets"][rb]), int(r["inst_offsets"][rb + 1])     # the single host read-back per image
+            o1 = min(o1, r["max_instances"])
+            if o1 > o0:
+                res["instances"] = Instances(
+                    (height, width), pred_masks=cw(r["masks"][o0:o1]).bool(), scores=r["scores"][o0:o1],
+                    pred_boxes=Boxes(r["boxes"][o0:o1]),
+                    pred_classes=(r["labels"][o0:o1] // self.meta["label_divisor"] - 1).long())
+        return res
+
+
+META_ARCH_REGISTRY = {"MaskRefiner": MaskRefiner}
+
+
+def build_model(cfg, precision="fp32"):
+    """detectron2.modeling.build_model for the registered meta-architecture (predictor.py:217)."""
+    model = META_ARCH_REGISTRY[cfg.MODEL.META_ARCHITECTURE](cfg, precision)
+    return model.to(torch.device(cfg.MODEL.DEVICE if torch.cuda.is_available() or cfg.MODEL.DEVICE == "cpu" else "cpu"))

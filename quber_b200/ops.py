@@ -232,6 +232,58 @@ def gemm_bias_act(a, weight, bias=None, act="none", out_dtype=None):
     return out.reshape(tuple(a.shape[:-1]) + (N,))
 
 
+def pack_input(image, offsets, mean, std):
+    """model.py:137-153 for a batch: image [B,C,H,W] uint8, offsets [B,CO,H,W] float32 | None, mean/std [C] float32
+    -> [B,C+CO,H,W] float32 = cat((image - mean) / std, offsets)."""
+    _need_cuda(image, "image", torch.uint8)
+    B, C, H, W = image.shape
+    CO = 0
+    if offsets is not None:
+        _need_cuda(offsets, "offsets", torch.float32)
+        CO = offsets.shape[1]
+    mean = mean.reshape(-1).to(device=image.device, dtype=torch.float32).contiguous()
+    std = std.reshape(-1).to(device=image.device, dtype=torch.float32).contiguous()
+    if mean.numel() != C or std.numel() != C:
+        raise ValueError("mean / std must have one entry per image channel")
+    out = torch.empty((B, C + CO, H, W), dtype=torch.float32, device=image.device)
+    with torch.cuda.device(image.device):
+        _lib.check(_lib.lib().quber_pack_input(_ptr(image), _ptr(offsets), _ptr(mean), _ptr(std), B, C, CO, H, W, _ptr(out),
+                                               _stream()), "quber_pack_input")
+    return out
+
+
+_FUSE_OPS = {"copy": 0, "sigmoid": 1, "softmax": 2}
+
+
+def fuse_concat(sources, ops_, layout="nchw", pitch=None):
+    """model.py:745-759: channel concat of [B,C_i,h,w] float32 sources, each passed through "copy" | "sigmoid" |
+    "softmax" (over its own channels).  layout "nchw" -> [B,sum C,h,w] float32; "nhwc_f32" / "nhwc_bf16" ->
+    channels-last rows [B*h*w, pitch] (pitch >= sum C, zero padded) for gemm_bias_act."""
+    if len(sources) != len(ops_) or not sources:
+        raise ValueError("sources and ops must have the same non-zero length")
+    for i, t in enumerate(sources):
+        _need_cuda(t, f"sources[{i}]", torch.float32)
+    B, _, h, w = sources[0].shape
+    if any(t.shape[0] != B or t.shape[2:] != sources[0].shape[2:] for t in sources):
+        raise ValueError("Sizes of tensors must match except in dimension 1")      # what torch.cat raises
+    ch = [int(t.shape[1]) for t in sources]
+    ctot = sum(ch)
+    lay = {"nchw": 0, "nhwc_f32": 1, "nhwc_bf16": 2}[layout]
+    if lay == 0:
+        pitch = ctot
+        out = torch.empty((B, ctot, h, w), dtype=torch.float32, device=sources[0].device)
+    else:
+        pitch = ctot if pitch is None else int(pitch)
+        out = torch.empty((B * h * w, pitch), dtype=torch.float32 if lay == 1 else torch.bfloat16, device=sources[0].device)
+    n = len(sources)
+    ptrs = (ctypes.c_void_p * n)(*[t.data_ptr() for t in sources])
+    chs = (ctypes.c_int * n)(*ch)
+    opc = (ctypes.c_int * n)(*[_FUSE_OPS[o] for o in ops_])
+    with torch.cuda.device(sources[0].device):
+        _lib.check(_lib.lib().quber_fuse_concat(ptrs, chs, opc, n, B, h, w, lay, pitch, _ptr(out), _stream()), "quber_fuse_concat")
+    return out
+
+
 # ---- torch.library registration: torch.ops.quber.* ----------------------------------------------
 def _register():
     try:

@@ -1,0 +1,183 @@
+"""GPU parity of the network-side kernels and of the drop-in meta-architecture / predictor.  B200 only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from quber_b200 import config as qcfg
+from quber_b200 import ops, synth
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CFG = os.path.join(ROOT, "configs", "mask-refiner-rgbd-concat-l2-gn-hf-b-fco-l3-b8.yaml")
+
+
+def _cfg(device):
+    c = qcfg.get_cfg()
+    c.merge_from_file(CFG)
+    c.MODEL.DEVICE = device
+    return c
+
+
+def _randomise(model, seed=0):
+    """Random-init predictors are N(0, 0.001) (model.py:418): logits would be ~0 and every comparison vacuous.
+    Give predictors, norms and BatchNorm statistics non-trivial seeded values."""
+    g = torch.Generator().manual_seed(seed)
+    for n, m in model.named_modules():
+        if isinstance(m, torch.nn.BatchNorm2d) or type(m).__name__ == "FrozenBatchNorm2d":
+            m.running_mean.copy_(torch.randn(m.running_mean.shape, generator=g) * 0.1)
+            m.running_var.copy_(torch.rand(m.running_var.shape, generator=g) + 0.5)
+        if n.endswith("_predictor.predictor"):
+            m.weight.data.copy_(torch.randn(m.weight.shape, generator=g) * 0.05)
+            m.bias.data.copy_(torch.randn(m.bias.shape, generator=g) * 0.1)
+
+
+def test_pack_input_bit_exact_with_torch():
+    g = torch.Generator(device=DEV).manual_seed(0)
+    img = torch.randint(0, 256, (3, 6, 48, 80), dtype=torch.uint8, device=DEV, generator=g)
+    off = torch.randn(3, 3, 48, 80, device=DEV, generator=g)
+    mean = torch.tensor([103.530, 116.280, 123.675, 127.5, 127.5, 127.5], device=DEV)
+    std = torch.tensor([1.0, 57.375, 1.0, 2.0, 0.3, 1.0], device=DEV)
+    out = ops.pack_input(img, off, mean, std)
+    ref = torch.cat([(img - mean.view(-1, 1, 1)) / std.view(-1, 1, 1), off], dim=1)     # model.py:138,153
+    assert torch.equal(out, ref)
+    assert torch.equal(ops.pack_input(img, None, mean, std), ref[:, :6])
+
+
+@pytest.mark.parametrize("hw", [(120, 160), (30, 37)])
+def test_fuse_concat_matches_torch_chain(hw):
+    h, w = hw
+    g = torch.Generator(device=DEV).manual_seed(1)
+    y = torch.randn(2, 128, h, w, device=DEV, generator=g)
+    feat = torch.randn(2, 32, h, w, device=DEV, generator=g)
+    eee = torch.randn(2, 4, h, w, device=DEV, generator=g) * 3
+    fg = torch.randn(2, 1, h, w, device=DEV, generator=g) * 3
+    ref = torch.cat([y, feat, eee.softmax(dim=1), fg.sigmoid()], dim=1)                 # model.py:745-759
+    out = ops.fuse_concat([y, feat, eee, fg], ["copy", "copy", "softmax", "sigmoid"])
+    assert out.shape == ref.shape
+    assert torch.equal(out[:, :160], ref[:, :160])                                      # copies are exact
+    torch.testing.assert_close(out, ref, rtol=0, atol=2e-6)                             # __expf vs expf
+    rows = ops.fuse_concat([y, feat, eee, fg], ["copy", "copy", "softmax", "sigmoid"], layout="nhwc_f32", pitch=168)
+    assert rows.shape == (2 * h * w, 168) and not rows[:, 165:].any()
+    torch.testing.assert_close(rows[:, :165], ref.permute(0, 2, 3, 1).reshape(-1, 165), rtol=0, atol=2e-6)
+    rb = ops.fuse_concat([y, feat, eee, fg], ["copy", "copy", "softmax", "sigmoid"], layout="nhwc_bf16", pitch=168)
+    torch.testing.assert_close(rb[:, :165].float(), ref.permute(0, 2, 3, 1).reshape(-1, 165), rtol=2 ** -8, atol=1e-6)
+    with pytest.raises(ValueError):
+        ops.fuse_concat([y, feat[:, :, :-1]], ["copy", "copy"])
+
+
+@pytest.fixture(scope="module")
+def models():
+    from quber_b200.meta_arch import build_model
+    torch.manual_seed(0)
+    cpu = build_model(_cfg("cpu")).eval()
+    _randomise(cpu)
+    gpu = build_model(_cfg("cuda")).eval()
+    gpu.load_state_dict(cpu.state_dict())                    # never re-initialise independently
+    return cpu, gpu
+
+
+def test_network_logits_fp32_within_1e3_of_cpu_restatement(models):
+    """North-star tolerance: float error logits within 1e-3 absolute in fp32.  Oracle = the same restated modules
+    in plain torch fp32 on the CPU (no kernels); product = GPU with fuse_concat in the loop, TF32 off."""
+    cpu, gpu = models
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    g = torch.Generator().manual_seed(3)
+    img = torch.randint(0, 256, (2, 6, 96, 128), dtype=torch.uint8, generator=g)
+    m = np.stack([synth.ellipse_masks(4, 96, 128, seed=s, axes=(8, 24), margin=10) for s in range(2)])
+    enc = torch.from_numpy(np.stack([oracle.encode_initial_masks(x) for x in m]))
+    x_cpu = torch.cat([(img - cpu.pixel_mean) / cpu.pixel_std, enc], dim=1)
+    with torch.no_grad():
+        ref = cpu.network_logits(x_cpu)
+        gpu.set_precision("fp32")
+        x_gpu = ops.pack_input(img.to(DEV), enc.to(DEV), gpu.pixel_mean, gpu.pixel_std)
+        assert torch.equal(x_gpu.cpu(), x_cpu)
+        out = gpu.network_logits(x_gpu)
+    for k in ref:
+        assert ref[k].abs().max() > 0.05, k                                             # not a vacuous comparison
+        torch.testing.assert_close(out[k].cpu(), ref[k], rtol=0, atol=1e-3)
+
+
+def test_network_logits_bf16_mode_stated_tolerance(models):
+    """C3: channels-last bf16 autocast for cuDNN + tcgen05 bf16 GEMM for the FusionLayers 1x1.  Stated tolerance:
+    max abs error <= 6 % of the logit range of each head (bf16 has 8 mantissa bits; ~60 layers deep)."""
+    cpu, gpu = models
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(2, 9, 96, 128, generator=g)
+    x[:, :6] *= 60
+    with torch.no_grad():
+        ref = cpu.network_logits(x)
+        gpu.set_precision("bf16")
+        out = gpu.network_logits(x.to(DEV))
+        gpu.set_precision("fp32")
+    from quber_b200 import _lib
+    assert _lib.lib().quber_gemm_timeouts() == 0
+    for k in ref:
+        rng = (ref[k].max() - ref[k].min()).item()
+        err = (out[k].cpu() - ref[k]).abs().max().item()
+        assert err <= 0.06 * rng, (k, err, rng)
+
+
+def test_meta_arch_forward_matches_oracle_on_synthetic_heads(models, monkeypatch):
+    """MaskRefiner.forward end to end (pack -> network -> fused post-processing -> output dicts) with the head
+    outputs replaced by synthetic ones that contain instances (random-init weights give none)."""
+    _, gpu = models
+    H, W, B = 240, 320, 2
+    ms = [synth.ellipse_masks(5, H, W, seed=10 + b, axes=(14, 40), margin=30) for b in range(B)]
+    heads = [synth.head_outputs(m, seed=b) for b, m in enumerate(ms)]
+    low = {k: torch.from_numpy(np.stack([h[k] for h in heads])).to(DEV) for k in heads[0]}
+    monkeypatch.setattr(gpu, "network_logits", lambda x: low)
+    inputs = [{"image": torch.zeros(6, H, W, dtype=torch.uint8), "initial_pred_offset": torch.zeros(3, H, W), "height": H, "width": W}
+              for _ in range(B)]
+    res = gpu(inputs)
+    assert len(res) == B
+    for b in range(B):
+        lowb = np.concatenate([heads[b]["foreground"], heads[b]["center"], heads[b]["offset"], heads[b]["eee_boundary"]], 0)
+        full = oracle.upsample_bilinear(lowb, 4)
+        full[2:4] *= 4.0
+        ref = oracle.post_process(full[0], full[1], full[2:4], full[4:8])
+        r = res[b]
+        assert set(r) == {"sem_seg", "eee_boundary", "panoptic_seg", "instances"}
+        np.testing.assert_array_equal(r["sem_seg"].cpu().numpy()[0], full[0])
+        np.testing.assert_array_equal(r["eee_boundary"].cpu().numpy(), full[4:8])
+        np.testing.assert_array_equal(r["panoptic_seg"][0].cpu().numpy(), ref["panoptic"])
+        inst = r["instances"]
+        assert len(inst) == len(ref["labels"]) > 0 and inst.image_size == (H, W)
+        np.testing.assert_array_equal(inst.pred_masks.cpu().numpy(), ref["masks"].astype(bool))
+        np.testing.assert_array_equal(inst.pred_boxes.tensor.cpu().numpy(), ref["boxes"])
+        np.testing.assert_allclose(inst.scores.cpu().numpy(), ref["scores"], rtol=1e-4, atol=1e-6)
+        assert (inst.pred_classes == 0).all()
+
+
+def test_predictor_predict_api_and_encoding():
+    from quber_b200.predictor import MaskRefinerPredictor
+    torch.manual_seed(0)
+    p = MaskRefinerPredictor(CFG)
+    H, W = 480, 640
+    rgb, depth = synth.rgbd_frame(H, W, seed=0)
+    masks = synth.ellipse_masks(20, H, W, seed=0)                                       # config C1
+    enc = p.encode(masks)[0].cpu().numpy()
+    np.testing.assert_array_equal(enc, oracle.encode_initial_masks(masks))
+    out = p.predict(rgb, depth, masks)
+    assert isinstance(out, list) and len(out) == 1
+    o = out[0]
+    assert tuple(o["sem_seg"].shape) == (1, H, W) and tuple(o["eee_boundary"].shape) == (4, H, W)
+    assert tuple(o["panoptic_seg"][0].shape) == (H, W) and o["panoptic_seg"][1] is None
+    # random-init predictors: centre map ~0 < threshold -> no centre.  The only possible "instance" is then the
+    # reference's stuff paste of a large enough foreground region (post_processing.py:152-160, label 1000 -> class 0)
+    if "instances" in o:
+        assert len(o["instances"]) == 1 and int(o["instances"].pred_classes[0]) == 0
+        assert set(np.unique(o["panoptic_seg"][0].cpu().numpy())) <= {-1.0, 1000.0}
+    outs = p.predict_batch([rgb, rgb], [depth, depth], [masks, masks[:3]])
+    assert len(outs) == 2
+    torch.testing.assert_close(outs[0]["sem_seg"], o["sem_seg"], rtol=0, atol=1e-4)
+    # armbench-shaped frame: width not a multiple of 16 / 8
+    m2 = synth.ellipse_masks(3, 120, 150, seed=2, axes=(8, 20), margin=12)
+    e2 = p.encode(m2)[0].cpu().numpy()
+    r2 = oracle.encode_initial_masks(m2)
+    np.testing.assert_array_equal(e2[:2], r2[:2])
+    np.testing.assert_allclose(e2[2], r2[2], rtol=2e-7, atol=0)

@@ -1,0 +1,117 @@
+"""Host-side mirror of the reference's config / registry / module layout (CPU): the YAML loader, the
+state_dict key layout a reference checkpoint has, and the shapes of the head outputs."""
+import os
+
+import pytest
+import torch
+
+from quber_b200 import config as qcfg
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CFG = os.path.join(ROOT, "configs", "mask-refiner-rgbd-concat-l2-gn-hf-b-fco-l3-b8.yaml")
+REF_CFG = "/root/reference/configs/uoais-sim/instance-segmentation/seed777/mask-refiner-rgbd-concat-l2-gn-hf-b-fco-l3-b8_new.yaml"
+
+
+def _cfg():
+    c = qcfg.get_cfg()
+    c.merge_from_file(CFG)
+    c.MODEL.DEVICE = "cpu"
+    return c
+
+
+def test_config_defaults_and_merge():
+    c = qcfg.get_cfg()
+    assert c.MODEL.PANOPTIC_DEEPLAB.CENTER_THRESHOLD == 0.1 and c.MODEL.INS_EMBED_HEAD.NORM == "SyncBN"   # config.py:79,93
+    assert c.MODEL.RESNETS.STEM_TYPE == "deeplab" and c.MODEL.RESNETS.RES5_MULTI_GRID == [1, 2, 4]
+    c = _cfg()
+    assert c.MODEL.PANOPTIC_DEEPLAB.CENTER_THRESHOLD == 0.3 and c.MODEL.INS_EMBED_HEAD.NORM == "GN"
+    assert c.MODEL.INS_EMBED_HEAD.HIERARCHY == [["eee_boundary"], ["foreground", "center", "offset"]]
+    assert c.MODEL.SEM_SEG_HEAD.USE_DEPTHWISE_SEPARABLE_CONV is False      # the key the head actually reads (model.py:637)
+    c.merge_from_list(["MODEL.PANOPTIC_DEEPLAB.TOP_K_INSTANCE", 50])
+    assert c.MODEL.PANOPTIC_DEEPLAB.TOP_K_INSTANCE == 50
+
+
+@pytest.mark.skipif(not os.path.exists(REF_CFG), reason="reference checkout not present (GPU box)")
+def test_reference_yaml_with_base_loads_unchanged():
+    ours, ref = _cfg(), qcfg.get_cfg()
+    ref.merge_from_file(REF_CFG)                                            # _BASE_: ../Base-Mask-Refiner.yaml
+    for sect in ("BACKBONE", "RESNETS", "INS_EMBED_HEAD", "PANOPTIC_DEEPLAB"):
+        for k, v in ours.MODEL[sect].items():
+            assert ref.MODEL[sect][k] == v, (sect, k, ref.MODEL[sect][k], v)
+    assert list(ref.MODEL.PIXEL_MEAN) == list(ours.MODEL.PIXEL_MEAN)
+    assert ref.INPUT.OFFSET_INPUT_ON and ref.INPUT.DEPTH_ON and ref.SEED == 777
+
+
+@pytest.fixture(scope="module")
+def model():
+    from quber_b200.meta_arch import build_model
+    torch.manual_seed(0)
+    return build_model(_cfg()).eval()
+
+
+def test_state_dict_layout_matches_reference_checkpoints(model):
+    sd = model.state_dict()
+    expect = {
+        "backbone.rgb_backbone.stem.conv1.weight": (32, 6, 3, 3),
+        "backbone.rgb_backbone.stem.conv3.norm.running_var": (64,),
+        "backbone.rgb_backbone.res2.0.shortcut.weight": (256, 64, 1, 1),
+        "backbone.rgb_backbone.res5.2.conv2.weight": (512, 512, 3, 3),
+        "backbone.depth_backbone.stem.conv1.weight": (32, 6, 3, 3),
+        "backbone.depth_backbone.depth_res2.0.conv1.norm.running_mean": (64,),          # resnet.py:169 prefix
+        "backbone.depth_backbone.depth_res5.0.shortcut.norm.weight": (2048,),
+        "backbone.fusion_res2.conv.weight": (256, 512, 1, 1),                           # resnet.py:473-485
+        "backbone.fusion_res2.gn1.weight": (256,),
+        "backbone.fusion_res3.conv1.weight": (512, 512, 3, 3),
+        "backbone.fusion_res5.conv.bias": (2048,),
+        "ins_embed_head.decoder.res5.project_conv.convs.0.weight": (256, 2048, 1, 1),
+        "ins_embed_head.decoder.res5.project_conv.convs.3.norm.weight": (256,),
+        "ins_embed_head.decoder.res5.project_conv.convs.4.1.bias": (256,),
+        "ins_embed_head.decoder.res5.project_conv.project.weight": (256, 1280, 1, 1),
+        "ins_embed_head.decoder.res3.project_conv.weight": (64, 512, 1, 1),
+        "ins_embed_head.decoder.res3.fuse_conv.0.weight": (128, 320, 3, 3),
+        "ins_embed_head.decoder.res2.fuse_conv.1.norm.bias": (128,),
+        "ins_embed_head.eee_boundary_pred_head.head.1.weight": (32, 128, 3, 3),
+        "ins_embed_head.eee_boundary_predictor.predictor.weight": (4, 32, 1, 1),
+        "ins_embed_head.offset_predictor.predictor.bias": (2,),
+        "ins_embed_head.fusion_layers_1.fusion_layers.0.weight": (128, 164, 1, 1),      # 128 + 32 + 4 (model.py:595-608)
+        "ins_embed_head.fusion_layers_1.fusion_layers.3.norm.running_mean": (128,),
+    }
+    for k, shape in expect.items():
+        assert k in sd, k
+        assert tuple(sd[k].shape) == shape, (k, tuple(sd[k].shape))
+    assert "backbone.fusion_res5.conv0.weight" not in sd                                # resnet.py:480-481
+    assert not any(k.startswith("ins_embed_head.eee_mask") for k in sd)                 # EEE_MASK_ON False
+    assert "pixel_mean" not in sd                                                       # non-persistent buffer (model.py:90)
+
+
+def test_head_output_shapes_and_res5_stride(model):
+    x = torch.randn(1, 9, 64, 96)
+    feats = model.backbone(x)
+    assert {k: tuple(v.shape[1:]) for k, v in feats.items()} == {"res2": (256, 16, 24), "res3": (512, 8, 12), "res5": (2048, 4, 6)}
+    out = model.network_logits(x)
+    assert {k: tuple(v.shape) for k, v in out.items()} == {"eee_boundary": (1, 4, 16, 24), "foreground": (1, 1, 16, 24),
+                                                           "center": (1, 1, 16, 24), "offset": (1, 2, 16, 24)}
+    full, _ = model.ins_embed_head(model.backbone(x))
+    assert tuple(full["offset"].shape) == (1, 2, 64, 96)
+    torch.testing.assert_close(full["offset"], torch.nn.functional.interpolate(out["offset"], scale_factor=4, mode="bilinear",
+                                                                               align_corners=False) * 4)
+
+
+def test_fusionlayers_bn_folding_is_exact_algebra(model):
+    fl = model.ins_embed_head.fusion_layers[1]
+    torch.manual_seed(1)
+    bn = fl.fusion_layers[0].norm
+    bn.running_mean.normal_(0, 0.1); bn.running_var.uniform_(0.5, 1.5); bn.weight.data.uniform_(0.5, 1.5); bn.bias.data.normal_()
+    x = torch.randn(2, 164, 5, 7)
+    ref = fl.fusion_layers[0](x)
+    w, b = fl.folded_1x1(168, torch.float32)
+    rows = torch.zeros(2 * 5 * 7, 168)
+    rows[:, :164] = x.permute(0, 2, 3, 1).reshape(-1, 164)
+    got = torch.relu(rows @ w.T + b).view(2, 5, 7, 128).permute(0, 3, 1, 2)
+    torch.testing.assert_close(got, ref, rtol=1e-4, atol=1e-5)
+
+
+def test_cpu_forward_refuses_postprocessing(model):
+    inp = {"image": torch.zeros(6, 32, 48, dtype=torch.uint8), "initial_pred_offset": torch.zeros(3, 32, 48), "height": 32, "width": 48}
+    with pytest.raises(RuntimeError, match="no CPU post-processing"):
+        model([inp])
