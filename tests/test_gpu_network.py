@@ -181,3 +181,70 @@ def test_predictor_predict_api_and_encoding():
     r2 = oracle.encode_initial_masks(m2)
     np.testing.assert_array_equal(e2[:2], r2[:2])
     np.testing.assert_allclose(e2[2], r2[2], rtol=2e-7, atol=0)
+
+
+# ------------------------------------------------------------------ A15: MSDeformAttn pixel decoder
+def _cpu_encoder_layer(layer, src, pos, ref, shapes, starts):
+    """msdeformattn.py:122-131 + ms_deform_attn.py:82-125 on the CPU, the sampling done by the oracle."""
+    a = layer.self_attn
+    N, S, C = src.shape
+    M, L, P = a.n_heads, a.n_levels, a.n_points
+    q = src + pos
+    value = a.value_proj(src).view(N, S, M, C // M)
+    off = a.sampling_offsets(q).view(N, S, M, L, P, 2)
+    aw = torch.softmax(a.attention_weights(q).view(N, S, M, L * P), -1).view(N, S, M, L, P)
+    norm = torch.stack([shapes[..., 1], shapes[..., 0]], -1)
+    loc = ref[:, :, None, :, None, :] + off / norm[None, None, None, :, None, :]
+    samp = torch.from_numpy(oracle.msda_forward(value.numpy(), shapes.numpy(), starts.numpy(), loc.contiguous().numpy(),
+                                                aw.contiguous().numpy()))
+    src = layer.norm1(src + a.output_proj(samp))
+    return layer.norm2(src + layer.linear2(torch.relu(layer.linear1(src))))
+
+
+def test_encoder_layer_fp32_tf32_bf16_against_cpu_restatement():
+    from quber_b200.pixel_decoder import MSDeformAttnTransformerEncoder, MSDeformAttnTransformerEncoderLayer
+    torch.manual_seed(0)
+    layer = MSDeformAttnTransformerEncoderLayer(256, 1024, 0.0, "relu", 3, 8, 4).eval()
+    with torch.no_grad():                                    # non-trivial offsets / attention (both weights are 0 at init)
+        layer.self_attn.sampling_offsets.weight.normal_(0, 0.02)
+        layer.self_attn.attention_weights.weight.normal_(0, 0.05)
+    hs = [(15, 20), (8, 10), (4, 5)]
+    S = sum(h * w for h, w in hs)
+    shapes = torch.tensor(hs, dtype=torch.long)
+    starts = torch.cat((shapes.new_zeros((1,)), shapes.prod(1).cumsum(0)[:-1]))
+    g = torch.Generator().manual_seed(1)
+    src, pos = torch.randn(2, S, 256, generator=g), torch.randn(2, S, 256, generator=g) * 0.5
+    ref = MSDeformAttnTransformerEncoder.get_reference_points(hs, torch.ones(2, 3, 2), "cpu")
+    torch.backends.cuda.matmul.allow_tf32 = False
+    with torch.no_grad():
+        want = _cpu_encoder_layer(layer, src, pos, ref, shapes, starts)
+        gl = layer.to(DEV)
+        args = (src.to(DEV), pos.to(DEV), ref.to(DEV), shapes.to(DEV), starts.to(DEV))
+        got = {}
+        for prec in ("fp32", "tf32", "bf16"):
+            gl.precision = prec
+            got[prec] = gl(*args).cpu()
+    torch.testing.assert_close(got["fp32"], want, rtol=0, atol=1e-3)        # north-star fp32 tolerance (measured ~1e-5)
+    torch.testing.assert_close(got["tf32"], want, rtol=0, atol=2e-2)        # 10-bit mantissa products, LayerNorm output O(1)
+    torch.testing.assert_close(got["bf16"], want, rtol=0, atol=1e-1)        # stated bf16 tolerance (8-bit mantissa)
+    assert (got["bf16"] - want).abs().mean() < 1.5e-2
+    from quber_b200 import _lib
+    assert _lib.lib().quber_gemm_timeouts() == 0
+
+
+def test_pixel_decoder_forward_features_shapes_and_precisions():
+    from quber_b200.pixel_decoder import MSDeformAttnPixelDecoder
+    shapes = {"res2": (256, 4), "res3": (512, 8), "res4": (1024, 16), "res5": (2048, 32)}
+    torch.manual_seed(0)
+    pd = MSDeformAttnPixelDecoder(shapes, transformer_enc_layers=6).eval().to(DEV)
+    g = torch.Generator(device=DEV).manual_seed(2)
+    feats = {k: torch.randn(2, c, 480 // s, 640 // s, device=DEV, generator=g) for k, (c, s) in shapes.items()}
+    outs = {}
+    for prec in ("fp32", "tf32", "bf16"):
+        pd.set_precision(prec)
+        mask_features, low, multi = pd.forward_features(feats)
+        assert tuple(mask_features.shape) == (2, 256, 120, 160) and tuple(low.shape) == (2, 256, 15, 20)
+        assert [tuple(m.shape[2:]) for m in multi] == [(15, 20), (30, 40), (60, 80)]       # S = 6300 tokens
+        outs[prec] = mask_features
+    torch.testing.assert_close(outs["tf32"], outs["fp32"], rtol=0, atol=5e-2)
+    assert (outs["bf16"] - outs["fp32"]).abs().mean() < 5e-2

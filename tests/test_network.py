@@ -115,3 +115,38 @@ def test_cpu_forward_refuses_postprocessing(model):
     inp = {"image": torch.zeros(6, 32, 48, dtype=torch.uint8), "initial_pred_offset": torch.zeros(3, 32, 48), "height": 32, "width": 48}
     with pytest.raises(RuntimeError, match="no CPU post-processing"):
         model([inp])
+
+
+def test_pixel_decoder_layout_and_position_embedding():
+    from quber_b200.pixel_decoder import MSDeformAttnPixelDecoder, PositionEmbeddingSine
+    shapes = {"res2": (256, 4), "res3": (512, 8), "res4": (1024, 16), "res5": (2048, 32)}
+    torch.manual_seed(0)
+    pd = MSDeformAttnPixelDecoder(shapes, transformer_enc_layers=2)
+    sd = pd.state_dict()
+    expect = {                                                                           # msdeformattn.py:205-287
+        "input_proj.0.0.weight": (256, 2048, 1, 1), "input_proj.2.1.weight": (256,),
+        "transformer.level_embed": (3, 256),
+        "transformer.encoder.layers.1.self_attn.sampling_offsets.weight": (192, 256),
+        "transformer.encoder.layers.0.self_attn.attention_weights.bias": (96,),
+        "transformer.encoder.layers.0.self_attn.value_proj.weight": (256, 256),
+        "transformer.encoder.layers.0.linear1.weight": (1024, 256), "transformer.encoder.layers.0.norm2.bias": (256,),
+        "adapter_1.weight": (256, 256, 1, 1), "layer_1.norm.weight": (256,), "mask_features.bias": (256,),
+    }
+    for k, s in expect.items():
+        assert k in sd and tuple(sd[k].shape) == s, k
+    assert pd.num_fpn_levels == 1 and pd.transformer_in_features == ["res3", "res4", "res5"]
+    # cached position embedding == the reference formula evaluated with an explicit all-False mask
+    pe = PositionEmbeddingSine(128, normalize=True)
+    x = torch.zeros(2, 8, 15, 20)
+    a = pe(x)
+    b = pe(x, mask=torch.zeros(2, 15, 20, dtype=torch.bool))
+    assert a.shape == (2, 256, 15, 20) and torch.equal(a, b) and torch.equal(pe(x), a)
+    # reference points of the encoder: (i + 0.5) / dim, x first (msdeformattn.py:141-153)
+    from quber_b200.pixel_decoder import MSDeformAttnTransformerEncoder
+    rp = MSDeformAttnTransformerEncoder.get_reference_points([(2, 3), (1, 2)], torch.ones(1, 2, 2), "cpu")
+    assert rp.shape == (1, 8, 2, 2)
+    torch.testing.assert_close(rp[0, 4, 0], torch.tensor([1.5 / 3, 1.5 / 2]))
+    # the CUDA-only op refuses CPU tensors like the reference's AT_ERROR
+    feats = {k: torch.randn(1, c, 64 // s, 96 // s) for k, (c, s) in shapes.items()}
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        pd.forward_features(feats)
