@@ -127,7 +127,7 @@ def algorithmic_bytes():
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from quber_b200 import _lib, ops
+    from quber_b200 import _lib, ops, sharding
     from quber_b200.pipeline import HotPath, RefinerConfig
     _lib.lib()     # fail loudly if the CUDA library is missing
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1))
@@ -165,7 +165,8 @@ def run_ours(args):
         r = hp.post(d["head"])
         mark()
         if world > 1:
-            dist.all_gather_into_tensor(gather_buf.view(-1), r["label_map"].view(-1))
+            counts = r["inst_offsets"][1:] - r["inst_offsets"][:-1]
+            sharding.gather_label_maps(r["label_map"], counts, out=gather_buf)
         return r
 
     def _ev():
@@ -222,7 +223,8 @@ def run_ours(args):
         o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"])
         hp.msda_layers(d["msda"], N_LAYERS)     # decoder activations never live on the host: resident inputs
         if world > 1:
-            dist.all_gather_into_tensor(gather_buf.view(-1), keep[2]["label_map"].view(-1))
+            rr = keep[2]
+            sharding.gather_label_maps(rr["label_map"], rr["inst_offsets"][1:] - rr["inst_offsets"][:-1], out=gather_buf)
         return o
     for i in range(max(1, min(args.warmup, 3))):
         o = e2e_step(i)

@@ -1,0 +1,46 @@
+"""Multi-GPU plumbing of the path: frames are independent, so the batch is sharded across ranks with
+no data-path collective; the only exchange is ONE all-gather per step of the refined label maps.
+
+The reference runs inference as one hand-started process per GPU (CUDA_VISIBLE_DEVICES, eval/run_eval.py:72,
+bash/eval_*.sh) at batch size 1 and never collects anything; here one process per GPU is launched by torchrun
+and rank r refines the frame blocks {r, r + G, r + 2G, ...}.  The payload is the fixed-shape int32 [B,H,W] label map
+(0 = void, j + 1 = j-th refined instance of the frame) — lossless, because the reference's instances are disjoint
+by construction (model.py:331) — plus the per-frame instance counts; per-instance bool masks [K,H,W] have a
+data-dependent K and are re-materialised by the consumer with `masks_from_label_map`.
+"""
+import torch
+import torch.distributed as dist
+
+
+def frame_blocks(n_frames, block, rank, world):
+    """[(start, stop), ...] of the contiguous frame blocks of size `block` that rank `rank` refines: block i goes to
+    rank i % world.  Every frame belongs to exactly one rank."""
+    if block <= 0 or world <= 0 or not 0 <= rank < world:
+        raise ValueError("bad sharding arguments")
+    n_blocks = (n_frames + block - 1) // block
+    return [(i * block, min((i + 1) * block, n_frames)) for i in range(rank, n_blocks, world)]
+
+
+def gather_label_maps(label_map, counts, group=None, out=None):
+    """label_map int32 [B,H,W], counts int32 [B] on this rank -> (maps [G,B,H,W], counts [G,B]) on every rank.
+    One collective for the maps (NCCL all_gather_into_tensor over NVLink; gloo falls back to all_gather)."""
+    if not dist.is_available() or not dist.is_initialized():
+        return label_map[None], counts[None]
+    world = dist.get_world_size(group)
+    if label_map.dtype != torch.int32 or counts.dtype != torch.int32:
+        raise ValueError("label_map and counts must be int32")
+    maps = out if out is not None else torch.empty((world,) + tuple(label_map.shape), dtype=label_map.dtype, device=label_map.device)
+    cnts = torch.empty((world,) + tuple(counts.shape), dtype=counts.dtype, device=counts.device)
+    if dist.get_backend(group) == "nccl":
+        dist.all_gather_into_tensor(maps.view(-1), label_map.contiguous().view(-1), group=group)
+        dist.all_gather_into_tensor(cnts.view(-1), counts.contiguous().view(-1), group=group)
+    else:
+        dist.all_gather(list(maps.unbind(0)), label_map.contiguous(), group=group)
+        dist.all_gather(list(cnts.unbind(0)), counts.contiguous(), group=group)
+    return maps, cnts
+
+
+def masks_from_label_map(label_map, n_instances):
+    """[H,W] int32 label map -> bool [n,H,W], the reference's `pred_masks` (model.py:331-336)."""
+    ids = torch.arange(1, int(n_instances) + 1, device=label_map.device, dtype=label_map.dtype)
+    return label_map[None] == ids[:, None, None]

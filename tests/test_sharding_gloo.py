@@ -1,0 +1,73 @@
+"""The N > 1 path on CPU: world_size-2 gloo processes shard frames and all-gather label maps."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from quber_b200 import sharding
+
+
+def test_frame_blocks_partition_every_frame_once():
+    for n, block, world in [(4096, 32, 8), (100, 32, 3), (5, 8, 2), (64, 32, 2)]:
+        seen = []
+        for r in range(world):
+            for a, b in sharding.frame_blocks(n, block, r, world):
+                assert 0 <= a < b <= n and b - a <= block
+                seen.extend(range(a, b))
+        assert sorted(seen) == list(range(n))
+    assert sharding.frame_blocks(4096, 32, 3, 8)[:2] == [(96, 128), (352, 384)]
+    with pytest.raises(ValueError):
+        sharding.frame_blocks(10, 4, 2, 2)
+
+
+def _label_maps(rank, B=3, H=12, W=16):
+    g = torch.Generator().manual_seed(100 + rank)
+    counts = torch.randint(1, 5, (B,), generator=g, dtype=torch.int32)
+    maps = torch.stack([torch.randint(0, int(c) + 1, (H, W), generator=g, dtype=torch.int32) for c in counts])
+    return maps, counts
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        maps, counts = _label_maps(rank)
+        allm, allc = sharding.gather_label_maps(maps, counts)
+        ok = allm.shape == (world, 3, 12, 16) and allc.shape == (world, 3)
+        for r in range(world):
+            em, ec = _label_maps(r)
+            ok = ok and torch.equal(allm[r], em) and torch.equal(allc[r], ec)
+        # a consumer on any rank re-materialises the per-instance masks of another rank's frame
+        other = (rank + 1) % world
+        m = sharding.masks_from_label_map(allm[other, 0], allc[other, 0])
+        ok = ok and m.shape[0] == int(allc[other, 0]) and bool((m.sum(0) == (allm[other, 0] > 0)).all())
+        # whole-job instance count = sum over ranks, as bench.py aggregates it
+        tot = allc.sum().clone()
+        mine = counts.sum().clone()
+        dist.all_reduce(mine)
+        ok = ok and int(tot) == int(mine)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_gloo_gather():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == [(0, True), (1, True)]
+
+
+def test_single_process_passthrough():
+    maps, counts = _label_maps(0)
+    a, c = sharding.gather_label_maps(maps, counts)
+    assert a.shape[0] == 1 and torch.equal(a[0], maps) and torch.equal(c[0], counts)
