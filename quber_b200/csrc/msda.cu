@@ -87,8 +87,8 @@ template <> struct Lane<__nv_bfloat16> {
 // the group with six width-LPG shuffles and every lane issues four unconditional 128-bit loads and four FMAs
 // per channel.  (w_i * a) * v_i differs from the reference's (sum_i w_i v_i) * a by rounding only
 // (measured: <= 6e-9 abs on the C2 inputs against the oracle, tolerance 1e-3).
-template <int D, typename VT>
-__global__ void __launch_bounds__(256, 4)
+template <int D, typename VT, int MINB>
+__global__ void __launch_bounds__(256, MINB)
 msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
                           const float *__restrict__ loc, const float *__restrict__ attn, int S, int M, int L, int Q, int P,
                           VT *__restrict__ out) {
@@ -111,7 +111,11 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
     const size_t qm = ((size_t)b * Q + q) * M + m;
     const float *lp = loc + qm * LP * 2;
     const float *ap = attn + qm * LP;
-    const VT *vb = value + (size_t)b * S * MD + m * D + lane * CPL;
+    // Gather addresses are 32-bit offsets in 16-byte units (one lane access) from a per-lane 64-bit base, so that each
+    // corner costs ONE IMAD.WIDE.U32 instead of a 64-bit add pair.  quber_msda_forward guarantees S*M*D < 2^31.
+    const uint4 *vlane = reinterpret_cast<const uint4 *>(value + (size_t)b * S * MD + m * D) + lane;
+    asm volatile("" : "+l"(vlane));                     // opaque: keeps (base + lane) in one register pair, see above
+    const uint32_t MDu = MD / CPL;                      // pixel pitch in 16-byte units
     float acc[CPL];
 #pragma unroll
     for (int c = 0; c < CPL; ++c) acc[c] = 0.f;
@@ -120,7 +124,7 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
     if (lane < LP) { raw_xy = ld_stream_u2(lp + 2 * lane); raw_a = ld_stream_u1(ap + lane); }
     for (int s0 = 0; s0 < LP; s0 += LPG) {
         const int tap = s0 + lane;
-        int o1 = 0, o3 = 0;
+        uint32_t o1 = 0, o3 = 0;
         float w1 = 0.f, w2 = 0.f, w3 = 0.f, w4 = 0.f;
         if (tap < LP) {
             const int l = tap / P;
@@ -133,8 +137,8 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
                 const bool y0 = hl >= 0, y1 = hl + 1 <= h - 1, x0 = wl >= 0, x1 = wl + 1 <= w - 1;
                 const int ry0 = max(hl, 0), ry1 = min(hl + 1, h - 1), cx0 = max(wl, 0);
                 const int start = s_start[l];
-                o1 = ((start + ry0 * w + cx0) * MD) | (int)(x0 && x1);                   // bit 0: the x+1 corner is a different pixel
-                o3 = (start + ry1 * w + cx0) * MD;
+                o1 = ((uint32_t)(start + ry0 * w + cx0) * MDu) | ((x0 && x1) ? 0x80000000u : 0u);   // bit 31: the x+1 corner is a different pixel
+                o3 = (uint32_t)(start + ry1 * w + cx0) * MDu;
                 w1 = (y0 && x0) ? hh * hw * a : 0.f;                                     // cuh:85, 0 where the reference reads v = 0
                 w2 = (y0 && x1) ? hh * lw * a : 0.f;
                 w3 = (y1 && x0) ? lh * hw * a : 0.f;
@@ -146,18 +150,20 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
 #pragma unroll
         for (int j = 0; j < LPG; ++j) {
             if (j < nt) {
-                int bo1 = __shfl_sync(0xffffffffu, o1, j, LPG);
-                const int bo3 = __shfl_sync(0xffffffffu, o3, j, LPG);
+                const uint32_t bo1 = __shfl_sync(0xffffffffu, o1, j, LPG);
+                const uint32_t bo3 = __shfl_sync(0xffffffffu, o3, j, LPG);
                 const float b1 = __shfl_sync(0xffffffffu, w1, j, LPG), b2 = __shfl_sync(0xffffffffu, w2, j, LPG);
                 const float b3 = __shfl_sync(0xffffffffu, w3, j, LPG), b4 = __shfl_sync(0xffffffffu, w4, j, LPG);
-                const int dx = (bo1 & 1) ? MD : 0;
-                bo1 &= ~1;
+                const uint32_t dx = (uint32_t)((int32_t)bo1 >> 31) & MDu;
+                uint32_t a1 = bo1 & 0x7fffffffu;
+                asm volatile("" : "+r"(a1));            // opaque, or the mask is folded into a 64-bit shift/add sequence
                 float v1[CPL], v2[CPL], v3[CPL], v4[CPL];
-                const uint4 r1 = Lane<VT>::load_raw(vb + bo1), r2 = Lane<VT>::load_raw(vb + bo1 + dx);
-                const uint4 r3 = Lane<VT>::load_raw(vb + bo3), r4 = Lane<VT>::load_raw(vb + bo3 + dx);
+                const uint4 r1 = __ldg(vlane + a1), r2 = __ldg(vlane + (a1 + dx));
+                const uint4 r3 = __ldg(vlane + bo3), r4 = __ldg(vlane + (bo3 + dx));
                 Lane<VT>::unpack(r1, v1); Lane<VT>::unpack(r2, v2); Lane<VT>::unpack(r3, v3); Lane<VT>::unpack(r4, v4);
 #pragma unroll
-                for (int c = 0; c < CPL; ++c) acc[c] += b1 * v1[c] + b2 * v2[c] + b3 * v3[c] + b4 * v4[c];
+                for (int c = 0; c < CPL; ++c)
+                    acc[c] = fmaf(b4, v4[c], fmaf(b3, v3[c], fmaf(b2, v2[c], fmaf(b1, v1[c], acc[c]))));
             }
         }
     }
@@ -198,13 +204,30 @@ msda_forward_scalar_kernel(const float *__restrict__ value, const int64_t *__res
     out[idx] = col;
 }
 
+// Resident CTAs per SM the gather kernel is compiled for: the L1 data pipe is the limit and throughput follows the
+// number of resident warps (ncu), so the default is the highest occupancy that does not spill.  QUBER_MSDA_MINB
+// (4 | 5 | 6, read once) overrides it for tuning runs.
+static int msda_minb() {
+    static const int v = [] {
+        const char *e = getenv("QUBER_MSDA_MINB");
+        const int x = e ? atoi(e) : 0;
+        return (x >= 4 && x <= 6) ? x : 5;
+    }();
+    return v;
+}
+
 template <int D, typename VT>
 static int launch_vec(const void *value, const int64_t *shapes, const int64_t *starts, const float *loc, const float *attn,
                       int B, int S, int M, int L, int Q, int P, void *out, cudaStream_t st) {
     constexpr int GPB = 256 / (D / Lane<VT>::CPL);
     dim3 grid(cdiv(Q, GPB), M, B);
-    msda_forward_kernel<D, VT><<<grid, 256, 0, st>>>(static_cast<const VT *>(value), shapes, starts, loc, attn, S, M, L, Q, P,
-                                                    static_cast<VT *>(out));
+    const VT *v = static_cast<const VT *>(value);
+    VT *o = static_cast<VT *>(out);
+    switch (msda_minb()) {
+        default: msda_forward_kernel<D, VT, 5><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+        case 6: msda_forward_kernel<D, VT, 6><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+        case 4: msda_forward_kernel<D, VT, 4><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+    }
     return check_launch("msda_forward_kernel");
 }
 

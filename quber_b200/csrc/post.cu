@@ -251,22 +251,90 @@ center_select_kernel(const float *__restrict__ center, int H, int W, int scale, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Eight consecutive full-resolution pixels (x0 .. x0+7, x0 % 8 == 0) of row y, sampled from a 1/4-resolution plane
+// with EXACTLY UpSampler::at's arithmetic (same products, same sums, same rounding), but with the per-row and
+// per-column set-up shared by every plane and 8 loads per plane instead of 32: at scale 4 the eight pixels only
+// touch source columns 2m-1 .. 2m+2 (m = x0 / 8).  Column c[i] is clamped into the plane, which reproduces the
+// reference's `+ (x1 < w - 1)` step at the right edge; at the left edge (m == 0) the clamped source coordinate
+// makes pixels 0 and 1 read columns (0, 1) instead of (-1, 0).
+// ------------------------------------------------------------------------------------------------
+struct Row8 {
+    int top, bot;            // element offsets of the two source rows
+    int c0, c1, c2, c3;      // the four source columns
+    float ly, hy;
+    float lx[8];
+    bool left;
+    __device__ __forceinline__ Row8(const UpSampler &up, int y, int x0) {
+        float sy = __fsub_rn(__fmul_rn(up.r, __fadd_rn((float)y, 0.5f)), 0.5f);
+        sy = sy < 0.f ? 0.f : sy;
+        const int y1 = (int)sy;
+        top = y1 * up.w;
+        bot = top + ((y1 < up.h - 1) ? up.w : 0);
+        ly = __fsub_rn(sy, (float)y1);
+        hy = __fsub_rn(1.f, ly);
+        const int m2 = x0 >> 2;                          // 2m
+        left = m2 == 0;
+        c0 = max(m2 - 1, 0); c1 = m2; c2 = min(m2 + 1, up.w - 1); c3 = min(m2 + 2, up.w - 1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float sx = __fsub_rn(__fmul_rn(up.r, __fadd_rn((float)(x0 + j), 0.5f)), 0.5f);
+            sx = sx < 0.f ? 0.f : sx;
+            const int x1 = (int)sx;
+            lx[j] = __fsub_rn(sx, (float)x1);
+        }
+    }
+    __device__ __forceinline__ void sample(const float *__restrict__ plane, float *out) const {
+        const float *t = plane + top, *b = plane + bot;
+        const float t0 = __ldg(t + c0), t1 = __ldg(t + c1), t2 = __ldg(t + c2), t3 = __ldg(t + c3);
+        const float b0 = __ldg(b + c0), b1 = __ldg(b + c1), b2 = __ldg(b + c2), b3 = __ldg(b + c3);
+        // pixel j reads source columns (x1, x1 + 1): j = 0,1 -> (2m-1, 2m); 2..5 -> (2m, 2m+1); 6,7 -> (2m+1, 2m+2)
+        const float ta[8] = {left ? t1 : t0, left ? t1 : t0, t1, t1, t1, t1, t2, t2};
+        const float tb[8] = {left ? t2 : t1, left ? t2 : t1, t2, t2, t2, t2, t3, t3};
+        const float ba[8] = {left ? b1 : b0, left ? b1 : b0, b1, b1, b1, b1, b2, b2};
+        const float bb[8] = {left ? b2 : b1, left ? b2 : b1, b2, b2, b2, b2, b3, b3};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float hx = __fsub_rn(1.f, lx[j]);
+            const float tp = __fadd_rn(__fmul_rn(hx, ta[j]), __fmul_rn(lx[j], tb[j]));
+            const float bt = __fadd_rn(__fmul_rn(hx, ba[j]), __fmul_rn(lx[j], bb[j]));
+            out[j] = __fadd_rn(__fmul_rn(hy, tp), __fmul_rn(ly, bt));
+        }
+    }
+};
+
+// Samples 8 pixels of one plane: the shared-set-up route at scale 4, UpSampler::at otherwise.
+template <bool S4>
+__device__ __forceinline__ void sample8(const UpSampler &up, const Row8 &r8, const float *__restrict__ plane, int y, int x0,
+                                        float *out) {
+    if (S4) { r8.sample(plane, out); return; }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) out[j] = up.at(plane, y, x0 + j);
+}
+
+// ------------------------------------------------------------------------------------------------
 // Fused per-pixel pass 1: up-sample, foreground test, nearest-centre grouping, area histogram,
 // error-map up-sample + argmax one-hot.   model.py:689-708,292; post_processing.py:44-76,103-107;
 // eval/eval_utils.py:311-313.
+//
+// Grouping = argmin_k sqrt(fma(dx,dx,dy*dy)) with the first minimum winning (torch.norm + argmin,
+// post_processing.py:71-73).  The loop runs over centres OUTSIDE and the thread's eight pixels inside (one
+// 8-byte shared-memory read per centre instead of sixteen 4-byte ones), and it compares SQUARED distances: sqrt
+// is monotone, so a candidate with d2 >= best_d2 never wins, and one with d2 < best_d2 * (1 - 2^-21) always does
+// (the two roots are then more than one ulp apart, so they cannot round to the same float).  Only in the 4-ulp
+// band in between can both roots round to one float — a tie the reference resolves in favour of the earlier
+// centre — and there the two correctly rounded roots are compared like the reference does.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(P_THREADS)
+template <bool S4>
+__global__ void __launch_bounds__(P_THREADS, S4 ? 3 : 2)
 group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ n_centers, uint16_t *__restrict__ ins,
              uint32_t *__restrict__ area) {
-    extern __shared__ float gsm[];
-    float *cy = gsm, *cx = gsm + p.top_k;
-    unsigned int *hist = reinterpret_cast<unsigned int *>(gsm + 2 * p.top_k);   // [top_k+1]
+    extern __shared__ __align__(8) float gsm[];
+    float2 *cyx = reinterpret_cast<float2 *>(gsm);                                // [top_k] (y, x)
+    unsigned int *hist = reinterpret_cast<unsigned int *>(gsm + 2 * p.top_k);     // [top_k+1]
     const int b = blockIdx.z, tid = threadIdx.x, H = p.H, W = p.W;
     const int n = n_centers[b];
-    for (int i = tid; i < n; i += P_THREADS) {
-        cy[i] = (float)io.centers_yx[((size_t)b * p.top_k + i) * 2];
-        cx[i] = (float)io.centers_yx[((size_t)b * p.top_k + i) * 2 + 1];
-    }
+    for (int i = tid; i < n; i += P_THREADS)
+        cyx[i] = make_float2((float)io.centers_yx[((size_t)b * p.top_k + i) * 2], (float)io.centers_yx[((size_t)b * p.top_k + i) * 2 + 1]);
     for (int i = tid; i <= p.top_k; i += P_THREADS) hist[i] = 0;
     __syncthreads();
     const UpSampler up(H, W, p.scale);
@@ -277,38 +345,55 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
         const size_t pix = (size_t)y * W + x0;
         const float *fgp = io.foreground + (size_t)b * hw;
         const float *oyp = io.offset + (size_t)b * 2 * hw, *oxp = oyp + hw;
+        const Row8 row(up, y, x0);
         float sem[8];
         unsigned id[8];
+        sample8<S4>(up, row, fgp, y, x0, sem);
+        unsigned fgm = 0;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const int x = x0 + j;
-            sem[j] = up.at(fgp, y, x);
             id[j] = 0;
-            if (sem[j] > QUBER_FG_LOGIT_CUT) {                     // r.sigmoid().round() == 1
-                if (n == 0) { id[j] = INS_STUFF; continue; }
-                const float ly = __fadd_rn((float)y, __fmul_rn(up.at(oyp, y, x), p.offset_mul));
-                const float lx = __fadd_rn((float)x, __fmul_rn(up.at(oxp, y, x), p.offset_mul));
-                // argmin_k sqrt(fma(dx,dx,dy*dy)), first minimum wins (torch.norm + argmin).  sqrt is
-                // monotone, so it is evaluated only when the squared distance improves.
-                float dy = __fsub_rn(cy[0], ly), dx = __fsub_rn(cx[0], lx);
-                float best_d2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
-                float best_s = __fsqrt_rn(best_d2);
-                int best = 0;
-                for (int k = 1; k < n; ++k) {
-                    dy = __fsub_rn(cy[k], ly); dx = __fsub_rn(cx[k], lx);
-                    const float d2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
-                    if (d2 < best_d2) {
-                        const float s = __fsqrt_rn(d2);
-                        if (s < best_s) { best_s = s; best_d2 = d2; best = k; }
-                    }
-                }
-                id[j] = best + 1;
-            }
+            if (sem[j] > QUBER_FG_LOGIT_CUT) fgm |= 1u << j;           // r.sigmoid().round() == 1
         }
         if (io.sem_seg) {
             float *o = io.sem_seg + (size_t)b * HW + pix;
             st_stream_f4(o, make_float4(sem[0], sem[1], sem[2], sem[3]));
             st_stream_f4(o + 4, make_float4(sem[4], sem[5], sem[6], sem[7]));
+        }
+        if (fgm && n == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (fgm >> j & 1) id[j] = INS_STUFF;
+        } else if (fgm) {
+            float ly[8], lx[8], bd2[8];
+            int best[8];
+            sample8<S4>(up, row, oyp, y, x0, ly);
+            sample8<S4>(up, row, oxp, y, x0, lx);
+            const float2 c0 = cyx[0];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                ly[j] = __fadd_rn((float)y, __fmul_rn(ly[j], p.offset_mul));
+                lx[j] = __fadd_rn((float)(x0 + j), __fmul_rn(lx[j], p.offset_mul));
+                const float dy = __fsub_rn(c0.x, ly[j]), dx = __fsub_rn(c0.y, lx[j]);
+                bd2[j] = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+                best[j] = 0;
+            }
+#pragma unroll 1
+            for (int k = 1; k < n; ++k) {
+                const float2 c = cyx[k];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float dy = __fsub_rn(c.x, ly[j]), dx = __fsub_rn(c.y, lx[j]);
+                    const float d2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+                    if (d2 < bd2[j]) {
+                        bool better = true;
+                        if (!(d2 < bd2[j] * 0.99999952316284179688f))                          // 1 - 2^-21: the 4-ulp band,
+                            better = __fsqrt_rn(d2) < __fsqrt_rn(bd2[j]);                      // compare the roots
+                        if (better) { bd2[j] = d2; best[j] = k; }
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (fgm >> j & 1) id[j] = best[j] + 1;
         }
         st_stream_u4(ins + (size_t)b * HW + pix,
                      make_uint4(id[0] | (id[1] << 16), id[2] | (id[3] << 16), id[4] | (id[5] << 16), id[6] | (id[7] << 16)));
@@ -336,14 +421,16 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
         if (C > 0 && io.eee && (io.eee_full || io.eee_onehot)) {
             float bestv[8];
             int bestc[8];
+            int x0e = x0;
+            asm volatile("" : "+r"(x0e));               // opaque: rebuild the row set-up here instead of keeping it live over the centre loop
+            const Row8 rowe(up, y, x0e);
             for (int c = 0; c < C; ++c) {
                 const float *ep = io.eee + ((size_t)b * C + c) * hw;
                 float v[8];
+                sample8<S4>(up, rowe, ep, y, x0, v);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    v[j] = up.at(ep, y, x0 + j);
+                for (int j = 0; j < 8; ++j)
                     if (c == 0 || v[j] > bestv[j]) { bestv[j] = v[j]; bestc[j] = c; }   // first maximum wins
-                }
                 if (io.eee_full) {
                     float *o = io.eee_full + ((size_t)b * C + c) * HW + pix;
                     st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
@@ -585,7 +672,10 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
         if (int rc = check_launch("center_select_kernel")) return rc;
     }
     dim3 pgrid(cdiv(p.W, P_TW), cdiv(p.H, P_TH), p.B);
-    group_kernel<<<pgrid, P_THREADS, (3 * (size_t)p.top_k + 1) * 4, st>>>(p, io, io.n_centers, ws.ins, ws.area);
+    if (p.scale == 4)
+        group_kernel<true><<<pgrid, P_THREADS, (3 * (size_t)p.top_k + 1) * 4, st>>>(p, io, io.n_centers, ws.ins, ws.area);
+    else
+        group_kernel<false><<<pgrid, P_THREADS, (3 * (size_t)p.top_k + 1) * 4, st>>>(p, io, io.n_centers, ws.ins, ws.area);
     if (int rc = check_launch("group_kernel")) return rc;
     relabel_kernel<<<p.B, SEL_THREADS, 0, st>>>(p, io.n_centers, ws.area, ws.newid, ws.n_inst, ws.has_stuff);
     if (int rc = check_launch("relabel_kernel")) return rc;

@@ -68,28 +68,78 @@ class HotPath:
     LAUNCHES = dict(encode=2, boundary=1, post=7, msda_layer=1)
 
     # --- end to end: host buffers in, host results out ------------------------------------------
-    def refine_batch_host(self, masks_host, head_host, out_host=None):
-        """The end-to-end call: host buffers in, host results out, everything on the current stream.
+    def _staging(self, masks_host, head_host):
+        """Persistent device staging buffers, pinned result buffers, copy streams and events, keyed by shape."""
+        key = (tuple(masks_host.shape),) + tuple((k, tuple(v.shape)) for k, v in sorted(head_host.items()))
+        st = getattr(self, "_stage", None)
+        if st is None or st["key"] != key:
+            dev = self.device
+            B, K, H, W = masks_host.shape
+            slab = self.cfg.max_instances_per_image
+            pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
+            st = dict(key=key, masks=torch.empty(masks_host.shape, dtype=torch.uint8, device=dev),
+                      head={k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in head_host.items()},
+                      h2d=torch.cuda.Stream(device=dev), d2h=torch.cuda.Stream(device=dev), free=None,
+                      out=dict(label_map=pin((B, H, W), torch.int32), boundary=pin((B, H, W), torch.uint8),
+                               inst_start=pin((B,), torch.int32), inst_counts=pin((B,), torch.int32),
+                               labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
+                               boxes=pin((B * slab, 4), torch.float32)))
+            self._stage = st
+        return st
+
+    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8):
+        """The end-to-end call: host buffers in, host results out.
 
         masks_host: pinned uint8 [B,K,H,W]; head_host: dict of pinned float32 head outputs (what the
-        network hands to post-processing).  Returns (host dict, device results): label_map [B,H,W] int32
-        (0 = void, j+1 = j-th refined instance of the frame — the lossless compact form of the
-        reference's pred_masks), per-instance labels / scores / boxes / offsets and the union
-        boundary [B,H,W] uint8 of the initial masks.  The host tensors are pinned and reused between
-        calls; they are valid after the caller synchronises the stream.
+        network hands to post-processing).  The batch is cut into chunks of `chunk_frames` frames (frames are
+        independent — the reference itself is batch 1, eval/run_eval.py:72) and pipelined over three streams:
+        host->device copies of chunk c+1 (copy stream) run under the kernels of chunk c (the caller's current
+        stream) and the device->host copies of chunk c-1 (second copy stream), so the call costs about the PCIe
+        time of the masks instead of copies + kernels.  Returns (host dict, device results per chunk):
+        label_map [B,H,W] int32 (0 = void, j+1 = j-th refined instance of the frame — the lossless compact
+        form of the reference's pred_masks), boundary [B,H,W] uint8 (union boundary of the initial
+        masks), inst_start / inst_counts [B] int32 (frame b's instances are rows inst_start[b] ... +inst_counts[b]
+        of labels / scores / boxes; every chunk owns a slab of chunk_frames * max_instances_per_image rows).
+        The host tensors are pinned and reused between calls; they are valid once the caller has synchronised
+        the current stream (which this call makes wait for both copy streams).
         """
         dev = self.device
-        masks = masks_host.to(dev, non_blocking=True)
-        head = {k: v.to(dev, non_blocking=True) for k, v in head_host.items()}
-        enc, per, uni, fg = self.encode_and_boundary(masks)
-        r = self.post(head)
-        src = dict(label_map=r["label_map"], inst_offsets=r["inst_offsets"], labels=r["labels"], scores=r["scores"],
-                   boxes=r["boxes"], boundary=uni)
-        if out_host is None:
-            out_host = getattr(self, "_out_host", None)
-        if out_host is None or any(out_host[k].shape != v.shape for k, v in src.items()):
-            out_host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in src.items()}
-            self._out_host = out_host
-        for k, v in src.items():
-            out_host[k].copy_(v, non_blocking=True)
-        return out_host, (enc, per, r)
+        st = self._staging(masks_host, head_host)
+        out = st["out"] if out_host is None else out_host
+        cur = torch.cuda.current_stream(dev)
+        h2d, d2h = st["h2d"], st["d2h"]
+        B = masks_host.shape[0]
+        slab = self.cfg.max_instances_per_image
+        if st["free"] is not None:
+            h2d.wait_event(st["free"])            # the previous call's kernels have finished reading the staging buffers
+        d2h.wait_stream(cur)                      # ... and whoever consumed the pinned results was ordered on `cur`
+        keep = []
+        for c0 in range(0, B, chunk_frames):
+            c1 = min(B, c0 + chunk_frames)
+            with torch.cuda.stream(h2d):
+                st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
+                for k, v in head_host.items():
+                    st["head"][k][c0:c1].copy_(v[c0:c1], non_blocking=True)
+                ready = h2d.record_event()
+            cur.wait_event(ready)
+            enc, per, uni, fg = self.encode_and_boundary(st["masks"][c0:c1])
+            r = self.post({k: v[c0:c1] for k, v in st["head"].items()})
+            off = r["inst_offsets"]
+            counts = off[1:] - off[:-1]
+            start = off[:-1] + c0 * slab
+            done = cur.record_event()
+            n = (c1 - c0) * slab
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(done)
+                out["label_map"][c0:c1].copy_(r["label_map"], non_blocking=True)
+                out["boundary"][c0:c1].copy_(uni, non_blocking=True)
+                out["inst_start"][c0:c1].copy_(start, non_blocking=True)
+                out["inst_counts"][c0:c1].copy_(counts, non_blocking=True)
+                out["labels"][c0 * slab:c0 * slab + n].copy_(r["labels"][:n], non_blocking=True)
+                out["scores"][c0 * slab:c0 * slab + n].copy_(r["scores"][:n], non_blocking=True)
+                out["boxes"][c0 * slab:c0 * slab + n].copy_(r["boxes"][:n], non_blocking=True)
+            keep.append((enc, per, r, start, counts))
+        st["free"] = cur.record_event()
+        cur.wait_stream(d2h)
+        self._keep = keep                         # device results stay alive until the next call replaces them
+        return out, keep

@@ -254,6 +254,34 @@ def test_reference_named_post_processing_functions():
         pp.get_panoptic_segmentation(fgseg, c[0], o, dict({1: 0}).values(), 1000, 2048, -1)
 
 
+def test_group_pixels_tie_band_first_centre_wins():
+    """Pixels landing within a few ulp of the bisector of two centres: squared distances differ while the rounded
+    roots are equal for ~10 % of them, a tie torch.argmin gives to the EARLIER centre (post_processing.py:71-75).
+    The kernel compares squared distances and takes the roots only inside that band (csrc/post.cu: group_kernel)."""
+    from quber_b200 import post_processing as pp
+    H, W = 64, 128
+    rng = np.random.default_rng(3)
+    yy, xx = np.meshgrid(np.arange(H, dtype=np.float32), np.arange(W, dtype=np.float32), indexing="ij")
+    steps = rng.integers(-6, 7, size=(H, W)).astype(np.float32)
+    tly = np.float32(30.0) + steps * np.float32(1.9073486e-06)
+    tlx = rng.uniform(0, 100, size=(H, W)).astype(np.float32)
+    off = np.stack([tly - yy, tlx - xx]).astype(np.float32)
+    ly, lx = (yy + off[0]).astype(np.float32), (xx + off[1]).astype(np.float32)
+
+    def d2(c):
+        dy, dx = np.float32(c[0]) - ly, np.float32(c[1]) - lx
+        return (dx.astype(np.float64) ** 2 + (dy * dy).astype(np.float64)).astype(np.float32)
+
+    a, b = d2((20, 30)), d2((40, 30))
+    assert int(((a != b) & (np.sqrt(a) == np.sqrt(b))).sum()) > 300          # the band is exercised
+    for ctr in ([[20, 30], [40, 30]], [[40, 30], [20, 30]], [[20, 30], [40, 30], [20, 30], [40, 30], [3, 3]]):
+        ctr = np.asarray(ctr, np.int32)
+        ref = oracle.group_pixels(ctr, off)
+        got = pp.group_pixels(cu(ctr.astype(np.int64)), cu(off))[0].cpu().numpy()
+        np.testing.assert_array_equal(got, ref)
+        assert set(np.unique(ref)) <= {1, 2}                                  # duplicates never beat their first copy
+
+
 def test_reference_named_boundary_functions_numpy():
     from quber_b200 import boundary as bd
     g = golden("boundary.npz")
