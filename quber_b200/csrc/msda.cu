@@ -87,7 +87,7 @@ template <> struct Lane<__nv_bfloat16> {
 // the group with six width-LPG shuffles and every lane issues four unconditional 128-bit loads and four FMAs
 // per channel.  (w_i * a) * v_i differs from the reference's (sum_i w_i v_i) * a by rounding only
 // (measured: <= 6e-9 abs on the C2 inputs against the oracle, tolerance 1e-3).
-template <int D, typename VT, int MINB>
+template <int D, typename VT, int MINB, bool LDSB>
 __global__ void __launch_bounds__(256, MINB)
 msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
                           const float *__restrict__ loc, const float *__restrict__ attn, int S, int M, int L, int Q, int P,
@@ -96,6 +96,13 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
     constexpr int LPG = D / CPL;
     constexpr int GPB = 256 / LPG;
     __shared__ int s_h[MSDA_MAX_L], s_w[MSDA_MAX_L], s_start[MSDA_MAX_L];
+    // LDSB: the prepared taps are broadcast through shared memory (one LDS.128 + one LDS.64 per tap, every lane of a
+    // group reading the same address) instead of six shuffles — fewer L1 data-pipe wavefronts, the limiter of this
+    // kernel (fp32, D = 32: 527 -> 497 us at C2).  Per warp and group g: recA[g * (LPG + 1) + t] = (o1, o3, w1, w2),
+    // recB[g * LPG + t] = (w3, w4); the +1 pad keeps the per-group broadcast addresses in distinct banks.
+    constexpr int GPW = 32 / LPG;                       // groups per warp
+    __shared__ __align__(16) uint4 s_recA[LDSB ? 8 * GPW * (LPG + 1) : 1];
+    __shared__ __align__(8) float2 s_recB[LDSB ? 8 * 32 : 1];
     const int tid = threadIdx.x;
     const int lane = tid % LPG, grp = tid / LPG;
     const int m = blockIdx.y, b = blockIdx.z;
@@ -147,13 +154,28 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
         }
         if (tap + LPG < LP) { raw_xy = ld_stream_u2(lp + 2 * (tap + LPG)); raw_a = ld_stream_u1(ap + tap + LPG); }
         const int nt = min(LPG, LP - s0);
+        uint4 *recA = s_recA + (LDSB ? (tid >> 5) * (GPW * (LPG + 1)) + ((tid & 31) / LPG) * (LPG + 1) : 0);
+        float2 *recB = s_recB + (LDSB ? (tid >> 5) * 32 + ((tid & 31) / LPG) * LPG : 0);
+        if (LDSB) {
+            recA[lane] = make_uint4(o1, o3, __float_as_uint(w1), __float_as_uint(w2));
+            recB[lane] = make_float2(w3, w4);
+            __syncwarp();
+        }
 #pragma unroll
         for (int j = 0; j < LPG; ++j) {
             if (j < nt) {
-                const uint32_t bo1 = __shfl_sync(0xffffffffu, o1, j, LPG);
-                const uint32_t bo3 = __shfl_sync(0xffffffffu, o3, j, LPG);
-                const float b1 = __shfl_sync(0xffffffffu, w1, j, LPG), b2 = __shfl_sync(0xffffffffu, w2, j, LPG);
-                const float b3 = __shfl_sync(0xffffffffu, w3, j, LPG), b4 = __shfl_sync(0xffffffffu, w4, j, LPG);
+                uint32_t bo1, bo3;
+                float b1, b2, b3, b4;
+                if (LDSB) {
+                    const uint4 ra = recA[j];
+                    const float2 rb = recB[j];
+                    bo1 = ra.x; bo3 = ra.y; b1 = __uint_as_float(ra.z); b2 = __uint_as_float(ra.w); b3 = rb.x; b4 = rb.y;
+                } else {
+                    bo1 = __shfl_sync(0xffffffffu, o1, j, LPG);
+                    bo3 = __shfl_sync(0xffffffffu, o3, j, LPG);
+                    b1 = __shfl_sync(0xffffffffu, w1, j, LPG); b2 = __shfl_sync(0xffffffffu, w2, j, LPG);
+                    b3 = __shfl_sync(0xffffffffu, w3, j, LPG); b4 = __shfl_sync(0xffffffffu, w4, j, LPG);
+                }
                 const uint32_t dx = (uint32_t)((int32_t)bo1 >> 31) & MDu;
                 uint32_t a1 = bo1 & 0x7fffffffu;
                 asm volatile("" : "+r"(a1));            // opaque, or the mask is folded into a 64-bit shift/add sequence
@@ -166,6 +188,7 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
                     acc[c] = fmaf(b4, v4[c], fmaf(b3, v3[c], fmaf(b2, v2[c], fmaf(b1, v1[c], acc[c]))));
             }
         }
+        if (LDSB) __syncwarp();
     }
     if (qreal < Q) Lane<VT>::store(out + qm * D + lane * CPL, acc);
 }
@@ -223,10 +246,16 @@ static int launch_vec(const void *value, const int64_t *shapes, const int64_t *s
     dim3 grid(cdiv(Q, GPB), M, B);
     const VT *v = static_cast<const VT *>(value);
     VT *o = static_cast<VT *>(out);
+    // QUBER_MSDA_BCAST=shfl selects the shuffle broadcast (kept for A/B measurements); default: shared memory.
+    static const bool shfl = [] { const char *e = getenv("QUBER_MSDA_BCAST"); return e && e[0] == 's'; }();
+    if (!shfl) {
+        msda_forward_kernel<D, VT, 5, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o);
+        return check_launch("msda_forward_kernel");
+    }
     switch (msda_minb()) {
-        default: msda_forward_kernel<D, VT, 5><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
-        case 6: msda_forward_kernel<D, VT, 6><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
-        case 4: msda_forward_kernel<D, VT, 4><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+        default: msda_forward_kernel<D, VT, 5, false><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+        case 6: msda_forward_kernel<D, VT, 6, false><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+        case 4: msda_forward_kernel<D, VT, 4, false><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
     }
     return check_launch("msda_forward_kernel");
 }

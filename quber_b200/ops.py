@@ -64,6 +64,19 @@ def encode_initial_masks(masks, sigma=10):
     return out
 
 
+def encode_initial_masks_any_width(masks, sigma=10):
+    """encode_initial_masks for frames whose width is not a multiple of 16 (armbench 750x1333): zero columns are
+    appended, which changes neither a centroid nor a paste inside the frame; only the x-offset plane is normalised by
+    the padded width and is rescaled here (float64, then one float32 rounding: <= 1 ulp from the reference value)."""
+    B, K, H, W = masks.shape
+    pad = (-W) % 16
+    if not pad:
+        return encode_initial_masks(masks, sigma)
+    enc = encode_initial_masks(torch.nn.functional.pad(masks, (0, pad)).contiguous(), sigma)[..., :W].contiguous()
+    enc[:, 2] = (enc[:, 2].double() * ((W + pad) / W)).float()
+    return enc
+
+
 def mask_boundary(masks, d, per_instance=True, union=True, fg=True):
     """explicit_error_estimation/util.py:62-99 for a batch: masks [B,K,H,W] uint8 ->
     (per-instance boundary [B,K,H,W] | None, union boundary [B,H,W] | None, fg [B,H,W] | None)."""

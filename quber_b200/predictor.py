@@ -68,16 +68,7 @@ class MaskRefinerPredictor:
         B, K, H, W = m.shape
         if K == 0:
             return torch.zeros((B, 3, H, W), dtype=torch.float32, device=m.device)
-        pad = (-W) % 16
-        if pad:
-            # zero columns change neither a centroid nor a paste inside the frame; only the x-offset plane is
-            # normalised by the padded width and is rescaled (float64, then one float32 rounding: <= 1 ulp)
-            m = torch.nn.functional.pad(m, (0, pad))
-        enc = ops.encode_initial_masks(m.contiguous(), self.sigma)
-        if pad:
-            enc = enc[..., :W].contiguous()
-            enc[:, 2] = (enc[:, 2].double() * ((W + pad) / W)).float()
-        return enc
+        return ops.encode_initial_masks_any_width(m.contiguous(), self.sigma)
 
     def predict_batch(self, rgb_imgs, depth_imgs, perturbed_masks_list):
         """Frames of equal size: lists of HxWx3 uint8 RGB / depth images and [N_i,H,W] masks -> list of output dicts."""

@@ -279,7 +279,7 @@ def test_group_pixels_tie_band_first_centre_wins():
         ref = oracle.group_pixels(ctr, off)
         got = pp.group_pixels(cu(ctr.astype(np.int64)), cu(off))[0].cpu().numpy()
         np.testing.assert_array_equal(got, ref)
-        assert set(np.unique(ref)) <= {1, 2}                                  # duplicates never beat their first copy
+        assert not np.isin(ref, (3, 4)).any()                                 # duplicates never beat their first copy
 
 
 def test_reference_named_boundary_functions_numpy():
