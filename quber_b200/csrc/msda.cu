@@ -99,10 +99,11 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
     // LDSB: the prepared taps are broadcast through shared memory (one LDS.128 + one LDS.64 per tap, every lane of a
     // group reading the same address) instead of six shuffles — fewer L1 data-pipe wavefronts, the limiter of this
     // kernel (fp32, D = 32: 527 -> 497 us at C2).  Per warp and group g: recA[g * (LPG + 1) + t] = (o1, o3, w1, w2),
-    // recB[g * LPG + t] = (w3, w4); the +1 pad keeps the per-group broadcast addresses in distinct banks.
+    // recB[g * (LPG + 1) + t] = (w3, w4); the +1 pad keeps the per-group broadcast addresses in distinct banks (an unpadded
+    // recB cost one bank conflict per tap: ncu l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_ld, r01 v7).
     constexpr int GPW = 32 / LPG;                       // groups per warp
     __shared__ __align__(16) uint4 s_recA[LDSB ? 8 * GPW * (LPG + 1) : 1];
-    __shared__ __align__(8) float2 s_recB[LDSB ? 8 * 32 : 1];
+    __shared__ __align__(8) float2 s_recB[LDSB ? 8 * GPW * (LPG + 1) : 1];
     const int tid = threadIdx.x;
     const int lane = tid % LPG, grp = tid / LPG;
     const int m = blockIdx.y, b = blockIdx.z;
@@ -155,7 +156,7 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
         if (tap + LPG < LP) { raw_xy = ld_stream_u2(lp + 2 * (tap + LPG)); raw_a = ld_stream_u1(ap + tap + LPG); }
         const int nt = min(LPG, LP - s0);
         uint4 *recA = s_recA + (LDSB ? (tid >> 5) * (GPW * (LPG + 1)) + ((tid & 31) / LPG) * (LPG + 1) : 0);
-        float2 *recB = s_recB + (LDSB ? (tid >> 5) * 32 + ((tid & 31) / LPG) * LPG : 0);
+        float2 *recB = s_recB + (LDSB ? (tid >> 5) * (GPW * (LPG + 1)) + ((tid & 31) / LPG) * (LPG + 1) : 0);
         if (LDSB) {
             recA[lane] = make_uint4(o1, o3, __float_as_uint(w1), __float_as_uint(w2));
             recB[lane] = make_float2(w3, w4);
