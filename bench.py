@@ -165,8 +165,13 @@ def run_ours(args):
         r = hp.post(d["head"])
         mark()
         if world > 1:
+            # the one collective of the path, on a side stream so that it runs under the next step's kernels
             counts = r["inst_offsets"][1:] - r["inst_offsets"][:-1]
-            sharding.gather_label_maps(r["label_map"], counts, out=gather_buf)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                sharding.gather_label_maps(r["label_map"], counts, out=gather_buf)
+            r["label_map"].record_stream(side)
+            counts.record_stream(side)
         return r
 
     def _ev():
@@ -197,6 +202,8 @@ def run_ours(args):
         r = step(i, True, evs)
         all_evs.append(evs)
         inst_counts.append(r["inst_offsets"][-1:])       # device tensor, read after the timed region
+    if world > 1:
+        torch.cuda.current_stream().wait_stream(side)       # the last gather is inside the timed region
     e1 = _ev()
     barrier()
     t1w = time.time()
@@ -288,11 +295,55 @@ def run_ours(args):
                      "avg_launch_ms": dv["ms"]},
         "roofline_all": roof_all,
     }
+    if world == 1 and not args.no_network:
+        enc0 = ops.encode_initial_masks(sets[0]["masks"], hp.cfg.sigma)
+        line["network"] = network_side_measurement(dev, enc0, n_inst_total / args.steps, ms / args.steps)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(budget_s=args.cpu_budget)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------------------------- network (disclosed aside)
+def network_side_measurement(dev, enc, inst_per_step, hot_ms):
+    """SURVEY §8-d's "Net" stage, reported NEXT TO the headline and never inside it: the cuDNN network between
+    encode and decode (two ResNet-50 streams, DeepLabV3+ decoder, hierarchical fusion heads; random-init weights of the
+    uoais-sim config) on the same 32-frame batch, fp32 and bf16-autocast, and the instances/s the step would give
+    with it added (random-init predictors yield no instance, so the post stage keeps its synthetic head outputs)."""
+    import torch
+    from quber_b200 import config as qcfg, ops
+    from quber_b200.meta_arch import build_model
+    out = {}
+    try:
+        cfg = qcfg.get_cfg()
+        cfg.merge_from_file(os.path.join(ROOT, "configs", "mask-refiner-rgbd-concat-l2-gn-hf-b-fco-l3-b8.yaml"))
+        cfg.MODEL.DEVICE = str(dev)
+        torch.manual_seed(0)
+        model = build_model(cfg, "fp32").eval()
+        g = torch.Generator(device=dev).manual_seed(0)
+        img = torch.randint(0, 256, (B, 6, H, W), dtype=torch.uint8, device=dev, generator=g)
+        x = ops.pack_input(img, enc, model.pixel_mean, model.pixel_std)
+        for prec in ("fp32", "bf16"):
+            model.set_precision(prec)
+            with torch.no_grad():
+                for _ in range(2):
+                    model.network_logits(x)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(3):
+                    model.network_logits(x)
+                e1.record()
+                torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 3
+            out[f"ms_per_step_{prec}"] = ms
+            out[f"instances_per_sec_with_network_{prec}"] = inst_per_step / ((hot_ms + ms) * 1e-3)
+        out["note"] = ("cuDNN/cuBLAS network forward for the same 32 frames, outside `value` and outside the reference arm "
+                       "(BASELINE.json times the CPU path without the network); tf32 off for fp32")
+    except Exception as e:      # the aside must never cost the headline line
+        out["error"] = f"{type(e).__name__}: {e}"[:300]
+    return out
 
 
 # --------------------------------------------------------------------------------------------- CPU legs
@@ -389,6 +440,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-network", action="store_true", help="skip the disclosed network-stage aside")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

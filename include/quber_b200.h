@@ -209,6 +209,23 @@ int quber_gemm_bias_act(const void *A, const void *W, const float *bias, void *C
                         int ldw, int ldc, int in_dtype, int out_dtype, int act, void *stream);
 int quber_gemm_timeouts(void);
 
+/* ---------------------------------------------------------------------------------------------
+ * GroupNorm (+ ReLU), inference forward — replaces nn.GroupNorm(G, C) followed by ReLU wherever the network uses
+ *     norm "GN": detectron2 Conv2d(norm=GN, activation=relu) in the decoder and prediction heads
+ *     (maskrefiner/modeling/mask_refiner/model.py:386-403, 431-451) and the nn.Conv2d -> nn.GroupNorm -> nn.ReLU
+ *     fusion blocks of the RGB-D backbone (maskrefiner/modeling/backbone/resnet.py:466-479).  PyTorch runs it as
+ *     native_group_norm + clamp_min (+ dtype casts under autocast).
+ *   x, y   dev [N,C,H*W] (layout 0, NCHW) or [N,H*W,C] (layout 1, channels-last); dtype 0: float32, 1: bfloat16;
+ *          y may alias x.  gamma, beta dev [C] float32.  Statistics and arithmetic in fp32 (combined in double),
+ *          biased variance, eps as nn.GroupNorm.  relu != 0 applies max(., 0).
+ *   Needs H*W % (16 / sizeof(dtype)) == 0 for layout 0, C % (16 / sizeof(dtype)) == 0 for layout 1
+ *   (QUBER_E_UNSUPPORTED otherwise), 16-byte aligned x, y, workspace.  Deterministic (no floating-point atomics).
+ * ------------------------------------------------------------------------------------------- */
+size_t quber_group_norm_workspace_bytes(int N, int C, int HW, int G, int layout);
+int quber_group_norm_relu(const void *x, void *y, const float *gamma, const float *beta, int N, int C, int HW, int G,
+                          float eps, int relu, int layout, int dtype, void *workspace, size_t workspace_bytes,
+                          void *stream);
+
 #ifdef __cplusplus
 }
 #endif

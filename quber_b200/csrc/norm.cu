@@ -1,0 +1,287 @@
+// GroupNorm (+ ReLU), inference forward, for the network side of the path.
+//
+// Reference: every `norm="GN"` convolution of the decoder / heads is detectron2 Conv2d -> nn.GroupNorm(32, C) ->
+// F.relu (maskrefiner/modeling/mask_refiner/model.py:386-403, 431-451 via get_norm), and the RGB-D fusion blocks are
+// nn.Conv2d -> nn.GroupNorm(32, C) -> nn.ReLU (maskrefiner/modeling/backbone/resnet.py:466-479).  PyTorch runs that as
+// RowwiseMoments + an elementwise apply + a separate clamp_min (plus fp32 <-> bf16 casts under autocast): 3 reads and
+// 2 writes of the activation.  Here: one read for the statistics, one read + one write for normalise + affine + ReLU,
+// for NCHW and channels-last (NHWC) tensors, fp32 or bf16 storage, fp32 arithmetic.
+//
+// Deterministic: per-tile partial sums are combined in a fixed order (no floating-point atomics).  Sums are taken
+// relative to a per-(sample, group) pivot (the group's first element), so var = (S2 - S1^2/n)/n does not cancel when
+// |mean| >> std; the final combine over tiles is in double.  HBM-bound: 2 reads + 1 write of the tensor.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace quber {
+
+constexpr int GN_THREADS = 256;
+constexpr int GN_TILE_PIX = 128;       // NHWC: pixels per CTA
+constexpr int GN_TILE_ELEMS = 16384;   // NCHW: elements of one (sample, group) slice per CTA
+
+template <typename T> struct Vec;      // one 16-byte access
+template <> struct Vec<float> {
+    static constexpr int N = 4;
+    static __device__ __forceinline__ void load(const float *p, float *v) {
+        const float4 r = *reinterpret_cast<const float4 *>(p);
+        v[0] = r.x; v[1] = r.y; v[2] = r.z; v[3] = r.w;
+    }
+    static __device__ __forceinline__ void store(float *p, const float *v) {
+        *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    static __device__ __forceinline__ float one(const float *p) { return *p; }
+};
+template <> struct Vec<__nv_bfloat16> {
+    static constexpr int N = 8;
+    static __device__ __forceinline__ void load(const __nv_bfloat16 *p, float *v) {
+        const uint4 r = *reinterpret_cast<const uint4 *>(p);
+        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            v[2 * i] = __uint_as_float(w[i] << 16);
+            v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        }
+    }
+    static __device__ __forceinline__ void store(__nv_bfloat16 *p, const float *v) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+            w[i] = *reinterpret_cast<const uint32_t *>(&h);
+        }
+        *reinterpret_cast<uint4 *>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    static __device__ __forceinline__ float one(const __nv_bfloat16 *p) { return __bfloat162float(*p); }
+};
+
+// fixed-order block reduction of (a, b); result valid in thread 0
+__device__ __forceinline__ void block_sum2(float &a, float &b, float *sm /* [2 * GN_THREADS / 32] */) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_down_sync(0xffffffffu, a, o);
+        b += __shfl_down_sync(0xffffffffu, b, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { sm[2 * w] = a; sm[2 * w + 1] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        a = 0.f; b = 0.f;
+        for (int i = 0; i < GN_THREADS / 32; ++i) { a += sm[2 * i]; b += sm[2 * i + 1]; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ NCHW
+// grid (T, N*G): partial (S1, S2) of tile t of the contiguous slice of (n, g), relative to the slice's first element
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS)
+gn_stats_nchw_kernel(const T *__restrict__ x, size_t slice, int tiles, float *__restrict__ part) {
+    constexpr int V = Vec<T>::N;
+    __shared__ float sm[2 * GN_THREADS / 32];
+    const size_t ng = blockIdx.y;
+    const T *p = x + ng * slice;
+    const float K = Vec<T>::one(p);
+    const size_t lo = (size_t)blockIdx.x * GN_TILE_ELEMS, hi = min(slice, lo + (size_t)GN_TILE_ELEMS);
+    float s1 = 0.f, s2 = 0.f;
+    for (size_t i = lo + (size_t)threadIdx.x * V; i < hi; i += (size_t)GN_THREADS * V) {     // slice % V == 0
+        float v[V];
+        Vec<T>::load(p + i, v);
+#pragma unroll
+        for (int j = 0; j < V; ++j) { const float d = v[j] - K; s1 += d; s2 = fmaf(d, d, s2); }
+    }
+    block_sum2(s1, s2, sm);
+    if (threadIdx.x == 0) {
+        part[(ng * tiles + blockIdx.x) * 2] = s1;
+        part[(ng * tiles + blockIdx.x) * 2 + 1] = s2;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS)
+gn_apply_nchw_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__restrict__ gamma, const float *__restrict__ beta,
+                     const float *__restrict__ stats /* [N*G][2] mean, rstd */, size_t slice, int HW, int cg, int G, int relu) {
+    constexpr int V = Vec<T>::N;
+    const size_t ng = blockIdx.y;
+    const int g = (int)(ng % G);
+    const float mean = stats[2 * ng], rstd = stats[2 * ng + 1];
+    const T *p = x + ng * slice;
+    T *q = y + ng * slice;
+    const size_t lo = (size_t)blockIdx.x * GN_TILE_ELEMS, hi = min(slice, lo + (size_t)GN_TILE_ELEMS);
+    for (size_t i = lo + (size_t)threadIdx.x * V; i < hi; i += (size_t)GN_THREADS * V) {     // HW % V == 0: one channel per vector
+        const int c = g * cg + (int)(i / HW);
+        const float a = rstd * __ldg(gamma + c), b = fmaf(-mean, a, __ldg(beta + c));
+        float v[V];
+        Vec<T>::load(p + i, v);
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            v[j] = fmaf(v[j], a, b);
+            if (relu) v[j] = fmaxf(v[j], 0.f);
+        }
+        Vec<T>::store(q + i, v);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ NHWC
+// grid (T, N): CTA = GN_TILE_PIX pixels x C channels.  Thread t owns the channel vectors {t, t + 256, ...} (< C / V)
+// when C / V >= 256, else vector t % (C / V) on pixel rows t / (C / V), t / (C / V) + rows, ...
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS)
+gn_stats_nhwc_kernel(const T *__restrict__ x, int HW, int C, int cg, int tiles, float *__restrict__ part /* [N][G][tiles][2] */) {
+    constexpr int V = Vec<T>::N;
+    extern __shared__ float acc[];                       // [rows][C][2]
+    const int n = blockIdx.y, t = blockIdx.x, tid = threadIdx.x;
+    const int TP = C / V;                                // vectors per pixel
+    const int rows = TP >= GN_THREADS ? 1 : GN_THREADS / TP;
+    const int row = TP >= GN_THREADS ? 0 : tid / TP;
+    const T *xs = x + (size_t)n * HW * C;
+    const int p0 = t * GN_TILE_PIX, p1 = min(HW, p0 + GN_TILE_PIX);
+    const int G = C / cg;
+    for (int ch = (TP >= GN_THREADS ? tid : tid % TP); ch < TP; ch += GN_THREADS) {
+        if (TP < GN_THREADS && tid >= rows * TP) break;  // 256 % TP != 0: surplus threads idle
+        float K[V], s1[V], s2[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            K[j] = Vec<T>::one(xs + ((ch * V + j) / cg) * cg);          // pivot: the group's first element of the sample
+            s1[j] = 0.f; s2[j] = 0.f;
+        }
+        for (int p = p0 + row; p < p1; p += rows) {
+            float v[V];
+            Vec<T>::load(xs + (size_t)p * C + ch * V, v);
+#pragma unroll
+            for (int j = 0; j < V; ++j) { const float d = v[j] - K[j]; s1[j] += d; s2[j] = fmaf(d, d, s2[j]); }
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            acc[((size_t)row * C + ch * V + j) * 2] = s1[j];
+            acc[((size_t)row * C + ch * V + j) * 2 + 1] = s2[j];
+        }
+        if (TP < GN_THREADS) break;
+    }
+    __syncthreads();
+    const int used_rows = TP >= GN_THREADS ? 1 : rows;
+    for (int g = tid; g < G; g += GN_THREADS) {          // fixed-order combine: rows, then the group's channels
+        float a = 0.f, b = 0.f;
+        for (int r = 0; r < used_rows; ++r)
+            for (int c = g * cg; c < (g + 1) * cg; ++c) { a += acc[((size_t)r * C + c) * 2]; b += acc[((size_t)r * C + c) * 2 + 1]; }
+        float *o = part + (((size_t)n * G + g) * tiles + t) * 2;
+        o[0] = a; o[1] = b;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS)
+gn_apply_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__restrict__ gamma, const float *__restrict__ beta,
+                     const float *__restrict__ stats, int HW, int C, int cg, int relu) {
+    constexpr int V = Vec<T>::N;
+    const int n = blockIdx.y, t = blockIdx.x, tid = threadIdx.x;
+    const int TP = C / V;
+    const int rows = TP >= GN_THREADS ? 1 : GN_THREADS / TP;
+    const int row = TP >= GN_THREADS ? 0 : tid / TP;
+    const int G = C / cg;
+    const size_t base = (size_t)n * HW * C;
+    const int p0 = t * GN_TILE_PIX, p1 = min(HW, p0 + GN_TILE_PIX);
+    for (int ch = (TP >= GN_THREADS ? tid : tid % TP); ch < TP; ch += GN_THREADS) {
+        if (TP < GN_THREADS && tid >= rows * TP) break;
+        float a[V], b[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            const int c = ch * V + j, g = c / cg;
+            const float mean = stats[((size_t)n * G + g) * 2], rstd = stats[((size_t)n * G + g) * 2 + 1];
+            a[j] = rstd * __ldg(gamma + c);
+            b[j] = fmaf(-mean, a[j], __ldg(beta + c));
+        }
+        for (int p = p0 + row; p < p1; p += rows) {
+            float v[V];
+            Vec<T>::load(x + base + (size_t)p * C + ch * V, v);
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+                v[j] = fmaf(v[j], a[j], b[j]);
+                if (relu) v[j] = fmaxf(v[j], 0.f);
+            }
+            Vec<T>::store(y + base + (size_t)p * C + ch * V, v);
+        }
+        if (TP < GN_THREADS) break;
+    }
+}
+
+// one thread per (n, g): combine the tile partials in double, in tile order
+template <typename T>
+__global__ void gn_finalize_kernel(const T *__restrict__ x, const float *__restrict__ part, int NG, int G, int tiles, double count,
+                                   size_t pivot_stride_n, size_t pivot_stride_g, float eps, float *__restrict__ stats) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= NG) return;
+    const int n = i / G, g = i % G;
+    const double K = (double)Vec<T>::one(x + (size_t)n * pivot_stride_n + (size_t)g * pivot_stride_g);
+    double s1 = 0.0, s2 = 0.0;
+    for (int t = 0; t < tiles; ++t) { s1 += (double)part[((size_t)i * tiles + t) * 2]; s2 += (double)part[((size_t)i * tiles + t) * 2 + 1]; }
+    const double m = s1 / count;
+    double var = s2 / count - m * m;                    // biased variance, as torch.nn.GroupNorm
+    if (var < 0.0) var = 0.0;
+    stats[2 * i] = (float)(K + m);
+    stats[2 * i + 1] = (float)(1.0 / sqrt(var + (double)eps));
+}
+
+static int gn_tiles(int C, int HW, int G, int layout) {
+    if (layout == 0) return (int)(((size_t)(C / G) * HW + GN_TILE_ELEMS - 1) / GN_TILE_ELEMS);
+    return (HW + GN_TILE_PIX - 1) / GN_TILE_PIX;
+}
+
+template <typename T>
+static int gn_run(const void *xv, void *yv, const float *gamma, const float *beta, int N, int C, int HW, int G, float eps, int relu,
+                  int layout, float *ws, cudaStream_t st) {
+    constexpr int V = Vec<T>::N;
+    const T *x = static_cast<const T *>(xv);
+    T *y = static_cast<T *>(yv);
+    const int cg = C / G, tiles = gn_tiles(C, HW, G, layout);
+    float *part = ws, *stats = ws + (size_t)N * G * tiles * 2;
+    const double count = (double)cg * HW;
+    if (layout == 0) {
+        if (HW % V != 0) return QUBER_E_UNSUPPORTED;
+        const size_t slice = (size_t)cg * HW;
+        dim3 grid(tiles, N * G);
+        gn_stats_nchw_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, slice, tiles, part);
+        if (int rc = check_launch("gn_stats_nchw_kernel")) return rc;
+        gn_finalize_kernel<T><<<cdiv(N * G, 128), 128, 0, st>>>(x, part, N * G, G, tiles, count, (size_t)C * HW, slice, eps, stats);
+        if (int rc = check_launch("gn_finalize_kernel")) return rc;
+        gn_apply_nchw_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, y, gamma, beta, stats, slice, HW, cg, G, relu);
+        return check_launch("gn_apply_nchw_kernel");
+    }
+    if (C % V != 0) return QUBER_E_UNSUPPORTED;
+    const int TP = C / V;
+    if (TP > GN_THREADS && TP % GN_THREADS != 0) return QUBER_E_UNSUPPORTED;
+    const int rows = TP >= GN_THREADS ? 1 : GN_THREADS / TP;
+    const size_t smem = (size_t)rows * C * 2 * sizeof(float);
+    if (smem > 48 * 1024) {
+        QUBER_CUDA_TRY(cudaFuncSetAttribute(gn_stats_nhwc_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    dim3 grid(tiles, N);
+    gn_stats_nhwc_kernel<T><<<grid, GN_THREADS, smem, st>>>(x, HW, C, cg, tiles, part);
+    if (int rc = check_launch("gn_stats_nhwc_kernel")) return rc;
+    gn_finalize_kernel<T><<<cdiv(N * G, 128), 128, 0, st>>>(x, part, N * G, G, tiles, count, (size_t)C * HW, (size_t)cg, eps, stats);
+    if (int rc = check_launch("gn_finalize_kernel")) return rc;
+    gn_apply_nhwc_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, y, gamma, beta, stats, HW, C, cg, relu);
+    return check_launch("gn_apply_nhwc_kernel");
+}
+
+}  // namespace quber
+
+extern "C" size_t quber_group_norm_workspace_bytes(int N, int C, int HW, int G, int layout) {
+    if (N <= 0 || C <= 0 || HW <= 0 || G <= 0 || C % G != 0 || (layout != 0 && layout != 1)) return 0;
+    return ((size_t)N * G * quber::gn_tiles(C, HW, G, layout) * 2 + (size_t)N * G * 2) * sizeof(float);
+}
+
+extern "C" int quber_group_norm_relu(const void *x, void *y, const float *gamma, const float *beta, int N, int C, int HW, int G,
+                                     float eps, int relu, int layout, int dtype, void *workspace, size_t workspace_bytes,
+                                     void *stream) {
+    using namespace quber;
+    if (!x || !y || !gamma || !beta || !workspace) return QUBER_E_INVALID;
+    if (N <= 0 || C <= 0 || HW <= 0 || G <= 0 || C % G != 0 || (layout != 0 && layout != 1) || (dtype != 0 && dtype != 1))
+        return QUBER_E_INVALID;
+    if (!aligned16(x) || !aligned16(y) || !aligned16(workspace)) return QUBER_E_ALIGN;
+    if (workspace_bytes < quber_group_norm_workspace_bytes(N, C, HW, G, layout)) return QUBER_E_WORKSPACE;
+    if (N > 65535 || (layout == 0 && (size_t)N * G > 65535)) return QUBER_E_UNSUPPORTED;
+    cudaStream_t st = (cudaStream_t)stream;
+    float *ws = static_cast<float *>(workspace);
+    if (dtype == 0) return gn_run<float>(x, y, gamma, beta, N, C, HW, G, eps, relu, layout, ws, st);
+    return gn_run<__nv_bfloat16>(x, y, gamma, beta, N, C, HW, G, eps, relu, layout, ws, st);
+}

@@ -96,6 +96,7 @@ class MaskRefiner(nn.Module):
         self.error_type = cfg.MODEL.INS_EMBED_HEAD.ERROR_TYPE
         self.common_stride = cfg.MODEL.INS_EMBED_HEAD.COMMON_STRIDE
         self.max_instances_per_image = 64
+        self.use_inference_plan = True      # folded BN + fused conv epilogues (network.Conv2d.plan); False = layer by layer
         self.set_precision(precision)
 
     def set_precision(self, precision):
@@ -134,12 +135,26 @@ class MaskRefiner(nn.Module):
         return torch.stack(out), sizes
 
     # ---- A3-A5: network ------------------------------------------------------------------------------
+    def _ensure_plan(self, device):
+        """(Re)build the convolutions' inference plan (network.prepare_inference) when the precision, the device or any
+        parameter / buffer changed since it was built (a checkpoint load, an in-place edit)."""
+        ver = sum(t._version for t in self.state_dict(keep_vars=True).values())
+        key = (self.precision, str(device), ver, self.training)
+        if getattr(self, "_plan_key", None) != key:
+            if self.training or not self.use_inference_plan:
+                network.drop_inference_plan(self)
+            else:
+                bf16 = self.precision == "bf16" and device.type == "cuda"
+                network.prepare_inference(self, torch.bfloat16 if bf16 else torch.float32, channels_last=bf16)
+            self._plan_key = key
+
     def network_logits(self, x):
         """[B,9,H,W] normalised input -> dict of 1/COMMON_STRIDE-resolution float32 logits (the head outputs
         before model.py:688-708's up-sampling)."""
+        self._ensure_plan(x.device)
         if self.precision == "bf16" and x.is_cuda:
             with torch.autocast("cuda", dtype=torch.bfloat16):
-                feats = self.backbone(x.contiguous(memory_format=torch.channels_last))
+                feats = self.backbone(x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
                 out = self.ins_embed_head.layers({k: v for k, v in feats.items()})
         else:
             feats = self.backbone(x)

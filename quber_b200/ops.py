@@ -265,6 +265,44 @@ def pack_input(image, offsets, mean, std):
     return out
 
 
+def group_norm_supported(x, groups):
+    """True when quber_group_norm_relu takes this tensor as it lies (CUDA, fp32 / bf16, dense NCHW or channels-last,
+    16-byte vectors along the contiguous dimension)."""
+    if not (isinstance(x, torch.Tensor) and x.is_cuda and x.dim() == 4 and x.dtype in (torch.float32, torch.bfloat16)):
+        return False
+    N, C, H, W = x.shape
+    v = 16 // x.element_size()
+    if C % groups or N == 0:
+        return False
+    if x.is_contiguous():
+        return (H * W) % v == 0 and N * groups <= 65535
+    if x.is_contiguous(memory_format=torch.channels_last):
+        tp = C // v
+        return C % v == 0 and (tp <= 256 or tp % 256 == 0)
+    return False
+
+
+def group_norm_relu(x, weight, bias, groups=32, eps=1e-5, relu=True, inplace=False):
+    """nn.GroupNorm(groups, C)(x) followed by ReLU (detectron2 Conv2d norm="GN" + F.relu, model.py:386-403;
+    resnet.py:466-479) in two passes over x (statistics; normalise + affine + ReLU).  x [N,C,H,W] float32 | bfloat16,
+    dense NCHW or channels-last; the result has x's dtype and memory format.  weight / bias [C] (any float dtype)."""
+    if not group_norm_supported(x, groups):
+        raise ValueError("group_norm_relu: unsupported tensor (needs a dense CUDA fp32/bf16 NCHW or channels-last tensor)")
+    N, C, H, W = x.shape
+    layout = 0 if x.is_contiguous() else 1
+    y = x if inplace else torch.empty_like(x)           # empty_like preserves the memory format
+    g = weight.detach().to(device=x.device, dtype=torch.float32).contiguous()
+    b = bias.detach().to(device=x.device, dtype=torch.float32).contiguous()
+    L = _lib.lib()
+    nbytes = L.quber_group_norm_workspace_bytes(N, C, H * W, groups, layout)
+    ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(L.quber_group_norm_relu(_ptr(x), _ptr(y), _ptr(g), _ptr(b), N, C, H * W, groups, float(eps), int(bool(relu)),
+                                           layout, 0 if x.dtype == torch.float32 else 1, _ptr(ws), nbytes, _stream()),
+                   "quber_group_norm_relu")
+    return y
+
+
 _FUSE_OPS = {"copy": 0, "sigmoid": 1, "softmax": 2}
 
 

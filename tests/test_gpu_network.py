@@ -248,3 +248,70 @@ def test_pixel_decoder_forward_features_shapes_and_precisions():
         outs[prec] = mask_features
     torch.testing.assert_close(outs["tf32"], outs["fp32"], rtol=0, atol=5e-2)
     assert (outs["bf16"] - outs["fp32"]).abs().mean() < 5e-2
+
+
+# ------------------------------------------------------------------ GroupNorm + ReLU (csrc/norm.cu)
+@pytest.mark.parametrize("C,H,W", [(32, 24, 40), (64, 30, 40), (128, 24, 40), (256, 12, 20), (512, 15, 20), (2048, 6, 8), (96, 8, 12)])
+@pytest.mark.parametrize("cl", [False, True])
+def test_group_norm_relu_matches_float64_reference(C, H, W, cl):
+    """nn.GroupNorm(32, C) + ReLU against a float64 torch reference: fp32 <= 2e-5 abs on unit-scale activations (torch's own
+    fp32 kernel is at the same distance), NCHW and channels-last, with a mean far from zero in half of the channels."""
+    g = torch.Generator(device=DEV).manual_seed(C + H)
+    x = torch.randn(3, C, H, W, device=DEV, generator=g) * 1.7
+    x[:, ::2] += 25.0                                                   # |mean| >> std inside every group
+    gn = torch.nn.GroupNorm(32, C).to(DEV)
+    gn.weight.data.uniform_(0.5, 1.5, generator=g); gn.bias.data.normal_(0, 0.5, generator=g)
+    if cl:
+        x = x.contiguous(memory_format=torch.channels_last)
+    if not ops.group_norm_supported(x, 32):
+        assert C == 96 and cl is True or (H * W) % 4 != 0
+        with pytest.raises(ValueError):
+            ops.group_norm_relu(x, gn.weight, gn.bias, 32)
+        return
+    ref = torch.relu(torch.nn.functional.group_norm(x.double(), 32, gn.weight.double(), gn.bias.double(), gn.eps))
+    out = ops.group_norm_relu(x, gn.weight, gn.bias, 32, gn.eps)
+    assert out.dtype == x.dtype and out.is_contiguous(memory_format=torch.channels_last if cl else torch.contiguous_format)
+    assert float((out.double() - ref).abs().max()) <= 2e-5
+    lin = ops.group_norm_relu(x, gn.weight, gn.bias, 32, gn.eps, relu=False)
+    ref_lin = torch.nn.functional.group_norm(x.double(), 32, gn.weight.double(), gn.bias.double(), gn.eps)
+    assert float((lin.double() - ref_lin).abs().max()) <= 2e-5
+    assert torch.equal(out, ops.group_norm_relu(x, gn.weight, gn.bias, 32, gn.eps))              # deterministic
+    y = x.clone(memory_format=torch.preserve_format)
+    assert ops.group_norm_relu(y, gn.weight, gn.bias, 32, gn.eps, inplace=True) is y and torch.equal(y, out)
+    # bf16 storage: same arithmetic on the bf16-rounded input, one bf16 rounding of the result
+    xb = x.bfloat16()
+    refb = torch.relu(torch.nn.functional.group_norm(xb.double(), 32, gn.weight.double(), gn.bias.double(), gn.eps))
+    if ops.group_norm_supported(xb, 32):
+        outb = ops.group_norm_relu(xb, gn.weight, gn.bias, 32, gn.eps)
+        assert outb.dtype == torch.bfloat16
+        assert float((outb.double() - refb).abs().max()) <= 2.0 ** -8 * float(refb.abs().max()) + 1e-3
+
+
+def test_group_norm_relu_full_size_and_many_tiles():
+    """C2 shapes (several tiles per sample): 128 x 120 x 160 channels-last bf16 and 256 x 120 x 160 NCHW fp32."""
+    g = torch.Generator(device=DEV).manual_seed(9)
+    for C, cl, dt, tol in [(128, True, torch.bfloat16, 2.5e-2), (256, False, torch.float32, 2e-5)]:
+        x = (torch.randn(2, C, 120, 160, device=DEV, generator=g) + 0.7).to(dt)
+        if cl:
+            x = x.contiguous(memory_format=torch.channels_last)
+        w = torch.rand(C, device=DEV, generator=g) + 0.5
+        b = torch.randn(C, device=DEV, generator=g)
+        ref = torch.relu(torch.nn.functional.group_norm(x.double(), 32, w.double(), b.double(), 1e-5))
+        out = ops.group_norm_relu(x, w, b, 32, 1e-5)
+        assert float((out.double() - ref).abs().max()) <= tol
+
+
+def test_network_inference_plan_matches_layer_by_layer():
+    """Folded BN + fused conv epilogues + the GroupNorm kernel against the layer-by-layer network (same weights), fp32."""
+    from quber_b200.meta_arch import build_model
+    torch.manual_seed(0)
+    model = build_model(_cfg(DEV), "fp32").eval()
+    _randomise(model, seed=3)
+    x = torch.randn(2, 9, 96, 128, device=DEV)
+    with torch.no_grad():
+        model.use_inference_plan = False
+        ref = model.network_logits(x)
+        model.use_inference_plan = True
+        out = model.network_logits(x)
+    for k in ref:
+        assert float((out[k] - ref[k]).abs().max()) <= 1e-3 * max(1.0, float(ref[k].abs().max())), k
