@@ -340,7 +340,7 @@ def network_side_measurement(dev, enc, inst_per_step, hot_ms):
             out[f"ms_per_step_{prec}"] = ms
             out[f"instances_per_sec_with_network_{prec}"] = inst_per_step / ((hot_ms + ms) * 1e-3)
         out["note"] = ("cuDNN/cuBLAS network forward for the same 32 frames, outside `value` and outside the reference arm "
-                       "(BASELINE.json times the CPU path without the network); tf32 off for fp32")
+                       "(BASELINE.json times the CPU path without the network); fp32 = PyTorch defaults (cuDNN convolutions may use TF32)")
     except Exception as e:      # the aside must never cost the headline line
         out["error"] = f"{type(e).__name__}: {e}"[:300]
     return out

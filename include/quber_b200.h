@@ -216,15 +216,25 @@ int quber_gemm_timeouts(void);
  *     fusion blocks of the RGB-D backbone (maskrefiner/modeling/backbone/resnet.py:466-479).  PyTorch runs it as
  *     native_group_norm + clamp_min (+ dtype casts under autocast).
  *   x, y   dev [N,C,H*W] (layout 0, NCHW) or [N,H*W,C] (layout 1, channels-last); dtype 0: float32, 1: bfloat16;
- *          y may alias x.  gamma, beta dev [C] float32.  Statistics and arithmetic in fp32 (combined in double),
+ *          y may alias x.  gamma, beta dev [C] float32.  pre_bias dev [C] float32 or NULL: the convolution's bias,
+ *          added to x before the statistics (GroupNorm(conv(x) + b) without a separate bias pass).  Statistics and arithmetic in fp32 (combined in double),
  *          biased variance, eps as nn.GroupNorm.  relu != 0 applies max(., 0).
  *   Needs H*W % (16 / sizeof(dtype)) == 0 for layout 0, C % (16 / sizeof(dtype)) == 0 for layout 1
  *   (QUBER_E_UNSUPPORTED otherwise), 16-byte aligned x, y, workspace.  Deterministic (no floating-point atomics).
  * ------------------------------------------------------------------------------------------- */
 size_t quber_group_norm_workspace_bytes(int N, int C, int HW, int G, int layout);
-int quber_group_norm_relu(const void *x, void *y, const float *gamma, const float *beta, int N, int C, int HW, int G,
+int quber_group_norm_relu(const void *x, void *y, const float *pre_bias, const float *gamma, const float *beta, int N, int C, int HW, int G,
                           float eps, int relu, int layout, int dtype, void *workspace, size_t workspace_bytes,
                           void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * quber_upsample_concat — one decoder step of detectron2's DeepLabV3PlusHead.layers (called at model.py:713):
+ *     y = F.interpolate(y, size=proj_x.shape[-2:], mode="bilinear", align_corners=False); torch.cat([proj_x, y], 1)
+ *   a dev [N,H,W,Ca] (proj_x; NULL iff Ca == 0), b dev [N,h,w,Cb] (y), out dev [N,H,W,Ca+Cb]: channels-last,
+ *   dtype 0: float32, 1: bfloat16 (fp32 blend).  Ca, Cb multiples of 16 / sizeof(dtype) (QUBER_E_UNSUPPORTED otherwise).
+ * ------------------------------------------------------------------------------------------- */
+int quber_upsample_concat(const void *a, const void *b, void *out, int N, int Ca, int Cb, int H, int W, int h, int w,
+                          int dtype, void *stream);
 
 #ifdef __cplusplus
 }

@@ -75,19 +75,22 @@ __device__ __forceinline__ void block_sum2(float &a, float &b, float *sm /* [2 *
 // grid (T, N*G): partial (S1, S2) of tile t of the contiguous slice of (n, g), relative to the slice's first element
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
-gn_stats_nchw_kernel(const T *__restrict__ x, size_t slice, int tiles, float *__restrict__ part) {
+gn_stats_nchw_kernel(const T *__restrict__ x, const float *__restrict__ pb, size_t slice, int HW, int cg, int G, int tiles,
+                     float *__restrict__ part) {
     constexpr int V = Vec<T>::N;
     __shared__ float sm[2 * GN_THREADS / 32];
     const size_t ng = blockIdx.y;
+    const int c0 = (int)(ng % G) * cg;
     const T *p = x + ng * slice;
-    const float K = Vec<T>::one(p);
+    const float K = Vec<T>::one(p) + (pb ? __ldg(pb + c0) : 0.f);
     const size_t lo = (size_t)blockIdx.x * GN_TILE_ELEMS, hi = min(slice, lo + (size_t)GN_TILE_ELEMS);
     float s1 = 0.f, s2 = 0.f;
     for (size_t i = lo + (size_t)threadIdx.x * V; i < hi; i += (size_t)GN_THREADS * V) {     // slice % V == 0
         float v[V];
         Vec<T>::load(p + i, v);
+        const float kb = K - (pb ? __ldg(pb + c0 + (int)(i / HW)) : 0.f);
 #pragma unroll
-        for (int j = 0; j < V; ++j) { const float d = v[j] - K; s1 += d; s2 = fmaf(d, d, s2); }
+        for (int j = 0; j < V; ++j) { const float d = v[j] - kb; s1 += d; s2 = fmaf(d, d, s2); }
     }
     block_sum2(s1, s2, sm);
     if (threadIdx.x == 0) {
@@ -98,8 +101,9 @@ gn_stats_nchw_kernel(const T *__restrict__ x, size_t slice, int tiles, float *__
 
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
-gn_apply_nchw_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__restrict__ gamma, const float *__restrict__ beta,
-                     const float *__restrict__ stats /* [N*G][2] mean, rstd */, size_t slice, int HW, int cg, int G, int relu) {
+gn_apply_nchw_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__restrict__ pb, const float *__restrict__ gamma,
+                     const float *__restrict__ beta, const float *__restrict__ stats /* [N*G][2] mean, rstd */, size_t slice, int HW,
+                     int cg, int G, int relu) {
     constexpr int V = Vec<T>::N;
     const size_t ng = blockIdx.y;
     const int g = (int)(ng % G);
@@ -109,7 +113,7 @@ gn_apply_nchw_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
     const size_t lo = (size_t)blockIdx.x * GN_TILE_ELEMS, hi = min(slice, lo + (size_t)GN_TILE_ELEMS);
     for (size_t i = lo + (size_t)threadIdx.x * V; i < hi; i += (size_t)GN_THREADS * V) {     // HW % V == 0: one channel per vector
         const int c = g * cg + (int)(i / HW);
-        const float a = rstd * __ldg(gamma + c), b = fmaf(-mean, a, __ldg(beta + c));
+        const float a = rstd * __ldg(gamma + c), b = fmaf((pb ? __ldg(pb + c) : 0.f) - mean, a, __ldg(beta + c));
         float v[V];
         Vec<T>::load(p + i, v);
 #pragma unroll
@@ -126,7 +130,8 @@ gn_apply_nchw_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
 // when C / V >= 256, else vector t % (C / V) on pixel rows t / (C / V), t / (C / V) + rows, ...
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
-gn_stats_nhwc_kernel(const T *__restrict__ x, int HW, int C, int cg, int tiles, float *__restrict__ part /* [N][G][tiles][2] */) {
+gn_stats_nhwc_kernel(const T *__restrict__ x, const float *__restrict__ pb, int HW, int C, int cg, int tiles,
+                     float *__restrict__ part /* [N][G][tiles][2] */) {
     constexpr int V = Vec<T>::N;
     extern __shared__ float acc[];                       // [rows][C][2]
     const int n = blockIdx.y, t = blockIdx.x, tid = threadIdx.x;
@@ -141,7 +146,9 @@ gn_stats_nhwc_kernel(const T *__restrict__ x, int HW, int C, int cg, int tiles, 
         float K[V], s1[V], s2[V];
 #pragma unroll
         for (int j = 0; j < V; ++j) {
-            K[j] = Vec<T>::one(xs + ((ch * V + j) / cg) * cg);          // pivot: the group's first element of the sample
+            const int c = ch * V + j, cf = (c / cg) * cg;
+            // pivot: the group's first element of the sample (bias included); the lane's own bias is folded into it
+            K[j] = Vec<T>::one(xs + cf) + (pb ? __ldg(pb + cf) - __ldg(pb + c) : 0.f);
             s1[j] = 0.f; s2[j] = 0.f;
         }
         for (int p = p0 + row; p < p1; p += rows) {
@@ -170,8 +177,8 @@ gn_stats_nhwc_kernel(const T *__restrict__ x, int HW, int C, int cg, int tiles, 
 
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
-gn_apply_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__restrict__ gamma, const float *__restrict__ beta,
-                     const float *__restrict__ stats, int HW, int C, int cg, int relu) {
+gn_apply_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__restrict__ pb, const float *__restrict__ gamma,
+                     const float *__restrict__ beta, const float *__restrict__ stats, int HW, int C, int cg, int relu) {
     constexpr int V = Vec<T>::N;
     const int n = blockIdx.y, t = blockIdx.x, tid = threadIdx.x;
     const int TP = C / V;
@@ -188,7 +195,7 @@ gn_apply_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
             const int c = ch * V + j, g = c / cg;
             const float mean = stats[((size_t)n * G + g) * 2], rstd = stats[((size_t)n * G + g) * 2 + 1];
             a[j] = rstd * __ldg(gamma + c);
-            b[j] = fmaf(-mean, a[j], __ldg(beta + c));
+            b[j] = fmaf((pb ? __ldg(pb + c) : 0.f) - mean, a[j], __ldg(beta + c));
         }
         for (int p = p0 + row; p < p1; p += rows) {
             float v[V];
@@ -206,12 +213,13 @@ gn_apply_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
 
 // one thread per (n, g): combine the tile partials in double, in tile order
 template <typename T>
-__global__ void gn_finalize_kernel(const T *__restrict__ x, const float *__restrict__ part, int NG, int G, int tiles, double count,
-                                   size_t pivot_stride_n, size_t pivot_stride_g, float eps, float *__restrict__ stats) {
+__global__ void gn_finalize_kernel(const T *__restrict__ x, const float *__restrict__ pb, int cg, const float *__restrict__ part, int NG,
+                                   int G, int tiles, double count, size_t pivot_stride_n, size_t pivot_stride_g, float eps,
+                                   float *__restrict__ stats) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= NG) return;
     const int n = i / G, g = i % G;
-    const double K = (double)Vec<T>::one(x + (size_t)n * pivot_stride_n + (size_t)g * pivot_stride_g);
+    const double K = (double)(Vec<T>::one(x + (size_t)n * pivot_stride_n + (size_t)g * pivot_stride_g) + (pb ? pb[g * cg] : 0.f));
     double s1 = 0.0, s2 = 0.0;
     for (int t = 0; t < tiles; ++t) { s1 += (double)part[((size_t)i * tiles + t) * 2]; s2 += (double)part[((size_t)i * tiles + t) * 2 + 1]; }
     const double m = s1 / count;
@@ -227,7 +235,7 @@ static int gn_tiles(int C, int HW, int G, int layout) {
 }
 
 template <typename T>
-static int gn_run(const void *xv, void *yv, const float *gamma, const float *beta, int N, int C, int HW, int G, float eps, int relu,
+static int gn_run(const void *xv, void *yv, const float *pb, const float *gamma, const float *beta, int N, int C, int HW, int G, float eps, int relu,
                   int layout, float *ws, cudaStream_t st) {
     constexpr int V = Vec<T>::N;
     const T *x = static_cast<const T *>(xv);
@@ -239,11 +247,11 @@ static int gn_run(const void *xv, void *yv, const float *gamma, const float *bet
         if (HW % V != 0) return QUBER_E_UNSUPPORTED;
         const size_t slice = (size_t)cg * HW;
         dim3 grid(tiles, N * G);
-        gn_stats_nchw_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, slice, tiles, part);
+        gn_stats_nchw_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, pb, slice, HW, cg, G, tiles, part);
         if (int rc = check_launch("gn_stats_nchw_kernel")) return rc;
-        gn_finalize_kernel<T><<<cdiv(N * G, 128), 128, 0, st>>>(x, part, N * G, G, tiles, count, (size_t)C * HW, slice, eps, stats);
+        gn_finalize_kernel<T><<<cdiv(N * G, 128), 128, 0, st>>>(x, pb, cg, part, N * G, G, tiles, count, (size_t)C * HW, slice, eps, stats);
         if (int rc = check_launch("gn_finalize_kernel")) return rc;
-        gn_apply_nchw_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, y, gamma, beta, stats, slice, HW, cg, G, relu);
+        gn_apply_nchw_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, y, pb, gamma, beta, stats, slice, HW, cg, G, relu);
         return check_launch("gn_apply_nchw_kernel");
     }
     if (C % V != 0) return QUBER_E_UNSUPPORTED;
@@ -255,12 +263,51 @@ static int gn_run(const void *xv, void *yv, const float *gamma, const float *bet
         QUBER_CUDA_TRY(cudaFuncSetAttribute(gn_stats_nhwc_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     dim3 grid(tiles, N);
-    gn_stats_nhwc_kernel<T><<<grid, GN_THREADS, smem, st>>>(x, HW, C, cg, tiles, part);
+    gn_stats_nhwc_kernel<T><<<grid, GN_THREADS, smem, st>>>(x, pb, HW, C, cg, tiles, part);
     if (int rc = check_launch("gn_stats_nhwc_kernel")) return rc;
-    gn_finalize_kernel<T><<<cdiv(N * G, 128), 128, 0, st>>>(x, part, N * G, G, tiles, count, (size_t)C * HW, (size_t)cg, eps, stats);
+    gn_finalize_kernel<T><<<cdiv(N * G, 128), 128, 0, st>>>(x, pb, cg, part, N * G, G, tiles, count, (size_t)C * HW, (size_t)cg, eps, stats);
     if (int rc = check_launch("gn_finalize_kernel")) return rc;
-    gn_apply_nhwc_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, y, gamma, beta, stats, HW, C, cg, relu);
+    gn_apply_nhwc_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, y, pb, gamma, beta, stats, HW, C, cg, relu);
     return check_launch("gn_apply_nhwc_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------ upsample + concat
+// DeepLabV3+ decoder step (detectron2 DeepLabV3PlusHead.layers, called from model.py:713):
+//     y = F.interpolate(y, size=proj_x.shape[-2:], mode="bilinear", align_corners=False);  cat([proj_x, y], dim=1)
+// as ONE pass over channels-last tensors: out[n,y,x,:] = [ a[n,y,x,:Ca] | bilinear(b)[n,y,x,:Cb] ].  PyTorch's source
+// index and lambda arithmetic (area_pixel_compute_source_index, fp32 accumulation for bf16).
+template <typename T>
+__global__ void __launch_bounds__(256)
+upsample_concat_kernel(const T *__restrict__ a, const T *__restrict__ b, T *__restrict__ out, size_t total, int Ca, int Cb, int H,
+                       int W, int h, int w, float rh, float rw) {
+    constexpr int V = Vec<T>::N;
+    const int TPa = Ca / V, TPo = (Ca + Cb) / V;
+    const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= total) return;
+    const int vec = (int)(idx % TPo);
+    const size_t pix = idx / TPo;                        // n * H * W + y * W + x
+    T *o = out + pix * (Ca + Cb) + (size_t)vec * V;
+    if (vec < TPa) {
+        *reinterpret_cast<uint4 *>(o) = *reinterpret_cast<const uint4 *>(a + pix * Ca + (size_t)vec * V);
+        return;
+    }
+    const int x = (int)(pix % W), y = (int)((pix / W) % H);
+    const size_t n = pix / ((size_t)W * H);
+    float sy = rh * ((float)y + 0.5f) - 0.5f, sx = rw * ((float)x + 0.5f) - 0.5f;
+    sy = sy < 0.f ? 0.f : sy;
+    sx = sx < 0.f ? 0.f : sx;
+    const int y1 = min((int)sy, h - 1), x1 = min((int)sx, w - 1);
+    const int yp = y1 < h - 1 ? 1 : 0, xp = x1 < w - 1 ? 1 : 0;
+    const float ly = sy - (float)y1, lx = sx - (float)x1, hy = 1.f - ly, hx = 1.f - lx;
+    const T *s = b + ((n * h + y1) * (size_t)w + x1) * Cb + (size_t)(vec - TPa) * V;
+    float v00[V], v01[V], v10[V], v11[V], r[V];
+    Vec<T>::load(s, v00);
+    Vec<T>::load(s + (size_t)xp * Cb, v01);
+    Vec<T>::load(s + (size_t)yp * w * Cb, v10);
+    Vec<T>::load(s + ((size_t)yp * w + xp) * Cb, v11);
+#pragma unroll
+    for (int j = 0; j < V; ++j) r[j] = hy * (hx * v00[j] + lx * v01[j]) + ly * (hx * v10[j] + lx * v11[j]);
+    Vec<T>::store(o, r);
 }
 
 }  // namespace quber
@@ -270,7 +317,7 @@ extern "C" size_t quber_group_norm_workspace_bytes(int N, int C, int HW, int G, 
     return ((size_t)N * G * quber::gn_tiles(C, HW, G, layout) * 2 + (size_t)N * G * 2) * sizeof(float);
 }
 
-extern "C" int quber_group_norm_relu(const void *x, void *y, const float *gamma, const float *beta, int N, int C, int HW, int G,
+extern "C" int quber_group_norm_relu(const void *x, void *y, const float *pre_bias, const float *gamma, const float *beta, int N, int C, int HW, int G,
                                      float eps, int relu, int layout, int dtype, void *workspace, size_t workspace_bytes,
                                      void *stream) {
     using namespace quber;
@@ -282,6 +329,29 @@ extern "C" int quber_group_norm_relu(const void *x, void *y, const float *gamma,
     if (N > 65535 || (layout == 0 && (size_t)N * G > 65535)) return QUBER_E_UNSUPPORTED;
     cudaStream_t st = (cudaStream_t)stream;
     float *ws = static_cast<float *>(workspace);
-    if (dtype == 0) return gn_run<float>(x, y, gamma, beta, N, C, HW, G, eps, relu, layout, ws, st);
-    return gn_run<__nv_bfloat16>(x, y, gamma, beta, N, C, HW, G, eps, relu, layout, ws, st);
+    if (dtype == 0) return gn_run<float>(x, y, pre_bias, gamma, beta, N, C, HW, G, eps, relu, layout, ws, st);
+    return gn_run<__nv_bfloat16>(x, y, pre_bias, gamma, beta, N, C, HW, G, eps, relu, layout, ws, st);
+}
+
+extern "C" int quber_upsample_concat(const void *a, const void *b, void *out, int N, int Ca, int Cb, int H, int W, int h, int w,
+                                     int dtype, void *stream) {
+    using namespace quber;
+    if (!b || !out || (Ca > 0 && !a) || N <= 0 || Ca < 0 || Cb <= 0 || H <= 0 || W <= 0 || h <= 0 || w <= 0 || (dtype != 0 && dtype != 1))
+        return QUBER_E_INVALID;
+    const int V = dtype == 0 ? 4 : 8;
+    if (Ca % V != 0 || Cb % V != 0) return QUBER_E_UNSUPPORTED;
+    if ((a && !aligned16(a)) || !aligned16(b) || !aligned16(out)) return QUBER_E_ALIGN;
+    const size_t total = (size_t)N * H * W * ((Ca + Cb) / V);
+    if ((total + 255) / 256 > 0x7fffffffull) return QUBER_E_UNSUPPORTED;
+    const float rh = (float)h / (float)H, rw = (float)w / (float)W;      // area_pixel_compute_scale, align_corners=False
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = (unsigned)((total + 255) / 256);
+    if (dtype == 0)
+        upsample_concat_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float *>(a), static_cast<const float *>(b),
+                                                          static_cast<float *>(out), total, Ca, Cb, H, W, h, w, rh, rw);
+    else
+        upsample_concat_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16 *>(a),
+                                                                  static_cast<const __nv_bfloat16 *>(b),
+                                                                  static_cast<__nv_bfloat16 *>(out), total, Ca, Cb, H, W, h, w, rh, rw);
+    return check_launch("upsample_concat_kernel");
 }

@@ -70,12 +70,13 @@ def _fused_conv(x, w, b, m, relu, add=None):
     return F.relu_(y) if relu else y
 
 
-def _gn_relu(gn, x, relu):
-    """GroupNorm (+ ReLU) in place through quber_group_norm_relu (csrc/norm.cu) when the tensor qualifies, else None."""
+def _gn_relu(gn, x, relu, pre_bias=None):
+    """GroupNorm (+ ReLU) in place through quber_group_norm_relu (csrc/norm.cu) when the tensor qualifies, else None.
+    `pre_bias`: the bias of the convolution that produced x, not yet added."""
     from . import ops
     if not x.is_cuda or not ops.group_norm_supported(x, gn.num_groups):
         return None
-    return ops.group_norm_relu(x, gn.weight, gn.bias, gn.num_groups, gn.eps, relu=relu, inplace=True)
+    return ops.group_norm_relu(x, gn.weight, gn.bias, gn.num_groups, gn.eps, relu=relu, inplace=True, pre_bias=pre_bias)
 
 
 def run_conv_gn_relu(seq, x, fast):
@@ -83,10 +84,23 @@ def run_conv_gn_relu(seq, x, fast):
     go through the fused kernel."""
     if not fast:
         return seq(x)
+    from . import ops
     mods = list(seq.children())
     i = 0
     while i < len(mods):
         m = mods[i]
+        if type(m) is nn.Conv2d and m.bias is not None and i + 1 < len(mods) and isinstance(mods[i + 1], nn.GroupNorm) and x.is_cuda:
+            # conv bias rides in the GroupNorm kernel's loads instead of a separate pass over the activation
+            y = F.conv2d(x, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
+            relu = i + 2 < len(mods) and isinstance(mods[i + 2], nn.ReLU)
+            z = _gn_relu(mods[i + 1], y, relu, pre_bias=m.bias) if ops.group_norm_supported(y, mods[i + 1].num_groups) else None
+            if z is not None:
+                x = z
+                i += 3 if relu else 2
+                continue
+            x = y + m.bias.reshape(1, -1, 1, 1).to(y.dtype)
+            i += 1
+            continue
         if isinstance(m, nn.GroupNorm):
             relu = i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU)
             y = _gn_relu(m, x, relu)
@@ -163,11 +177,16 @@ class Conv2d(nn.Conv2d):
             act = relu or self.activation is F.relu
             assert self.activation in (None, F.relu)
             return _fused_conv(x, w, b, self, act, add)
-        x = F.conv2d(x if x.dtype == w.dtype else x.to(w.dtype), w, b, self.stride, self.padding, self.dilation, self.groups)
-        if isinstance(self.norm, nn.GroupNorm) and add is None and self.activation in (None, F.relu):
-            y = _gn_relu(self.norm, x, relu or self.activation is F.relu)
+        xin = x if x.dtype == w.dtype else x.to(w.dtype)
+        if isinstance(self.norm, nn.GroupNorm) and add is None and self.activation in (None, F.relu) and x.is_cuda:
+            x = F.conv2d(xin, w, None, self.stride, self.padding, self.dilation, self.groups)
+            y = _gn_relu(self.norm, x, relu or self.activation is F.relu, pre_bias=b)
             if y is not None:
                 return y
+            if b is not None:
+                x = x + b.reshape(1, -1, 1, 1)
+        else:
+            x = F.conv2d(xin, w, b, self.stride, self.padding, self.dilation, self.groups)
         x = self.norm(x)
         if self.activation is not None:
             x = self.activation(x)
@@ -181,7 +200,7 @@ def prepare_inference(module, dtype=torch.float32, channels_last=False):
     for m in module.modules():
         if isinstance(m, Conv2d):
             m.plan(dtype, channels_last)
-        if isinstance(m, RGBDFusionBackbone):
+        if isinstance(m, (RGBDFusionBackbone, DeepLabV3PlusDecoder)):
             m.__dict__["_fast"] = True
 
 
@@ -189,7 +208,7 @@ def drop_inference_plan(module):
     for m in module.modules():
         if isinstance(m, Conv2d):
             m.drop_plan()
-        if isinstance(m, RGBDFusionBackbone):
+        if isinstance(m, (RGBDFusionBackbone, DeepLabV3PlusDecoder)):
             m.__dict__["_fast"] = False
 
 
@@ -442,9 +461,19 @@ class DeepLabV3PlusDecoder(nn.Module):
             if self.decoder[f]["fuse_conv"] is None:
                 y = proj_x
             else:
-                y = F.interpolate(y, size=proj_x.size()[2:], mode="bilinear", align_corners=False)
-                y = self.decoder[f]["fuse_conv"](torch.cat([proj_x, y], dim=1))
+                y = self.decoder[f]["fuse_conv"](self._up_cat(proj_x, y))
         return y
+
+    def _up_cat(self, proj_x, y):
+        """cat([proj_x, bilinear(y -> proj_x's size)], 1): one quber_upsample_concat pass on the inference plan."""
+        if self.__dict__.get("_fast") and proj_x.is_cuda:
+            from . import ops
+            a = proj_x.contiguous(memory_format=torch.channels_last)
+            b = y.to(a.dtype).contiguous(memory_format=torch.channels_last)
+            if ops.upsample_concat_supported(a, b):
+                return ops.upsample_concat(a, b)
+        y = F.interpolate(y, size=proj_x.size()[2:], mode="bilinear", align_corners=False)
+        return torch.cat([proj_x, y], dim=1)
 
 
 # ------------------------------------------------------------------------------------------------ heads

@@ -282,10 +282,11 @@ def group_norm_supported(x, groups):
     return False
 
 
-def group_norm_relu(x, weight, bias, groups=32, eps=1e-5, relu=True, inplace=False):
+def group_norm_relu(x, weight, bias, groups=32, eps=1e-5, relu=True, inplace=False, pre_bias=None):
     """nn.GroupNorm(groups, C)(x) followed by ReLU (detectron2 Conv2d norm="GN" + F.relu, model.py:386-403;
     resnet.py:466-479) in two passes over x (statistics; normalise + affine + ReLU).  x [N,C,H,W] float32 | bfloat16,
-    dense NCHW or channels-last; the result has x's dtype and memory format.  weight / bias [C] (any float dtype)."""
+    dense NCHW or channels-last; the result has x's dtype and memory format.  weight / bias [C] (any float dtype).
+    pre_bias [C] | None: the preceding convolution's bias, added to x before the statistics."""
     if not group_norm_supported(x, groups):
         raise ValueError("group_norm_relu: unsupported tensor (needs a dense CUDA fp32/bf16 NCHW or channels-last tensor)")
     N, C, H, W = x.shape
@@ -293,14 +294,43 @@ def group_norm_relu(x, weight, bias, groups=32, eps=1e-5, relu=True, inplace=Fal
     y = x if inplace else torch.empty_like(x)           # empty_like preserves the memory format
     g = weight.detach().to(device=x.device, dtype=torch.float32).contiguous()
     b = bias.detach().to(device=x.device, dtype=torch.float32).contiguous()
+    pb = None if pre_bias is None else pre_bias.detach().to(device=x.device, dtype=torch.float32).contiguous()
     L = _lib.lib()
     nbytes = L.quber_group_norm_workspace_bytes(N, C, H * W, groups, layout)
     ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
     with torch.cuda.device(x.device):
-        _lib.check(L.quber_group_norm_relu(_ptr(x), _ptr(y), _ptr(g), _ptr(b), N, C, H * W, groups, float(eps), int(bool(relu)),
+        _lib.check(L.quber_group_norm_relu(_ptr(x), _ptr(y), _ptr(pb), _ptr(g), _ptr(b), N, C, H * W, groups, float(eps), int(bool(relu)),
                                            layout, 0 if x.dtype == torch.float32 else 1, _ptr(ws), nbytes, _stream()),
                    "quber_group_norm_relu")
     return y
+
+
+def upsample_concat_supported(a, b):
+    if not (isinstance(b, torch.Tensor) and b.is_cuda and b.dim() == 4 and b.dtype in (torch.float32, torch.bfloat16)):
+        return False
+    v = 16 // b.element_size()
+    cl = lambda t: t.is_contiguous(memory_format=torch.channels_last)
+    if b.shape[1] % v or not cl(b):
+        return False
+    if a is not None and not (a.is_cuda and a.dtype == b.dtype and a.shape[0] == b.shape[0] and a.shape[1] % v == 0 and cl(a)):
+        return False
+    return True
+
+
+def upsample_concat(a, b, size=None):
+    """torch.cat([a, F.interpolate(b, size=a.shape[-2:], mode="bilinear", align_corners=False)], dim=1) in one pass
+    (DeepLabV3PlusHead.layers, model.py:713).  a [N,Ca,H,W] | None (then `size` = (H, W)), b [N,Cb,h,w]; channels-last
+    float32 | bfloat16 CUDA tensors; the result is channels-last [N,Ca+Cb,H,W]."""
+    if not upsample_concat_supported(a, b):
+        raise ValueError("upsample_concat: needs channels-last CUDA fp32/bf16 tensors with channel counts that fill 16-byte vectors")
+    N, Cb, h, w = b.shape
+    Ca = 0 if a is None else a.shape[1]
+    H, W = (a.shape[2], a.shape[3]) if a is not None else (int(size[0]), int(size[1]))
+    out = torch.empty((N, Ca + Cb, H, W), dtype=b.dtype, device=b.device, memory_format=torch.channels_last)
+    with torch.cuda.device(b.device):
+        _lib.check(_lib.lib().quber_upsample_concat(_ptr(a), _ptr(b), _ptr(out), N, Ca, Cb, H, W, h, w,
+                                                    0 if b.dtype == torch.float32 else 1, _stream()), "quber_upsample_concat")
+    return out
 
 
 _FUSE_OPS = {"copy": 0, "sigmoid": 1, "softmax": 2}

@@ -315,3 +315,37 @@ def test_network_inference_plan_matches_layer_by_layer():
         out = model.network_logits(x)
     for k in ref:
         assert float((out[k] - ref[k]).abs().max()) <= 1e-3 * max(1.0, float(ref[k].abs().max())), k
+
+
+def test_group_norm_pre_bias_equals_bias_then_norm():
+    g = torch.Generator(device=DEV).manual_seed(21)
+    for cl in (False, True):
+        x = torch.randn(2, 256, 12, 20, device=DEV, generator=g)
+        if cl:
+            x = x.contiguous(memory_format=torch.channels_last)
+        pb = torch.randn(256, device=DEV, generator=g) * 3
+        w = torch.rand(256, device=DEV, generator=g) + 0.5
+        b = torch.randn(256, device=DEV, generator=g)
+        ref = torch.relu(torch.nn.functional.group_norm((x + pb.view(1, -1, 1, 1)).double(), 32, w.double(), b.double(), 1e-5))
+        out = ops.group_norm_relu(x, w, b, 32, 1e-5, pre_bias=pb)
+        assert float((out.double() - ref).abs().max()) <= 2e-5
+
+
+@pytest.mark.parametrize("dt,tol", [(torch.float32, 2e-6), (torch.bfloat16, 2.0 ** -7)])
+@pytest.mark.parametrize("shape", [((2, 64, 60, 80), (2, 256, 30, 40)), ((1, 32, 24, 40), (1, 128, 12, 20)), ((2, 0, 47, 83), (2, 16, 12, 21))])
+def test_upsample_concat_matches_torch(dt, tol, shape):
+    """cat([proj_x, F.interpolate(y, size=proj_x.shape[-2:], bilinear, align_corners=False)], 1) — the decoder step
+    (DeepLabV3PlusHead.layers) — against torch on the same channels-last tensors; non-integer scale in the last case."""
+    (N, Ca, H, W), (_, Cb, h, w) = shape
+    g = torch.Generator(device=DEV).manual_seed(H + Cb)
+    b = torch.randn(N, Cb, h, w, device=DEV, generator=g).to(dt).contiguous(memory_format=torch.channels_last)
+    a = torch.randn(N, Ca, H, W, device=DEV, generator=g).to(dt).contiguous(memory_format=torch.channels_last) if Ca else None
+    up = torch.nn.functional.interpolate(b.float(), size=(H, W), mode="bilinear", align_corners=False)
+    ref = up if a is None else torch.cat([a.float(), up], dim=1)
+    out = ops.upsample_concat(a, b, size=(H, W))
+    assert out.shape == ref.shape and out.dtype == dt and out.is_contiguous(memory_format=torch.channels_last)
+    if a is not None:
+        assert torch.equal(out[:, :Ca], a)
+    assert float((out.float() - ref).abs().max()) <= tol * max(1.0, float(ref.abs().max()))
+    with pytest.raises(ValueError):
+        ops.upsample_concat(a, b.contiguous(), size=(H, W))              # NCHW operand
