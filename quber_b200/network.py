@@ -17,6 +17,8 @@ GPU with `use_kernels=True`:
     -> ops.gemm_bias_act on channels-last rows (tcgen05, csrc/gemm.cu) with the BatchNorm folded into W, b
 On CPU (the test oracle for this file) the same modules run in plain torch fp32.
 """
+import os
+
 import torch
 import torch.nn.functional as F
 from torch import nn
@@ -143,10 +145,10 @@ class Conv2d(nn.Conv2d):
             w = w * s.reshape(-1, 1, 1, 1)
             folded = True
         w = w.to(dtype)
-        # dilated 3x3s stay NCHW: with channels-last operands cuDNN 9 falls to conv2d_grouped_direct_kernel for the
-        # ASPP branch with dilation 18 on a 30x40 map (298 ms instead of 0.5 ms for 32 frames, measured on B200)
-        channels_last = channels_last and max(self.dilation) == 1
-        self.__dict__["_nchw_input"] = max(self.dilation) > 1
+        # cuDNN 9 on B200: a 3x3 whose dilation exceeds half the map (ASPP dilation 18 on 30x40) falls to
+        # conv2d_grouped_direct_kernel with channels-last operands — 298 ms instead of 1.1 ms for 32 frames in bf16
+        # (scripts/bench_dilated_conv.py); such calls get NCHW operands (forward() decides per input shape).
+        self.__dict__["_w_nchw"] = w.contiguous() if (channels_last and max(self.dilation) > 1) else None
         if channels_last:
             w = w.contiguous(memory_format=torch.channels_last)
         self.__dict__["_plan"] = (w.contiguous() if not channels_last else w, None if b is None else b.to(dtype).contiguous(), folded,
@@ -171,8 +173,9 @@ class Conv2d(nn.Conv2d):
             self.plan(*self.__dict__["_plan_args"])
             p = self.__dict__["_plan"]
         w, b, folded = p[:3]
-        if self.__dict__.get("_nchw_input") and not x.is_contiguous():
-            x = x.contiguous()
+        wn = self.__dict__.get("_w_nchw")
+        if wn is not None and 2 * max(self.dilation) > min(x.shape[-2:]):
+            w, x = wn, x.contiguous()
         if self.norm is None or folded:
             act = relu or self.activation is F.relu
             assert self.activation in (None, F.relu)
@@ -234,6 +237,14 @@ class BottleneckBlock(nn.Module):
     def forward(self, x):
         out = self.conv1(x, relu=True)
         out = self.conv2(out, relu=True)
+        ps = self.shortcut.__dict__.get("_plan") if self.shortcut is not None else None
+        p3 = self.conv3.__dict__.get("_plan")
+        if ps is not None and p3 is not None and not self.training and ps[2] and p3[2] and x.is_cuda \
+                and ps[3] == self.shortcut._sig() and p3[3] == self.conv3._sig():
+            # both BatchNorms folded: the shortcut's bias moves into conv3's epilogue (one bias pass less)
+            sc = F.conv2d(x if x.dtype == ps[0].dtype else x.to(ps[0].dtype), ps[0], None, self.shortcut.stride,
+                          self.shortcut.padding, self.shortcut.dilation, self.shortcut.groups)
+            return _fused_conv(out, p3[0], p3[1] + ps[1], self.conv3, True, sc)
         shortcut = self.shortcut(x) if self.shortcut is not None else x
         return self.conv3(out, relu=True, add=shortcut)
 
@@ -420,7 +431,10 @@ class ASPP(nn.Module):
     def forward(self, x):
         size = x.shape[-2:]
         res = [conv(x) for conv in self.convs]
-        res[-1] = F.interpolate(res[-1], size=size, mode="bilinear", align_corners=False)
+        if self.convs[0].__dict__.get("_plan") is not None and not self.training:
+            res[-1] = res[-1].expand(-1, -1, size[0], size[1])     # bilinear up-sampling of a 1x1 map is a broadcast
+        else:
+            res[-1] = F.interpolate(res[-1], size=size, mode="bilinear", align_corners=False)
         res = self.project(torch.cat(res, dim=1))
         return F.dropout(res, self.dropout, training=self.training) if self.dropout > 0 else res
 
@@ -472,6 +486,8 @@ class DeepLabV3PlusDecoder(nn.Module):
             b = y.to(a.dtype).contiguous(memory_format=torch.channels_last)
             if ops.upsample_concat_supported(a, b):
                 return ops.upsample_concat(a, b)
+            if os.environ.get("QUBER_DEBUG"):
+                print("upsample_concat fallback:", a.shape, a.dtype, a.stride(), b.shape, b.dtype, b.stride())
         y = F.interpolate(y, size=proj_x.size()[2:], mode="bilinear", align_corners=False)
         return torch.cat([proj_x, y], dim=1)
 
