@@ -85,6 +85,7 @@ gn_stats_nchw_kernel(const T *__restrict__ x, const float *__restrict__ pb, size
     const float K = Vec<T>::one(p) + (pb ? __ldg(pb + c0) : 0.f);
     const size_t lo = (size_t)blockIdx.x * GN_TILE_ELEMS, hi = min(slice, lo + (size_t)GN_TILE_ELEMS);
     float s1 = 0.f, s2 = 0.f;
+#pragma unroll 4
     for (size_t i = lo + (size_t)threadIdx.x * V; i < hi; i += (size_t)GN_THREADS * V) {     // slice % V == 0
         float v[V];
         Vec<T>::load(p + i, v);
@@ -111,6 +112,7 @@ gn_apply_nchw_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
     const T *p = x + ng * slice;
     T *q = y + ng * slice;
     const size_t lo = (size_t)blockIdx.x * GN_TILE_ELEMS, hi = min(slice, lo + (size_t)GN_TILE_ELEMS);
+#pragma unroll 4
     for (size_t i = lo + (size_t)threadIdx.x * V; i < hi; i += (size_t)GN_THREADS * V) {     // HW % V == 0: one channel per vector
         const int c = g * cg + (int)(i / HW);
         const float a = rstd * __ldg(gamma + c), b = fmaf((pb ? __ldg(pb + c) : 0.f) - mean, a, __ldg(beta + c));
@@ -151,6 +153,7 @@ gn_stats_nhwc_kernel(const T *__restrict__ x, const float *__restrict__ pb, int 
             K[j] = Vec<T>::one(xs + cf) + (pb ? __ldg(pb + cf) - __ldg(pb + c) : 0.f);
             s1[j] = 0.f; s2[j] = 0.f;
         }
+#pragma unroll 4
         for (int p = p0 + row; p < p1; p += rows) {
             float v[V];
             Vec<T>::load(xs + (size_t)p * C + ch * V, v);
@@ -197,6 +200,7 @@ gn_apply_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
             a[j] = rstd * __ldg(gamma + c);
             b[j] = fmaf((pb ? __ldg(pb + c) : 0.f) - mean, a[j], __ldg(beta + c));
         }
+#pragma unroll 4
         for (int p = p0 + row; p < p1; p += rows) {
             float v[V];
             Vec<T>::load(x + base + (size_t)p * C + ch * V, v);

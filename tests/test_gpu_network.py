@@ -349,3 +349,21 @@ def test_upsample_concat_matches_torch(dt, tol, shape):
     assert float((out.float() - ref).abs().max()) <= tol * max(1.0, float(ref.abs().max()))
     with pytest.raises(ValueError):
         ops.upsample_concat(a, b.contiguous(), size=(H, W))              # NCHW operand
+
+
+def test_network_cuda_graph_replay_matches_eager():
+    from quber_b200.meta_arch import build_model
+    torch.manual_seed(0)
+    model = build_model(_cfg(DEV), "bf16").eval()
+    _randomise(model, seed=4)
+    xs = [torch.randn(2, 9, 64, 96, device=DEV) for _ in range(3)]
+    with torch.no_grad():
+        eager = [model.network_logits(x) for x in xs]
+        model.use_cuda_graph = True
+        graphed = [model.network_logits(x) for x in xs]          # first call captures, the others replay
+        again = model.network_logits(xs[0])
+    for e, g in zip(eager, graphed):
+        for k in e:
+            assert torch.equal(e[k], g[k]), k
+    for k in again:
+        assert torch.equal(again[k], eager[0][k])
