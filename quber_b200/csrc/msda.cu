@@ -250,7 +250,11 @@ static int launch_vec(const void *value, const int64_t *shapes, const int64_t *s
     // QUBER_MSDA_BCAST=shfl selects the shuffle broadcast (kept for A/B measurements); default: shared memory.
     static const bool shfl = [] { const char *e = getenv("QUBER_MSDA_BCAST"); return e && e[0] == 's'; }();
     if (!shfl) {
-        msda_forward_kernel<D, VT, 5, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o);
+        switch (msda_minb()) {
+            default: msda_forward_kernel<D, VT, 5, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+            case 6: msda_forward_kernel<D, VT, 6, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+            case 4: msda_forward_kernel<D, VT, 4, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
+        }
         return check_launch("msda_forward_kernel");
     }
     switch (msda_minb()) {
