@@ -294,46 +294,56 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
     for (int k = 0; k < K; ++k) {
         uint32_t *cur = S(k);
         if (!mbar_wait(&full[k & 1], (k >> 1) & 1)) { s_abort = 1; atomicAdd(&g_tma_timeouts, 1u); }
-        // ---- census + bit packing: one pass over the staged bytes, 16 pixels per shared load ----
+        // ---- pass A: is the staged tile (+ halo) all zero?  ~87 % of the (tile, plane) pairs at C2 are, and they
+        //      leave after this OR (8 instructions per 16 pixels) without the census / bit packing below ----
         const int slot = (k % 3) * 2;
+        const uint4 *c4 = reinterpret_cast<const uint4 *>(cur);
+        const int n16 = R * WS16;
         {
-            uint32_t o = 0u, a = 0xffffffffu;
-            const uint4 *c4 = reinterpret_cast<const uint4 *>(cur);
-            uint16_t *b16 = reinterpret_cast<uint16_t *>(bits);
-            const int n16 = R * WS16;
+            uint32_t o = 0u;
             for (int idx = tid; idx < n16; idx += B_THREADS) {
-                const int r = idx / WS16, c = idx - r * WS16;
                 const uint4 x = c4[idx];
-                const uint32_t t0 = nonzero_bytes01(x.x), t1 = nonzero_bytes01(x.y), t2 = nonzero_bytes01(x.z), t3 = nonzero_bytes01(x.w);
                 o |= x.x | x.y | x.z | x.w;
-                a &= (x.x | ~(t0 * 255u)) & (x.y | ~(t1 * 255u)) & (x.z | ~(t2 * 255u)) & (x.w | ~(t3 * 255u));
-                const uint32_t pk = ((t0 * 0x01020408u) >> 24) | (((t1 * 0x01020408u) >> 24) << 4) |
-                                    (((t2 * 0x01020408u) >> 24) << 8) | (((t3 * 0x01020408u) >> 24) << 12);
-                b16[r * (2 * RW32) + c] = (uint16_t)pk;
             }
             o = __reduce_or_sync(0xffffffffu, o);
-            a = __reduce_and_sync(0xffffffffu, a);
-            if (lane == 0) {
-                if (o) atomicOr(&red[slot], o);
-                if (a != 0xffffffffu) atomicAnd(&red[slot + 1], a);
-            }
+            if (lane == 0 && o) atomicOr(&red[slot], o);
         }
-        __syncthreads();                                    // S1: census complete, every read of `cur` above is done
+        __syncthreads();                                    // S1a: OR census complete
         if (s_abort) break;
-        const uint32_t oc = red[slot], ac = red[slot + 1];
+        const uint32_t oc = red[slot];
         const uint32_t v = (oc | (oc >> 8) | (oc >> 16) | (oc >> 24)) & 0xffu;          // OR of all bytes
-        const uint32_t va = (ac & (ac >> 8) & (ac >> 16) & (ac >> 24)) & 0xffu;         // AND of the non-zero bytes
-        const bool empty = v == 0u, binary = v == va;
+        const bool empty = v == 0u;
         if (tid == 0) {
             const int s2 = ((k + 2) % 3) * 2;               // next written two iterations from now, last read one ago
             red[s2] = 0u;
             red[s2 + 1] = 0xffffffffu;
-            if ((empty || binary) && k + 2 < K) issue(k + 2);   // the stage is dead already on these routes
+            if (empty && k + 2 < K) issue(k + 2);           // every read of the stage is done
         }
         if (empty) {
             if (has_per && tid == 0) { tma_store_3d(&out_map, Z, tx0, ty0, b * K + k); tma_commit(); }
             continue;
         }
+        // ---- pass B: AND census of the non-zero bytes (binary plane?) + bit packing, 16 pixels per shared load ----
+        {
+            uint32_t a = 0xffffffffu;
+            uint16_t *b16 = reinterpret_cast<uint16_t *>(bits);
+            for (int idx = tid; idx < n16; idx += B_THREADS) {
+                const int r = idx / WS16, c = idx - r * WS16;
+                const uint4 x = c4[idx];
+                const uint32_t t0 = nonzero_bytes01(x.x), t1 = nonzero_bytes01(x.y), t2 = nonzero_bytes01(x.z), t3 = nonzero_bytes01(x.w);
+                a &= (x.x | ~(t0 * 255u)) & (x.y | ~(t1 * 255u)) & (x.z | ~(t2 * 255u)) & (x.w | ~(t3 * 255u));
+                const uint32_t pk = ((t0 * 0x01020408u) >> 24) | (((t1 * 0x01020408u) >> 24) << 4) |
+                                    (((t2 * 0x01020408u) >> 24) << 8) | (((t3 * 0x01020408u) >> 24) << 12);
+                b16[r * (2 * RW32) + c] = (uint16_t)pk;
+            }
+            a = __reduce_and_sync(0xffffffffu, a);
+            if (lane == 0 && a != 0xffffffffu) atomicAnd(&red[slot + 1], a);
+        }
+        __syncthreads();                                    // S1b: census + bit rows complete, `cur` is dead on the binary route
+        const uint32_t ac = red[slot + 1];
+        const uint32_t va = (ac & (ac >> 8) & (ac >> 16) & (ac >> 24)) & 0xffu;         // AND of the non-zero bytes
+        const bool binary = v == va;
+        if (tid == 0 && binary && k + 2 < K) issue(k + 2);
         uint32_t bdw[8], mw[8];
         if (binary) {
             // ---- horizontal erosion on bit rows: window [x-d, x+d] for the four central 32-pixel words ----

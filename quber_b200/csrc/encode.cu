@@ -36,9 +36,19 @@ encode_reduce_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, Enc
     const size_t pix = (size_t)y * W + x0;
     uint32_t last_lo = 0xffffffffu, last_hi = 0xffffffffu;   // packed per-pixel last k
     const uint8_t *base = masks + (size_t)b * K * HW + pix;
+    constexpr int PF = 4;                   // planes fetched together: the streaming loads are the only latency here
+    uint2 vbuf[PF];
     for (int k = 0; k < K; ++k) {
-        uint2 v = make_uint2(0, 0);
-        if (inb) v = ld_stream_u2(base + (size_t)k * HW);
+        if (k % PF == 0) {
+#pragma unroll
+            for (int j = 0; j < PF; ++j) {
+                vbuf[j] = make_uint2(0, 0);
+                if (inb && k + j < K) vbuf[j] = ld_stream_u2(base + (size_t)(k + j) * HW);
+            }
+        }
+        uint2 v = vbuf[0];
+#pragma unroll
+        for (int j = 1; j < PF; ++j) if (k % PF == j) v = vbuf[j];
         const bool nz = (v.x | v.y) != 0;
         if (__any_sync(0xffffffffu, nz)) {
             unsigned n = 0, sx = 0;
