@@ -292,7 +292,10 @@ def run_ours(args):
         "stage_ms": per_stage,
         "roofline": {"kernel": dominant, "bound": "hbm", "achieved": dv["achieved_gbs"], "peak": peak_gbs, "unit": "GB/s",
                      "frac": dv["frac"], "traffic": None, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": dv["bytes"],
-                     "avg_launch_ms": dv["ms"]},
+                     "avg_launch_ms": dv["ms"],
+                     "note": ("msda fp32 is bounded by the L1 data pipe, not HBM: 48 gathered 128-byte lines per (query, head) = "
+                              "266 us/launch at 128 B/clk/SM, i.e. frac <= 0.37 for any L1/shared-memory gather (DESIGN.md 3.1); "
+                              "ncu dram bytes per launch in profiles/") if dominant.startswith("msda") else None},
         "roofline_all": roof_all,
     }
     if world == 1 and not args.no_network:

@@ -87,6 +87,28 @@ class HotPath:
             self._stage = st
         return st
 
+    @staticmethod
+    def chunk_schedule(B, chunk_frames, min_tail=2):
+        """[(start, stop), ...]: chunks of `chunk_frames` frames, the last one halved repeatedly down to `min_tail`
+        frames — what runs after the final host->device copy (kernels + device->host copy of the last chunk) is the
+        only part of the call the copies cannot hide, so the last chunk is kept small."""
+        sizes = [chunk_frames] * (B // chunk_frames)
+        if B % chunk_frames:
+            sizes.append(B % chunk_frames)
+        if sizes:
+            last = sizes.pop()
+            while last > min_tail:
+                half = (last + 1) // 2
+                sizes.append(half)
+                last -= half
+            sizes.append(last)
+        out, c0 = [], 0
+        for n in sizes:
+            if n > 0:
+                out.append((c0, c0 + n))
+                c0 += n
+        return out
+
     def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8):
         """The end-to-end call: host buffers in, host results out.
 
@@ -114,8 +136,7 @@ class HotPath:
             h2d.wait_event(st["free"])            # the previous call's kernels have finished reading the staging buffers
         d2h.wait_stream(cur)                      # ... and whoever consumed the pinned results was ordered on `cur`
         keep = []
-        for c0 in range(0, B, chunk_frames):
-            c1 = min(B, c0 + chunk_frames)
+        for c0, c1 in self.chunk_schedule(B, chunk_frames):
             with torch.cuda.stream(h2d):
                 st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
                 for k, v in head_host.items():
