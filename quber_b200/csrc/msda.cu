@@ -17,7 +17,9 @@
 // launch at C2 = 266 us at 1.965 GHz, before the per-tap broadcast of the set-up (one more write-back
 // cycle per 32-bit value).  l1tex__lsu_writeback_active sits at 72 % and l1tex__data_pipe_lsu_wavefronts
 // at 75 %; 54 % of warp samples wait in long_scoreboard on that pipe.  Measured alternatives, all slower
-// at C2 (fp32, us/launch): set-up recomputed by every lane 594; 7-value shuffle broadcast 568; 16-byte
+// at C2 (fp32, us/launch): two of the four corners through the texture pipe (tex1Dfetch of raw 16-byte texels on a
+// linear texture of `value`) 507 against 497, all four 665 — TEX shares the L1 data stage, it is not a second path;
+// set-up recomputed by every lane 594; 7-value shuffle broadcast 568; 16-byte
 // shared-memory tap records read with LDS.128 648; 4-value broadcast + per-lane weights 587; register
 // software pipelining of the corner loads 681 (3 CTAs/SM) and 903 (2 CTAs/SM) — throughput follows
 // resident warps, not loads in flight; 2-D query patches 585.  Kept: the variant with the fewest
