@@ -236,6 +236,22 @@ int quber_group_norm_relu(const void *x, void *y, const float *pre_bias, const f
 int quber_upsample_concat(const void *a, const void *b, void *out, int N, int Ca, int Cb, int H, int W, int h, int w,
                           int dtype, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * quber_filter_instances — the caller-side filter of the refined instances, eval/refiner_model.py:271-288:
+ *     keep instance j  <=>  sum(mask_j & fg_mask) / sum(mask_j) > thr (0.3, float64 division as numpy),
+ *     then (OCID / DoPose) every kept mask loses its zero-depth pixels.
+ *   label_map      dev [B,H,W] int32: 0 = void, j + 1 = j-th refined instance of the frame (quber_post_process)
+ *   counts         dev [B] int32 instances per frame (labels above min(counts[b], max_per) are dropped)
+ *   fg             dev [B,H,W] uint8 foreground mask (non-zero = foreground) or NULL (no overlap test)
+ *   zero_depth     dev [B,H,W] uint8 (non-zero = pixel without depth) or NULL
+ *   out_label_map  dev [B,H,W] int32: kept instances renumbered 1..new_counts[b] in their original order
+ *   keep           dev [B,max_per] uint8, new_counts dev [B] int32.  H*W % 4 == 0.
+ * ------------------------------------------------------------------------------------------- */
+size_t quber_filter_workspace_bytes(int B, int max_per);
+int quber_filter_instances(const int32_t *label_map, const int32_t *counts, const uint8_t *fg, const uint8_t *zero_depth,
+                           int B, int H, int W, int max_per, double thr, int32_t *out_label_map, uint8_t *keep,
+                           int32_t *new_counts, void *workspace, size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

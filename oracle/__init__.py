@@ -182,3 +182,19 @@ def msda_forward(value, shapes, starts, loc, attn):
     fn = lib().oracle_msda_forward_f64 if dt == np.float64 else lib().oracle_msda_forward_f32
     fn(_p(value), _p(shapes), _p(starts), _p(loc), _p(attn), B, S, M, D, L, Q, P, _p(out))
     return out
+
+
+def filter_instances(masks, fg_mask=None, zero_depth=None, thr=0.3):
+    """eval/refiner_model.py:271-288, restated with numpy: masks [N,H,W] bool -> (kept masks [N',H,W] bool, keep [N] bool).
+    keep j iff np.sum(mask & fg) / np.sum(mask) > thr (int64 / int64 true division); the zero-depth pixels of the
+    kept masks are cleared afterwards (:279-288)."""
+    masks = np.asarray(masks).astype(bool)
+    keep = np.ones(len(masks), bool)
+    if fg_mask is not None:
+        fgb = np.asarray(fg_mask).astype(bool)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            keep = np.array([np.sum(np.bitwise_and(m, fgb)) / np.sum(m) > thr for m in masks], bool)
+    out = masks[keep].copy()
+    if zero_depth is not None:
+        out[:, np.asarray(zero_depth).astype(bool)] = False
+    return out, keep

@@ -624,6 +624,74 @@ finalize_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Caller-side filter of the refined instances (eval/refiner_model.py:271-288):
+//   keep instance j  <=>  sum(mask_j & fg) / sum(mask_j) > thr        (thr = 0.3; numpy int64 / int64 -> float64)
+//   OCID / DoPose: kept masks lose their zero-depth pixels            (refined_mask[zero_depth] = False)
+// on the label-map form of the instances (0 = void, j + 1 = j-th instance): one counting pass (integer atomics,
+// deterministic), one tiny per-frame pass that decides and renumbers, one relabel pass.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+filter_count_kernel(const int32_t *__restrict__ lmap, const uint8_t *__restrict__ fg, int HW, int max_per,
+                    uint32_t *__restrict__ cnt /* [B][max_per][2]: area, overlap */) {
+    extern __shared__ uint32_t fsm[];                    // [max_per][2]
+    const int b = blockIdx.y;
+    for (int i = threadIdx.x; i < 2 * max_per; i += 256) fsm[i] = 0;
+    __syncthreads();
+    const size_t base = (size_t)b * HW;
+    for (int i = (blockIdx.x * 256 + threadIdx.x) * 4; i < HW; i += gridDim.x * 256 * 4) {     // HW % 4 == 0
+        const int4 l = *reinterpret_cast<const int4 *>(lmap + base + i);
+        uint32_t f = 0x01010101u;
+        if (fg) f = *reinterpret_cast<const uint32_t *>(fg + base + i);
+        const int ls[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (ls[j] > 0 && ls[j] <= max_per) {
+                atomicAdd(&fsm[2 * (ls[j] - 1)], 1u);
+                if ((f >> (8 * j)) & 0xffu) atomicAdd(&fsm[2 * (ls[j] - 1) + 1], 1u);
+            }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * max_per; i += 256)
+        if (fsm[i]) atomicAdd(&cnt[(size_t)b * 2 * max_per + i], fsm[i]);
+}
+
+__global__ void filter_decide_kernel(const uint32_t *__restrict__ cnt, const int32_t *__restrict__ counts, int B, int max_per, double thr,
+                                     int use_fg, uint8_t *__restrict__ keep, int32_t *__restrict__ newid /* [B][max_per] */,
+                                     int32_t *__restrict__ new_counts) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const int n = min(counts[b], max_per);
+    int m = 0;
+    for (int j = 0; j < max_per; ++j) {
+        const uint32_t area = cnt[((size_t)b * max_per + j) * 2], ov = cnt[((size_t)b * max_per + j) * 2 + 1];
+        // numpy: int64 / int64 -> float64 true division; 0 / 0 = nan fails the comparison
+        const bool k = j < n && (!use_fg || (area > 0 && (double)ov / (double)area > thr));
+        keep[(size_t)b * max_per + j] = k;
+        newid[(size_t)b * max_per + j] = k ? ++m : 0;
+    }
+    new_counts[b] = m;
+}
+
+__global__ void __launch_bounds__(256)
+filter_relabel_kernel(const int32_t *__restrict__ lmap, const uint8_t *__restrict__ zero_depth, const int32_t *__restrict__ newid,
+                      int HW, int max_per, int32_t *__restrict__ out) {
+    const int b = blockIdx.y;
+    const size_t base = (size_t)b * HW;
+    const int32_t *nid = newid + (size_t)b * max_per;
+    for (int i = (blockIdx.x * 256 + threadIdx.x) * 4; i < HW; i += gridDim.x * 256 * 4) {
+        const int4 l = *reinterpret_cast<const int4 *>(lmap + base + i);
+        uint32_t z = 0u;
+        if (zero_depth) z = *reinterpret_cast<const uint32_t *>(zero_depth + base + i);
+        const int ls[4] = {l.x, l.y, l.z, l.w};
+        int o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            o[j] = (ls[j] > 0 && ls[j] <= max_per && !((z >> (8 * j)) & 0xffu)) ? __ldg(nid + ls[j] - 1) : 0;
+        *reinterpret_cast<int4 *>(out + base + i) = make_int4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 }  // namespace quber
 
 static int post_validate(const quber_post_params *p) {
@@ -690,4 +758,36 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
     }
     finalize_kernel<<<p.B, P_THREADS, 0, st>>>(p, io, ws.n_inst, ws.has_stuff, ws.stats);
     return check_launch("finalize_kernel");
+}
+
+extern "C" size_t quber_filter_workspace_bytes(int B, int max_per) {
+    if (B <= 0 || max_per <= 0) return 0;
+    return quber::align_up((size_t)B * max_per * 2 * sizeof(uint32_t), 256) + quber::align_up((size_t)B * max_per * sizeof(int32_t), 256);
+}
+
+extern "C" int quber_filter_instances(const int32_t *label_map, const int32_t *counts, const uint8_t *fg, const uint8_t *zero_depth,
+                                      int B, int H, int W, int max_per, double thr, int32_t *out_label_map, uint8_t *keep,
+                                      int32_t *new_counts, void *workspace, size_t workspace_bytes, void *stream) {
+    using namespace quber;
+    if (!label_map || !counts || !out_label_map || !keep || !new_counts || !workspace) return QUBER_E_INVALID;
+    if (B <= 0 || H <= 0 || W <= 0 || max_per <= 0 || max_per > 4096) return QUBER_E_INVALID;
+    const long long HWl = (long long)H * W;
+    if (HWl % 4 != 0 || HWl > 0x7fffffffll || B > 65535) return QUBER_E_UNSUPPORTED;
+    if (!aligned16(label_map) || !aligned16(out_label_map) || (fg && (reinterpret_cast<uintptr_t>(fg) & 3u)) ||
+        (zero_depth && (reinterpret_cast<uintptr_t>(zero_depth) & 3u)) || !aligned16(workspace))
+        return QUBER_E_ALIGN;
+    if (workspace_bytes < quber_filter_workspace_bytes(B, max_per)) return QUBER_E_WORKSPACE;
+    const int HW = (int)HWl;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint32_t *cnt = static_cast<uint32_t *>(workspace);
+    int32_t *newid = reinterpret_cast<int32_t *>(static_cast<char *>(workspace) + align_up((size_t)B * max_per * 2 * sizeof(uint32_t), 256));
+    QUBER_CUDA_TRY(cudaMemsetAsync(cnt, 0, (size_t)B * max_per * 2 * sizeof(uint32_t), st));
+    const int gx = max(1, min(cdiv(HW, 256 * 4 * 4), 64));
+    dim3 grid(gx, B);
+    filter_count_kernel<<<grid, 256, (size_t)max_per * 2 * sizeof(uint32_t), st>>>(label_map, fg, HW, max_per, cnt);
+    if (int rc = check_launch("filter_count_kernel")) return rc;
+    filter_decide_kernel<<<cdiv(B, 64), 64, 0, st>>>(cnt, counts, B, max_per, thr, fg != nullptr, keep, newid, new_counts);
+    if (int rc = check_launch("filter_decide_kernel")) return rc;
+    filter_relabel_kernel<<<grid, 256, 0, st>>>(label_map, zero_depth, newid, HW, max_per, out_label_map);
+    return check_launch("filter_relabel_kernel");
 }

@@ -265,6 +265,33 @@ def pack_input(image, offsets, mean, std):
     return out
 
 
+def filter_instances(label_map, counts, fg=None, zero_depth=None, thr=0.3, max_per=64):
+    """eval/refiner_model.py:271-288 on the label-map form of the refined instances: keep instance j iff
+    sum(mask_j & fg) / sum(mask_j) > thr, then clear the zero-depth pixels of the kept masks (OCID).
+    label_map [B,H,W] int32, counts [B] int32, fg / zero_depth [B,H,W] uint8 | None ->
+    (filtered label map [B,H,W] int32 with kept instances renumbered, keep [B,max_per] uint8, new counts [B] int32)."""
+    _need_cuda(label_map, "label_map", torch.int32)
+    _need_cuda(counts, "counts", torch.int32)
+    for t, n in ((fg, "fg"), (zero_depth, "zero_depth")):
+        if t is not None:
+            _need_cuda(t, n, torch.uint8)
+            if t.shape != label_map.shape:
+                raise ValueError(f"{n} must have the label map's shape")
+    B, H, W = label_map.shape
+    dev = label_map.device
+    out = torch.empty_like(label_map)
+    keep = torch.empty((B, max_per), dtype=torch.uint8, device=dev)
+    new_counts = torch.empty((B,), dtype=torch.int32, device=dev)
+    L = _lib.lib()
+    nbytes = L.quber_filter_workspace_bytes(B, max_per)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(L.quber_filter_instances(_ptr(label_map), _ptr(counts), _ptr(fg), _ptr(zero_depth), B, H, W, max_per, float(thr),
+                                            _ptr(out), _ptr(keep), _ptr(new_counts), _ptr(ws), nbytes, _stream()),
+                   "quber_filter_instances")
+    return out, keep, new_counts
+
+
 def group_norm_supported(x, groups):
     """True when quber_group_norm_relu takes this tensor as it lies (CUDA, fp32 / bf16, dense NCHW or channels-last,
     16-byte vectors along the contiguous dimension)."""

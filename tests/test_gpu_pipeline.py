@@ -72,3 +72,36 @@ def test_refine_batch_host_new_inputs_between_calls():
         out, _ = hp.refine_batch_host(hm, hh, chunk_frames=2)
         torch.cuda.current_stream().synchronize()
         assert np.array_equal(out["label_map"].numpy(), expect[it % 3])
+
+
+@pytest.mark.parametrize("use_fg,use_zd", [(True, True), (True, False), (False, True)])
+def test_filter_instances_matches_reference_loop(use_fg, use_zd):
+    """Foreground-overlap filter (> 0.3, float64 division) and OCID zero-depth clear (eval/refiner_model.py:271-288)
+    against the numpy restatement, on label maps of disjoint instances incl. ratios at exactly 0.3."""
+    rng = np.random.default_rng(5)
+    B, Hh, Ww, n = 3, 120, 160, 12
+    lm = np.zeros((B, Hh, Ww), np.int32)
+    for b in range(B):
+        for j in range(n):                                              # disjoint 10-row bands split in two widths
+            lm[b, 10 * j:10 * j + 10, 5 * j:5 * j + 60] = j + 1
+    fg = (rng.random((B, Hh, Ww)) < 0.35).astype(np.uint8) * 255
+    fg[0, 0:10, :] = 0
+    fg[0, 0:3, 0:60] = 1                                                # instance 1 of frame 0: overlap 180 / 600 = 0.3 exactly -> dropped
+    fg[0, 10:20, :] = 0
+    fg[0, 10:13, 5:65] = 7; fg[0, 13, 5] = 9                            # instance 2: 181 / 600 > 0.3 -> kept
+    zd = (rng.random((B, Hh, Ww)) < 0.1).astype(np.uint8)
+    counts = np.array([n, n - 2, n], np.int32)                          # frame 1 reports fewer instances: the last two labels are dropped
+    out, keep, newc = ops.filter_instances(torch.from_numpy(lm).cuda(), torch.from_numpy(counts).cuda(),
+                                           torch.from_numpy(fg).cuda() if use_fg else None,
+                                           torch.from_numpy(zd).cuda() if use_zd else None, thr=0.3, max_per=16)
+    out, keep, newc = out.cpu().numpy(), keep.cpu().numpy().astype(bool), newc.cpu().numpy()
+    for b in range(B):
+        masks = np.stack([lm[b] == j + 1 for j in range(counts[b])])
+        ref, rkeep = oracle.filter_instances(masks, fg[b] if use_fg else None, zd[b] if use_zd else None, 0.3)
+        assert np.array_equal(keep[b, :counts[b]], rkeep) and not keep[b, counts[b]:].any()
+        assert newc[b] == len(ref)
+        for i in range(len(ref)):
+            assert np.array_equal(out[b] == i + 1, ref[i]), (b, i)
+        assert out[b].max() <= len(ref)
+    if use_fg:
+        assert not keep[0, 0] and keep[0, 1]

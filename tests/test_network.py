@@ -150,3 +150,19 @@ def test_pixel_decoder_layout_and_position_embedding():
     feats = {k: torch.randn(1, c, 64 // s, 96 // s) for k, (c, s) in shapes.items()}
     with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
         pd.forward_features(feats)
+
+
+def test_caller_side_helpers_match_reference_values():
+    """normalize_depth (eval/preprocess_utils.py:12-28) on values whose expected bytes were produced by the reference's
+    own function in the build container, and the armbench resize rule (eval/refiner_model.py:228)."""
+    import numpy as np
+    from quber_b200.refiner_model import normalize_depth, resize_shortest_edge_shape
+    d = np.array([[0, 100, 250, 251.3, 600.7, 875, 1234.56, 1499.9, 1500, 1501, 65535]], np.float32)
+    out = normalize_depth(d)
+    assert out.shape == (1, 11, 3) and out.dtype == np.uint8
+    assert out[0, :, 0].tolist() == [0, 0, 0, 0, 71, 127, 200, 254, 255, 255, 255] and (out[..., 0] == out[..., 2]).all()
+    assert d[0, 0] == 0                                                   # the input is left untouched
+    d2 = np.array([[0, 0.1, 0.25, 0.4, 0.9, 1.2, 1.4999, 1.5, 9]], np.float32)
+    assert normalize_depth(d2, 0.25, 1.5)[0, :, 0].tolist() == [0, 0, 0, 30, 132, 193, 254, 255, 255]
+    assert resize_shortest_edge_shape(1080, 1920) == (750, 1333)
+    assert resize_shortest_edge_shape(480, 640) == (800, 1067)
