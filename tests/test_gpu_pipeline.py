@@ -105,3 +105,42 @@ def test_filter_instances_matches_reference_loop(use_fg, use_zd):
         assert out[b].max() <= len(ref)
     if use_fg:
         assert not keep[0, 0] and keep[0, 1]
+
+
+def test_refiner_model_adapter_filters_like_the_reference():
+    """quber_b200.refiner_model.MaskRefiner.predict (eval/refiner_model.py:224-297) around a stub predictor: OSD keeps the
+    fg-overlapping instances, OCID also clears zero-depth pixels, armbench returns the instances untouched."""
+    from quber_b200.meta_arch import Instances
+    from quber_b200.refiner_model import MaskRefiner
+    Hh, Ww = 240, 320
+    masks = synth.ellipse_masks(7, Hh, Ww, seed=3, axes=(12, 30), margin=30) != 0
+    taken = np.zeros((Hh, Ww), bool)
+    for m in masks:                                                    # refined instances are disjoint (model.py:331)
+        m &= ~taken
+        taken |= m
+    rng = np.random.default_rng(1)
+    fg = np.zeros((Hh, Ww), bool)
+    for j in (0, 2, 3, 6):
+        fg |= masks[j]
+    fg &= rng.random((Hh, Ww)) < 0.8
+    depth = rng.integers(300, 1400, (Hh, Ww)).astype(np.uint16)
+    depth[rng.random((Hh, Ww)) < 0.08] = 0
+
+    class Stub:
+        def predict(self, rgb, dep, init):
+            assert init.dtype == np.uint8 and init.max() == 255        # bool masks become 0 / 255 (:267)
+            assert dep is None or (dep.dtype == np.uint8 and dep.shape == (Hh, Ww, 3))
+            return [{"instances": Instances((Hh, Ww), pred_masks=torch.from_numpy(masks).cuda())}]
+
+    rgb = np.zeros((Hh, Ww, 3), np.uint8)
+    for dataset in ("OSD", "OCID", "armbench"):
+        r = MaskRefiner.__new__(MaskRefiner)
+        r.refiner_predictor, r.dataset, r.fg_model, r.inpaint = Stub(), dataset, None, None
+        got, output, secs, fgm = r.predict(rgb, None if dataset == "armbench" else depth, masks, fg_mask=fg)
+        if dataset == "armbench":
+            assert np.array_equal(got, masks) and fgm is None
+            continue
+        ref, keep = oracle.filter_instances(masks, fg, depth == 0 if dataset == "OCID" else None, 0.3)
+        assert keep.sum() == 4 and got.dtype == bool
+        assert np.array_equal(got, ref), dataset
+        assert "instances" in output and secs >= 0
