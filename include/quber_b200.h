@@ -252,6 +252,14 @@ int quber_filter_instances(const int32_t *label_map, const int32_t *counts, cons
                            int B, int H, int W, int max_per, double thr, int32_t *out_label_map, uint8_t *keep,
                            int32_t *new_counts, void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * quber_maxpool3x3s2 — F.max_pool2d(x, kernel_size=3, stride=2, padding=1) closing the ResNet stems
+ *     (maskrefiner/modeling/backbone/resnet.py:76, :125), channels-last.
+ *   x dev [N,H,W,C], y dev [N,Ho,Wo,C] with Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1; dtype 0: float32, 1: bfloat16;
+ *   C a multiple of 16 / sizeof(dtype).  Bit-exact with PyTorch on NaN-free input.
+ * ------------------------------------------------------------------------------------------- */
+int quber_maxpool3x3s2(const void *x, void *y, int N, int C, int H, int W, int dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -314,6 +314,41 @@ upsample_concat_kernel(const T *__restrict__ a, const T *__restrict__ b, T *__re
     Vec<T>::store(o, r);
 }
 
+// ------------------------------------------------------------------------------------------------ max-pool 3x3 / 2
+// F.max_pool2d(x, kernel_size=3, stride=2, padding=1) of the ResNet stems (maskrefiner/modeling/backbone/resnet.py:76,125)
+// on channels-last tensors: one thread per (output pixel, 16-byte channel vector), nine vector loads (L1-resident
+// neighbours), padding = -inf as PyTorch.
+template <typename T>
+__global__ void __launch_bounds__(256)
+maxpool3x3s2_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, size_t total, int C, int H, int W, int Ho, int Wo) {
+    constexpr int V = Vec<T>::N;
+    const int TP = C / V;
+    const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= total) return;
+    const int vec = (int)(idx % TP);
+    const size_t pix = idx / TP;
+    const int ox = (int)(pix % Wo), oy = (int)((pix / Wo) % Ho);
+    const size_t n = pix / ((size_t)Wo * Ho);
+    float m[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) m[j] = -INFINITY;
+#pragma unroll
+    for (int dy = -1; dy <= 1; ++dy) {
+        const int iy = 2 * oy + dy;
+        if (iy < 0 || iy >= H) continue;
+#pragma unroll
+        for (int dx = -1; dx <= 1; ++dx) {
+            const int ix = 2 * ox + dx;
+            if (ix < 0 || ix >= W) continue;
+            float v[V];
+            Vec<T>::load(x + ((n * H + iy) * (size_t)W + ix) * C + (size_t)vec * V, v);
+#pragma unroll
+            for (int j = 0; j < V; ++j) m[j] = fmaxf(m[j], v[j]);        // NaN-free activations (post-ReLU)
+        }
+    }
+    Vec<T>::store(y + pix * C + (size_t)vec * V, m);
+}
+
 }  // namespace quber
 
 extern "C" size_t quber_group_norm_workspace_bytes(int N, int C, int HW, int G, int layout) {
@@ -358,4 +393,23 @@ extern "C" int quber_upsample_concat(const void *a, const void *b, void *out, in
                                                                   static_cast<const __nv_bfloat16 *>(b),
                                                                   static_cast<__nv_bfloat16 *>(out), total, Ca, Cb, H, W, h, w, rh, rw);
     return check_launch("upsample_concat_kernel");
+}
+
+extern "C" int quber_maxpool3x3s2(const void *x, void *y, int N, int C, int H, int W, int dtype, void *stream) {
+    using namespace quber;
+    if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0 || (dtype != 0 && dtype != 1)) return QUBER_E_INVALID;
+    const int V = dtype == 0 ? 4 : 8;
+    if (C % V != 0) return QUBER_E_UNSUPPORTED;
+    if (!aligned16(x) || !aligned16(y)) return QUBER_E_ALIGN;
+    const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+    const size_t total = (size_t)N * Ho * Wo * (C / V);
+    if ((total + 255) / 256 > 0x7fffffffull) return QUBER_E_UNSUPPORTED;
+    const unsigned grid = (unsigned)((total + 255) / 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == 0)
+        maxpool3x3s2_nhwc_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float *>(x), static_cast<float *>(y), total, C, H, W, Ho, Wo);
+    else
+        maxpool3x3s2_nhwc_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16 *>(x),
+                                                                    static_cast<__nv_bfloat16 *>(y), total, C, H, W, Ho, Wo);
+    return check_launch("maxpool3x3s2_nhwc_kernel");
 }

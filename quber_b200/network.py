@@ -81,6 +81,15 @@ def _gn_relu(gn, x, relu, pre_bias=None):
     return ops.group_norm_relu(x, gn.weight, gn.bias, gn.num_groups, gn.eps, relu=relu, inplace=True, pre_bias=pre_bias)
 
 
+def _maxpool(conv, x):
+    """The stems' 3x3 / 2 max-pool: quber_maxpool3x3s2 on the inference plan, F.max_pool2d otherwise."""
+    if conv.__dict__.get("_plan") is not None and not conv.training and x.is_cuda:
+        from . import ops
+        if ops.maxpool3x3s2_supported(x):
+            return ops.maxpool3x3s2(x)
+    return F.max_pool2d(x, kernel_size=3, stride=2, padding=1)
+
+
 def run_conv_gn_relu(seq, x, fast):
     """An nn.Sequential of nn.Conv2d / nn.GroupNorm / nn.ReLU (resnet.py:466-479); with `fast`, GroupNorm + ReLU pairs
     go through the fused kernel."""
@@ -265,7 +274,7 @@ class DeepLabStem(nn.Module):
         x = self.conv1(x, relu=True)
         x = self.conv2(x, relu=True)
         x = self.conv3(x, relu=True)
-        return F.max_pool2d(x, kernel_size=3, stride=2, padding=1)
+        return _maxpool(self.conv3, x)
 
 
 class BasicStem(nn.Module):
@@ -278,7 +287,7 @@ class BasicStem(nn.Module):
                              norm=get_norm(norm, out_channels))
 
     def forward(self, x):
-        return F.max_pool2d(self.conv_1(x, relu=True), kernel_size=3, stride=2, padding=1)
+        return _maxpool(self.conv_1, self.conv_1(x, relu=True))
 
 
 class ResNet(nn.Module):

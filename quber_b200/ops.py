@@ -292,6 +292,23 @@ def filter_instances(label_map, counts, fg=None, zero_depth=None, thr=0.3, max_p
     return out, keep, new_counts
 
 
+def maxpool3x3s2_supported(x):
+    return (isinstance(x, torch.Tensor) and x.is_cuda and x.dim() == 4 and x.dtype in (torch.float32, torch.bfloat16)
+            and x.shape[1] % (16 // x.element_size()) == 0 and x.is_contiguous(memory_format=torch.channels_last))
+
+
+def maxpool3x3s2(x):
+    """F.max_pool2d(x, kernel_size=3, stride=2, padding=1) (resnet.py:76, :125) on a channels-last CUDA tensor."""
+    if not maxpool3x3s2_supported(x):
+        raise ValueError("maxpool3x3s2: needs a channels-last CUDA fp32/bf16 tensor whose channels fill 16-byte vectors")
+    N, C, H, W = x.shape
+    y = torch.empty((N, C, (H - 1) // 2 + 1, (W - 1) // 2 + 1), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().quber_maxpool3x3s2(_ptr(x), _ptr(y), N, C, H, W, 0 if x.dtype == torch.float32 else 1, _stream()),
+                   "quber_maxpool3x3s2")
+    return y
+
+
 def group_norm_supported(x, groups):
     """True when quber_group_norm_relu takes this tensor as it lies (CUDA, fp32 / bf16, dense NCHW or channels-last,
     16-byte vectors along the contiguous dimension)."""

@@ -367,3 +367,16 @@ def test_network_cuda_graph_replay_matches_eager():
             assert torch.equal(e[k], g[k]), k
     for k in again:
         assert torch.equal(again[k], eager[0][k])
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(2, 64, 48, 64), (1, 128, 37, 51), (2, 8, 5, 7)])
+def test_maxpool3x3s2_bit_exact_with_torch(dt, shape):
+    g = torch.Generator(device=DEV).manual_seed(sum(shape))
+    x = torch.randn(*shape, device=DEV, generator=g).to(dt).contiguous(memory_format=torch.channels_last)
+    ref = torch.nn.functional.max_pool2d(x, kernel_size=3, stride=2, padding=1)
+    out = ops.maxpool3x3s2(x)
+    assert out.shape == ref.shape and out.is_contiguous(memory_format=torch.channels_last)
+    assert torch.equal(out, ref)
+    with pytest.raises(ValueError):
+        ops.maxpool3x3s2(x.contiguous())
