@@ -188,6 +188,11 @@ int quber_pack_input(const uint8_t *image, const float *offsets, const float *me
                      int CO, int H, int W, float *out, void *stream);
 int quber_fuse_concat(const float *const *sources, const int *channels, const int *ops, int n_sources, int B, int h,
                       int w, int layout, int pitch, void *out, void *stream);
+/* quber_fuse_concat_rows — the same chain (model.py:745-759) for sources that are already channels-last rows:
+ *   sources[i] dev [rows, channels[i]] float32 (src_bf16[i] == 0) or bfloat16 (!= 0), rows = B*h*w;
+ *   out dev [rows, pitch] float32 | bfloat16 (out_bf16), columns >= sum(channels) zero-filled. */
+int quber_fuse_concat_rows(const void *const *sources, const int *channels, const int *ops, const int *src_bf16,
+                           int n_sources, size_t rows, int pitch, int out_bf16, void *out, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Dense projections on tcgen05 / TMEM:  C[M,N] = act(A[M,K] * W[N,K]^T + bias[N])

@@ -47,6 +47,7 @@ SYMBOLS = {
     "quber_gemm_timeouts": (c_i, []),
     "quber_pack_input": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_fuse_concat": (c_i, [c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
+    "quber_fuse_concat_rows": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_sz, c_i, c_i, c_vp, c_vp]),
     "quber_post_workspace_bytes": (c_sz, [ctypes.POINTER(PostParams)]),
     "quber_post_process": (c_i, [ctypes.POINTER(PostParams), ctypes.POINTER(PostIO), c_vp, c_sz, c_vp]),
     "quber_group_norm_workspace_bytes": (c_sz, [c_i, c_i, c_i, c_i, c_i]),

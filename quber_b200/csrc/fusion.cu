@@ -121,6 +121,57 @@ fuse_concat_kernel(FuseArgs a, int ctot, int pitch, size_t hw, void *__restrict_
     }
 }
 
+// ---------------------------------------------------------------------------------------------- fuse_concat, NHWC sources
+// Same operation as fuse_concat_kernel for sources that are already channels-last rows [rows, C_s] in fp32 or bf16 (what
+// the cuDNN tensor-core convolutions produce): one warp per pixel row, lanes across channels, no layout copies.
+struct FuseRowsArgs {
+    const void *src[QUBER_FUSE_MAX_SOURCES];
+    int channels[QUBER_FUSE_MAX_SOURCES];
+    int op[QUBER_FUSE_MAX_SOURCES];
+    int bf16[QUBER_FUSE_MAX_SOURCES];
+    int n;
+};
+
+template <bool OUT_BF16>
+__global__ void __launch_bounds__(256)
+fuse_concat_rows_kernel(FuseRowsArgs a, int ctot, int pitch, size_t rows, void *__restrict__ out) {
+    const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    auto put = [&](int c, float v) {
+        if (OUT_BF16) static_cast<__nv_bfloat16 *>(out)[row * pitch + c] = __float2bfloat16_rn(v);
+        else static_cast<float *>(out)[row * pitch + c] = v;
+    };
+    int coff = 0;
+    for (int s = 0; s < a.n; ++s) {
+        const int C = a.channels[s];
+        auto get = [&](int c) -> float {
+            return a.bf16[s] ? __bfloat162float(static_cast<const __nv_bfloat16 *>(a.src[s])[row * C + c])
+                             : __ldg(static_cast<const float *>(a.src[s]) + row * C + c);
+        };
+        if (a.op[s] == 2) {                               // softmax over C <= 8 channels, lanes 0..C-1
+            const float v = lane < C ? get(lane) : -INFINITY;
+            float mx = v;
+#pragma unroll
+            for (int o = 4; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            const float e = lane < C ? __expf(v - mx) : 0.f;
+            float sum = e;
+#pragma unroll
+            for (int o = 4; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (lane < C) put(coff + lane, e * (1.0f / sum));
+        } else {
+            const bool sg = a.op[s] == 1;
+            for (int c = lane; c < C; c += 32) {
+                float v = get(c);
+                if (sg) v = sigmoid_f(v);
+                put(coff + c, v);
+            }
+        }
+        coff += C;
+    }
+    for (int c = ctot + lane; c < pitch; c += 32) put(c, 0.f);
+}
+
 }  // namespace quber
 
 extern "C" int quber_pack_input(const uint8_t *image, const float *offsets, const float *mean, const float *stdv, int B, int C,
@@ -169,4 +220,27 @@ extern "C" int quber_fuse_concat(const float *const *sources, const int *channel
         fuse_concat_kernel<2><<<grid, F_THREADS, smem, st>>>(a, ctot, pitch, hw, out);
     }
     return check_launch("fuse_concat_kernel");
+}
+
+extern "C" int quber_fuse_concat_rows(const void *const *sources, const int *channels, const int *ops, const int *src_bf16,
+                                      int n_sources, size_t rows, int pitch, int out_bf16, void *out, void *stream) {
+    using namespace quber;
+    if (!sources || !channels || !ops || !src_bf16 || !out || n_sources <= 0 || n_sources > QUBER_FUSE_MAX_SOURCES || rows == 0)
+        return QUBER_E_INVALID;
+    FuseRowsArgs a;
+    a.n = n_sources;
+    int ctot = 0;
+    for (int s = 0; s < n_sources; ++s) {
+        if (!sources[s] || channels[s] <= 0 || ops[s] < 0 || ops[s] > 2) return QUBER_E_INVALID;
+        if (ops[s] == 2 && channels[s] > QUBER_FUSE_MAX_SOFTMAX) return QUBER_E_UNSUPPORTED;
+        a.src[s] = sources[s]; a.channels[s] = channels[s]; a.op[s] = ops[s]; a.bf16[s] = src_bf16[s] != 0;
+        ctot += channels[s];
+    }
+    if (pitch < ctot) return QUBER_E_INVALID;
+    if ((rows + 7) / 8 > 0x7fffffffull) return QUBER_E_UNSUPPORTED;
+    const unsigned grid = (unsigned)((rows + 7) / 8);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (out_bf16) fuse_concat_rows_kernel<true><<<grid, 256, 0, st>>>(a, ctot, pitch, rows, out);
+    else fuse_concat_rows_kernel<false><<<grid, 256, 0, st>>>(a, ctot, pitch, rows, out);
+    return check_launch("fuse_concat_rows_kernel");
 }

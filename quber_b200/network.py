@@ -639,6 +639,10 @@ class MaskRefinerInsEmbedHead(DeepLabV3PlusDecoder):
                 srcs.append(output_dict[k]); ops_.append("softmax" if "eee" in k else "sigmoid")
         if self.use_kernels and y.is_cuda:
             from . import ops
+            cl = torch.channels_last
+            if self.gemm_1x1 and all(s.dtype in (torch.float32, torch.bfloat16) and s.is_contiguous(memory_format=cl) for s in srcs):
+                ctot = sum(s.shape[1] for s in srcs)        # channels-last already: no NCHW fp32 copies
+                return None, ops.fuse_concat_rows(srcs, ops_, pitch=(ctot + 7) // 8 * 8)
             srcs = [s.float().contiguous() for s in srcs]
             if self.gemm_1x1:
                 ctot = sum(s.shape[1] for s in srcs)

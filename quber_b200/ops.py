@@ -409,6 +409,34 @@ def fuse_concat(sources, ops_, layout="nchw", pitch=None):
     return out
 
 
+def fuse_concat_rows(sources, ops_, pitch=None, out_dtype=torch.bfloat16):
+    """fuse_concat for channels-last sources (model.py:745-759): each source [B,C_i,h,w] float32 | bfloat16 dense in
+    channels-last memory -> rows [B*h*w, pitch] (zero padded), no layout copies."""
+    if len(sources) != len(ops_) or not sources:
+        raise ValueError("sources and ops must have the same non-zero length")
+    B, _, h, w = sources[0].shape
+    for i, t in enumerate(sources):
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype in (torch.float32, torch.bfloat16)
+                and t.is_contiguous(memory_format=torch.channels_last)):
+            raise ValueError(f"sources[{i}] must be a channels-last CUDA float32 / bfloat16 tensor")
+        if t.shape[0] != B or t.shape[2:] != sources[0].shape[2:]:
+            raise ValueError("Sizes of tensors must match except in dimension 1")
+    ch = [int(t.shape[1]) for t in sources]
+    ctot = sum(ch)
+    pitch = ctot if pitch is None else int(pitch)
+    rows = B * h * w
+    out = torch.empty((rows, pitch), dtype=out_dtype, device=sources[0].device)
+    n = len(sources)
+    ptrs = (ctypes.c_void_p * n)(*[t.data_ptr() for t in sources])
+    chs = (ctypes.c_int * n)(*ch)
+    opc = (ctypes.c_int * n)(*[_FUSE_OPS[o] for o in ops_])
+    bf = (ctypes.c_int * n)(*[int(t.dtype == torch.bfloat16) for t in sources])
+    with torch.cuda.device(sources[0].device):
+        _lib.check(_lib.lib().quber_fuse_concat_rows(ptrs, chs, opc, bf, n, rows, pitch, int(out_dtype == torch.bfloat16), _ptr(out),
+                                                     _stream()), "quber_fuse_concat_rows")
+    return out
+
+
 # ---- torch.library registration: torch.ops.quber.* ----------------------------------------------
 def _register():
     try:

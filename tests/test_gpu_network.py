@@ -380,3 +380,23 @@ def test_maxpool3x3s2_bit_exact_with_torch(dt, shape):
     assert torch.equal(out, ref)
     with pytest.raises(ValueError):
         ops.maxpool3x3s2(x.contiguous())
+
+
+def test_fuse_concat_rows_matches_torch_chain_on_channels_last_sources():
+    g = torch.Generator(device=DEV).manual_seed(11)
+    cl = lambda t: t.contiguous(memory_format=torch.channels_last)
+    y = cl(torch.randn(2, 128, 30, 37, device=DEV, generator=g).bfloat16())
+    feat = cl(torch.randn(2, 32, 30, 37, device=DEV, generator=g).bfloat16())
+    eee = cl(torch.randn(2, 4, 30, 37, device=DEV, generator=g) * 3)                     # float32 logits
+    fg = cl(torch.randn(2, 1, 30, 37, device=DEV, generator=g).bfloat16() * 3)
+    ref = torch.cat([y.float(), feat.float(), eee.softmax(dim=1), fg.float().sigmoid()], dim=1)      # model.py:745-759
+    ref_rows = ref.permute(0, 2, 3, 1).reshape(-1, 165)
+    rows = ops.fuse_concat_rows([y, feat, eee, fg], ["copy", "copy", "softmax", "sigmoid"], pitch=168)
+    assert rows.shape == (2 * 30 * 37, 168) and rows.dtype == torch.bfloat16
+    torch.testing.assert_close(rows[:, :165].float(), ref_rows, rtol=2 ** -8, atol=1e-6)
+    assert torch.equal(rows[:, :160], torch.cat([y, feat], 1).permute(0, 2, 3, 1).reshape(-1, 160))   # copies are exact
+    assert not rows[:, 165:].any()
+    r32 = ops.fuse_concat_rows([y, feat, eee, fg], ["copy", "copy", "softmax", "sigmoid"], out_dtype=torch.float32)
+    torch.testing.assert_close(r32, ref_rows, rtol=1e-5, atol=2e-6)
+    with pytest.raises(ValueError):
+        ops.fuse_concat_rows([y.contiguous(), feat], ["copy", "copy"])
