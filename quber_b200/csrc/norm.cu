@@ -17,7 +17,8 @@
 namespace quber {
 
 constexpr int GN_THREADS = 256;
-constexpr int GN_TILE_PIX = 128;       // NHWC: pixels per CTA
+// NHWC: pixels per CTA, chosen per call (gn_tile_pix): large enough to amortise the per-CTA prologue (pivot loads) and the
+// serial fixed-order combine, small enough for >= ~4 CTAs per SM
 constexpr int GN_TILE_ELEMS = 16384;   // NCHW: elements of one (sample, group) slice per CTA
 
 template <typename T> struct Vec;      // one 16-byte access
@@ -132,7 +133,7 @@ gn_apply_nchw_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
 // when C / V >= 256, else vector t % (C / V) on pixel rows t / (C / V), t / (C / V) + rows, ...
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
-gn_stats_nhwc_kernel(const T *__restrict__ x, const float *__restrict__ pb, int HW, int C, int cg, int tiles,
+gn_stats_nhwc_kernel(const T *__restrict__ x, const float *__restrict__ pb, int HW, int C, int cg, int tiles, int tile_pix,
                      float *__restrict__ part /* [N][G][tiles][2] */) {
     constexpr int V = Vec<T>::N;
     extern __shared__ float acc[];                       // [rows][C][2]
@@ -141,7 +142,7 @@ gn_stats_nhwc_kernel(const T *__restrict__ x, const float *__restrict__ pb, int 
     const int rows = TP >= GN_THREADS ? 1 : GN_THREADS / TP;
     const int row = TP >= GN_THREADS ? 0 : tid / TP;
     const T *xs = x + (size_t)n * HW * C;
-    const int p0 = t * GN_TILE_PIX, p1 = min(HW, p0 + GN_TILE_PIX);
+    const int p0 = t * tile_pix, p1 = min(HW, p0 + tile_pix);
     const int G = C / cg;
     for (int ch = (TP >= GN_THREADS ? tid : tid % TP); ch < TP; ch += GN_THREADS) {
         if (TP < GN_THREADS && tid >= rows * TP) break;  // 256 % TP != 0: surplus threads idle
@@ -181,7 +182,7 @@ gn_stats_nhwc_kernel(const T *__restrict__ x, const float *__restrict__ pb, int 
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
 gn_apply_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__restrict__ pb, const float *__restrict__ gamma,
-                     const float *__restrict__ beta, const float *__restrict__ stats, int HW, int C, int cg, int relu) {
+                     const float *__restrict__ beta, const float *__restrict__ stats, int HW, int C, int cg, int relu, int tile_pix) {
     constexpr int V = Vec<T>::N;
     const int n = blockIdx.y, t = blockIdx.x, tid = threadIdx.x;
     const int TP = C / V;
@@ -189,7 +190,7 @@ gn_apply_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
     const int row = TP >= GN_THREADS ? 0 : tid / TP;
     const int G = C / cg;
     const size_t base = (size_t)n * HW * C;
-    const int p0 = t * GN_TILE_PIX, p1 = min(HW, p0 + GN_TILE_PIX);
+    const int p0 = t * tile_pix, p1 = min(HW, p0 + tile_pix);
     for (int ch = (TP >= GN_THREADS ? tid : tid % TP); ch < TP; ch += GN_THREADS) {
         if (TP < GN_THREADS && tid >= rows * TP) break;
         float a[V], b[V];
@@ -233,9 +234,15 @@ __global__ void gn_finalize_kernel(const T *__restrict__ x, const float *__restr
     stats[2 * i + 1] = (float)(1.0 / sqrt(var + (double)eps));
 }
 
-static int gn_tiles(int C, int HW, int G, int layout) {
+static int gn_tile_pix(int N, int HW) {
+    long long t = ((long long)HW * N / 592 + 63) / 64 * 64;          // ~4 CTAs per SM over the launch
+    return (int)(t < 64 ? 64 : t > 512 ? 512 : t);
+}
+
+static int gn_tiles(int N, int C, int HW, int G, int layout) {
     if (layout == 0) return (int)(((size_t)(C / G) * HW + GN_TILE_ELEMS - 1) / GN_TILE_ELEMS);
-    return (HW + GN_TILE_PIX - 1) / GN_TILE_PIX;
+    const int tp = gn_tile_pix(N, HW);
+    return (HW + tp - 1) / tp;
 }
 
 template <typename T>
@@ -244,7 +251,7 @@ static int gn_run(const void *xv, void *yv, const float *pb, const float *gamma,
     constexpr int V = Vec<T>::N;
     const T *x = static_cast<const T *>(xv);
     T *y = static_cast<T *>(yv);
-    const int cg = C / G, tiles = gn_tiles(C, HW, G, layout);
+    const int cg = C / G, tiles = gn_tiles(N, C, HW, G, layout), tile_pix = gn_tile_pix(N, HW);
     float *part = ws, *stats = ws + (size_t)N * G * tiles * 2;
     const double count = (double)cg * HW;
     if (layout == 0) {
@@ -267,11 +274,11 @@ static int gn_run(const void *xv, void *yv, const float *pb, const float *gamma,
         QUBER_CUDA_TRY(cudaFuncSetAttribute(gn_stats_nhwc_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     dim3 grid(tiles, N);
-    gn_stats_nhwc_kernel<T><<<grid, GN_THREADS, smem, st>>>(x, pb, HW, C, cg, tiles, part);
+    gn_stats_nhwc_kernel<T><<<grid, GN_THREADS, smem, st>>>(x, pb, HW, C, cg, tiles, tile_pix, part);
     if (int rc = check_launch("gn_stats_nhwc_kernel")) return rc;
     gn_finalize_kernel<T><<<cdiv(N * G, 128), 128, 0, st>>>(x, pb, cg, part, N * G, G, tiles, count, (size_t)C * HW, (size_t)cg, eps, stats);
     if (int rc = check_launch("gn_finalize_kernel")) return rc;
-    gn_apply_nhwc_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, y, pb, gamma, beta, stats, HW, C, cg, relu);
+    gn_apply_nhwc_kernel<T><<<grid, GN_THREADS, 0, st>>>(x, y, pb, gamma, beta, stats, HW, C, cg, relu, tile_pix);
     return check_launch("gn_apply_nhwc_kernel");
 }
 
@@ -353,7 +360,7 @@ maxpool3x3s2_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, size_t tota
 
 extern "C" size_t quber_group_norm_workspace_bytes(int N, int C, int HW, int G, int layout) {
     if (N <= 0 || C <= 0 || HW <= 0 || G <= 0 || C % G != 0 || (layout != 0 && layout != 1)) return 0;
-    return ((size_t)N * G * quber::gn_tiles(C, HW, G, layout) * 2 + (size_t)N * G * 2) * sizeof(float);
+    return ((size_t)N * G * quber::gn_tiles(N, C, HW, G, layout) * 2 + (size_t)N * G * 2) * sizeof(float);
 }
 
 extern "C" int quber_group_norm_relu(const void *x, void *y, const float *pre_bias, const float *gamma, const float *beta, int N, int C, int HW, int G,
