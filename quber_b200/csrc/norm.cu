@@ -129,7 +129,7 @@ gn_apply_nchw_kernel(const T *__restrict__ x, T *__restrict__ y, const float *__
 }
 
 // ------------------------------------------------------------------------------------------------ NHWC
-// grid (T, N): CTA = GN_TILE_PIX pixels x C channels.  Thread t owns the channel vectors {t, t + 256, ...} (< C / V)
+// grid (T, N): CTA = tile_pix pixels x C channels.  Thread t owns the channel vectors {t, t + 256, ...} (< C / V)
 // when C / V >= 256, else vector t % (C / V) on pixel rows t / (C / V), t / (C / V) + rows, ...
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
