@@ -309,6 +309,47 @@ def maxpool3x3s2(x):
     return y
 
 
+def add_layer_norm(a, b, weight, bias, eps=1e-5, want_bf16=False):
+    """LayerNorm(a + b) over the last dimension (msdeformattn.py:119-120, :126-127) in one pass.  a, b [..., C] float32
+    CUDA (b may be None), C a multiple of 128 (<= 1024) -> y float32 [, y_bf16]."""
+    _need_cuda(a, "a", torch.float32)
+    if b is not None:
+        _need_cuda(b, "b", torch.float32)
+        if b.shape != a.shape:
+            raise ValueError("a and b must have the same shape")
+    C = a.shape[-1]
+    if C % 128 or C > 1024 or C // 128 in (5, 7):
+        raise ValueError("add_layer_norm: the normalised dimension must be 128 * {1,2,3,4,6,8}")
+    rows = a.numel() // C
+    y = torch.empty_like(a)
+    y16 = torch.empty(a.shape, dtype=torch.bfloat16, device=a.device) if want_bf16 else None
+    g = weight.detach().float().contiguous()
+    bt = bias.detach().float().contiguous()
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.lib().quber_add_layer_norm(_ptr(a), _ptr(b), _ptr(g), _ptr(bt), rows, C, float(eps), _ptr(y), _ptr(y16),
+                                                   _stream()), "quber_add_layer_norm")
+    return (y, y16) if want_bf16 else y
+
+
+def msda_prepare(oa, reference_points, spatial_shapes, n_heads, n_levels, n_points):
+    """OPS/modules/ms_deform_attn.py:102-109: the fused sampling_offsets | attention_weights projection
+    oa [N,Q,M*L*P*3] float32 and reference_points [N,Q,L,2] -> (sampling_locations [N,Q,M,L,P,2], attention weights
+    [N,Q,M,L,P] after the softmax over L*P)."""
+    _need_cuda(oa, "oa", torch.float32)
+    _need_cuda(reference_points, "reference_points", torch.float32)
+    _need_cuda(spatial_shapes, "spatial_shapes", torch.int64)
+    N, Q, ld = oa.shape
+    M, L, P = n_heads, n_levels, n_points
+    if ld != M * L * P * 3 or tuple(reference_points.shape) != (N, Q, L, 2):
+        raise ValueError("msda_prepare: oa must be [N,Q,M*L*P*3] and reference_points [N,Q,L,2]")
+    loc = torch.empty((N, Q, M, L, P, 2), dtype=torch.float32, device=oa.device)
+    aw = torch.empty((N, Q, M, L, P), dtype=torch.float32, device=oa.device)
+    with torch.cuda.device(oa.device):
+        _lib.check(_lib.lib().quber_msda_prepare(_ptr(oa), ld, _ptr(reference_points), _ptr(spatial_shapes), N * Q, M, L, P,
+                                                 _ptr(loc), _ptr(aw), _stream()), "quber_msda_prepare")
+    return loc, aw
+
+
 def group_norm_supported(x, groups):
     """True when quber_group_norm_relu takes this tensor as it lies (CUDA, fp32 / bf16, dense NCHW or channels-last,
     16-byte vectors along the contiguous dimension)."""

@@ -129,22 +129,34 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
             value = value.masked_fill(padding_mask[..., None], float(0))
         oa = ops.gemm_bias_act(q, *W["qk"], out_dtype=torch.float32)                          # :102-103, one GEMM
         n_off = M * L * P * 2
-        off = oa[..., :n_off].reshape(N, S, M, L, P, 2)
-        aw = F.softmax(oa[..., n_off:].reshape(N, S, M, L * P), -1).view(N, S, M, L, P).contiguous()
-        if reference_points.shape[-1] == 2:                                                   # :106-109
-            normalizer = torch.stack([spatial_shapes[..., 1], spatial_shapes[..., 0]], -1)
-            loc = reference_points[:, :, None, :, None, :] + off / normalizer[None, None, None, :, None, :]
-        elif reference_points.shape[-1] == 4:
-            loc = reference_points[:, :, None, :, None, :2] + off / P * reference_points[:, :, None, :, None, 2:] * 0.5
+        if reference_points.shape[-1] == 2 and reference_points.dtype == torch.float32:
+            # offsets / (W_l, H_l) + reference, and the softmax over L*P, in one pass over the GEMM output
+            loc, aw = ops.msda_prepare(oa.view(N, S, -1), reference_points.contiguous(), spatial_shapes, M, L, P)
         else:
-            raise ValueError('Last dim of reference_points must be 2 or 4, but get {} instead.'.format(reference_points.shape[-1]))
-        samp = ops.msda_forward(value.view(N, S, M, C // M), spatial_shapes, level_start_index, loc.contiguous(), aw)
+            off = oa[..., :n_off].reshape(N, S, M, L, P, 2)
+            aw = F.softmax(oa[..., n_off:].reshape(N, S, M, L * P), -1).view(N, S, M, L, P).contiguous()
+            if reference_points.shape[-1] == 2:                                               # :106-109
+                normalizer = torch.stack([spatial_shapes[..., 1], spatial_shapes[..., 0]], -1)
+                loc = reference_points[:, :, None, :, None, :] + off / normalizer[None, None, None, :, None, :]
+            elif reference_points.shape[-1] == 4:
+                loc = reference_points[:, :, None, :, None, :2] + off / P * reference_points[:, :, None, :, None, 2:] * 0.5
+            else:
+                raise ValueError('Last dim of reference_points must be 2 or 4, but get {} instead.'.format(reference_points.shape[-1]))
+            loc = loc.contiguous()
+        samp = ops.msda_forward(value.view(N, S, M, C // M), spatial_shapes, level_start_index, loc, aw)
         src2 = ops.gemm_bias_act(samp, *W["o"], out_dtype=torch.float32)                      # :124
-        src = self.norm1(src + src2)
+        fused_ln = C % 128 == 0 and C <= 1024 and C // 128 not in (5, 7)
+        if fused_ln:                                                                          # norm1(src + src2), one pass
+            r = ops.add_layer_norm(src.contiguous(), src2.view(N, S, C), self.norm1.weight, self.norm1.bias, self.norm1.eps, want_bf16=bf16)
+            src, src16 = r if bf16 else (r, None)
+        else:
+            src, src16 = self.norm1(src + src2), None
         if self.activation_name != "relu":
             return self.forward_ffn(src)
-        hmid = ops.gemm_bias_act(src.to(dt), *W["l1"], act="relu", out_dtype=dt)              # msdeformattn.py:116-120
+        hmid = ops.gemm_bias_act(src16 if src16 is not None else src.to(dt), *W["l1"], act="relu", out_dtype=dt)   # msdeformattn.py:116-120
         src2 = ops.gemm_bias_act(hmid, *W["l2"], out_dtype=torch.float32)
+        if fused_ln:
+            return ops.add_layer_norm(src, src2.view(N, S, C), self.norm2.weight, self.norm2.bias, self.norm2.eps)
         return self.norm2(src + src2)
 
     def forward(self, src, pos, reference_points, spatial_shapes, level_start_index, padding_mask=None):

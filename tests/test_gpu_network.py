@@ -400,3 +400,40 @@ def test_fuse_concat_rows_matches_torch_chain_on_channels_last_sources():
     torch.testing.assert_close(r32, ref_rows, rtol=1e-5, atol=2e-6)
     with pytest.raises(ValueError):
         ops.fuse_concat_rows([y.contiguous(), feat], ["copy", "copy"])
+
+
+@pytest.mark.parametrize("C", [128, 256, 768, 1024])
+def test_add_layer_norm_matches_float64_reference(C):
+    g = torch.Generator(device=DEV).manual_seed(C)
+    a = torch.randn(3, 701, C, device=DEV, generator=g) * 2 + 5.0
+    b = torch.randn(3, 701, C, device=DEV, generator=g)
+    ln = torch.nn.LayerNorm(C).to(DEV)
+    ln.weight.data.uniform_(0.5, 1.5, generator=g); ln.bias.data.normal_(0, 0.5, generator=g)
+    ref = torch.nn.functional.layer_norm((a + b).double(), (C,), ln.weight.double(), ln.bias.double(), ln.eps)
+    y, y16 = ops.add_layer_norm(a, b, ln.weight, ln.bias, ln.eps, want_bf16=True)
+    assert float((y.double() - ref).abs().max()) <= 5e-6
+    assert torch.equal(y16, y.bfloat16())
+    y1 = ops.add_layer_norm(a, None, ln.weight, ln.bias, ln.eps)
+    ref1 = torch.nn.functional.layer_norm(a.double(), (C,), ln.weight.double(), ln.bias.double(), ln.eps)
+    assert float((y1.double() - ref1).abs().max()) <= 5e-6
+    torch_y = ln(a + b)
+    assert float((y - torch_y).abs().max()) <= 5e-6                          # and as close to torch's own kernel
+    with pytest.raises(ValueError):
+        ops.add_layer_norm(a[..., :100].contiguous(), None, ln.weight[:100], ln.bias[:100])
+
+
+def test_msda_prepare_matches_module_arithmetic():
+    """OPS/modules/ms_deform_attn.py:102-109 restated with torch on the same GEMM output."""
+    g = torch.Generator(device=DEV).manual_seed(8)
+    N, Q, M, L, P = 2, 333, 8, 3, 4
+    oa = torch.randn(N, Q, M * L * P * 3, device=DEV, generator=g)
+    ref_pts = torch.rand(N, Q, L, 2, device=DEV, generator=g)
+    shapes = torch.tensor([[15, 20], [30, 40], [60, 80]], dtype=torch.long, device=DEV)
+    loc, aw = ops.msda_prepare(oa, ref_pts, shapes, M, L, P)
+    off = oa[..., : M * L * P * 2].reshape(N, Q, M, L, P, 2)
+    aw_ref = torch.softmax(oa[..., M * L * P * 2:].reshape(N, Q, M, L * P), -1).view(N, Q, M, L, P)
+    norm = torch.stack([shapes[..., 1], shapes[..., 0]], -1)
+    loc_ref = ref_pts[:, :, None, :, None, :] + off / norm[None, None, None, :, None, :]
+    assert torch.equal(loc, loc_ref)                                          # one division and one add per element: exact
+    torch.testing.assert_close(aw, aw_ref, rtol=2e-6, atol=1e-8)
+    torch.testing.assert_close(aw.sum((-1, -2)), torch.ones(N, Q, M, device=DEV), rtol=0, atol=1e-6)
