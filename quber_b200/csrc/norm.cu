@@ -439,6 +439,46 @@ msda_prepare_kernel(const float *__restrict__ oa, int ld, const float *__restric
     }
 }
 
+// P == 4 (every config of the path): 16-byte accesses, the head's logits and offsets held in registers.
+template <int L>
+__global__ void __launch_bounds__(256)
+msda_prepare_p4_kernel(const float *__restrict__ oa, int ld, const float *__restrict__ ref, const int64_t *__restrict__ shapes,
+                       size_t rows, int M, float *__restrict__ loc, float *__restrict__ attn) {
+    constexpr int LP = L * 4;
+    const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= rows * M) return;
+    const size_t row = idx / M;
+    const int m = (int)(idx % M);
+    const float4 *off4 = reinterpret_cast<const float4 *>(oa + row * ld + (size_t)m * LP * 2);
+    const float4 *lg4 = reinterpret_cast<const float4 *>(oa + row * ld + (size_t)M * LP * 2 + (size_t)m * LP);
+    float4 lgv[L];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int l = 0; l < L; ++l) {
+        lgv[l] = __ldg(lg4 + l);
+        mx = fmaxf(fmaxf(mx, fmaxf(lgv[l].x, lgv[l].y)), fmaxf(lgv[l].z, lgv[l].w));
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int l = 0; l < L; ++l) {                        // same summation order as the scalar kernel
+        lgv[l].x = expf(lgv[l].x - mx); sum += lgv[l].x;
+        lgv[l].y = expf(lgv[l].y - mx); sum += lgv[l].y;
+        lgv[l].z = expf(lgv[l].z - mx); sum += lgv[l].z;
+        lgv[l].w = expf(lgv[l].w - mx); sum += lgv[l].w;
+    }
+    const float inv = 1.0f / sum;
+    float4 *lo4 = reinterpret_cast<float4 *>(loc + idx * LP * 2), *ao4 = reinterpret_cast<float4 *>(attn + idx * LP);
+#pragma unroll
+    for (int l = 0; l < L; ++l) {
+        const float w = (float)shapes[2 * l + 1], h = (float)shapes[2 * l];
+        const float2 r = __ldg(reinterpret_cast<const float2 *>(ref + (row * L + l) * 2));
+        const float4 o0 = __ldg(off4 + 2 * l), o1 = __ldg(off4 + 2 * l + 1);
+        lo4[2 * l] = make_float4(r.x + o0.x / w, r.y + o0.y / h, r.x + o0.z / w, r.y + o0.w / h);
+        lo4[2 * l + 1] = make_float4(r.x + o1.x / w, r.y + o1.y / h, r.x + o1.z / w, r.y + o1.w / h);
+        ao4[l] = make_float4(lgv[l].x * inv, lgv[l].y * inv, lgv[l].z * inv, lgv[l].w * inv);
+    }
+}
+
 }  // namespace quber
 
 extern "C" size_t quber_group_norm_workspace_bytes(int N, int C, int HW, int G, int layout) {
@@ -534,7 +574,13 @@ extern "C" int quber_msda_prepare(const float *oa, int ld, const float *referenc
         return QUBER_E_INVALID;
     const size_t n = rows * (size_t)M;
     if ((n + 255) / 256 > 0x7fffffffull) return QUBER_E_UNSUPPORTED;
-    msda_prepare_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(oa, ld, reference_points, shapes, rows, M, L, P,
-                                                                                      loc, attn);
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool vec = P == 4 && ld % 4 == 0 && aligned16(oa) && aligned16(loc) && aligned16(attn) &&
+                     (reinterpret_cast<uintptr_t>(reference_points) & 7u) == 0;
+    if (vec && L == 3) msda_prepare_p4_kernel<3><<<grid, 256, 0, st>>>(oa, ld, reference_points, shapes, rows, M, loc, attn);
+    else if (vec && L == 4) msda_prepare_p4_kernel<4><<<grid, 256, 0, st>>>(oa, ld, reference_points, shapes, rows, M, loc, attn);
+    else if (vec && L == 1) msda_prepare_p4_kernel<1><<<grid, 256, 0, st>>>(oa, ld, reference_points, shapes, rows, M, loc, attn);
+    else msda_prepare_kernel<<<grid, 256, 0, st>>>(oa, ld, reference_points, shapes, rows, M, L, P, loc, attn);
     return check_launch("msda_prepare_kernel");
 }

@@ -437,3 +437,11 @@ def test_msda_prepare_matches_module_arithmetic():
     assert torch.equal(loc, loc_ref)                                          # one division and one add per element: exact
     torch.testing.assert_close(aw, aw_ref, rtol=2e-6, atol=1e-8)
     torch.testing.assert_close(aw.sum((-1, -2)), torch.ones(N, Q, M, device=DEV), rtol=0, atol=1e-6)
+    # generic (scalar) route: P != 4
+    P2 = 3
+    oa2 = torch.randn(N, Q, M * L * P2 * 3, device=DEV, generator=g)
+    loc2, aw2 = ops.msda_prepare(oa2, ref_pts, shapes, M, L, P2)
+    off2 = oa2[..., : M * L * P2 * 2].reshape(N, Q, M, L, P2, 2)
+    assert torch.equal(loc2, ref_pts[:, :, None, :, None, :] + off2 / norm[None, None, None, :, None, :])
+    torch.testing.assert_close(aw2, torch.softmax(oa2[..., M * L * P2 * 2:].reshape(N, Q, M, L * P2), -1).view(N, Q, M, L, P2),
+                               rtol=2e-6, atol=1e-8)
