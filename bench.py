@@ -301,6 +301,7 @@ def run_ours(args):
     if world == 1 and not args.no_network:
         enc0 = ops.encode_initial_masks(sets[0]["masks"], hp.cfg.sigma)
         line["network"] = network_side_measurement(dev, enc0, n_inst_total / args.steps, ms / args.steps)
+        line["encoder"] = encoder_side_measurement(dev)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(budget_s=args.cpu_budget)
     print(json.dumps(line))
@@ -347,6 +348,40 @@ def network_side_measurement(dev, enc, inst_per_step, hot_ms):
                        "GroupNorm+ReLU / upsample+concat / fuse-concat / tcgen05 1x1 kernels, CUDA graph), outside `value` and outside the reference arm "
                        "(BASELINE.json times the CPU path without the network); fp32 = PyTorch defaults (cuDNN convolutions may use TF32)")
     except Exception as e:      # the aside must never cost the headline line
+        out["error"] = f"{type(e).__name__}: {e}"[:300]
+    return out
+
+
+# --------------------------------------------------------------------------------------------- encoder (disclosed aside)
+def encoder_side_measurement(dev):
+    """The caller of the sampling kernel: the 6-layer MSDeformAttn transformer encoder of the optional
+    pixel decoder on the same 32 frames (S = 6300, d_model 256, FFN 1024) — tcgen05 GEMMs, quber_msda_prepare,
+    quber_msda_forward, fused residual + LayerNorm — next to torch's fp32 layer-by-layer module."""
+    import torch
+    out = {}
+    try:
+        from quber_b200.pixel_decoder import MSDeformAttnTransformerEncoderOnly
+        torch.manual_seed(0)
+        enc = MSDeformAttnTransformerEncoderOnly(256, 8, N_LAYERS, 1024, 0.0, "relu", 3, 4).to(dev).eval()
+        shapes = [(15, 20), (30, 40), (60, 80)]
+        srcs = [torch.randn(B, 256, h, w, device=dev) for h, w in shapes]
+        pos = [torch.randn(B, 256, h, w, device=dev) * 0.1 for h, w in shapes]
+        with torch.no_grad():
+            for prec in ("fp32", "tf32", "bf16"):
+                enc.set_precision(prec)
+                for _ in range(2):
+                    enc(srcs, pos)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(3):
+                    enc(srcs, pos)
+                e1.record()
+                torch.cuda.synchronize()
+                out[f"ms_per_step_{prec}"] = e0.elapsed_time(e1) / 3
+        out["note"] = ("6 encoder layers for 32 frames; fp32 = torch nn.Linear / LayerNorm modules around quber_msda_forward, "
+                       "tf32 / bf16 = tcgen05 GEMMs + fused glue kernels; outside `value`")
+    except Exception as e:
         out["error"] = f"{type(e).__name__}: {e}"[:300]
     return out
 
