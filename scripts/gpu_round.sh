@@ -14,3 +14,6 @@ ls -la gpurun_out
 timeout 300 python scripts/bench_norm.py > gpurun_out/bench_norm_$TAG.txt 2>&1; tail -4 gpurun_out/bench_norm_$TAG.txt
 for mb in 4 5 6; do echo "LDS MINB=$mb f32: $(QUBER_MSDA_MINB=$mb timeout 300 python scripts/bench_msda.py 32 f32 2>&1 | head -1)"; done | tee gpurun_out/msda_minb_$TAG.log
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:'gn_|upsample_concat' -c 8 -o gpurun_out/full_norm_$TAG -f python scripts/bench_norm.py > gpurun_out/ncu_norm_$TAG.log 2>&1
+timeout 300 python scripts/bench_gemm.py > gpurun_out/bench_gemm_$TAG.txt 2>&1; cat gpurun_out/bench_gemm_$TAG.txt
+timeout 300 python scripts/bench_encoder.py 2>&1 | grep "encoder x6" | tee gpurun_out/bench_encoder_$TAG.txt
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'gemm_bias_act|add_layer_norm|msda_prepare' -c 6 -o gpurun_out/full_gemm_$TAG -f python scripts/bench_encoder.py > gpurun_out/ncu_gemm_$TAG.log 2>&1
