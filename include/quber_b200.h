@@ -271,13 +271,15 @@ int quber_maxpool3x3s2(const void *x, void *y, int N, int C, int H, int W, int d
  * quber_add_layer_norm — y = LayerNorm(a + b) * gamma + beta over rows [rows, C] float32 (b may be NULL): the
  *     `src = norm(src + src2)` pairs (msdeformattn.py:126-127, :119-120).  C a multiple of 128, <= 1024.
  *     y_bf16 (optional, dev [rows, C] bfloat16) receives a rounded copy, the A operand of the next bf16 GEMM.
+ *     q (optional, with pos dev [rows, C] float32): q = y + pos, the next layer's query (with_pos_embed,
+ *     msdeformattn.py:124), float32 or bfloat16 (q_bf16).
  * quber_msda_prepare — from the fused sampling_offsets | attention_weights GEMM output rows
  *     oa dev [rows, ld] float32 (first M*L*P*2 offsets, then M*L*P logits) and reference_points dev [rows, L, 2]:
  *     loc dev [rows, M, L, P, 2] = reference + offset / (W_l, H_l)  (ms_deform_attn.py:106-109) and
  *     attn dev [rows, M, L, P] = softmax over L*P (:104-105); shapes dev [L,2] int64 (H_l, W_l).
  * ------------------------------------------------------------------------------------------- */
 int quber_add_layer_norm(const float *a, const float *b, const float *gamma, const float *beta, size_t rows, int C,
-                         float eps, float *y, void *y_bf16, void *stream);
+                         float eps, float *y, void *y_bf16, const float *pos, void *q, int q_bf16, void *stream);
 int quber_msda_prepare(const float *oa, int ld, const float *reference_points, const int64_t *shapes, size_t rows, int M,
                        int L, int P, float *loc, float *attn, void *stream);
 

@@ -56,7 +56,7 @@ SYMBOLS = {
     "quber_filter_workspace_bytes": (c_sz, [c_i, c_i]),
     "quber_filter_instances": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_d, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "quber_maxpool3x3s2": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_vp]),
-    "quber_add_layer_norm": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_i, ctypes.c_float, c_vp, c_vp, c_vp]),
+    "quber_add_layer_norm": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_i, ctypes.c_float, c_vp, c_vp, c_vp, c_vp, c_i, c_vp]),
     "quber_msda_prepare": (c_i, [c_vp, c_i, c_vp, c_vp, c_sz, c_i, c_i, c_i, c_vp, c_vp, c_vp]),
     "quber_msda_forward": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
 }

@@ -196,6 +196,142 @@ msda_forward_kernel(const VT *__restrict__ value, const int64_t *__restrict__ sh
     if (qreal < Q) Lane<VT>::store(out + qm * D + lane * CPL, acc);
 }
 
+// P == 4 variant with ONE 16-byte record per tap.  Every 32-bit value a warp broadcasts costs one L1 data-pipe
+// wavefront (ncu: 5.95 shared wavefronts per tap step with the 6-value records above), so the record is cut to four
+// words: (offset | flags, A, B, f) with
+//   corner weights  w1 = A (1 - f), w2 = A f, w3 = B (1 - f), w4 = B f,
+//   A = hh a g, B = lh a g (0 for a row outside the map), f = lw when both columns are inside, else 0 with the surviving
+//   column's weight folded into g (both loads then read that one pixel), bit 31 = "x + 1 is a different pixel",
+//   bit 30 = "y + 1 is a different row" (the row pitch of the tap's level is read once per round of LPG taps).
+// The products are associated differently from the reference's hh * hw * v (cuh:85): rounding only.
+// VB = bytes per lane and corner: 16 (LDG.128) or 32 (LDG.256, sm_100: a group is D*sizeof(VT)/32 lanes, so one
+// broadcast serves twice as many (query, head) pairs per warp and the gather still moves whole 128-byte lines).
+template <int VB> __device__ __forceinline__ void ld_corner(const char *p, uint32_t *w);
+template <> __device__ __forceinline__ void ld_corner<16>(const char *p, uint32_t *w) {
+    const uint4 r = __ldg(reinterpret_cast<const uint4 *>(p));
+    w[0] = r.x; w[1] = r.y; w[2] = r.z; w[3] = r.w;
+}
+template <> __device__ __forceinline__ void ld_corner<32>(const char *p, uint32_t *w) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(p));
+}
+template <typename VT, int NW> __device__ __forceinline__ void fma_corner(float wgt, const uint32_t *w, float *acc) {
+    if constexpr (sizeof(VT) == 4) {
+#pragma unroll
+        for (int i = 0; i < NW; ++i) acc[i] = fmaf(wgt, __uint_as_float(w[i]), acc[i]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            acc[2 * i] = fmaf(wgt, __uint_as_float(w[i] << 16), acc[2 * i]);
+            acc[2 * i + 1] = fmaf(wgt, __uint_as_float(w[i] & 0xffff0000u), acc[2 * i + 1]);
+        }
+    }
+}
+
+template <int D, typename VT, int MINB, int VB>
+__global__ void __launch_bounds__(256, MINB)
+msda_forward_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
+                       const float *__restrict__ loc, const float *__restrict__ attn, int S, int M, int L, int Q,
+                       VT *__restrict__ out) {
+    constexpr int P = 4;
+    constexpr int NW = VB / 4;                          // 32-bit words per lane and corner
+    constexpr int CPL = VB / (int)sizeof(VT);
+    constexpr int LPG = D / CPL;
+    static_assert(LPG >= 1 && LPG <= 32 && (LPG % P == 0 || P % LPG == 0), "a round of LPG taps must stay level-aligned");
+    constexpr int NLR = LPG >= P ? LPG / P : 1;         // levels per round
+    constexpr int GPB = 256 / LPG;
+    constexpr int GPW = 32 / LPG;
+    __shared__ int s_h[MSDA_MAX_L], s_w[MSDA_MAX_L], s_start[MSDA_MAX_L];
+    __shared__ __align__(16) uint4 s_rec[8 * GPW * (LPG + 1)];
+    const int tid = threadIdx.x;
+    const int lane = tid % LPG, grp = tid / LPG;
+    const int m = blockIdx.y, b = blockIdx.z;
+    const int LP = L * P, MD = M * D;
+    if (tid < L) {
+        s_h[tid] = (int)__ldg(shapes + 2 * tid);
+        s_w[tid] = (int)__ldg(shapes + 2 * tid + 1);
+        s_start[tid] = (int)__ldg(starts + tid);
+    }
+    __syncthreads();
+    const int qreal = blockIdx.x * GPB + grp;
+    const int q = min(qreal, Q - 1);
+    const size_t qm = ((size_t)b * Q + q) * M + m;
+    const float *lp = loc + qm * LP * 2;
+    const float *ap = attn + qm * LP;
+    const char *vlane = reinterpret_cast<const char *>(value + (size_t)b * S * MD + m * D) + lane * VB;
+    asm volatile("" : "+l"(vlane));                     // opaque: (base + lane) stays one register pair
+    const uint32_t MDu = MD / CPL;                      // pixel pitch in VB-byte units
+    float acc[CPL];
+#pragma unroll
+    for (int c = 0; c < CPL; ++c) acc[c] = 0.f;
+    uint2 raw_xy = make_uint2(0u, 0u);
+    uint32_t raw_a = 0u;
+    if (lane < LP) { raw_xy = ld_stream_u2(lp + 2 * lane); raw_a = ld_stream_u1(ap + lane); }
+    uint4 *rec = s_rec + (tid >> 5) * (GPW * (LPG + 1)) + ((tid & 31) / LPG) * (LPG + 1);
+    for (int s0 = 0; s0 < LP; s0 += LPG) {
+        const int tap = s0 + lane;
+        uint32_t o1 = 0;
+        float A = 0.f, Bw = 0.f, f = 0.f;
+        if (tap < LP) {
+            const int l = tap / P;
+            const int h = s_h[l], w = s_w[l];
+            const float him = __uint_as_float(raw_xy.y) * h - 0.5f, wim = __uint_as_float(raw_xy.x) * w - 0.5f;   // cuh:290-291
+            if (him > -1.f && wim > -1.f && him < (float)h && wim < (float)w) {          // cuh:293
+                const float a = __uint_as_float(raw_a);
+                const int hl = (int)floorf(him), wl = (int)floorf(wim);
+                const float lh = him - hl, lw = wim - wl, hh = 1.f - lh, hw = 1.f - lw;
+                const bool y0 = hl >= 0, y1 = hl + 1 <= h - 1, x0 = wl >= 0, x1 = wl + 1 <= w - 1;
+                const int ry0 = max(hl, 0), cx0 = max(wl, 0);
+                const bool xb = x0 && x1, yb = y0 && y1;
+                const float ag = xb ? a : a * (x0 ? hw : lw);                            // one column left: its weight goes into g
+                f = xb ? lw : 0.f;
+                A = y0 ? hh * ag : 0.f;                                                  // 0 where the reference reads v = 0 (cuh:58-81)
+                Bw = y1 ? lh * ag : 0.f;
+                o1 = ((uint32_t)(s_start[l] + ry0 * w + cx0) * MDu) | (xb ? 0x80000000u : 0u) | (yb ? 0x40000000u : 0u);
+            }
+        }
+        if (tap + LPG < LP) { raw_xy = ld_stream_u2(lp + 2 * (tap + LPG)); raw_a = ld_stream_u1(ap + tap + LPG); }
+        const int nt = min(LPG, LP - s0);
+        uint32_t pitch[NLR];
+#pragma unroll
+        for (int r = 0; r < NLR; ++r) pitch[r] = (uint32_t)s_w[min(s0 / P + r, L - 1)] * MDu;
+        rec[lane] = make_uint4(o1, __float_as_uint(A), __float_as_uint(Bw), __float_as_uint(f));
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < LPG; ++j) {
+            if (j < nt) {
+                const uint4 ra = rec[j];
+                const uint32_t dx = (uint32_t)((int32_t)ra.x >> 31) & MDu;
+                const uint32_t dy = (uint32_t)((int32_t)(ra.x << 1) >> 31) & pitch[j / P];
+                uint32_t a1 = ra.x & 0x3fffffffu;
+                asm volatile("" : "+r"(a1));
+                const uint32_t a3 = a1 + dy;
+                const float bf = __uint_as_float(ra.w), bg = 1.f - bf;
+                const float b1 = __uint_as_float(ra.y) * bg, b2 = __uint_as_float(ra.y) * bf;
+                const float b3 = __uint_as_float(ra.z) * bg, b4 = __uint_as_float(ra.z) * bf;
+                uint32_t r1[NW], r2[NW], r3[NW], r4[NW];
+                ld_corner<VB>(vlane + (size_t)a1 * VB, r1);
+                ld_corner<VB>(vlane + (size_t)(a1 + dx) * VB, r2);
+                ld_corner<VB>(vlane + (size_t)a3 * VB, r3);
+                ld_corner<VB>(vlane + (size_t)(a3 + dx) * VB, r4);
+                fma_corner<VT, NW>(b1, r1, acc); fma_corner<VT, NW>(b2, r2, acc);
+                fma_corner<VT, NW>(b3, r3, acc); fma_corner<VT, NW>(b4, r4, acc);
+            }
+        }
+        __syncwarp();
+    }
+    if (qreal < Q) {
+        VT *o = out + qm * D + lane * CPL;
+        if constexpr (sizeof(VT) == 4) {
+#pragma unroll
+            for (int c = 0; c < CPL; c += 4) st_stream_f4(o + c, make_float4(acc[c], acc[c + 1], acc[c + 2], acc[c + 3]));
+        } else {
+#pragma unroll
+            for (int c = 0; c < CPL; c += 8) Lane<__nv_bfloat16>::store(o + c, acc + c);
+        }
+    }
+}
+
 // Any D (the reference's own mapping: one thread per output scalar), fp32 only.
 __global__ void __launch_bounds__(256)
 msda_forward_scalar_kernel(const float *__restrict__ value, const int64_t *__restrict__ shapes,
@@ -237,7 +373,7 @@ static int msda_minb() {
     static const int v = [] {
         const char *e = getenv("QUBER_MSDA_MINB");
         const int x = e ? atoi(e) : 0;
-        return (x >= 4 && x <= 6) ? x : 5;
+        return (x >= 3 && x <= 6) ? x : 0;               // 0: the variant's own default
     }();
     return v;
 }
@@ -251,6 +387,29 @@ static int launch_vec(const void *value, const int64_t *shapes, const int64_t *s
     VT *o = static_cast<VT *>(out);
     // QUBER_MSDA_BCAST=shfl selects the shuffle broadcast (kept for A/B measurements); default: shared memory.
     static const bool shfl = [] { const char *e = getenv("QUBER_MSDA_BCAST"); return e && e[0] == 's'; }();
+    // QUBER_MSDA_BCAST=rec4 | wide: the one-record variants (P == 4), 128-bit or 256-bit corner loads.
+    static const int rec = [] { const char *e = getenv("QUBER_MSDA_BCAST"); return !e ? 0 : e[0] == 'r' ? 16 : e[0] == 'w' ? 32 : 0; }();
+    constexpr int DB = D * (int)sizeof(VT);             // bytes of one head's channels
+    if constexpr (DB % 64 == 0) {                       // >= 4 lanes of 16 bytes, >= 2 lanes of 32 bytes
+        if (rec && P == 4) {
+            constexpr int G16 = 256 / (DB / 16), G32 = 256 / (DB / 32);
+            const dim3 g16(cdiv(Q, G16), M, B), g32(cdiv(Q, G32), M, B);
+            if (rec == 16) {
+                switch (msda_minb()) {
+                    default: msda_forward_p4_kernel<D, VT, 5, 16><<<g16, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
+                    case 6: msda_forward_p4_kernel<D, VT, 6, 16><<<g16, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
+                    case 4: msda_forward_p4_kernel<D, VT, 4, 16><<<g16, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
+                }
+            } else {
+                switch (msda_minb()) {
+                    default: msda_forward_p4_kernel<D, VT, 4, 32><<<g32, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
+                    case 5: msda_forward_p4_kernel<D, VT, 5, 32><<<g32, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
+                    case 3: msda_forward_p4_kernel<D, VT, 3, 32><<<g32, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
+                }
+            }
+            return check_launch("msda_forward_p4_kernel");
+        }
+    }
     if (!shfl) {
         switch (msda_minb()) {
             default: msda_forward_kernel<D, VT, 5, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;

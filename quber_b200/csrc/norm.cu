@@ -364,7 +364,8 @@ maxpool3x3s2_nhwc_kernel(const T *__restrict__ x, T *__restrict__ y, size_t tota
 template <int VPL>                                      // float4 vectors per lane: C = 128 * VPL
 __global__ void __launch_bounds__(256)
 add_layer_norm_kernel(const float *__restrict__ a, const float *__restrict__ b, const float *__restrict__ gamma,
-                      const float *__restrict__ beta, size_t rows, float eps, float *__restrict__ y, __nv_bfloat16 *__restrict__ y16) {
+                      const float *__restrict__ beta, size_t rows, float eps, float *__restrict__ y, __nv_bfloat16 *__restrict__ y16,
+                      const float *__restrict__ pos, void *__restrict__ qout, int q_bf16) {
     constexpr int C = 128 * VPL;
     const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -402,6 +403,17 @@ add_layer_norm_kernel(const float *__restrict__ a, const float *__restrict__ b, 
         if (y16) {
             const __nv_bfloat162 lo = __floats2bfloat162_rn(r.x, r.y), hi = __floats2bfloat162_rn(r.z, r.w);
             *reinterpret_cast<uint2 *>(y16 + row * C + c) = make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
+        }
+        if (qout) {                                      // the next layer's query: with_pos_embed(y, pos), msdeformattn.py:124
+            const float4 p = *reinterpret_cast<const float4 *>(pos + row * C + c);
+            const float4 t = make_float4(r.x + p.x, r.y + p.y, r.z + p.z, r.w + p.w);
+            if (q_bf16) {
+                const __nv_bfloat162 lo = __floats2bfloat162_rn(t.x, t.y), hi = __floats2bfloat162_rn(t.z, t.w);
+                *reinterpret_cast<uint2 *>(static_cast<__nv_bfloat16 *>(qout) + row * C + c) =
+                    make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
+            } else {
+                *reinterpret_cast<float4 *>(static_cast<float *>(qout) + row * C + c) = t;
+            }
         }
     }
 }
@@ -545,10 +557,11 @@ extern "C" int quber_maxpool3x3s2(const void *x, void *y, int N, int C, int H, i
 }
 
 extern "C" int quber_add_layer_norm(const float *a, const float *b, const float *gamma, const float *beta, size_t rows, int C,
-                                    float eps, float *y, void *y_bf16, void *stream) {
+                                    float eps, float *y, void *y_bf16, const float *pos, void *q, int q_bf16, void *stream) {
     using namespace quber;
-    if (!a || !gamma || !beta || !y || rows == 0 || C <= 0) return QUBER_E_INVALID;
+    if (!a || !gamma || !beta || !y || rows == 0 || C <= 0 || (q && !pos)) return QUBER_E_INVALID;
     if (C % 128 != 0 || C > 1024) return QUBER_E_UNSUPPORTED;
+    if ((pos && !aligned16(pos)) || (q && !aligned16(q))) return QUBER_E_ALIGN;
     if (!aligned16(a) || (b && !aligned16(b)) || !aligned16(gamma) || !aligned16(beta) || !aligned16(y) || (y_bf16 && !aligned16(y_bf16)))
         return QUBER_E_ALIGN;
     if ((rows + 7) / 8 > 0x7fffffffull) return QUBER_E_UNSUPPORTED;
@@ -556,12 +569,12 @@ extern "C" int quber_add_layer_norm(const float *a, const float *b, const float 
     cudaStream_t st = (cudaStream_t)stream;
     __nv_bfloat16 *y16 = static_cast<__nv_bfloat16 *>(y_bf16);
     switch (C / 128) {
-        case 1: add_layer_norm_kernel<1><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16); break;
-        case 2: add_layer_norm_kernel<2><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16); break;
-        case 3: add_layer_norm_kernel<3><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16); break;
-        case 4: add_layer_norm_kernel<4><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16); break;
-        case 6: add_layer_norm_kernel<6><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16); break;
-        case 8: add_layer_norm_kernel<8><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16); break;
+        case 1: add_layer_norm_kernel<1><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16, pos, q, q_bf16); break;
+        case 2: add_layer_norm_kernel<2><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16, pos, q, q_bf16); break;
+        case 3: add_layer_norm_kernel<3><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16, pos, q, q_bf16); break;
+        case 4: add_layer_norm_kernel<4><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16, pos, q, q_bf16); break;
+        case 6: add_layer_norm_kernel<6><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16, pos, q, q_bf16); break;
+        case 8: add_layer_norm_kernel<8><<<grid, 256, 0, st>>>(a, b, gamma, beta, rows, eps, y, y16, pos, q, q_bf16); break;
         default: return QUBER_E_UNSUPPORTED;
     }
     return check_launch("add_layer_norm_kernel");

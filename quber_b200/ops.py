@@ -309,9 +309,10 @@ def maxpool3x3s2(x):
     return y
 
 
-def add_layer_norm(a, b, weight, bias, eps=1e-5, want_bf16=False):
+def add_layer_norm(a, b, weight, bias, eps=1e-5, want_bf16=False, pos=None, q_dtype=None):
     """LayerNorm(a + b) over the last dimension (msdeformattn.py:119-120, :126-127) in one pass.  a, b [..., C] float32
-    CUDA (b may be None), C a multiple of 128 (<= 1024) -> y float32 [, y_bf16]."""
+    CUDA (b may be None), C a multiple of 128 (<= 1024) -> y float32 [, y_bf16] [, q = y + pos in `q_dtype`, the next
+    layer's query (with_pos_embed, msdeformattn.py:124)]."""
     _need_cuda(a, "a", torch.float32)
     if b is not None:
         _need_cuda(b, "b", torch.float32)
@@ -323,12 +324,20 @@ def add_layer_norm(a, b, weight, bias, eps=1e-5, want_bf16=False):
     rows = a.numel() // C
     y = torch.empty_like(a)
     y16 = torch.empty(a.shape, dtype=torch.bfloat16, device=a.device) if want_bf16 else None
+    q = None
+    if pos is not None:
+        _need_cuda(pos, "pos", torch.float32)
+        if pos.shape != a.shape or q_dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("pos must have a's shape and q_dtype must be float32 or bfloat16")
+        q = torch.empty(a.shape, dtype=q_dtype, device=a.device)
     g = weight.detach().float().contiguous()
     bt = bias.detach().float().contiguous()
     with torch.cuda.device(a.device):
         _lib.check(_lib.lib().quber_add_layer_norm(_ptr(a), _ptr(b), _ptr(g), _ptr(bt), rows, C, float(eps), _ptr(y), _ptr(y16),
-                                                   _stream()), "quber_add_layer_norm")
-    return (y, y16) if want_bf16 else y
+                                                   _ptr(pos), _ptr(q), int(q_dtype == torch.bfloat16), _stream()),
+                   "quber_add_layer_norm")
+    out = (y,) + ((y16,) if want_bf16 else ()) + ((q,) if pos is not None else ())
+    return out if len(out) > 1 else y
 
 
 def msda_prepare(oa, reference_points, spatial_shapes, n_heads, n_levels, n_points):

@@ -115,15 +115,21 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
                                         l2=(f(self.linear2.weight), g(self.linear2.bias))))
         return self._packed[1]
 
-    def _forward_kernels(self, src, pos, reference_points, spatial_shapes, level_start_index, padding_mask):
+    def _forward_kernels(self, src, pos, reference_points, spatial_shapes, level_start_index, padding_mask, pre=None,
+                         emit_next=False):
+        """`pre` = (x, q) already in the GEMM dtype, written by the previous layer's last LayerNorm pass; `emit_next`
+        asks this layer's last LayerNorm for the same pair (returned as the second value)."""
         a = self.self_attn
         bf16 = self.precision == "bf16"
         dt = torch.bfloat16 if bf16 else torch.float32
         W = self._weights(dt)
         N, S, C = src.shape
         M, L, P = a.n_heads, a.n_levels, a.n_points
-        q = self.with_pos_embed(src, pos).to(dt)
-        x = src.to(dt)
+        if pre is not None:
+            x, q = pre
+        else:
+            q = self.with_pos_embed(src, pos).to(dt)
+            x = src.to(dt)
         value = ops.gemm_bias_act(x, *W["v"], out_dtype=dt)                                   # ms_deform_attn.py:98
         if padding_mask is not None:
             value = value.masked_fill(padding_mask[..., None], float(0))
@@ -152,12 +158,22 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
         else:
             src, src16 = self.norm1(src + src2), None
         if self.activation_name != "relu":
-            return self.forward_ffn(src)
+            out = self.forward_ffn(src)
+            return (out, None) if emit_next else out
         hmid = ops.gemm_bias_act(src16 if src16 is not None else src.to(dt), *W["l1"], act="relu", out_dtype=dt)   # msdeformattn.py:116-120
         src2 = ops.gemm_bias_act(hmid, *W["l2"], out_dtype=torch.float32)
-        if fused_ln:
-            return ops.add_layer_norm(src, src2.view(N, S, C), self.norm2.weight, self.norm2.bias, self.norm2.eps)
-        return self.norm2(src + src2)
+        if not emit_next:
+            if fused_ln:
+                return ops.add_layer_norm(src, src2.view(N, S, C), self.norm2.weight, self.norm2.bias, self.norm2.eps)
+            return self.norm2(src + src2)
+        if fused_ln and pos is not None and pos.dtype == torch.float32 and pos.shape == src.shape:
+            # norm2 also writes the next layer's operands: x (bf16 copy; the fp32 result itself in tf32) and q = x + pos
+            r = ops.add_layer_norm(src, src2.view(N, S, C), self.norm2.weight, self.norm2.bias, self.norm2.eps, want_bf16=bf16,
+                                   pos=pos.contiguous(), q_dtype=dt)
+            return r[0], ((r[1], r[2]) if bf16 else (r[0], r[1]))
+        out = ops.add_layer_norm(src, src2.view(N, S, C), self.norm2.weight, self.norm2.bias, self.norm2.eps) if fused_ln \
+            else self.norm2(src + src2)
+        return out, None
 
     def forward(self, src, pos, reference_points, spatial_shapes, level_start_index, padding_mask=None):
         if self.precision != "fp32" and src.is_cuda:
@@ -192,8 +208,15 @@ class MSDeformAttnTransformerEncoder(nn.Module):
         output = src
         shapes = host_shapes if host_shapes is not None else spatial_shapes.tolist()
         reference_points = self.get_reference_points(shapes, valid_ratios, device=src.device)
-        for layer in self.layers:
-            output = layer(output, pos, reference_points, spatial_shapes, level_start_index, padding_mask)
+        pre = None
+        for i, layer in enumerate(self.layers):
+            if layer.precision != "fp32" and output.is_cuda:
+                nxt = i + 1 < len(self.layers) and self.layers[i + 1].precision == layer.precision
+                r = layer._forward_kernels(output, pos, reference_points, spatial_shapes, level_start_index, padding_mask,
+                                           pre=pre, emit_next=nxt)
+                output, pre = r if nxt else (r, None)
+            else:
+                output, pre = layer(output, pos, reference_points, spatial_shapes, level_start_index, padding_mask), None
         return output
 
 

@@ -422,6 +422,54 @@ def test_add_layer_norm_matches_float64_reference(C):
         ops.add_layer_norm(a[..., :100].contiguous(), None, ln.weight[:100], ln.bias[:100])
 
 
+@pytest.mark.parametrize("qd", [torch.float32, torch.bfloat16])
+def test_add_layer_norm_emits_next_query(qd):
+    """q = LayerNorm(a + b) + pos (with_pos_embed of the next layer, msdeformattn.py:124) from the same pass: the fp32 sum
+    is the one torch makes, the bf16 variant its rounding."""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    a, b = torch.randn(2, 333, 256, device=DEV, generator=g), torch.randn(2, 333, 256, device=DEV, generator=g)
+    pos = torch.randn(2, 333, 256, device=DEV, generator=g) * 0.5
+    ln = torch.nn.LayerNorm(256).to(DEV)
+    y0 = ops.add_layer_norm(a, b, ln.weight, ln.bias, ln.eps)
+    y, y16, q = ops.add_layer_norm(a, b, ln.weight, ln.bias, ln.eps, want_bf16=True, pos=pos, q_dtype=qd)
+    assert torch.equal(y, y0) and torch.equal(y16, y.bfloat16())
+    assert q.dtype == qd and torch.equal(q, (y + pos).to(qd))
+    y2, q2 = ops.add_layer_norm(a, b, ln.weight, ln.bias, ln.eps, pos=pos, q_dtype=qd)
+    assert torch.equal(y2, y0) and torch.equal(q2, q)
+    with pytest.raises(ValueError):
+        ops.add_layer_norm(a, b, ln.weight, ln.bias, ln.eps, pos=pos[:, :10].contiguous(), q_dtype=qd)
+
+
+@pytest.mark.parametrize("prec", ["tf32", "bf16"])
+def test_encoder_chained_operands_equal_layer_by_layer(prec):
+    """The encoder hands each layer the (x, q) pair its predecessor's last LayerNorm wrote; the result is bit-identical to
+    calling the layers one by one (each making its own casts)."""
+    from quber_b200.pixel_decoder import MSDeformAttnTransformerEncoder, MSDeformAttnTransformerEncoderLayer
+    torch.manual_seed(3)
+    layer = MSDeformAttnTransformerEncoderLayer(256, 1024, 0.0, "relu", 3, 8, 4).eval()
+    enc = MSDeformAttnTransformerEncoder(layer, 3).eval()
+    with torch.no_grad():
+        for l in enc.layers:
+            l.self_attn.sampling_offsets.weight.normal_(0, 0.02)
+            l.self_attn.attention_weights.weight.normal_(0, 0.05)
+            l.precision = prec
+    enc = enc.to(DEV)
+    hs = [(15, 20), (8, 10), (4, 5)]
+    S = sum(h * w for h, w in hs)
+    shapes = torch.tensor(hs, dtype=torch.long, device=DEV)
+    starts = torch.cat((shapes.new_zeros((1,)), shapes.prod(1).cumsum(0)[:-1]))
+    g = torch.Generator(device=DEV).manual_seed(4)
+    src, pos = torch.randn(2, S, 256, device=DEV, generator=g), torch.randn(2, S, 256, device=DEV, generator=g) * 0.5
+    ones = torch.ones(2, 3, 2, device=DEV)
+    with torch.no_grad():
+        got = enc(src, shapes, starts, ones, pos, None, host_shapes=hs)
+        ref_pts = enc.get_reference_points(hs, ones, DEV)
+        out = src
+        for l in enc.layers:
+            out = l(out, pos, ref_pts, shapes, starts, None)
+    assert torch.equal(got, out)
+
+
 def test_msda_prepare_matches_module_arithmetic():
     """OPS/modules/ms_deform_attn.py:102-109 restated with torch on the same GEMM output."""
     g = torch.Generator(device=DEV).manual_seed(8)
