@@ -253,8 +253,26 @@ def run_ours(args):
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         e2e_ms, e2e_inst = float(tmax[0]), float(tsum[1])
-    h2d = sets[0]["h_masks"].numel() + sum(v.numel() * 4 for v in sets[0]["h_head"].values())
+    packed = bool(hp.pack_masks)                              # decided on the first call (HotPath._calibrate_pack)
+    h2d = sets[0]["h_masks"].numel() // (8 if packed else 1) + sum(v.numel() * 4 for v in sets[0]["h_head"].values())
     d2h = sum(v.numel() * v.element_size() for v in o.values())
+    # what this box's host link gives a plain pinned copy of the same mask bytes (the floor under e2e; it differs between
+    # boxes of the pool by NUMA placement of the pinned pages)
+    pcie = {}
+    if rank == 0:
+        hm = sets[0]["h_masks"]
+        dm = torch.empty(hm.shape, dtype=hm.dtype, device=dev)
+        back = torch.empty(hm.shape, dtype=hm.dtype).pin_memory()
+        for name, fn in (("h2d_gbs", lambda: dm.copy_(hm, non_blocking=True)), ("d2h_gbs", lambda: back.copy_(dm, non_blocking=True))):
+            fn(); torch.cuda.synchronize()
+            c0 = _ev()
+            for _ in range(3):
+                fn()
+            c1 = _ev()
+            torch.cuda.synchronize()
+            pcie[name] = 3 * hm.numel() / (c0.elapsed_time(c1) * 1e-3) / 1e9
+        pcie["h2d_floor_ms_per_step"] = h2d / (pcie["h2d_gbs"] * 1e9) * 1e3
+        del dm, back
 
     if rank != 0:
         if world > 1:
@@ -272,12 +290,12 @@ def run_ours(args):
     roof_all = {
         "encode(reduce+emit)": {"ms": per_stage["encode"], "bytes": ab["encode"]},
         "boundary_kernel": {"ms": per_stage["boundary"], "bytes": ab["boundary"]},
-        "msda_forward_kernel": {"ms": per_stage["msda"] / N_LAYERS, "bytes": ab["msda_layer"]},
+        "msda_forward_p4_kernel": {"ms": per_stage["msda"] / N_LAYERS, "bytes": ab["msda_layer"]},
     }
     for v in roof_all.values():
         v["achieved_gbs"] = v["bytes"] / (v["ms"] * 1e-3) / 1e9
         v["frac"] = v["achieved_gbs"] / peak_gbs
-    dominant = max(("boundary_kernel", "msda_forward_kernel", "encode(reduce+emit)"),
+    dominant = max(("boundary_kernel", "msda_forward_p4_kernel", "encode(reduce+emit)"),
                    key=lambda k: roof_all[k]["ms"] * (N_LAYERS if k.startswith("msda") else 1))
     dv = roof_all[dominant]
     launches = (2 + 1 + N_LAYERS + 7) * args.steps
@@ -286,7 +304,10 @@ def run_ours(args):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(world), "clocks": clocks,
         "e2e": {"value": e2e_inst / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
+                "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps, "host_link": pcie,
+                "mask_transfer": ("one bit per pixel, packed on %d host threads inside the timed region" % hp.pack_threads) if packed
+                                 else "bytes",
+                "pack_calibration": getattr(hp, "pack_calibration", None)},
         "gpu_launches": launches,
         "instances_per_step": n_inst_total / args.steps, "post_status": status,
         "stage_ms": per_stage,

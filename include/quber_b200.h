@@ -283,6 +283,20 @@ int quber_add_layer_norm(const float *a, const float *b, const float *gamma, con
 int quber_msda_prepare(const float *oa, int ld, const float *reference_points, const int64_t *shapes, size_t rows, int M,
                        int L, int P, float *loc, float *attn, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Packed mask transfer for the host-buffer (end-to-end) path.  The reference moves the [K,H,W] uint8 initial masks
+ * to the GPU byte for byte (maskrefiner/predictor.py:304-310, `torch.as_tensor(...).to(device)` in eval/refiner_model.py);
+ * here the host packs them to one bit per pixel and the device expands them again.
+ * quber_host_pack_masks — HOST function (no CUDA call): bit i of dst[w] = (src[32 w + i] != 0), n_bytes a multiple of 32,
+ *     on up to n_threads persistent worker threads (AVX2 when the CPU has it).  *value = the one value every set pixel
+ *     carries (1, or 255 as eval/refiner_model.py:230-231 makes the masks), 0 for an all-zero buffer, -1 when the buffer
+ *     holds more than one non-zero value (dst is still written; the caller should send the bytes instead, since the
+ *     per-instance boundary keeps the mask's own values, explicit_error_estimation/util.py:72-90).
+ * quber_unpack_masks — packed dev [n_words] uint32 -> out dev [32 n_words] uint8 (0 / value), out 16-byte aligned.
+ * ------------------------------------------------------------------------------------------- */
+int quber_host_pack_masks(const uint8_t *src, size_t n_bytes, uint32_t *dst, int n_threads, int *value);
+int quber_unpack_masks(const uint32_t *packed, size_t n_words, int value, uint8_t *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,6 +57,8 @@ SYMBOLS = {
     "quber_filter_instances": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_d, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "quber_maxpool3x3s2": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_vp]),
     "quber_add_layer_norm": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_i, ctypes.c_float, c_vp, c_vp, c_vp, c_vp, c_i, c_vp]),
+    "quber_host_pack_masks": (c_i, [c_vp, c_sz, c_vp, c_i, c_vp]),
+    "quber_unpack_masks": (c_i, [c_vp, c_sz, c_i, c_vp, c_vp]),
     "quber_msda_prepare": (c_i, [c_vp, c_i, c_vp, c_vp, c_sz, c_i, c_i, c_i, c_vp, c_vp, c_vp]),
     "quber_msda_forward": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
 }

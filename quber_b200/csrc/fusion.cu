@@ -174,6 +174,34 @@ fuse_concat_rows_kernel(FuseRowsArgs a, int ctot, int pitch, size_t rows, void *
 
 }  // namespace quber
 
+namespace quber {
+// Expansion of bit-packed masks (quber_host_pack_masks, hostpack.cpp): bit i of word w -> byte 32 w + i = `value`.
+// One word per thread, two 128-bit streaming stores.
+__global__ void __launch_bounds__(256)
+unpack_masks_kernel(const uint32_t *__restrict__ packed, size_t n_words, uint32_t value, uint8_t *__restrict__ out) {
+    const size_t w = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (w >= n_words) return;
+    const uint32_t bits = __ldg(packed + w);
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const uint32_t nib = (bits >> (4 * j)) & 0xfu;
+        // spread the four bits of a nibble to the low bit of four bytes: multiply puts bit k at 7k + k, mask keeps bit 8k
+        o[j] = ((nib * 0x00204081u) & 0x01010101u) * value;
+    }
+    st_stream_u4(out + 32 * w, make_uint4(o[0], o[1], o[2], o[3]));
+    st_stream_u4(out + 32 * w + 16, make_uint4(o[4], o[5], o[6], o[7]));
+}
+}  // namespace quber
+
+extern "C" int quber_unpack_masks(const uint32_t *packed, size_t n_words, int value, uint8_t *out, void *stream) {
+    using namespace quber;
+    if (!packed || !out || n_words == 0 || value < 0 || value > 255) return QUBER_E_INVALID;
+    if (!aligned16(out) || (reinterpret_cast<uintptr_t>(packed) & 3u)) return QUBER_E_ALIGN;
+    unpack_masks_kernel<<<(unsigned)cdiv(n_words, (size_t)256), 256, 0, (cudaStream_t)stream>>>(packed, n_words, (uint32_t)value, out);
+    return check_launch("unpack_masks_kernel");
+}
+
 extern "C" int quber_pack_input(const uint8_t *image, const float *offsets, const float *mean, const float *stdv, int B, int C,
                                 int CO, int H, int W, float *out, void *stream) {
     using namespace quber;

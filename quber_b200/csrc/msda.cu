@@ -385,16 +385,18 @@ static int launch_vec(const void *value, const int64_t *shapes, const int64_t *s
     dim3 grid(cdiv(Q, GPB), M, B);
     const VT *v = static_cast<const VT *>(value);
     VT *o = static_cast<VT *>(out);
-    // QUBER_MSDA_BCAST=shfl selects the shuffle broadcast (kept for A/B measurements); default: shared memory.
-    static const bool shfl = [] { const char *e = getenv("QUBER_MSDA_BCAST"); return e && e[0] == 's'; }();
-    // QUBER_MSDA_BCAST=rec4 | wide: the one-record variants (P == 4), 128-bit or 256-bit corner loads.
-    static const int rec = [] { const char *e = getenv("QUBER_MSDA_BCAST"); return !e ? 0 : e[0] == 'r' ? 16 : e[0] == 'w' ? 32 : 0; }();
+    // Default: the one-record kernel when P == 4 (fp32 486 us, bf16 354 us per launch at C2), else the two-record
+    // shared-memory broadcast (497 / 366).  QUBER_MSDA_BCAST = lds | shfl | rec4 | wide forces a variant for A/B runs
+    // (wide = 256-bit corner loads, half as many lanes per group: 500 / 433 us — more bytes per lane in flight did not
+    // help, nor did letting the compiler overlap the taps of a level at 4 or 3 CTAs/SM: 505 / 541 us).
+    static const char mode = [] { const char *e = getenv("QUBER_MSDA_BCAST"); return e ? e[0] : '\0'; }();
+    const bool shfl = mode == 's';
     constexpr int DB = D * (int)sizeof(VT);             // bytes of one head's channels
     if constexpr (DB % 64 == 0) {                       // >= 4 lanes of 16 bytes, >= 2 lanes of 32 bytes
-        if (rec && P == 4) {
+        if (P == 4 && mode != 'l' && mode != 's') {
             constexpr int G16 = 256 / (DB / 16), G32 = 256 / (DB / 32);
             const dim3 g16(cdiv(Q, G16), M, B), g32(cdiv(Q, G32), M, B);
-            if (rec == 16) {
+            if (mode != 'w') {
                 switch (msda_minb()) {
                     default: msda_forward_p4_kernel<D, VT, 5, 16><<<g16, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
                     case 6: msda_forward_p4_kernel<D, VT, 6, 16><<<g16, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;

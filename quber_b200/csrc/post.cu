@@ -83,6 +83,28 @@ center_nms_kernel(const float *__restrict__ center, int H, int W, int scale, flo
     const int b = blockIdx.z, ty0 = blockIdx.y * N_TH, tx0 = blockIdx.x * N_TW;
     const float *plane = center + (size_t)b * up.h * up.w;
     const int tid = threadIdx.x;
+    if (threshold > 0.f && scale > 1) {
+        // A bilinear sample is a convex combination of its four low-resolution neighbours (up to rounding), so a tile
+        // whose low-resolution footprint (a superset: one cell beyond on every side) stays below the threshold by a
+        // relative 1e-4 has no candidate: every thresholded value is -1.  Typical frames: more than half of the tiles.
+        const int ly0 = max(0, (ty0 - p) / scale - 1), ly1 = min(up.h - 1, (ty0 + N_TH - 1 + p) / scale + 1);
+        const int lx0 = max(0, (tx0 - p) / scale - 1), lx1 = min(up.w - 1, (tx0 + N_TW - 1 + p) / scale + 1);
+        const int fw = lx1 - lx0 + 1, fn = max(0, (ly1 - ly0 + 1) * fw);
+        const float cut = threshold * 0.9999f;
+        int any = 0;
+        for (int idx = tid; idx < fn; idx += P_THREADS) {
+            const int r = idx / fw, c = idx - r * fw;
+            any |= !(__ldg(plane + (size_t)(ly0 + r) * up.w + lx0 + c) <= cut);   // NaN counts as "may be a candidate"
+        }
+        if (!__syncthreads_or(any)) {
+            const int WB0 = (W + 31) / 32;
+            if (tid < N_TH * 2) {
+                const int gy = ty0 + (tid >> 1), wx = (tx0 >> 5) + (tid & 1);
+                if (gy < H && wx < WB0) bitmask[((size_t)b * H + gy) * WB0 + wx] = 0u;
+            }
+            return;
+        }
+    }
     for (int idx = tid; idx < THp * TWp; idx += P_THREADS) {
         const int r = idx / TWp, c = idx - r * TWp;
         const int gy = ty0 - p + r, gx = tx0 - p + c;
@@ -519,11 +541,14 @@ emit_kernel(quber_post_params p, quber_post_io io, const uint16_t *__restrict__ 
     const UpSampler up(H, W, p.scale);
     const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
     const int y = blockIdx.y * P_TH + (tid >> 4), x0 = blockIdx.x * P_TW + (tid & 15) * 8;
-    if (y < H && x0 < W) {
-        const size_t pix = (size_t)y * W + x0;
+    const bool inb = y < H && x0 < W;                       // every lane stays alive: the statistics use warp collectives
+    int idx[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) idx[j] = -1;
+    const size_t pix = (size_t)y * W + x0;
+    if (inb) {
         const uint4 raw = *reinterpret_cast<const uint4 *>(ins + (size_t)b * HW + pix);
         const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
-        int idx[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const unsigned v = (rw[j >> 1] >> (16 * (j & 1))) & 0xffffu;
@@ -548,45 +573,102 @@ emit_kernel(quber_post_params p, quber_post_io io, const uint16_t *__restrict__ 
         }
         if (io.masks) {
             const int off = io.inst_offsets[b];
-            for (int i = 0; i < ninst; ++i) {
-                if (off + i >= p.max_instances) break;
-                uint32_t lo = 0, hi = 0;
+            const int ne = min(ninst, p.max_instances - off);
+            uint8_t *mo = io.masks + (size_t)off * HW + pix;
+            if (ninst <= 254) {
+                // ids as bytes (0 = none), one SIMD byte compare per plane and 4 pixels instead of 4 compares + shifts
+                uint32_t plo = 0, phi = 0;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    lo |= (uint32_t)(idx[j] == i) << (8 * j);
-                    hi |= (uint32_t)(idx[4 + j] == i) << (8 * j);
+                    plo |= (uint32_t)(idx[j] + 1) << (8 * j);
+                    phi |= (uint32_t)(idx[4 + j] + 1) << (8 * j);
                 }
-                st_stream_u2(io.masks + (size_t)(off + i) * HW + pix, make_uint2(lo, hi));
-            }
-        }
-        // statistics, run-length compressed per thread
-        const float *fgp = io.foreground + (size_t)b * hw;
-        int cur = -1;
-        unsigned cnt = 0, sx = 0, mnx = 0, mxx = 0;
-        unsigned long long sig = 0;
-        auto flush = [&]() {
-            if (cur < 0 || cnt == 0) return;
-            InstStat *s = sst + cur;
-            atomicAdd(&s->sig, sig);
-            atomicAdd(&s->sy, (unsigned long long)cnt * (unsigned)y);
-            atomicAdd(&s->sx, (unsigned long long)sx);
-            atomicAdd(&s->cnt, cnt);
-            atomicMax(&s->maxx, mxx);
-            atomicMax(&s->maxnx, (unsigned)(W - 1) - mnx);
-            atomicMax(&s->maxy, (unsigned)y);
-            atomicMax(&s->maxny, (unsigned)(H - 1 - y));
-        };
+                for (int i = 0; i < ne; ++i, mo += HW) {
+                    const uint32_t key = (uint32_t)(i + 1) * 0x01010101u;
+                    st_stream_u2(mo, make_uint2(__vcmpeq4(plo, key) & 0x01010101u, __vcmpeq4(phi, key) & 0x01010101u));
+                }
+            } else {
+                for (int i = 0; i < ne; ++i, mo += HW) {
+                    uint32_t lo = 0, hi = 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            if (idx[j] != cur) { flush(); cur = idx[j]; cnt = 0; sx = 0; sig = 0; mnx = x0 + j; }
-            if (cur >= 0) {
-                const float x = up.at(fgp, y, x0 + j);
-                const float sg = __fdividef(1.0f, 1.0f + __expf(-x));       // model.py:319 sigmoid
-                sig += __float2ull_rn(sg * 4294967296.0f);
-                ++cnt; sx += x0 + j; mxx = x0 + j;
+                    for (int j = 0; j < 4; ++j) {
+                        lo |= (uint32_t)(idx[j] == i) << (8 * j);
+                        hi |= (uint32_t)(idx[4 + j] == i) << (8 * j);
+                    }
+                    st_stream_u2(mo, make_uint2(lo, hi));
+                }
             }
         }
-        flush();
+    }
+    // Statistics.  A thread whose eight pixels belong to one instance (all but the threads on an instance border) joins
+    // the other such lanes of its warp: match.any groups the lanes by instance and redux.sync adds / maximises inside
+    // the group, so that one lane issues the eight shared-memory atomics instead of up to 32 lanes colliding on the same
+    // slot.  All sums are integers (the sigmoid in 32.32 fixed point), so the result does not depend on the grouping.
+    {
+        const float *fgp = io.foreground + (size_t)b * hw;
+        bool uni = true, anyfg = false;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { uni &= idx[j] == idx[0]; anyfg |= idx[j] >= 0; }
+        unsigned long long q[8];
+        if (anyfg) {
+            float fgv[8];
+            if (p.scale == 4) { const Row8 row(up, y, x0); row.sample(fgp, fgv); }
+            else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) fgv[j] = up.at(fgp, y, x0 + j);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float sg = __fdividef(1.0f, 1.0f + __expf(-fgv[j]));     // model.py:319 sigmoid
+                q[j] = __float2ull_rn(sg * 4294967296.0f);
+            }
+        }
+        const bool fast = uni && idx[0] >= 0;
+        const unsigned act = __ballot_sync(0xffffffffu, fast);
+        if (fast) {
+            unsigned long long sig = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sig += q[j];
+            const unsigned grp = __match_any_sync(act, idx[0]);
+            const unsigned shi = __reduce_add_sync(grp, (unsigned)(sig >> 16)), slo = __reduce_add_sync(grp, (unsigned)(sig & 0xffffu));
+            const unsigned cn = __reduce_add_sync(grp, 8u), sys = __reduce_add_sync(grp, 8u * (unsigned)y);
+            const unsigned sxs = __reduce_add_sync(grp, 8u * (unsigned)x0 + 28u);
+            const unsigned mx = __reduce_max_sync(grp, (unsigned)(x0 + 7)), mnx = __reduce_max_sync(grp, (unsigned)(W - 1 - x0));
+            const unsigned my = __reduce_max_sync(grp, (unsigned)y), mny = __reduce_max_sync(grp, (unsigned)(H - 1 - y));
+            if ((tid & 31) == __ffs(grp) - 1) {
+                InstStat *s = sst + idx[0];
+                atomicAdd(&s->sig, ((unsigned long long)shi << 16) + slo);
+                atomicAdd(&s->sy, (unsigned long long)sys);
+                atomicAdd(&s->sx, (unsigned long long)sxs);
+                atomicAdd(&s->cnt, cn);
+                atomicMax(&s->maxx, mx);
+                atomicMax(&s->maxnx, mnx);
+                atomicMax(&s->maxy, my);
+                atomicMax(&s->maxny, mny);
+            }
+        } else if (anyfg) {                                                    // instance border: run-length compressed per thread
+            int cur = -1;
+            unsigned cnt = 0, sx = 0, mnx = 0, mxx = 0;
+            unsigned long long sig = 0;
+            auto flush = [&]() {
+                if (cur < 0 || cnt == 0) return;
+                InstStat *s = sst + cur;
+                atomicAdd(&s->sig, sig);
+                atomicAdd(&s->sy, (unsigned long long)cnt * (unsigned)y);
+                atomicAdd(&s->sx, (unsigned long long)sx);
+                atomicAdd(&s->cnt, cnt);
+                atomicMax(&s->maxx, mxx);
+                atomicMax(&s->maxnx, (unsigned)(W - 1) - mnx);
+                atomicMax(&s->maxy, (unsigned)y);
+                atomicMax(&s->maxny, (unsigned)(H - 1 - y));
+            };
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (idx[j] != cur) { flush(); cur = idx[j]; cnt = 0; sx = 0; sig = 0; mnx = x0 + j; }
+                if (cur >= 0) { sig += q[j]; ++cnt; sx += x0 + j; mxx = x0 + j; }
+            }
+            flush();
+        }
     }
     __syncthreads();
     for (int i = tid; i < ninst; i += P_THREADS) {

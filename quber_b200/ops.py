@@ -8,6 +8,8 @@ custom ops at the bottom of the file.
 import ctypes
 
 import numpy as np
+import os
+
 import torch
 
 from . import _lib
@@ -307,6 +309,49 @@ def maxpool3x3s2(x):
         _lib.check(_lib.lib().quber_maxpool3x3s2(_ptr(x), _ptr(y), N, C, H, W, 0 if x.dtype == torch.float32 else 1, _stream()),
                    "quber_maxpool3x3s2")
     return y
+
+
+def host_pack_masks(masks_host, out=None, threads=None):
+    """HOST: bit-pack a contiguous uint8 CPU tensor (numel % 32 == 0) -> (int32 CPU tensor [numel / 32], value).
+    `value` = the one value every set pixel carries (1, or 255 as eval/refiner_model.py:230-231 makes the masks), 0 for
+    an all-zero buffer, -1 when there is more than one non-zero value (send the bytes then).  The reference moves the
+    bytes (predictor.py:304-310)."""
+    if masks_host.is_cuda or masks_host.dtype != torch.uint8 or not masks_host.is_contiguous():
+        raise ValueError("masks_host must be a contiguous uint8 CPU tensor")
+    n = masks_host.numel()
+    if n == 0 or n % 32:
+        raise ValueError("number of mask bytes must be a positive multiple of 32")
+    if out is None:
+        out = torch.empty(n // 32, dtype=torch.int32)
+    elif out.is_cuda or out.dtype != torch.int32 or out.numel() < n // 32 or not out.is_contiguous():
+        raise ValueError("out must be a contiguous int32 CPU tensor of numel / 32 words")
+    if threads is None:
+        threads = min(len(os.sched_getaffinity(0)), 32)
+    value = ctypes.c_int(-1)
+    _lib.check(_lib.lib().quber_host_pack_masks(masks_host.data_ptr(), n, out.data_ptr(), int(threads), ctypes.byref(value)),
+               "quber_host_pack_masks")
+    return out, int(value.value)
+
+
+def unpack_masks(packed, shape, value=1, out=None):
+    """int32 CUDA tensor of packed words -> uint8 CUDA tensor `shape` (prod(shape) == 32 * words), set pixels = value."""
+    _need_cuda(packed, "packed", torch.int32)
+    n = 1
+    for d in shape:
+        n *= int(d)
+    if n != 32 * packed.numel():
+        raise ValueError("shape does not match the number of packed words")
+    if not 0 <= int(value) <= 255:
+        raise ValueError("value must be a byte")
+    if out is None:
+        out = torch.empty(tuple(shape), dtype=torch.uint8, device=packed.device)
+    else:
+        _need_cuda(out, "out", torch.uint8)
+        if out.numel() != n or out.device != packed.device:
+            raise ValueError("out does not match shape")
+    with torch.cuda.device(packed.device):
+        _lib.check(_lib.lib().quber_unpack_masks(_ptr(packed), packed.numel(), int(value), _ptr(out), _stream()), "quber_unpack_masks")
+    return out
 
 
 def add_layer_norm(a, b, weight, bias, eps=1e-5, want_bf16=False, pos=None, q_dtype=None):

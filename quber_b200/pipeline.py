@@ -11,12 +11,18 @@ The network between A1 and A6 (backbone / DeepLabV3+ decoder / heads: cuDNN, SUR
 callable the caller supplies (`head_fn`); bench.py feeds synthetic head outputs instead because
 random-init predictors give no instance (SURVEY §8-d hazard).
 """
+import os
 from dataclasses import dataclass, field
 
 import numpy as np
 import torch
 
 from . import ops
+
+# Host-buffer path: pack the masks to one bit per pixel before the host->device copy?  None = time both routes on the
+# first call (HotPath._calibrate_pack).  On the 16-core B200 boxes of this pool 12 threads pack 8 cold frames in 0.63 ms
+# against 1.34 ms for their byte copy (scripts/bench_hostpack.py, profiles/r01_hostpack_v12.txt; DESIGN.md 3.8).
+PACK_MASKS_DEFAULT = None
 
 
 @dataclass
@@ -40,6 +46,12 @@ class HotPath:
         self.cfg = cfg or RefinerConfig()
         self.device = torch.device(device)
         self.launches_per_step = 0
+        # host-buffer path: send the 0/1 masks as one bit per pixel (csrc/hostpack.cpp).  QUBER_PACK_MASKS=0|1 overrides.
+        # None = decide on the first call by timing both routes on this host (_calibrate_pack).
+        env = os.environ.get("QUBER_PACK_MASKS")
+        self.pack_masks = PACK_MASKS_DEFAULT if env is None else (None if env == "auto" else env == "1")
+        cores = len(os.sched_getaffinity(0))
+        self.pack_threads = max(1, min(cores - 4, 12)) if cores > 4 else 1   # measured best on the 16-core boxes: 12
 
     # --- resident: every input already on the device -------------------------------------------
     def encode_and_boundary(self, masks):
@@ -80,12 +92,38 @@ class HotPath:
             st = dict(key=key, masks=torch.empty(masks_host.shape, dtype=torch.uint8, device=dev),
                       head={k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in head_host.items()},
                       h2d=torch.cuda.Stream(device=dev), d2h=torch.cuda.Stream(device=dev), free=None,
+                      packed_host=pin((masks_host.numel() + 31) // 32, torch.int32),
+                      packed_dev=torch.empty((masks_host.numel() + 31) // 32, dtype=torch.int32, device=dev), copied={},
                       out=dict(label_map=pin((B, H, W), torch.int32), boundary=pin((B, H, W), torch.uint8),
                                inst_start=pin((B,), torch.int32), inst_counts=pin((B,), torch.int32),
                                labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
                                boxes=pin((B * slab, 4), torch.float32)))
             self._stage = st
         return st
+
+    def _calibrate_pack(self, masks_host, st, sched):
+        """True when packing a chunk on the host cores is clearly cheaper than copying its bytes: both are timed once on
+        the second chunk (cold in the host caches), after a warm-up on the first.  The margin covers what the packing
+        loses when it runs beside the thread that enqueues the kernels."""
+        import time
+        fb = masks_host[0].numel()
+        if fb % 32 or not masks_host.is_contiguous() or self.pack_threads < 2:
+            return False
+        (a0, a1), (b0, b1) = sched[0], sched[min(1, len(sched) - 1)]
+        ops.host_pack_masks(masks_host[a0:a1], st["packed_host"][a0 * fb // 32:a1 * fb // 32], self.pack_threads)
+        t = time.perf_counter()
+        _, value = ops.host_pack_masks(masks_host[b0:b1], st["packed_host"][b0 * fb // 32:b1 * fb // 32], self.pack_threads)
+        t_pack = time.perf_counter() - t
+        h2d = st["h2d"]
+        with torch.cuda.stream(h2d):
+            st["masks"][a0:a1].copy_(masks_host[a0:a1], non_blocking=True)
+            e0 = h2d.record_event(torch.cuda.Event(enable_timing=True))
+            st["masks"][b0:b1].copy_(masks_host[b0:b1], non_blocking=True)
+            e1 = h2d.record_event(torch.cuda.Event(enable_timing=True))
+        e1.synchronize()
+        t_copy = e0.elapsed_time(e1) * 1e-3
+        self.pack_calibration = dict(pack_s=t_pack, copy_s=t_copy, frames=b1 - b0, threads=self.pack_threads)
+        return value >= 0 and t_pack < 0.6 * t_copy
 
     @staticmethod
     def chunk_schedule(B, chunk_frames, min_tail=2):
@@ -136,13 +174,44 @@ class HotPath:
             h2d.wait_event(st["free"])            # the previous call's kernels have finished reading the staging buffers
         d2h.wait_stream(cur)                      # ... and whoever consumed the pinned results was ordered on `cur`
         keep = []
-        for c0, c1 in self.chunk_schedule(B, chunk_frames):
+        frame_bytes = masks_host[0].numel()
+        sched = self.chunk_schedule(B, chunk_frames)
+        if self.pack_masks is None:
+            if st["free"] is not None:
+                st["free"].synchronize()
+            self.pack_masks = self._calibrate_pack(masks_host, st, sched)
+        pack = self.pack_masks and frame_bytes % 32 == 0 and masks_host.is_contiguous()
+        futs = None
+        if pack:
+            # One bit per pixel over the host link (csrc/hostpack.cpp).  The chunks are packed in order by a helper
+            # thread (the C call releases the GIL) while this thread enqueues copies and kernels of the chunks already
+            # packed.  The pinned words may still be read by the previous call's copies: wait for those first.
+            for ev in st["copied"].values():
+                ev.synchronize()
+            if getattr(self, "_packer", None) is None:
+                from concurrent.futures import ThreadPoolExecutor
+                self._packer = ThreadPoolExecutor(max_workers=1, thread_name_prefix="quber-pack")
+            futs = [self._packer.submit(ops.host_pack_masks, masks_host[c0:c1],
+                                        st["packed_host"][c0 * frame_bytes // 32:c1 * frame_bytes // 32], self.pack_threads)
+                    for c0, c1 in sched]
+        for ci, (c0, c1) in enumerate(sched):
+            packed, value = False, -1
+            if futs is not None:
+                w0, w1 = c0 * frame_bytes // 32, c1 * frame_bytes // 32
+                _, value = futs[ci].result()
+                packed = value >= 0                                         # one value on every set pixel (1 or 255)
             with torch.cuda.stream(h2d):
-                st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
+                if packed:
+                    st["packed_dev"][w0:w1].copy_(st["packed_host"][w0:w1], non_blocking=True)
+                else:                                                       # several non-zero values: the bytes as they are
+                    st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
                 for k, v in head_host.items():
                     st["head"][k][c0:c1].copy_(v[c0:c1], non_blocking=True)
                 ready = h2d.record_event()
+            st["copied"][(c0, c1)] = ready
             cur.wait_event(ready)
+            if packed:
+                ops.unpack_masks(st["packed_dev"][w0:w1], st["masks"][c0:c1].shape, value=value, out=st["masks"][c0:c1])
             enc, per, uni, fg = self.encode_and_boundary(st["masks"][c0:c1])
             r = self.post({k: v[c0:c1] for k, v in st["head"].items()})
             off = r["inst_offsets"]

@@ -230,6 +230,32 @@ def test_post_many_candidates_radix_paths():
             np.testing.assert_array_equal(r["ins_seg"][0].cpu().numpy(), oracle.group_pixels(ref_c, of))
 
 
+def test_center_nms_sparse_peaks_at_tile_borders():
+    """Tiles whose low-resolution footprint stays under the threshold are skipped (csrc/post.cu: center_nms_kernel);
+    single low-resolution peaks next to every kind of tile border, values straddling the threshold by a few ulp, must give
+    the oracle's centres exactly."""
+    h, w, scale, thr = 64, 96, 4, 0.3
+    rng = np.random.default_rng(12)
+    for trial in range(6):
+        low = np.full((h, w), 0.29, np.float32) if trial % 2 else rng.uniform(-1.0, 0.25, (h, w)).astype(np.float32)
+        # full-resolution NMS tiles are 64 x 32 -> low-resolution cells 16 x 8; put peaks on both sides of the borders
+        for (y, x) in [(7, 15), (8, 16), (15, 31), (16, 32), (0, 0), (h - 1, w - 1), (31, 47), (40, 17), (23, 80)]:
+            low[y, x] = np.float32(thr) + np.float32(rng.choice([-3e-8, 3e-8, 1e-3, 0.2]))
+        full = oracle.upsample_bilinear(low[None], scale)[0]
+        ref_c = oracle.find_instance_center(full, thr, 7, 200)
+        fg = np.full((h, w), 3.0, np.float32)
+        of = np.zeros((2, h, w), np.float32)
+        r = ops.post_process(cu(fg[None, None]), cu(low[None, None]), cu(of[None]), None, scale=scale, top_k=200, nms_kernel=7,
+                             want=("panoptic",))
+        n = int(r["n_centers"][0])
+        np.testing.assert_array_equal(r["centers_yx"][0, :n].cpu().numpy(), ref_c)
+    # an all-quiet map: no centre at all
+    low = np.full((h, w), 0.1, np.float32)
+    r = ops.post_process(cu(np.full((1, 1, h, w), 3.0, np.float32)), cu(low[None, None]), cu(np.zeros((1, 2, h, w), np.float32)), None,
+                         scale=scale, want=("panoptic",))
+    assert int(r["n_centers"][0]) == 0
+
+
 def test_reference_named_post_processing_functions():
     from quber_b200 import post_processing as pp
     g = golden("post.npz")
@@ -326,6 +352,30 @@ def test_msda_oracle_shapes_and_bf16(D):
         ob = ops.msda_forward(cu(inp["value"]).bfloat16(), *args)
         assert ob.dtype == torch.bfloat16
         # bf16 value/out, fp32 weights and accumulation: values ~1e-2, bf16 eps 2^-8 -> stated tolerance 2e-2 relative
+        np.testing.assert_allclose(ob.float().cpu().numpy(), ref, rtol=2e-2, atol=1e-5)
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 8])
+def test_msda_other_point_counts_take_the_generic_vector_kernel(P):
+    """P != 4 goes to the two-record kernel (csrc/msda.cu: msda_forward_kernel), P == 4 to the one-record kernel."""
+    inp = synth.msda_inputs(B=2, shapes=((15, 20), (8, 10), (4, 5)), M=4, D=32, P=P, Q=200, seed=40 + P, mode="border")
+    ref = oracle.msda_forward(inp["value"], inp["shapes"], inp["starts"], inp["loc"], inp["attn"])
+    args = (cu(inp["shapes"]), cu(inp["starts"]), cu(inp["loc"]), cu(inp["attn"]))
+    np.testing.assert_allclose(ops.msda_forward(cu(inp["value"]), *args).cpu().numpy(), ref, rtol=0, atol=1e-7)
+    ob = ops.msda_forward(cu(inp["value"]).bfloat16(), *args)
+    np.testing.assert_allclose(ob.float().cpu().numpy(), ref, rtol=2e-2, atol=1e-5)
+
+
+@pytest.mark.parametrize("shapes", [((1, 5), (4, 1), (1, 1)), ((2, 2), (1, 7)), ((9, 1),)])
+def test_msda_degenerate_levels_single_row_or_column(shapes):
+    """Levels one pixel wide or high: both x (or y) corners of a tap fall on the same pixel, one of them outside the map
+    (ms_deform_im2col_cuda.cuh:58-81 reads v = 0 there) — the one-record kernel folds the surviving weight."""
+    for D in (16, 32, 64):
+        inp = synth.msda_inputs(B=2, shapes=shapes, M=2, D=D, P=4, Q=257, seed=7 + D, mode="border")
+        ref = oracle.msda_forward(inp["value"], inp["shapes"], inp["starts"], inp["loc"], inp["attn"])
+        args = (cu(inp["shapes"]), cu(inp["starts"]), cu(inp["loc"]), cu(inp["attn"]))
+        np.testing.assert_allclose(ops.msda_forward(cu(inp["value"]), *args).cpu().numpy(), ref, rtol=0, atol=1e-7)
+        ob = ops.msda_forward(cu(inp["value"]).bfloat16(), *args)
         np.testing.assert_allclose(ob.float().cpu().numpy(), ref, rtol=2e-2, atol=1e-5)
 
 

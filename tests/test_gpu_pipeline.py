@@ -55,6 +55,45 @@ def test_refine_batch_host_matches_resident_path_and_oracle(B, chunk):
     assert keep[0][0].is_cuda                               # device results of every chunk stay alive
 
 
+def test_refine_batch_host_packed_mask_transfer_is_identical():
+    """One bit per pixel over the host link (quber_host_pack_masks + quber_unpack_masks) gives the same device masks,
+    hence the same results; a chunk carrying more than one non-zero value falls back to the byte copy."""
+    K, H, W, B = 6, 240, 320, 7
+    sets = []
+    for s in range(2):
+        masks, head = _inputs(B, K, H, W, seed=300 + s)
+        sets.append((torch.from_numpy(masks).pin_memory(), {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}))
+    plain, packed = HotPath(RefinerConfig(), "cuda"), HotPath(RefinerConfig(), "cuda")
+    plain.pack_masks, packed.pack_masks = False, True
+    for it in range(4):                                     # alternate inputs: pinned packed words are reused between calls
+        hm, hh = sets[it % 2]
+        o0, k0 = plain.refine_batch_host(hm, hh, chunk_frames=2)
+        o1, k1 = packed.refine_batch_host(hm, hh, chunk_frames=2)
+        torch.cuda.current_stream().synchronize()
+        assert torch.equal(packed._stage["masks"], hm.cuda())
+        for key in ("label_map", "boundary", "inst_start", "inst_counts"):
+            assert torch.equal(o0[key], o1[key]), key
+        for b in range(B):                                  # rows past inst_counts[b] are never written
+            s0, n = int(o0["inst_start"][b]), int(o0["inst_counts"][b])
+            for key in ("labels", "scores", "boxes"):
+                assert torch.equal(o0[key][s0:s0 + n], o1[key][s0:s0 + n]), (key, b)
+        for a, b in zip(k0, k1):
+            assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])      # encoding and per-instance boundaries
+    hm = sets[0][0].clone().pin_memory()
+    hm[3][hm[3] != 0] = 7                                   # frame 3 (chunk 2..3) carries a second value: byte copy
+    hm[5, 2][hm[5, 2] != 0] = 9                             # two values inside one frame
+    o0, k0 = plain.refine_batch_host(hm, sets[0][1], chunk_frames=2)
+    o1, k1 = packed.refine_batch_host(hm, sets[0][1], chunk_frames=2)
+    torch.cuda.current_stream().synchronize()
+    assert torch.equal(packed._stage["masks"], hm.cuda())
+    for a, b in zip(k0, k1):
+        assert torch.equal(a[1], b[1])                      # boundary values follow the mask's own value (util.py:72-90)
+    for src in (sets[1][0], (sets[1][0] != 0).to(torch.uint8)):            # 0/255 as the reference's eval makes them, and 0/1
+        words, value = ops.host_pack_masks(src)
+        assert value == int(src.max())
+        assert torch.equal(ops.unpack_masks(words.cuda(), src.shape, value=value).cpu(), src)
+
+
 def test_refine_batch_host_new_inputs_between_calls():
     """Back-to-back calls with different inputs must not race on the shared staging buffers."""
     K, H, W, B = 5, 240, 320, 4
