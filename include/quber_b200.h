@@ -295,6 +295,13 @@ int quber_msda_prepare(const float *oa, int ld, const float *reference_points, c
  * quber_unpack_masks — packed dev [n_words] uint32 -> out dev [32 n_words] uint8 (0 / value), out 16-byte aligned.
  * ------------------------------------------------------------------------------------------- */
 int quber_host_pack_masks(const uint8_t *src, size_t n_bytes, uint32_t *dst, int n_threads, int *value);
+/* The same, asynchronous and chunked: _begin returns at once; n_threads pool threads pack the chunks
+ * [chunk_end_bytes[c-1], chunk_end_bytes[c]) (ascending, multiples of 32, the last one == n_bytes; n_chunks <= 256) in
+ * order; _wait blocks until chunk c of the job in flight is packed and returns its *value as above.  One job at a time:
+ * a second _begin first waits for the previous job to finish. */
+int quber_host_pack_begin(const uint8_t *src, size_t n_bytes, uint32_t *dst, int n_threads, const size_t *chunk_end_bytes,
+                          int n_chunks);
+int quber_host_pack_wait(int chunk, int *value);
 int quber_unpack_masks(const uint32_t *packed, size_t n_words, int value, uint8_t *out, void *stream);
 
 #ifdef __cplusplus

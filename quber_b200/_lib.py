@@ -58,6 +58,8 @@ SYMBOLS = {
     "quber_maxpool3x3s2": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_vp]),
     "quber_add_layer_norm": (c_i, [c_vp, c_vp, c_vp, c_vp, c_sz, c_i, ctypes.c_float, c_vp, c_vp, c_vp, c_vp, c_i, c_vp]),
     "quber_host_pack_masks": (c_i, [c_vp, c_sz, c_vp, c_i, c_vp]),
+    "quber_host_pack_begin": (c_i, [c_vp, c_sz, c_vp, c_i, c_vp, c_i]),
+    "quber_host_pack_wait": (c_i, [c_i, c_vp]),
     "quber_unpack_masks": (c_i, [c_vp, c_sz, c_i, c_vp, c_vp]),
     "quber_msda_prepare": (c_i, [c_vp, c_i, c_vp, c_vp, c_sz, c_i, c_i, c_i, c_vp, c_vp, c_vp]),
     "quber_msda_forward": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),

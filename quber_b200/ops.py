@@ -333,6 +333,27 @@ def host_pack_masks(masks_host, out=None, threads=None):
     return out, int(value.value)
 
 
+def host_pack_begin(masks_host, out, threads, chunk_end_bytes):
+    """HOST, asynchronous: start packing `masks_host` (contiguous uint8 CPU tensor) into `out` (int32 CPU tensor of
+    numel / 32 words) on `threads` pool threads, chunk after chunk (`chunk_end_bytes`: ascending multiples of 32 ending at
+    numel).  Returns at once; host_pack_wait(c) blocks until chunk c is packed.  The caller keeps both tensors alive."""
+    if masks_host.is_cuda or masks_host.dtype != torch.uint8 or not masks_host.is_contiguous():
+        raise ValueError("masks_host must be a contiguous uint8 CPU tensor")
+    n = masks_host.numel()
+    if out.is_cuda or out.dtype != torch.int32 or out.numel() < n // 32 or not out.is_contiguous():
+        raise ValueError("out must be a contiguous int32 CPU tensor of numel / 32 words")
+    ends = (ctypes.c_size_t * len(chunk_end_bytes))(*[int(e) for e in chunk_end_bytes])
+    _lib.check(_lib.lib().quber_host_pack_begin(masks_host.data_ptr(), n, out.data_ptr(), int(threads), ends, len(chunk_end_bytes)),
+               "quber_host_pack_begin")
+
+
+def host_pack_wait(chunk):
+    """Blocks until `chunk` of the job started by host_pack_begin is packed -> its value (see host_pack_masks)."""
+    value = ctypes.c_int(-1)
+    _lib.check(_lib.lib().quber_host_pack_wait(int(chunk), ctypes.byref(value)), "quber_host_pack_wait")
+    return int(value.value)
+
+
 def unpack_masks(packed, shape, value=1, out=None):
     """int32 CUDA tensor of packed words -> uint8 CUDA tensor `shape` (prod(shape) == 32 * words), set pixels = value."""
     _need_cuda(packed, "packed", torch.int32)

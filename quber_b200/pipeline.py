@@ -50,8 +50,9 @@ class HotPath:
         # None = decide on the first call by timing both routes on this host (_calibrate_pack).
         env = os.environ.get("QUBER_PACK_MASKS")
         self.pack_masks = PACK_MASKS_DEFAULT if env is None else (None if env == "auto" else env == "1")
+        self.use_graphs = os.environ.get("QUBER_E2E_GRAPHS", "1") == "1"   # host-buffer path: one CUDA graph per chunk
         cores = len(os.sched_getaffinity(0))
-        self.pack_threads = max(1, min(cores - 4, 12)) if cores > 4 else 1   # measured best on the 16-core boxes: 12
+        self.pack_threads = max(1, min(cores - 2, 16)) if cores > 2 else 1   # the caller packs too while it waits
 
     # --- resident: every input already on the device -------------------------------------------
     def encode_and_boundary(self, masks):
@@ -94,12 +95,36 @@ class HotPath:
                       h2d=torch.cuda.Stream(device=dev), d2h=torch.cuda.Stream(device=dev), free=None,
                       packed_host=pin((masks_host.numel() + 31) // 32, torch.int32),
                       packed_dev=torch.empty((masks_host.numel() + 31) // 32, dtype=torch.int32, device=dev), copied={},
+                      graphs={},
                       out=dict(label_map=pin((B, H, W), torch.int32), boundary=pin((B, H, W), torch.uint8),
                                inst_start=pin((B,), torch.int32), inst_counts=pin((B,), torch.int32),
                                labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
                                boxes=pin((B * slab, 4), torch.float32)))
             self._stage = st
         return st
+
+    def _run_chunk(self, st, c0, c1, slab):
+        """Kernels of one chunk on the current stream: encode, boundaries, post-processing, slab offsets.  With
+        `use_graphs` the ~25 launches are captured once per chunk into a CUDA graph (inputs are the persistent staging
+        buffers, outputs live in the graph's pool and are overwritten by the next replay) — the host then spends one
+        graph launch per chunk instead of 0.3 ms of enqueueing, which is what bounds the call once the masks travel
+        bit-packed."""
+        def body():
+            enc, per, uni, fg = self.encode_and_boundary(st["masks"][c0:c1])
+            r = self.post({k: v[c0:c1] for k, v in st["head"].items()})
+            off = r["inst_offsets"]
+            return enc, per, uni, r, off[:-1] + c0 * slab, off[1:] - off[:-1]
+        if not self.use_graphs:
+            return body()
+        ent = st["graphs"].get((c0, c1))
+        if ent is None:
+            body()                                # eager once: lazy tables, function attributes, allocator warm-up
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                outs = body()
+            ent = st["graphs"][(c0, c1)] = (g, outs)
+        ent[0].replay()
+        return ent[1]
 
     def _calibrate_pack(self, masks_host, st, sched):
         """True when packing a chunk on the host cores is clearly cheaper than copying its bytes: both are timed once on
@@ -181,24 +206,18 @@ class HotPath:
                 st["free"].synchronize()
             self.pack_masks = self._calibrate_pack(masks_host, st, sched)
         pack = self.pack_masks and frame_bytes % 32 == 0 and masks_host.is_contiguous()
-        futs = None
         if pack:
-            # One bit per pixel over the host link (csrc/hostpack.cpp).  The chunks are packed in order by a helper
-            # thread (the C call releases the GIL) while this thread enqueues copies and kernels of the chunks already
-            # packed.  The pinned words may still be read by the previous call's copies: wait for those first.
+            # One bit per pixel over the host link (csrc/hostpack.cpp): the pool threads pack the chunks in order while
+            # this thread enqueues copies and kernels of the chunks already packed.  The pinned words may still be read
+            # by the previous call's copies: wait for those first.
             for ev in st["copied"].values():
                 ev.synchronize()
-            if getattr(self, "_packer", None) is None:
-                from concurrent.futures import ThreadPoolExecutor
-                self._packer = ThreadPoolExecutor(max_workers=1, thread_name_prefix="quber-pack")
-            futs = [self._packer.submit(ops.host_pack_masks, masks_host[c0:c1],
-                                        st["packed_host"][c0 * frame_bytes // 32:c1 * frame_bytes // 32], self.pack_threads)
-                    for c0, c1 in sched]
+            ops.host_pack_begin(masks_host, st["packed_host"], self.pack_threads, [c1 * frame_bytes for _, c1 in sched])
         for ci, (c0, c1) in enumerate(sched):
             packed, value = False, -1
-            if futs is not None:
+            if pack:
                 w0, w1 = c0 * frame_bytes // 32, c1 * frame_bytes // 32
-                _, value = futs[ci].result()
+                value = ops.host_pack_wait(ci)
                 packed = value >= 0                                         # one value on every set pixel (1 or 255)
             with torch.cuda.stream(h2d):
                 if packed:
@@ -212,11 +231,7 @@ class HotPath:
             cur.wait_event(ready)
             if packed:
                 ops.unpack_masks(st["packed_dev"][w0:w1], st["masks"][c0:c1].shape, value=value, out=st["masks"][c0:c1])
-            enc, per, uni, fg = self.encode_and_boundary(st["masks"][c0:c1])
-            r = self.post({k: v[c0:c1] for k, v in st["head"].items()})
-            off = r["inst_offsets"]
-            counts = off[1:] - off[:-1]
-            start = off[:-1] + c0 * slab
+            enc, per, uni, r, start, counts = self._run_chunk(st, c0, c1, slab)
             done = cur.record_event()
             n = (c1 - c0) * slab
             with torch.cuda.stream(d2h):
