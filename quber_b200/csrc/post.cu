@@ -399,9 +399,32 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
                 bd2[j] = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
                 best[j] = 0;
             }
+            // Pruning (exact): the eight voted positions of a thread lie in a small box (midpoint m, half diagonal r).
+            // A centre at distance D from m is at least D - r from each of them, so it cannot beat any current best when
+            // D > max_j best_j + r; the bound carries a relative 2e-5 + absolute 1e-3 slack, far wider than the fp32
+            // rounding of the distances (3e-7) and than the tie band below, so a skipped centre never wins or ties.
+            float mny = ly[0], mxy = ly[0], mnx = lx[0], mxx = lx[0];
+#pragma unroll
+            for (int j = 1; j < 8; ++j) {
+                mny = fminf(mny, ly[j]); mxy = fmaxf(mxy, ly[j]);
+                mnx = fminf(mnx, lx[j]); mxx = fmaxf(mxx, lx[j]);
+            }
+            const float my = 0.5f * (mny + mxy), mx = 0.5f * (mnx + mxx);
+            const float rad = sqrtf((mxy - my) * (mxy - my) + (mxx - mx) * (mxx - mx)) * 1.0001f + 1e-3f;
+            auto prune_bound = [&]() {
+                float b = bd2[0];
+#pragma unroll
+                for (int j = 1; j < 8; ++j) b = fmaxf(b, bd2[j]);
+                const float s_ = sqrtf(b) + rad;
+                return s_ * s_ * 1.00002f + 1e-3f;
+            };
+            float cut2 = prune_bound();
 #pragma unroll 1
             for (int k = 1; k < n; ++k) {
                 const float2 c = cyx[k];
+                const float my_ = c.x - my, mx_ = c.y - mx;
+                if (my_ * my_ + mx_ * mx_ > cut2) continue;                                    // NaN bound: never skips
+                bool changed = false;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const float dy = __fsub_rn(c.x, ly[j]), dx = __fsub_rn(c.y, lx[j]);
@@ -410,9 +433,10 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
                         bool better = true;
                         if (!(d2 < bd2[j] * 0.99999952316284179688f))                          // 1 - 2^-21: the 4-ulp band,
                             better = __fsqrt_rn(d2) < __fsqrt_rn(bd2[j]);                      // compare the roots
-                        if (better) { bd2[j] = d2; best[j] = k; }
+                        if (better) { bd2[j] = d2; best[j] = k; changed = true; }
                     }
                 }
+                if (changed) cut2 = prune_bound();
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) if (fgm >> j & 1) id[j] = best[j] + 1;
