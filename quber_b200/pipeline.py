@@ -120,9 +120,16 @@ class HotPath:
         ent = st["graphs"].get((c0, c1))
         if ent is None:
             body()                                # eager once: lazy tables, function attributes, allocator warm-up
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                outs = body()
+            try:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    outs = body()
+            except RuntimeError as e:             # capture refused (another thread allocating, driver quirk): stay eager
+                import warnings
+                warnings.warn(f"quber_b200: CUDA graph capture of the chunk kernels failed, launching eagerly ({e})")
+                self.use_graphs = False
+                torch.cuda.synchronize(self.device)
+                return body()
             ent = st["graphs"][(c0, c1)] = (g, outs)
         ent[0].replay()
         return ent[1]
@@ -216,37 +223,43 @@ class HotPath:
             for ev in st["copied"].values():
                 ev.synchronize()
             ops.host_pack_begin(masks_host, st["packed_host"], self.pack_threads, [c1 * frame_bytes for _, c1 in sched])
-        for ci, (c0, c1) in enumerate(sched):
-            packed, value = False, -1
-            if pack:
-                w0, w1 = c0 * frame_bytes // 32, c1 * frame_bytes // 32
-                value = ops.host_pack_wait(ci)
-                packed = value >= 0                                         # one value on every set pixel (1 or 255)
-            with torch.cuda.stream(h2d):
+        try:
+            for ci, (c0, c1) in enumerate(sched):
+                packed, value = False, -1
+                if pack:
+                    w0, w1 = c0 * frame_bytes // 32, c1 * frame_bytes // 32
+                    value = ops.host_pack_wait(ci)
+                    packed = value >= 0                                         # one value on every set pixel (1 or 255)
+                with torch.cuda.stream(h2d):
+                    if packed:
+                        st["packed_dev"][w0:w1].copy_(st["packed_host"][w0:w1], non_blocking=True)
+                    else:                                                       # several non-zero values: the bytes as they are
+                        st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
+                    for k, v in head_host.items():
+                        st["head"][k][c0:c1].copy_(v[c0:c1], non_blocking=True)
+                    ready = h2d.record_event()
+                st["copied"][(c0, c1)] = ready
+                cur.wait_event(ready)
                 if packed:
-                    st["packed_dev"][w0:w1].copy_(st["packed_host"][w0:w1], non_blocking=True)
-                else:                                                       # several non-zero values: the bytes as they are
-                    st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
-                for k, v in head_host.items():
-                    st["head"][k][c0:c1].copy_(v[c0:c1], non_blocking=True)
-                ready = h2d.record_event()
-            st["copied"][(c0, c1)] = ready
-            cur.wait_event(ready)
-            if packed:
-                ops.unpack_masks(st["packed_dev"][w0:w1], st["masks"][c0:c1].shape, value=value, out=st["masks"][c0:c1])
-            enc, per, uni, r, start, counts = self._run_chunk(st, c0, c1, slab)
-            done = cur.record_event()
-            n = (c1 - c0) * slab
-            with torch.cuda.stream(d2h):
-                d2h.wait_event(done)
-                out["label_map"][c0:c1].copy_(r["label_map"], non_blocking=True)
-                out["boundary"][c0:c1].copy_(uni, non_blocking=True)
-                out["inst_start"][c0:c1].copy_(start, non_blocking=True)
-                out["inst_counts"][c0:c1].copy_(counts, non_blocking=True)
-                out["labels"][c0 * slab:c0 * slab + n].copy_(r["labels"][:n], non_blocking=True)
-                out["scores"][c0 * slab:c0 * slab + n].copy_(r["scores"][:n], non_blocking=True)
-                out["boxes"][c0 * slab:c0 * slab + n].copy_(r["boxes"][:n], non_blocking=True)
-            keep.append((enc, per, r, start, counts))
+                    ops.unpack_masks(st["packed_dev"][w0:w1], st["masks"][c0:c1].shape, value=value, out=st["masks"][c0:c1])
+                enc, per, uni, r, start, counts = self._run_chunk(st, c0, c1, slab)
+                done = cur.record_event()
+                n = (c1 - c0) * slab
+                with torch.cuda.stream(d2h):
+                    d2h.wait_event(done)
+                    out["label_map"][c0:c1].copy_(r["label_map"], non_blocking=True)
+                    out["boundary"][c0:c1].copy_(uni, non_blocking=True)
+                    out["inst_start"][c0:c1].copy_(start, non_blocking=True)
+                    out["inst_counts"][c0:c1].copy_(counts, non_blocking=True)
+                    out["labels"][c0 * slab:c0 * slab + n].copy_(r["labels"][:n], non_blocking=True)
+                    out["scores"][c0 * slab:c0 * slab + n].copy_(r["scores"][:n], non_blocking=True)
+                    out["boxes"][c0 * slab:c0 * slab + n].copy_(r["boxes"][:n], non_blocking=True)
+                keep.append((enc, per, r, start, counts))
+        except BaseException:
+            if pack:
+                for c in range(len(sched)):           # the pool must not go on reading the caller's buffers
+                    ops.host_pack_wait(c)
+            raise
         st["free"] = cur.record_event()
         cur.wait_stream(d2h)
         self._keep = keep                         # device results stay alive until the next call replaces them
