@@ -361,7 +361,10 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
     __syncthreads();
     const UpSampler up(H, W, p.scale);
     const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
-    const int y = blockIdx.y * P_TH + (tid >> 4), x0 = blockIdx.x * P_TW + (tid & 15) * 8;
+    // a warp covers 8 rows x 32 pixels of the tile (not 2 x 128): the compact footprint is what lets the centre pruning
+    // below skip a centre for the WHOLE warp
+    const int wrp = tid >> 5, ln = tid & 31;
+    const int y = blockIdx.y * P_TH + (wrp >> 2) * 8 + (ln >> 2), x0 = blockIdx.x * P_TW + ((wrp & 3) * 4 + (ln & 3)) * 8;
     const bool inb = y < H && x0 < W;
     if (inb) {
         const size_t pix = (size_t)y * W + x0;
