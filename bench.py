@@ -226,12 +226,13 @@ def run_ours(args):
     # ---- end to end (host buffers in, host results out) ----
     outs_host = None
     E2E_CHUNK = int(os.environ.get("QUBER_E2E_CHUNK", "16"))     # frames per pipeline chunk (measured 4 | 8 | 16 | 32: 4.89 | 4.85 | 4.50 | 4.56 ms)
+    E2E_TAIL = int(os.environ.get("QUBER_E2E_TAIL", "8"))        # smallest chunk of the halving tail
     def e2e_step(s):
         d = sets[s % NSETS]
         # decoder activations never live on the host (resident inputs); launched first so the sampling kernels run
         # under the first host->device copies of refine_batch_host's chunk pipeline
         hp.msda_layers(d["msda"], N_LAYERS)
-        o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK)
+        o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL)
         if world > 1:
             lm = torch.cat([k[2]["label_map"] for k in keep])
             sharding.gather_label_maps(lm, torch.cat([k[4] for k in keep]), out=gather_buf)

@@ -182,7 +182,7 @@ class HotPath:
                 c0 += n
         return out
 
-    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8):
+    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2):
         """The end-to-end call: host buffers in, host results out.
 
         masks_host: pinned uint8 [B,K,H,W]; head_host: dict of pinned float32 head outputs (what the
@@ -210,7 +210,7 @@ class HotPath:
         d2h.wait_stream(cur)                      # ... and whoever consumed the pinned results was ordered on `cur`
         keep = []
         frame_bytes = masks_host[0].numel()
-        sched = self.chunk_schedule(B, chunk_frames)
+        sched = self.chunk_schedule(B, chunk_frames, min_tail)
         if self.pack_masks is None:
             if st["free"] is not None:
                 st["free"].synchronize()
