@@ -146,7 +146,9 @@ def run_ours(args):
         hh = {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}
         sets.append(dict(h_masks=hm, h_head=hh, masks=hm.to(dev), head={k: v.to(dev) for k, v in hh.items()},
                          msda={k: torch.from_numpy(v).to(dev) for k, v in msda.items()}))
-    gather_buf = torch.empty((world, B, H, W), dtype=torch.int32, device=dev) if world > 1 else None
+    # label maps travel as uint8 (at most max_instances_per_image = 64 ids per frame): 9.8 MB per rank instead of 39 MB
+    compact = hp.cfg.max_instances_per_image <= 255
+    gather_buf = torch.empty((world, B, H, W), dtype=torch.uint8 if compact else torch.int32, device=dev) if world > 1 else None
     side = torch.cuda.Stream(device=dev) if world > 1 else None
 
     stage_names = ["encode", "boundary", "msda", "post"]
@@ -169,7 +171,7 @@ def run_ours(args):
             counts = r["inst_offsets"][1:] - r["inst_offsets"][:-1]
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                sharding.gather_label_maps(r["label_map"], counts, out=gather_buf)
+                sharding.gather_label_maps(r["label_map"], counts, out=gather_buf, compact=compact)
             r["label_map"].record_stream(side)
             counts.record_stream(side)
         return r
@@ -235,7 +237,7 @@ def run_ours(args):
         o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL)
         if world > 1:
             lm = torch.cat([k[2]["label_map"] for k in keep])
-            sharding.gather_label_maps(lm, torch.cat([k[4] for k in keep]), out=gather_buf)
+            sharding.gather_label_maps(lm, torch.cat([k[4] for k in keep]), out=gather_buf, compact=compact)
         return o
     for i in range(max(1, min(args.warmup, 3))):
         o = e2e_step(i)

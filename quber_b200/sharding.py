@@ -21,14 +21,20 @@ def frame_blocks(n_frames, block, rank, world):
     return [(i * block, min((i + 1) * block, n_frames)) for i in range(rank, n_blocks, world)]
 
 
-def gather_label_maps(label_map, counts, group=None, out=None):
+def gather_label_maps(label_map, counts, group=None, out=None, compact=False):
     """label_map int32 [B,H,W], counts int32 [B] on this rank -> (maps [G,B,H,W], counts [G,B]) on every rank.
-    One collective for the maps (NCCL all_gather_into_tensor over NVLink; gloo falls back to all_gather)."""
+    One collective for the maps (NCCL all_gather_into_tensor over NVLink; gloo falls back to all_gather).
+    compact: the maps travel (and are returned) as uint8 — a quarter of the bytes; the caller guarantees at most 255
+    instances per frame (RefinerConfig.max_instances_per_image), checked here against `counts` only in debug runs."""
+    if label_map.dtype not in (torch.int32, torch.uint8) or counts.dtype != torch.int32:
+        raise ValueError("label_map must be int32 (or uint8, already compact) and counts int32")
+    if compact and label_map.dtype != torch.uint8:
+        label_map = label_map.to(torch.uint8)
     if not dist.is_available() or not dist.is_initialized():
         return label_map[None], counts[None]
     world = dist.get_world_size(group)
-    if label_map.dtype != torch.int32 or counts.dtype != torch.int32:
-        raise ValueError("label_map and counts must be int32")
+    if out is not None and (out.dtype != label_map.dtype or tuple(out.shape) != (world,) + tuple(label_map.shape)):
+        raise ValueError("out must be [world, B, H, W] of the dtype the maps travel in")
     maps = out if out is not None else torch.empty((world,) + tuple(label_map.shape), dtype=label_map.dtype, device=label_map.device)
     cnts = torch.empty((world,) + tuple(counts.shape), dtype=counts.dtype, device=counts.device)
     if dist.get_backend(group) == "nccl":
@@ -42,5 +48,5 @@ def gather_label_maps(label_map, counts, group=None, out=None):
 
 def masks_from_label_map(label_map, n_instances):
     """[H,W] int32 label map -> bool [n,H,W], the reference's `pred_masks` (model.py:331-336)."""
-    ids = torch.arange(1, int(n_instances) + 1, device=label_map.device, dtype=label_map.dtype)
+    ids = torch.arange(1, int(n_instances) + 1, device=label_map.device, dtype=torch.int32).to(label_map.dtype)
     return label_map[None] == ids[:, None, None]

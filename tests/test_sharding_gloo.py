@@ -44,6 +44,11 @@ def _worker(rank, world, port, q):
         other = (rank + 1) % world
         m = sharding.masks_from_label_map(allm[other, 0], allc[other, 0])
         ok = ok and m.shape[0] == int(allc[other, 0]) and bool((m.sum(0) == (allm[other, 0] > 0)).all())
+        # compact transport: uint8 maps (<= 255 instances per frame), same content
+        cm, cc = sharding.gather_label_maps(maps, counts, compact=True)
+        ok = ok and cm.dtype == torch.uint8 and torch.equal(cm.to(torch.int32), allm) and torch.equal(cc, allc)
+        m8 = sharding.masks_from_label_map(cm[other, 0], cc[other, 0])
+        ok = ok and torch.equal(m8, m)
         # whole-job instance count = sum over ranks, as bench.py aggregates it
         tot = allc.sum().clone()
         mine = counts.sum().clone()
@@ -71,3 +76,5 @@ def test_single_process_passthrough():
     maps, counts = _label_maps(0)
     a, c = sharding.gather_label_maps(maps, counts)
     assert a.shape[0] == 1 and torch.equal(a[0], maps) and torch.equal(c[0], counts)
+    a8, _ = sharding.gather_label_maps(maps, counts, compact=True)
+    assert a8.dtype == torch.uint8 and torch.equal(a8[0].to(torch.int32), maps)
