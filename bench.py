@@ -111,6 +111,27 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------------- ours
+def ncu_dram_bytes(kernel_substr):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of a kernel, from the newest committed `ncu --set full`
+    summary under profiles/ (scripts/ncu_summary.py; the capture is a separate run under the profiler, never this one).
+    -> (bytes | None, file name | None)."""
+    import csv, glob, re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_v*_ncu_full_summary.csv")),
+                   key=lambda f: [int(x) for x in re.findall(r"\d+", os.path.basename(f))])
+    for f in reversed(files):
+        try:
+            rows = list(csv.reader(open(f)))
+            h, units = rows[0], rows[1]
+            ir, iw = h.index("dram__bytes_read.sum"), h.index("dram__bytes_write.sum")
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            vals = [float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]] for r in rows[2:] if kernel_substr in r[0]]
+            if vals:
+                return sum(vals) / len(vals), os.path.basename(f)
+        except Exception:
+            continue
+    return None, None
+
+
 def algorithmic_bytes():
     """Per launch, B frames (SURVEY §8-d formulas)."""
     HW = H * W
@@ -299,6 +320,7 @@ def run_ours(args):
     for v in roof_all.values():
         v["achieved_gbs"] = v["bytes"] / (v["ms"] * 1e-3) / 1e9
         v["frac"] = v["achieved_gbs"] / peak_gbs
+    ncu_traffic, ncu_src = ncu_dram_bytes("msda_forward")
     dominant = max(("boundary_kernel", "msda_forward_p4_kernel", "encode(reduce+emit)"),
                    key=lambda k: roof_all[k]["ms"] * (N_LAYERS if k.startswith("msda") else 1))
     dv = roof_all[dominant]
@@ -316,7 +338,8 @@ def run_ours(args):
         "instances_per_step": n_inst_total / args.steps, "post_status": status,
         "stage_ms": per_stage,
         "roofline": {"kernel": dominant, "bound": "hbm", "achieved": dv["achieved_gbs"], "peak": peak_gbs, "unit": "GB/s",
-                     "frac": dv["frac"], "traffic": None, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": dv["bytes"],
+                     "frac": dv["frac"], "traffic": ncu_traffic if dominant.startswith("msda") else None, "traffic_source": ncu_src,
+                     "peak_kind": peak_kind, "algorithmic_bytes_per_launch": dv["bytes"],
                      "avg_launch_ms": dv["ms"],
                      "note": ("msda fp32 is bounded by the L1 data pipe, not HBM: 48 gathered 128-byte lines per (query, head) = "
                               "266 us/launch at 128 B/clk/SM, i.e. frac <= 0.37 for any L1/shared-memory gather (DESIGN.md 3.1); "
