@@ -94,6 +94,38 @@ def test_refine_batch_host_packed_mask_transfer_is_identical():
         assert torch.equal(ops.unpack_masks(words.cuda(), src.shape, value=value).cpu(), src)
 
 
+def test_refine_batch_host_full_size_c2_packed_graphs_equal_resident():
+    """BASELINE.json C2 shape (32 frames 640x480, 30 masks of 0/255) through the call bench.py times — packed transfer,
+    one CUDA graph per chunk, 16 + 8 + 8 frames — against the resident path on the same inputs, twice (graph replays)."""
+    B, K, H, W = 32, 30, 480, 640
+    base_m, base_h = _inputs(4, K, H, W, seed=900)
+    masks = np.concatenate([base_m[(np.arange(4) + s) % 4] for s in range(B // 4)])
+    head = {k: np.concatenate([v[(np.arange(4) + s) % 4] for s in range(B // 4)]) for k, v in base_h.items()}
+    hm = torch.from_numpy(masks).pin_memory()
+    hh = {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}
+    hp = HotPath(RefinerConfig(), "cuda")
+    hp.pack_masks, hp.use_graphs = True, True
+    ref = HotPath(RefinerConfig(), "cuda")
+    enc, per, uni, fg = ref.encode_and_boundary(hm.cuda())
+    r = ref.post({k: v.cuda() for k, v in hh.items()})
+    offs = r["inst_offsets"].cpu().numpy()
+    for rep in range(3):
+        out, keep = hp.refine_batch_host(hm, hh, chunk_frames=16, min_tail=8)
+        torch.cuda.current_stream().synchronize()
+        assert [k[0].shape[0] for k in keep] == [16, 8, 8]
+        assert torch.equal(hp._stage["masks"], hm.cuda())
+        assert np.array_equal(out["label_map"].numpy(), r["label_map"].cpu().numpy())
+        assert np.array_equal(out["boundary"].numpy(), uni.cpu().numpy())
+        assert np.array_equal(out["inst_counts"].numpy(), offs[1:] - offs[:-1])
+        assert torch.equal(torch.cat([k[0] for k in keep]), enc) and torch.equal(torch.cat([k[1] for k in keep]), per)
+        for b in (0, 15, 16, 31):
+            s0, n = int(out["inst_start"][b]), int(out["inst_counts"][b])
+            assert n > 0
+            for key in ("labels", "scores", "boxes"):
+                assert np.array_equal(out[key][s0:s0 + n].numpy(), r[key][offs[b]:offs[b + 1]].cpu().numpy()), (key, b)
+    assert int(out["inst_counts"].sum()) >= 5 * B          # size-independent sanity: every frame keeps most of its objects
+
+
 def test_refine_batch_host_new_inputs_between_calls():
     """Back-to-back calls with different inputs must not race on the shared staging buffers."""
     K, H, W, B = 5, 240, 320, 4
