@@ -248,12 +248,17 @@ def run_ours(args):
 
     # ---- end to end (host buffers in, host results out) ----
     outs_host = None
-    E2E_CHUNK = int(os.environ.get("QUBER_E2E_CHUNK", "16"))     # frames per pipeline chunk (measured 4 | 8 | 16 | 32: 4.89 | 4.85 | 4.50 | 4.56 ms)
-    E2E_TAIL = int(os.environ.get("QUBER_E2E_TAIL", "8"))        # smallest chunk of the halving tail
+    # frames per pipeline chunk and smallest chunk of the halving tail: 8 / 2 -> 8 + 8 + 8 + 4 + 2 + 2.  On a quiet host
+    # 16 / 8, 8 / 4 and 8 / 2 all give 4.4-4.5 ms per step; on a box with a slow host (device->host at 25 GB/s, packing at
+    # half speed) 8 / 2 gave 5.0 ms where 16 / 8 gave 7.1 ms, so the fine schedule is the default.
+    E2E_CHUNK = int(os.environ.get("QUBER_E2E_CHUNK", "8"))
+    E2E_TAIL = int(os.environ.get("QUBER_E2E_TAIL", "2"))
     def e2e_step(s):
         d = sets[s % NSETS]
         # decoder activations never live on the host (resident inputs); launched first so the sampling kernels run
-        # under the first host->device copies of refine_batch_host's chunk pipeline
+        # under the host-side packing / host->device copies of refine_batch_host's chunk pipeline.  (Putting the chunk
+        # pipeline on a second, high-priority stream next to the sampling kernels was measured: 4.36-4.46 against
+        # 4.43-4.47 ms per step — the sampling kernels fill the register files, the two only time-share.)
         hp.msda_layers(d["msda"], N_LAYERS)
         o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL)
         if world > 1:
