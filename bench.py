@@ -262,8 +262,7 @@ def run_ours(args):
         hp.msda_layers(d["msda"], N_LAYERS)
         o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL)
         if world > 1:
-            lm = torch.cat([k[2]["label_map"] for k in keep])
-            sharding.gather_label_maps(lm, torch.cat([k[4] for k in keep]), out=gather_buf, compact=compact)
+            sharding.gather_label_maps(keep[0][2]["label_map"], torch.cat([k[4] for k in keep]), out=gather_buf, compact=compact)
         return o
     for i in range(max(1, min(args.warmup, 3))):
         o = e2e_step(i)

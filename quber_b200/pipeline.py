@@ -104,20 +104,14 @@ class HotPath:
             self._stage = st
         return st
 
-    def _run_chunk(self, st, c0, c1, slab):
-        """Kernels of one chunk on the current stream: encode, boundaries, post-processing, slab offsets.  With
-        `use_graphs` the ~25 launches are captured once per chunk into a CUDA graph (inputs are the persistent staging
-        buffers, outputs live in the graph's pool and are overwritten by the next replay) — the host then spends one
-        graph launch per chunk instead of 0.3 ms of enqueueing, which is what bounds the call once the masks travel
-        bit-packed."""
-        def body():
-            enc, per, uni, fg = self.encode_and_boundary(st["masks"][c0:c1])
-            r = self.post({k: v[c0:c1] for k, v in st["head"].items()})
-            off = r["inst_offsets"]
-            return enc, per, uni, r, off[:-1] + c0 * slab, off[1:] - off[:-1]
+    def _run_graphed(self, st, key, body):
+        """`body()` (kernel launches on the current stream, inputs = the persistent staging buffers) eagerly, or with
+        `use_graphs` captured once per `key` into a CUDA graph and replayed (outputs live in the graph's pool and are
+        overwritten by the next replay) — the host then spends one graph launch instead of 0.1-0.3 ms of enqueueing,
+        which is what bounds the call once the masks travel bit-packed."""
         if not self.use_graphs:
             return body()
-        ent = st["graphs"].get((c0, c1))
+        ent = st["graphs"].get(key)
         if ent is None:
             body()                                # eager once: lazy tables, function attributes, allocator warm-up
             try:
@@ -126,11 +120,11 @@ class HotPath:
                     outs = body()
             except RuntimeError as e:             # capture refused (another thread allocating, driver quirk): stay eager
                 import warnings
-                warnings.warn(f"quber_b200: CUDA graph capture of the chunk kernels failed, launching eagerly ({e})")
+                warnings.warn(f"quber_b200: CUDA graph capture failed, launching eagerly ({e})")
                 self.use_graphs = False
                 torch.cuda.synchronize(self.device)
                 return body()
-            ent = st["graphs"][(c0, c1)] = (g, outs)
+            ent = st["graphs"][key] = (g, outs)
         ent[0].replay()
         return ent[1]
 
@@ -194,7 +188,9 @@ class HotPath:
         label_map [B,H,W] int32 (0 = void, j+1 = j-th refined instance of the frame — the lossless compact
         form of the reference's pred_masks), boundary [B,H,W] uint8 (union boundary of the initial
         masks), inst_start / inst_counts [B] int32 (frame b's instances are rows inst_start[b] ... +inst_counts[b]
-        of labels / scores / boxes; every chunk owns a slab of chunk_frames * max_instances_per_image rows).
+        of labels / scores / boxes).  Post-processing runs once for the whole batch as soon as the head outputs have
+        arrived; the chunks carry the masks (encode, boundaries).  `keep` = per chunk (encoding, per-instance boundaries,
+        the batch's post-processing result, inst_start slice, inst_counts slice).
         The host tensors are pinned and reused between calls; they are valid once the caller has synchronised
         the current stream (which this call makes wait for both copy streams).
         """
@@ -224,6 +220,26 @@ class HotPath:
                 ev.synchronize()
             ops.host_pack_begin(masks_host, st["packed_host"], self.pack_threads, [c1 * frame_bytes for _, c1 in sched])
         try:
+            # Post-processing needs the head outputs only (20 MB): they go first and the whole batch is post-processed in
+            # one launch sequence (full grids, one set of the small serial kernels) while the masks are packed / copied.
+            with torch.cuda.stream(h2d):
+                for k, v in head_host.items():
+                    st["head"][k].copy_(v, non_blocking=True)
+                heads_ready = h2d.record_event()
+            st["copied"]["heads"] = heads_ready
+            cur.wait_event(heads_ready)
+            r = self._run_graphed(st, "post", lambda: self.post(st["head"]))
+            off = r["inst_offsets"]
+            start, counts = off[:-1], off[1:] - off[:-1]
+            post_done = cur.record_event()
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(post_done)
+                out["label_map"].copy_(r["label_map"], non_blocking=True)
+                out["inst_start"].copy_(start, non_blocking=True)
+                out["inst_counts"].copy_(counts, non_blocking=True)
+                out["labels"].copy_(r["labels"][:B * slab], non_blocking=True)
+                out["scores"].copy_(r["scores"][:B * slab], non_blocking=True)
+                out["boxes"].copy_(r["boxes"][:B * slab], non_blocking=True)
             for ci, (c0, c1) in enumerate(sched):
                 packed, value = False, -1
                 if pack:
@@ -235,26 +251,17 @@ class HotPath:
                         st["packed_dev"][w0:w1].copy_(st["packed_host"][w0:w1], non_blocking=True)
                     else:                                                       # several non-zero values: the bytes as they are
                         st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
-                    for k, v in head_host.items():
-                        st["head"][k][c0:c1].copy_(v[c0:c1], non_blocking=True)
                     ready = h2d.record_event()
                 st["copied"][(c0, c1)] = ready
                 cur.wait_event(ready)
                 if packed:
                     ops.unpack_masks(st["packed_dev"][w0:w1], st["masks"][c0:c1].shape, value=value, out=st["masks"][c0:c1])
-                enc, per, uni, r, start, counts = self._run_chunk(st, c0, c1, slab)
+                enc, per, uni, fg = self._run_graphed(st, (c0, c1), lambda: self.encode_and_boundary(st["masks"][c0:c1]))
                 done = cur.record_event()
-                n = (c1 - c0) * slab
                 with torch.cuda.stream(d2h):
                     d2h.wait_event(done)
-                    out["label_map"][c0:c1].copy_(r["label_map"], non_blocking=True)
                     out["boundary"][c0:c1].copy_(uni, non_blocking=True)
-                    out["inst_start"][c0:c1].copy_(start, non_blocking=True)
-                    out["inst_counts"][c0:c1].copy_(counts, non_blocking=True)
-                    out["labels"][c0 * slab:c0 * slab + n].copy_(r["labels"][:n], non_blocking=True)
-                    out["scores"][c0 * slab:c0 * slab + n].copy_(r["scores"][:n], non_blocking=True)
-                    out["boxes"][c0 * slab:c0 * slab + n].copy_(r["boxes"][:n], non_blocking=True)
-                keep.append((enc, per, r, start, counts))
+                keep.append((enc, per, r, start[c0:c1], counts[c0:c1]))
         except BaseException:
             if pack:
                 for c in range(len(sched)):           # the pool must not go on reading the caller's buffers

@@ -26,15 +26,15 @@ def step(i):
 for i in range(4):
     step(i); torch.cuda.synchronize()
 ev, host = [], []
-orig_run, orig_wait = hp._run_chunk, ops.host_pack_wait
-def run(st, c0, c1, slab):
+orig_run, orig_wait = hp._run_graphed, ops.host_pack_wait
+def run(st, key, body):
     a = torch.cuda.Event(enable_timing=True); a.record()
-    r = orig_run(st, c0, c1, slab)
+    r = orig_run(st, key, body)
     b = torch.cuda.Event(enable_timing=True); b.record()
-    ev.append((c0, c1, a, b)); return r
+    ev.append((key, a, b)); return r
 def wait(c):
     t0 = time.perf_counter(); r = orig_wait(c); host.append((c, t0, time.perf_counter())); return r
-hp._run_chunk, ops.host_pack_wait = run, wait
+hp._run_graphed, ops.host_pack_wait = run, wait
 for rep in range(3):
     ev.clear(); host.clear()
     torch.cuda.synchronize()
@@ -51,6 +51,7 @@ for rep in range(3):
     t_sync = time.perf_counter() - t0
     print(f"rep {rep}: msda enqueued {t_msda_enq * 1e3:.2f} ms, call returned {t_ret * 1e3:.2f} ms, synchronised {t_sync * 1e3:.2f} ms; "
           f"GPU: msda done {e0.elapsed_time(em):.2f} ms, all done {e0.elapsed_time(e1):.2f} ms")
-    for (c0, c1, a, b), (c, w0, w1) in zip(ev, host):
-        print(f"   chunk {c0:2d}..{c1:2d}: host waited for pack {(w0 - t0) * 1e3:.2f} -> {(w1 - t0) * 1e3:.2f} ms; "
-              f"GPU kernels {e0.elapsed_time(a):.2f} -> {e0.elapsed_time(b):.2f} ms")
+    for key, a, b in ev:
+        print(f"   graph {str(key):10s}: GPU {e0.elapsed_time(a):.2f} -> {e0.elapsed_time(b):.2f} ms")
+    for c, w0, w1 in host:
+        print(f"   pack chunk {c}: host waited {(w0 - t0) * 1e3:.2f} -> {(w1 - t0) * 1e3:.2f} ms")
