@@ -66,6 +66,12 @@ size_t quber_encode_workspace_bytes(int B, int K, int H, int W);
 int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int sigma,
                                const float *gauss, float *out, void *workspace, size_t workspace_bytes,
                                void *stream);
+/* The same from bit-packed masks (quber_host_pack_masks): packed dev uint32 [B*K*H*W / 32], set pixels carry `value`
+ * (1..255).  Also writes the byte planes masks_out dev [B,K,H,W] uint8 (0 / value) — what quber_unpack_masks would give —
+ * for quber_mask_boundary, so the expansion costs no pass of its own. */
+int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t *masks_out, int B, int K, int H, int W,
+                                      int sigma, const float *gauss, float *out, void *workspace, size_t workspace_bytes,
+                                      void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K2  boundary extraction by erosion — replaces mask_to_boundary / masks_to_boundary /

@@ -23,9 +23,13 @@ constexpr uint8_t E_NONE = 0xff;
 
 struct EncSums { unsigned long long n, sy, sx; };
 
+// PACKED: `masks` holds one bit per pixel (quber_host_pack_masks: bit i of word w = pixel 32 w + i of the flattened
+// [B,K,H,W] array) and the kernel also writes the byte planes (0 / value) to `unpacked` for the boundary kernel — the
+// expansion rides on the pass that reads every plane anyway instead of costing a kernel of its own.
+template <bool PACKED>
 __global__ void __launch_bounds__(E_THREADS)
 encode_reduce_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, EncSums *__restrict__ sums,
-                     uint8_t *__restrict__ lastk) {
+                     uint8_t *__restrict__ lastk, uint8_t *__restrict__ unpacked, uint32_t value) {
     extern __shared__ unsigned int acc[];   // [K][3]
     const int tid = threadIdx.x, b = blockIdx.z;
     for (int i = tid; i < 3 * K; i += E_THREADS) acc[i] = 0;
@@ -35,7 +39,8 @@ encode_reduce_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, Enc
     const size_t HW = (size_t)H * W;
     const size_t pix = (size_t)y * W + x0;
     uint32_t last_lo = 0xffffffffu, last_hi = 0xffffffffu;   // packed per-pixel last k
-    const uint8_t *base = masks + (size_t)b * K * HW + pix;
+    const size_t plane0 = (size_t)b * K * HW + pix;                  // pixel index of this thread's 8 pixels in plane 0
+    const uint8_t *base = masks + (PACKED ? plane0 / 8 : plane0);   // PACKED: one byte = these 8 pixels (pix % 8 == 0)
     constexpr int PF = 4;                   // planes fetched together: the streaming loads are the only latency here
     uint2 vbuf[PF];
     for (int k = 0; k < K; ++k) {
@@ -43,7 +48,17 @@ encode_reduce_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, Enc
 #pragma unroll
             for (int j = 0; j < PF; ++j) {
                 vbuf[j] = make_uint2(0, 0);
-                if (inb && k + j < K) vbuf[j] = ld_stream_u2(base + (size_t)(k + j) * HW);
+                if (inb && k + j < K) {
+                    if (PACKED) {
+                        const uint32_t bits = __ldg(base + (size_t)(k + j) * (HW / 8));
+                        // four bits -> the low bit of four bytes (multiply puts bit i at 7 i + i, the mask keeps bit 8 i)
+                        vbuf[j] = make_uint2((((bits & 0xfu) * 0x00204081u) & 0x01010101u) * value,
+                                             (((bits >> 4) * 0x00204081u) & 0x01010101u) * value);
+                        st_stream_u2(unpacked + plane0 + (size_t)(k + j) * HW, vbuf[j]);
+                    } else {
+                        vbuf[j] = ld_stream_u2(base + (size_t)(k + j) * HW);
+                    }
+                }
             }
         }
         uint2 v = vbuf[0];
@@ -171,11 +186,13 @@ extern "C" size_t quber_encode_workspace_bytes(int B, int K, int H, int W) {
     return quber::align_up((size_t)B * K * sizeof(quber::EncSums), 256) + quber::align_up((size_t)B * H * W, 256);
 }
 
-extern "C" int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int sigma, const float *gauss,
-                                          float *out, void *workspace, size_t workspace_bytes, void *stream) {
+static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *unpacked, int B, int K, int H, int W, int sigma,
+                         const float *gauss, float *out, void *workspace, size_t workspace_bytes, void *stream) {
     using namespace quber;
     if (!masks || !gauss || !out || B <= 0 || K <= 0 || K > 254 || H <= 0 || W <= 0 || sigma < 1) return QUBER_E_INVALID;
-    if (W % 16 != 0 || !aligned16(masks) || !aligned16(out)) return QUBER_E_ALIGN;
+    if (W % 16 != 0 || !aligned16(out) || (reinterpret_cast<uintptr_t>(masks) & (packed ? 3u : 15u))) return QUBER_E_ALIGN;
+    if (packed && (!unpacked || value < 1 || value > 255)) return QUBER_E_INVALID;
+    if (packed && !aligned16(unpacked)) return QUBER_E_ALIGN;
     if (!workspace || workspace_bytes < quber_encode_workspace_bytes(B, K, H, W) || !aligned16(workspace)) return QUBER_E_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     EncSums *sums = reinterpret_cast<EncSums *>(workspace);
@@ -183,8 +200,23 @@ extern "C" int quber_encode_initial_masks(const uint8_t *masks, int B, int K, in
     uint8_t *lastk = reinterpret_cast<uint8_t *>(workspace) + sums_bytes;
     QUBER_CUDA_TRY(cudaMemsetAsync(sums, 0, sums_bytes, st));
     dim3 grid(cdiv(W, E_TW), cdiv(H, E_TH), B);
-    encode_reduce_kernel<<<grid, E_THREADS, 3 * K * sizeof(unsigned), st>>>(masks, K, H, W, sums, lastk);
+    if (packed)
+        encode_reduce_kernel<true><<<grid, E_THREADS, 3 * K * sizeof(unsigned), st>>>(masks, K, H, W, sums, lastk, unpacked, (uint32_t)value);
+    else
+        encode_reduce_kernel<false><<<grid, E_THREADS, 3 * K * sizeof(unsigned), st>>>(masks, K, H, W, sums, lastk, nullptr, 0u);
     if (int rc = check_launch("encode_reduce_kernel")) return rc;
     encode_emit_kernel<<<grid, E_THREADS, K * (sizeof(EncCentre) + sizeof(int)), st>>>(sums, lastk, K, H, W, sigma, gauss, out);
     return check_launch("encode_emit_kernel");
+}
+
+extern "C" int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int sigma, const float *gauss,
+                                          float *out, void *workspace, size_t workspace_bytes, void *stream) {
+    return encode_launch(masks, false, 0, nullptr, B, K, H, W, sigma, gauss, out, workspace, workspace_bytes, stream);
+}
+
+extern "C" int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t *masks_out, int B, int K, int H, int W,
+                                                 int sigma, const float *gauss, float *out, void *workspace,
+                                                 size_t workspace_bytes, void *stream) {
+    return encode_launch(reinterpret_cast<const uint8_t *>(packed), true, value, masks_out, B, K, H, W, sigma, gauss, out,
+                         workspace, workspace_bytes, stream);
 }

@@ -66,6 +66,25 @@ def encode_initial_masks(masks, sigma=10):
     return out
 
 
+def encode_initial_masks_packed(packed, value, masks_out, sigma=10):
+    """encode_initial_masks from bit-packed masks (host_pack_masks): packed int32 CUDA [B*K*H*W / 32], set pixels carry
+    `value`; masks_out uint8 CUDA [B,K,H,W] receives the byte planes (0 / value) on the way -> [B,3,H,W] float32."""
+    _need_cuda(packed, "packed", torch.int32)
+    _need_cuda(masks_out, "masks_out", torch.uint8)
+    B, K, H, W = masks_out.shape
+    if packed.numel() * 32 != masks_out.numel():
+        raise ValueError("packed words do not match masks_out")
+    L = _lib.lib()
+    out = torch.empty((B, 3, H, W), dtype=torch.float32, device=packed.device)
+    nbytes = L.quber_encode_workspace_bytes(B, K, H, W)
+    ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=packed.device)
+    g = gaussian_table(sigma, packed.device)
+    with torch.cuda.device(packed.device):
+        _lib.check(L.quber_encode_initial_masks_packed(_ptr(packed), int(value), _ptr(masks_out), B, K, H, W, sigma, _ptr(g), _ptr(out),
+                                                       _ptr(ws), nbytes, _stream()), "quber_encode_initial_masks_packed")
+    return out
+
+
 def encode_initial_masks_any_width(masks, sigma=10):
     """encode_initial_masks for frames whose width is not a multiple of 16 (armbench 750x1333): zero columns are
     appended, which changes neither a centroid nor a paste inside the frame; only the x-offset plane is normalised by

@@ -64,6 +64,18 @@ class HotPath:
         per, uni, fg = ops.mask_boundary(masks, d)
         return enc, per, uni, fg
 
+    def encode_and_boundary_packed(self, st, c0, c1, w0, w1, value):
+        """encode_and_boundary for a chunk whose masks arrived bit-packed (refine_batch_host)."""
+        c = self.cfg
+        masks = st["masks"][c0:c1]
+        B, K, H, W = masks.shape
+        if W % 16:                                # the packed encode shares the byte kernel's width rule
+            ops.unpack_masks(st["packed_dev"][w0:w1], masks.shape, value=value, out=masks)
+            return self.encode_and_boundary(masks)
+        enc = ops.encode_initial_masks_packed(st["packed_dev"][w0:w1], value, masks, c.sigma)
+        per, uni, fg = ops.mask_boundary(masks, ops.boundary_dilation(H, W, c.boundary_ratio))
+        return enc, per, uni, fg
+
     def post(self, head):
         c = self.cfg
         B = head["foreground"].shape[0]
@@ -254,9 +266,11 @@ class HotPath:
                     ready = h2d.record_event()
                 st["copied"][(c0, c1)] = ready
                 cur.wait_event(ready)
-                if packed:
-                    ops.unpack_masks(st["packed_dev"][w0:w1], st["masks"][c0:c1].shape, value=value, out=st["masks"][c0:c1])
-                enc, per, uni, fg = self._run_graphed(st, (c0, c1), lambda: self.encode_and_boundary(st["masks"][c0:c1]))
+                if packed:                        # the encode pass expands the bits into the staging bytes on its way
+                    enc, per, uni, fg = self._run_graphed(st, (c0, c1, max(value, 1)),
+                                                          lambda: self.encode_and_boundary_packed(st, c0, c1, w0, w1, max(value, 1)))
+                else:
+                    enc, per, uni, fg = self._run_graphed(st, (c0, c1), lambda: self.encode_and_boundary(st["masks"][c0:c1]))
                 done = cur.record_event()
                 with torch.cuda.stream(d2h):
                     d2h.wait_event(done)

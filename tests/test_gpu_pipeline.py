@@ -94,6 +94,24 @@ def test_refine_batch_host_packed_mask_transfer_is_identical():
         assert torch.equal(ops.unpack_masks(words.cuda(), src.shape, value=value).cpu(), src)
 
 
+@pytest.mark.parametrize("K,value", [(7, 255), (4, 1), (30, 255)])
+def test_encode_from_packed_words_equals_encode_from_bytes(K, value):
+    """quber_encode_initial_masks_packed: same encoding, and the byte planes it writes on the way are the masks."""
+    B, H, W = 3, 240, 320
+    masks = np.stack([synth.ellipse_masks(K, H, W, seed=70 + b, axes=(14, 60), margin=20, empty_tail=1 if K > 4 else 0) for b in range(B)])
+    masks = ((masks != 0) * value).astype(np.uint8)
+    hm = torch.from_numpy(masks)
+    words, v = ops.host_pack_masks(hm)
+    assert v == value
+    out_masks = torch.full(hm.shape, 77, dtype=torch.uint8, device="cuda")
+    enc = ops.encode_initial_masks_packed(words.cuda(), v, out_masks)
+    assert torch.equal(out_masks.cpu(), hm)
+    assert torch.equal(enc, ops.encode_initial_masks(hm.cuda()))
+    np.testing.assert_array_equal(enc[1].cpu().numpy(), oracle.encode_initial_masks(masks[1]))
+    with pytest.raises(ValueError):
+        ops.encode_initial_masks_packed(words.cuda()[:-1], v, out_masks)
+
+
 def test_refine_batch_host_full_size_c2_packed_graphs_equal_resident():
     """BASELINE.json C2 shape (32 frames 640x480, 30 masks of 0/255) through the call bench.py times — packed transfer,
     one CUDA graph per chunk, 16 + 8 + 8 frames — against the resident path on the same inputs, twice (graph replays)."""
