@@ -158,7 +158,9 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    hp = HotPath(RefinerConfig(), dev)
+    # label maps leave the emit kernel as uint8 (at most top_k = 200 ids per frame; QUBER_POST_LABEL_U8): 9.8 MB per step
+    # instead of 39 MB to write, to all-gather and to send to the host
+    hp = HotPath(RefinerConfig(compact_label_map=os.environ.get("QUBER_LABEL_U8", "1") == "1"), dev)
 
     sets = []
     for s in range(NSETS):
@@ -167,8 +169,7 @@ def run_ours(args):
         hh = {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}
         sets.append(dict(h_masks=hm, h_head=hh, masks=hm.to(dev), head={k: v.to(dev) for k, v in hh.items()},
                          msda={k: torch.from_numpy(v).to(dev) for k, v in msda.items()}))
-    # label maps travel as uint8 (at most max_instances_per_image = 64 ids per frame): 9.8 MB per rank instead of 39 MB
-    compact = hp.cfg.max_instances_per_image <= 255
+    compact = hp.cfg.max_instances_per_image <= 255          # int32 maps (QUBER_LABEL_U8=0) are narrowed before the gather
     gather_buf = torch.empty((world, B, H, W), dtype=torch.uint8 if compact else torch.int32, device=dev) if world > 1 else None
     side = torch.cuda.Stream(device=dev) if world > 1 else None
 
@@ -253,6 +254,9 @@ def run_ours(args):
     # half speed) 8 / 2 gave 5.0 ms where 16 / 8 gave 7.1 ms, so the fine schedule is the default.
     E2E_CHUNK = int(os.environ.get("QUBER_E2E_CHUNK", "8"))
     E2E_TAIL = int(os.environ.get("QUBER_E2E_TAIL", "2"))
+    # encode / boundary kernels once per group of chunks holding this many frames (0 = per chunk): the masks still cross
+    # the link chunk by chunk behind the packing, the kernels run on full grids after the sampling kernels
+    E2E_KERNEL = int(os.environ.get("QUBER_E2E_KERNEL_FRAMES", "0"))
     def e2e_step(s):
         d = sets[s % NSETS]
         # decoder activations never live on the host (resident inputs); launched first so the sampling kernels run
@@ -260,7 +264,7 @@ def run_ours(args):
         # pipeline on a second, high-priority stream next to the sampling kernels was measured: 4.36-4.46 against
         # 4.43-4.47 ms per step — the sampling kernels fill the register files, the two only time-share.)
         hp.msda_layers(d["msda"], N_LAYERS)
-        o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL)
+        o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL, kernel_frames=E2E_KERNEL)
         if world > 1:
             sharding.gather_label_maps(keep[0][2]["label_map"], torch.cat([k[4] for k in keep]), out=gather_buf, compact=compact)
         return o
@@ -337,7 +341,9 @@ def run_ours(args):
                 "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps, "host_link": pcie,
                 "mask_transfer": ("one bit per pixel, packed on %d host threads inside the timed region" % hp.pack_threads) if packed
                                  else "bytes",
-                "pack_calibration": getattr(hp, "pack_calibration", None)},
+                "pack_calibration": getattr(hp, "pack_calibration", None),
+                "schedule": {"chunk_frames": E2E_CHUNK, "min_tail": E2E_TAIL, "kernel_frames": E2E_KERNEL,
+                             "label_map": "uint8" if hp.cfg.compact_label_map else "int32"}},
         "gpu_launches": launches,
         "instances_per_step": n_inst_total / args.steps, "post_status": status,
         "stage_ms": per_stage,

@@ -129,6 +129,10 @@ typedef struct quber_post_params {
 /* find_instance_center(top_k=None) (post_processing.py:36-37): every positive NMS survivor is a
  * centre; top_k is then only the capacity of centers_yx (status bit 2 is set if it overflowed) */
 #define QUBER_POST_NO_TOPK 2
+/* label_map points to uint8 [B,H,W] instead of int32: a quarter of the bytes to write, to send to the
+ * host and to all-gather.  Needs top_k <= 255 (an image never has more instances than centres), else
+ * QUBER_E_INVALID. */
+#define QUBER_POST_LABEL_U8 4
 
 typedef struct quber_post_io {
     /* inputs, dev float32; low resolution [B,C,H/scale,W/scale] */
@@ -141,7 +145,8 @@ typedef struct quber_post_io {
     float *eee_full;         /* opt [B,C,H,W]  up-sampled error logits ("eee_boundary") */
     uint8_t *eee_onehot;     /* opt [B,C,H,W]  argmax one-hot (TP,TN,FP,FN) */
     float *panoptic;         /* opt [B,H,W]    void_label / label_divisor (+ running id) */
-    int32_t *label_map;      /* opt [B,H,W]    0 = void, j+1 = j-th instance of the image (collective payload) */
+    void *label_map;         /* opt [B,H,W] int32 (uint8 with QUBER_POST_LABEL_U8)  0 = void, j+1 = j-th instance of
+                                the image (collective payload) */
     int32_t *ins_seg;        /* opt [B,H,W]    foreground * grouped centre id (get_instance_segmentation, :107) */
     uint8_t *masks;          /* opt [max_instances,H,W] 0/1, images back to back (inst_offsets) */
     int32_t *centers_yx;     /* req [B,top_k,2] */

@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libquber_b200.so")
 
 QUBER_OK, E_INVALID, E_WORKSPACE, E_CUDA, E_ALIGN, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5
-POST_GIVEN_CENTERS, POST_NO_TOPK = 1, 2
+POST_GIVEN_CENTERS, POST_NO_TOPK, POST_LABEL_U8 = 1, 2, 4
 
 c_vp, c_i, c_sz, c_f, c_d = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_float, ctypes.c_double
 

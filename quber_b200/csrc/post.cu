@@ -593,8 +593,16 @@ emit_kernel(quber_post_params p, quber_post_io io, const uint16_t *__restrict__ 
             st_stream_f4(o, make_float4(pv[0], pv[1], pv[2], pv[3]));
             st_stream_f4(o + 4, make_float4(pv[4], pv[5], pv[6], pv[7]));
         }
-        if (io.label_map) {
-            int32_t *o = io.label_map + (size_t)b * HW + pix;
+        if (io.label_map && (p.flags & QUBER_POST_LABEL_U8)) {               // ids <= top_k <= 255 (post_validate)
+            uint32_t lo = 0, hi = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                lo |= (uint32_t)(idx[j] + 1) << (8 * j);
+                hi |= (uint32_t)(idx[4 + j] + 1) << (8 * j);
+            }
+            st_stream_u2(static_cast<uint8_t *>(io.label_map) + (size_t)b * HW + pix, make_uint2(lo, hi));
+        } else if (io.label_map) {
+            int32_t *o = static_cast<int32_t *>(io.label_map) + (size_t)b * HW + pix;
             st_stream_u4(o, make_uint4(idx[0] + 1, idx[1] + 1, idx[2] + 1, idx[3] + 1));
             st_stream_u4(o + 4, make_uint4(idx[4] + 1, idx[5] + 1, idx[6] + 1, idx[7] + 1));
         }
@@ -807,7 +815,8 @@ static int post_validate(const quber_post_params *p) {
     if (!p) return QUBER_E_INVALID;
     if (p->B <= 0 || p->H <= 0 || p->W <= 0 || p->scale < 1 || p->top_k < 1 || p->top_k > 1024 ||
         p->nms_kernel < 1 || p->nms_kernel > 15 || (p->nms_kernel & 1) == 0 || p->max_instances < 0 ||
-        (p->eee_channels != 0 && (p->eee_channels < 2 || p->eee_channels > 4)))
+        (p->eee_channels != 0 && (p->eee_channels < 2 || p->eee_channels > 4)) ||
+        ((p->flags & QUBER_POST_LABEL_U8) && p->top_k > 255))
         return QUBER_E_INVALID;
     if (p->W % 8 != 0 || p->H % p->scale != 0 || p->W % p->scale != 0) return QUBER_E_UNSUPPORTED;
     return QUBER_OK;

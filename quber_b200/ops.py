@@ -129,14 +129,19 @@ def quadruple_maps(gt, pred):
 def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=None, threshold=0.3, nms_kernel=7,
                  top_k=200, min_area=512, stuff_area=2048, label_divisor=1000, void_label=-1.0, max_instances=None,
                  want=("sem_seg", "eee_full", "eee_onehot", "panoptic", "label_map", "masks"), centers=None,
-                 n_centers=None, no_topk=False):
+                 n_centers=None, no_topk=False, label_dtype=torch.int32):
     """One fused call for model.py:689-708 + :260-356 + post_processing.py:9-221 + eval_utils.py:308-328.
 
     foreground [B,1,h,w], center [B,1,h,w], offset [B,2,h,w], eee [B,C,h,w] float32 CUDA tensors at
     1/scale resolution (scale=1: full-resolution maps).  Returns a dict of device tensors; nothing is
-    synchronised or copied to the host.
+    synchronised or copied to the host.  label_dtype=torch.uint8 (QUBER_POST_LABEL_U8, needs top_k <= 255) makes
+    `label_map` a byte map: a quarter of the bytes to write, to send to the host and to all-gather.
     """
     _need_cuda(foreground, "foreground", torch.float32)
+    if label_dtype not in (torch.int32, torch.uint8):
+        raise ValueError("label_dtype must be torch.int32 or torch.uint8")
+    if label_dtype == torch.uint8 and top_k > 255:
+        raise ValueError("a uint8 label map needs top_k <= 255")
     _need_cuda(center, "center", torch.float32)
     _need_cuda(offset, "offset", torch.float32)
     if center.dim() != 4 or foreground.dim() != 4:
@@ -164,7 +169,9 @@ def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=No
     eee_full = mk("eee_full", (B, C, H, W), f32) if C else None
     onehot = mk("eee_onehot", (B, C, H, W), u8) if C else None
     pan = mk("panoptic", (B, H, W), f32)
-    lmap = mk("label_map", (B, H, W), i32)
+    lmap = mk("label_map", (B, H, W), label_dtype)
+    if lmap is not None and label_dtype == u8:
+        flags |= _lib.POST_LABEL_U8
     iseg = mk("ins_seg", (B, H, W), i32)
     masks = mk("masks", (max(max_instances, 1), H, W), u8)
     if centers is not None:

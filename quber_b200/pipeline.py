@@ -38,6 +38,7 @@ class RefinerConfig:
     sigma: int = 10                    # predictor.py:246
     boundary_ratio: float = 0.01       # masks_to_boundary default (util.py:92)
     max_instances_per_image: int = 64
+    compact_label_map: bool = False    # label maps as uint8 (QUBER_POST_LABEL_U8; needs top_k <= 255): 1/4 of the bytes
     want: tuple = ("label_map", "masks", "eee_onehot")
 
 
@@ -82,7 +83,8 @@ class HotPath:
         return ops.post_process(head["foreground"], head["center"], head["offset"], head.get("eee_boundary"),
                                 scale=c.common_stride, threshold=c.center_threshold, nms_kernel=c.nms_kernel,
                                 top_k=c.top_k, min_area=c.min_area, stuff_area=c.stuff_area,
-                                label_divisor=c.label_divisor, max_instances=B * c.max_instances_per_image, want=c.want)
+                                label_divisor=c.label_divisor, max_instances=B * c.max_instances_per_image, want=c.want,
+                                label_dtype=torch.uint8 if c.compact_label_map and c.top_k <= 255 else torch.int32)
 
     def msda_layers(self, msda, n_layers=6):
         out = None
@@ -96,7 +98,8 @@ class HotPath:
     # --- end to end: host buffers in, host results out ------------------------------------------
     def _staging(self, masks_host, head_host):
         """Persistent device staging buffers, pinned result buffers, copy streams and events, keyed by shape."""
-        key = (tuple(masks_host.shape),) + tuple((k, tuple(v.shape)) for k, v in sorted(head_host.items()))
+        ldt = torch.uint8 if self.cfg.compact_label_map and self.cfg.top_k <= 255 else torch.int32
+        key = (tuple(masks_host.shape), ldt) + tuple((k, tuple(v.shape)) for k, v in sorted(head_host.items()))
         st = getattr(self, "_stage", None)
         if st is None or st["key"] != key:
             dev = self.device
@@ -109,7 +112,7 @@ class HotPath:
                       packed_host=pin((masks_host.numel() + 31) // 32, torch.int32),
                       packed_dev=torch.empty((masks_host.numel() + 31) // 32, dtype=torch.int32, device=dev), copied={},
                       graphs={},
-                      out=dict(label_map=pin((B, H, W), torch.int32), boundary=pin((B, H, W), torch.uint8),
+                      out=dict(label_map=pin((B, H, W), ldt), boundary=pin((B, H, W), torch.uint8),
                                inst_start=pin((B,), torch.int32), inst_counts=pin((B,), torch.int32),
                                labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
                                boxes=pin((B * slab, 4), torch.float32)))
@@ -188,7 +191,7 @@ class HotPath:
                 c0 += n
         return out
 
-    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2):
+    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2, kernel_frames=0):
         """The end-to-end call: host buffers in, host results out.
 
         masks_host: pinned uint8 [B,K,H,W]; head_host: dict of pinned float32 head outputs (what the
@@ -201,7 +204,10 @@ class HotPath:
         form of the reference's pred_masks), boundary [B,H,W] uint8 (union boundary of the initial
         masks), inst_start / inst_counts [B] int32 (frame b's instances are rows inst_start[b] ... +inst_counts[b]
         of labels / scores / boxes).  Post-processing runs once for the whole batch as soon as the head outputs have
-        arrived; the chunks carry the masks (encode, boundaries).  `keep` = per chunk (encoding, per-instance boundaries,
+        arrived; the chunks carry the masks (encode, boundaries).  `kernel_frames` > 0 decouples the two granularities:
+        the masks still cross the link chunk by chunk (fine chunks keep the copies right behind the packing), but encode /
+        boundary kernels are launched once per group of consecutive chunks holding at least `kernel_frames` frames — full
+        grids and one graph launch instead of one small launch sequence per chunk.  `keep` = per kernel group (encoding, per-instance boundaries,
         the batch's post-processing result, inst_start slice, inst_counts slice).
         The host tensors are pinned and reused between calls; they are valid once the caller has synchronised
         the current stream (which this call makes wait for both copy streams).
@@ -252,6 +258,7 @@ class HotPath:
                 out["labels"].copy_(r["labels"][:B * slab], non_blocking=True)
                 out["scores"].copy_(r["scores"][:B * slab], non_blocking=True)
                 out["boxes"].copy_(r["boxes"][:B * slab], non_blocking=True)
+            pend = []                                 # chunks copied but not yet processed: (c0, c1, packed, value)
             for ci, (c0, c1) in enumerate(sched):
                 packed, value = False, -1
                 if pack:
@@ -265,17 +272,28 @@ class HotPath:
                         st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
                     ready = h2d.record_event()
                 st["copied"][(c0, c1)] = ready
-                cur.wait_event(ready)
-                if packed:                        # the encode pass expands the bits into the staging bytes on its way
-                    enc, per, uni, fg = self._run_graphed(st, (c0, c1, max(value, 1)),
-                                                          lambda: self.encode_and_boundary_packed(st, c0, c1, w0, w1, max(value, 1)))
+                pend.append((c0, c1, packed, max(value, 1)))
+                if ci + 1 < len(sched) and kernel_frames and pend[-1][1] - pend[0][0] < kernel_frames:
+                    continue                      # copy-only chunk: its kernels run with the following ones
+                cur.wait_event(ready)             # the copies are in stream order: this one covers the whole group
+                if len({(pk, v) for _, _, pk, v in pend}) > 1:
+                    groups = [[q] for q in pend]  # mixed routes / values inside the group: chunk by chunk
                 else:
-                    enc, per, uni, fg = self._run_graphed(st, (c0, c1), lambda: self.encode_and_boundary(st["masks"][c0:c1]))
-                done = cur.record_event()
-                with torch.cuda.stream(d2h):
-                    d2h.wait_event(done)
-                    out["boundary"][c0:c1].copy_(uni, non_blocking=True)
-                keep.append((enc, per, r, start[c0:c1], counts[c0:c1]))
+                    groups = [pend]
+                for grp in groups:
+                    g0, g1, pk, v = grp[0][0], grp[-1][1], grp[0][2], grp[0][3]
+                    if pk:                        # the encode pass expands the bits into the staging bytes on its way
+                        enc, per, uni, fg = self._run_graphed(
+                            st, (g0, g1, v), lambda: self.encode_and_boundary_packed(
+                                st, g0, g1, g0 * frame_bytes // 32, g1 * frame_bytes // 32, v))
+                    else:
+                        enc, per, uni, fg = self._run_graphed(st, (g0, g1), lambda: self.encode_and_boundary(st["masks"][g0:g1]))
+                    done = cur.record_event()
+                    with torch.cuda.stream(d2h):
+                        d2h.wait_event(done)
+                        out["boundary"][g0:g1].copy_(uni, non_blocking=True)
+                    keep.append((enc, per, r, start[g0:g1], counts[g0:g1]))
+                pend = []
         except BaseException:
             if pack:
                 for c in range(len(sched)):           # the pool must not go on reading the caller's buffers

@@ -233,3 +233,61 @@ def test_refiner_model_adapter_filters_like_the_reference():
         assert keep.sum() == 4 and got.dtype == bool
         assert np.array_equal(got, ref), dataset
         assert "instances" in output and secs >= 0
+
+
+def test_post_process_uint8_label_map_equals_int32():
+    """QUBER_POST_LABEL_U8: the emit kernel writes the same ids as bytes; more than 255 possible ids is refused."""
+    masks, head = _inputs(3, 9, 240, 320, seed=510)
+    h = {k: torch.from_numpy(v).cuda() for k, v in head.items()}
+    a = ops.post_process(h["foreground"], h["center"], h["offset"], h["eee_boundary"], want=("label_map", "masks"))
+    b = ops.post_process(h["foreground"], h["center"], h["offset"], h["eee_boundary"], want=("label_map", "masks"),
+                         label_dtype=torch.uint8)
+    assert b["label_map"].dtype == torch.uint8 and a["label_map"].dtype == torch.int32
+    assert int(a["label_map"].max()) > 0
+    assert torch.equal(a["label_map"], b["label_map"].to(torch.int32))
+    for key in ("masks", "labels", "scores", "boxes", "inst_offsets"):
+        n = int(a["inst_offsets"][-1])
+        assert torch.equal(a[key][:n] if key != "inst_offsets" else a[key], b[key][:n] if key != "inst_offsets" else b[key]), key
+    with pytest.raises(ValueError):
+        ops.post_process(h["foreground"], h["center"], h["offset"], None, top_k=256, label_dtype=torch.uint8)
+
+
+@pytest.mark.parametrize("B,chunk,tail,kf,sizes", [(7, 2, 1, 4, [4, 3]), (7, 2, 1, 100, [7]), (6, 4, 2, 0, [4, 2])])
+def test_refine_batch_host_kernel_groups_and_uint8_label_map(B, chunk, tail, kf, sizes):
+    """kernel_frames: the masks cross the link chunk by chunk, encode / boundary run once per group of chunks; with
+    compact_label_map the host label map is uint8.  Same results as the per-chunk int32 call, packed or not; a group whose
+    chunks took different routes (one of them carries two mask values) falls back to chunk-by-chunk launches."""
+    K, H, W = 6, 240, 320
+    masks, head = _inputs(B, K, H, W, seed=620)
+    hm = torch.from_numpy(masks).pin_memory()
+    hh = {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}
+    ref = HotPath(RefinerConfig(), "cuda")
+    ref.pack_masks = False
+    for pack in (False, True):
+        hp = HotPath(RefinerConfig(compact_label_map=True), "cuda")
+        hp.pack_masks = pack
+        for rep in range(3):
+            o1, k1 = hp.refine_batch_host(hm, hh, chunk_frames=chunk, min_tail=tail, kernel_frames=kf)
+            torch.cuda.current_stream().synchronize()
+        o0, k0 = ref.refine_batch_host(hm, hh, chunk_frames=chunk, min_tail=tail)
+        torch.cuda.current_stream().synchronize()
+        assert [k[0].shape[0] for k in k1] == sizes
+        assert o1["label_map"].dtype == torch.uint8 and o0["label_map"].dtype == torch.int32
+        assert torch.equal(o1["label_map"].to(torch.int32), o0["label_map"])
+        for key in ("boundary", "inst_start", "inst_counts"):
+            assert torch.equal(o0[key], o1[key]), key
+        assert torch.equal(torch.cat([k[0] for k in k1]), torch.cat([k[0] for k in k0]))
+        assert torch.equal(torch.cat([k[1] for k in k1]), torch.cat([k[1] for k in k0]))
+        assert torch.equal(hp._stage["masks"], hm.cuda())
+    if kf:
+        hm2 = hm.clone().pin_memory()
+        hm2[1][hm2[1] != 0] = 7                              # chunk (0, 2) now carries two values: byte route for it
+        hp = HotPath(RefinerConfig(compact_label_map=True), "cuda")
+        hp.pack_masks = True
+        o1, k1 = hp.refine_batch_host(hm2, hh, chunk_frames=chunk, min_tail=tail, kernel_frames=kf)
+        o0, k0 = ref.refine_batch_host(hm2, hh, chunk_frames=chunk, min_tail=tail)
+        torch.cuda.current_stream().synchronize()
+        assert sum(k[0].shape[0] for k in k1) == B and len(k1) > len(sizes)
+        assert torch.equal(o0["boundary"], o1["boundary"])
+        assert torch.equal(torch.cat([k[1] for k in k1]), torch.cat([k[1] for k in k0]))
+        assert torch.equal(hp._stage["masks"], hm2.cuda())
