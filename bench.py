@@ -255,8 +255,9 @@ def run_ours(args):
     E2E_CHUNK = int(os.environ.get("QUBER_E2E_CHUNK", "8"))
     E2E_TAIL = int(os.environ.get("QUBER_E2E_TAIL", "2"))
     # encode / boundary kernels once per group of chunks holding this many frames (0 = per chunk): the masks still cross
-    # the link chunk by chunk behind the packing, the kernels run on full grids after the sampling kernels
-    E2E_KERNEL = int(os.environ.get("QUBER_E2E_KERNEL_FRAMES", "0"))
+    # the link chunk by chunk behind the packing, the kernels run on full grids after the sampling kernels.  v16 sweep
+    # (profiles/r01_e2e_sweep_v16.txt): 0 -> 3.98, 16 -> 3.86, 32 -> 3.92 ms per step
+    E2E_KERNEL = int(os.environ.get("QUBER_E2E_KERNEL_FRAMES", "16"))
     def e2e_step(s):
         d = sets[s % NSETS]
         # decoder activations never live on the host (resident inputs); launched first so the sampling kernels run
