@@ -104,7 +104,11 @@ encode_reduce_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, Enc
 
 struct EncCentre { double cy, cx; int uly, ulx; };
 
-__global__ void __launch_bounds__(E_THREADS)
+// EARLY: the last-mask bytes of this thread's pixels are requested before the per-CTA centre set-up, so that their
+// DRAM latency runs under the set-up (sums load, float64 divisions, barrier) instead of after the paste loop; MINB =
+// resident CTAs per SM asked of the compiler (QUBER_ENCODE_EMIT=0|1|2 selects old / early / early + 5 CTAs for A/B runs).
+template <bool EARLY, int MINB>
+__global__ void __launch_bounds__(E_THREADS, MINB)
 encode_emit_kernel(const EncSums *__restrict__ sums, const uint8_t *__restrict__ lastk, int K, int H, int W, int sigma,
                    const float *__restrict__ gauss, float *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char smraw[];
@@ -114,6 +118,11 @@ encode_emit_kernel(const EncSums *__restrict__ sums, const uint8_t *__restrict__
     const int tid = threadIdx.x, b = blockIdx.z;
     const int gs = 6 * sigma + 3, half = 3 * sigma + 1;
     const int ty0 = blockIdx.y * E_TH, tx0 = blockIdx.x * E_TW;
+    const int y = ty0 + (tid >> 4), x0 = tx0 + (tid & 15) * 8;
+    const size_t HW = (size_t)H * W, pix = (size_t)y * W + x0;
+    const bool inside = y < H && x0 < W;
+    uint2 lk = make_uint2(0u, 0u);
+    if (EARLY && inside) lk = ld_stream_u2(lastk + (size_t)b * HW + pix);
     if (tid == 0) nlist = 0;
     __syncthreads();
     for (int k = tid; k < K; k += E_THREADS) {
@@ -131,9 +140,7 @@ encode_emit_kernel(const EncSums *__restrict__ sums, const uint8_t *__restrict__
         ctr[k] = c;
     }
     __syncthreads();
-    const int y = ty0 + (tid >> 4), x0 = tx0 + (tid & 15) * 8;
-    if (y >= H || x0 >= W) return;
-    const size_t HW = (size_t)H * W, pix = (size_t)y * W + x0;
+    if (!inside) return;
     float cen[8], oy[8], ox[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) cen[j] = 0.f;
@@ -149,7 +156,7 @@ encode_emit_kernel(const EncSums *__restrict__ sums, const uint8_t *__restrict__
             if ((unsigned)gx < (unsigned)gs) cen[j] = fmaxf(cen[j], __ldg(grow + gx));
         }
     }
-    const uint2 lk = *reinterpret_cast<const uint2 *>(lastk + (size_t)b * HW + pix);
+    if (!EARLY) lk = *reinterpret_cast<const uint2 *>(lastk + (size_t)b * HW + pix);
     const double dH = (double)H, dW = (double)W;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -205,7 +212,11 @@ static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *
     else
         encode_reduce_kernel<false><<<grid, E_THREADS, 3 * K * sizeof(unsigned), st>>>(masks, K, H, W, sums, lastk, nullptr, 0u);
     if (int rc = check_launch("encode_reduce_kernel")) return rc;
-    encode_emit_kernel<<<grid, E_THREADS, K * (sizeof(EncCentre) + sizeof(int)), st>>>(sums, lastk, K, H, W, sigma, gauss, out);
+    static const char emit_mode = [] { const char *e = getenv("QUBER_ENCODE_EMIT"); return e ? e[0] : '1'; }();
+    const size_t esm = K * (sizeof(EncCentre) + sizeof(int));
+    if (emit_mode == '0') encode_emit_kernel<false, 4><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, sigma, gauss, out);
+    else if (emit_mode == '2') encode_emit_kernel<true, 5><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, sigma, gauss, out);
+    else encode_emit_kernel<true, 4><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, sigma, gauss, out);
     return check_launch("encode_emit_kernel");
 }
 
