@@ -102,6 +102,91 @@ encode_reduce_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, Enc
         }
 }
 
+// Same pass with the plane loop unrolled by the fetch group (no per-plane select of the fetched word), the three warp
+// sums as redux.sync adds instead of shuffle trees, and — DB — the next group's loads issued before the current group
+// is processed.  Integer arithmetic throughout, so the sums and the last-mask map are identical to the kernel above
+// (QUBER_ENCODE_REDUCE=0 old | 1 unrolled | 2 unrolled + double-buffered, for A/B runs).
+template <bool PACKED, bool DB>
+__global__ void __launch_bounds__(E_THREADS)
+encode_reduce_unrolled_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, EncSums *__restrict__ sums,
+                              uint8_t *__restrict__ lastk, uint8_t *__restrict__ unpacked, uint32_t value) {
+    extern __shared__ unsigned int acc[];   // [K][3]
+    const int tid = threadIdx.x, b = blockIdx.z;
+    for (int i = tid; i < 3 * K; i += E_THREADS) acc[i] = 0;
+    __syncthreads();
+    const int y = blockIdx.y * E_TH + (tid >> 4), x0 = blockIdx.x * E_TW + (tid & 15) * 8;
+    const bool inb = y < H && x0 < W;
+    const size_t HW = (size_t)H * W;
+    const size_t pix = (size_t)y * W + x0;
+    uint32_t last_lo = 0xffffffffu, last_hi = 0xffffffffu;
+    const size_t plane0 = (size_t)b * K * HW + pix;
+    const uint8_t *base = masks + (PACKED ? plane0 / 8 : plane0);
+    constexpr int PF = 4;
+    auto fetch = [&](int k) -> uint2 {
+        uint2 v = make_uint2(0, 0);
+        if (inb && k < K) {
+            if (PACKED) {
+                const uint32_t bits = __ldg(base + (size_t)k * (HW / 8));
+                v = make_uint2((((bits & 0xfu) * 0x00204081u) & 0x01010101u) * value,
+                               (((bits >> 4) * 0x00204081u) & 0x01010101u) * value);
+                st_stream_u2(unpacked + plane0 + (size_t)k * HW, v);
+            } else {
+                v = ld_stream_u2(base + (size_t)k * HW);
+            }
+        }
+        return v;
+    };
+    auto process = [&](int k, uint2 v) {
+        const bool nz = (v.x | v.y) != 0;
+        if (!__any_sync(0xffffffffu, nz)) return;
+        unsigned n = 0, sx = 0;
+        if (nz) {
+            const uint32_t mlo = __vcmpne4(v.x, 0u), mhi = __vcmpne4(v.y, 0u);
+            const uint32_t kk = (uint32_t)k * 0x01010101u;
+            last_lo = (last_lo & ~mlo) | (kk & mlo);
+            last_hi = (last_hi & ~mhi) | (kk & mhi);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const unsigned a = (mlo >> (8 * j)) & 1u, c = (mhi >> (8 * j)) & 1u;
+                n += a + c;
+                sx += a * (unsigned)(x0 + j) + c * (unsigned)(x0 + 4 + j);
+            }
+        }
+        unsigned sy = n * (unsigned)y;
+        n = __reduce_add_sync(0xffffffffu, n);
+        sy = __reduce_add_sync(0xffffffffu, sy);
+        sx = __reduce_add_sync(0xffffffffu, sx);
+        if ((tid & 31) == 0) {
+            atomicAdd(&acc[3 * k], n); atomicAdd(&acc[3 * k + 1], sy); atomicAdd(&acc[3 * k + 2], sx);
+        }
+    };
+    uint2 nxt[PF];
+    if (DB) {
+#pragma unroll
+        for (int j = 0; j < PF; ++j) nxt[j] = fetch(j);
+    }
+    for (int k0 = 0; k0 < K; k0 += PF) {
+        uint2 cur[PF];
+#pragma unroll
+        for (int j = 0; j < PF; ++j) cur[j] = DB ? nxt[j] : fetch(k0 + j);
+        if (DB) {
+#pragma unroll
+            for (int j = 0; j < PF; ++j) nxt[j] = fetch(k0 + PF + j);
+        }
+#pragma unroll
+        for (int j = 0; j < PF; ++j) process(k0 + j, cur[j]);    // planes past K were fetched as zeros: skipped by the vote
+    }
+    if (inb) st_stream_u2(lastk + (size_t)b * HW + pix, make_uint2(last_lo, last_hi));
+    __syncthreads();
+    for (int k = tid; k < K; k += E_THREADS)
+        if (acc[3 * k]) {
+            EncSums *s = sums + (size_t)b * K + k;
+            atomicAdd(&s->n, (unsigned long long)acc[3 * k]);
+            atomicAdd(&s->sy, (unsigned long long)acc[3 * k + 1]);
+            atomicAdd(&s->sx, (unsigned long long)acc[3 * k + 2]);
+        }
+}
+
 struct EncCentre { double cy, cx; int uly, ulx; };
 
 // EARLY: the last-mask bytes of this thread's pixels are requested before the per-CTA centre set-up, so that their
@@ -207,10 +292,15 @@ static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *
     uint8_t *lastk = reinterpret_cast<uint8_t *>(workspace) + sums_bytes;
     QUBER_CUDA_TRY(cudaMemsetAsync(sums, 0, sums_bytes, st));
     dim3 grid(cdiv(W, E_TW), cdiv(H, E_TH), B);
-    if (packed)
-        encode_reduce_kernel<true><<<grid, E_THREADS, 3 * K * sizeof(unsigned), st>>>(masks, K, H, W, sums, lastk, unpacked, (uint32_t)value);
-    else
-        encode_reduce_kernel<false><<<grid, E_THREADS, 3 * K * sizeof(unsigned), st>>>(masks, K, H, W, sums, lastk, nullptr, 0u);
+    static const char reduce_mode = [] { const char *e = getenv("QUBER_ENCODE_REDUCE"); return e ? e[0] : '1'; }();
+    const size_t rsm = 3 * K * sizeof(unsigned);
+    const uint32_t val = packed ? (uint32_t)value : 0u;
+    uint8_t *unp = packed ? unpacked : nullptr;
+#define QUBER_REDUCE_LAUNCH(KERNEL) KERNEL<<<grid, E_THREADS, rsm, st>>>(masks, K, H, W, sums, lastk, unp, val)
+    if (reduce_mode == '1') { if (packed) QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<true, false>)); else QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<false, false>)); }
+    else if (reduce_mode == '2') { if (packed) QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<true, true>)); else QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<false, true>)); }
+    else { if (packed) QUBER_REDUCE_LAUNCH(encode_reduce_kernel<true>); else QUBER_REDUCE_LAUNCH(encode_reduce_kernel<false>); }
+#undef QUBER_REDUCE_LAUNCH
     if (int rc = check_launch("encode_reduce_kernel")) return rc;
     static const char emit_mode = [] { const char *e = getenv("QUBER_ENCODE_EMIT"); return e ? e[0] : '1'; }();
     const size_t esm = K * (sizeof(EncCentre) + sizeof(int));
