@@ -1,6 +1,7 @@
 #!/bin/bash
 # v17: parity on the defaults (emit kernel with early last-mask load, 3-stage boundary ring), then A/B of
 # QUBER_ENCODE_EMIT (0 old, 1 early, 2 early + 5 CTAs/SM) x QUBER_BOUNDARY_STAGES (2, 3, 4) x QUBER_ENCODE_REDUCE (0 old, 1 unrolled + redux, 2 + double-buffered), then parity on the alternatives.
+# (QUBER_BOUNDARY_STAGES existed only in the experimental boundary kernel of this run: not kept)
 mkdir -p gpurun_out
 timeout 300 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_v17.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu_v17.log; tail -3 gpurun_out/pytest_gpu_v17.log
 : > gpurun_out/ab_v17.txt
