@@ -107,10 +107,148 @@ def ref_msda():
     return load_by_path("ref_msda_func", f"{ops}/functions/ms_deform_attn_func.py")
 
 
-def main():
-    os.makedirs(OUT, exist_ok=True)
-    torch.set_num_threads(1)
+def _method_node(path, cls, meth):
+    src = open(path).read()
+    for node in ast.walk(ast.parse(src)):
+        if isinstance(node, ast.ClassDef) and node.name == cls:
+            for f in node.body:
+                if isinstance(f, ast.FunctionDef) and f.name == meth:
+                    return src, f
+    raise RuntimeError(f"{cls}.{meth} not found in {path}")
 
+
+class _Bag:
+    """Attribute bag standing in for detectron2's `Instances` container (un-vendored): model.py:326-353 only sets
+    attributes on it."""
+    def __init__(self, image_size=None):
+        self.image_size = image_size
+
+
+class _BitMasks:
+    """detectron2/structures/masks.py::BitMasks.get_bounding_boxes (un-vendored, SURVEY Appendix C) — the only
+    restated piece of the instance loop: [x_min, y_min, x_max + 1, y_max + 1] of the set pixels, zeros if empty."""
+    def __init__(self, tensor):
+        self.tensor = tensor
+
+    def get_bounding_boxes(self):
+        boxes = torch.zeros(self.tensor.shape[0], 4, dtype=torch.float32)
+        x_any, y_any = torch.any(self.tensor, dim=1), torch.any(self.tensor, dim=2)
+        for i in range(self.tensor.shape[0]):
+            x, y = torch.where(x_any[i, :])[0], torch.where(y_any[i, :])[0]
+            if len(x) > 0 and len(y) > 0:
+                boxes[i, :] = torch.as_tensor([x[0], y[0], x[-1] + 1, y[-1] + 1], dtype=torch.float32)
+        return boxes
+
+
+def ref_instance_loop():
+    """The per-instance loop of MaskRefiner.forward (model.py:318-354: `for panoptic_label in np.unique(...)`),
+    AST-extracted and EXECUTED as written, with attribute-bag stand-ins for detectron2's Instances / BitMasks.
+    Returns run(panoptic_image [H,W] f32, r [1,H,W] logits, c [1,H,W]) -> labels, scores, boxes."""
+    import textwrap
+    path = f"{REF}/maskrefiner/modeling/mask_refiner/model.py"
+    src, fwd = _method_node(path, "MaskRefiner", "forward")
+    loop = None
+    for node in ast.walk(fwd):
+        if (isinstance(node, ast.For) and isinstance(node.iter, ast.Call) and ast.unparse(node.iter.func) == "np.unique"
+                and ast.unparse(node.target) == "panoptic_label"):
+            loop = node
+    assert loop is not None, "instance loop not found"
+    code = compile(textwrap.dedent("\n".join(src.splitlines()[loop.lineno - 1:loop.end_lineno])), path, "exec")
+
+    def run(panoptic_image, r, c, label_divisor=1000):
+        ns = {"np": np, "torch": torch, "Instances": _Bag, "BitMasks": _BitMasks,
+              "self": types.SimpleNamespace(meta=types.SimpleNamespace(label_divisor=label_divisor)),
+              "height": panoptic_image.shape[0], "width": panoptic_image.shape[1],
+              "panoptic_image": panoptic_image, "semantic_prob": r.sigmoid().squeeze(0), "c": c,       # model.py:309
+              "panoptic_image_cpu": panoptic_image.cpu().detach().numpy(), "idx": 0, "instances": []}  # :317-320
+        exec(code, ns)
+        labs = [float(x) for x in np.unique(ns["panoptic_image_cpu"]) if x != -1]
+        inst = ns["instances"]
+        assert len(inst) == len(labs)
+        for i, lab in zip(inst, labs):
+            assert torch.equal(i.pred_masks[0], panoptic_image == lab)
+        return (np.array(labs, np.int32), np.array([float(i.scores[0]) for i in inst], np.float32),
+                np.array([i.pred_boxes[0].tolist() for i in inst], np.float32).reshape(-1, 4))
+    return run
+
+
+def ref_error_decode():
+    """eval/eval_utils.py:310-313 (`eee_boundary.argmax(0, keepdim=True)`, `torch.cat([eee_boundary == i ...])`,
+    `.detach().cpu().numpy()`), AST-extracted and executed.  Returns run(logits [C,H,W]) -> bool [4,H,W]
+    (the reference hard-codes range(4); with a 2- / 3-channel head the surplus planes are all False)."""
+    path = f"{REF}/eval/eval_utils.py"
+    src = open(path).read()
+    stmts = []
+    for node in ast.walk(ast.parse(src)):
+        if isinstance(node, ast.If) and "'eee_boundary' in refined_output.keys()" in ast.unparse(node.test):
+            for st in node.body:
+                if isinstance(st, ast.Assign) and ast.unparse(st.targets[0]) == "eee_boundary":
+                    stmts.append(ast.get_source_segment(src, st))
+    assert len(stmts) == 4, stmts
+    code = compile("\n".join(stmts), path, "exec")
+
+    def run(logits):
+        ns = {"torch": torch, "refined_output": {"eee_boundary": logits}}
+        exec(code, ns)
+        return ns["eee_boundary"]
+    return run
+
+
+def ref_quadruple():
+    """tools/ours/panoptic2eee.py: masks_to_fg_mask / mask_to_boundary / masks_to_boundary (:23-59, FunctionDefs) and
+    the eight TP/TN/FP/FN statements of the script body (:110-123), AST-extracted and executed.
+    Returns run(gt_masks, perturbed_masks, h, w) -> dict of the eight uint8 maps."""
+    import cv2
+    path = f"{REF}/tools/ours/panoptic2eee.py"
+    src = open(path).read()
+    tree = ast.parse(src)
+    fns = {"np": np, "cv2": cv2}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name in ("masks_to_fg_mask", "mask_to_boundary", "masks_to_boundary"):
+            exec(ast.get_source_segment(src, node), fns)
+    names = [f"{a}_{b}" for b in ("mask", "boundary") for a in ("tp", "tn", "fp", "fn")]
+    stmts = []
+    for node in ast.walk(tree):
+        if isinstance(node, ast.Assign) and ast.unparse(node.targets[0]) in names + [
+                "gt_fg_mask", "gt_boundary", "perturbed_fg_mask", "perturbed_boundary"]:
+            stmts.append((node.lineno, ast.get_source_segment(src, node)))
+    stmts = [t for _, t in sorted(stmts)]
+    assert len(stmts) == 12, stmts
+    code = compile("\n".join(stmts), path, "exec")
+
+    def run(gt_masks, perturbed_masks, h, w):
+        ns = dict(fns, gt_masks=gt_masks, perturbed_masks=perturbed_masks, h=h, w=w)
+        exec(code, ns)
+        return {n: np.asarray(ns[n]).astype(np.uint8) for n in names}
+    return run
+
+
+def ref_loader_quadruple():
+    """explicit_error_estimation/loader.py:183-192 — the same four maps with the NAMES of TN and FN swapped relative
+    to panoptic2eee.py:116,118 (SURVEY §8 A13 NB).  The eight statements, AST-extracted and executed."""
+    path = f"{REF}/explicit_error_estimation/loader.py"
+    src = open(path).read()
+    names = [f"{a}_{b}" for b in ("mask", "boundary") for a in ("tp", "tn", "fp", "fn")]
+    seen, stmts = set(), []
+    for node in ast.walk(ast.parse(src)):
+        if isinstance(node, ast.Assign) and ast.unparse(node.targets[0]) in names:
+            t = ast.get_source_segment(src, node)
+            if ast.unparse(node.targets[0]) not in seen and "input_" in t:       # first occurrence (:183-192)
+                seen.add(ast.unparse(node.targets[0]))
+                stmts.append((node.lineno, t))
+    stmts = [t for _, t in sorted(stmts)]
+    assert len(stmts) == 8, stmts
+    code = compile("\n".join(stmts), path, "exec")
+
+    def run(gt_fg_mask, input_fg_mask, gt_boundary, input_boundary):
+        ns = dict(np=np, gt_fg_mask=gt_fg_mask, input_fg_mask=input_fg_mask, gt_boundary=gt_boundary,
+                  input_boundary=input_boundary)
+        exec(code, ns)
+        return {n: ns[n] for n in names}
+    return run
+
+
+def gen_encode():
     # ---------------- A1 encode ----------------
     cases = {
         "small": dict(K=6, H=120, W=160, axes=(6, 20), margin=10, seed=3, empty_tail=1),
@@ -137,6 +275,9 @@ def main():
     np.savez_compressed(os.path.join(OUT, "encode.npz"), **enc)
     print("encode.npz", {k: v.shape for k, v in enc.items() if "sha" not in k})
 
+
+
+def gen_boundary():
     # ---------------- A13 boundary ----------------
     bfn = ref_boundary_fns()
     bnd = {}
@@ -169,26 +310,38 @@ def main():
     np.savez_compressed(os.path.join(OUT, "boundary.npz"), **bnd)
     print("boundary.npz ok")
 
+
+
+PCASES = {
+    "small": dict(K=5, H=240, W=320, axes=(18, 40), margin=40, seed=11, top_k=200),
+    "topk": dict(K=12, H=240, W=320, axes=(14, 30), margin=30, seed=12, top_k=8),
+    "plateau": dict(K=12, H=240, W=320, axes=(14, 30), margin=30, seed=12, top_k=8),
+    "nocentre": dict(K=3, H=240, W=320, axes=(30, 50), margin=60, seed=13, top_k=200),
+    "c1": dict(K=20, H=480, W=640, axes=(20, 60), margin=60, seed=0, top_k=200),
+}
+
+
+def post_case_low(name, eee_channels=4):
+    """The seeded 1/4-resolution head outputs of a post-processing case: [4 + C, h, w] float32."""
+    c = PCASES[name]
+    m = synth.ellipse_masks(c["K"], c["H"], c["W"], seed=c["seed"], axes=c["axes"], margin=c["margin"])
+    ho = synth.head_outputs(m, stride=4, seed=c["seed"], eee_channels=eee_channels)
+    if name == "nocentre":
+        ho["center"] = ho["center"] * 0.2          # below CENTER_THRESHOLD everywhere -> stuff branch
+    if name == "plateau":
+        # equal-valued plateaus: every plateau pixel survives the NMS, the k-th score ties the
+        # maximum and the strict `>` at post_processing.py:41 leaves nothing
+        ho["center"] = np.round(ho["center"] * 8) / 8
+    return np.concatenate([ho["foreground"], ho["center"], ho["offset"], ho["eee_boundary"]], 0)
+
+
+def gen_post():
     # ---------------- A8-A12 post-processing ----------------
     pp = ref_post_processing()
+    inst_loop, decode = ref_instance_loop(), ref_error_decode()
     post = {}
-    pcases = {
-        "small": dict(K=5, H=240, W=320, axes=(18, 40), margin=40, seed=11, top_k=200),
-        "topk": dict(K=12, H=240, W=320, axes=(14, 30), margin=30, seed=12, top_k=8),
-        "plateau": dict(K=12, H=240, W=320, axes=(14, 30), margin=30, seed=12, top_k=8),
-        "nocentre": dict(K=3, H=240, W=320, axes=(30, 50), margin=60, seed=13, top_k=200),
-        "c1": dict(K=20, H=480, W=640, axes=(20, 60), margin=60, seed=0, top_k=200),
-    }
-    for name, c in pcases.items():
-        m = synth.ellipse_masks(c["K"], c["H"], c["W"], seed=c["seed"], axes=c["axes"], margin=c["margin"])
-        ho = synth.head_outputs(m, stride=4, seed=c["seed"])
-        if name == "nocentre":
-            ho["center"] = ho["center"] * 0.2          # below CENTER_THRESHOLD everywhere -> stuff branch
-        if name == "plateau":
-            # equal-valued plateaus: every plateau pixel survives the NMS, the k-th score ties the
-            # maximum and the strict `>` at post_processing.py:41 leaves nothing
-            ho["center"] = np.round(ho["center"] * 8) / 8
-        low = np.concatenate([ho["foreground"], ho["center"], ho["offset"], ho["eee_boundary"]], 0)
+    for name, c in PCASES.items():
+        low = post_case_low(name)
         full = oracle.upsample_bilinear(low, 4)
         full[2:4] *= 4.0                                # model.py:698
         r, cmap, o, b = full[0:1], full[1:2], full[2:4], full[4:8]
@@ -200,24 +353,11 @@ def main():
         centres = pp.find_instance_center(ct.clone(), threshold=0.3, nms_kernel=7, top_k=c["top_k"])
         grouped = pp.group_pixels(centres, ot) if len(centres) else torch.zeros(1, c["H"], c["W"], dtype=torch.long)
         pan = pan.squeeze(0)
-        # instance extraction exactly as model.py:318-356 words it (torch ops; Instances/BitMasks are
-        # detectron2 containers, un-vendored — only their arithmetic is reproduced)
-        sem_prob = rt.sigmoid().squeeze(0)
-        labels, scores, boxes, cyx = [], [], [], []
-        for lab in np.unique(pan.numpy()):
-            if lab == -1:
-                continue
-            mask = pan == lab
-            s = torch.mean(sem_prob.clone()[mask])
-            idx = torch.nonzero(mask).float()
-            cy, cx = torch.mean(idx[:, 0]), torch.mean(idx[:, 1])
-            cs = ct[0, int(cy.item()), int(cx.item())]
-            labels.append(int(lab)); scores.append(float(s * cs)); cyx.append([float(cy), float(cx)])
-            ys, xs = torch.nonzero(mask.any(1)).flatten(), torch.nonzero(mask.any(0)).flatten()
-            boxes.append([float(xs.min()), float(ys.min()), float(xs.max() + 1), float(ys.max() + 1)])
-        bt = torch.from_numpy(b)
-        am = bt.argmax(0, keepdim=True)                 # eval/eval_utils.py:311-313
-        onehot = torch.cat([am == i for i in range(4)], 0).numpy()
+        # instance extraction: model.py:318-354 EXECUTED (ref_instance_loop); the centroids are kept as a by-product
+        labels, scores, boxes = inst_loop(pan, rt, ct)
+        cyx = [[float(torch.nonzero(pan == lab).float()[:, 0].mean()), float(torch.nonzero(pan == lab).float()[:, 1].mean())]
+               for lab in labels]
+        onehot = decode(torch.from_numpy(b))             # eval/eval_utils.py:310-313 executed
         post[f"{name}_low"] = low
         post[f"{name}_topk"] = np.array(c["top_k"])
         post[f"{name}_fgseg"] = np.packbits(fgseg.numpy().astype(bool))
@@ -238,6 +378,9 @@ def main():
         print(name, "centres", len(centres), "instances", len(labels), "up diff", post[f"{name}_torch_up_maxabs"])
     np.savez_compressed(os.path.join(OUT, "post.npz"), **post)
 
+
+
+def gen_msda():
     # ---------------- A14 MSDA ----------------
     msda = ref_msda()
     md = {}
@@ -260,6 +403,124 @@ def main():
         md[f"{name}_out_f32"] = o32     # computed from their float32 roundings
     np.savez_compressed(os.path.join(OUT, "msda.npz"), **md)
     print("msda.npz ok")
+
+
+def gen_post_ii():
+    """Mode (ii), SURVEY Appendix A: the reference's REAL chain on the 1/4-resolution head outputs —
+    F.interpolate(x4, bilinear, align_corners=False) per output, offset x4 (model.py:689-708), sem_seg_postprocess
+    (identity at equal size, :266-289), r.sigmoid().round() (:292), get_panoptic_segmentation (:291-302), the instance
+    loop (:318-354), the caller's argmax decode (eval_utils.py:310-313).  PyTorch's up-sampler rounds differently from
+    the oracle's / the kernels' (and CPU differs from CUDA), so each pixel also gets its MARGIN to the nearest decision
+    threshold; a product pixel may differ only inside the stated bands, and the in-band count is stored."""
+    pp = ref_post_processing()
+    inst_loop, decode = ref_instance_loop(), ref_error_decode()
+    F = torch.nn.functional
+    out = {}
+    FG_BAND, CE_BAND, EEE_BAND, GRP_BAND = 1e-5, 1e-5, 1e-5, 1e-4
+    out["bands"] = np.array([FG_BAND, CE_BAND, EEE_BAND, GRP_BAND])
+    for name, c in PCASES.items():
+        low = torch.from_numpy(post_case_low(name))[None]
+        up = lambda t: F.interpolate(t, scale_factor=4, mode="bilinear", align_corners=False)       # model.py:689-708
+        r, ce, o, b = up(low[:, 0:1])[0], up(low[:, 1:2])[0], (up(low[:, 2:4]) * 4)[0], up(low[:, 4:8])[0]
+        fgseg = r.sigmoid().round()
+        pan, ctr = pp.get_panoptic_segmentation(
+            fgseg, ce.clone(), o, thing_ids=dict({1: 0}).values(), label_divisor=1000, stuff_area=2048, void_label=-1,
+            threshold=0.3, nms_kernel=7, top_k=c["top_k"])
+        pan = pan.squeeze(0)
+        centres = ctr.reshape(-1, 2)
+        labels, scores, boxes = inst_loop(pan, r, ce)
+        onehot = decode(b)
+        # ---- margins (float64 on torch's own full-resolution values)
+        H, W = pan.shape
+        band_fg = r[0].abs().numpy() <= FG_BAND
+        cen = ce[0].double()
+        near_thr = int(((cen - 0.3).abs() <= CE_BAND).sum())
+        pooled = F.max_pool2d(cen[None, None], 7, 1, 3)[0, 0]
+        near_nms = int(((cen > 0.3) & (cen != pooled) & ((pooled - cen) <= CE_BAND)).sum())
+        top2 = torch.topk(b.double(), 2, dim=0).values
+        band_eee = ((top2[0] - top2[1]) <= EEE_BAND).numpy()
+        band_grp = np.zeros((H, W), bool)
+        if len(centres) > 1:
+            yy, xx = torch.meshgrid(torch.arange(H, dtype=torch.float64), torch.arange(W, dtype=torch.float64), indexing="ij")
+            ly, lx = yy + o[0].double(), xx + o[1].double()
+            d = torch.sqrt((centres[:, 0].double()[:, None, None] - ly) ** 2 + (centres[:, 1].double()[:, None, None] - lx) ** 2)
+            d2 = torch.topk(d, 2, dim=0, largest=False).values
+            band_grp = ((d2[1] - d2[0]) <= GRP_BAND).numpy()
+        areas = [int((pan == float(l)).sum()) for l in labels]
+        out[f"{name}_panoptic"] = pan.numpy().astype(np.int16)
+        out[f"{name}_centres"] = centres.numpy().astype(np.int32)
+        out[f"{name}_fgseg"] = np.packbits(fgseg.numpy().astype(bool))
+        out[f"{name}_onehot"] = np.packbits(onehot)
+        out[f"{name}_labels"], out[f"{name}_scores"], out[f"{name}_boxes"] = labels, scores, boxes
+        out[f"{name}_areas"] = np.array(areas, np.int64)
+        out[f"{name}_band_fg"] = np.packbits(band_fg)
+        out[f"{name}_band_grp"] = np.packbits(band_grp)
+        out[f"{name}_band_eee"] = np.packbits(band_eee)
+        out[f"{name}_band_counts"] = np.array([int(band_fg.sum()), near_thr, near_nms, int(band_grp.sum()), int(band_eee.sum())])
+        out[f"{name}_sem_seg_q"] = r[0, ::4, ::4].numpy().copy()
+        out[f"{name}_eee_q"] = b[:, ::8, ::8].numpy().copy()
+        print("ii", name, "centres", len(centres), "instances", len(labels), "in-band [fg, thr, nms, grp, eee] =",
+              out[f"{name}_band_counts"].tolist())
+    np.savez_compressed(os.path.join(OUT, "post_ii.npz"), **out)
+
+
+def gen_decode_types():
+    """ERROR_TYPE e2 / e33 / e32 heads (model.py:215-226, channel counts :549-568: 2 / 3 / 2): the caller's decode
+    (eval_utils.py:310-313, executed) on 2- and 3-channel logits."""
+    decode = ref_error_decode()
+    out = {}
+    for C, seed in ((2, 21), (3, 22)):
+        c = PCASES["small"]
+        m = synth.ellipse_masks(c["K"], c["H"], c["W"], seed=c["seed"], axes=c["axes"], margin=c["margin"])
+        low = synth.head_outputs(m, stride=4, seed=seed, eee_channels=C)["eee_boundary"]
+        full = oracle.upsample_bilinear(low, 4)                       # mode (i): decision on the oracle's up-sampler
+        oh = decode(torch.from_numpy(full))
+        assert oh.shape[0] == 4 and not oh[C:].any()
+        out[f"c{C}_low"] = low
+        out[f"c{C}_onehot"] = np.packbits(oh[:C])
+        out[f"c{C}_seed"] = np.array(seed)
+    np.savez_compressed(os.path.join(OUT, "decode_types.npz"), **out)
+    print("decode_types.npz ok")
+
+
+def gen_quadruple():
+    """A13 quadruple maps: tools/ours/panoptic2eee.py executed (ref_quadruple), and the loader's variant with the
+    TN / FN names swapped (explicit_error_estimation/loader.py:183-192, executed)."""
+    quad, loader = ref_quadruple(), ref_loader_quadruple()
+    bfn = ref_boundary_fns()
+    out = {}
+    for name, (K, H, W, seed) in {"small": (6, 120, 160, 31), "c1": (20, 480, 640, 0)}.items():
+        gt = synth.ellipse_masks(K, H, W, seed=seed, axes=(6, 30) if name == "small" else (20, 60), margin=10 if name == "small" else 60)
+        pr = synth.perturb_masks(gt, seed=seed + 1)
+        q = quad(gt, list(pr), H, W)            # perturbed masks are a list of decoded RLEs in the script (:95-107)
+        out[f"{name}_gt"] = np.packbits(gt != 0)
+        out[f"{name}_pred"] = np.packbits(pr != 0)
+        out[f"{name}_shape"] = np.array(gt.shape)
+        for k, v in q.items():
+            assert set(np.unique(v)) <= {0, 1}
+            out[f"{name}_{k}"] = np.packbits(v)
+        # loader.py: same inputs through util.py's functions; its tn_* is panoptic2eee's fn_* and vice versa
+        gfg, ifg = bfn["masks_to_fg_mask"](gt), bfn["masks_to_fg_mask"](pr)
+        gb, ib = bfn["masks_to_boundary"](gt), bfn["masks_to_boundary"](pr)
+        lq = loader(gfg, ifg, gb, ib)
+        for t in ("mask", "boundary"):
+            assert np.array_equal(lq[f"tp_{t}"], q[f"tp_{t}"]) and np.array_equal(lq[f"fp_{t}"], q[f"fp_{t}"])
+            assert np.array_equal(lq[f"tn_{t}"], q[f"fn_{t}"]) and np.array_equal(lq[f"fn_{t}"], q[f"tn_{t}"])
+        out[f"{name}_loader_swaps_tn_fn"] = np.array(1)
+    np.savez_compressed(os.path.join(OUT, "quadruple.npz"), **out)
+    print("quadruple.npz ok")
+
+
+SECTIONS = {"encode": gen_encode, "boundary": gen_boundary, "post": gen_post, "msda": gen_msda,
+            "post_ii": gen_post_ii, "decode_types": gen_decode_types, "quadruple": gen_quadruple}
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(1)
+    only = sys.argv[1:] or list(SECTIONS)
+    for name in only:
+        SECTIONS[name]()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -95,7 +95,7 @@ class MaskRefiner(nn.Module):
         self.eee_boundary_on = cfg.MODEL.INS_EMBED_HEAD.EEE_BOUNDARY_ON
         self.error_type = cfg.MODEL.INS_EMBED_HEAD.ERROR_TYPE
         self.common_stride = cfg.MODEL.INS_EMBED_HEAD.COMMON_STRIDE
-        self.max_instances_per_image = 64
+        self.max_instances_per_image = max(int(self.top_k), 1)   # instances <= centres <= top_k: the pool can not overflow
         self.use_cuda_graph = False         # capture / replay network_logits (fixed shapes; see network_logits)
         self.use_inference_plan = True      # folded BN + fused conv epilogues (network.Conv2d.plan); False = layer by layer
         self.set_precision(precision)
@@ -216,6 +216,7 @@ class MaskRefiner(nn.Module):
             # sem_seg_postprocess is the identity: up-sample inside the fused kernels
             r = ops.post_process(out["foreground"], out["center"], out["offset"], eee, scale=s,
                                  max_instances=B * self.max_instances_per_image, **kw)
+            self._check_pool(r)
             mfull = None
             if self.eee_mask_on:
                 mfull = torch.nn.functional.interpolate(out["eee_mask"], scale_factor=s, mode="bilinear", align_corners=False)
@@ -233,9 +234,17 @@ class MaskRefiner(nn.Module):
                 padw = (lambda t: torch.nn.functional.pad(t, (0, pad), value=-1e4).contiguous()) if pad else (lambda t: t)
                 r = ops.post_process(padw(pp(full["foreground"])), padw(pp(full["center"])), padw(pp(full["offset"])),
                                      None if e is None else padw(e), scale=1, max_instances=self.max_instances_per_image, **kw)
+                self._check_pool(r)
                 m = pp(full["eee_mask"])[0] if self.eee_mask_on else None
                 results.append(self._result(r, 0, b, heights[b], Wb, m, crop=Wb if pad else None))
         return results
+
+    @staticmethod
+    def _check_pool(r):
+        """Never clamp silently: quber_post_process sets status bit 0 when the instance pool was too small."""
+        if int(r["status"][0]) & 1:
+            raise RuntimeError(f"quber_post_process: more refined instances than the output pool holds "
+                               f"({r['max_instances']} rows); raise MaskRefiner.max_instances_per_image")
 
     def _result(self, r, rb, b, height, width, eee_mask, crop=None):
         cw = (lambda t: t[..., :crop]) if crop else (lambda t: t)
@@ -247,7 +256,6 @@ class MaskRefiner(nn.Module):
         res["panoptic_seg"] = (cw(r["panoptic"][rb]), None)
         if self.predict_instances:
             o0, o1 = int(r["inst_offsets"][rb]), int(r["inst_offsets"][rb + 1])     # the single host read-back per image
-            o1 = min(o1, r["max_instances"])
             if o1 > o0:
                 res["instances"] = Instances(
                     (height, width), pred_masks=cw(r["masks"][o0:o1]).bool(), scores=r["scores"][o0:o1],

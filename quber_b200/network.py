@@ -212,6 +212,8 @@ def prepare_inference(module, dtype=torch.float32, channels_last=False):
     for m in module.modules():
         if isinstance(m, Conv2d):
             m.plan(dtype, channels_last)
+        if isinstance(m, FusionLayers):
+            m._folded = None
         if isinstance(m, (RGBDFusionBackbone, DeepLabV3PlusDecoder)):
             m.__dict__["_fast"] = True
 
@@ -220,6 +222,8 @@ def drop_inference_plan(module):
     for m in module.modules():
         if isinstance(m, Conv2d):
             m.drop_plan()
+        if isinstance(m, FusionLayers):
+            m._folded = None
         if isinstance(m, (RGBDFusionBackbone, DeepLabV3PlusDecoder)):
             m.__dict__["_fast"] = False
 
@@ -555,9 +559,11 @@ class FusionLayers(nn.Module):
     # ---- tcgen05 route for the opening 1x1: eval-mode BatchNorm folded into (W, b) -----------------
     def folded_1x1(self, pitch, dtype):
         """(W' [out, pitch], b' [out]) with BN(conv(x)) == x W'^T + b' in eval mode; W' zero-padded to `pitch`."""
-        key = (pitch, dtype)
+        l0 = self.fusion_layers[0]
+        # keyed on identity + version of every tensor it derives from (Conv2d._sig), like the convolutions' own plan:
+        # a checkpoint load, an in-place edit or .to() after a bf16 forward must not leave stale folded weights behind
+        key = (pitch, dtype, l0._sig())
         if self._folded is None or self._folded[0] != key:
-            l0 = self.fusion_layers[0]
             bn = l0.norm
             scale = bn.weight * (bn.running_var + bn.eps).rsqrt()
             w = l0.weight.reshape(self.out_channels, self.in_channels) * scale[:, None]

@@ -158,7 +158,10 @@ def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=No
     if offset_mul is None:
         offset_mul = float(scale)          # model.py:698
     if max_instances is None:
-        max_instances = B * min(top_k, 64)
+        # worst case by construction: an image never has more instances than centres (<= top_k; one stuff paste when
+        # there is no centre), so the default pool can not overflow.  The reference returns up to top_k - 1 instances
+        # per image (post_processing.py:40-41).  A caller that passes a smaller pool must check out["status"] & 1.
+        max_instances = B * max(top_k, 1)
     flags = 0
     p = _lib.PostParams(B, H, W, scale, offset_mul, C, threshold, nms_kernel, top_k, min_area, stuff_area, label_divisor,
                         void_label, max_instances, 0)

@@ -37,7 +37,8 @@ class RefinerConfig:
     common_stride: int = 4             # MODEL.SEM_SEG_HEAD.COMMON_STRIDE
     sigma: int = 10                    # predictor.py:246
     boundary_ratio: float = 0.01       # masks_to_boundary default (util.py:92)
-    max_instances_per_image: int = 64
+    max_instances_per_image: int = 0   # rows of the output pool per frame; 0 = top_k, the worst case (instances <= centres
+                                       # <= top_k), so the pool can not overflow; a smaller value sets status bit 0 on overflow
     compact_label_map: bool = False    # label maps as uint8 (QUBER_POST_LABEL_U8; needs top_k <= 255): 1/4 of the bytes
     want: tuple = ("label_map", "masks", "eee_onehot")
 
@@ -83,8 +84,13 @@ class HotPath:
         return ops.post_process(head["foreground"], head["center"], head["offset"], head.get("eee_boundary"),
                                 scale=c.common_stride, threshold=c.center_threshold, nms_kernel=c.nms_kernel,
                                 top_k=c.top_k, min_area=c.min_area, stuff_area=c.stuff_area,
-                                label_divisor=c.label_divisor, max_instances=B * c.max_instances_per_image, want=c.want,
+                                label_divisor=c.label_divisor, max_instances=B * self.slab, want=c.want,
                                 label_dtype=torch.uint8 if c.compact_label_map and c.top_k <= 255 else torch.int32)
+
+    @property
+    def slab(self):
+        """Rows of the instance pool per frame."""
+        return self.cfg.max_instances_per_image or max(self.cfg.top_k, 1)
 
     def msda_layers(self, msda, n_layers=6):
         out = None
@@ -104,7 +110,7 @@ class HotPath:
         if st is None or st["key"] != key:
             dev = self.device
             B, K, H, W = masks_host.shape
-            slab = self.cfg.max_instances_per_image
+            slab = self.slab
             pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
             st = dict(key=key, masks=torch.empty(masks_host.shape, dtype=torch.uint8, device=dev),
                       head={k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in head_host.items()},
@@ -114,7 +120,7 @@ class HotPath:
                       graphs={},
                       out=dict(label_map=pin((B, H, W), ldt), boundary=pin((B, H, W), torch.uint8),
                                inst_start=pin((B,), torch.int32), inst_counts=pin((B,), torch.int32),
-                               labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
+                               status=pin((1,), torch.int32), labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
                                boxes=pin((B * slab, 4), torch.float32)))
             self._stage = st
         return st
@@ -218,7 +224,7 @@ class HotPath:
         cur = torch.cuda.current_stream(dev)
         h2d, d2h = st["h2d"], st["d2h"]
         B = masks_host.shape[0]
-        slab = self.cfg.max_instances_per_image
+        slab = self.slab
         if st["free"] is not None:
             h2d.wait_event(st["free"])            # the previous call's kernels have finished reading the staging buffers
         d2h.wait_stream(cur)                      # ... and whoever consumed the pinned results was ordered on `cur`
@@ -255,6 +261,7 @@ class HotPath:
                 out["label_map"].copy_(r["label_map"], non_blocking=True)
                 out["inst_start"].copy_(start, non_blocking=True)
                 out["inst_counts"].copy_(counts, non_blocking=True)
+                out["status"].copy_(r["status"], non_blocking=True)     # bit 0: instance pool overflow (never with slab = top_k)
                 out["labels"].copy_(r["labels"][:B * slab], non_blocking=True)
                 out["scores"].copy_(r["scores"][:B * slab], non_blocking=True)
                 out["boxes"].copy_(r["boxes"][:B * slab], non_blocking=True)

@@ -524,3 +524,87 @@ def test_gemm_leading_dims_and_general_fp32_inputs():
     assert ((y.double() - ref).abs() <= bound + 1e-5).all()
     with pytest.raises(ValueError):
         ops.gemm_bias_act(x, w.bfloat16(), b)
+
+
+# ------------------------------------------------------------------ round 2: executed-reference goldens on the kernels
+@pytest.mark.parametrize("case", ["small", "topk", "plateau", "nocentre", "c1"])
+def test_post_mode_ii_reference_interpolate_chain(case):
+    """SURVEY Appendix A mode (ii): the kernels up-sample the 1/4-resolution head outputs themselves and are compared
+    with the reference's real F.interpolate -> sigmoid().round() -> get_panoptic_segmentation -> instance loop ->
+    argmax chain (tests/golden/post_ii.npz); equality outside the margin bands, in-band pixel count printed."""
+    from test_oracle_golden import check_mode_ii
+    g = golden("post.npz")
+    fg, ce, of, ee = _low(g, case)
+    r = ops.post_process(cu(fg), cu(ce), cu(of), cu(ee), scale=4, top_k=int(g[f"{case}_topk"]))
+    n = int(r["inst_offsets"][1])
+    check_mode_ii(case, r["panoptic"][0].cpu().numpy(), r["centers_yx"][0, : int(r["n_centers"][0])].cpu().numpy(),
+                  r["eee_onehot"][0].cpu().numpy(), r["labels"][:n].cpu().numpy(), r["boxes"][:n].cpu().numpy(),
+                  r["scores"][:n].cpu().numpy(), sem_seg=r["sem_seg"][0, 0].cpu().numpy(),
+                  eee_full=r["eee_full"][0].cpu().numpy(), who="kernels")
+
+
+@pytest.mark.parametrize("C", [2, 3])
+def test_error_decode_e2_e33_e32_heads(C):
+    """2- and 3-channel error heads (ERROR_TYPE e2 / e32 / e33, model.py:215-226) through group_kernel's decode."""
+    g = golden("decode_types.npz")
+    low = g[f"c{C}_low"]
+    h, w = low.shape[1:]
+    pg = golden("post.npz")
+    fg, ce, of, _ = _low(pg, "small")
+    assert fg.shape[-2:] == (h, w)
+    r = ops.post_process(cu(fg), cu(ce), cu(of), cu(low[None]), scale=4)
+    H, W = 4 * h, 4 * w
+    ref = np.unpackbits(g[f"c{C}_onehot"])[: C * H * W].reshape(C, H, W)
+    assert r["eee_onehot"].shape == (1, C, H, W)
+    np.testing.assert_array_equal(r["eee_onehot"][0].cpu().numpy(), ref)
+    np.testing.assert_array_equal(r["eee_full"][0].cpu().numpy(), oracle.upsample_bilinear(low, 4))
+    # the rest of the outputs does not depend on the error head
+    np.testing.assert_array_equal(r["panoptic"][0].cpu().numpy().astype(np.int16), pg["small_panoptic"])
+
+
+@pytest.mark.parametrize("case", ["small", "c1"])
+def test_quadruple_maps_match_executed_panoptic2eee(case):
+    """quber_mask_boundary + quber_quadruple_maps against tools/ours/panoptic2eee.py executed (tests/golden/quadruple.npz)."""
+    g = golden("quadruple.npz")
+    shape = tuple(int(x) for x in g[f"{case}_shape"])
+    K, H, W = shape
+    n = K * H * W
+    gt = np.unpackbits(g[f"{case}_gt"])[:n].reshape(shape).astype(np.uint8) * 255
+    pr = np.unpackbits(g[f"{case}_pred"])[:n].reshape(shape).astype(np.uint8) * 255
+    d = ops.boundary_dilation(H, W, 0.01)
+    _, gb, gf = ops.mask_boundary(cu(gt)[None], d, per_instance=False)
+    _, pb, pf = ops.mask_boundary(cu(pr)[None], d, per_instance=False)
+    qm, qb = ops.quadruple_maps(gf, pf)[0].cpu().numpy(), ops.quadruple_maps(gb, pb)[0].cpu().numpy()
+    for i, name in enumerate(("tp", "tn", "fp", "fn")):
+        np.testing.assert_array_equal(qm[i], np.unpackbits(g[f"{case}_{name}_mask"])[: H * W].reshape(H, W))
+        np.testing.assert_array_equal(qb[i], np.unpackbits(g[f"{case}_{name}_boundary"])[: H * W].reshape(H, W))
+
+
+def test_c2_all_32_frames_against_oracle():
+    """Every frame of configs[1] (32 frames 640x480, 30 masks) against the oracle, bit for bit: encode, per-instance and
+    union boundaries, foreground, and the whole post-processing output set."""
+    from concurrent.futures import ThreadPoolExecutor
+    B, K, H, W = 32, 30, 480, 640
+    masks = np.stack([synth.ellipse_masks(K, H, W, seed=300 + b) for b in range(B)])
+    lows = np.stack([np.concatenate(list(synth.head_outputs(masks[b], seed=300 + b).values()), 0) for b in range(B)])
+    dm = cu(masks)
+    enc = ops.encode_initial_masks(dm).cpu().numpy()
+    per, uni, fg = (t.cpu().numpy() for t in ops.mask_boundary(dm, ops.boundary_dilation(H, W, 0.01)))
+    r = ops.post_process(cu(lows[:, 0:1]), cu(lows[:, 1:2]), cu(lows[:, 2:4]), cu(lows[:, 4:8]), scale=4, max_instances=B * 64)
+    r = {k: (v.cpu() if isinstance(v, torch.Tensor) else v) for k, v in r.items()}
+
+    def one(b):                       # the oracle is C called through ctypes: the GIL is released, frames run in parallel
+        u, p = oracle.masks_to_boundary(masks[b], 0.01, return_per_instance=True)
+        full = oracle.upsample_bilinear(lows[b], 4)
+        full[2:4] *= 4.0
+        return (oracle.encode_initial_masks(masks[b]), u, p, oracle.masks_to_fg_mask(masks[b]),
+                oracle.post_process(full[0], full[1], full[2:4], full[4:8]))
+
+    with ThreadPoolExecutor(8) as ex:
+        refs = list(ex.map(one, range(B)))
+    for b, (e, u, p, f, post) in enumerate(refs):
+        np.testing.assert_array_equal(enc[b], e)
+        np.testing.assert_array_equal(per[b], p)
+        np.testing.assert_array_equal(uni[b], u)
+        np.testing.assert_array_equal(fg[b], f)
+        _check_post(r, post, H, W, b=b)
