@@ -315,6 +315,36 @@ int quber_host_pack_begin(const uint8_t *src, size_t n_bytes, uint32_t *dst, int
 int quber_host_pack_wait(int chunk, int *value);
 int quber_unpack_masks(const uint32_t *packed, size_t n_words, int value, uint8_t *out, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * COCO run-length encoded masks — replaces pycocotools.mask.decode / encode / frPyObjects (a
+ *     third-party dependency of the reference, cocoapi common/maskApi.c) at the reference's call sites:
+ *     mask_util.decode  maskrefiner/data/dataset_mappers/perturbed_panoptic_dataset_mapper.py:195-214,
+ *                       tools/ours/panoptic2eee.py:95-97
+ *     mask_util.encode  tools/ours/panoptic2eee.py:61-64,125-132
+ *     frPyObjects       maskrefiner/data/datasets/register_uoais_sim_instance.py:207-209
+ *     and the dataset fields maskrefiner/data/datasets/register_uoais_sim_panoptic.py:121-144 carries in this form.
+ *   An RLE = run lengths of the mask in COLUMN-major order, starting with a (possibly empty) run of zeros.
+ * quber_rle_decode: counts dev uint32 [total_counts] (the n masks' counts back to back), offsets dev int64 [n+1]
+ *     (mask i owns counts[offsets[i] .. offsets[i+1])) -> ROW-major masks:
+ *       packed_out dev uint32 [n*H*W/32] (bit i of word w = pixel 32 w + i; needs W % 32 == 0; the input format of
+ *                  quber_encode_initial_masks_packed) and / or masks_out dev uint8 [n,H,W] (0 / value); either may be NULL.
+ *     status dev int32 [1]: bit 0 = some mask's counts do not sum to H*W (decoded as far as they go, rest 0).
+ * quber_rle_encode: masks dev uint8 [n,H,W] (non-zero = set) -> counts_out dev uint32 [cap], offsets_out dev int64 [n+1];
+ *     status bit 1 = cap too small (offsets_out is still complete: offsets_out[n] is the capacity needed).
+ * quber_rle_from_string / quber_rle_to_string: HOST, the compressed ASCII form (maskApi.c rleFrString / rleToString);
+ *     return the number of counts / characters (which exceeds `cap` when the buffer was too small), or a negative
+ *     QUBER_E_* code for a malformed string.
+ * ------------------------------------------------------------------------------------------- */
+size_t quber_rle_decode_workspace_bytes(size_t total_counts);
+int quber_rle_decode(const uint32_t *counts, const int64_t *offsets, size_t total_counts, int n, int H, int W, int value,
+                     uint32_t *packed_out, uint8_t *masks_out, void *workspace, size_t workspace_bytes, int32_t *status,
+                     void *stream);
+size_t quber_rle_encode_workspace_bytes(int n, int H, int W, size_t cap);
+int quber_rle_encode(const uint8_t *masks, int n, int H, int W, uint32_t *counts_out, size_t cap, int64_t *offsets_out,
+                     void *workspace, size_t workspace_bytes, int32_t *status, void *stream);
+long long quber_rle_from_string(const char *s, size_t len, uint32_t *counts, size_t cap);
+long long quber_rle_to_string(const uint32_t *counts, size_t m, char *s, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

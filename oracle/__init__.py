@@ -198,3 +198,40 @@ def filter_instances(masks, fg_mask=None, zero_depth=None, thr=0.3):
     if zero_depth is not None:
         out[:, np.asarray(zero_depth).astype(bool)] = False
     return out, keep
+
+
+# ---- (f)4 COCO RLE (pycocotools.mask restated; see the header of that section in quber_oracle.c) ----------------
+def rle_encode(mask):
+    """pycocotools.mask.encode for one [H,W] mask -> uncompressed counts (uint32), column-major runs starting with zeros."""
+    mask = _c(mask, np.uint8)
+    H, W = mask.shape
+    cnts = np.empty(H * W + 1, np.uint32)
+    lib().oracle_rle_encode.restype = ctypes.c_size_t
+    m = lib().oracle_rle_encode(_p(mask), H, W, _p(cnts), ctypes.c_size_t(cnts.size))
+    return cnts[:m].copy()
+
+
+def rle_decode(counts, H, W):
+    """pycocotools.mask.decode for one RLE -> [H,W] uint8 0/1."""
+    counts = _c(counts, np.uint32)
+    out = np.empty((H, W), np.uint8)
+    if lib().oracle_rle_decode(_p(counts), ctypes.c_size_t(counts.size), H, W, _p(out)) != 0:
+        raise ValueError("RLE counts exceed the mask size")
+    return out
+
+
+def rle_to_string(counts):
+    counts = _c(counts, np.uint32)
+    buf = ctypes.create_string_buffer(6 * counts.size + 1)
+    lib().oracle_rle_to_string.restype = ctypes.c_size_t
+    n = lib().oracle_rle_to_string(_p(counts), ctypes.c_size_t(counts.size), buf)
+    return buf.raw[:n]
+
+
+def rle_from_string(s):
+    if isinstance(s, str):
+        s = s.encode("ascii")
+    cnts = np.empty(max(len(s), 1), np.uint32)
+    lib().oracle_rle_from_string.restype = ctypes.c_size_t
+    m = lib().oracle_rle_from_string(ctypes.c_char_p(s), _p(cnts))
+    return cnts[:m].copy()

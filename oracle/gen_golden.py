@@ -511,8 +511,44 @@ def gen_quadruple():
     print("quadruple.npz ok")
 
 
+def gen_rle():
+    """(f)4 COCO RLE.  pycocotools is not installed anywhere in this image and is not vendored by the reference, so the
+    vectors come from an INDEPENDENT implementation of the same uncompressed format that ships here as library code:
+    transformers' SAM post-processing (`_mask_to_rle`: "in the format expected by pycoco tools", `_rle_to_mask`).  The
+    compressed ASCII strings stored beside them are the oracle's own (maskApi.c rleToString restated) — a frozen
+    regression vector, NOT an independent pin: parity of the string codec stays unpinned."""
+    from transformers.models.sam.image_processing_sam import _mask_to_rle, _rle_to_mask
+    out = {}
+    cases = {
+        "blobs": synth.ellipse_masks(6, 120, 160, seed=41, axes=(6, 40), margin=4, empty_tail=1),
+        "c1": synth.ellipse_masks(20, 480, 640, seed=0),
+        "odd": synth.ellipse_masks(3, 75, 133, seed=42, axes=(5, 30), margin=3),          # W % 32 != 0: byte output only
+    }
+    rng = np.random.default_rng(7)
+    noise = (rng.random((3, 64, 96)) < 0.4).astype(np.uint8)
+    noise[1, 0, 0] = 1                  # a mask that starts with a set pixel: first count 0
+    noise[2] = 1                        # a full mask: counts [0, h*w]
+    cases["noise"] = noise
+    for name, m in cases.items():
+        mb = torch.from_numpy(m != 0)
+        rles = _mask_to_rle(mb)
+        back = torch.stack([_rle_to_mask(r) for r in rles])
+        assert torch.equal(back, mb)
+        counts = [np.asarray(r["counts"], np.uint32) for r in rles]
+        offsets = np.zeros(len(counts) + 1, np.int64)
+        np.cumsum([len(c) for c in counts], out=offsets[1:])
+        out[f"{name}_masks"] = np.packbits(m != 0)
+        out[f"{name}_shape"] = np.array(m.shape)
+        out[f"{name}_counts"] = np.concatenate(counts)
+        out[f"{name}_offsets"] = offsets
+        strs = [oracle.rle_to_string(c) for c in counts]
+        out[f"{name}_strings"] = np.frombuffer(b"\n".join(strs), np.uint8)
+        print("rle", name, m.shape, "runs", int(offsets[-1]))
+    np.savez_compressed(os.path.join(OUT, "rle.npz"), **out)
+
+
 SECTIONS = {"encode": gen_encode, "boundary": gen_boundary, "post": gen_post, "msda": gen_msda,
-            "post_ii": gen_post_ii, "decode_types": gen_decode_types, "quadruple": gen_quadruple}
+            "post_ii": gen_post_ii, "decode_types": gen_decode_types, "quadruple": gen_quadruple, "rle": gen_rle}
 
 
 def main():

@@ -63,6 +63,12 @@ SYMBOLS = {
     "quber_host_pack_wait": (c_i, [c_i, c_vp]),
     "quber_unpack_masks": (c_i, [c_vp, c_sz, c_i, c_vp, c_vp]),
     "quber_msda_prepare": (c_i, [c_vp, c_i, c_vp, c_vp, c_sz, c_i, c_i, c_i, c_vp, c_vp, c_vp]),
+    "quber_rle_decode_workspace_bytes": (c_sz, [c_sz]),
+    "quber_rle_decode": (c_i, [c_vp, c_vp, c_sz, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp, c_vp]),
+    "quber_rle_encode_workspace_bytes": (c_sz, [c_i, c_i, c_i, c_sz]),
+    "quber_rle_encode": (c_i, [c_vp, c_i, c_i, c_i, c_vp, c_sz, c_vp, c_vp, c_sz, c_vp, c_vp]),
+    "quber_rle_from_string": (ctypes.c_longlong, [ctypes.c_char_p, c_sz, c_vp, c_sz]),
+    "quber_rle_to_string": (ctypes.c_longlong, [c_vp, c_sz, c_vp, c_sz]),
     "quber_msda_forward": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
 }
 

@@ -582,6 +582,83 @@ def fuse_concat_rows(sources, ops_, pitch=None, out_dtype=torch.bfloat16):
     return out
 
 
+
+def rle_decode(counts, offsets, n, H, W, value=1, packed=False, out=None, check=False):
+    """pycocotools.mask.decode on the device (perturbed_panoptic_dataset_mapper.py:195-214): `counts` uint32-as-int32
+    CUDA tensor holding the run lengths of `n` masks back to back (column-major runs, starting with zeros), `offsets`
+    int64 CUDA [n+1] -> ROW-major masks: uint8 [n,H,W] (0 / value), or with packed=True int32 [n*H*W/32] words
+    (bit i of word w = pixel 32 w + i; W % 32 == 0), the input of encode_initial_masks_packed.
+    Returns (masks, status int32 CUDA [1]); check=True synchronises and raises if some counts do not sum to H*W."""
+    _need_cuda(counts, "counts", torch.int32)
+    _need_cuda(offsets, "offsets", torch.int64)
+    if offsets.numel() != n + 1:
+        raise ValueError("offsets must have n + 1 entries")
+    dev = counts.device
+    if out is None:
+        out = (torch.empty(n * H * W // 32, dtype=torch.int32, device=dev) if packed
+               else torch.empty((n, H, W), dtype=torch.uint8, device=dev))
+    else:
+        _need_cuda(out, "out", torch.int32 if packed else torch.uint8)
+        if out.numel() * (32 if packed else 1) != n * H * W:
+            raise ValueError("out does not match n*H*W")
+    if packed and W % 32:
+        raise ValueError("packed RLE decode needs W % 32 == 0")
+    L = _lib.lib()
+    nbytes = L.quber_rle_decode_workspace_bytes(counts.numel())
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    status = torch.empty(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(L.quber_rle_decode(_ptr(counts), _ptr(offsets), counts.numel(), int(n), int(H), int(W), int(value),
+                                      _ptr(out) if packed else None, None if packed else _ptr(out), _ptr(ws), nbytes,
+                                      _ptr(status), _stream()), "quber_rle_decode")
+    if check and int(status[0]) & 1:
+        raise ValueError("RLE counts do not sum to H*W")
+    return out, status
+
+
+def rle_encode(masks, cap=None):
+    """pycocotools.mask.encode on the device (tools/ours/panoptic2eee.py:61-64,125-132): masks uint8 CUDA [n,H,W]
+    (non-zero = set) -> (counts int32 CUDA [cap] holding uint32 run lengths, offsets int64 CUDA [n+1], status int32 [1]).
+    `cap` = capacity of the counts buffer (default: 4 runs per column and mask + 2, which every blob-like mask fits;
+    status bit 1 is set when it was too small and offsets[n] then holds the capacity needed)."""
+    _need_cuda(masks, "masks", torch.uint8)
+    n, H, W = masks.shape
+    dev = masks.device
+    if cap is None:
+        cap = n * (4 * W + 2)
+    counts = torch.empty(int(cap), dtype=torch.int32, device=dev)
+    offsets = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    status = torch.empty(1, dtype=torch.int32, device=dev)
+    L = _lib.lib()
+    nbytes = L.quber_rle_encode_workspace_bytes(n, H, W, int(cap))
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(L.quber_rle_encode(_ptr(masks), n, H, W, _ptr(counts), int(cap), _ptr(offsets), _ptr(ws), nbytes,
+                                      _ptr(status), _stream()), "quber_rle_encode")
+    return counts, offsets, status
+
+
+def rle_from_string(s):
+    """HOST: compressed COCO RLE string (bytes / str) -> uint32 numpy counts (maskApi.c rleFrString)."""
+    if isinstance(s, str):
+        s = s.encode("ascii")
+    out = np.empty(max(len(s), 1), np.uint32)
+    m = _lib.lib().quber_rle_from_string(s, len(s), out.ctypes.data_as(ctypes.c_void_p), out.size)
+    if m < 0:
+        raise ValueError("malformed RLE string")
+    return out[:m].copy()
+
+
+def rle_to_string(counts):
+    """HOST: uint32 counts -> compressed COCO RLE bytes (maskApi.c rleToString)."""
+    counts = np.ascontiguousarray(counts, np.uint32)
+    buf = ctypes.create_string_buffer(7 * counts.size + 1)
+    n = _lib.lib().quber_rle_to_string(counts.ctypes.data_as(ctypes.c_void_p), counts.size, buf, len(buf))
+    if n < 0 or n >= len(buf):
+        raise ValueError("rle_to_string failed")
+    return buf.raw[:n]
+
+
 # ---- torch.library registration: torch.ops.quber.* ----------------------------------------------
 def _register():
     try:

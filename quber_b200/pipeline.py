@@ -103,24 +103,28 @@ class HotPath:
 
     # --- end to end: host buffers in, host results out ------------------------------------------
     def _staging(self, masks_host, head_host):
+        return self._staging_shape(tuple(masks_host.shape), head_host)
+
+    def _staging_shape(self, shape, head_host):
         """Persistent device staging buffers, pinned result buffers, copy streams and events, keyed by shape."""
         ldt = torch.uint8 if self.cfg.compact_label_map and self.cfg.top_k <= 255 else torch.int32
-        key = (tuple(masks_host.shape), ldt) + tuple((k, tuple(v.shape)) for k, v in sorted(head_host.items()))
+        key = (tuple(shape), ldt) + tuple((k, tuple(v.shape)) for k, v in sorted(head_host.items()))
         st = getattr(self, "_stage", None)
         if st is None or st["key"] != key:
             dev = self.device
-            B, K, H, W = masks_host.shape
+            B, K, H, W = shape
+            numel = B * K * H * W
             slab = self.slab
             pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
-            st = dict(key=key, masks=torch.empty(masks_host.shape, dtype=torch.uint8, device=dev),
+            st = dict(key=key, masks=torch.empty(shape, dtype=torch.uint8, device=dev),
                       head={k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in head_host.items()},
                       h2d=torch.cuda.Stream(device=dev), d2h=torch.cuda.Stream(device=dev), free=None,
-                      packed_host=pin((masks_host.numel() + 31) // 32, torch.int32),
-                      packed_dev=torch.empty((masks_host.numel() + 31) // 32, dtype=torch.int32, device=dev), copied={},
+                      packed_host=pin((numel + 31) // 32, torch.int32),
+                      packed_dev=torch.empty((numel + 31) // 32, dtype=torch.int32, device=dev), copied={},
                       graphs={},
                       out=dict(label_map=pin((B, H, W), ldt), boundary=pin((B, H, W), torch.uint8),
                                inst_start=pin((B,), torch.int32), inst_counts=pin((B,), torch.int32),
-                               status=pin((1,), torch.int32), labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
+                               status=pin((1,), torch.int32), rle_status=pin((1,), torch.int32), labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
                                boxes=pin((B * slab, 4), torch.float32)))
             self._stage = st
         return st
@@ -309,4 +313,74 @@ class HotPath:
         st["free"] = cur.record_event()
         cur.wait_stream(d2h)
         self._keep = keep                         # device results stay alive until the next call replaces them
+        return out, keep
+
+    def refine_batch_rle(self, counts_host, offsets_host, shape, head_host, value=255, out_host=None, kernel_frames=16):
+        """The end-to-end call with the initial masks in the form the reference's datasets hold them: COCO run-length
+        encodings (register_uoais_sim_panoptic.py:121-144 -> mask_util.decode at
+        perturbed_panoptic_dataset_mapper.py:195-214).  counts_host: pinned int32 [total] (uint32 run lengths of the
+        B*K masks back to back, `rle.pack_rles`), offsets_host: pinned int64 [B*K+1], shape = (B, K, H, W); head_host as
+        refine_batch_host.  ~0.6 MB cross the host link instead of 295 MB (C2): quber_rle_decode writes the bit-packed
+        planes that the encode pass reads anyway.  Same results and result layout as refine_batch_host."""
+        dev = self.device
+        B, K, H, W = shape
+        if W % 32:
+            raise ValueError("refine_batch_rle needs W % 32 == 0 (decode the RLEs with ops.rle_decode and use the dense call)")
+        st = self._staging_shape((B, K, H, W), head_host)
+        out = st["out"] if out_host is None else out_host
+        cur = torch.cuda.current_stream(dev)
+        h2d, d2h = st["h2d"], st["d2h"]
+        slab = self.slab
+        if st["free"] is not None:
+            h2d.wait_event(st["free"])
+        d2h.wait_stream(cur)
+        n = B * K
+        total = int(counts_host.numel())
+        if st.get("rle_cap", 0) < total:
+            st["rle_counts"] = torch.empty(max(total * 2, 1 << 16), dtype=torch.int32, device=dev)
+            st["rle_offsets"] = torch.empty(n + 1, dtype=torch.int64, device=dev)
+            st["rle_cap"] = st["rle_counts"].numel()
+        with torch.cuda.stream(h2d):
+            for k, v in head_host.items():
+                st["head"][k].copy_(v, non_blocking=True)
+            heads_ready = h2d.record_event()
+            st["rle_counts"][:total].copy_(counts_host, non_blocking=True)
+            st["rle_offsets"].copy_(offsets_host, non_blocking=True)
+            rle_ready = h2d.record_event()
+        st["copied"]["heads"] = heads_ready
+        cur.wait_event(heads_ready)
+        r = self._run_graphed(st, "post", lambda: self.post(st["head"]))
+        off = r["inst_offsets"]
+        start, counts = off[:-1], off[1:] - off[:-1]
+        post_done = cur.record_event()
+        with torch.cuda.stream(d2h):
+            d2h.wait_event(post_done)
+            out["label_map"].copy_(r["label_map"], non_blocking=True)
+            out["inst_start"].copy_(start, non_blocking=True)
+            out["inst_counts"].copy_(counts, non_blocking=True)
+            out["status"].copy_(r["status"], non_blocking=True)
+            out["labels"].copy_(r["labels"][:B * slab], non_blocking=True)
+            out["scores"].copy_(r["scores"][:B * slab], non_blocking=True)
+            out["boxes"].copy_(r["boxes"][:B * slab], non_blocking=True)
+        cur.wait_event(rle_ready)
+        _, rle_status = ops.rle_decode(st["rle_counts"][:total], st["rle_offsets"], n, H, W, value=value, packed=True,
+                                       out=st["packed_dev"])
+        keep = []
+        fw = K * H * W // 32
+        step = kernel_frames if kernel_frames and kernel_frames < B else B
+        for g0 in range(0, B, step):
+            g1 = min(B, g0 + step)
+            enc, per, uni, fg = self._run_graphed(
+                st, (g0, g1, value), lambda: self.encode_and_boundary_packed(st, g0, g1, g0 * fw, g1 * fw, value))
+            done = cur.record_event()
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(done)
+                out["boundary"][g0:g1].copy_(uni, non_blocking=True)
+            keep.append((enc, per, r, start[g0:g1], counts[g0:g1]))
+        with torch.cuda.stream(d2h):
+            d2h.wait_event(cur.record_event())
+            out["rle_status"].copy_(rle_status, non_blocking=True)
+        st["free"] = cur.record_event()
+        cur.wait_stream(d2h)
+        self._keep = keep
         return out, keep

@@ -291,3 +291,35 @@ def test_refine_batch_host_kernel_groups_and_uint8_label_map(B, chunk, tail, kf,
         assert torch.equal(o0["boundary"], o1["boundary"])
         assert torch.equal(torch.cat([k[1] for k in k1]), torch.cat([k[1] for k in k0]))
         assert torch.equal(hp._stage["masks"], hm2.cuda())
+
+
+@pytest.mark.parametrize("B,K,H,W,kf", [(5, 7, 240, 320, 2), (8, 30, 480, 640, 0)])
+def test_refine_batch_rle_equals_dense_host_call(B, K, H, W, kf):
+    """The RLE route (counts over the host link, quber_rle_decode on the device) gives the dense call's results bit for
+    bit; the RLEs come from the oracle's encoder as compressed strings, parsed by quber_rle_from_string."""
+    from quber_b200 import rle
+    masks, head = _inputs(B, K, H, W, seed=700)
+    rles = [{"size": [H, W], "counts": oracle.rle_to_string(oracle.rle_encode(m))} for m in masks.reshape(-1, H, W)]
+    counts, offsets, hw = rle.pack_rles(rles)
+    assert hw == (H, W) and counts.nbytes < masks.nbytes // 100
+    hc, ho = torch.from_numpy(counts).pin_memory(), torch.from_numpy(offsets).pin_memory()
+    hm = torch.from_numpy(masks).pin_memory()
+    hh = {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}
+    dense, sparse = HotPath(RefinerConfig(), "cuda"), HotPath(RefinerConfig(), "cuda")
+    o0, k0 = dense.refine_batch_host(hm, hh, chunk_frames=max(B // 2, 1))
+    torch.cuda.current_stream().synchronize()
+    o0 = {k: v.clone() for k, v in o0.items()}
+    for rep in range(3):                                    # graph replays, staging reuse
+        o1, k1 = sparse.refine_batch_rle(hc, ho, (B, K, H, W), hh, value=255, kernel_frames=kf)
+        torch.cuda.current_stream().synchronize()
+        assert int(o1["rle_status"][0]) == 0 and int(o1["status"][0]) == 0
+        assert torch.equal(sparse._stage["masks"], hm.cuda())
+        for key in ("label_map", "boundary", "inst_start", "inst_counts"):
+            assert torch.equal(o0[key], o1[key]), key
+        for b in range(B):
+            s0, n = int(o0["inst_start"][b]), int(o0["inst_counts"][b])
+            for key in ("labels", "scores", "boxes"):
+                assert torch.equal(o0[key][s0:s0 + n], o1[key][s0:s0 + n]), (key, b)
+    enc0 = torch.cat([k[0] for k in k0]); enc1 = torch.cat([k[0] for k in k1])
+    assert torch.equal(enc0, enc1)
+    np.testing.assert_array_equal(enc1[B - 1].cpu().numpy(), oracle.encode_initial_masks(masks[B - 1]))
