@@ -167,7 +167,8 @@ int quber_post_process(const quber_post_params *p, const quber_post_io *io, void
  * K1  MSDeformAttn forward — replaces MultiScaleDeformableAttention.ms_deform_attn_forward
  *     (OPS/src/vision.cpp:18-21 -> OPS/src/cuda/ms_deform_attn_cuda.cu:25-85 ->
  *     OPS/src/cuda/ms_deform_im2col_cuda.cuh:242-304).
- *   value   dev [B,S,M,D]      float32 (dtype 0) or bfloat16 (dtype 1)
+ *   value   dev [B,S,M,D]      float32 (dtype 0), bfloat16 (dtype 1) or float64 (dtype 2: loc, attn and out are then
+ *                              float64 as well — the reference dispatches both floating types, ms_deform_attn_cuda.cu:69)
  *   shapes  dev [L,2] int64 (H_l, W_l);  starts dev [L] int64  — int64 as in the reference API
  *   loc     dev [B,Q,M,L,P,2]  float32 (x,y) in [0,1];  attn dev [B,Q,M,L,P] float32
  *   out     dev [B,Q,M*D]      float32 (dtype 0) / bfloat16 (dtype 1)
@@ -178,6 +179,18 @@ int quber_post_process(const quber_post_params *p, const quber_post_io *io, void
 int quber_msda_forward(const void *value, const int64_t *shapes, const int64_t *starts, const float *loc,
                        const float *attn, int B, int S, int M, int D, int L, int Q, int P, int dtype,
                        void *out, void *stream);
+/* The same sampling with MSDeformAttn.forward's operand arithmetic (OPS/modules/ms_deform_attn.py:102-117) inside the
+ * kernel's set-up phase: no loc / attn tensors, no preparation pass.
+ *   oa                dev [B*Q, ld] float32 — the output rows of ONE GEMM over the concatenated sampling_offsets |
+ *                     attention_weights Linear layers: columns [0, M*L*P*2) = offsets in (m, l, p, xy) order,
+ *                     [M*L*P*2, M*L*P*3) = attention logits in (m, l, p) order (ld >= M*L*P*3, even)
+ *   reference_points  dev [B*Q, L, 2] float32 (x, y) in [0,1]
+ *   loc = reference_points + offsets / (W_l, H_l) (:106-109), attention = softmax over L*P (:104-105), then as
+ *   quber_msda_forward.  P == 4, L <= 4 and D*sizeof(value) a multiple of 64 bytes; QUBER_E_UNSUPPORTED otherwise
+ *   (callers then use quber_msda_prepare + quber_msda_forward). */
+int quber_msda_forward_fused(const void *value, const int64_t *shapes, const int64_t *starts, const float *oa, int ld,
+                             const float *reference_points, int B, int S, int M, int D, int L, int Q, int P, int dtype,
+                             void *out, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Network glue that is pure bandwidth (csrc/fusion.cu).
@@ -224,6 +237,17 @@ int quber_fuse_concat_rows(const void *const *sources, const int *channels, cons
 int quber_gemm_bias_act(const void *A, const void *W, const float *bias, void *C, int M, int N, int K, int lda,
                         int ldw, int ldc, int in_dtype, int out_dtype, int act, void *stream);
 int quber_gemm_timeouts(void);
+/* fp32-accurate variant ("3xTF32", split operands): the reference runs these layers in fp32
+ * (`autocast(enabled=False)`, MSMF/modeling/pixel_decoder/msdeformattn.py:314; nn.Linear -> cuBLAS sgemm).  Each fp32
+ * operand is split into hi (its top 19 bits, what kind::tf32 reads) and lo = x - hi, and
+ * A W^T ~= A_hi W_hi^T + A_hi W_lo^T + A_lo W_hi^T is accumulated in one fp32 TMEM tile (three tcgen05.mma per k-step);
+ * relative error ~2^-21 of sum |a||w|, against 2^-10 for a single TF32 product.
+ * quber_split_tf32: w dev [n] float32 -> hi, lo dev [n] float32 (once per weight).
+ * quber_gemm_bias_act_x3: as quber_gemm_bias_act with float32 A [M,K] (split inside the kernel, in shared memory) and
+ *   the pre-split weight W_hi / W_lo dev [N,K] (pitch ldw). */
+int quber_split_tf32(const float *w, size_t n, float *hi, float *lo, void *stream);
+int quber_gemm_bias_act_x3(const float *A, const float *W_hi, const float *W_lo, const float *bias, void *C, int M, int N, int K,
+                           int lda, int ldw, int ldc, int out_dtype, int act, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * GroupNorm (+ ReLU), inference forward — replaces nn.GroupNorm(G, C) followed by ReLU wherever the network uses

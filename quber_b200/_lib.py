@@ -46,6 +46,8 @@ SYMBOLS = {
     "quber_tma_timeouts": (c_i, []),
     "quber_gemm_bias_act": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp]),
     "quber_gemm_timeouts": (c_i, []),
+    "quber_split_tf32": (c_i, [c_vp, c_sz, c_vp, c_vp, c_vp]),
+    "quber_gemm_bias_act_x3": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp]),
     "quber_pack_input": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_fuse_concat": (c_i, [c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_fuse_concat_rows": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_sz, c_i, c_i, c_vp, c_vp]),
@@ -69,6 +71,7 @@ SYMBOLS = {
     "quber_rle_encode": (c_i, [c_vp, c_i, c_i, c_i, c_vp, c_sz, c_vp, c_vp, c_sz, c_vp, c_vp]),
     "quber_rle_from_string": (ctypes.c_longlong, [ctypes.c_char_p, c_sz, c_vp, c_sz]),
     "quber_rle_to_string": (ctypes.c_longlong, [c_vp, c_sz, c_vp, c_sz]),
+    "quber_msda_forward_fused": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_msda_forward": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
 }
 

@@ -17,6 +17,15 @@
 //            tcgen05.commit frees the smem stage / signals the epilogue
 //   warps 2-5  epilogue: tcgen05.ld (32 lanes x 32 columns per instruction) -> + bias -> activation ->
 //            128B-swizzled staging in the (now dead) pipeline stages -> TMA store of 32-row x 128-byte boxes
+//
+// fp32-accurate mode (SPLIT, "3xTF32"): the reference runs these layers in fp32 (`autocast(enabled=False)`,
+// msdeformattn.py:314) and a single TF32 product only carries 10 mantissa bits.  Every fp32 operand is split into
+// hi = its top 19 bits (what the tensor core reads of an fp32 word) and lo = x - hi (exact in fp32), and
+//   A W^T ~= A_hi W_hi^T + A_hi W_lo^T + A_lo W_hi^T          (the lo * lo term is 2^-22 relative and dropped)
+// is accumulated in the same fp32 TMEM tile by three tcgen05.mma per k-step.  W_hi / W_lo are prepared once per weight
+// (quber_split_tf32); A is split IN SHARED MEMORY by the otherwise idle epilogue warps between the TMA's arrival and the
+// MMA issue (the transform is elementwise, so it is oblivious of the 128B swizzle), so A still crosses HBM once.
+// These GEMMs sit at 85 FLOP/B (N = K = 256), far below the ridge, which is why three times the MMAs cost little.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -76,25 +85,29 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
     return d;
 }
 
-template <int BN, bool TF32, typename OT>
+template <int BN, bool TF32, typename OT, bool SPLIT = false>
 __global__ void __launch_bounds__(G_THREADS)
 gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
-                     const __grid_constant__ CUtensorMap map_c, const float *__restrict__ bias, int M, int N, int K, int act) {
+                     const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_c,
+                     const float *__restrict__ bias, int M, int N, int K, int act) {
+    static_assert(!SPLIT || TF32, "the split mode is an fp32 mode");
+    constexpr int NST = SPLIT ? 2 : G_STAGES;           // SPLIT stages hold A_hi | A_lo | W_hi | W_lo: twice the bytes
     extern __shared__ __align__(1024) unsigned char gsm_raw[];
     // SWIZZLE_128B tiles must sit on 1024-byte boundaries of the SHARED address space
     unsigned char *gsm = gsm_raw + ((1024u - (g_smem_u32(gsm_raw) & 1023u)) & 1023u);
-    __shared__ __align__(8) uint64_t full[G_STAGES], empty[G_STAGES], tmem_full;
+    __shared__ __align__(8) uint64_t full[G_STAGES], empty[G_STAGES], conv[G_STAGES], tmem_full;
     __shared__ uint32_t tmem_base_s;
     __shared__ float bias_s[BN];
     __shared__ int abort_s;
-    constexpr int A_BYTES = G_BM * G_KBYTES, W_BYTES = BN * G_KBYTES, STAGE = A_BYTES + W_BYTES;
+    constexpr int A_BYTES = G_BM * G_KBYTES, W_BYTES = BN * G_KBYTES, STAGE = (SPLIT ? 2 : 1) * (A_BYTES + W_BYTES);
+    constexpr int W_OFF = (SPLIT ? 2 : 1) * A_BYTES;    // stage layout: A [| A_lo] | W [| W_lo]
     constexpr int KELEMS = TF32 ? 32 : 64;              // elements of K per stage
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * G_BM, n0 = blockIdx.x * BN;   // N tiles fastest: neighbours share the A tile in L2
     const int nkb = (K + KELEMS - 1) / KELEMS;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < G_STAGES; ++s) { g_mbar_init(&full[s], 1); g_mbar_init(&empty[s], 1); }
+        for (int s = 0; s < G_STAGES; ++s) { g_mbar_init(&full[s], 1); g_mbar_init(&empty[s], 1); g_mbar_init(&conv[s], G_THREADS - 64); }
         g_mbar_init(&tmem_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         abort_s = 0;
@@ -113,12 +126,13 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         if (lane == 0) {
             // ===== TMA producer =====
             for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb % G_STAGES;
-                if (kb >= G_STAGES && !g_mbar_wait(&empty[s], ((kb / G_STAGES) - 1) & 1)) { abort_s = 1; break; }
-                unsigned char *sa = gsm + (size_t)s * STAGE, *sw = sa + A_BYTES;
-                g_mbar_expect_tx(&full[s], STAGE);
+                const int s = kb % NST;
+                if (kb >= NST && !g_mbar_wait(&empty[s], ((kb / NST) - 1) & 1)) { abort_s = 1; break; }
+                unsigned char *sa = gsm + (size_t)s * STAGE, *sw = sa + W_OFF;
+                g_mbar_expect_tx(&full[s], A_BYTES + (SPLIT ? 2 : 1) * W_BYTES);
                 g_tma_load_2d(sa, &map_a, &full[s], kb * KELEMS, m0);
                 g_tma_load_2d(sw, &map_w, &full[s], kb * KELEMS, n0);
+                if (SPLIT) g_tma_load_2d(sw + W_BYTES, &map_wlo, &full[s], kb * KELEMS, n0);
             }
         }
     } else if (warp == 1) {
@@ -130,15 +144,23 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(G_BM >> 4) << 24);
             bool ok = true;
             for (int kb = 0; kb < nkb && ok; ++kb) {
-                const int s = kb % G_STAGES;
-                ok = g_mbar_wait(&full[s], (kb / G_STAGES) & 1);
+                const int s = kb % NST;
+                ok = g_mbar_wait(SPLIT ? &conv[s] : &full[s], (kb / NST) & 1);      // SPLIT: the converter warps have written A_hi / A_lo
                 if (!ok) { abort_s = 1; break; }
                 tc_fence_after();
-                const uint32_t sa = g_smem_u32(gsm + (size_t)s * STAGE), sw = sa + A_BYTES;
+                const uint32_t sa = g_smem_u32(gsm + (size_t)s * STAGE), sw = sa + W_OFF;
                 const uint64_t ad = umma_desc_k128(sa), wd = umma_desc_k128(sw);
 #pragma unroll
-                for (int k = 0; k < G_KBYTES / 32; ++k)          // 32 bytes of K per instruction: +2 in the 16-byte address field
-                    tc_mma(tmem_d, ad + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, TF32);
+                for (int k = 0; k < G_KBYTES / 32; ++k) {        // 32 bytes of K per instruction: +2 in the 16-byte address field
+                    if (SPLIT) {                                 // small terms first, then hi * hi
+                        const uint64_t ald = umma_desc_k128(sa + A_BYTES), wld = umma_desc_k128(sw + W_BYTES);
+                        tc_mma(tmem_d, ald + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, 1);
+                        tc_mma(tmem_d, ad + 2 * k, wld + 2 * k, idesc, 1, 1);
+                        tc_mma(tmem_d, ad + 2 * k, wd + 2 * k, idesc, 1, 1);
+                    } else {
+                        tc_mma(tmem_d, ad + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, TF32);
+                    }
+                }
                 tc_commit(&empty[s]);                            // frees the stage when these MMAs have read it
             }
             tc_commit(&tmem_full);                               // accumulator complete (or abort: release the epilogue)
@@ -151,6 +173,30 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         // edge are clipped by the hardware.  Two staging buffers per warp: the store of chunk c overlaps the
         // TMEM read of chunk c + 1.
         const int q = warp & 3;
+        if (SPLIT) {
+            // ===== operand split (warps 2..5 = 128 threads): A -> A_hi (in place), A_lo, 16 KB per stage, elementwise =====
+            const int t = threadIdx.x - 64;
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % NST;
+                if (!g_mbar_wait(&full[s], (kb / NST) & 1)) { abort_s = 1; break; }
+                uint4 *pa = reinterpret_cast<uint4 *>(gsm + (size_t)s * STAGE), *pl = pa + A_BYTES / 16;
+#pragma unroll
+                for (int i = 0; i < A_BYTES / 16 / (G_THREADS - 64); ++i) {
+                    const uint4 v = pa[i * (G_THREADS - 64) + t];
+                    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        hi[j] = w[j] & 0xffffe000u;                                       // the 19 bits kind::tf32 reads
+                        lo[j] = __float_as_uint(__fsub_rn(__uint_as_float(w[j]), __uint_as_float(hi[j])));   // exact
+                    }
+                    pa[i * (G_THREADS - 64) + t] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                    pl[i * (G_THREADS - 64) + t] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");             // generic-proxy writes -> tensor-core reads
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(g_smem_u32(&conv[s])) : "memory");
+            }
+        }
         const bool ok = g_mbar_wait(&tmem_full, 0);
         tc_fence_after();
         if (ok && !abort_s) {
@@ -244,15 +290,26 @@ static bool gemm_map(CUtensorMap *m, const void *base, int rows, int K, int ld, 
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int BN, bool TF32, typename OT>
-static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUtensorMap &mc, const float *bias, int M, int N, int K,
-                       int act, cudaStream_t st) {
-    const size_t smem = (size_t)G_STAGES * (G_BM + BN) * G_KBYTES + 1024;
-    QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_bias_act_kernel<BN, TF32, OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+template <int BN, bool TF32, typename OT, bool SPLIT = false>
+static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUtensorMap &mwlo, const CUtensorMap &mc, const float *bias,
+                       int M, int N, int K, int act, cudaStream_t st) {
+    const size_t smem = (SPLIT ? (size_t)2 * 2 : (size_t)G_STAGES) * (G_BM + BN) * G_KBYTES + 1024;
+    QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_bias_act_kernel<BN, TF32, OT, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (cdiv(M, G_BM) > 65535) return QUBER_E_UNSUPPORTED;
     dim3 grid(cdiv(N, BN), cdiv(M, G_BM));
-    gemm_bias_act_kernel<BN, TF32, OT><<<grid, G_THREADS, smem, st>>>(ma, mw, mc, bias, M, N, K, act);
+    gemm_bias_act_kernel<BN, TF32, OT, SPLIT><<<grid, G_THREADS, smem, st>>>(ma, mw, mwlo, mc, bias, M, N, K, act);
     return check_launch("gemm_bias_act_kernel");
+}
+
+// w -> hi = w with the 13 low mantissa bits cleared (what kind::tf32 reads), lo = w - hi (exact)
+__global__ void __launch_bounds__(256)
+split_tf32_kernel(const float *__restrict__ w, size_t n, float *__restrict__ hi, float *__restrict__ lo) {
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
+        const float x = w[i];
+        const float h = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+        hi[i] = h;
+        lo[i] = __fsub_rn(x, h);
+    }
 }
 
 }  // namespace quber
@@ -280,7 +337,7 @@ extern "C" int quber_gemm_bias_act(const void *A, const void *W, const float *bi
         return QUBER_E_CUDA;
     }
     cudaStream_t st = (cudaStream_t)stream;
-#define QG(BN_, TF_, OT_) return gemm_launch<BN_, TF_, OT_>(ma, mw, mc, bias, M, N, K, act, st)
+#define QG(BN_, TF_, OT_) return gemm_launch<BN_, TF_, OT_>(ma, mw, mw, mc, bias, M, N, K, act, st)
     if (BN == 128) {
         if (tf32) { if (out_dtype == 0) QG(128, true, float); else QG(128, true, __nv_bfloat16); }
         else      { if (out_dtype == 0) QG(128, false, float); else QG(128, false, __nv_bfloat16); }
@@ -289,4 +346,38 @@ extern "C" int quber_gemm_bias_act(const void *A, const void *W, const float *bi
         else      { if (out_dtype == 0) QG(64, false, float); else QG(64, false, __nv_bfloat16); }
     }
 #undef QG
+}
+
+extern "C" int quber_split_tf32(const float *w, size_t n, float *hi, float *lo, void *stream) {
+    using namespace quber;
+    if (!w || !hi || !lo || n == 0) return QUBER_E_INVALID;
+    const unsigned blocks = (unsigned)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184);
+    split_tf32_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, n, hi, lo);
+    return check_launch("split_tf32_kernel");
+}
+
+extern "C" int quber_gemm_bias_act_x3(const float *A, const float *W_hi, const float *W_lo, const float *bias, void *C, int M, int N,
+                                      int K, int lda, int ldw, int ldc, int out_dtype, int act, void *stream) {
+    using namespace quber;
+    if (!A || !W_hi || !W_lo || !C || M <= 0 || N <= 0 || K <= 0) return QUBER_E_INVALID;
+    if ((out_dtype != 0 && out_dtype != 1) || (act != 0 && act != 1)) return QUBER_E_INVALID;
+    const int os = out_dtype == 0 ? 4 : 2;
+    if (lda < K || ldw < K || ldc < N) return QUBER_E_INVALID;
+    if (!aligned16(A) || !aligned16(W_hi) || !aligned16(W_lo) || !aligned16(C) || ((size_t)lda * 4) % 16 || ((size_t)ldw * 4) % 16 ||
+        ((size_t)ldc * os) % 16)
+        return QUBER_E_ALIGN;
+    const int BN = (N % 128 == 0 || N > 192) ? 128 : 64;
+    CUtensorMap ma, mw, mwl, mc;
+    if (!gemm_map(&ma, A, M, K, lda, G_BM, 4) || !gemm_map(&mw, W_hi, N, K, ldw, BN, 4) || !gemm_map(&mwl, W_lo, N, K, ldw, BN, 4) ||
+        !gemm_map(&mc, C, M, N, ldc, 32, os)) {
+        set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
+        return QUBER_E_CUDA;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (BN == 128) {
+        if (out_dtype == 0) return gemm_launch<128, true, float, true>(ma, mw, mwl, mc, bias, M, N, K, act, st);
+        return gemm_launch<128, true, __nv_bfloat16, true>(ma, mw, mwl, mc, bias, M, N, K, act, st);
+    }
+    if (out_dtype == 0) return gemm_launch<64, true, float, true>(ma, mw, mwl, mc, bias, M, N, K, act, st);
+    return gemm_launch<64, true, __nv_bfloat16, true>(ma, mw, mwl, mc, bias, M, N, K, act, st);
 }

@@ -25,7 +25,6 @@
 // resident warps, not loads in flight; 2-D query patches 585.  Kept: the variant with the fewest
 // instructions per gathered byte (558).
 #include <cuda_bf16.h>
-#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -332,11 +331,177 @@ msda_forward_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__
     }
 }
 
-// Any D (the reference's own mapping: one thread per output scalar), fp32 only.
+
+// ------------------------------------------------------------------------------------------------
+// MSDeformAttn.forward between its Linear layers and the output projection in ONE kernel
+// (OPS/modules/ms_deform_attn.py:102-117 + OPS/src/cuda/ms_deform_im2col_cuda.cuh:242-304): the set-up phase of the
+// one-record kernel above reads the fused sampling_offsets | attention_weights GEMM output row directly
+//   oa [B*Q, ld] = [offsets (M, L, P, 2) | logits (M, L, P)]
+// does the softmax over the L*P logits of its (query, head) inside the lane group (two shuffle reductions) and
+//   loc = reference_points[:, :, None, :, None, :] + offsets / (W_l, H_l)                       (:106-109)
+// with the module's own arithmetic (IEEE division, then the add), then samples as above.  The separate preparation
+// pass (quber_msda_prepare: 464 MB of traffic and 110 us per layer at C2) and the loc / attn tensors disappear; the
+// bytes this kernel reads are the same (288 floats per row either way).
+// ------------------------------------------------------------------------------------------------
+template <int D, typename VT, int MINB, int L>
+__global__ void __launch_bounds__(256, MINB)
+msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
+                     const float *__restrict__ oa, int ld, const float *__restrict__ ref, int S, int M, int Q,
+                     VT *__restrict__ out) {
+    constexpr int P = 4, VB = 16;
+    constexpr int NW = VB / 4;
+    constexpr int CPL = VB / (int)sizeof(VT);
+    constexpr int LPG = D / CPL;
+    static_assert(LPG >= 1 && LPG <= 32 && (LPG % P == 0 || P % LPG == 0), "a round of LPG taps must stay level-aligned");
+    constexpr int LP = L * P;
+    constexpr int NR = (LP + LPG - 1) / LPG;            // rounds of LPG taps
+    constexpr int NLR = LPG >= P ? LPG / P : 1;         // levels per round
+    constexpr int GPB = 256 / LPG;
+    constexpr int GPW = 32 / LPG;
+    __shared__ int s_h[MSDA_MAX_L], s_w[MSDA_MAX_L], s_start[MSDA_MAX_L];
+    __shared__ __align__(16) uint4 s_rec[8 * GPW * (LPG + 1)];
+    const int tid = threadIdx.x;
+    const int lane = tid % LPG, grp = tid / LPG;
+    const int m = blockIdx.y, b = blockIdx.z;
+    const int MD = M * D;
+    if (tid < L) {
+        s_h[tid] = (int)__ldg(shapes + 2 * tid);
+        s_w[tid] = (int)__ldg(shapes + 2 * tid + 1);
+        s_start[tid] = (int)__ldg(starts + tid);
+    }
+    __syncthreads();
+    const int qreal = blockIdx.x * GPB + grp;
+    const int q = min(qreal, Q - 1);
+    const size_t row = (size_t)b * Q + q;
+    const float *orow = oa + row * (size_t)ld;
+    const float *offp = orow + (size_t)m * LP * 2;                   // (l, p, xy) of this head
+    const float *lgp = orow + (size_t)M * LP * 2 + (size_t)m * LP;   // (l, p) logits of this head
+    const float *refp = ref + row * L * 2;
+    const char *vlane = reinterpret_cast<const char *>(value + (size_t)b * S * MD + m * D) + lane * VB;
+    asm volatile("" : "+l"(vlane));
+    const uint32_t MDu = MD / CPL;
+    // first round's offsets and reference point are requested before the softmax's shuffles
+    uint2 raw_off = make_uint2(0u, 0u), raw_ref = make_uint2(0u, 0u);
+    if (lane < LP) { raw_off = ld_stream_u2(offp + 2 * lane); raw_ref = ld_stream_u2(refp + 2 * (lane / P)); }
+    // softmax over the L*P logits of (query, head): lane t holds taps t, t + LPG, ...   (ms_deform_attn.py:104-105)
+    float aw[NR];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const int tap = r * LPG + lane;
+        aw[r] = tap < LP ? __uint_as_float(ld_stream_u1(lgp + tap)) : -INFINITY;
+        mx = fmaxf(mx, aw[r]);
+    }
+#pragma unroll
+    for (int o = LPG / 2; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o, LPG));
+    float sum = 0.f;
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        aw[r] = (r * LPG + lane < LP) ? expf(aw[r] - mx) : 0.f;
+        sum += aw[r];
+    }
+#pragma unroll
+    for (int o = LPG / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o, LPG);
+    const float inv = 1.0f / sum;
+    float acc[CPL];
+#pragma unroll
+    for (int c = 0; c < CPL; ++c) acc[c] = 0.f;
+    uint4 *rec = s_rec + (tid >> 5) * (GPW * (LPG + 1)) + ((tid & 31) / LPG) * (LPG + 1);
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const int s0 = r * LPG;
+        const int tap = s0 + lane;
+        uint32_t o1 = 0;
+        float A = 0.f, Bw = 0.f, f = 0.f;
+        if (tap < LP) {
+            const int l = tap / P;
+            const int h = s_h[l], w = s_w[l];
+            const float lx = __fadd_rn(__uint_as_float(raw_ref.x), __fdiv_rn(__uint_as_float(raw_off.x), (float)w));   // :106-109
+            const float ly = __fadd_rn(__uint_as_float(raw_ref.y), __fdiv_rn(__uint_as_float(raw_off.y), (float)h));
+            const float him = ly * h - 0.5f, wim = lx * w - 0.5f;                              // cuh:290-291
+            if (him > -1.f && wim > -1.f && him < (float)h && wim < (float)w) {               // cuh:293
+                const float a = aw[r] * inv;
+                const int hl = (int)floorf(him), wl = (int)floorf(wim);
+                const float lh = him - hl, lw = wim - wl, hh = 1.f - lh, hw = 1.f - lw;
+                const bool y0 = hl >= 0, y1 = hl + 1 <= h - 1, x0 = wl >= 0, x1 = wl + 1 <= w - 1;
+                const int ry0 = max(hl, 0), cx0 = max(wl, 0);
+                const bool xb = x0 && x1, yb = y0 && y1;
+                const float ag = xb ? a : a * (x0 ? hw : lw);
+                f = xb ? lw : 0.f;
+                A = y0 ? hh * ag : 0.f;
+                Bw = y1 ? lh * ag : 0.f;
+                o1 = ((uint32_t)(s_start[l] + ry0 * w + cx0) * MDu) | (xb ? 0x80000000u : 0u) | (yb ? 0x40000000u : 0u);
+            }
+        }
+        if (r + 1 < NR && tap + LPG < LP) {
+            raw_off = ld_stream_u2(offp + 2 * (tap + LPG));
+            raw_ref = ld_stream_u2(refp + 2 * ((tap + LPG) / P));
+        }
+        const int nt = min(LPG, LP - s0);
+        uint32_t pitch[NLR];
+#pragma unroll
+        for (int k = 0; k < NLR; ++k) pitch[k] = (uint32_t)s_w[min(s0 / P + k, L - 1)] * MDu;
+        rec[lane] = make_uint4(o1, __float_as_uint(A), __float_as_uint(Bw), __float_as_uint(f));
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < LPG; ++j) {
+            if (j < nt) {
+                const uint4 ra = rec[j];
+                const uint32_t dx = (uint32_t)((int32_t)ra.x >> 31) & MDu;
+                const uint32_t dy = (uint32_t)((int32_t)(ra.x << 1) >> 31) & pitch[j / P];
+                uint32_t a1 = ra.x & 0x3fffffffu;
+                asm volatile("" : "+r"(a1));
+                const uint32_t a3 = a1 + dy;
+                const float bf = __uint_as_float(ra.w), bg = 1.f - bf;
+                const float b1 = __uint_as_float(ra.y) * bg, b2 = __uint_as_float(ra.y) * bf;
+                const float b3 = __uint_as_float(ra.z) * bg, b4 = __uint_as_float(ra.z) * bf;
+                uint32_t r1[NW], r2[NW], r3[NW], r4[NW];
+                ld_corner<VB>(vlane + (size_t)a1 * VB, r1);
+                ld_corner<VB>(vlane + (size_t)(a1 + dx) * VB, r2);
+                ld_corner<VB>(vlane + (size_t)a3 * VB, r3);
+                ld_corner<VB>(vlane + (size_t)(a3 + dx) * VB, r4);
+                fma_corner<VT, NW>(b1, r1, acc); fma_corner<VT, NW>(b2, r2, acc);
+                fma_corner<VT, NW>(b3, r3, acc); fma_corner<VT, NW>(b4, r4, acc);
+            }
+        }
+        __syncwarp();
+    }
+    if (qreal < Q) {
+        VT *o = out + (row * M + m) * D + lane * CPL;
+        if constexpr (sizeof(VT) == 4) {
+#pragma unroll
+            for (int c = 0; c < CPL; c += 4) st_stream_f4(o + c, make_float4(acc[c], acc[c + 1], acc[c + 2], acc[c + 3]));
+        } else {
+#pragma unroll
+            for (int c = 0; c < CPL; c += 8) Lane<__nv_bfloat16>::store(o + c, acc + c);
+        }
+    }
+}
+
+template <int D, typename VT>
+static int launch_fused(const void *value, const int64_t *shapes, const int64_t *starts, const float *oa, int ld, const float *ref,
+                        int B, int S, int M, int L, int Q, void *out, cudaStream_t st) {
+    constexpr int GPB = 256 / (D * (int)sizeof(VT) / 16);
+    const dim3 grid(cdiv(Q, GPB), M, B);
+    const VT *v = static_cast<const VT *>(value);
+    VT *o = static_cast<VT *>(out);
+    switch (L) {
+        case 1: msda_fused_p4_kernel<D, VT, 5, 1><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o); break;
+        case 2: msda_fused_p4_kernel<D, VT, 5, 2><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o); break;
+        case 3: msda_fused_p4_kernel<D, VT, 5, 3><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o); break;
+        case 4: msda_fused_p4_kernel<D, VT, 5, 4><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o); break;
+        default: return QUBER_E_UNSUPPORTED;
+    }
+    return check_launch("msda_fused_p4_kernel");
+}
+
+// Any D, any P, float32 or float64 (the reference dispatches both, ms_deform_attn_cuda.cu:69): the reference's own
+// mapping, one thread per output scalar, evaluated entirely in T.
+template <typename T>
 __global__ void __launch_bounds__(256)
-msda_forward_scalar_kernel(const float *__restrict__ value, const int64_t *__restrict__ shapes,
-                           const int64_t *__restrict__ starts, const float *__restrict__ loc, const float *__restrict__ attn,
-                           size_t n, int S, int M, int D, int L, int Q, int P, float *__restrict__ out) {
+msda_forward_scalar_kernel(const T *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
+                           const T *__restrict__ loc, const T *__restrict__ attn, size_t n, int S, int M, int D, int L, int Q, int P,
+                           T *__restrict__ out) {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= n) return;
     const int c = idx % D;
@@ -344,87 +509,47 @@ msda_forward_scalar_kernel(const float *__restrict__ value, const int64_t *__res
     const int m = qm % M;
     const size_t b = qm / M / Q;
     const int MD = M * D;
-    float col = 0.f;
+    T col = 0;
     for (int l = 0; l < L; ++l) {
         const int h = (int)shapes[2 * l], w = (int)shapes[2 * l + 1];
-        const float *v = value + (b * S + (size_t)starts[l]) * MD + m * D + c;
+        const T *v = value + (b * S + (size_t)starts[l]) * MD + m * D + c;
         for (int pt = 0; pt < P; ++pt) {
             const size_t lpi = (qm * L + l) * P + pt;
-            const float lw_ = loc[2 * lpi], lh_ = loc[2 * lpi + 1], a = attn[lpi];
-            const float him = lh_ * h - 0.5f, wim = lw_ * w - 0.5f;
-            if (!(him > -1.f && wim > -1.f && him < (float)h && wim < (float)w)) continue;
-            const int hl = (int)floorf(him), wl = (int)floorf(wim);
-            const float lh = him - hl, lw = wim - wl, hh = 1.f - lh, hw = 1.f - lw;
-            float v1 = 0, v2 = 0, v3 = 0, v4 = 0;
+            const T lw_ = loc[2 * lpi], lh_ = loc[2 * lpi + 1], a = attn[lpi];
+            const T him = lh_ * h - T(0.5), wim = lw_ * w - T(0.5);                        // cuh:290-291
+            if (!(him > T(-1) && wim > T(-1) && him < (T)h && wim < (T)w)) continue;       // cuh:293
+            const int hl = (int)floor(him), wl = (int)floor(wim);
+            const T lh = him - hl, lw = wim - wl, hh = T(1) - lh, hw = T(1) - lw;
+            T v1 = 0, v2 = 0, v3 = 0, v4 = 0;
             if (hl >= 0 && wl >= 0) v1 = v[((size_t)hl * w + wl) * MD];
             if (hl >= 0 && wl + 1 <= w - 1) v2 = v[((size_t)hl * w + wl + 1) * MD];
             if (hl + 1 <= h - 1 && wl >= 0) v3 = v[((size_t)(hl + 1) * w + wl) * MD];
             if (hl + 1 <= h - 1 && wl + 1 <= w - 1) v4 = v[((size_t)(hl + 1) * w + wl + 1) * MD];
-            col += (hh * hw * v1 + hh * lw * v2 + lh * hw * v3 + lh * lw * v4) * a;
+            col += (hh * hw * v1 + hh * lw * v2 + lh * hw * v3 + lh * lw * v4) * a;        // cuh:85, :297
         }
     }
     out[idx] = col;
 }
 
-// Resident CTAs per SM the gather kernel is compiled for: the L1 data pipe is the limit and throughput follows the
-// number of resident warps (ncu), so the default is the highest occupancy that does not spill.  QUBER_MSDA_MINB
-// (4 | 5 | 6, read once) overrides it for tuning runs.
-static int msda_minb() {
-    static const int v = [] {
-        const char *e = getenv("QUBER_MSDA_MINB");
-        const int x = e ? atoi(e) : 0;
-        return (x >= 3 && x <= 6) ? x : 0;               // 0: the variant's own default
-    }();
-    return v;
-}
-
+// One variant per shape class in the shipped library (the A/B switches of round 1 live in git history and
+// profiles/r01_msda_variants_*.log): P == 4 and a head of >= 64 bytes -> the one-record kernel (fp32 486 us, bf16
+// 354 us per launch at C2); anything else with a vectorisable head -> the two-record shared-memory broadcast.
+// 5 resident CTAs per SM: the L1 data pipe is the limit and throughput follows the number of resident warps.
 template <int D, typename VT>
 static int launch_vec(const void *value, const int64_t *shapes, const int64_t *starts, const float *loc, const float *attn,
                       int B, int S, int M, int L, int Q, int P, void *out, cudaStream_t st) {
     constexpr int GPB = 256 / (D / Lane<VT>::CPL);
-    dim3 grid(cdiv(Q, GPB), M, B);
+    const dim3 grid(cdiv(Q, GPB), M, B);
     const VT *v = static_cast<const VT *>(value);
     VT *o = static_cast<VT *>(out);
-    // Default: the one-record kernel when P == 4 (fp32 486 us, bf16 354 us per launch at C2), else the two-record
-    // shared-memory broadcast (497 / 366).  QUBER_MSDA_BCAST = lds | shfl | rec4 | wide forces a variant for A/B runs
-    // (wide = 256-bit corner loads, half as many lanes per group: 500 / 433 us — more bytes per lane in flight did not
-    // help, nor did letting the compiler overlap the taps of a level at 4 or 3 CTAs/SM: 505 / 541 us).
-    static const char mode = [] { const char *e = getenv("QUBER_MSDA_BCAST"); return e ? e[0] : '\0'; }();
-    const bool shfl = mode == 's';
     constexpr int DB = D * (int)sizeof(VT);             // bytes of one head's channels
-    if constexpr (DB % 64 == 0) {                       // >= 4 lanes of 16 bytes, >= 2 lanes of 32 bytes
-        if (P == 4 && mode != 'l' && mode != 's') {
-            constexpr int G16 = 256 / (DB / 16), G32 = 256 / (DB / 32);
-            const dim3 g16(cdiv(Q, G16), M, B), g32(cdiv(Q, G32), M, B);
-            if (mode != 'w') {
-                switch (msda_minb()) {
-                    default: msda_forward_p4_kernel<D, VT, 5, 16><<<g16, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
-                    case 6: msda_forward_p4_kernel<D, VT, 6, 16><<<g16, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
-                    case 4: msda_forward_p4_kernel<D, VT, 4, 16><<<g16, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
-                }
-            } else {
-                switch (msda_minb()) {
-                    default: msda_forward_p4_kernel<D, VT, 4, 32><<<g32, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
-                    case 5: msda_forward_p4_kernel<D, VT, 5, 32><<<g32, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
-                    case 3: msda_forward_p4_kernel<D, VT, 3, 32><<<g32, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o); break;
-                }
-            }
+    if constexpr (DB % 64 == 0) {
+        if (P == 4) {
+            msda_forward_p4_kernel<D, VT, 5, 16><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, o);
             return check_launch("msda_forward_p4_kernel");
         }
     }
-    if (!shfl) {
-        switch (msda_minb()) {
-            default: msda_forward_kernel<D, VT, 5, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
-            case 6: msda_forward_kernel<D, VT, 6, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
-            case 4: msda_forward_kernel<D, VT, 4, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
-        }
-        return check_launch("msda_forward_kernel");
-    }
-    switch (msda_minb()) {
-        default: msda_forward_kernel<D, VT, 5, false><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
-        case 6: msda_forward_kernel<D, VT, 6, false><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
-        case 4: msda_forward_kernel<D, VT, 4, false><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o); break;
-    }
+    msda_forward_kernel<D, VT, 5, true><<<grid, 256, 0, st>>>(v, shapes, starts, loc, attn, S, M, L, Q, P, o);
     return check_launch("msda_forward_kernel");
 }
 
@@ -436,9 +561,16 @@ extern "C" int quber_msda_forward(const void *value, const int64_t *shapes, cons
     using namespace quber;
     if (!value || !shapes || !starts || !loc || !attn || !out) return QUBER_E_INVALID;
     if (B <= 0 || S <= 0 || M <= 0 || D <= 0 || L <= 0 || L > MSDA_MAX_L || Q <= 0 || P <= 0) return QUBER_E_INVALID;
-    if (dtype != 0 && dtype != 1) return QUBER_E_INVALID;
+    if (dtype != 0 && dtype != 1 && dtype != 2) return QUBER_E_INVALID;
     if (M > 65535 || B > 65535 || (long long)S * M * D >= (1ll << 31)) return QUBER_E_UNSUPPORTED;
     cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == 2) {                                    // float64: value, loc, attn and out are all double
+        const size_t n = (size_t)B * Q * M * D;
+        msda_forward_scalar_kernel<double><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+            static_cast<const double *>(value), shapes, starts, reinterpret_cast<const double *>(loc),
+            reinterpret_cast<const double *>(attn), n, S, M, D, L, Q, P, static_cast<double *>(out));
+        return check_launch("msda_forward_scalar_kernel<double>");
+    }
     const bool vec_ok = aligned16(value) && aligned16(out) && ((reinterpret_cast<uintptr_t>(loc) & 7u) == 0);
     if (dtype == 1) {
         if (!vec_ok) return QUBER_E_ALIGN;
@@ -460,7 +592,35 @@ extern "C" int quber_msda_forward(const void *value, const int64_t *shapes, cons
         }
     }
     const size_t n = (size_t)B * Q * M * D;
-    msda_forward_scalar_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+    msda_forward_scalar_kernel<float><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
         static_cast<const float *>(value), shapes, starts, loc, attn, n, S, M, D, L, Q, P, static_cast<float *>(out));
     return check_launch("msda_forward_scalar_kernel");
+}
+
+extern "C" int quber_msda_forward_fused(const void *value, const int64_t *shapes, const int64_t *starts, const float *oa, int ld,
+                                        const float *reference_points, int B, int S, int M, int D, int L, int Q, int P,
+                                        int dtype, void *out, void *stream) {
+    using namespace quber;
+    if (!value || !shapes || !starts || !oa || !reference_points || !out) return QUBER_E_INVALID;
+    if (B <= 0 || S <= 0 || M <= 0 || D <= 0 || L <= 0 || Q <= 0 || P <= 0 || ld < M * L * P * 3) return QUBER_E_INVALID;
+    if (dtype != 0 && dtype != 1) return QUBER_E_INVALID;
+    if (P != 4 || L > 4) return QUBER_E_UNSUPPORTED;                  // callers fall back to quber_msda_prepare + quber_msda_forward
+    if (M > 65535 || B > 65535 || (long long)S * M * D >= (1ll << 31)) return QUBER_E_UNSUPPORTED;
+    if (!aligned16(value) || !aligned16(out) || (reinterpret_cast<uintptr_t>(oa) & 7u) || (ld & 1) ||
+        (reinterpret_cast<uintptr_t>(reference_points) & 7u))
+        return QUBER_E_ALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == 1) {
+        switch (D) {
+            case 32: return launch_fused<32, __nv_bfloat16>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
+            case 64: return launch_fused<64, __nv_bfloat16>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
+            default: return QUBER_E_UNSUPPORTED;
+        }
+    }
+    switch (D) {
+        case 16: return launch_fused<16, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
+        case 32: return launch_fused<32, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
+        case 64: return launch_fused<64, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
+        default: return QUBER_E_UNSUPPORTED;
+    }
 }

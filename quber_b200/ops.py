@@ -211,21 +211,25 @@ def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=No
 def msda_forward(value, spatial_shapes, level_start_index, sampling_locations, attention_weights, im2col_step=None):
     """MultiScaleDeformableAttention.ms_deform_attn_forward (OPS/src/vision.cpp:18-21).
 
-    value [B,S,M,D] float32 | bfloat16, spatial_shapes [L,2] int64, level_start_index [L] int64,
-    sampling_locations [B,Q,M,L,P,2] float32, attention_weights [B,Q,M,L,P] float32 -> [B,Q,M*D] (value dtype).
+    value [B,S,M,D] float32 | bfloat16 | float64, spatial_shapes [L,2] int64, level_start_index [L] int64,
+    sampling_locations [B,Q,M,L,P,2] and attention_weights [B,Q,M,L,P] float32 (float64 with a float64 value)
+    -> [B,Q,M*D] (value dtype).
     `im2col_step` is accepted for signature compatibility and ignored (the batch is one launch).
     """
     _need_cuda(value, "value")
     _need_cuda(spatial_shapes, "spatial_shapes", torch.int64)
     _need_cuda(level_start_index, "level_start_index", torch.int64)
-    _need_cuda(sampling_locations, "sampling_loc", torch.float32)
-    _need_cuda(attention_weights, "attn_weight", torch.float32)
     if value.dtype == torch.float32:
         dt = 0
     elif value.dtype == torch.bfloat16:
         dt = 1
+    elif value.dtype == torch.float64:        # real fp64, as the reference's AT_DISPATCH_FLOATING_TYPES (ms_deform_attn_cuda.cu:69)
+        dt = 2
     else:
-        raise ValueError(f"value must be float32 or bfloat16, got {value.dtype}")
+        raise ValueError(f"value must be float32, float64 or bfloat16, got {value.dtype}")
+    aux = torch.float64 if dt == 2 else torch.float32
+    _need_cuda(sampling_locations, "sampling_loc", aux)
+    _need_cuda(attention_weights, "attn_weight", aux)
     B, S, M, D = value.shape
     _, Q, _, Lv, P, _ = sampling_locations.shape
     out = torch.empty((B, Q, M * D), dtype=value.dtype, device=value.device)
@@ -233,6 +237,38 @@ def msda_forward(value, spatial_shapes, level_start_index, sampling_locations, a
         _lib.check(_lib.lib().quber_msda_forward(_ptr(value), _ptr(spatial_shapes), _ptr(level_start_index),
                                                  _ptr(sampling_locations), _ptr(attention_weights), B, S, M, D, Lv, Q, P, dt,
                                                  _ptr(out), _stream()), "quber_msda_forward")
+    return out
+
+
+def msda_fused_supported(value, n_levels, n_points):
+    """True when quber_msda_forward_fused takes this shape (P == 4, L <= 4, a head of a multiple of 64 bytes)."""
+    D = value.shape[-1]
+    return (n_points == 4 and n_levels <= 4 and value.dtype in (torch.float32, torch.bfloat16)
+            and (D * value.element_size()) % 64 == 0 and D in (16, 32, 64))
+
+
+def msda_forward_fused(value, spatial_shapes, level_start_index, oa, reference_points, n_levels, n_points):
+    """MSDeformAttn.forward between its Linear layers and the output projection in one kernel
+    (OPS/modules/ms_deform_attn.py:102-117 + ms_deform_attn_forward): value [N,S,M,D] float32 | bfloat16, oa [N,Q,ld]
+    float32 = the fused sampling_offsets | attention_weights GEMM output, reference_points [N,Q,L,2] float32
+    -> [N,Q,M*D] in value's dtype.  The softmax and `ref + off / (W_l, H_l)` happen in the kernel's set-up phase."""
+    _need_cuda(value, "value")
+    _need_cuda(spatial_shapes, "spatial_shapes", torch.int64)
+    _need_cuda(level_start_index, "level_start_index", torch.int64)
+    _need_cuda(oa, "oa", torch.float32)
+    _need_cuda(reference_points, "reference_points", torch.float32)
+    if not msda_fused_supported(value, n_levels, n_points):
+        raise ValueError("msda_forward_fused: unsupported shape (needs P == 4, L <= 4, D in {16, 32, 64})")
+    N, S, M, D = value.shape
+    Q, ld = oa.shape[1], oa.shape[2]
+    if oa.shape[0] != N or ld < M * n_levels * n_points * 3 or tuple(reference_points.shape) != (N, Q, n_levels, 2):
+        raise ValueError("msda_forward_fused: oa must be [N,Q,>=M*L*P*3] and reference_points [N,Q,L,2]")
+    out = torch.empty((N, Q, M * D), dtype=value.dtype, device=value.device)
+    with torch.cuda.device(value.device):
+        _lib.check(_lib.lib().quber_msda_forward_fused(_ptr(value), _ptr(spatial_shapes), _ptr(level_start_index), _ptr(oa), ld,
+                                                       _ptr(reference_points), N, S, M, D, n_levels, Q, n_points,
+                                                       0 if value.dtype == torch.float32 else 1, _ptr(out), _stream()),
+                   "quber_msda_forward_fused")
     return out
 
 
@@ -273,6 +309,47 @@ def gemm_bias_act(a, weight, bias=None, act="none", out_dtype=None):
                                                       weight.stride(0), N, 1 if a.dtype == torch.bfloat16 else 2,
                                                       0 if out_dtype == torch.float32 else 1, 1 if act == "relu" else 0,
                                                       _stream()), "quber_gemm_bias_act")
+    return out.reshape(tuple(a.shape[:-1]) + (N,))
+
+
+def split_tf32(w):
+    """fp32 CUDA tensor -> (hi, lo): hi = w with the 13 low mantissa bits cleared (what a TF32 tensor-core product
+    reads), lo = w - hi (exact).  The pre-split weight of gemm_bias_act_x3."""
+    _need_cuda(w, "w", torch.float32)
+    hi, lo = torch.empty_like(w), torch.empty_like(w)
+    with torch.cuda.device(w.device):
+        _lib.check(_lib.lib().quber_split_tf32(_ptr(w), w.numel(), _ptr(hi), _ptr(lo), _stream()), "quber_split_tf32")
+    return hi, lo
+
+
+def gemm_bias_act_x3(a, w_hi, w_lo, bias=None, act="none", out_dtype=torch.float32):
+    """C = act(a @ W.T + bias) at fp32 accuracy on the TF32 tensor cores (three split-operand products,
+    quber_gemm_bias_act_x3): a [..., K] float32, (w_hi, w_lo) = split_tf32(W [N,K])."""
+    _need_cuda(w_hi, "w_hi", torch.float32)
+    _need_cuda(w_lo, "w_lo", torch.float32)
+    if not isinstance(a, torch.Tensor) or not a.is_cuda or a.dtype != torch.float32:
+        raise ValueError("a must be a float32 CUDA tensor")
+    K, N = a.shape[-1], w_hi.shape[0]
+    if w_hi.dim() != 2 or w_hi.shape[1] != K or w_lo.shape != w_hi.shape:
+        raise ValueError(f"w_hi / w_lo must be [N, {K}]")
+    a2 = a.reshape(-1, K)
+    if a2.stride(1) != 1:
+        a2 = a2.contiguous()
+    M = a2.shape[0]
+    if out_dtype not in (torch.float32, torch.bfloat16):
+        raise ValueError("out_dtype must be float32 or bfloat16")
+    if bias is not None:
+        _need_cuda(bias, "bias", torch.float32)
+        if bias.numel() != N:
+            raise ValueError("bias must have N elements")
+    if act not in ("none", "relu"):
+        raise ValueError("act must be 'none' or 'relu'")
+    out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    if M > 0:
+        with torch.cuda.device(a.device):
+            _lib.check(_lib.lib().quber_gemm_bias_act_x3(_ptr(a2), _ptr(w_hi), _ptr(w_lo), _ptr(bias), _ptr(out), M, N, K, a2.stride(0),
+                                                         w_hi.stride(0), N, 0 if out_dtype == torch.float32 else 1,
+                                                         1 if act == "relu" else 0, _stream()), "quber_gemm_bias_act_x3")
     return out.reshape(tuple(a.shape[:-1]) + (N,))
 
 

@@ -9,11 +9,11 @@ cfg.MODEL.SEM_SEG_HEAD.PIXEL_DECODER_NAME == "MSDeformAttnPixelDecoder" (maskref
 What runs where, per encoder layer (rows = B * S tokens, S = sum of level pixels):
   sampling_offsets + attention_weights Linear (ONE GEMM on the concatenated [288, 256] weight — both read
   query = src + pos), value_proj, output_proj, FFN linear1 (+ReLU) / linear2   -> quber_gemm_bias_act (tcgen05)
-  multi-scale bilinear sampling                                             -> quber_msda_forward
-  softmax over L*P, reference-point arithmetic, residual + LayerNorm          -> torch elementwise
-`precision`: "fp32" = torch fp32 Linear layers (bit-for-bit the reference's arithmetic up to cuBLAS) + fp32 sampling;
-"tf32" = tcgen05 kind::tf32 GEMMs on the fp32 tensors; "bf16" = bf16 GEMMs, bf16 value tensor and bf16 sampling
-(fp32 weights / accumulation inside the sampler).  Dropout layers are kept for state-dict / repr parity; inference only.
+  softmax over L*P, reference-point arithmetic, multi-scale bilinear sampling -> quber_msda_forward_fused (one kernel)
+  residual + LayerNorm (+ the next layer's operands)                          -> quber_add_layer_norm
+`precision`: "fp32" (the reference's, `autocast(enabled=False)` msdeformattn.py:314) = split-operand 3xTF32 tcgen05 GEMMs
+(fp32 accuracy, quber_gemm_bias_act_x3) + fp32 sampling; "tf32" = one kind::tf32 product per GEMM; "bf16" = bf16 GEMMs,
+bf16 value tensor and bf16 sampling (fp32 weights / accumulation inside the sampler).  No cuBLAS call on any of them.  Dropout layers are kept for state-dict / repr parity; inference only.
 """
 import math
 
@@ -23,6 +23,7 @@ import torch.nn.functional as F
 from torch import nn
 
 from . import ops
+from .linear import PackedLinear
 from .msda import MSDeformAttn
 from .network import Conv2d, get_norm
 
@@ -89,7 +90,6 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
         self.dropout3 = nn.Dropout(dropout)
         self.norm2 = nn.LayerNorm(d_model)
         self.precision = "fp32"
-        self._packed = None
 
     @staticmethod
     def with_pos_embed(tensor, pos):
@@ -100,57 +100,39 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
         src = src + self.dropout3(src2)
         return self.norm2(src)
 
-    # ---- tcgen05 route ------------------------------------------------------------------------------------
-    def _weights(self, dtype):
-        """Linear weights in the GEMM's input dtype; sampling_offsets and attention_weights concatenated."""
-        if self._packed is None or self._packed[0] != dtype:
-            a = self.self_attn
-            cat_w = torch.cat([a.sampling_offsets.weight, a.attention_weights.weight], 0)
-            cat_b = torch.cat([a.sampling_offsets.bias, a.attention_weights.bias], 0)
-            f = lambda w: w.detach().to(dtype).contiguous()
-            g = lambda b: b.detach().float().contiguous()
-            self._packed = (dtype, dict(qk=(f(cat_w), g(cat_b)), v=(f(a.value_proj.weight), g(a.value_proj.bias)),
-                                        o=(f(a.output_proj.weight), g(a.output_proj.bias)),
-                                        l1=(f(self.linear1.weight), g(self.linear1.bias)),
-                                        l2=(f(self.linear2.weight), g(self.linear2.bias))))
-        return self._packed[1]
+    # ---- kernels (every precision; there is no cuBLAS / torch route on the GPU) -----------------------------
+    def _ffn(self):
+        p = self.__dict__.get("_ffn_packed")
+        if p is None:
+            p = dict(l1=PackedLinear(self.linear1), l2=PackedLinear(self.linear2))
+            self.__dict__["_ffn_packed"] = p
+        return p
 
     def _forward_kernels(self, src, pos, reference_points, spatial_shapes, level_start_index, padding_mask, pre=None,
                          emit_next=False):
-        """`pre` = (x, q) already in the GEMM dtype, written by the previous layer's last LayerNorm pass; `emit_next`
-        asks this layer's last LayerNorm for the same pair (returned as the second value)."""
+        """msdeformattn.py:122-131 on this repo's kernels.  `pre` = (x, q) already in the GEMM dtype, written by the
+        previous layer's last LayerNorm pass; `emit_next` asks this layer's last LayerNorm for the same pair (returned
+        as the second value)."""
         a = self.self_attn
-        bf16 = self.precision == "bf16"
+        prec = self.precision
+        a.precision = prec
+        bf16 = prec == "bf16"
         dt = torch.bfloat16 if bf16 else torch.float32
-        W = self._weights(dt)
+        pk, ffn = a._packs(), self._ffn()
         N, S, C = src.shape
-        M, L, P = a.n_heads, a.n_levels, a.n_points
+        M = a.n_heads
         if pre is not None:
             x, q = pre
         else:
             q = self.with_pos_embed(src, pos).to(dt)
             x = src.to(dt)
-        value = ops.gemm_bias_act(x, *W["v"], out_dtype=dt)                                   # ms_deform_attn.py:98
+        value = pk["v"](x, prec, out_dtype=dt)                                                # ms_deform_attn.py:98
         if padding_mask is not None:
             value = value.masked_fill(padding_mask[..., None], float(0))
-        oa = ops.gemm_bias_act(q, *W["qk"], out_dtype=torch.float32)                          # :102-103, one GEMM
-        n_off = M * L * P * 2
-        if reference_points.shape[-1] == 2 and reference_points.dtype == torch.float32:
-            # offsets / (W_l, H_l) + reference, and the softmax over L*P, in one pass over the GEMM output
-            loc, aw = ops.msda_prepare(oa.view(N, S, -1), reference_points.contiguous(), spatial_shapes, M, L, P)
-        else:
-            off = oa[..., :n_off].reshape(N, S, M, L, P, 2)
-            aw = F.softmax(oa[..., n_off:].reshape(N, S, M, L * P), -1).view(N, S, M, L, P).contiguous()
-            if reference_points.shape[-1] == 2:                                               # :106-109
-                normalizer = torch.stack([spatial_shapes[..., 1], spatial_shapes[..., 0]], -1)
-                loc = reference_points[:, :, None, :, None, :] + off / normalizer[None, None, None, :, None, :]
-            elif reference_points.shape[-1] == 4:
-                loc = reference_points[:, :, None, :, None, :2] + off / P * reference_points[:, :, None, :, None, 2:] * 0.5
-            else:
-                raise ValueError('Last dim of reference_points must be 2 or 4, but get {} instead.'.format(reference_points.shape[-1]))
-            loc = loc.contiguous()
-        samp = ops.msda_forward(value.view(N, S, M, C // M), spatial_shapes, level_start_index, loc, aw)
-        src2 = ops.gemm_bias_act(samp, *W["o"], out_dtype=torch.float32)                      # :124
+        oa = pk["qk"](q, prec, out_dtype=torch.float32)                                       # :102-103, one GEMM
+        # softmax over L*P, ref + off / (W_l, H_l) and the sampling in ONE kernel (:104-117)
+        samp = a.sample(value.view(N, S, M, C // M), oa.view(N, S, -1), reference_points, spatial_shapes, level_start_index)
+        src2 = pk["o"](samp, prec, out_dtype=torch.float32)                                   # :124
         fused_ln = C % 128 == 0 and C <= 1024 and C // 128 not in (5, 7)
         if fused_ln:                                                                          # norm1(src + src2), one pass
             r = ops.add_layer_norm(src.contiguous(), src2.view(N, S, C), self.norm1.weight, self.norm1.bias, self.norm1.eps, want_bf16=bf16)
@@ -160,14 +142,14 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
         if self.activation_name != "relu":
             out = self.forward_ffn(src)
             return (out, None) if emit_next else out
-        hmid = ops.gemm_bias_act(src16 if src16 is not None else src.to(dt), *W["l1"], act="relu", out_dtype=dt)   # msdeformattn.py:116-120
-        src2 = ops.gemm_bias_act(hmid, *W["l2"], out_dtype=torch.float32)
+        hmid = ffn["l1"](src16 if src16 is not None else src, prec, act="relu", out_dtype=dt)  # msdeformattn.py:116-120
+        src2 = ffn["l2"](hmid, prec, out_dtype=torch.float32)
         if not emit_next:
             if fused_ln:
                 return ops.add_layer_norm(src, src2.view(N, S, C), self.norm2.weight, self.norm2.bias, self.norm2.eps)
             return self.norm2(src + src2)
         if fused_ln and pos is not None and pos.dtype == torch.float32 and pos.shape == src.shape:
-            # norm2 also writes the next layer's operands: x (bf16 copy; the fp32 result itself in tf32) and q = x + pos
+            # norm2 also writes the next layer's operands: x (bf16 copy; the fp32 result itself otherwise) and q = x + pos
             r = ops.add_layer_norm(src, src2.view(N, S, C), self.norm2.weight, self.norm2.bias, self.norm2.eps, want_bf16=bf16,
                                    pos=pos.contiguous(), q_dtype=dt)
             return r[0], ((r[1], r[2]) if bf16 else (r[0], r[1]))
@@ -176,12 +158,9 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
         return out, None
 
     def forward(self, src, pos, reference_points, spatial_shapes, level_start_index, padding_mask=None):
-        if self.precision != "fp32" and src.is_cuda:
-            return self._forward_kernels(src, pos, reference_points, spatial_shapes, level_start_index, padding_mask)
-        src2 = self.self_attn(self.with_pos_embed(src, pos), reference_points, src, spatial_shapes, level_start_index, padding_mask)
-        src = src + self.dropout1(src2)
-        src = self.norm1(src)
-        return self.forward_ffn(src)
+        if not src.is_cuda:
+            raise RuntimeError("Not implemented on the CPU")          # as the op itself (OPS/src/ms_deform_attn.h:43)
+        return self._forward_kernels(src, pos, reference_points, spatial_shapes, level_start_index, padding_mask)
 
 
 class MSDeformAttnTransformerEncoder(nn.Module):
@@ -210,7 +189,7 @@ class MSDeformAttnTransformerEncoder(nn.Module):
         reference_points = self.get_reference_points(shapes, valid_ratios, device=src.device)
         pre = None
         for i, layer in enumerate(self.layers):
-            if layer.precision != "fp32" and output.is_cuda:
+            if output.is_cuda:
                 nxt = i + 1 < len(self.layers) and self.layers[i + 1].precision == layer.precision
                 r = layer._forward_kernels(output, pos, reference_points, spatial_shapes, level_start_index, padding_mask,
                                            pre=pre, emit_next=nxt)

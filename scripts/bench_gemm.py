@@ -27,3 +27,18 @@ for name, M, N, K in cases:
         us_t = t(lambda: torch.relu_(torch.nn.functional.linear(a, w, b.to(dt))))
         kind = ("bf16" if dt == torch.bfloat16 else "tf32") + "->" + ("bf16" if od == torch.bfloat16 else "f32")
         print(f"{name:30s} {M}x{N}x{K} {kind}: {us:7.1f} us  {2*M*N*K/us/1e6:6.1f} TFLOP/s  {byt/us/1e3:5.0f} GB/s   cuBLAS linear+relu_: {us_t:7.1f} us", flush=True)
+
+# fp32-accurate split-operand mode (3xTF32) against cuBLAS sgemm (TF32 disabled)
+torch.backends.cuda.matmul.allow_tf32 = False
+for name, M, N, K in cases[:4]:
+    a = torch.randn(M, K, device="cuda"); a2 = torch.randn(M, K, device="cuda")
+    w = torch.randn(N, K, device="cuda") / K ** 0.5; b = torch.randn(N, device="cuda")
+    hi, lo = ops.split_tf32(w)
+    it = [0]
+    def f():
+        it[0] ^= 1
+        ops.gemm_bias_act_x3(a if it[0] else a2, hi, lo, b, act="relu")
+    us = t(f)
+    us_t = t(lambda: torch.relu_(torch.nn.functional.linear(a, w, b)))
+    byt = M * K * 4 + 2 * N * K * 4 + M * N * 4
+    print(f"{name:30s} {M}x{N}x{K} 3xTF32->f32: {us:7.1f} us  {2*M*N*K/us/1e6:6.1f} TFLOP/s (x3 issued)  {byt/us/1e3:5.0f} GB/s   cuBLAS sgemm+relu_: {us_t:7.1f} us", flush=True)

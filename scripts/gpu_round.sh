@@ -19,7 +19,8 @@ for s in $STEPS; do
     full*)  RX=${s#full}; RX=${RX#:}; RX=${RX:-msda|boundary|encode|group|emit|nms|rle}
             timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-network > gpurun_out/plain_f_$TAG.log 2>&1 &&
             timeout 900 ncu --set full --clock-control none --import-source on -k regex:"$RX" -s 40 -c 14 -o gpurun_out/full_$TAG -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-network > gpurun_out/ncu_f_$TAG.log 2>&1; tail -2 gpurun_out/ncu_f_$TAG.log ;;
-    extra)  for f in bench_msda bench_gemm bench_encoder bench_norm; do [ -f scripts/$f.py ] && timeout 300 python scripts/$f.py > gpurun_out/${f}_$TAG.txt 2>&1; tail -6 gpurun_out/${f}_$TAG.txt; done ;;
+    extra)  for f in bench_msda bench_gemm bench_encoder bench_norm; do [ -f scripts/$f.py ] && timeout 300 python scripts/$f.py > gpurun_out/${f}_$TAG.txt 2>&1; grep -v "^-\|^ *Name\|^Self\|cudaLaunch\|^$" gpurun_out/${f}_$TAG.txt | head -30; done
+            timeout 300 python scripts/bench_msda.py 32 bf16 > gpurun_out/bench_msda_bf16_$TAG.txt 2>&1; cat gpurun_out/bench_msda_bf16_$TAG.txt ;;
     *) echo "unknown step $s" ;;
   esac
 done

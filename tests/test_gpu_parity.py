@@ -608,3 +608,89 @@ def test_c2_all_32_frames_against_oracle():
         np.testing.assert_array_equal(uni[b], u)
         np.testing.assert_array_equal(fg[b], f)
         _check_post(r, post, H, W, b=b)
+
+
+# ------------------------------------------------------------------ round 2: fused MSDA, fp64 MSDA, 3xTF32 GEMM
+@pytest.mark.parametrize("D,dt", [(32, "f32"), (16, "f32"), (64, "f32"), (32, "bf16"), (64, "bf16")])
+@pytest.mark.parametrize("L", [1, 3, 4])
+def test_msda_fused_equals_prepare_plus_forward_and_oracle(D, dt, L):
+    """quber_msda_forward_fused (softmax + ref + off / (W,H) in the set-up phase) against the two-kernel route and, with
+    torch's softmax / location arithmetic in between, the oracle.  OPS/modules/ms_deform_attn.py:102-117."""
+    shapes_l = [(15, 20), (8, 10), (4, 5), (2, 3)][:L]
+    g = torch.Generator(device=DEV).manual_seed(100 * D + L)
+    N, M, P, Q = 2, 8, 4, 777
+    shapes = torch.tensor(shapes_l, dtype=torch.long, device=DEV)
+    starts = torch.cat((shapes.new_zeros((1,)), shapes.prod(1).cumsum(0)[:-1]))
+    S = int(shapes.prod(1).sum())
+    value = torch.rand(N, S, M, D, device=DEV, generator=g) * 0.01
+    oa = torch.randn(N, Q, M * L * P * 3, device=DEV, generator=g) * 2.0            # offsets of a few pixels: border crossings
+    ref_pts = torch.rand(N, Q, L, 2, device=DEV, generator=g) * 1.1 - 0.05
+    vt = value.bfloat16() if dt == "bf16" else value
+    fused = ops.msda_forward_fused(vt, shapes, starts, oa, ref_pts, L, P)
+    loc, aw = ops.msda_prepare(oa, ref_pts, shapes, M, L, P)
+    two = ops.msda_forward(vt, shapes, starts, loc, aw)
+    assert fused.dtype == vt.dtype and fused.shape == (N, Q, M * D)
+    tol = 1e-4 if dt == "bf16" else 2e-8                                            # softmax summed in a different order
+    np.testing.assert_allclose(fused.float().cpu().numpy(), two.float().cpu().numpy(), rtol=0, atol=tol)
+    if dt == "f32":
+        n_off = M * L * P * 2
+        off = oa[..., :n_off].reshape(N, Q, M, L, P, 2)
+        aw_t = torch.softmax(oa[..., n_off:].reshape(N, Q, M, L * P), -1).view(N, Q, M, L, P)
+        wh = torch.stack([shapes[..., 1], shapes[..., 0]], -1)
+        loc_t = ref_pts[:, :, None, :, None, :] + off / wh[None, None, None, :, None, :]
+        want = oracle.msda_forward(value.cpu().numpy(), shapes.cpu().numpy(), starts.cpu().numpy(),
+                                   loc_t.contiguous().cpu().numpy(), aw_t.contiguous().cpu().numpy())
+        np.testing.assert_allclose(fused.cpu().numpy(), want, rtol=0, atol=1e-7)
+
+
+@pytest.mark.parametrize("case", list(MSDA_CASES))
+def test_msda_float64_is_real_float64(case):
+    """The reference dispatches fp64 (ms_deform_attn_cuda.cu:69, OPS/test.py:24-44 checks it with allclose at fp64
+    tolerances): fp64 inputs are computed in fp64, not in fp32 and cast back."""
+    from quber_b200.msda import MSDeformAttnFunction
+    g = golden("msda.npz")
+    inp = synth.msda_inputs(dtype=np.float64, **MSDA_CASES[case])
+    out = MSDeformAttnFunction.apply(cu(inp["value"]), cu(inp["shapes"]), cu(inp["starts"]), cu(inp["loc"]), cu(inp["attn"]), 2)
+    assert out.dtype == torch.float64
+    np.testing.assert_allclose(out.cpu().numpy(), g[f"{case}_out_f64"], rtol=1e-9, atol=1e-12)
+
+
+@pytest.mark.parametrize("shape", [(128, 128, 64), (300, 256, 256), (1000, 288, 256), (515, 1024, 256), (515, 256, 1024),
+                                   (77, 40, 168), (333, 100, 72), (6300, 256, 256)])
+def test_gemm_x3_fp32_accuracy_on_arbitrary_inputs(shape):
+    """quber_gemm_bias_act_x3 (split-operand 3xTF32) on arbitrary fp32 inputs against float64: <= 1e-5 of the row scale
+    sum|a||w| (a single TF32 product is at 1e-3); cuBLAS sgemm itself sits at ~1e-6."""
+    from quber_b200 import _lib
+    M, N, K = shape
+    g = torch.Generator(device="cuda").manual_seed(M * 3 + N + K)
+    a = torch.randn(M, K, device=DEV, generator=g) * torch.rand(M, 1, device=DEV, generator=g) * 10
+    w = torch.randn(N, K, device=DEV, generator=g) / K ** 0.5
+    b = torch.randn(N, device=DEV, generator=g)
+    hi, lo = ops.split_tf32(w)
+    assert torch.equal(hi + lo, w) and int((hi.view(torch.int32) & 0x1FFF).abs().max()) == 0
+    ref = torch.relu(a.double() @ w.double().T + b.double())
+    scale = a.abs().double() @ w.abs().double().T + b.abs().double()
+    out = ops.gemm_bias_act_x3(a, hi, lo, b, act="relu")
+    err = ((out.double() - ref).abs() / scale).max().item()
+    one = ops.gemm_bias_act(a, w, b, act="relu")
+    err1 = ((one.double() - ref).abs() / scale).max().item()
+    print(f"[x3 gemm {shape}] max err / sum|a||w|: 3xTF32 {err:.2e}, 1xTF32 {err1:.2e}")
+    assert err <= 1e-5 and err1 > err
+    lin = ops.gemm_bias_act_x3(a, hi, lo, None, out_dtype=torch.bfloat16) if N % 8 == 0 else None
+    if lin is not None:
+        torch.testing.assert_close(lin.double(), a.double() @ w.double().T, rtol=2 ** -7, atol=1e-3 * float(scale.max()))
+    assert _lib.lib().quber_gemm_timeouts() == 0
+
+
+def test_extension_module_name_resolves_to_these_kernels():
+    """`import MultiScaleDeformableAttention as MSDA` (OPS/functions/ms_deform_attn_func.py:21)."""
+    import sys
+    from quber_b200 import msda
+    sys.modules.pop("MultiScaleDeformableAttention", None)
+    msda.install_extension_module()
+    import MultiScaleDeformableAttention as MSDA
+    inp = synth.msda_inputs(**MSDA_CASES["medium"])
+    out = MSDA.ms_deform_attn_forward(cu(inp["value"]), cu(inp["shapes"]), cu(inp["starts"]), cu(inp["loc"]), cu(inp["attn"]), 64)
+    np.testing.assert_allclose(out.cpu().numpy(), golden("msda.npz")["medium_out_f32"], rtol=0, atol=1e-6)
+    with pytest.raises(NotImplementedError):
+        MSDA.ms_deform_attn_backward()

@@ -166,3 +166,29 @@ def test_caller_side_helpers_match_reference_values():
     assert normalize_depth(d2, 0.25, 1.5)[0, :, 0].tolist() == [0, 0, 0, 30, 132, 193, 254, 255, 255]
     assert resize_shortest_edge_shape(1080, 1920) == (750, 1333)
     assert resize_shortest_edge_shape(480, 640) == (800, 1067)
+
+
+def test_msdeformattn_fresh_module_initialises_like_the_reference():
+    """A seeded fresh MSDeformAttn equals the reference module built under the same seed, parameter for parameter
+    (OPS/modules/ms_deform_attn.py:34-80, executed from /root/reference when it is there — the build container)."""
+    import os
+    import sys
+    import types
+    ops_dir = "/root/reference/ext_modules/UnseenObjectsWithMeanShift/MSMFormer/meanshiftformer/modeling/pixel_decoder/ops"
+    if not os.path.exists(ops_dir):
+        pytest.skip("reference checkout not present (GPU box)")
+    from quber_b200.msda import MSDeformAttn
+    sys.modules.setdefault("MultiScaleDeformableAttention", types.ModuleType("MultiScaleDeformableAttention"))
+    src = open(ops_dir + "/modules/ms_deform_attn.py").read().replace(
+        "from ..functions import MSDeformAttnFunction", "MSDeformAttnFunction = None").replace(
+        "from ..functions.ms_deform_attn_func import ms_deform_attn_core_pytorch", "ms_deform_attn_core_pytorch = None")
+    ns = {}
+    exec(compile(src, ops_dir + "/modules/ms_deform_attn.py", "exec"), ns)
+    for args in ((256, 3, 8, 4), (64, 2, 4, 4), (256, 4, 8, 4)):
+        torch.manual_seed(5)
+        ref = ns["MSDeformAttn"](*args)
+        torch.manual_seed(5)
+        ours = MSDeformAttn(*args)
+        assert list(ref.state_dict()) == list(ours.state_dict())
+        for k, v in ref.state_dict().items():
+            assert torch.equal(v, ours.state_dict()[k]), k
