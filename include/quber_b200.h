@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define QUBER_ABI_VERSION 1
+#define QUBER_ABI_VERSION 2
 
 enum {
     QUBER_OK = 0,
@@ -82,6 +82,9 @@ int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t
  *   per_instance  dev [B,K,H,W] uint8 or NULL: mask - erode_d(mask)      (util.py:72-90)
  *   boundary      dev [B,H,W] uint8 or NULL: (uint8 sum over k of per-instance) > 0   (util.py:92-99)
  *   fg            dev [B,H,W] uint8 or NULL: (uint8 sum over k of masks) > 0          (util.py:62-68)
+ *   status        dev int32 [1] or NULL: cleared by the call; bit 0 is set if a TMA tile load never arrived (the kernel
+ *                 gives up instead of hanging the GPU) — the outputs of THIS call are then invalid.  Always 0 on a
+ *                 healthy device; the Python shim copies it out with the results and raises.
  *   W must be a multiple of 16 and the pointers 16-byte aligned.
  * quber_quadruple_maps: TP/TN/FP/FN of two binary maps (tools/ours/panoptic2eee.py:110-123),
  *   gt, pred dev [B,n] uint8 (non-zero = set) -> out dev [B,4,n] uint8 in (TP,TN,FP,FN) order
@@ -89,11 +92,11 @@ int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t
  * ------------------------------------------------------------------------------------------- */
 int quber_boundary_dilation(int H, int W, double ratio);
 int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
-                        uint8_t *boundary, uint8_t *fg, void *stream);
+                        uint8_t *boundary, uint8_t *fg, int32_t *status, void *stream);
 int quber_quadruple_maps(const uint8_t *gt, const uint8_t *pred, int B, size_t n, uint8_t *out, void *stream);
 /* Diagnostic, NOT on the hot path (synchronises the device): number of TMA tile loads that
- * quber_mask_boundary gave up waiting for since the library was loaded (always 0 on a healthy
- * device; a non-zero value means the outputs of that call are invalid), or -1 on a CUDA error. */
+ * quber_mask_boundary gave up waiting for since the library was loaded (process-wide counter; the per-call signal is
+ * `status` above), or -1 on a CUDA error. */
 int quber_tma_timeouts(void);
 
 /* ---------------------------------------------------------------------------------------------

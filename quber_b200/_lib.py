@@ -9,6 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libquber_b200.so")
 
+ABI_VERSION = 2      # QUBER_ABI_VERSION of include/quber_b200.h
 QUBER_OK, E_INVALID, E_WORKSPACE, E_CUDA, E_ALIGN, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 POST_GIVEN_CENTERS, POST_NO_TOPK, POST_LABEL_U8 = 1, 2, 4
 
@@ -41,7 +42,7 @@ SYMBOLS = {
     "quber_encode_initial_masks": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "quber_encode_initial_masks_packed": (c_i, [c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "quber_boundary_dilation": (c_i, [c_i, c_i, c_d]),
-    "quber_mask_boundary": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp]),
+    "quber_mask_boundary": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "quber_quadruple_maps": (c_i, [c_vp, c_vp, c_i, c_sz, c_vp, c_vp]),
     "quber_tma_timeouts": (c_i, []),
     "quber_gemm_bias_act": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp]),
@@ -94,8 +95,8 @@ def lib():
         for name, (res, args) in SYMBOLS.items():
             fn = getattr(l, name)          # AttributeError if the .so does not export a declared symbol
             fn.restype, fn.argtypes = res, args
-        if l.quber_version() != 1:
-            raise QuberExtensionMissing(f"{SO_PATH}: ABI version {l.quber_version()} != 1, rebuild")
+        if l.quber_version() != ABI_VERSION:
+            raise QuberExtensionMissing(f"{SO_PATH}: ABI version {l.quber_version()} != {ABI_VERSION}, rebuild")
         _lib = l
     return _lib
 

@@ -15,7 +15,11 @@ def _to_dev(a):
 
 
 def _back(t, as_numpy):
-    return t.cpu().numpy() if as_numpy else t
+    if not as_numpy:
+        return t                                   # device callers read ops.boundary_status() with their results
+    out = t.cpu().numpy()                          # the copy synchronises: the call's status word is final
+    ops.boundary_status(t.device, check=True)      # never hand back the buffers of a call whose TMA load was lost
+    return out
 
 
 def _pad16(m):

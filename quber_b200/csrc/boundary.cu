@@ -12,7 +12,6 @@
 // union (`boundary`) and foreground (`fg`) sums live in registers and are written once.
 // A tile (+halo) whose bytes are all equal has no boundary: it is detected on load and skipped.
 #include <cuda.h>
-#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -29,130 +28,8 @@ __device__ __forceinline__ uint32_t shift_bytes(uint32_t lo, uint32_t hi, int s)
     return __byte_perm(lo, hi, 0x3210 + 0x1111 * s);
 }
 
-__global__ void __launch_bounds__(B_THREADS)
-boundary_ldg_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, int d, uint8_t *__restrict__ per_instance,
-                uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg) {
-    extern __shared__ uint32_t smem[];
-    const int hw = (d + 3) >> 2;            // halo words per side
-    const int WS = B_TWW + 2 * hw;          // words per staged row
-    const int R = B_TH + 2 * d;             // staged rows
-    uint32_t *bufA = smem, *bufB = smem + (size_t)R * WS;
-    const int tid = threadIdx.x;
-    const int b = blockIdx.z;
-    const int ty0 = blockIdx.y * B_TH, tx0 = blockIdx.x * B_TW;
-    const int Ww = W >> 2;                  // words per image row
-    const size_t HW = (size_t)H * W;
-    const int w = 2 * d + 1;
-    int p_top = 1;
-    while (p_top * 2 <= w) p_top *= 2;
-    const int lead = 4 * hw - d;            // byte offset of (x - d) relative to staged byte 0 for central x = 4*hw
-
-    const int ci = tid & 31, cr0 = tid >> 5;   // central word column, first central row
-    uint32_t uni_acc[B_RPT], fg_acc[B_RPT];
-#pragma unroll
-    for (int j = 0; j < B_RPT; ++j) uni_acc[j] = fg_acc[j] = 0;
-
-    for (int k = 0; k < K; ++k) {
-        const uint32_t *plane = reinterpret_cast<const uint32_t *>(masks + ((size_t)b * K + k) * HW);
-        // ---- stage tile + halo (zero outside the image) ----
-        uint32_t diff = 0, first = 0;
-        {
-            const int gy = ty0 - d, gxw = (tx0 >> 2) - hw;
-            if (gy >= 0 && gxw >= 0) first = __ldg(plane + (size_t)gy * Ww + gxw);
-            first = (first & 0xffu) * 0x01010101u;
-        }
-        for (int idx = tid; idx < R * WS; idx += B_THREADS) {
-            const int r = idx / WS, i = idx - r * WS;
-            const int gy = ty0 - d + r, gxw = (tx0 >> 2) - hw + i;
-            uint32_t v = 0;
-            if (gy >= 0 && gy < H && gxw >= 0 && gxw < Ww) v = ld_stream_u1(plane + (size_t)gy * Ww + gxw);
-            bufA[idx] = v;
-            diff |= v ^ first;
-        }
-        uint32_t orig[B_RPT];
-        const int any = __syncthreads_or(diff != 0);
-        uint32_t er[B_RPT];
-        if (!any) {
-            // uniform tile + halo: eroded == mask everywhere -> boundary 0
-#pragma unroll
-            for (int j = 0; j < B_RPT; ++j) { orig[j] = first; er[j] = first; }
-        } else {
-#pragma unroll
-            for (int j = 0; j < B_RPT; ++j) orig[j] = bufA[(size_t)(cr0 + 8 * j + d) * WS + hw + ci];
-            // ---- horizontal pass: doubling on every staged row ----
-            uint32_t *src = bufA, *dst = bufB;
-            for (int p = 1; p < p_top; p <<= 1) {
-                const int sw = p >> 2, sb = p & 3;
-                for (int idx = tid; idx < R * WS; idx += B_THREADS) {
-                    const int r = idx / WS, i = idx - r * WS;
-                    const uint32_t *row = src + (size_t)r * WS;
-                    const int j0 = i + sw;
-                    const uint32_t lo = j0 < WS ? row[j0] : 0u, hi = j0 + 1 < WS ? row[j0 + 1] : 0u;
-                    dst[idx] = __vminu4(row[i], sb ? shift_bytes(lo, hi, sb) : lo);
-                }
-                __syncthreads();
-                uint32_t *t = src; src = dst; dst = t;
-            }
-            // combine: Hmin[x] = min(F_p[x-d], F_p[x+d+1-p]) for the central words; written compactly
-            // (B_TWW words per row) into dst
-            {
-                const int o1 = lead, o2 = lead + w - p_top;     // byte offsets relative to word (i - hw)*4 ... see below
-                for (int idx = tid; idx < R * B_TWW; idx += B_THREADS) {
-                    const int r = idx >> 5, i = idx & 31;
-                    const uint32_t *row = src + (size_t)r * WS;
-                    // central word i covers staged bytes [4*(hw+i), +4); window start byte = 4*(hw+i) - d = 4*i + lead
-                    const int a1 = 4 * i + o1, a2 = 4 * i + o2;
-                    const int w1 = a1 >> 2, s1 = a1 & 3, w2 = a2 >> 2, s2 = a2 & 3;
-                    const uint32_t v1 = shift_bytes(row[w1], w1 + 1 < WS ? row[w1 + 1] : 0u, s1);
-                    const uint32_t v2 = shift_bytes(row[w2], w2 + 1 < WS ? row[w2 + 1] : 0u, s2);
-                    dst[idx] = __vminu4(v1, v2);
-                }
-                __syncthreads();
-                uint32_t *t = src; src = dst; dst = t;
-            }
-            // ---- vertical pass on the compact [R][32] array ----
-            for (int p = 1; p < p_top; p <<= 1) {
-                for (int idx = tid; idx < R * B_TWW; idx += B_THREADS) {
-                    const int r = idx >> 5;
-                    const uint32_t other = (r + p < R) ? src[idx + p * B_TWW] : 0u;
-                    dst[idx] = __vminu4(src[idx], other);
-                }
-                __syncthreads();
-                uint32_t *t = src; src = dst; dst = t;
-            }
-#pragma unroll
-            for (int j = 0; j < B_RPT; ++j) {
-                const int r = cr0 + 8 * j;      // output row r <-> staged rows r .. r+2d
-                er[j] = __vminu4(src[r * B_TWW + ci], src[(r + w - p_top) * B_TWW + ci]);
-            }
-        }
-        // ---- write / accumulate ----
-#pragma unroll
-        for (int j = 0; j < B_RPT; ++j) {
-            const int gy = ty0 + cr0 + 8 * j, gxw = (tx0 >> 2) + ci;
-            const uint32_t bd = __vsub4(orig[j], er[j]);
-            uni_acc[j] = __vadd4(uni_acc[j], bd);
-            fg_acc[j] = __vadd4(fg_acc[j], orig[j]);
-            if (per_instance && gy < H && gxw < Ww)
-                st_stream_u1(per_instance + ((size_t)b * K + k) * HW + (size_t)gy * W + 4 * gxw, bd);
-        }
-        __syncthreads();   // staged buffers are reused by the next plane
-    }
-#pragma unroll
-    for (int j = 0; j < B_RPT; ++j) {
-        const int gy = ty0 + cr0 + 8 * j, gxw = (tx0 >> 2) + ci;
-        if (gy < H && gxw < Ww) {
-            const size_t o = (size_t)b * HW + (size_t)gy * W + 4 * gxw;
-            // per byte: (sum > 0) -> 1.  __vcmpne4 gives 0xff per non-zero byte.
-            if (boundary) st_stream_u1(boundary + o, __vcmpne4(uni_acc[j], 0u) & 0x01010101u);
-            if (fg) st_stream_u1(fg + o, __vcmpne4(fg_acc[j], 0u) & 0x01010101u);
-        }
-    }
-}
-
-
 // ------------------------------------------------------------------------------------------------
-// TMA version (default).  The (tile + halo) box of every mask plane is fetched by ONE
+// The (tile + halo) box of every mask plane is fetched by ONE
 // cp.async.bulk.tensor.3d per plane — out-of-image bytes arrive as zeros, which IS the erosion's
 // zero padding — two planes ahead of the compute through two mbarriers, and the per-instance
 // result leaves through a TMA store (clipped at the image edge by the hardware).  No thread issues
@@ -170,7 +47,7 @@ boundary_ldg_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, int 
 //           back to bytes only for the 128x64 central tile.  This is the route every real mask takes
 //           (the reference feeds 0/255 or 0/1 masks).
 //   bytes   anything else                        -> the exact uint8 min filter (window doubling on
-//           packed bytes, as in boundary_ldg_kernel), so arbitrary planes still match cv2 bit for bit.
+//           packed bytes, see the header), so arbitrary planes still match cv2 bit for bit.
 // The union maps are uint8 WRAPPING sums over the planes (util.py:96-98 sums uint8 arrays), kept as
 // packed byte accumulators in registers in every route.
 // ------------------------------------------------------------------------------------------------
@@ -241,7 +118,7 @@ __device__ unsigned int g_tma_timeouts = 0;     // diagnostic: mbarrier waits th
 
 __global__ void __launch_bounds__(B_THREADS)
 boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map, int K, int H, int W,
-                    int d, int has_per, uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg) {
+                    int d, int has_per, uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg, int32_t *__restrict__ status) {
     extern __shared__ __align__(128) unsigned char sm_raw[];
     __shared__ __align__(8) uint64_t full[2];
     __shared__ uint32_t red[6];                 // 3 rotating (OR, AND) slots of the per-plane byte census
@@ -293,7 +170,10 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
 
     for (int k = 0; k < K; ++k) {
         uint32_t *cur = S(k);
-        if (!mbar_wait(&full[k & 1], (k >> 1) & 1)) { s_abort = 1; atomicAdd(&g_tma_timeouts, 1u); }
+        if (!mbar_wait(&full[k & 1], (k >> 1) & 1)) {            // a lost TMA: this CTA's outputs are invalid — say so per call
+            s_abort = 1;
+            if (tid == 0) { atomicAdd(&g_tma_timeouts, 1u); if (status) atomicOr(status, 1); }
+        }
         // ---- pass A: is the staged tile (+ halo) all zero?  ~87 % of the (tile, plane) pairs at C2 are, and they
         //      leave after this OR (8 instructions per 16 pixels) without the census / bit packing below ----
         const int slot = (k % 3) * 2;
@@ -529,7 +409,7 @@ static bool make_map(CUtensorMap *m, const void *base, int planes, int H, int W,
 }  // namespace quber
 
 extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
-                                   uint8_t *boundary, uint8_t *fg, void *stream) {
+                                   uint8_t *boundary, uint8_t *fg, int32_t *status, void *stream) {
     using namespace quber;
     if (!masks || B <= 0 || K <= 0 || H <= 0 || W <= 0 || d < 1 || d > 64) return QUBER_E_INVALID;
     if (!per_instance && !boundary && !fg) return QUBER_E_INVALID;
@@ -538,25 +418,18 @@ extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, in
         return QUBER_E_ALIGN;
     if (B > 65535) return QUBER_E_UNSUPPORTED;
     dim3 grid(cdiv(W, B_TW), cdiv(H, B_TH), B);
-    const char *impl = getenv("QUBER_BOUNDARY_IMPL");      // "ldg": the plain-load kernel (kept for A/B checks)
-    if (!(impl && impl[0] == 'l')) {
-        const BGeom g(d);
-        CUtensorMap in_map, out_map;
-        if (!make_map(&in_map, masks, B * K, H, W, g.SW, g.R) ||
-            !make_map(&out_map, per_instance ? per_instance : masks, B * K, H, W, B_TW, B_TH)) {
-            set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
-            return QUBER_E_CUDA;
-        }
-        QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
-        boundary_tma_kernel<<<grid, B_THREADS, g.smem, (cudaStream_t)stream>>>(in_map, out_map, K, H, W, d, per_instance != nullptr,
-                                                                              boundary, fg);
-        return check_launch("boundary_tma_kernel");
+    const BGeom g(d);
+    CUtensorMap in_map, out_map;
+    if (!make_map(&in_map, masks, B * K, H, W, g.SW, g.R) ||
+        !make_map(&out_map, per_instance ? per_instance : masks, B * K, H, W, B_TW, B_TH)) {
+        set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
+        return QUBER_E_CUDA;
     }
-    const int hw = (d + 3) >> 2, WS = B_TWW + 2 * hw, R = B_TH + 2 * d;
-    const size_t smem = 2 * (size_t)R * WS * sizeof(uint32_t);
-    QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_ldg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    boundary_ldg_kernel<<<grid, B_THREADS, smem, (cudaStream_t)stream>>>(masks, K, H, W, d, per_instance, boundary, fg);
-    return check_launch("boundary_ldg_kernel");
+    QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+    if (status) QUBER_CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(int32_t), (cudaStream_t)stream));
+    boundary_tma_kernel<<<grid, B_THREADS, g.smem, (cudaStream_t)stream>>>(in_map, out_map, K, H, W, d, per_instance != nullptr,
+                                                                          boundary, fg, status);
+    return check_launch("boundary_tma_kernel");
 }
 
 extern "C" int quber_tma_timeouts(void) {

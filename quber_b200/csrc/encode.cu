@@ -23,89 +23,15 @@ constexpr uint8_t E_NONE = 0xff;
 
 struct EncSums { unsigned long long n, sy, sx; };
 
-// PACKED: `masks` holds one bit per pixel (quber_host_pack_masks: bit i of word w = pixel 32 w + i of the flattened
-// [B,K,H,W] array) and the kernel also writes the byte planes (0 / value) to `unpacked` for the boundary kernel — the
-// expansion rides on the pass that reads every plane anyway instead of costing a kernel of its own.
-template <bool PACKED>
-__global__ void __launch_bounds__(E_THREADS)
-encode_reduce_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, EncSums *__restrict__ sums,
-                     uint8_t *__restrict__ lastk, uint8_t *__restrict__ unpacked, uint32_t value) {
-    extern __shared__ unsigned int acc[];   // [K][3]
-    const int tid = threadIdx.x, b = blockIdx.z;
-    for (int i = tid; i < 3 * K; i += E_THREADS) acc[i] = 0;
-    __syncthreads();
-    const int y = blockIdx.y * E_TH + (tid >> 4), x0 = blockIdx.x * E_TW + (tid & 15) * 8;
-    const bool inb = y < H && x0 < W;       // W % 16 == 0 -> the 8 pixels are all in or all out
-    const size_t HW = (size_t)H * W;
-    const size_t pix = (size_t)y * W + x0;
-    uint32_t last_lo = 0xffffffffu, last_hi = 0xffffffffu;   // packed per-pixel last k
-    const size_t plane0 = (size_t)b * K * HW + pix;                  // pixel index of this thread's 8 pixels in plane 0
-    const uint8_t *base = masks + (PACKED ? plane0 / 8 : plane0);   // PACKED: one byte = these 8 pixels (pix % 8 == 0)
-    constexpr int PF = 4;                   // planes fetched together: the streaming loads are the only latency here
-    uint2 vbuf[PF];
-    for (int k = 0; k < K; ++k) {
-        if (k % PF == 0) {
-#pragma unroll
-            for (int j = 0; j < PF; ++j) {
-                vbuf[j] = make_uint2(0, 0);
-                if (inb && k + j < K) {
-                    if (PACKED) {
-                        const uint32_t bits = __ldg(base + (size_t)(k + j) * (HW / 8));
-                        // four bits -> the low bit of four bytes (multiply puts bit i at 7 i + i, the mask keeps bit 8 i)
-                        vbuf[j] = make_uint2((((bits & 0xfu) * 0x00204081u) & 0x01010101u) * value,
-                                             (((bits >> 4) * 0x00204081u) & 0x01010101u) * value);
-                        st_stream_u2(unpacked + plane0 + (size_t)(k + j) * HW, vbuf[j]);
-                    } else {
-                        vbuf[j] = ld_stream_u2(base + (size_t)(k + j) * HW);
-                    }
-                }
-            }
-        }
-        uint2 v = vbuf[0];
-#pragma unroll
-        for (int j = 1; j < PF; ++j) if (k % PF == j) v = vbuf[j];
-        const bool nz = (v.x | v.y) != 0;
-        if (__any_sync(0xffffffffu, nz)) {
-            unsigned n = 0, sx = 0;
-            if (nz) {
-                const uint32_t mlo = __vcmpne4(v.x, 0u), mhi = __vcmpne4(v.y, 0u);   // 0xff per set byte
-                const uint32_t kk = (uint32_t)k * 0x01010101u;
-                last_lo = (last_lo & ~mlo) | (kk & mlo);
-                last_hi = (last_hi & ~mhi) | (kk & mhi);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const unsigned a = (mlo >> (8 * j)) & 1u, c = (mhi >> (8 * j)) & 1u;
-                    n += a + c;
-                    sx += a * (unsigned)(x0 + j) + c * (unsigned)(x0 + 4 + j);
-                }
-            }
-            unsigned sy = n * (unsigned)y;
-#pragma unroll
-            for (int o = 16; o; o >>= 1) {
-                n += __shfl_xor_sync(0xffffffffu, n, o);
-                sy += __shfl_xor_sync(0xffffffffu, sy, o);
-                sx += __shfl_xor_sync(0xffffffffu, sx, o);
-            }
-            if ((tid & 31) == 0) {
-                atomicAdd(&acc[3 * k], n); atomicAdd(&acc[3 * k + 1], sy); atomicAdd(&acc[3 * k + 2], sx);
-            }
-        }
-    }
-    if (inb) st_stream_u2(lastk + (size_t)b * HW + pix, make_uint2(last_lo, last_hi));
-    __syncthreads();
-    for (int k = tid; k < K; k += E_THREADS)
-        if (acc[3 * k]) {
-            EncSums *s = sums + (size_t)b * K + k;
-            atomicAdd(&s->n, (unsigned long long)acc[3 * k]);
-            atomicAdd(&s->sy, (unsigned long long)acc[3 * k + 1]);
-            atomicAdd(&s->sx, (unsigned long long)acc[3 * k + 2]);
-        }
-}
-
-// Same pass with the plane loop unrolled by the fetch group (no per-plane select of the fetched word), the three warp
-// sums as redux.sync adds instead of shuffle trees, and — DB — the next group's loads issued before the current group
-// is processed.  Integer arithmetic throughout, so the sums and the last-mask map are identical to the kernel above
-// (QUBER_ENCODE_REDUCE=0 old | 1 unrolled | 2 unrolled + double-buffered, for A/B runs).
+// Pass 1 (reduce): streams the K planes of a 128x16 tile once with 64-bit loads (a fetch group of four planes at a time,
+// the plane loop unrolled by the group), accumulates per mask (count, sum y, sum x) as integers — warp sums by
+// redux.sync, shared-memory atomics per CTA, one global atomic per CTA and mask — and records per pixel the LAST mask
+// covering it (the reference's overwrite order, predictor.py:337-356).
+// PACKED: `masks` holds one bit per pixel (quber_host_pack_masks / quber_rle_decode: bit i of word w = pixel 32 w + i of
+// the flattened [B,K,H,W] array) and the kernel also writes the byte planes (0 / value) to `unpacked` for the boundary
+// kernel — the expansion rides on the pass that reads every plane anyway instead of costing a kernel of its own.
+// DB (not instantiated in the shipped library: measured equal, 12 more registers): the next group's loads issued before
+// the current group is processed.
 template <bool PACKED, bool DB>
 __global__ void __launch_bounds__(E_THREADS)
 encode_reduce_unrolled_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, EncSums *__restrict__ sums,
@@ -292,21 +218,16 @@ static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *
     uint8_t *lastk = reinterpret_cast<uint8_t *>(workspace) + sums_bytes;
     QUBER_CUDA_TRY(cudaMemsetAsync(sums, 0, sums_bytes, st));
     dim3 grid(cdiv(W, E_TW), cdiv(H, E_TH), B);
-    static const char reduce_mode = [] { const char *e = getenv("QUBER_ENCODE_REDUCE"); return e ? e[0] : '1'; }();
     const size_t rsm = 3 * K * sizeof(unsigned);
     const uint32_t val = packed ? (uint32_t)value : 0u;
     uint8_t *unp = packed ? unpacked : nullptr;
 #define QUBER_REDUCE_LAUNCH(KERNEL) KERNEL<<<grid, E_THREADS, rsm, st>>>(masks, K, H, W, sums, lastk, unp, val)
-    if (reduce_mode == '1') { if (packed) QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<true, false>)); else QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<false, false>)); }
-    else if (reduce_mode == '2') { if (packed) QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<true, true>)); else QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<false, true>)); }
-    else { if (packed) QUBER_REDUCE_LAUNCH(encode_reduce_kernel<true>); else QUBER_REDUCE_LAUNCH(encode_reduce_kernel<false>); }
+    if (packed) QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<true, false>));
+    else QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<false, false>));
 #undef QUBER_REDUCE_LAUNCH
     if (int rc = check_launch("encode_reduce_kernel")) return rc;
-    static const char emit_mode = [] { const char *e = getenv("QUBER_ENCODE_EMIT"); return e ? e[0] : '1'; }();
     const size_t esm = K * (sizeof(EncCentre) + sizeof(int));
-    if (emit_mode == '0') encode_emit_kernel<false, 4><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, sigma, gauss, out);
-    else if (emit_mode == '2') encode_emit_kernel<true, 5><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, sigma, gauss, out);
-    else encode_emit_kernel<true, 4><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, sigma, gauss, out);
+    encode_emit_kernel<true, 4><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, sigma, gauss, out);
     return check_launch("encode_emit_kernel");
 }
 

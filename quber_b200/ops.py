@@ -98,17 +98,40 @@ def encode_initial_masks_any_width(masks, sigma=10):
     return enc
 
 
-def mask_boundary(masks, d, per_instance=True, union=True, fg=True):
+_BOUNDARY_STATUS = {}
+
+
+def boundary_status(device=None, check=False):
+    """The per-call status word of the LAST mask_boundary call on `device` (int32 CUDA [1]; bit 0 = a TMA tile load never
+    arrived and that call's outputs are invalid).  check=True synchronises and raises instead of returning."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    st = _BOUNDARY_STATUS.get(dev)
+    if check and st is not None and int(st[0]) & 1:
+        raise RuntimeError("quber_mask_boundary: a TMA tile load timed out; the boundary outputs of that call are invalid")
+    return st
+
+
+def mask_boundary(masks, d, per_instance=True, union=True, fg=True, status=None):
     """explicit_error_estimation/util.py:62-99 for a batch: masks [B,K,H,W] uint8 ->
-    (per-instance boundary [B,K,H,W] | None, union boundary [B,H,W] | None, fg [B,H,W] | None)."""
+    (per-instance boundary [B,K,H,W] | None, union boundary [B,H,W] | None, fg [B,H,W] | None).
+    The call's device status word (see boundary_status) is written to `status` (int32 CUDA [1]) or to a per-device
+    word that boundary_status() returns; nothing is synchronised here."""
     _need_cuda(masks, "masks", torch.uint8)
     B, K, H, W = masks.shape
     per = torch.empty_like(masks) if per_instance else None
     uni = torch.empty((B, H, W), dtype=torch.uint8, device=masks.device) if union else None
     fgm = torch.empty((B, H, W), dtype=torch.uint8, device=masks.device) if fg else None
+    if status is None:
+        status = _BOUNDARY_STATUS.get(masks.device)
+        if status is None:
+            status = _BOUNDARY_STATUS[masks.device] = torch.zeros(1, dtype=torch.int32, device=masks.device)
+    else:
+        _need_cuda(status, "status", torch.int32)
     with torch.cuda.device(masks.device):
         _lib.check(_lib.lib().quber_mask_boundary(_ptr(masks), B, K, H, W, int(d), _ptr(per), _ptr(uni), _ptr(fgm),
-                                                  _stream()), "quber_mask_boundary")
+                                                  _ptr(status), _stream()), "quber_mask_boundary")
     return per, uni, fgm
 
 

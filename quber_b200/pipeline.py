@@ -58,24 +58,24 @@ class HotPath:
         self.pack_threads = max(1, min(cores - 2, 16))      # the caller packs too while it waits
 
     # --- resident: every input already on the device -------------------------------------------
-    def encode_and_boundary(self, masks):
+    def encode_and_boundary(self, masks, status=None):
         c = self.cfg
         B, K, H, W = masks.shape
         enc = ops.encode_initial_masks(masks, c.sigma)
         d = ops.boundary_dilation(H, W, c.boundary_ratio)
-        per, uni, fg = ops.mask_boundary(masks, d)
+        per, uni, fg = ops.mask_boundary(masks, d, status=status)
         return enc, per, uni, fg
 
-    def encode_and_boundary_packed(self, st, c0, c1, w0, w1, value):
+    def encode_and_boundary_packed(self, st, c0, c1, w0, w1, value, status=None):
         """encode_and_boundary for a chunk whose masks arrived bit-packed (refine_batch_host)."""
         c = self.cfg
         masks = st["masks"][c0:c1]
         B, K, H, W = masks.shape
         if W % 16:                                # the packed encode shares the byte kernel's width rule
             ops.unpack_masks(st["packed_dev"][w0:w1], masks.shape, value=value, out=masks)
-            return self.encode_and_boundary(masks)
+            return self.encode_and_boundary(masks, status)
         enc = ops.encode_initial_masks_packed(st["packed_dev"][w0:w1], value, masks, c.sigma)
-        per, uni, fg = ops.mask_boundary(masks, ops.boundary_dilation(H, W, c.boundary_ratio))
+        per, uni, fg = ops.mask_boundary(masks, ops.boundary_dilation(H, W, c.boundary_ratio), status=status)
         return enc, per, uni, fg
 
     def post(self, head):
@@ -121,11 +121,14 @@ class HotPath:
                       h2d=torch.cuda.Stream(device=dev), d2h=torch.cuda.Stream(device=dev), free=None,
                       packed_host=pin((numel + 31) // 32, torch.int32),
                       packed_dev=torch.empty((numel + 31) // 32, dtype=torch.int32, device=dev), copied={},
-                      graphs={},
+                      graphs={}, bstatus=torch.zeros(B + 1, dtype=torch.int32, device=dev),
                       out=dict(label_map=pin((B, H, W), ldt), boundary=pin((B, H, W), torch.uint8),
                                inst_start=pin((B,), torch.int32), inst_counts=pin((B,), torch.int32),
-                               status=pin((1,), torch.int32), rle_status=pin((1,), torch.int32), labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
+                               status=pin((1,), torch.int32), rle_status=pin((1,), torch.int32),
+                               boundary_status=pin((B + 1,), torch.int32), labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),
                                boxes=pin((B * slab, 4), torch.float32)))
+            for k in ("status", "rle_status", "boundary_status"):
+                st["out"][k].zero_()
             self._stage = st
         return st
 
@@ -293,12 +296,13 @@ class HotPath:
                     groups = [pend]
                 for grp in groups:
                     g0, g1, pk, v = grp[0][0], grp[-1][1], grp[0][2], grp[0][3]
+                    bs = st["bstatus"][g0:g0 + 1]   # this group's status word (quber_mask_boundary clears and sets it)
                     if pk:                        # the encode pass expands the bits into the staging bytes on its way
                         enc, per, uni, fg = self._run_graphed(
                             st, (g0, g1, v), lambda: self.encode_and_boundary_packed(
-                                st, g0, g1, g0 * frame_bytes // 32, g1 * frame_bytes // 32, v))
+                                st, g0, g1, g0 * frame_bytes // 32, g1 * frame_bytes // 32, v, bs))
                     else:
-                        enc, per, uni, fg = self._run_graphed(st, (g0, g1), lambda: self.encode_and_boundary(st["masks"][g0:g1]))
+                        enc, per, uni, fg = self._run_graphed(st, (g0, g1), lambda: self.encode_and_boundary(st["masks"][g0:g1], bs))
                     done = cur.record_event()
                     with torch.cuda.stream(d2h):
                         d2h.wait_event(done)
@@ -310,10 +314,24 @@ class HotPath:
                 for c in range(len(sched)):           # the pool must not go on reading the caller's buffers
                     ops.host_pack_wait(c)
             raise
+        with torch.cuda.stream(d2h):
+            d2h.wait_event(cur.record_event())
+            out["boundary_status"].copy_(st["bstatus"], non_blocking=True)     # non-zero: a TMA load was lost, see check_status
         st["free"] = cur.record_event()
         cur.wait_stream(d2h)
         self._keep = keep                         # device results stay alive until the next call replaces them
         return out, keep
+
+    @staticmethod
+    def check_status(out):
+        """Call after synchronising: raises if the instance pool overflowed, a boundary TMA load was lost or an RLE did
+        not sum to H*W — the host results of that call are then not to be used."""
+        if int(out["status"][0]) & 1:
+            raise RuntimeError("quber_post_process: instance pool overflow (RefinerConfig.max_instances_per_image too small)")
+        if int(out["boundary_status"].max()) != 0:
+            raise RuntimeError("quber_mask_boundary: a TMA tile load timed out; boundary outputs invalid")
+        if "rle_status" in out and int(out["rle_status"][0]) & 1:
+            raise ValueError("quber_rle_decode: RLE counts do not sum to H*W")
 
     def refine_batch_rle(self, counts_host, offsets_host, shape, head_host, value=255, out_host=None, kernel_frames=16):
         """The end-to-end call with the initial masks in the form the reference's datasets hold them: COCO run-length
@@ -370,8 +388,9 @@ class HotPath:
         step = kernel_frames if kernel_frames and kernel_frames < B else B
         for g0 in range(0, B, step):
             g1 = min(B, g0 + step)
+            bs = st["bstatus"][g0:g0 + 1]
             enc, per, uni, fg = self._run_graphed(
-                st, (g0, g1, value), lambda: self.encode_and_boundary_packed(st, g0, g1, g0 * fw, g1 * fw, value))
+                st, (g0, g1, value), lambda: self.encode_and_boundary_packed(st, g0, g1, g0 * fw, g1 * fw, value, bs))
             done = cur.record_event()
             with torch.cuda.stream(d2h):
                 d2h.wait_event(done)
@@ -380,6 +399,7 @@ class HotPath:
         with torch.cuda.stream(d2h):
             d2h.wait_event(cur.record_event())
             out["rle_status"].copy_(rle_status, non_blocking=True)
+            out["boundary_status"].copy_(st["bstatus"], non_blocking=True)
         st["free"] = cur.record_event()
         cur.wait_stream(d2h)
         self._keep = keep
