@@ -106,6 +106,8 @@ class MaskRefiner(nn.Module):
         self.precision = precision
         self.ins_embed_head.use_kernels = True
         self.ins_embed_head.gemm_1x1 = precision == "bf16"
+        if getattr(self.ins_embed_head, "pixel_decoder", None) is not None:
+            self.ins_embed_head.pixel_decoder.set_precision(precision)
 
     @property
     def device(self):
@@ -268,6 +270,9 @@ META_ARCH_REGISTRY = {"MaskRefiner": MaskRefiner}
 
 
 def build_model(cfg, precision="fp32"):
-    """detectron2.modeling.build_model for the registered meta-architecture (predictor.py:217)."""
+    """detectron2.modeling.build_model for the registered meta-architecture (predictor.py:217).  Also registers the
+    path's entry points with detectron2 when it is importable (quber_b200/registry.py)."""
+    from .registry import register
+    register()
     model = META_ARCH_REGISTRY[cfg.MODEL.META_ARCHITECTURE](cfg, precision)
     return model.to(torch.device(cfg.MODEL.DEVICE if torch.cuda.is_available() or cfg.MODEL.DEVICE == "cpu" else "cpu"))

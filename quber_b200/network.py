@@ -633,6 +633,17 @@ class MaskRefinerInsEmbedHead(DeepLabV3PlusDecoder):
                 self.add_module("fusion_layers_{}".format(i), self.fusion_layers[i])
         self.use_kernels = False           # set by MaskRefiner: route softmax/sigmoid/cat (+1x1) through the CUDA kernels
         self.gemm_1x1 = False              # bf16 mode: opening 1x1 of FusionLayers on tcgen05
+        # Optional pixel decoder, selected by the reference's own key (maskrefiner/config.py:172, :202-205):
+        # MODEL.SEM_SEG_HEAD.PIXEL_DECODER_NAME == "MSDeformAttnPixelDecoder" replaces the DeepLabV3+ decoder by the
+        # multi-scale deformable-attention pixel decoder (MSMF/modeling/pixel_decoder/msdeformattn.py:164-358); its
+        # stride-COMMON_STRIDE `mask_features` (CONVS_DIM channels) are what the hierarchy of heads consumes.
+        self.pixel_decoder = None
+        pd_name = cfg.MODEL.SEM_SEG_HEAD.get("PIXEL_DECODER_NAME", "BasePixelDecoder")
+        if pd_name in ("MSDeformAttnPixelDecoder",):
+            from .pixel_decoder import SEM_SEG_HEADS_REGISTRY
+            feats = {k: v for k, v in input_shape.items() if k in in_features}
+            self.pixel_decoder = SEM_SEG_HEADS_REGISTRY[pd_name].from_config(cfg, feats, mask_dim=d0, in_features=in_features)
+            del self.decoder               # the DeepLabV3+ decoder is not built into this variant's state_dict
 
     def _stage_input(self, y, feature_dict, output_dict, prev):
         """model.py:745-759 -> (NCHW tensor | None, channels-last rows | None)."""
@@ -658,7 +669,10 @@ class MaskRefinerInsEmbedHead(DeepLabV3PlusDecoder):
         return torch.cat(parts, dim=1), None
 
     def layers(self, features):
-        y = self.decode(features)
+        if self.pixel_decoder is not None:
+            y = self.pixel_decoder.forward_features({k: v for k, v in features.items()})[0].to(next(iter(features.values())).dtype)
+        else:
+            y = self.decode(features)
         feature_dict, output_dict = {}, {}
         if not self.hierarchical_fusion_on:
             keys = (["eee_mask"] if self.eee_mask_on else []) + (["eee_boundary"] if self.eee_boundary_on else []) + \

@@ -247,7 +247,7 @@ class MSDeformAttnPixelDecoder(nn.Module):
 
     def __init__(self, input_shape, *, transformer_dropout=0.0, transformer_nheads=8, transformer_dim_feedforward=1024,
                  transformer_enc_layers=6, conv_dim=256, mask_dim=256, norm="GN",
-                 transformer_in_features=("res3", "res4", "res5"), common_stride=4):
+                 transformer_in_features=("res3", "res4", "res5"), common_stride=4, transformer_enc_n_points=4):
         super().__init__()
         tin = sorted(((k, v) for k, v in input_shape.items() if k in transformer_in_features), key=lambda kv: kv[1][1])
         items = sorted(input_shape.items(), key=lambda kv: kv[1][1])
@@ -266,7 +266,8 @@ class MSDeformAttnPixelDecoder(nn.Module):
             nn.init.constant_(proj[0].bias, 0)
         self.transformer = MSDeformAttnTransformerEncoderOnly(
             d_model=conv_dim, dropout=transformer_dropout, nhead=transformer_nheads, dim_feedforward=transformer_dim_feedforward,
-            num_encoder_layers=transformer_enc_layers, num_feature_levels=self.transformer_num_feature_levels)
+            num_encoder_layers=transformer_enc_layers, num_feature_levels=self.transformer_num_feature_levels,
+            enc_n_points=transformer_enc_n_points)
         self.pe_layer = PositionEmbeddingSine(conv_dim // 2, normalize=True)
         self.mask_dim = mask_dim
         self.mask_features = Conv2d(conv_dim, mask_dim, kernel_size=1, stride=1, padding=0)
@@ -287,13 +288,25 @@ class MSDeformAttnPixelDecoder(nn.Module):
         self.lateral_convs, self.output_convs = lateral_convs[::-1], output_convs[::-1]
 
     @classmethod
-    def from_config(cls, cfg, input_shape):
+    def from_config(cls, cfg, input_shape, mask_dim=None, in_features=None):
+        """msdeformattn.py:290-311 (`from_config`): the keys of maskrefiner/config.py:172,186,202-205.  `input_shape`
+        {name: (channels, stride)} or detectron2 ShapeSpecs; `in_features` / `mask_dim` override SEM_SEG_HEAD.IN_FEATURES /
+        MASK_DIM (the maskrefiner head feeds it the RGB-D fusion backbone's levels and wants CONVS_DIM channels back)."""
         h = cfg.MODEL.SEM_SEG_HEAD
-        mf = cfg.MODEL.get("MASK_FORMER", {})
-        return cls({k: v for k, v in input_shape.items() if k in h.IN_FEATURES}, transformer_dropout=mf.get("DROPOUT", 0.0),
-                   transformer_nheads=mf.get("NHEADS", 8), transformer_dim_feedforward=1024,
-                   transformer_enc_layers=h.TRANSFORMER_ENC_LAYERS, conv_dim=h.CONVS_DIM, mask_dim=h.MASK_DIM, norm=h.NORM,
-                   transformer_in_features=list(h.DEFORMABLE_TRANSFORMER_ENCODER_IN_FEATURES), common_stride=h.COMMON_STRIDE)
+        mf = cfg.MODEL.get("MASK_FORMER", {}) or {}
+        shapes = {k: (v if isinstance(v, tuple) else (v.channels, v.stride)) for k, v in input_shape.items()}
+        feats = list(h.IN_FEATURES) if in_features is None else list(in_features)
+        shapes = {k: v for k, v in shapes.items() if k in feats}
+        tin = [f for f in h.DEFORMABLE_TRANSFORMER_ENCODER_IN_FEATURES if f in shapes]
+        if not tin:
+            raise ValueError("DEFORMABLE_TRANSFORMER_ENCODER_IN_FEATURES names no feature of the backbone: "
+                             f"{list(h.DEFORMABLE_TRANSFORMER_ENCODER_IN_FEATURES)} vs {sorted(shapes)}")
+        return cls(shapes, transformer_dropout=mf.get("DROPOUT", 0.0),
+                   transformer_nheads=h.get("DEFORMABLE_TRANSFORMER_ENCODER_N_HEADS", mf.get("NHEADS", 8)),
+                   transformer_dim_feedforward=1024, transformer_enc_layers=h.TRANSFORMER_ENC_LAYERS or 6,
+                   conv_dim=h.CONVS_DIM, mask_dim=h.MASK_DIM if mask_dim is None else mask_dim, norm=h.NORM,
+                   transformer_in_features=tin, common_stride=h.COMMON_STRIDE,
+                   transformer_enc_n_points=h.get("DEFORMABLE_TRANSFORMER_ENCODER_N_POINTS", 4))
 
     def set_precision(self, precision):
         self.transformer.set_precision(precision)

@@ -493,3 +493,48 @@ def test_msda_prepare_matches_module_arithmetic():
     assert torch.equal(loc2, ref_pts[:, :, None, :, None, :] + off2 / norm[None, None, None, :, None, :])
     torch.testing.assert_close(aw2, torch.softmax(oa2[..., M * L * P2 * 2:].reshape(N, Q, M, L * P2), -1).view(N, Q, M, L, P2),
                                rtol=2e-6, atol=1e-8)
+
+
+def test_maskrefiner_with_msdeformattn_pixel_decoder_end_to_end(tmp_path):
+    """PIXEL_DECODER_NAME: "MSDeformAttnPixelDecoder" (maskrefiner/config.py:172): the head consumes the deformable-
+    attention decoder's stride-4 mask features; forward runs on the repo's kernels in fp32 (3xTF32) and bf16."""
+    import os
+    from quber_b200.config import get_cfg
+    from quber_b200.meta_arch import build_model
+    base = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "configs",
+                        "mask-refiner-rgbd-concat-l2-gn-hf-b-fco-l3-b8.yaml")
+    y = tmp_path / "msda.yaml"
+    y.write_text(f"""_BASE_: "{base}"
+MODEL:
+  SEM_SEG_HEAD:
+    PIXEL_DECODER_NAME: "MSDeformAttnPixelDecoder"
+    CONVS_DIM: 256
+    TRANSFORMER_ENC_LAYERS: 2
+""")
+    cfg = get_cfg()
+    cfg.merge_from_file(str(y))
+    torch.manual_seed(0)
+    model = build_model(cfg).eval()
+    with torch.no_grad():                                     # non-trivial offsets (zero weights at init)
+        for l in model.ins_embed_head.pixel_decoder.transformer.encoder.layers:
+            l.self_attn.sampling_offsets.weight.normal_(0, 0.02)
+            l.self_attn.attention_weights.weight.normal_(0, 0.05)
+    g = torch.Generator(device=DEV).manual_seed(1)
+    x = torch.randn(2, 9, 256, 320, device=DEV, generator=g)
+    outs = {}
+    for prec in ("fp32", "bf16"):
+        model.set_precision(prec)
+        with torch.no_grad():
+            o = model.network_logits(x)
+        assert set(o) == {"eee_boundary", "foreground", "center", "offset"}
+        assert tuple(o["eee_boundary"].shape) == (2, 4, 64, 80) and tuple(o["offset"].shape) == (2, 2, 64, 80)
+        assert all(torch.isfinite(v).all() for v in o.values())
+        outs[prec] = o
+    for k in outs["fp32"]:
+        scale = float(outs["fp32"][k].abs().max()) + 1e-6
+        assert float((outs["bf16"][k] - outs["fp32"][k]).abs().max()) <= 0.15 * scale + 5e-3, k
+    # the whole predictor-level forward (post-processing included) runs too
+    inp = [{"image": torch.randint(0, 255, (6, 256, 320), dtype=torch.uint8), "initial_pred_offset": torch.zeros(3, 256, 320),
+            "height": 256, "width": 320} for _ in range(2)]
+    res = model(inp)
+    assert len(res) == 2 and tuple(res[0]["sem_seg"].shape) == (1, 256, 320) and "panoptic_seg" in res[0]

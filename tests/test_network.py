@@ -192,3 +192,84 @@ def test_msdeformattn_fresh_module_initialises_like_the_reference():
         assert list(ref.state_dict()) == list(ours.state_dict())
         for k, v in ref.state_dict().items():
             assert torch.equal(v, ours.state_dict()[k]), k
+
+
+def test_registers_with_detectron2_when_importable(monkeypatch):
+    """registration 'iff import detectron2 succeeds'.  detectron2 is absent from this image, so a
+    stand-in package with fvcore-style registries is put on sys.modules; the reference's names must resolve to this
+    implementation, and a name that is already taken is left alone unless override=True."""
+    import sys
+    import types
+    import quber_b200
+    from quber_b200 import meta_arch, network, pixel_decoder
+
+    class Reg:                                       # fvcore.common.registry.Registry, as far as registration goes
+        def __init__(self, name):
+            self._name, self._obj_map = name, {}
+
+        def register(self, obj=None):
+            assert obj.__name__ not in self._obj_map, "An object named '{}' was already registered".format(obj.__name__)
+            self._obj_map[obj.__name__] = obj
+            return obj
+
+        def get(self, name):
+            return self._obj_map[name]
+
+    d2, mod = types.ModuleType("detectron2"), types.ModuleType("detectron2.modeling")
+    mod.META_ARCH_REGISTRY, mod.BACKBONE_REGISTRY, mod.SEM_SEG_HEADS_REGISTRY = Reg("META_ARCH"), Reg("BACKBONE"), Reg("SEM_SEG_HEADS")
+    d2.modeling = mod
+    taken = object()
+    mod.BACKBONE_REGISTRY._obj_map["build_resnet_deeplab_fusion_backbone"] = taken
+    monkeypatch.setitem(sys.modules, "detectron2", d2)
+    monkeypatch.setitem(sys.modules, "detectron2.modeling", mod)
+    monkeypatch.delitem(sys.modules, "MultiScaleDeformableAttention", raising=False)
+    done = quber_b200.register()
+    assert done["META_ARCH_REGISTRY"] == ["MaskRefiner"] and mod.META_ARCH_REGISTRY.get("MaskRefiner") is meta_arch.MaskRefiner
+    assert mod.BACKBONE_REGISTRY.get("build_resnet_deeplab_rgbd_fusion_backbone") is network.build_resnet_deeplab_rgbd_fusion_backbone
+    assert mod.BACKBONE_REGISTRY.get("build_resnet_deeplab_fusion_backbone") is taken          # not clobbered
+    assert mod.SEM_SEG_HEADS_REGISTRY.get("MSDeformAttnPixelDecoder") is pixel_decoder.MSDeformAttnPixelDecoder
+    assert quber_b200.register()["META_ARCH_REGISTRY"] == []                                   # idempotent
+    quber_b200.register(override=True)
+    assert mod.BACKBONE_REGISTRY.get("build_resnet_deeplab_fusion_backbone") is network.build_resnet_deeplab_fusion_backbone
+    import MultiScaleDeformableAttention as MSDA                                               # OPS/functions/ms_deform_attn_func.py:21
+    assert callable(MSDA.ms_deform_attn_forward) and callable(MSDA.ms_deform_attn_backward)
+
+
+def test_model_builds_with_msdeformattn_pixel_decoder_from_yaml(tmp_path):
+    """MODEL.SEM_SEG_HEAD.PIXEL_DECODER_NAME: "MSDeformAttnPixelDecoder" (maskrefiner/config.py:172, :202-205) selects the
+    deformable-attention pixel decoder in the head builder."""
+    import os
+    from quber_b200.config import get_cfg
+    from quber_b200.meta_arch import build_model
+    from quber_b200.pixel_decoder import MSDeformAttnPixelDecoder
+    base = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "configs",
+                        "mask-refiner-rgbd-concat-l2-gn-hf-b-fco-l3-b8.yaml")
+    y = tmp_path / "msda.yaml"
+    y.write_text(f"""_BASE_: "{base}"
+MODEL:
+  DEVICE: "cpu"
+  SEM_SEG_HEAD:
+    PIXEL_DECODER_NAME: "MSDeformAttnPixelDecoder"
+    CONVS_DIM: 256
+    TRANSFORMER_ENC_LAYERS: 2
+    DEFORMABLE_TRANSFORMER_ENCODER_IN_FEATURES: ["res3", "res4", "res5"]
+    DEFORMABLE_TRANSFORMER_ENCODER_N_POINTS: 4
+    DEFORMABLE_TRANSFORMER_ENCODER_N_HEADS: 8
+""")
+    cfg = get_cfg()
+    cfg.merge_from_file(str(y))
+    model = build_model(cfg)
+    pd = model.ins_embed_head.pixel_decoder
+    assert isinstance(pd, MSDeformAttnPixelDecoder)
+    assert pd.transformer_in_features == ["res3", "res5"]                  # the RGB-D fusion backbone has no res4
+    assert pd.mask_dim == cfg.MODEL.INS_EMBED_HEAD.CONVS_DIM and len(pd.transformer.encoder.layers) == 2
+    sd = model.state_dict()
+    assert "ins_embed_head.pixel_decoder.transformer.encoder.layers.1.self_attn.sampling_offsets.weight" in sd
+    assert not any(k.startswith("ins_embed_head.decoder.") for k in sd)    # the DeepLabV3+ decoder is not built
+    assert "ins_embed_head.fusion_layers_1.fusion_layers.0.weight" in sd   # the hierarchy of heads is unchanged
+    # default config: DeepLabV3+ decoder, no pixel decoder
+    cfg2 = get_cfg()
+    cfg2.merge_from_file(base)
+    cfg2.MODEL.DEVICE = "cpu"
+    m2 = build_model(cfg2)
+    assert m2.ins_embed_head.pixel_decoder is None and any(k.startswith("ins_embed_head.decoder.") for k in m2.state_dict())
