@@ -760,15 +760,23 @@ def rle_to_string(counts):
 
 
 # ---- torch.library registration: torch.ops.quber.* ----------------------------------------------
+# Every device entry point of the C ABI is a PyTorch custom op with a fake (meta) kernel, so the path is visible to
+# torch.compile / torch.export as opaque CUDA ops (no graph break, fullgraph=True works) and has NO decomposition into
+# aten ops — there is nothing for a compiler to "fall back" to.  The functions above are the implementations.
+POST_OUTPUTS = ("sem_seg", "eee_full", "eee_onehot", "panoptic", "label_map", "masks", "centers_yx", "n_centers",
+                "inst_offsets", "labels", "scores", "boxes", "status")
+
+
 def _register():
     try:
         from torch.library import custom_op
     except Exception:        # pragma: no cover - very old torch
         return
+    from typing import Optional, Sequence
+    T = torch.Tensor
 
     @custom_op("quber::msda_forward", mutates_args=(), device_types="cuda")
-    def _msda(value: torch.Tensor, spatial_shapes: torch.Tensor, level_start_index: torch.Tensor,
-              sampling_locations: torch.Tensor, attention_weights: torch.Tensor) -> torch.Tensor:
+    def _msda(value: T, spatial_shapes: T, level_start_index: T, sampling_locations: T, attention_weights: T) -> T:
         return msda_forward(value, spatial_shapes, level_start_index, sampling_locations, attention_weights)
 
     @_msda.register_fake
@@ -776,8 +784,26 @@ def _register():
         B, S, M, D = value.shape
         return value.new_empty((B, sampling_locations.shape[1], M * D))
 
+    @custom_op("quber::msda_forward_fused", mutates_args=(), device_types="cuda")
+    def _msdaf(value: T, spatial_shapes: T, level_start_index: T, oa: T, reference_points: T, n_levels: int, n_points: int) -> T:
+        return msda_forward_fused(value, spatial_shapes, level_start_index, oa, reference_points, n_levels, n_points)
+
+    @_msdaf.register_fake
+    def _(value, spatial_shapes, level_start_index, oa, reference_points, n_levels, n_points):
+        B, S, M, D = value.shape
+        return value.new_empty((B, oa.shape[1], M * D))
+
+    @custom_op("quber::msda_prepare", mutates_args=(), device_types="cuda")
+    def _prep(oa: T, reference_points: T, spatial_shapes: T, n_heads: int, n_levels: int, n_points: int) -> tuple[T, T]:
+        return msda_prepare(oa, reference_points, spatial_shapes, n_heads, n_levels, n_points)
+
+    @_prep.register_fake
+    def _(oa, reference_points, spatial_shapes, n_heads, n_levels, n_points):
+        N, Q, _ = oa.shape
+        return (oa.new_empty((N, Q, n_heads, n_levels, n_points, 2)), oa.new_empty((N, Q, n_heads, n_levels, n_points)))
+
     @custom_op("quber::encode_initial_masks", mutates_args=(), device_types="cuda")
-    def _enc(masks: torch.Tensor, sigma: int) -> torch.Tensor:
+    def _enc(masks: T, sigma: int) -> T:
         return encode_initial_masks(masks, sigma)
 
     @_enc.register_fake
@@ -785,8 +811,25 @@ def _register():
         B, K, H, W = masks.shape
         return masks.new_empty((B, 3, H, W), dtype=torch.float32)
 
+    @custom_op("quber::encode_initial_masks_packed", mutates_args=("masks_out",), device_types="cuda")
+    def _encp(packed: T, value: int, masks_out: T, sigma: int) -> T:
+        return encode_initial_masks_packed(packed, value, masks_out, sigma)
+
+    @_encp.register_fake
+    def _(packed, value, masks_out, sigma):
+        B, K, H, W = masks_out.shape
+        return packed.new_empty((B, 3, H, W), dtype=torch.float32)
+
+    @custom_op("quber::unpack_masks", mutates_args=(), device_types="cuda")
+    def _unp(packed: T, shape: Sequence[int], value: int) -> T:
+        return unpack_masks(packed, tuple(shape), value)
+
+    @_unp.register_fake
+    def _(packed, shape, value):
+        return packed.new_empty(tuple(shape), dtype=torch.uint8)
+
     @custom_op("quber::mask_boundary", mutates_args=(), device_types="cuda")
-    def _bnd(masks: torch.Tensor, d: int) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    def _bnd(masks: T, d: int) -> tuple[T, T, T]:
         return mask_boundary(masks, d)
 
     @_bnd.register_fake
@@ -795,12 +838,147 @@ def _register():
         return torch.empty_like(masks), masks.new_empty((B, H, W)), masks.new_empty((B, H, W))
 
     @custom_op("quber::quadruple_maps", mutates_args=(), device_types="cuda")
-    def _quad(gt: torch.Tensor, pred: torch.Tensor) -> torch.Tensor:
+    def _quad(gt: T, pred: T) -> T:
         return quadruple_maps(gt, pred)
 
     @_quad.register_fake
     def _(gt, pred):
         return gt.new_empty((gt.shape[0], 4) + tuple(gt.shape[1:]))
+
+    @custom_op("quber::post_process", mutates_args=(), device_types="cuda")
+    def _post(foreground: T, center: T, offset: T, eee: Optional[T], scale: int, offset_mul: float, threshold: float, nms_kernel: int,
+              top_k: int, min_area: int, stuff_area: int, label_divisor: int, void_label: float, max_instances: int,
+              label_u8: bool) -> tuple[T, T, T, T, T, T, T, T, T, T, T, T, T]:
+        r = post_process(foreground, center, offset, eee, scale=scale, offset_mul=offset_mul, threshold=threshold,
+                         nms_kernel=nms_kernel, top_k=top_k, min_area=min_area, stuff_area=stuff_area, label_divisor=label_divisor,
+                         void_label=void_label, max_instances=max_instances,
+                         label_dtype=torch.uint8 if label_u8 else torch.int32)
+        B, _, h, w = foreground.shape
+        empty = foreground.new_empty((B, 0, h * scale, w * scale))
+        r.setdefault("eee_full", empty)
+        r.setdefault("eee_onehot", empty.to(torch.uint8))
+        return tuple(r[k] for k in POST_OUTPUTS)
+
+    @_post.register_fake
+    def _(foreground, center, offset, eee, scale, offset_mul, threshold, nms_kernel, top_k, min_area, stuff_area, label_divisor,
+          void_label, max_instances, label_u8):
+        B, _, h, w = foreground.shape
+        H, W = h * scale, w * scale
+        C = 0 if eee is None else eee.shape[1]
+        n = max(max_instances, 1)
+        f, i32, u8 = torch.float32, torch.int32, torch.uint8
+        e = lambda shape, dt: foreground.new_empty(shape, dtype=dt)
+        return (e((B, 1, H, W), f), e((B, C, H, W), f), e((B, C, H, W), u8), e((B, H, W), f),
+                e((B, H, W), u8 if label_u8 else i32), e((n, H, W), u8), e((B, top_k, 2), i32), e((B,), i32), e((B + 1,), i32),
+                e((n,), i32), e((n,), f), e((n, 4), f), e((1,), i32))
+
+    @custom_op("quber::gemm_bias_act", mutates_args=(), device_types="cuda")
+    def _gemm(a: T, weight: T, bias: Optional[T], relu: bool, out_bf16: bool) -> T:
+        return gemm_bias_act(a, weight, bias, act="relu" if relu else "none", out_dtype=torch.bfloat16 if out_bf16 else torch.float32)
+
+    @_gemm.register_fake
+    def _(a, weight, bias, relu, out_bf16):
+        return a.new_empty(tuple(a.shape[:-1]) + (weight.shape[0],), dtype=torch.bfloat16 if out_bf16 else torch.float32)
+
+    @custom_op("quber::gemm_bias_act_x3", mutates_args=(), device_types="cuda")
+    def _gemm3(a: T, w_hi: T, w_lo: T, bias: Optional[T], relu: bool, out_bf16: bool) -> T:
+        return gemm_bias_act_x3(a, w_hi, w_lo, bias, act="relu" if relu else "none", out_dtype=torch.bfloat16 if out_bf16 else torch.float32)
+
+    @_gemm3.register_fake
+    def _(a, w_hi, w_lo, bias, relu, out_bf16):
+        return a.new_empty(tuple(a.shape[:-1]) + (w_hi.shape[0],), dtype=torch.bfloat16 if out_bf16 else torch.float32)
+
+    @custom_op("quber::split_tf32", mutates_args=(), device_types="cuda")
+    def _split(w: T) -> tuple[T, T]:
+        return split_tf32(w)
+
+    @_split.register_fake
+    def _(w):
+        return torch.empty_like(w), torch.empty_like(w)
+
+    @custom_op("quber::pack_input", mutates_args=(), device_types="cuda")
+    def _pack(image: T, offsets: Optional[T], mean: T, std: T) -> T:
+        return pack_input(image, offsets, mean, std)
+
+    @_pack.register_fake
+    def _(image, offsets, mean, std):
+        B, C, H, W = image.shape
+        return image.new_empty((B, C + (0 if offsets is None else offsets.shape[1]), H, W), dtype=torch.float32)
+
+    @custom_op("quber::fuse_concat", mutates_args=(), device_types="cuda")
+    def _fuse(sources: Sequence[T], op_codes: Sequence[int], layout: int, pitch: int) -> T:
+        names = {v: k for k, v in _FUSE_OPS.items()}
+        return fuse_concat(list(sources), [names[c] for c in op_codes], layout=("nchw", "nhwc_f32", "nhwc_bf16")[layout],
+                           pitch=pitch if layout else None)
+
+    @_fuse.register_fake
+    def _(sources, op_codes, layout, pitch):
+        B, _, h, w = sources[0].shape
+        ctot = sum(t.shape[1] for t in sources)
+        if layout == 0:
+            return sources[0].new_empty((B, ctot, h, w), dtype=torch.float32)
+        return sources[0].new_empty((B * h * w, pitch), dtype=torch.float32 if layout == 1 else torch.bfloat16)
+
+    @custom_op("quber::group_norm_relu", mutates_args=(), device_types="cuda")
+    def _gn(x: T, weight: T, bias: T, groups: int, eps: float, relu: bool, pre_bias: Optional[T]) -> T:
+        return group_norm_relu(x, weight, bias, groups, eps, relu, False, pre_bias)
+
+    @_gn.register_fake
+    def _(x, weight, bias, groups, eps, relu, pre_bias):
+        return torch.empty_like(x)
+
+    @custom_op("quber::upsample_concat", mutates_args=(), device_types="cuda")
+    def _upc(a: T, b: T) -> T:
+        return upsample_concat(a, b)
+
+    @_upc.register_fake
+    def _(a, b):
+        return torch.empty((b.shape[0], a.shape[1] + b.shape[1], a.shape[2], a.shape[3]), dtype=b.dtype, device=b.device,
+                           memory_format=torch.channels_last)
+
+    @custom_op("quber::maxpool3x3s2", mutates_args=(), device_types="cuda")
+    def _mp(x: T) -> T:
+        return maxpool3x3s2(x)
+
+    @_mp.register_fake
+    def _(x):
+        N, C, H, W = x.shape
+        return torch.empty((N, C, (H - 1) // 2 + 1, (W - 1) // 2 + 1), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+
+    @custom_op("quber::add_layer_norm", mutates_args=(), device_types="cuda")
+    def _aln(a: T, b: Optional[T], weight: T, bias: T, eps: float) -> T:
+        return add_layer_norm(a, b, weight, bias, eps)
+
+    @_aln.register_fake
+    def _(a, b, weight, bias, eps):
+        return torch.empty_like(a)
+
+    @custom_op("quber::filter_instances", mutates_args=(), device_types="cuda")
+    def _filt(label_map: T, counts: T, fg: Optional[T], zero_depth: Optional[T], thr: float, max_per: int) -> tuple[T, T, T]:
+        return filter_instances(label_map, counts, fg, zero_depth, thr, max_per)
+
+    @_filt.register_fake
+    def _(label_map, counts, fg, zero_depth, thr, max_per):
+        B = label_map.shape[0]
+        return torch.empty_like(label_map), label_map.new_empty((B, max_per), dtype=torch.uint8), label_map.new_empty((B,), dtype=torch.int32)
+
+    @custom_op("quber::rle_decode", mutates_args=(), device_types="cuda")
+    def _rled(counts: T, offsets: T, n: int, H: int, W: int, value: int, packed: bool) -> tuple[T, T]:
+        return rle_decode(counts, offsets, n, H, W, value=value, packed=packed)
+
+    @_rled.register_fake
+    def _(counts, offsets, n, H, W, value, packed):
+        out = counts.new_empty((n * H * W // 32,), dtype=torch.int32) if packed else counts.new_empty((n, H, W), dtype=torch.uint8)
+        return out, counts.new_empty((1,), dtype=torch.int32)
+
+    @custom_op("quber::rle_encode", mutates_args=(), device_types="cuda")
+    def _rlee(masks: T, cap: int) -> tuple[T, T, T]:
+        return rle_encode(masks, cap)
+
+    @_rlee.register_fake
+    def _(masks, cap):
+        return (masks.new_empty((cap,), dtype=torch.int32), masks.new_empty((masks.shape[0] + 1,), dtype=torch.int64),
+                masks.new_empty((1,), dtype=torch.int32))
 
 
 _register()

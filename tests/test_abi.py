@@ -118,3 +118,52 @@ def test_ops_fail_loudly_without_cuda():
         msda.ms_deform_attn_forward(torch.zeros(1, 4, 1, 8), torch.zeros(1, 2, dtype=torch.long),
                                     torch.zeros(1, dtype=torch.long), torch.zeros(1, 1, 1, 1, 1, 2),
                                     torch.zeros(1, 1, 1, 1, 1), 64)
+
+
+def test_every_device_entry_point_is_a_custom_op_with_a_fake_kernel():
+    """north_star: "registered as PyTorch custom ops".  Fake-tensor propagation (what torch.compile / export run) works
+    without a GPU: fake CUDA tensors through torch.ops.quber.* give the shapes / dtypes the kernels produce."""
+    import torch
+    from torch._subclasses.fake_tensor import FakeTensorMode
+    from quber_b200 import ops
+    names = {n for n in dir(torch.ops.quber) if not n.startswith("_") and n != "name"}
+    want = {"msda_forward", "msda_forward_fused", "msda_prepare", "encode_initial_masks", "encode_initial_masks_packed",
+            "unpack_masks", "mask_boundary", "quadruple_maps", "post_process", "gemm_bias_act", "gemm_bias_act_x3", "split_tf32",
+            "pack_input", "fuse_concat", "group_norm_relu", "upsample_concat", "maxpool3x3s2", "add_layer_norm",
+            "filter_instances", "rle_decode", "rle_encode"}
+    assert want <= names, want - names
+    q = torch.ops.quber
+    with FakeTensorMode():
+        e = lambda *s, dt=torch.float32: torch.empty(*s, dtype=dt, device="cuda")
+        fg, ce, of, ee = e(2, 1, 60, 80), e(2, 1, 60, 80), e(2, 2, 60, 80), e(2, 3, 60, 80)
+        out = dict(zip(ops.POST_OUTPUTS, q.post_process(fg, ce, of, ee, 4, 4.0, 0.3, 7, 200, 512, 2048, 1000, -1.0, 400, True)))
+        assert tuple(out["sem_seg"].shape) == (2, 1, 240, 320) and tuple(out["eee_onehot"].shape) == (2, 3, 240, 320)
+        assert out["label_map"].dtype == torch.uint8 and tuple(out["masks"].shape) == (400, 240, 320)
+        assert tuple(out["inst_offsets"].shape) == (3,) and out["eee_onehot"].dtype == torch.uint8
+        out = q.post_process(fg, ce, of, None, 4, 4.0, 0.3, 7, 200, 512, 2048, 1000, -1.0, 400, False)
+        assert tuple(out[1].shape) == (2, 0, 240, 320) and out[4].dtype == torch.int32
+        assert q.gemm_bias_act(e(3, 100, 256), e(192, 256), None, True, True).shape == (3, 100, 192)
+        assert q.gemm_bias_act_x3(e(100, 256), e(192, 256), e(192, 256), e(192), False, False).dtype == torch.float32
+        v = e(2, 500, 8, 32, dt=torch.bfloat16)
+        sh, st = e(3, 2, dt=torch.int64), e(3, dt=torch.int64)
+        assert q.msda_forward_fused(v, sh, st, e(2, 77, 288), e(2, 77, 3, 2), 3, 4).shape == (2, 77, 256)
+        loc, aw = q.msda_prepare(e(2, 77, 288), e(2, 77, 3, 2), sh, 8, 3, 4)
+        assert loc.shape == (2, 77, 8, 3, 4, 2) and aw.shape == (2, 77, 8, 3, 4)
+        assert q.msda_forward(v, sh, st, loc, aw).dtype == torch.bfloat16
+        m = e(2, 5, 64, 96, dt=torch.uint8)
+        per, uni, fgm = q.mask_boundary(m, 8)
+        assert per.shape == m.shape and uni.shape == (2, 64, 96) and fgm.dtype == torch.uint8
+        assert q.encode_initial_masks(m, 10).shape == (2, 3, 64, 96)
+        pk, stt = q.rle_decode(e(100, dt=torch.int32), e(11, dt=torch.int64), 10, 64, 96, 255, True)
+        assert pk.shape == (10 * 64 * 96 // 32,) and pk.dtype == torch.int32 and stt.shape == (1,)
+        c, o, s2 = q.rle_encode(m[0], 1000)
+        assert c.shape == (1000,) and o.shape == (6,) and o.dtype == torch.int64
+        x = e(2, 64, 8, 12).to(memory_format=torch.channels_last)
+        assert q.maxpool3x3s2(x).shape == (2, 64, 4, 6)
+        assert q.upsample_concat(e(2, 32, 16, 24).to(memory_format=torch.channels_last), x).shape == (2, 96, 16, 24)
+        assert q.fuse_concat([e(2, 8, 6, 6), e(2, 4, 6, 6)], [0, 2], 2, 16).shape == (72, 16)
+        assert q.group_norm_relu(x, e(64), e(64), 32, 1e-5, True, None).shape == x.shape
+        assert q.add_layer_norm(e(10, 256), e(10, 256), e(256), e(256), 1e-5).shape == (10, 256)
+        assert q.pack_input(e(2, 6, 16, 16, dt=torch.uint8), e(2, 3, 16, 16), e(6), e(6)).shape == (2, 9, 16, 16)
+        lm, keep, nc = q.filter_instances(e(2, 16, 16, dt=torch.int32), e(2, dt=torch.int32), None, None, 0.3, 64)
+        assert lm.shape == (2, 16, 16) and keep.shape == (2, 64) and nc.shape == (2,)

@@ -323,3 +323,32 @@ def test_refine_batch_rle_equals_dense_host_call(B, K, H, W, kf):
     enc0 = torch.cat([k[0] for k in k0]); enc1 = torch.cat([k[0] for k in k1])
     assert torch.equal(enc0, enc1)
     np.testing.assert_array_equal(enc1[B - 1].cpu().numpy(), oracle.encode_initial_masks(masks[B - 1]))
+
+
+def test_custom_ops_compile_fullgraph_and_opcheck():
+    """torch.compile(fullgraph=True) traces the path's custom ops without a graph break (fake kernels) and the compiled
+    function returns the eager kernels' bits; torch.library.opcheck validates schema and fake-tensor consistency."""
+    K, H, W = 6, 240, 320
+    masks, head = _inputs(2, K, H, W, seed=77)
+    fg, ce, of, ee = (torch.from_numpy(head[k]).cuda() for k in ("foreground", "center", "offset", "eee_boundary"))
+    dm = torch.from_numpy(masks).cuda()
+    args = (fg, ce, of, ee, 4, 4.0, 0.3, 7, 200, 512, 2048, 1000, -1.0, 2 * 200, True)
+
+    def f(dm, fg, ce, of, ee):
+        enc = torch.ops.quber.encode_initial_masks(dm, 10)
+        per, uni, fgm = torch.ops.quber.mask_boundary(dm, 3)
+        post = torch.ops.quber.post_process(fg, ce, of, ee, 4, 4.0, 0.3, 7, 200, 512, 2048, 1000, -1.0, 2 * 200, True)
+        return enc, uni, post[3], post[4], post[8]
+
+    eager = f(dm, fg, ce, of, ee)
+    comp = torch.compile(f, fullgraph=True, backend="eager")(dm, fg, ce, of, ee)
+    for a, b in zip(eager, comp):
+        assert torch.equal(a, b)
+    ref = ops.post_process(fg, ce, of, ee, scale=4, max_instances=400, label_dtype=torch.uint8)
+    assert torch.equal(eager[2], ref["panoptic"]) and torch.equal(eager[3], ref["label_map"])
+    torch.library.opcheck(torch.ops.quber.post_process.default, args, test_utils=("test_schema", "test_faketensor"))
+    torch.library.opcheck(torch.ops.quber.mask_boundary.default, (dm, 3), test_utils=("test_schema", "test_faketensor"))
+    a = torch.randn(300, 256, device="cuda")
+    w = torch.randn(192, 256, device="cuda")
+    hi, lo = torch.ops.quber.split_tf32(w)
+    torch.library.opcheck(torch.ops.quber.gemm_bias_act_x3.default, (a, hi, lo, None, True, False), test_utils=("test_schema", "test_faketensor"))
