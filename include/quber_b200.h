@@ -124,6 +124,12 @@ typedef struct quber_post_params {
     float void_label;       /* -1 */
     int32_t max_instances;  /* capacity (rows) of masks/labels/scores/boxes over the whole batch */
     int32_t flags;          /* QUBER_POST_* bits */
+    /* Cropped frames — detectron2's sem_seg_postprocess as called at model.py:266-289 crops the up-sampled maps to the
+     * image size (`result[:, :img_h, :img_w]`) before the (identity) resize: armbench frames are 750 x 1333 while the
+     * head outputs are 188 x 334 (x4 = 752 x 1336).  All three 0 = no crop (in_h = H / scale, in_w = W / scale). */
+    int32_t in_h, in_w;     /* low-resolution input size; in_h * scale >= H, in_w * scale >= valid_w */
+    int32_t valid_w;        /* logical frame width <= W; W stays the row pitch of every output (W % 8 == 0) and the
+                               columns valid_w .. W-1 are void (never foreground, never a centre) */
 } quber_post_params;
 
 /* centers_yx / n_centers are INPUTS (group_pixels with caller-supplied centres, post_processing.py:44);
@@ -371,6 +377,20 @@ int quber_rle_encode(const uint8_t *masks, int n, int H, int W, uint32_t *counts
                      void *workspace, size_t workspace_bytes, int32_t *status, void *stream);
 long long quber_rle_from_string(const char *s, size_t len, uint32_t *counts, size_t cap);
 long long quber_rle_to_string(const uint32_t *counts, size_t m, char *s, size_t cap);
+
+/* ---------------------------------------------------------------------------------------------
+ * Size-changing steps either side of the path (csrc/resize.cu).
+ * quber_upsample_crop_resize — MaskRefinerInsEmbedHead's x`scale` bilinear up-sampling (model.py:689-708, `mul` = the
+ *     offset's post-scale, :698) + detectron2 sem_seg_postprocess as called at model.py:266-289 (crop to the image size
+ *     `result[:, :crop_h, :crop_w]`, bilinear resize to (out_h, out_w), align_corners=False) in one pass:
+ *     src dev [B,C,h,w] float32 -> dst dev [B,C,out_h,out_w] float32.  out == crop is the identity resize (the crop only).
+ *     Bit-exact with the oracle; within 2e-6 of PyTorch's two F.interpolate calls on unit-scale maps.
+ * quber_resize_nearest_u8 — cv2.resize(mask, (out_w, out_h), interpolation=cv2.INTER_NEAREST) on n uint8 planes
+ *     (maskrefiner/data/dataset_mappers/target_generator.py:238, eval/refiner_model.py:226-236): bit-exact with OpenCV.
+ * ------------------------------------------------------------------------------------------- */
+int quber_upsample_crop_resize(const float *src, int B, int C, int h, int w, int scale, float mul, int crop_h, int crop_w,
+                               int out_h, int out_w, float *dst, void *stream);
+int quber_resize_nearest_u8(const uint8_t *src, int n, int h, int w, int out_h, int out_w, uint8_t *dst, void *stream);
 
 #ifdef __cplusplus
 }

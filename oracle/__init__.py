@@ -235,3 +235,21 @@ def rle_from_string(s):
     lib().oracle_rle_from_string.restype = ctypes.c_size_t
     m = lib().oracle_rle_from_string(ctypes.c_char_p(s), _p(cnts))
     return cnts[:m].copy()
+
+
+def upsample_crop_resize(src, scale, crop_hw, out_hw, mul=1.0):
+    """model.py:689-708 + detectron2 sem_seg_postprocess (model.py:266-289): [C,h,w] -> [C,out_h,out_w]."""
+    src = _c(src, np.float32)
+    C, h, w = src.shape
+    out = np.empty((C, int(out_hw[0]), int(out_hw[1])), np.float32)
+    lib().oracle_upsample_crop_resize(_p(src), C, h, w, int(scale), ctypes.c_float(mul), int(crop_hw[0]), int(crop_hw[1]),
+                                      int(out_hw[0]), int(out_hw[1]), _p(out))
+    return out
+
+
+def resize_nearest(mask, out_hw):
+    """cv2.resize(mask, (out_w, out_h), interpolation=cv2.INTER_NEAREST) for one [h,w] uint8 plane."""
+    mask = _c(mask, np.uint8)
+    out = np.empty((int(out_hw[0]), int(out_hw[1])), np.uint8)
+    lib().oracle_resize_nearest_u8(_p(mask), mask.shape[0], mask.shape[1], out.shape[0], out.shape[1], _p(out))
+    return out

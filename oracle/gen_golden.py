@@ -547,8 +547,38 @@ def gen_rle():
     np.savez_compressed(os.path.join(OUT, "rle.npz"), **out)
 
 
+def gen_resize():
+    """A7 (detectron2 sem_seg_postprocess as called at model.py:266-289, un-vendored: restated as
+    `F.interpolate(result[:, :h, :w].expand(1,-1,-1,-1), size=(oh, ow), mode="bilinear", align_corners=False)[0]` on top of
+    the head's x4 F.interpolate, model.py:689-708) executed with torch, and cv2.resize INTER_NEAREST on masks
+    (target_generator.py:238) executed with cv2.  The float vectors are torch CPU's: the oracle / kernels agree with
+    them to ~2e-6 (PyTorch's CPU and CUDA builds differ from each other at that level), not bit for bit."""
+    import cv2
+    F = torch.nn.functional
+    rng = np.random.default_rng(17)
+    out = {}
+    low = rng.normal(0, 3, (3, 24, 42)).astype(np.float32)
+    out["low"] = low
+    cases = {"crop_only": ((94, 166), (94, 166)), "armbench": ((94, 166), (141, 250)), "down": ((96, 168), (60, 100)),
+             "near_identity": ((75, 150), (76, 149))}
+    for name, (crop, size) in cases.items():
+        up = F.interpolate(torch.from_numpy(low)[None], scale_factor=4, mode="bilinear", align_corners=False)[0] * 4.0
+        res = F.interpolate(up[:, :crop[0], :crop[1]].expand(1, -1, -1, -1), size=size, mode="bilinear", align_corners=False)[0]
+        out[f"{name}_crop"], out[f"{name}_size"] = np.array(crop), np.array(size)
+        out[f"{name}_out"] = res.numpy()
+    m = (rng.random((2, 97, 131)) < 0.3).astype(np.uint8) * 255
+    out["nn_masks"] = np.packbits(m != 0)
+    out["nn_shape"] = np.array(m.shape)
+    for i, size in enumerate(((480, 640), (50, 77), (97, 131), (200, 131))):
+        r = np.stack([cv2.resize(x, (size[1], size[0]), interpolation=cv2.INTER_NEAREST) for x in m])
+        out[f"nn{i}_size"] = np.array(size)
+        out[f"nn{i}_out"] = np.packbits(r != 0)
+    np.savez_compressed(os.path.join(OUT, "resize.npz"), **out)
+    print("resize.npz ok")
+
+
 SECTIONS = {"encode": gen_encode, "boundary": gen_boundary, "post": gen_post, "msda": gen_msda,
-            "post_ii": gen_post_ii, "decode_types": gen_decode_types, "quadruple": gen_quadruple, "rle": gen_rle}
+            "post_ii": gen_post_ii, "decode_types": gen_decode_types, "quadruple": gen_quadruple, "rle": gen_rle, "resize": gen_resize}
 
 
 def main():

@@ -222,6 +222,59 @@ ORACLE_API void oracle_upsample_bilinear(const float *src, int C, int h, int w, 
             }
 }
 
+/* The same sample for an arbitrary ratio r = in / out: the source index r * (dst + 0.5) - 0.5 is ONE fused
+ * multiply-add, as both PyTorch builds evaluate it (nvcc contracts it in area_pixel_compute_source_index, the CPU kernel's
+ * compiler does the same) — at r = 1/4 the product is exact and the two forms agree, at other ratios the unfused form
+ * moves the interpolation weight by up to an ulp of the coordinate (3e-5 at x = 300). */
+static inline float resize_sample_at(const float *src, int h, int w, float rh, float rw, int oy, int ox) {
+    float sy = fmaf(rh, (float)oy + 0.5f, -0.5f); if (sy < 0.f) sy = 0.f;
+    float sx = fmaf(rw, (float)ox + 0.5f, -0.5f); if (sx < 0.f) sx = 0.f;
+    const int y1 = (int)sy, x1 = (int)sx;
+    const int yp = (y1 < h - 1) ? 1 : 0, xp = (x1 < w - 1) ? 1 : 0;
+    const float ly = sy - (float)y1, lx = sx - (float)x1;
+    const float hy = 1.f - ly, hx = 1.f - lx;
+    const float a = src[(size_t)y1 * w + x1], b = src[(size_t)y1 * w + x1 + xp];
+    const float c = src[(size_t)(y1 + yp) * w + x1], d = src[(size_t)(y1 + yp) * w + x1 + xp];
+    const float top = hx * a + lx * b, bot = hx * c + lx * d;
+    return hy * top + ly * bot;
+}
+
+/* A7: detectron2 sem_seg_postprocess (modeling/postprocessing.py, un-vendored; called at model.py:266-289):
+ *   F.interpolate(result[:, :img_h, :img_w].expand(1,-1,-1,-1), size=(out_h, out_w), mode="bilinear", align_corners=False)[0]
+ * on top of the x-scale up-sampling of model.py:689-708.  src [C,h,w] low-resolution maps -> dst [C,out_h,out_w].
+ * With a `size` and no scale factor PyTorch uses r = (float)in / out per axis (aten UpSample.h
+ * area_pixel_compute_scale), otherwise the same kernel as above; out == crop is the identity. */
+ORACLE_API void oracle_upsample_crop_resize(const float *src, int C, int h, int w, int scale, float mul, int crop_h, int crop_w,
+                                            int out_h, int out_w, float *dst) {
+    const int H = h * scale, W = w * scale;
+    float *full = (float *)malloc(sizeof(float) * (size_t)H * W);
+    float *crop = (float *)malloc(sizeof(float) * (size_t)crop_h * crop_w);
+    const float rh = (float)crop_h / (float)out_h, rw = (float)crop_w / (float)out_w;
+    for (int c = 0; c < C; ++c) {
+        oracle_upsample_bilinear(src + (size_t)c * h * w, 1, h, w, scale, mul, full);
+        for (int y = 0; y < crop_h; ++y) memcpy(crop + (size_t)y * crop_w, full + (size_t)y * W, sizeof(float) * crop_w);
+        for (int y = 0; y < out_h; ++y)
+            for (int x = 0; x < out_w; ++x)
+                dst[((size_t)c * out_h + y) * out_w + x] =
+                    (out_h == crop_h && out_w == crop_w) ? crop[(size_t)y * crop_w + x] : resize_sample_at(crop, crop_h, crop_w, rh, rw, y, x);
+    }
+    free(full); free(crop);
+}
+
+/* cv2.resize(mask, (out_w, out_h), interpolation=cv2.INTER_NEAREST) on one uint8 plane (target_generator.py:238,
+ * perturbed_panoptic_dataset_mapper.py:197): OpenCV's resizeNN takes source index min(floor(dst * (src / dst_size)), src - 1)
+ * with the ratio in double. */
+ORACLE_API void oracle_resize_nearest_u8(const uint8_t *src, int h, int w, int out_h, int out_w, uint8_t *dst) {
+    const double fy = (double)h / out_h, fx = (double)w / out_w;
+    for (int y = 0; y < out_h; ++y) {
+        int sy = (int)floor(y * fy); if (sy > h - 1) sy = h - 1;
+        for (int x = 0; x < out_w; ++x) {
+            int sx = (int)floor(x * fx); if (sx > w - 1) sx = w - 1;
+            dst[(size_t)y * out_w + x] = src[(size_t)sy * w + sx];
+        }
+    }
+}
+
 /* ------------------------------------------------------------------------- */
 /* A8: find_instance_center — post_processing.py:9-41                          */
 /* ------------------------------------------------------------------------- */

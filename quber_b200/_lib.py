@@ -22,7 +22,8 @@ class PostParams(ctypes.Structure):
                 ("offset_mul", c_f), ("eee_channels", ctypes.c_int32), ("threshold", c_f),
                 ("nms_kernel", ctypes.c_int32), ("top_k", ctypes.c_int32), ("min_area", ctypes.c_int32),
                 ("stuff_area", ctypes.c_int32), ("label_divisor", ctypes.c_int32), ("void_label", c_f),
-                ("max_instances", ctypes.c_int32), ("flags", ctypes.c_int32)]
+                ("max_instances", ctypes.c_int32), ("flags", ctypes.c_int32),
+                ("in_h", ctypes.c_int32), ("in_w", ctypes.c_int32), ("valid_w", ctypes.c_int32)]
 
 
 class PostIO(ctypes.Structure):
@@ -72,6 +73,8 @@ SYMBOLS = {
     "quber_rle_encode": (c_i, [c_vp, c_i, c_i, c_i, c_vp, c_sz, c_vp, c_vp, c_sz, c_vp, c_vp]),
     "quber_rle_from_string": (ctypes.c_longlong, [ctypes.c_char_p, c_sz, c_vp, c_sz]),
     "quber_rle_to_string": (ctypes.c_longlong, [c_vp, c_sz, c_vp, c_sz]),
+    "quber_upsample_crop_resize": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_f, c_i, c_i, c_i, c_i, c_vp, c_vp]),
+    "quber_resize_nearest_u8": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_msda_forward_fused": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_msda_forward": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
 }

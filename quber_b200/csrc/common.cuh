@@ -73,6 +73,9 @@ struct UpSampler {
     int h, w, scale;
     float r;
     __host__ __device__ UpSampler(int H, int W, int s) : h(H / s), w(W / s), scale(s), r(1.0f / (float)s) {}
+    // explicit low-resolution size: the full-resolution map is then a CROP of the up-sampled one (sem_seg_postprocess'
+    // `result[:, :img_h, :img_w]`, detectron2 as called at model.py:266-289), e.g. 188 x 334 -> 750 x 1333
+    __host__ __device__ UpSampler(int h_, int w_, int s, bool) : h(h_), w(w_), scale(s), r(1.0f / (float)s) {}
     __device__ __forceinline__ float at(const float *__restrict__ plane, int oy, int ox) const {
         if (scale == 1) return __ldg(plane + (size_t)oy * w + ox);
         float sy = __fsub_rn(__fmul_rn(r, __fadd_rn((float)oy, 0.5f)), 0.5f);

@@ -42,6 +42,12 @@ struct PostWs {
     size_t total;
 };
 
+// low-resolution input size and logical width of the frames (quber_post_params.in_h / in_w / valid_w, 0 = derived)
+__host__ __device__ inline UpSampler up_of(const quber_post_params &p) {
+    return UpSampler(p.in_h > 0 ? p.in_h : p.H / p.scale, p.in_w > 0 ? p.in_w : p.W / p.scale, p.scale, true);
+}
+__host__ __device__ inline int valid_w_of(const quber_post_params &p) { return p.valid_w > 0 ? p.valid_w : p.W; }
+
 static PostWs carve(const quber_post_params &p, void *base) {
     PostWs w;
     const size_t B = p.B, H = p.H, W = p.W, WB = (W + 31) / 32, K1 = (size_t)p.top_k + 1;
@@ -73,13 +79,14 @@ static PostWs carve(const quber_post_params &p, void *base) {
 // (only positive survivors can pass the final `> max(kth, 0)` test at :37/:41).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(P_THREADS)
-center_nms_kernel(const float *__restrict__ center, int H, int W, int scale, float threshold, int nms_kernel,
-                  uint32_t *__restrict__ bitmask) {
+center_nms_kernel(const float *__restrict__ center, quber_post_params pp, uint32_t *__restrict__ bitmask) {
     extern __shared__ float nsm[];
+    const int H = pp.H, W = pp.W, scale = pp.scale, nms_kernel = pp.nms_kernel, Wv = valid_w_of(pp);
+    const float threshold = pp.threshold;
     const int p = (nms_kernel - 1) / 2;
     const int TWp = N_TW + nms_kernel - 1, THp = N_TH + nms_kernel - 1;
     float *T = nsm, *RM = nsm + THp * TWp;        // RM: [THp][N_TW]
-    const UpSampler up(H, W, scale);
+    const UpSampler up = up_of(pp);
     const int b = blockIdx.z, ty0 = blockIdx.y * N_TH, tx0 = blockIdx.x * N_TW;
     const float *plane = center + (size_t)b * up.h * up.w;
     const int tid = threadIdx.x;
@@ -108,8 +115,8 @@ center_nms_kernel(const float *__restrict__ center, int H, int W, int scale, flo
     for (int idx = tid; idx < THp * TWp; idx += P_THREADS) {
         const int r = idx / TWp, c = idx - r * TWp;
         const int gy = ty0 - p + r, gx = tx0 - p + c;
-        float t = -INFINITY;                         // max_pool2d pads with -inf
-        if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+        float t = -INFINITY;                         // max_pool2d pads with -inf (columns past the cropped width too)
+        if (gy >= 0 && gy < H && gx >= 0 && gx < Wv) {
             const float v = up.at(plane, gy, gx);
             t = v > threshold ? v : -1.0f;          // F.threshold(x, thr, -1)
         }
@@ -130,7 +137,7 @@ center_nms_kernel(const float *__restrict__ center, int H, int W, int scale, flo
         float m = RM[row * N_TW + xx];
         for (int j = 1; j < nms_kernel; ++j) m = fmaxf(m, RM[(row + j) * N_TW + xx]);
         const float v = T[(row + p) * TWp + xx + p];
-        const bool cand = gy < H && gx < W && v == m && v > 0.f;
+        const bool cand = gy < H && gx < Wv && v == m && v > 0.f;
         const uint32_t word = __ballot_sync(0xffffffffu, cand);
         const int wx = (tx0 >> 5) + half;
         if (lane == 0 && gy < H && wx < WB) bitmask[((size_t)b * H + gy) * WB + wx] = word;
@@ -164,14 +171,15 @@ __device__ __forceinline__ int block_excl_scan(int v, int *warp_tot, int &total)
 // raster-ordered emission.  post_processing.py:36-41.  One CTA per image.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(SEL_THREADS)
-center_select_kernel(const float *__restrict__ center, int H, int W, int scale, int top_k, int no_topk,
+center_select_kernel(const float *__restrict__ center, quber_post_params pp, int no_topk,
                      const uint32_t *__restrict__ bitmask, int32_t *__restrict__ centers_yx, int32_t *__restrict__ n_centers,
                      int32_t *__restrict__ overflow) {
+    const int H = pp.H, W = pp.W, top_k = pp.top_k;
     __shared__ float vals[SEL_SMEM_VALS];
     __shared__ int hist[256];
     __shared__ int warp_tot[32];
     __shared__ int s_n, s_fill, s_bin, s_remaining;
-    const UpSampler up(H, W, scale);
+    const UpSampler up = up_of(pp);
     const int b = blockIdx.x, tid = threadIdx.x, WB = (W + 31) / 32, nwords = H * WB;
     const float *plane = center + (size_t)b * up.h * up.w;
     const uint32_t *bm = bitmask + (size_t)b * nwords;
@@ -359,7 +367,8 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
         cyx[i] = make_float2((float)io.centers_yx[((size_t)b * p.top_k + i) * 2], (float)io.centers_yx[((size_t)b * p.top_k + i) * 2 + 1]);
     for (int i = tid; i <= p.top_k; i += P_THREADS) hist[i] = 0;
     __syncthreads();
-    const UpSampler up(H, W, p.scale);
+    const UpSampler up = up_of(p);
+    const int Wv = valid_w_of(p);
     const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
     // a warp covers 8 rows x 32 pixels of the tile (not 2 x 128): the compact footprint is what lets the centre pruning
     // below skip a centre for the WHOLE warp
@@ -378,7 +387,7 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             id[j] = 0;
-            if (sem[j] > QUBER_FG_LOGIT_CUT) fgm |= 1u << j;           // r.sigmoid().round() == 1
+            if (sem[j] > QUBER_FG_LOGIT_CUT && x0 + j < Wv) fgm |= 1u << j;   // r.sigmoid().round() == 1 (inside the crop)
         }
         if (io.sem_seg) {
             float *o = io.sem_seg + (size_t)b * HW + pix;
@@ -565,7 +574,7 @@ emit_kernel(quber_post_params p, quber_post_io io, const uint16_t *__restrict__ 
     for (int i = tid; i < ninst * (int)(sizeof(InstStat) / 4); i += P_THREADS) reinterpret_cast<uint32_t *>(sst)[i] = 0;
     for (int i = tid; i <= nc; i += P_THREADS) nid[i] = newid[(size_t)b * (p.top_k + 1) + i];
     __syncthreads();
-    const UpSampler up(H, W, p.scale);
+    const UpSampler up = up_of(p);
     const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
     const int y = blockIdx.y * P_TH + (tid >> 4), x0 = blockIdx.x * P_TW + (tid & 15) * 8;
     const bool inb = y < H && x0 < W;                       // every lane stays alive: the statistics use warp collectives
@@ -723,7 +732,7 @@ finalize_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict
                 const int32_t *__restrict__ has_stuff, const InstStat *__restrict__ stats) {
     const int b = blockIdx.x;
     const int ninst = n_inst[b], hs = has_stuff[b], off = io.inst_offsets[b];
-    const UpSampler up(p.H, p.W, p.scale);
+    const UpSampler up = up_of(p);
     const float *cplane = io.center + (size_t)b * up.h * up.w;
     for (int i = threadIdx.x; i < ninst; i += blockDim.x) {
         const int row = off + i;
@@ -818,7 +827,13 @@ static int post_validate(const quber_post_params *p) {
         (p->eee_channels != 0 && (p->eee_channels < 2 || p->eee_channels > 4)) ||
         ((p->flags & QUBER_POST_LABEL_U8) && p->top_k > 255))
         return QUBER_E_INVALID;
-    if (p->W % 8 != 0 || p->H % p->scale != 0 || p->W % p->scale != 0) return QUBER_E_UNSUPPORTED;
+    if (p->in_h < 0 || p->in_w < 0 || p->valid_w < 0 || p->valid_w > p->W) return QUBER_E_INVALID;
+    if (p->W % 8 != 0) return QUBER_E_UNSUPPORTED;
+    if (p->in_h == 0 && p->H % p->scale != 0) return QUBER_E_UNSUPPORTED;       // derived low-resolution size must be exact
+    if (p->in_w == 0 && p->W % p->scale != 0) return QUBER_E_UNSUPPORTED;
+    // a cropped frame must lie inside the up-sampled map
+    if (p->in_h > 0 && (long long)p->in_h * p->scale < p->H) return QUBER_E_INVALID;
+    if (p->in_w > 0 && (long long)p->in_w * p->scale < (p->valid_w > 0 ? p->valid_w : p->W)) return QUBER_E_INVALID;
     return QUBER_OK;
 }
 
@@ -851,9 +866,9 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
         const int TWp = N_TW + p.nms_kernel - 1, THp = N_TH + p.nms_kernel - 1;
         const size_t smem = ((size_t)THp * TWp + (size_t)THp * N_TW) * sizeof(float);
         dim3 grid(cdiv(p.W, N_TW), cdiv(p.H, N_TH), p.B);
-        center_nms_kernel<<<grid, P_THREADS, smem, st>>>(io.center, p.H, p.W, p.scale, p.threshold, p.nms_kernel, ws.bitmask);
+        center_nms_kernel<<<grid, P_THREADS, smem, st>>>(io.center, p, ws.bitmask);
         if (int rc = check_launch("center_nms_kernel")) return rc;
-        center_select_kernel<<<p.B, SEL_THREADS, 0, st>>>(io.center, p.H, p.W, p.scale, p.top_k, (p.flags & QUBER_POST_NO_TOPK) != 0,
+        center_select_kernel<<<p.B, SEL_THREADS, 0, st>>>(io.center, p, (p.flags & QUBER_POST_NO_TOPK) != 0,
                                                          ws.bitmask, io.centers_yx, io.n_centers, io.status);
         if (int rc = check_launch("center_select_kernel")) return rc;
     }

@@ -209,36 +209,36 @@ class MaskRefiner(nn.Module):
         heights = [bi.get("height", sz[0]) for bi, sz in zip(batched_inputs, sizes)]
         widths = [bi.get("width", sz[1]) for bi, sz in zip(batched_inputs, sizes)]
         eee = out.get("eee_boundary") if self.eee_boundary_on else None
-        identity = all(sz == (x.shape[2], x.shape[3]) and (h, w) == sz for sz, h, w in zip(sizes, heights, widths))
         want = ("sem_seg", "panoptic", "masks") + (("eee_full",) if eee is not None else ())
         kw = dict(threshold=self.threshold, nms_kernel=self.nms_kernel, top_k=self.top_k, stuff_area=self.stuff_area,
                   label_divisor=self.meta["label_divisor"], want=want)
-        results = []
-        if identity and x.shape[3] % 8 == 0:
-            # sem_seg_postprocess is the identity: up-sample inside the fused kernels
-            r = ops.post_process(out["foreground"], out["center"], out["offset"], eee, scale=s,
-                                 max_instances=B * self.max_instances_per_image, **kw)
+        results = [None] * B
+        # sem_seg_postprocess (model.py:266-289) = crop to the image size, bilinear resize to (height, width).  Frames that
+        # share (image size, output size) go through the kernels together.
+        groups = {}
+        for b in range(B):
+            groups.setdefault((tuple(sizes[b]), (int(heights[b]), int(widths[b]))), []).append(b)
+        full_hw = (out["foreground"].shape[2] * s, out["foreground"].shape[3] * s)
+        for (size, out_hw), idx in groups.items():
+            sel = (lambda t: t) if len(idx) == B else (lambda t: t[idx].contiguous())
+            fg, ce, of = sel(out["foreground"]), sel(out["center"]), sel(out["offset"])
+            ee = None if eee is None else sel(eee)
+            n = len(idx)
+            if out_hw == size:
+                # the resize is the identity: up-sample inside the fused kernels; a frame smaller than
+                # the up-sampled maps (armbench 750 x 1333 of 752 x 1336) is their top-left corner
+                crop = None if (size == full_hw and size[1] % 8 == 0) else size
+                r = ops.post_process(fg, ce, of, ee, scale=s, max_instances=n * self.max_instances_per_image, crop=crop, **kw)
+            else:
+                # a real resize: full-resolution maps in one pass per head (up-sample, crop, resize), then the same kernels
+                rs = lambda t, mul=1.0: ops.upsample_crop_resize(t, s, size, out_hw, mul)
+                r = ops.post_process(rs(fg), rs(ce), rs(of, float(s)), None if ee is None else rs(ee), scale=1, offset_mul=1.0,
+                                     max_instances=n * self.max_instances_per_image, crop=out_hw, **kw)
             self._check_pool(r)
-            mfull = None
-            if self.eee_mask_on:
-                mfull = torch.nn.functional.interpolate(out["eee_mask"], scale_factor=s, mode="bilinear", align_corners=False)
-            for b in range(B):
-                results.append(self._result(r, b, b, heights[b], widths[b], None if mfull is None else mfull[b]))
-        else:
-            up = lambda t: torch.nn.functional.interpolate(t, scale_factor=s, mode="bilinear", align_corners=False)
-            full = {k: up(v) for k, v in out.items()}
-            full["offset"] = full["offset"] * s
-            for b in range(B):
-                pp = lambda t: network.sem_seg_postprocess(t[b], sizes[b], heights[b], widths[b])[None].contiguous()
-                e = pp(full["eee_boundary"]) if eee is not None else None
-                Wb = widths[b]
-                pad = (-Wb) % 8
-                padw = (lambda t: torch.nn.functional.pad(t, (0, pad), value=-1e4).contiguous()) if pad else (lambda t: t)
-                r = ops.post_process(padw(pp(full["foreground"])), padw(pp(full["center"])), padw(pp(full["offset"])),
-                                     None if e is None else padw(e), scale=1, max_instances=self.max_instances_per_image, **kw)
-                self._check_pool(r)
-                m = pp(full["eee_mask"])[0] if self.eee_mask_on else None
-                results.append(self._result(r, 0, b, heights[b], Wb, m, crop=Wb if pad else None))
+            mfull = ops.upsample_crop_resize(sel(out["eee_mask"]), s, size, out_hw) if self.eee_mask_on else None   # model.py:282-284
+            for j, b in enumerate(idx):
+                results[b] = self._result(r, j, b, out_hw[0], out_hw[1], None if mfull is None else mfull[j],
+                                          crop=out_hw[1] if r["valid_w"] != r["panoptic"].shape[-1] else None)
         return results
 
     @staticmethod

@@ -152,13 +152,16 @@ def quadruple_maps(gt, pred):
 def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=None, threshold=0.3, nms_kernel=7,
                  top_k=200, min_area=512, stuff_area=2048, label_divisor=1000, void_label=-1.0, max_instances=None,
                  want=("sem_seg", "eee_full", "eee_onehot", "panoptic", "label_map", "masks"), centers=None,
-                 n_centers=None, no_topk=False, label_dtype=torch.int32):
+                 n_centers=None, no_topk=False, label_dtype=torch.int32, crop=None):
     """One fused call for model.py:689-708 + :260-356 + post_processing.py:9-221 + eval_utils.py:308-328.
 
     foreground [B,1,h,w], center [B,1,h,w], offset [B,2,h,w], eee [B,C,h,w] float32 CUDA tensors at
     1/scale resolution (scale=1: full-resolution maps).  Returns a dict of device tensors; nothing is
     synchronised or copied to the host.  label_dtype=torch.uint8 (QUBER_POST_LABEL_U8, needs top_k <= 255) makes
     `label_map` a byte map: a quarter of the bytes to write, to send to the host and to all-gather.
+    crop=(Hc, Wc): the frames are the top-left Hc x Wc corner of the up-sampled maps (sem_seg_postprocess' crop,
+    model.py:266-289; armbench 188 x 334 -> 750 x 1333).  Every map output then has Hc rows and a row PITCH of Wc rounded
+    up to 8 (out["valid_w"] = Wc; columns past it are void) — slice `[..., :Wc]` for the reference's shape.
     """
     _need_cuda(foreground, "foreground", torch.float32)
     if label_dtype not in (torch.int32, torch.uint8):
@@ -174,6 +177,12 @@ def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=No
     dev = foreground.device
     B, _, h, w = foreground.shape
     H, W = h * scale, w * scale
+    in_h = in_w = valid_w = 0
+    if crop is not None:
+        Hc, Wc = int(crop[0]), int(crop[1])
+        if not (0 < Hc <= h * scale and 0 < Wc <= w * scale):
+            raise ValueError("crop must lie inside the up-sampled maps")
+        H, W, in_h, in_w, valid_w = Hc, (Wc + 7) // 8 * 8, h, w, Wc
     C = 0
     if eee is not None:
         _need_cuda(eee, "eee", torch.float32)
@@ -187,7 +196,7 @@ def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=No
         max_instances = B * max(top_k, 1)
     flags = 0
     p = _lib.PostParams(B, H, W, scale, offset_mul, C, threshold, nms_kernel, top_k, min_area, stuff_area, label_divisor,
-                        void_label, max_instances, 0)
+                        void_label, max_instances, 0, in_h, in_w, valid_w)
     out = {}
     i32, f32, u8 = torch.int32, torch.float32, torch.uint8
     mk = lambda name, shape, dt: out.setdefault(name, torch.empty(shape, dtype=dt, device=dev)) if name in want else None
@@ -228,6 +237,7 @@ def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=No
     with torch.cuda.device(dev):
         _lib.check(L.quber_post_process(ctypes.byref(p), ctypes.byref(io), _ptr(ws), nbytes, _stream()), "quber_post_process")
     out["max_instances"] = max_instances
+    out["valid_w"] = valid_w if valid_w else W
     return out
 
 
@@ -683,6 +693,33 @@ def fuse_concat_rows(sources, ops_, pitch=None, out_dtype=torch.bfloat16):
 
 
 
+def upsample_crop_resize(x, scale, crop_hw, out_hw, mul=1.0):
+    """model.py:689-708 + detectron2 sem_seg_postprocess (model.py:266-289) in one pass: x [B,C,h,w] float32 head
+    outputs -> [B,C,out_h,out_w] = resize(crop(upsample(x, scale) * mul, crop_hw), out_hw), bilinear,
+    align_corners=False at both steps (the second is the identity when out_hw == crop_hw)."""
+    _need_cuda(x, "x", torch.float32)
+    B, C, h, w = x.shape
+    ch, cw, oh, ow = int(crop_hw[0]), int(crop_hw[1]), int(out_hw[0]), int(out_hw[1])
+    out = torch.empty((B, C, oh, ow), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().quber_upsample_crop_resize(_ptr(x), B, C, h, w, int(scale), float(mul), ch, cw, oh, ow, _ptr(out),
+                                                         _stream()), "quber_upsample_crop_resize")
+    return out
+
+
+def resize_nearest(masks, out_hw):
+    """cv2.resize(m, (out_w, out_h), interpolation=cv2.INTER_NEAREST) for every plane of masks uint8 [...,h,w] (CUDA)."""
+    _need_cuda(masks, "masks", torch.uint8)
+    h, w = masks.shape[-2:]
+    n = masks.numel() // (h * w)
+    oh, ow = int(out_hw[0]), int(out_hw[1])
+    out = torch.empty(tuple(masks.shape[:-2]) + (oh, ow), dtype=torch.uint8, device=masks.device)
+    if n:
+        with torch.cuda.device(masks.device):
+            _lib.check(_lib.lib().quber_resize_nearest_u8(_ptr(masks), n, h, w, oh, ow, _ptr(out), _stream()), "quber_resize_nearest_u8")
+    return out
+
+
 def rle_decode(counts, offsets, n, H, W, value=1, packed=False, out=None, check=False):
     """pycocotools.mask.decode on the device (perturbed_panoptic_dataset_mapper.py:195-214): `counts` uint32-as-int32
     CUDA tensor holding the run lengths of `n` masks back to back (column-major runs, starting with zeros), `offsets`
@@ -961,6 +998,22 @@ def _register():
     def _(label_map, counts, fg, zero_depth, thr, max_per):
         B = label_map.shape[0]
         return torch.empty_like(label_map), label_map.new_empty((B, max_per), dtype=torch.uint8), label_map.new_empty((B,), dtype=torch.int32)
+
+    @custom_op("quber::upsample_crop_resize", mutates_args=(), device_types="cuda")
+    def _ucr(x: T, scale: int, crop_h: int, crop_w: int, out_h: int, out_w: int, mul: float) -> T:
+        return upsample_crop_resize(x, scale, (crop_h, crop_w), (out_h, out_w), mul)
+
+    @_ucr.register_fake
+    def _(x, scale, crop_h, crop_w, out_h, out_w, mul):
+        return x.new_empty((x.shape[0], x.shape[1], out_h, out_w))
+
+    @custom_op("quber::resize_nearest", mutates_args=(), device_types="cuda")
+    def _rn(masks: T, out_h: int, out_w: int) -> T:
+        return resize_nearest(masks, (out_h, out_w))
+
+    @_rn.register_fake
+    def _(masks, out_h, out_w):
+        return masks.new_empty(tuple(masks.shape[:-2]) + (out_h, out_w))
 
     @custom_op("quber::rle_decode", mutates_args=(), device_types="cuda")
     def _rled(counts: T, offsets: T, n: int, H: int, W: int, value: int, packed: bool) -> tuple[T, T]:
