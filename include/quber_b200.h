@@ -59,19 +59,21 @@ const char *quber_last_cuda_error(void);
  *   out    dev [B,3,H,W] float32 = (centre heat-map, offset_y/H, offset_x/W)
  *   Later masks overwrite earlier ones in the offset planes, empty masks are skipped, centroid
  *   arithmetic is float64 exactly as in the reference.  W must be a multiple of 16 and `masks`
- *   16-byte aligned (QUBER_E_ALIGN otherwise).
+ *   16-byte aligned (QUBER_E_ALIGN otherwise).  valid_w (0 = W): frames whose width is not a multiple of 16
+ *   (armbench 750 x 1333) are stored with a zero-padded row pitch W and their own width valid_w, which is what the
+ *   x-offset plane is normalised by (predictor.py:346); the zero columns change neither a centroid nor a paste.
  * ------------------------------------------------------------------------------------------- */
 void quber_gaussian_table(int sigma, float *host_table);
 size_t quber_encode_workspace_bytes(int B, int K, int H, int W);
-int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int sigma,
+int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int valid_w, int sigma,
                                const float *gauss, float *out, void *workspace, size_t workspace_bytes,
                                void *stream);
 /* The same from bit-packed masks (quber_host_pack_masks): packed dev uint32 [B*K*H*W / 32], set pixels carry `value`
  * (1..255).  Also writes the byte planes masks_out dev [B,K,H,W] uint8 (0 / value) — what quber_unpack_masks would give —
  * for quber_mask_boundary, so the expansion costs no pass of its own. */
 int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t *masks_out, int B, int K, int H, int W,
-                                      int sigma, const float *gauss, float *out, void *workspace, size_t workspace_bytes,
-                                      void *stream);
+                                      int valid_w, int sigma, const float *gauss, float *out, void *workspace,
+                                      size_t workspace_bytes, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K2  boundary extraction by erosion — replaces mask_to_boundary / masks_to_boundary /

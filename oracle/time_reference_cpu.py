@@ -28,6 +28,47 @@ def med(f, n=3):
     return float(np.median(ts))
 
 
+_REF = {}
+
+
+def reference_frame(c, g, seed, threads, n_layers=6):
+    """ONE frame of a bench.py config through the reference's OWN Python, timed: the predictor's encode block
+    (predictor.py:304-357), the cv2 erosions (util.py:72-99), `n_layers` x ms_deform_attn_core_pytorch, F.interpolate x4 +
+    sem_seg_postprocess' crop + sigmoid().round() + get_panoptic_segmentation + the instance loop's masks + the argmax
+    decode (model.py:689-708, :266-336; eval_utils.py:310-313).  -> (instances, seconds).  bench.py --impl reference."""
+    import cv2
+    torch.set_num_threads(threads)
+    cv2.setNumThreads(threads)
+    if not _REF:
+        _REF.update(bfn=gg.ref_boundary_fns(), pp=gg.ref_post_processing(), mf=gg.ref_msda())
+    K, H, W = c["K"], c["H"], c["W"]
+    m = synth.ellipse_masks(K, g["Hf"], g["Wf"], seed=seed, axes=c["axes"], margin=c["margin"])
+    m[:, H:, :] = 0
+    m[:, :, W:] = 0
+    ho = synth.head_outputs(m, seed=seed)
+    low = torch.from_numpy(np.concatenate([ho["foreground"], ho["center"], ho["offset"], ho["eee_boundary"]], 0))[None]
+    masks = np.ascontiguousarray(m[:, :H, :W])
+    msda = synth.msda_inputs(B=1, shapes=c["levels"], mode="module", seed=seed)
+    v, sh = torch.from_numpy(msda["value"]), torch.from_numpy(msda["shapes"])
+    loc, at = torch.from_numpy(msda["loc"]), torch.from_numpy(msda["attn"])
+    bfn, pp, mf = _REF["bfn"], _REF["pp"], _REF["mf"]
+    t0 = time.perf_counter()
+    gg.ref_encode(masks, H, W)
+    per = [bfn["mask_to_boundary"](x, 0.01) for x in masks]
+    bfn["masks_to_boundary"](masks, 0.01)
+    for _ in range(n_layers):
+        mf.ms_deform_attn_core_pytorch(v, sh, loc, at)
+    up = torch.nn.functional.interpolate(low, scale_factor=4, mode="bilinear", align_corners=False)[0][:, :H, :W]
+    fg = up[0:1].sigmoid().round()
+    pan, _ = pp.get_panoptic_segmentation(fg, up[1:2].clone(), up[2:4] * 4, thing_ids={1}, label_divisor=1000, stuff_area=2048,
+                                          void_label=-1, threshold=0.3, nms_kernel=7, top_k=200)
+    pan = pan[0].numpy()
+    masks_out = [pan == l for l in np.unique(pan) if l != -1]
+    am = up[4:8].argmax(0)
+    torch.stack([am == i for i in range(4)])
+    return len(masks_out), time.perf_counter() - t0
+
+
 def main():
     threads = int(sys.argv[1]) if len(sys.argv) > 1 else len(os.sched_getaffinity(0))
     torch.set_num_threads(threads)
@@ -82,7 +123,7 @@ def main():
            "oracle_port_single_thread_instances_per_s": port() / t_port,
            "instances_per_frame": n_inst}
     os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
-    with open(os.path.join(ROOT, "profiles", "r01_reference_python_cpu.json"), "w") as f:
+    with open(os.path.join(ROOT, "profiles", "r02_reference_python_cpu.json"), "w") as f:
         json.dump(out, f, indent=1)
     print(json.dumps(out, indent=1))
 

@@ -40,8 +40,8 @@ SYMBOLS = {
     "quber_last_cuda_error": (ctypes.c_char_p, []),
     "quber_gaussian_table": (None, [c_i, c_vp]),
     "quber_encode_workspace_bytes": (c_sz, [c_i, c_i, c_i, c_i]),
-    "quber_encode_initial_masks": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp]),
-    "quber_encode_initial_masks_packed": (c_i, [c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "quber_encode_initial_masks": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "quber_encode_initial_masks_packed": (c_i, [c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "quber_boundary_dilation": (c_i, [c_i, c_i, c_d]),
     "quber_mask_boundary": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "quber_quadruple_maps": (c_i, [c_vp, c_vp, c_i, c_sz, c_vp, c_vp]),

@@ -120,7 +120,7 @@ struct EncCentre { double cy, cx; int uly, ulx; };
 // resident CTAs per SM asked of the compiler (QUBER_ENCODE_EMIT=0|1|2 selects old / early / early + 5 CTAs for A/B runs).
 template <bool EARLY, int MINB>
 __global__ void __launch_bounds__(E_THREADS, MINB)
-encode_emit_kernel(const EncSums *__restrict__ sums, const uint8_t *__restrict__ lastk, int K, int H, int W, int sigma,
+encode_emit_kernel(const EncSums *__restrict__ sums, const uint8_t *__restrict__ lastk, int K, int H, int W, int norm_w, int sigma,
                    const float *__restrict__ gauss, float *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char smraw[];
     EncCentre *ctr = reinterpret_cast<EncCentre *>(smraw);            // [K]
@@ -168,7 +168,7 @@ encode_emit_kernel(const EncSums *__restrict__ sums, const uint8_t *__restrict__
         }
     }
     if (!EARLY) lk = *reinterpret_cast<const uint2 *>(lastk + (size_t)b * HW + pix);
-    const double dH = (double)H, dW = (double)W;
+    const double dH = (double)H, dW = (double)norm_w;                 // W is the row pitch, norm_w the frame's width
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const uint32_t k = ((j < 4 ? lk.x : lk.y) >> (8 * (j & 3))) & 0xffu;
@@ -204,10 +204,11 @@ extern "C" size_t quber_encode_workspace_bytes(int B, int K, int H, int W) {
     return quber::align_up((size_t)B * K * sizeof(quber::EncSums), 256) + quber::align_up((size_t)B * H * W, 256);
 }
 
-static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *unpacked, int B, int K, int H, int W, int sigma,
+static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *unpacked, int B, int K, int H, int W, int valid_w, int sigma,
                          const float *gauss, float *out, void *workspace, size_t workspace_bytes, void *stream) {
     using namespace quber;
     if (!masks || !gauss || !out || B <= 0 || K <= 0 || K > 254 || H <= 0 || W <= 0 || sigma < 1) return QUBER_E_INVALID;
+    if (valid_w < 0 || valid_w > W) return QUBER_E_INVALID;
     if (W % 16 != 0 || !aligned16(out) || (reinterpret_cast<uintptr_t>(masks) & (packed ? 3u : 15u))) return QUBER_E_ALIGN;
     if (packed && (!unpacked || value < 1 || value > 255)) return QUBER_E_INVALID;
     if (packed && !aligned16(unpacked)) return QUBER_E_ALIGN;
@@ -227,18 +228,18 @@ static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *
 #undef QUBER_REDUCE_LAUNCH
     if (int rc = check_launch("encode_reduce_kernel")) return rc;
     const size_t esm = K * (sizeof(EncCentre) + sizeof(int));
-    encode_emit_kernel<true, 4><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, sigma, gauss, out);
+    encode_emit_kernel<true, 4><<<grid, E_THREADS, esm, st>>>(sums, lastk, K, H, W, valid_w > 0 ? valid_w : W, sigma, gauss, out);
     return check_launch("encode_emit_kernel");
 }
 
-extern "C" int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int sigma, const float *gauss,
+extern "C" int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int valid_w, int sigma, const float *gauss,
                                           float *out, void *workspace, size_t workspace_bytes, void *stream) {
-    return encode_launch(masks, false, 0, nullptr, B, K, H, W, sigma, gauss, out, workspace, workspace_bytes, stream);
+    return encode_launch(masks, false, 0, nullptr, B, K, H, W, valid_w, sigma, gauss, out, workspace, workspace_bytes, stream);
 }
 
 extern "C" int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t *masks_out, int B, int K, int H, int W,
-                                                 int sigma, const float *gauss, float *out, void *workspace,
+                                                 int valid_w, int sigma, const float *gauss, float *out, void *workspace,
                                                  size_t workspace_bytes, void *stream) {
-    return encode_launch(reinterpret_cast<const uint8_t *>(packed), true, value, masks_out, B, K, H, W, sigma, gauss, out,
+    return encode_launch(reinterpret_cast<const uint8_t *>(packed), true, value, masks_out, B, K, H, W, valid_w, sigma, gauss, out,
                          workspace, workspace_bytes, stream);
 }

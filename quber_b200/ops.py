@@ -51,8 +51,9 @@ def boundary_dilation(H, W, ratio):
     return int(_lib.lib().quber_boundary_dilation(int(H), int(W), float(ratio)))
 
 
-def encode_initial_masks(masks, sigma=10):
-    """maskrefiner/predictor.py:304-357 for a batch: masks [B,K,H,W] uint8 -> [B,3,H,W] float32."""
+def encode_initial_masks(masks, sigma=10, valid_w=0):
+    """maskrefiner/predictor.py:304-357 for a batch: masks [B,K,H,W] uint8 -> [B,3,H,W] float32.
+    valid_w (0 = W): the frames' own width when W is a zero-padded row pitch (see encode_initial_masks_any_width)."""
     _need_cuda(masks, "masks", torch.uint8)
     B, K, H, W = masks.shape
     L = _lib.lib()
@@ -61,12 +62,12 @@ def encode_initial_masks(masks, sigma=10):
     ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=masks.device)
     g = gaussian_table(sigma, masks.device)
     with torch.cuda.device(masks.device):
-        _lib.check(L.quber_encode_initial_masks(_ptr(masks), B, K, H, W, sigma, _ptr(g), _ptr(out), _ptr(ws), nbytes,
+        _lib.check(L.quber_encode_initial_masks(_ptr(masks), B, K, H, W, int(valid_w), sigma, _ptr(g), _ptr(out), _ptr(ws), nbytes,
                                                 _stream()), "quber_encode_initial_masks")
     return out
 
 
-def encode_initial_masks_packed(packed, value, masks_out, sigma=10):
+def encode_initial_masks_packed(packed, value, masks_out, sigma=10, valid_w=0):
     """encode_initial_masks from bit-packed masks (host_pack_masks): packed int32 CUDA [B*K*H*W / 32], set pixels carry
     `value`; masks_out uint8 CUDA [B,K,H,W] receives the byte planes (0 / value) on the way -> [B,3,H,W] float32."""
     _need_cuda(packed, "packed", torch.int32)
@@ -80,22 +81,20 @@ def encode_initial_masks_packed(packed, value, masks_out, sigma=10):
     ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=packed.device)
     g = gaussian_table(sigma, packed.device)
     with torch.cuda.device(packed.device):
-        _lib.check(L.quber_encode_initial_masks_packed(_ptr(packed), int(value), _ptr(masks_out), B, K, H, W, sigma, _ptr(g), _ptr(out),
+        _lib.check(L.quber_encode_initial_masks_packed(_ptr(packed), int(value), _ptr(masks_out), B, K, H, W, int(valid_w), sigma, _ptr(g), _ptr(out),
                                                        _ptr(ws), nbytes, _stream()), "quber_encode_initial_masks_packed")
     return out
 
 
 def encode_initial_masks_any_width(masks, sigma=10):
     """encode_initial_masks for frames whose width is not a multiple of 16 (armbench 750x1333): zero columns are
-    appended, which changes neither a centroid nor a paste inside the frame; only the x-offset plane is normalised by
-    the padded width and is rescaled here (float64, then one float32 rounding: <= 1 ulp from the reference value)."""
+    appended, which changes neither a centroid nor a paste inside the frame, and the kernel normalises the x-offset
+    plane by the frame's own width (valid_w) — bit-exact with the reference on the unpadded frame."""
     B, K, H, W = masks.shape
     pad = (-W) % 16
     if not pad:
         return encode_initial_masks(masks, sigma)
-    enc = encode_initial_masks(torch.nn.functional.pad(masks, (0, pad)).contiguous(), sigma)[..., :W].contiguous()
-    enc[:, 2] = (enc[:, 2].double() * ((W + pad) / W)).float()
-    return enc
+    return encode_initial_masks(torch.nn.functional.pad(masks, (0, pad)).contiguous(), sigma, valid_w=W)[..., :W].contiguous()
 
 
 _BOUNDARY_STATUS = {}
@@ -152,7 +151,7 @@ def quadruple_maps(gt, pred):
 def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=None, threshold=0.3, nms_kernel=7,
                  top_k=200, min_area=512, stuff_area=2048, label_divisor=1000, void_label=-1.0, max_instances=None,
                  want=("sem_seg", "eee_full", "eee_onehot", "panoptic", "label_map", "masks"), centers=None,
-                 n_centers=None, no_topk=False, label_dtype=torch.int32, crop=None):
+                 n_centers=None, no_topk=False, label_dtype=torch.int32, crop=None, label_map_out=None):
     """One fused call for model.py:689-708 + :260-356 + post_processing.py:9-221 + eval_utils.py:308-328.
 
     foreground [B,1,h,w], center [B,1,h,w], offset [B,2,h,w], eee [B,C,h,w] float32 CUDA tensors at
@@ -204,7 +203,14 @@ def post_process(foreground, center, offset, eee=None, *, scale=4, offset_mul=No
     eee_full = mk("eee_full", (B, C, H, W), f32) if C else None
     onehot = mk("eee_onehot", (B, C, H, W), u8) if C else None
     pan = mk("panoptic", (B, H, W), f32)
-    lmap = mk("label_map", (B, H, W), label_dtype)
+    if label_map_out is not None and "label_map" in want:
+        # caller-owned payload buffer (the all-gather's send buffer): the map is written straight into it
+        _need_cuda(label_map_out, "label_map_out", label_dtype)
+        if label_map_out.numel() != B * H * W:
+            raise ValueError("label_map_out must hold B*H*W elements")
+        lmap = out["label_map"] = label_map_out.view(B, H, W)
+    else:
+        lmap = mk("label_map", (B, H, W), label_dtype)
     if lmap is not None and label_dtype == u8:
         flags |= _lib.POST_LABEL_U8
     iseg = mk("ins_seg", (B, H, W), i32)

@@ -22,7 +22,7 @@ from . import ops
 # Host-buffer path: pack the masks to one bit per pixel before the host->device copy?  None = time both routes on the
 # first call (HotPath._calibrate_pack).  On the 16-core B200 boxes of this pool 12 threads pack 8 cold frames in 0.63 ms
 # against 1.34 ms for their byte copy (scripts/bench_hostpack.py, profiles/r01_hostpack_v12.txt).
-PACK_MASKS_DEFAULT = None
+PACK_MIN_THREADS = 4
 
 
 @dataclass
@@ -40,7 +40,12 @@ class RefinerConfig:
     max_instances_per_image: int = 0   # rows of the output pool per frame; 0 = top_k, the worst case (instances <= centres
                                        # <= top_k), so the pool can not overflow; a smaller value sets status bit 0 on overflow
     compact_label_map: bool = False    # label maps as uint8 (QUBER_POST_LABEL_U8; needs top_k <= 255): 1/4 of the bytes
-    want: tuple = ("label_map", "masks", "eee_onehot")
+    # what quber_post_process writes: everything MaskRefiner.forward returns ("sem_seg", "eee_boundary" = eee_full,
+    # "panoptic_seg", "instances".pred_masks, model.py:303-356), the caller-side error decode (eval_utils.py:310-313) and the
+    # label map (the collective / host payload)
+    want: tuple = ("sem_seg", "eee_full", "panoptic", "masks", "eee_onehot", "label_map")
+    crop: tuple = None                 # (H, W) of the frames when they are a crop of the up-sampled maps (armbench 750 x 1333)
+    valid_w: int = 0                   # the frames' own width when the mask planes carry a zero-padded row pitch
 
 
 class HotPath:
@@ -50,19 +55,24 @@ class HotPath:
         self.launches_per_step = 0
         # host-buffer path: send the 0/1 masks as one bit per pixel (csrc/hostpack.cpp).  QUBER_PACK_MASKS=0|1 overrides.
         # None = decide on the first call by timing both routes on this host (_calibrate_pack).
-        env = os.environ.get("QUBER_PACK_MASKS")
-        self.pack_masks = PACK_MASKS_DEFAULT if env is None else (None if env == "auto" else env == "1")
         self.use_graphs = os.environ.get("QUBER_E2E_GRAPHS", "1") == "1"   # host-buffer path: one CUDA graph per chunk
         # this rank's share of the box's cores (torchrun exports LOCAL_WORLD_SIZE), two left for the launching threads
         cores = len(os.sched_getaffinity(0)) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
         self.pack_threads = max(1, min(cores - 2, 16))      # the caller packs too while it waits
+        # Deterministic route (no timing race inside the call): packing 8 frames takes 12 threads 0.63 ms against 1.34 ms
+        # for their DMA, 2 threads 5.0 ms against 3.7 ms (profiles/r01_hostpack_v12.txt, r01_bench_n8_v14.json) — the
+        # break-even is at about 4 threads, so that is the rule.  QUBER_PACK_MASKS=0|1 overrides; "auto" times both routes
+        # on the first call (_calibrate_pack, kept as a tool).
+        env = os.environ.get("QUBER_PACK_MASKS")
+        self.pack_rule = f"pack iff >= {PACK_MIN_THREADS} host threads per rank ({self.pack_threads} here)"
+        self.pack_masks = (self.pack_threads >= PACK_MIN_THREADS) if env is None else (None if env == "auto" else env == "1")
 
     # --- resident: every input already on the device -------------------------------------------
     def encode_and_boundary(self, masks, status=None):
         c = self.cfg
         B, K, H, W = masks.shape
-        enc = ops.encode_initial_masks(masks, c.sigma)
-        d = ops.boundary_dilation(H, W, c.boundary_ratio)
+        enc = ops.encode_initial_masks(masks, c.sigma, c.valid_w)
+        d = ops.boundary_dilation(H, c.valid_w or W, c.boundary_ratio)
         per, uni, fg = ops.mask_boundary(masks, d, status=status)
         return enc, per, uni, fg
 
@@ -74,18 +84,19 @@ class HotPath:
         if W % 16:                                # the packed encode shares the byte kernel's width rule
             ops.unpack_masks(st["packed_dev"][w0:w1], masks.shape, value=value, out=masks)
             return self.encode_and_boundary(masks, status)
-        enc = ops.encode_initial_masks_packed(st["packed_dev"][w0:w1], value, masks, c.sigma)
-        per, uni, fg = ops.mask_boundary(masks, ops.boundary_dilation(H, W, c.boundary_ratio), status=status)
+        enc = ops.encode_initial_masks_packed(st["packed_dev"][w0:w1], value, masks, c.sigma, c.valid_w)
+        per, uni, fg = ops.mask_boundary(masks, ops.boundary_dilation(H, c.valid_w or W, c.boundary_ratio), status=status)
         return enc, per, uni, fg
 
-    def post(self, head):
+    def post(self, head, label_map_out=None):
         c = self.cfg
         B = head["foreground"].shape[0]
         return ops.post_process(head["foreground"], head["center"], head["offset"], head.get("eee_boundary"),
                                 scale=c.common_stride, threshold=c.center_threshold, nms_kernel=c.nms_kernel,
                                 top_k=c.top_k, min_area=c.min_area, stuff_area=c.stuff_area,
                                 label_divisor=c.label_divisor, max_instances=B * self.slab, want=c.want,
-                                label_dtype=torch.uint8 if c.compact_label_map and c.top_k <= 255 else torch.int32)
+                                label_dtype=torch.uint8 if c.compact_label_map and c.top_k <= 255 else torch.int32,
+                                crop=c.crop, label_map_out=label_map_out)
 
     @property
     def slab(self):
@@ -93,9 +104,16 @@ class HotPath:
         return self.cfg.max_instances_per_image or max(self.cfg.top_k, 1)
 
     def msda_layers(self, msda, n_layers=6):
+        """The sampling of `n_layers` encoder layers.  With the module's operands (`oa` = the sampling_offsets |
+        attention_weights projection rows, `ref` = reference points) the fused kernel does ms_deform_attn.py:102-117 and
+        the sampling in one launch; with precomputed loc / attn the op alone (ms_deform_attn_forward)."""
         out = None
         for _ in range(n_layers):
-            out = ops.msda_forward(msda["value"], msda["shapes"], msda["starts"], msda["loc"], msda["attn"])
+            if "oa" in msda:
+                L = msda["ref"].shape[2]
+                out = ops.msda_forward_fused(msda["value"], msda["shapes"], msda["starts"], msda["oa"], msda["ref"], L, 4)
+            else:
+                out = ops.msda_forward(msda["value"], msda["shapes"], msda["starts"], msda["loc"], msda["attn"])
         return out
 
     # kernels launched per call (for bench.py's gpu_launches; memsets are not kernels)
@@ -115,6 +133,7 @@ class HotPath:
             B, K, H, W = shape
             numel = B * K * H * W
             slab = self.slab
+            Ho, Wo = (self.cfg.crop[0], (self.cfg.crop[1] + 7) // 8 * 8) if self.cfg.crop else (H, W)   # post outputs' rows / pitch
             pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
             st = dict(key=key, masks=torch.empty(shape, dtype=torch.uint8, device=dev),
                       head={k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in head_host.items()},
@@ -122,7 +141,7 @@ class HotPath:
                       packed_host=pin((numel + 31) // 32, torch.int32),
                       packed_dev=torch.empty((numel + 31) // 32, dtype=torch.int32, device=dev), copied={},
                       graphs={}, bstatus=torch.zeros(B + 1, dtype=torch.int32, device=dev),
-                      out=dict(label_map=pin((B, H, W), ldt), boundary=pin((B, H, W), torch.uint8),
+                      out=dict(label_map=pin((B, Ho, Wo), ldt), boundary=pin((B, H, W), torch.uint8),
                                inst_start=pin((B,), torch.int32), inst_counts=pin((B,), torch.int32),
                                status=pin((1,), torch.int32), rle_status=pin((1,), torch.int32),
                                boundary_status=pin((B + 1,), torch.int32), labels=pin((B * slab,), torch.int32), scores=pin((B * slab,), torch.float32),

@@ -46,6 +46,37 @@ def gather_label_maps(label_map, counts, group=None, out=None, compact=False):
     return maps, cnts
 
 
+class Payload:
+    """The ONE buffer a rank contributes to the step's collective: the uint8 label maps [B,H,W] followed (16-byte
+    aligned) by the int32 instance counts [B].  quber_post_process writes the maps straight into `maps`
+    (ops.post_process(label_map_out=...)), the counts are a B-element copy; `gather()` is then a single
+    all_gather_into_tensor — north_star: "results are collected with a single NCCL all-gather"."""
+
+    def __init__(self, B, H, W, device, world=1):
+        self.B, self.H, self.W, self.world = B, H, W, world
+        self.map_bytes = (B * H * W + 15) // 16 * 16
+        self.nbytes = self.map_bytes + 4 * B
+        self.buf = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
+        self.maps = self.buf[: B * H * W].view(B, H, W)
+        self.counts = self.buf[self.map_bytes:].view(torch.int32)
+        self.all = torch.empty((world, self.nbytes), dtype=torch.uint8, device=device) if world > 1 else self.buf[None]
+
+    def gather(self, group=None):
+        """-> (maps [G,B,H,W] uint8, counts [G,B] int32) on every rank; one collective."""
+        if self.world > 1:
+            if dist.get_backend(group) == "nccl":
+                dist.all_gather_into_tensor(self.all.view(-1), self.buf, group=group)
+            else:
+                dist.all_gather(list(self.all.unbind(0)), self.buf, group=group)
+        return self.unpack(self.all)
+
+    def unpack(self, gathered):
+        G = gathered.shape[0]
+        maps = gathered[:, : self.B * self.H * self.W].view(G, self.B, self.H, self.W)
+        counts = gathered[:, self.map_bytes:].contiguous().view(torch.int32).view(G, self.B)
+        return maps, counts
+
+
 def masks_from_label_map(label_map, n_instances):
     """[H,W] int32 label map -> bool [n,H,W], the reference's `pred_masks` (model.py:331-336)."""
     ids = torch.arange(1, int(n_instances) + 1, device=label_map.device, dtype=torch.int32).to(label_map.dtype)

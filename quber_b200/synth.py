@@ -86,11 +86,14 @@ def head_outputs(masks, stride=4, seed=0, eee_channels=4, sigma=10):
 
 
 def msda_inputs(B=1, shapes=((60, 80), (30, 40), (15, 20)), M=8, D=32, P=4, Q=None, seed=0,
-                mode="rand", dtype=np.float32):
+                mode="rand", dtype=np.float32, operands=False):
     """MSDeformAttn inputs.  mode "rand": OPS/test.py:36-39 (value=rand*0.01, loc=rand, attn=rand+1e-5
     normalised over L*P); "border": locs in [-0.1, 1.1]; "module": reference points + the module's
     initial sampling-offset grid (OPS/modules/ms_deform_attn.py:66-74), i.e. what a random-init
-    encoder layer actually feeds the op (Q = S)."""
+    encoder layer actually feeds the op (Q = S).  operands=True (mode "module" only) also returns what the MODULE
+    computes them from: `oa` [B,Q,M*L*P*3] = the sampling_offsets | attention_weights projection rows (offsets in
+    pixels, logits = log(attn) so that their softmax is attn) and `ref` [B,Q,L,2] reference points — the inputs of
+    quber_msda_forward_fused; loc / attn are then what ms_deform_attn.py:104-109 makes of them (up to rounding)."""
     rng = np.random.default_rng(seed)
     shapes = np.asarray(shapes, np.int64)
     L = len(shapes)
@@ -120,6 +123,12 @@ def msda_inputs(B=1, shapes=((60, 80), (30, 40), (15, 20)), M=8, D=32, P=4, Q=No
         offs = np.broadcast_to(offs, (M, L, P, 2)) + rng.normal(0, 0.25, (B, Q, M, L, P, 2))
         norm = np.stack([shapes[:, 1], shapes[:, 0]], -1).astype(np.float32)   # (W_l, H_l)
         loc = (ref[None, :, None, None, None, :] + offs / norm[None, None, None, :, None, :]).astype(dtype)
+        if operands:
+            oa = np.concatenate([offs.astype(np.float32).reshape(B, Q, M * L * P * 2),
+                                 np.log(attn.astype(np.float64)).astype(np.float32).reshape(B, Q, M * L * P)], -1)
+            refp = np.ascontiguousarray(np.broadcast_to(ref[None, :, None, :], (B, Q, L, 2)).astype(np.float32))
+            return dict(value=value, shapes=shapes, starts=starts, loc=np.ascontiguousarray(loc), attn=attn,
+                        oa=np.ascontiguousarray(oa), ref=refp)
     else:
         raise ValueError(mode)
     return dict(value=value, shapes=shapes, starts=starts, loc=np.ascontiguousarray(loc), attn=attn)

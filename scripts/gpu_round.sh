@@ -1,6 +1,6 @@
 #!/bin/bash
 # One GPU-box pass, parameterised:  scripts/gpu_round.sh TAG [steps...]
-#   steps (default "test smoke bench"): test | testk:<pytest -k expr> | smoke | bench | ref | launches | full[:regex] | extra
+#   steps (default "test smoke bench"): test | testk:<one-word pytest -k expr> | smoke | bench | bench:<c2|c3|c4|c5> | ref | launches | full[:regex] | extra
 # Everything lands in gpurun_out/ with the TAG in the name; copy what should be judged into profiles/.
 # ncu steps run only after the same bench command has exited 0 without ncu in this call (the `bench` step).
 TAG=${1:-r02}; shift
@@ -13,6 +13,7 @@ for s in $STEPS; do
     testk:*) timeout 1200 python -m pytest tests -m gpu -x -q -s -k "${s#testk:}" > gpurun_out/pytest_k_$TAG.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_k_$TAG.log; tail -30 gpurun_out/pytest_k_$TAG.log ;;
     smoke)  timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke_$TAG.log 2>&1; tail -2 gpurun_out/smoke_$TAG.log ;;
     bench)  timeout 900 python bench.py --steps 20 --warmup 3 > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err && BENCH_OK=1; echo "bench ok=$BENCH_OK"; cat gpurun_out/bench_$TAG.json; tail -3 gpurun_out/bench_$TAG.err ;;
+    bench:*) CFG=${s#bench:}; timeout 900 python bench.py --config $CFG --steps 20 --warmup 3 --no-network > gpurun_out/bench_${CFG}_$TAG.json 2> gpurun_out/bench_${CFG}_$TAG.err; echo "bench $CFG rc=$?"; cat gpurun_out/bench_${CFG}_$TAG.json; tail -3 gpurun_out/bench_${CFG}_$TAG.err ;;
     ref)    timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_$TAG.json 2> gpurun_out/bench_ref_$TAG.err; cat gpurun_out/bench_ref_$TAG.json ;;
     launches) timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-network > gpurun_out/plain_l_$TAG.log 2>&1 &&
             timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_$TAG.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-network > gpurun_out/ncu_l_$TAG.log 2>&1; tail -2 gpurun_out/ncu_l_$TAG.log ;;

@@ -64,7 +64,7 @@ def test_error_strings_and_exception_mapping():
 def test_argument_validation_without_gpu():
     """Argument checks run before any CUDA call, so they are testable on a CPU-only host."""
     L = _lib.lib()
-    assert L.quber_encode_initial_masks(None, 1, 1, 16, 16, 10, None, None, None, 0, None) == _lib.E_INVALID
+    assert L.quber_encode_initial_masks(None, 1, 1, 16, 16, 0, 10, None, None, None, 0, None) == _lib.E_INVALID
     assert L.quber_mask_boundary(None, 1, 1, 16, 16, 8, None, None, None, None, None) == _lib.E_INVALID
     assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 24, 8, ctypes.c_void_p(16), None, None, None, None) == _lib.E_ALIGN
     assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 16, 0, ctypes.c_void_p(16), None, None, None, None) == _lib.E_INVALID

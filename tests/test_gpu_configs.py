@@ -78,10 +78,8 @@ def test_c4_armbench_boundary_and_encode_750x1333():
     ref = oracle.encode_initial_masks(masks)
     np.testing.assert_array_equal(enc[0], ref[0])                                       # centre heat-map
     np.testing.assert_array_equal(enc[1], ref[1])                                       # (c_y - y) / H
-    # (c_x - x) / W: W % 16 != 0 -> computed on the padded width and rescaled, <= 1 ulp (ops.encode_initial_masks_any_width)
-    ulp = np.spacing(np.abs(ref[2]).astype(np.float32))
-    assert (np.abs(enc[2] - ref[2]) <= ulp).all()
-    assert np.array_equal(enc[2] != 0, ref[2] != 0)
+    # (c_x - x) / W with W % 16 != 0: zero-padded row pitch, normalised by the frame's own width inside the kernel (valid_w)
+    np.testing.assert_array_equal(enc[2], ref[2])
 
 
 def test_c4_armbench_post_752x1336():

@@ -49,6 +49,12 @@ def _worker(rank, world, port, q):
         ok = ok and cm.dtype == torch.uint8 and torch.equal(cm.to(torch.int32), allm) and torch.equal(cc, allc)
         m8 = sharding.masks_from_label_map(cm[other, 0], cc[other, 0])
         ok = ok and torch.equal(m8, m)
+        # the single-collective payload (maps + counts in ONE buffer, one all-gather per step)
+        pl = sharding.Payload(3, 12, 16, "cpu", world)
+        pl.maps.copy_(maps.to(torch.uint8))
+        pl.counts.copy_(counts)
+        pm, pc = pl.gather()
+        ok = ok and pm.shape == (world, 3, 12, 16) and torch.equal(pm.to(torch.int32), allm) and torch.equal(pc, allc)
         # whole-job instance count = sum over ranks, as bench.py aggregates it
         tot = allc.sum().clone()
         mine = counts.sum().clone()
@@ -70,6 +76,14 @@ def test_world_size_2_gloo_gather():
     for p in procs:
         p.join(timeout=60)
     assert res == [(0, True), (1, True)]
+
+
+def test_payload_single_process_layout():
+    pl = sharding.Payload(2, 5, 7, "cpu")                  # 70 map bytes -> counts start at the next 16-byte boundary
+    assert pl.map_bytes == 80 and pl.nbytes == 88 and pl.counts.dtype == torch.int32 and pl.counts.numel() == 2
+    pl.maps.fill_(3); pl.counts.copy_(torch.tensor([4, 9], dtype=torch.int32))
+    m, c = pl.gather()
+    assert m.shape == (1, 2, 5, 7) and int(m.sum()) == 210 and c.tolist() == [[4, 9]]
 
 
 def test_single_process_passthrough():
