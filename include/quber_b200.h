@@ -394,6 +394,29 @@ int quber_upsample_crop_resize(const float *src, int B, int C, int h, int w, int
                                int out_h, int out_w, float *dst, void *stream);
 int quber_resize_nearest_u8(const uint8_t *src, int n, int h, int w, int out_h, int out_w, uint8_t *dst, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Evaluation metrics, the per-pixel part — replaces the loops of multilabel_metrics
+ *     (eval/evaluation.py:57-274) over every (gt label, predicted label) pair: np.unique, the pairwise
+ *     intersection / area counts (:180-197), seg2bmap of every mask (eval/utilities.py:672-696 = cv2.findContours
+ *     RETR_EXTERNAL + drawContours) and boundary_overlap of every pair (:22-55: cv2.dilate with skimage's disk(radius)).
+ *     The K x K' float64 ratios and the Hungarian assignment stay on the host (quber_b200/evaluation.py).
+ *   pred, gt        dev [B,H,W] int32 label maps, labels in [0, 65535], 0 = background
+ *   max_labels      ML <= 255: capacity of the per-image label lists / matrices
+ *   radius          bound_pix of evaluation.py:34-35;  boundary != 0 computes the boundary counts as well
+ *   pred_labels, gt_labels dev [B,ML] int32 ascending (np.unique minus 0);  n_pred, n_gt dev [B] int32
+ *   inter_full      dev [B,ML+1,ML+1] int32: co-occurrence counts of (gt index, pred index), index 0 = background, so
+ *                   inter_full[b][i+1][j+1] = |gt_i & pred_j| and the row / column sums are the mask areas
+ *   bcount_pred/gt  dev [B,ML] int32: boundary pixels of every mask;  btp dev [B,ML,ML,2] int32: (precision tps, recall tps)
+ *   bmaps_out       dev [2,B,H,W] uint8 or NULL: the boundary maps themselves (k+1 on the boundary of the k-th label; [0] = pred)
+ *   status          dev int32 [1]: bit 0 more than ML labels in a map, bit 1 a label outside [0, 65535], bit 2 a mask whose
+ *                   bounding box does not fit one SM's shared memory as a bit plane (> ~1.6 M pixels)
+ * ------------------------------------------------------------------------------------------- */
+size_t quber_eval_workspace_bytes(int B, int H, int W, int max_labels);
+int quber_eval_counts(const int32_t *pred, const int32_t *gt, int B, int H, int W, int max_labels, int radius, int boundary,
+                      int32_t *pred_labels, int32_t *n_pred, int32_t *gt_labels, int32_t *n_gt, int32_t *inter_full,
+                      int32_t *bcount_pred, int32_t *bcount_gt, int32_t *btp, uint8_t *bmaps_out, void *workspace,
+                      size_t workspace_bytes, int32_t *status, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -253,3 +253,29 @@ def resize_nearest(mask, out_hw):
     out = np.empty((int(out_hw[0]), int(out_hw[1])), np.uint8)
     lib().oracle_resize_nearest_u8(_p(mask), mask.shape[0], mask.shape[1], out.shape[0], out.shape[1], _p(out))
     return out
+
+
+# ---- (f)3 evaluation metrics (eval/evaluation.py, eval/utilities.py:672) --------------------------------------------
+def seg2bmap(mask):
+    """eval/utilities.py:672-696 for one [H,W] mask -> uint8 0/1 boundary map."""
+    mask = _c(np.asarray(mask) != 0, np.uint8)
+    out = np.empty_like(mask)
+    lib().oracle_seg2bmap(_p(mask), mask.shape[0], mask.shape[1], _p(out))
+    return out
+
+
+def eval_counts(prediction, gt, radius, cap=256):
+    """The integer counts multilabel_metrics (eval/evaluation.py:57-274) is made of, for one pair of label maps."""
+    prediction, gt = _c(prediction, np.int32), _c(gt, np.int32)
+    H, W = gt.shape
+    pl, gl = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+    n_p, n_g = ctypes.c_int32(), ctypes.c_int32()
+    inter, btp = np.zeros((cap, cap), np.int64), np.zeros((cap, cap, 2), np.int64)
+    ap, ag, bp, bg = (np.zeros(cap, np.int64) for _ in range(4))
+    rc = lib().oracle_eval_counts(_p(prediction), _p(gt), H, W, cap, int(radius), _p(pl), ctypes.byref(n_p), _p(gl), ctypes.byref(n_g),
+                                  _p(inter), _p(ap), _p(ag), _p(bp), _p(bg), _p(btp))
+    if rc != 0:
+        raise ValueError("more labels than cap")
+    np_, ng = n_p.value, n_g.value
+    return dict(pred_labels=pl[:np_].copy(), gt_labels=gl[:ng].copy(), inter=inter[:ng, :np_].copy(), area_pred=ap[:np_].copy(),
+                area_gt=ag[:ng].copy(), bcount_pred=bp[:np_].copy(), bcount_gt=bg[:ng].copy(), btp=btp[:ng, :np_].copy())

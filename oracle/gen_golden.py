@@ -577,8 +577,135 @@ def gen_resize():
     print("resize.npz ok")
 
 
+EVAL_KEYS = ["Objects F-measure", "Objects Precision", "Objects Recall", "Boundary F-measure", "Boundary Precision",
+             "Boundary Recall", "Objects OSN F-measure", "Objects OSN Precision", "Objects OSN Recall", "Boundary OSN F-measure",
+             "Boundary OSN Precision", "Boundary OSN Recall", "obj_detected", "obj_detected_075", "obj_gt",
+             "obj_detected_075_percentage", "obj_detected_075_percentage_normalized", "obj_mIOU_osn", "obj_mIOU"]
+
+
+def ref_evaluation():
+    """eval/evaluation.py imported where it lies (with eval/utilities.py and eval/munkres.py).  Absent third-party
+    modules it only touches for plotting / notebooks are stubbed (matplotlib, IPython); `skimage.morphology.disk` — the one
+    skimage function boundary_overlap calls (evaluation.py:41-44), scikit-image is not installed here — is restated as
+    published: the (2r+1)^2 grid of points with x^2 + y^2 <= r^2."""
+    for name in ("matplotlib", "matplotlib.pyplot", "IPython", "IPython.display"):
+        try:
+            __import__(name)
+        except Exception:
+            m = types.ModuleType(name)
+            sys.modules[name] = m
+            if name == "IPython.display":
+                m.HTML = m.Image = m.display = None
+    try:
+        import skimage.morphology  # noqa: F401
+    except Exception:
+        sk, mo = types.ModuleType("skimage"), types.ModuleType("skimage.morphology")
+
+        def disk(radius, dtype=np.uint8):
+            L = np.arange(-radius, radius + 1)
+            X, Y = np.meshgrid(L, L)
+            return np.array((X ** 2 + Y ** 2) <= radius ** 2, dtype=dtype)
+        mo.disk = disk
+        sk.morphology = mo
+        sys.modules["skimage"], sys.modules["skimage.morphology"] = sk, mo
+    if f"{REF}/eval" not in sys.path:
+        sys.path.insert(0, f"{REF}/eval")
+    import evaluation as ev
+    import utilities as ut
+    return ev, ut
+
+
+def eval_case_maps(name):
+    """Seeded (prediction, gt) label maps of an evaluation case."""
+    rng = np.random.default_rng(abs(hash(name)) % 1000 + 7) if False else np.random.default_rng(sum(map(ord, name)))
+    def label_map(masks, labels):
+        out = np.zeros(masks.shape[1:], np.int32)
+        for m, l in zip(masks, labels):
+            out[m > 0] = l
+        return out
+    if name in ("pred_empty", "gt_empty", "both_empty"):
+        m = synth.ellipse_masks(3, 96, 128, seed=5, axes=(8, 25), margin=10)
+        full = label_map(m, [1, 2, 3])
+        z = np.zeros_like(full)
+        return {"pred_empty": (z, full), "gt_empty": (full, z), "both_empty": (z, z)}[name]
+    if name == "c1":
+        m = synth.ellipse_masks(20, 480, 640, seed=0)
+        p = synth.perturb_masks(m, seed=1, max_shift=6)
+        return label_map(p[:18], list(range(2, 20))), label_map(m, list(range(1, 21)))
+    if name == "holes":
+        H, W = 120, 160
+        yy, xx = np.mgrid[0:H, 0:W]
+        gt = np.zeros((H, W), np.int32)
+        d = (yy - 60) ** 2 + (xx - 60) ** 2
+        gt[(d <= 40 ** 2) & (d >= 28 ** 2)] = 3                  # a ring: its hole border is NOT an external contour
+        gt[d <= 12 ** 2] = 7                                     # an object nested inside the hole
+        gt[(abs(yy - 30) < 12) & (abs(xx - 130) < 20)] = 4
+        gt[20:25, 125:130] = 0                                   # a pinhole
+        gt[100:103, 100:160] = 9                                 # a thin bar touching the image edge
+        pr = np.roll(np.roll(gt, 2, 0), -3, 1).copy()
+        pr[pr == 9] = 11
+        pr[0:8, 0:8] = 5                                         # a false positive in the corner
+        return pr, gt
+    K = {"normal": (5, 4), "more_pred": (4, 7)}[name]
+    m = synth.ellipse_masks(max(K), 120, 160, seed=3 if name == "normal" else 9, axes=(8, 30), margin=10)
+    p = synth.perturb_masks(m, seed=4)
+    return label_map(p[:K[1]], [k + 2 for k in range(K[1])]), label_map(m[:K[0]], [k + 1 for k in range(K[0])])
+
+
+def gen_eval():
+    """(f)3: eval/evaluation.py::multilabel_metrics, boundary_overlap and eval/utilities.py::seg2bmap EXECUTED on seeded
+    label maps / masks (normal, unequal counts, rings + nested objects + pinholes + frame-touching bars, the three empty
+    edge cases, a C1-sized frame)."""
+    ev, ut = ref_evaluation()
+    out = {"keys": np.array(EVAL_KEYS)}
+    for name in ("normal", "more_pred", "holes", "pred_empty", "gt_empty", "both_empty", "c1"):
+        pr, gt = eval_case_maps(name)
+        with np.errstate(all="ignore"):
+            r = ev.multilabel_metrics(pr.astype(np.int64), gt.astype(np.int64), 0, 1)
+        out[f"{name}_pred"], out[f"{name}_gt"] = pr.astype(np.int16), gt.astype(np.int16)
+        out[f"{name}_metrics"] = np.array([np.nan if k not in r or r[k] is None else float(r[k]) for k in EVAL_KEYS], np.float64)
+        out[f"{name}_has"] = np.array([k in r for k in EVAL_KEYS])
+        print("eval", name, {k: round(float(v), 4) for k, v in list(r.items())[:3]})
+    # seg2bmap on masks that separate "boundary against the outer background" from "any mask pixel next to a zero"
+    rng = np.random.default_rng(23)
+    masks = []
+    for t in range(24):
+        H, W = 40, 56
+        yy, xx = np.mgrid[0:H, 0:W]
+        if t % 3 == 0:
+            m = rng.random((H, W)) < rng.uniform(0.3, 0.7)
+        elif t % 3 == 1:
+            m = np.zeros((H, W), bool)
+            for _ in range(3):
+                y, x, r = rng.integers(0, H), rng.integers(0, W), rng.integers(3, 14)
+                d = (yy - y) ** 2 + (xx - x) ** 2
+                m |= (d <= r * r) & (d >= (r - rng.integers(1, 4)) ** 2)
+        else:
+            m = np.zeros((H, W), bool)
+            m[1:-1, 1:-1] = True; m[4:-4, 4:-4] = False; m[8:-8, 8:-8] = True; m[12:-12, 12:-12] = False
+        masks.append(m)
+    masks = np.stack(masks)
+    bm = np.stack([ut.seg2bmap(m) for m in masks])
+    out["bmap_masks"], out["bmap_out"], out["bmap_shape"] = np.packbits(masks), np.packbits(bm != 0), np.array(masks.shape)
+    pr, gt = eval_case_maps("holes")
+    out["overlap_holes_3"] = np.array(ev.boundary_overlap(pr == 3, gt == 3))
+    out["overlap_holes_4_vs_3"] = np.array(ev.boundary_overlap(pr == 4, gt == 3))
+    # eval/munkres.py executed on cost matrices full of ties (what obj_F.max() - obj_F looks like: most pairs do not overlap)
+    import munkres as ref_munkres
+    rng = np.random.default_rng(29)
+    for t, (n, m) in enumerate([(3, 3), (4, 6), (6, 4), (5, 5), (1, 4), (7, 7), (8, 5), (2, 9), (10, 10), (6, 6)]):
+        c = rng.integers(0, 3, (n, m)).astype(np.float64) * rng.choice([1.0, 0.37])
+        if t >= 6:
+            c[rng.random((n, m)) < 0.6] = c.max()               # sparse overlaps
+        out[f"munkres{t}_cost"] = c
+        out[f"munkres{t}_assign"] = np.array(ref_munkres.Munkres().compute(c.copy()), np.int32).reshape(-1, 2)
+    out["munkres_n"] = np.array(10)
+    np.savez_compressed(os.path.join(OUT, "eval.npz"), **out)
+    print("eval.npz ok")
+
+
 SECTIONS = {"encode": gen_encode, "boundary": gen_boundary, "post": gen_post, "msda": gen_msda,
-            "post_ii": gen_post_ii, "decode_types": gen_decode_types, "quadruple": gen_quadruple, "rle": gen_rle, "resize": gen_resize}
+            "post_ii": gen_post_ii, "decode_types": gen_decode_types, "quadruple": gen_quadruple, "rle": gen_rle, "resize": gen_resize, "eval": gen_eval}
 
 
 def main():

@@ -636,3 +636,117 @@ ORACLE_API size_t oracle_rle_from_string(const char *s, uint32_t *cnts) {
     }
     return m;
 }
+
+/* ------------------------------------------------------------------------- */
+/* (f)3: evaluation metrics — eval/evaluation.py:22-274, eval/utilities.py:672 */
+/* ------------------------------------------------------------------------- */
+
+/* seg2bmap (eval/utilities.py:672-696): cv2.findContours(seg, RETR_EXTERNAL, CHAIN_APPROX_NONE) + drawContours(thickness 1).
+ * With 8-connected foreground, Suzuki-Abe border following visits exactly the 1-pixels that have a 0-pixel of the
+ * SURROUNDING background in their 4-neighbourhood, RETR_EXTERNAL keeps only borders against the background component that
+ * contains the image frame (hole borders and components nested inside holes are dropped), and consecutive contour
+ * points are 8-adjacent, so drawing them with thickness 1 adds nothing:
+ *     bmap = mask AND (has a 4-neighbour in F or outside the image),  F = 0-pixels 4-connected to the frame.
+ * Checked against cv2 on random / ring / nested / diagonal masks by oracle/gen_golden.py::gen_eval (tests/golden/eval.npz). */
+ORACLE_API void oracle_seg2bmap(const uint8_t *mask, int H, int W, uint8_t *bmap) {
+    const int PW = W + 2, PH = H + 2;
+    uint8_t *outer = (uint8_t *)calloc((size_t)PH * PW, 1);     /* padded grid: the pad ring is the frame */
+    int *stack = (int *)malloc(sizeof(int) * (size_t)PH * PW);
+    int sp = 0;
+    outer[0] = 1; stack[sp++] = 0;
+    while (sp) {
+        const int p = stack[--sp], y = p / PW, x = p % PW;
+        const int ny[4] = {y - 1, y + 1, y, y}, nx[4] = {x, x, x - 1, x + 1};
+        for (int k = 0; k < 4; ++k) {
+            if (ny[k] < 0 || ny[k] >= PH || nx[k] < 0 || nx[k] >= PW) continue;
+            const int q = ny[k] * PW + nx[k];
+            if (outer[q]) continue;
+            const int inside = ny[k] >= 1 && ny[k] <= H && nx[k] >= 1 && nx[k] <= W;
+            if (inside && mask[(size_t)(ny[k] - 1) * W + nx[k] - 1]) continue;
+            outer[q] = 1; stack[sp++] = q;
+        }
+    }
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            const int p = (y + 1) * PW + x + 1;
+            bmap[(size_t)y * W + x] = mask[(size_t)y * W + x] && (outer[p - PW] || outer[p + PW] || outer[p - 1] || outer[p + 1]);
+        }
+    free(outer); free(stack);
+}
+
+static int cmp_i32(const void *a, const void *b) { const int32_t x = *(const int32_t *)a, y = *(const int32_t *)b; return (x > y) - (x < y); }
+
+static int unique_labels(const int32_t *map, size_t n, int32_t *out, int cap) {
+    int32_t *tmp = (int32_t *)malloc(sizeof(int32_t) * n);
+    memcpy(tmp, map, sizeof(int32_t) * n);
+    qsort(tmp, n, sizeof(int32_t), cmp_i32);
+    int m = 0;
+    for (size_t i = 0; i < n; ++i)
+        if (tmp[i] != 0 && (i == 0 || tmp[i] != tmp[i - 1])) { if (m < cap) out[m] = tmp[i]; ++m; }   /* BACKGROUND_LABEL = 0 */
+    free(tmp);
+    return m;
+}
+
+/* The integer counts multilabel_metrics is made of (evaluation.py:83-207), for one (prediction, gt) pair of label maps:
+ *   labels (np.unique minus the background 0), intersection / area counts of every (gt i, pred j) pair (:180-197),
+ *   boundary pixel counts of every mask (seg2bmap, :163-173) and boundary_overlap's (precision tps, recall tps) of every pair
+ *   (:22-55: both boundaries dilated with skimage's disk(radius), cv2.dilate).  radius = bound_pix of :34-35.
+ * Matrices are [cap][cap] row-major (gt index first).  Returns 0, or -1 if a map has more than cap labels. */
+ORACLE_API int oracle_eval_counts(const int32_t *pred, const int32_t *gt, int H, int W, int cap, int radius,
+                                  int32_t *pred_labels, int32_t *n_pred, int32_t *gt_labels, int32_t *n_gt,
+                                  int64_t *inter, int64_t *area_pred, int64_t *area_gt,
+                                  int64_t *bcount_pred, int64_t *bcount_gt, int64_t *btp /* [cap][cap][2] */) {
+    const size_t HW = (size_t)H * W;
+    const int np_ = unique_labels(pred, HW, pred_labels, cap), ng = unique_labels(gt, HW, gt_labels, cap);
+    *n_pred = np_; *n_gt = ng;
+    if (np_ > cap || ng > cap) return -1;
+    memset(inter, 0, sizeof(int64_t) * cap * cap);
+    memset(btp, 0, sizeof(int64_t) * cap * cap * 2);
+    uint8_t *m = (uint8_t *)malloc(HW);
+    uint8_t *bp = (uint8_t *)malloc(HW * (size_t)(np_ > 0 ? np_ : 1)), *bg = (uint8_t *)malloc(HW * (size_t)(ng > 0 ? ng : 1));
+    for (int j = 0; j < np_; ++j) {
+        int64_t a = 0;
+        for (size_t i = 0; i < HW; ++i) { m[i] = pred[i] == pred_labels[j]; a += m[i]; }
+        area_pred[j] = a;
+        oracle_seg2bmap(m, H, W, bp + HW * j);
+        int64_t c = 0; for (size_t i = 0; i < HW; ++i) c += bp[HW * j + i];
+        bcount_pred[j] = c;
+    }
+    for (int i = 0; i < ng; ++i) {
+        int64_t a = 0;
+        for (size_t k = 0; k < HW; ++k) { m[k] = gt[k] == gt_labels[i]; a += m[k]; }
+        area_gt[i] = a;
+        oracle_seg2bmap(m, H, W, bg + HW * i);
+        int64_t c = 0; for (size_t k = 0; k < HW; ++k) c += bg[HW * i + k];
+        bcount_gt[i] = c;
+    }
+    for (int i = 0; i < ng; ++i)
+        for (int j = 0; j < np_; ++j) {
+            int64_t n = 0;
+            for (size_t k = 0; k < HW; ++k) n += (gt[k] == gt_labels[i]) && (pred[k] == pred_labels[j]);
+            inter[(size_t)i * cap + j] = n;
+            /* boundary_overlap(pred_j_mask, gt_i_mask): fg_match = fg_boundary & dilate(gt_boundary, disk), and vice versa */
+            int64_t tp_p = 0, tp_r = 0;
+            const uint8_t *B0 = bp + HW * j, *B1 = bg + HW * i;
+            for (int y = 0; y < H; ++y)
+                for (int x = 0; x < W; ++x) {
+                    const int f = B0[(size_t)y * W + x], g = B1[(size_t)y * W + x];
+                    if (!f && !g) continue;
+                    int near_g = 0, near_f = 0;
+                    for (int dy = -radius; dy <= radius; ++dy)
+                        for (int dx = -radius; dx <= radius; ++dx) {
+                            if (dx * dx + dy * dy > radius * radius) continue;          /* skimage.morphology.disk */
+                            const int yy = y + dy, xx = x + dx;
+                            if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+                            near_g |= B1[(size_t)yy * W + xx];
+                            near_f |= B0[(size_t)yy * W + xx];
+                        }
+                    tp_p += f && near_g;
+                    tp_r += g && near_f;
+                }
+            btp[((size_t)i * cap + j) * 2] = tp_p;
+            btp[((size_t)i * cap + j) * 2 + 1] = tp_r;
+        }
+    free(m); free(bp); free(bg);
+    return 0;
+}

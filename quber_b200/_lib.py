@@ -73,6 +73,9 @@ SYMBOLS = {
     "quber_rle_encode": (c_i, [c_vp, c_i, c_i, c_i, c_vp, c_sz, c_vp, c_vp, c_sz, c_vp, c_vp]),
     "quber_rle_from_string": (ctypes.c_longlong, [ctypes.c_char_p, c_sz, c_vp, c_sz]),
     "quber_rle_to_string": (ctypes.c_longlong, [c_vp, c_sz, c_vp, c_sz]),
+    "quber_eval_workspace_bytes": (c_sz, [c_i, c_i, c_i, c_i]),
+    "quber_eval_counts": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                c_sz, c_vp, c_vp]),
     "quber_upsample_crop_resize": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_f, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_resize_nearest_u8": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_msda_forward_fused": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),

@@ -726,6 +726,54 @@ def resize_nearest(masks, out_hw):
     return out
 
 
+def eval_counts(prediction, gt, radius, max_labels=64, boundary=True, want_bmaps=False):
+    """The integer counts of multilabel_metrics (eval/evaluation.py:57-274) for a batch of label-map pairs:
+    prediction, gt int32 CUDA [B,H,W] (labels in [0, 65535], 0 = background) -> dict of device tensors:
+    pred_labels / gt_labels [B,ML], n_pred / n_gt [B], inter [B,ML,ML] (gt index first), area_pred / area_gt [B,ML],
+    bcount_pred / bcount_gt [B,ML], btp [B,ML,ML,2], status [1] (+ bmaps [2,B,H,W] uint8 with want_bmaps)."""
+    _need_cuda(prediction, "prediction", torch.int32)
+    _need_cuda(gt, "gt", torch.int32)
+    if prediction.shape != gt.shape or prediction.dim() != 3:
+        raise ValueError("prediction and gt must both be [B,H,W]")
+    B, H, W = prediction.shape
+    ML = int(max_labels)
+    if not 0 < ML <= 255:
+        raise ValueError("max_labels must be in 1..255")
+    dev = prediction.device
+    i32 = torch.int32
+    e = lambda *shape: torch.empty(shape, dtype=i32, device=dev)
+    out = dict(pred_labels=e(B, ML), n_pred=e(B), gt_labels=e(B, ML), n_gt=e(B), bcount_pred=e(B, ML), bcount_gt=e(B, ML),
+               btp=e(B, ML, ML, 2), status=e(1))
+    full = e(B, ML + 1, ML + 1)
+    bm = torch.empty((2, B, H, W), dtype=torch.uint8, device=dev) if want_bmaps else None
+    L = _lib.lib()
+    nbytes = L.quber_eval_workspace_bytes(B, H, W, ML)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(L.quber_eval_counts(_ptr(prediction), _ptr(gt), B, H, W, ML, int(radius), int(bool(boundary)), _ptr(out["pred_labels"]),
+                                       _ptr(out["n_pred"]), _ptr(out["gt_labels"]), _ptr(out["n_gt"]), _ptr(full), _ptr(out["bcount_pred"]),
+                                       _ptr(out["bcount_gt"]), _ptr(out["btp"]), _ptr(bm), _ptr(ws), nbytes, _ptr(out["status"]), _stream()),
+                   "quber_eval_counts")
+    out["inter"] = full[:, 1:, 1:]
+    out["area_gt"] = full[:, 1:, :].sum(-1)                     # row sums incl. the background column
+    out["area_pred"] = full[:, :, 1:].sum(-2)
+    if not boundary:
+        out["bcount_pred"].zero_(); out["bcount_gt"].zero_(); out["btp"].zero_()
+    if want_bmaps:
+        out["bmaps"] = bm
+    return out
+
+
+def seg2bmap(masks):
+    """eval/utilities.py:672-696 for a batch of binary maps: masks [B,H,W] (non-zero = inside, any integer dtype) ->
+    uint8 [B,H,W] 0/1, the one-pixel outer boundary (cv2.findContours RETR_EXTERNAL + drawContours)."""
+    if not isinstance(masks, torch.Tensor) or not masks.is_cuda:
+        raise ValueError("masks must be a CUDA tensor")
+    m = (masks != 0).to(torch.int32).contiguous()
+    r = eval_counts(m, m, 0, max_labels=1, boundary=True, want_bmaps=True)
+    return r["bmaps"][0]
+
+
 def rle_decode(counts, offsets, n, H, W, value=1, packed=False, out=None, check=False):
     """pycocotools.mask.decode on the device (perturbed_panoptic_dataset_mapper.py:195-214): `counts` uint32-as-int32
     CUDA tensor holding the run lengths of `n` masks back to back (column-major runs, starting with zeros), `offsets`
