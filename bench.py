@@ -427,7 +427,7 @@ def run_ours(args):
         "encode(reduce+emit)": {"ms": per_stage["encode"], "bytes": ab["encode"], "launches": 2},
         "boundary_tma_kernel": {"ms": per_stage["boundary"], "bytes": ab["boundary"], "launches": 1},
         msda_kernel: {"ms": per_stage["msda"] / N_LAYERS, "bytes": ab["msda_layer"], "launches": 1},
-        "post(nms+select+group+relabel+offsets+emit+finalize)": {"ms": per_stage["post"], "bytes": ab["post"], "launches": 7},
+        "post(nms+select+group+eee+relabel+offsets+emit+finalize)": {"ms": per_stage["post"], "bytes": ab["post"], "launches": 8},
     }
     for v in roof_all.values():
         v["achieved_gbs"] = v["bytes"] / (v["ms"] * 1e-3) / 1e9
@@ -442,7 +442,7 @@ def run_ours(args):
     sm_mhz = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
     n_lines = B * g["S"] * M_HEADS * L * N_POINTS * 4
     l1_floor_us = n_lines / 148.0 / (sm_mhz * 1e6) * 1e6
-    launches = (2 + 1 + N_LAYERS + 7) * steps
+    launches = (2 + 1 + N_LAYERS + 8) * steps
     bound = "l1" if dominant == msda_kernel else "hbm"
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": args.warmup,

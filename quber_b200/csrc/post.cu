@@ -10,10 +10,12 @@
 //   eval/eval_utils.py:308-328                           error-map argmax -> one-hot
 //
 // Launch sequence on one stream (B images per launch, no host synchronisation):
-//   memset(zeroed workspace) -> center_nms -> center_select -> group -> relabel -> offsets -> emit -> finalize
+//   memset(zeroed workspace) -> center_nms -> center_select -> group -> eee -> relabel -> offsets -> emit -> finalize
 // The 1/4-resolution head outputs are the only float inputs read from HBM; the up-sampled maps are
 // recomputed where they are consumed (the bilinear formula is deterministic) and written once when
 // the caller asks for them (sem_seg, eee_full).
+#include <limits.h>
+
 #include "common.cuh"
 
 namespace quber {
@@ -33,12 +35,12 @@ struct InstStat {                 // per (image, instance index); zero-initialis
 struct PostWs {
     uint32_t *bitmask;   // [B,H,WB]
     uint16_t *ins;       // [B,H,W]
-    uint32_t *area;      // [B,top_k+1]   (index 0: foreground pixels of a centre-less image)   zeroed
-    InstStat *stats;     // [B,top_k]                                                         zeroed
-    uint32_t *newid;     // [B,top_k+1]
+    InstStat *stats;     // [B,top_k+1]  per GROUPED id (index 0: foreground pixels of a centre-less image)   zeroed
+    uint32_t *newid;     // [B,top_k+1]  grouped id -> instance index + 1 (0 = dropped)
+    uint32_t *oldid;     // [B,top_k+1]  instance index -> grouped id
     int32_t *n_inst;     // [B]
     int32_t *has_stuff;  // [B]
-    size_t zero_bytes;   // area + stats are contiguous
+    size_t zero_bytes;
     size_t total;
 };
 
@@ -54,20 +56,20 @@ static PostWs carve(const quber_post_params &p, void *base) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
     char *b = static_cast<char *>(base);
-    const size_t o_area = take(B * K1 * 4);
-    const size_t o_stats = take(B * (size_t)p.top_k * sizeof(InstStat));
+    const size_t o_stats = take(B * K1 * sizeof(InstStat));
     w.zero_bytes = off;
     const size_t o_bit = take(B * H * WB * 4);
     const size_t o_ins = take(B * H * W * 2);
     const size_t o_new = take(B * K1 * 4);
+    const size_t o_old = take(B * K1 * 4);
     const size_t o_ni = take(B * 4);
     const size_t o_hs = take(B * 4);
     w.total = off;
-    w.area = reinterpret_cast<uint32_t *>(b + o_area);
     w.stats = reinterpret_cast<InstStat *>(b + o_stats);
     w.bitmask = reinterpret_cast<uint32_t *>(b + o_bit);
     w.ins = reinterpret_cast<uint16_t *>(b + o_ins);
     w.newid = reinterpret_cast<uint32_t *>(b + o_new);
+    w.oldid = reinterpret_cast<uint32_t *>(b + o_old);
     w.n_inst = reinterpret_cast<int32_t *>(b + o_ni);
     w.has_stuff = reinterpret_cast<int32_t *>(b + o_hs);
     return w;
@@ -342,79 +344,143 @@ __device__ __forceinline__ void sample8(const UpSampler &up, const Row8 &r8, con
 }
 
 // ------------------------------------------------------------------------------------------------
-// Fused per-pixel pass 1: up-sample, foreground test, nearest-centre grouping, area histogram,
-// error-map up-sample + argmax one-hot.   model.py:689-708,292; post_processing.py:44-76,103-107;
-// eval/eval_utils.py:311-313.
+// Fused per-pixel pass 1: up-sample, foreground test, nearest-centre grouping, per-id statistics (area, score sums,
+// centroid sums, box), error-map up-sample + argmax one-hot.   model.py:689-708,292,318-353; post_processing.py:44-76,
+// 103-107; eval/eval_utils.py:311-313.
 //
 // Grouping = argmin_k sqrt(fma(dx,dx,dy*dy)) with the first minimum winning (torch.norm + argmin,
-// post_processing.py:71-73).  The loop runs over centres OUTSIDE and the thread's eight pixels inside (one
-// 8-byte shared-memory read per centre instead of sixteen 4-byte ones), and it compares SQUARED distances: sqrt
-// is monotone, so a candidate with d2 >= best_d2 never wins, and one with d2 < best_d2 * (1 - 2^-21) always does
-// (the two roots are then more than one ulp apart, so they cannot round to the same float).  Only in the 4-ulp
-// band in between can both roots round to one float — a tie the reference resolves in favour of the earlier
-// centre — and there the two correctly rounded roots are compared like the reference does.
+// post_processing.py:71-73).  Three levels of exact pruning keep the K' x HW distance evaluations of the reference
+// (12 K' HW bytes materialised there) down to a few centres per pixel:
+//   CTA     the voted positions of the tile's foreground pixels lie in a box; a centre whose minimum distance to the box
+//           exceeds the smallest maximum distance of any centre to it can not win (or tie) for any pixel of the tile.
+//           Survivors are a bit set in shared memory, walked in ascending order (the first-minimum rule needs that order).
+//   thread  the same argument on the thread's eight pixels against their current bests.
+//   pixel   SQUARED distances are compared: sqrt is monotone, so a candidate with d2 >= best_d2 never wins, and one with
+//           d2 < best_d2 * (1 - 2^-21) always does (the two roots are then more than one ulp apart).  Only in the 4-ulp band
+//           in between can both roots round to one float — a tie the reference gives to the earlier centre — and there the
+//           two correctly rounded roots are compared like the reference does.
+// The statistics of model.py:318-353 are accumulated here, per GROUPED id and in integers (the sigmoid in 2^-32 fixed
+// point), while the up-sampled foreground logits are still in registers; relabel_kernel later maps ids to instances.
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }   // order-preserving
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
 template <bool S4>
-__global__ void __launch_bounds__(P_THREADS, S4 ? 3 : 2)
+__global__ void __launch_bounds__(P_THREADS, S4 ? 4 : 2)
 group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ n_centers, uint16_t *__restrict__ ins,
-             uint32_t *__restrict__ area) {
-    extern __shared__ __align__(8) float gsm[];
-    float2 *cyx = reinterpret_cast<float2 *>(gsm);                                // [top_k] (y, x)
-    unsigned int *hist = reinterpret_cast<unsigned int *>(gsm + 2 * p.top_k);     // [top_k+1]
+             InstStat *__restrict__ stats) {
+    extern __shared__ __align__(16) unsigned char gsm_raw[];
     const int b = blockIdx.z, tid = threadIdx.x, H = p.H, W = p.W;
     const int n = n_centers[b];
+    InstStat *sst = reinterpret_cast<InstStat *>(gsm_raw);                           // [n+1] (0 = stuff)
+    float2 *cyx = reinterpret_cast<float2 *>(sst + (p.top_k + 1));                    // [top_k] (y, x)
+    uint32_t *cand = reinterpret_cast<uint32_t *>(cyx + p.top_k);                     // [(top_k+31)/32] surviving centres
+    __shared__ int s_box[4];          // ordered-int min y, max y, min x, max x of the tile's voted positions
+    __shared__ int s_bound;           // ordered-int of the smallest maximum distance
+    __shared__ int s_noprune;
+    const int nwords = (n + 31) >> 5;
     for (int i = tid; i < n; i += P_THREADS)
         cyx[i] = make_float2((float)io.centers_yx[((size_t)b * p.top_k + i) * 2], (float)io.centers_yx[((size_t)b * p.top_k + i) * 2 + 1]);
-    for (int i = tid; i <= p.top_k; i += P_THREADS) hist[i] = 0;
+    for (int i = tid; i < (n + 1) * (int)(sizeof(InstStat) / 4); i += P_THREADS) reinterpret_cast<uint32_t *>(sst)[i] = 0;
+    for (int i = tid; i < nwords; i += P_THREADS) cand[i] = 0;
+    if (tid == 0) { s_box[0] = s_box[2] = INT_MAX; s_box[1] = s_box[3] = INT_MIN; s_bound = INT_MAX; s_noprune = 0; }
     __syncthreads();
     const UpSampler up = up_of(p);
     const int Wv = valid_w_of(p);
     const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
-    // a warp covers 8 rows x 32 pixels of the tile (not 2 x 128): the compact footprint is what lets the centre pruning
-    // below skip a centre for the WHOLE warp
+    // a warp covers 8 rows x 32 pixels of the tile (not 2 x 128): the compact footprint is what lets the thread-level
+    // pruning skip a centre for the WHOLE warp
     const int wrp = tid >> 5, ln = tid & 31;
     const int y = blockIdx.y * P_TH + (wrp >> 2) * 8 + (ln >> 2), x0 = blockIdx.x * P_TW + ((wrp & 3) * 4 + (ln & 3)) * 8;
     const bool inb = y < H && x0 < W;
-    if (inb) {
-        const size_t pix = (size_t)y * W + x0;
-        const float *fgp = io.foreground + (size_t)b * hw;
-        const float *oyp = io.offset + (size_t)b * 2 * hw, *oxp = oyp + hw;
-        const Row8 row(up, y, x0);
-        float sem[8];
-        unsigned id[8];
-        sample8<S4>(up, row, fgp, y, x0, sem);
-        unsigned fgm = 0;
+    const size_t pix = (size_t)y * W + x0;
+    float sem[8], ly[8], lx[8];
+    unsigned id[8];
+    unsigned fgm = 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            id[j] = 0;
+    for (int j = 0; j < 8; ++j) { id[j] = 0; sem[j] = 0.f; ly[j] = lx[j] = 0.f; }
+    if (inb) {
+        const float *fgp = io.foreground + (size_t)b * hw;
+        const Row8 row(up, y, x0);
+        sample8<S4>(up, row, fgp, y, x0, sem);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
             if (sem[j] > QUBER_FG_LOGIT_CUT && x0 + j < Wv) fgm |= 1u << j;   // r.sigmoid().round() == 1 (inside the crop)
-        }
         if (io.sem_seg) {
             float *o = io.sem_seg + (size_t)b * HW + pix;
             st_stream_f4(o, make_float4(sem[0], sem[1], sem[2], sem[3]));
             st_stream_f4(o + 4, make_float4(sem[4], sem[5], sem[6], sem[7]));
         }
-        if (fgm && n == 0) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) if (fgm >> j & 1) id[j] = INS_STUFF;
-        } else if (fgm) {
-            float ly[8], lx[8], bd2[8];
-            int best[8];
+        if (fgm && n > 0) {
+            const float *oyp = io.offset + (size_t)b * 2 * hw, *oxp = oyp + hw;
             sample8<S4>(up, row, oyp, y, x0, ly);
             sample8<S4>(up, row, oxp, y, x0, lx);
-            const float2 c0 = cyx[0];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 ly[j] = __fadd_rn((float)y, __fmul_rn(ly[j], p.offset_mul));
                 lx[j] = __fadd_rn((float)(x0 + j), __fmul_rn(lx[j], p.offset_mul));
-                const float dy = __fsub_rn(c0.x, ly[j]), dx = __fsub_rn(c0.y, lx[j]);
-                bd2[j] = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
-                best[j] = 0;
             }
-            // Pruning (exact): the eight voted positions of a thread lie in a small box (midpoint m, half diagonal r).
-            // A centre at distance D from m is at least D - r from each of them, so it cannot beat any current best when
-            // D > max_j best_j + r; the bound carries a relative 2e-5 + absolute 1e-3 slack, far wider than the fp32
-            // rounding of the distances (3e-7) and than the tie band below, so a skipped centre never wins or ties.
+        }
+    }
+    // ---- CTA-level pruning: box of the voted positions of the tile's foreground pixels
+    if (n > 1) {
+        float mny = INFINITY, mxy = -INFINITY, mnx = INFINITY, mxx = -INFINITY;
+        bool weird = false;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (fgm >> j & 1) {
+                weird |= !(fabsf(ly[j]) < 1e30f) || !(fabsf(lx[j]) < 1e30f);          // NaN / inf offsets: no pruning at all
+                mny = fminf(mny, ly[j]); mxy = fmaxf(mxy, ly[j]);
+                mnx = fminf(mnx, lx[j]); mxx = fmaxf(mxx, lx[j]);
+            }
+        const unsigned any = __ballot_sync(0xffffffffu, fgm != 0);
+        if (any) {
+            const int a0 = __reduce_min_sync(0xffffffffu, f2ord(mny)), a1 = __reduce_max_sync(0xffffffffu, f2ord(mxy));
+            const int a2 = __reduce_min_sync(0xffffffffu, f2ord(mnx)), a3 = __reduce_max_sync(0xffffffffu, f2ord(mxx));
+            const unsigned wd = __ballot_sync(0xffffffffu, weird);
+            if (ln == 0) {
+                atomicMin(&s_box[0], a0); atomicMax(&s_box[1], a1); atomicMin(&s_box[2], a2); atomicMax(&s_box[3], a3);
+                if (wd) s_noprune = 1;
+            }
+        }
+        __syncthreads();
+        const bool have = s_box[0] != INT_MAX;
+        const float by0 = ord2f(s_box[0]), by1 = ord2f(s_box[1]), bx0 = ord2f(s_box[2]), bx1 = ord2f(s_box[3]);
+        if (have && !s_noprune) {
+            for (int k = tid; k < n; k += P_THREADS) {          // largest distance from centre k to the box: at a corner
+                const float2 c = cyx[k];
+                const float dy = fmaxf(fabsf(c.x - by0), fabsf(c.x - by1)), dx = fmaxf(fabsf(c.y - bx0), fabsf(c.y - bx1));
+                atomicMin(&s_bound, f2ord(sqrtf(dy * dy + dx * dx)));
+            }
+        }
+        __syncthreads();
+        if (have) {
+            // keep k iff its smallest distance to the box does not exceed the bound; slack (relative 1e-4, absolute 1e-2 px) is
+            // orders of magnitude above the fp32 rounding of these distances, so a dropped centre never wins or ties
+            const float bound = s_noprune ? INFINITY : ord2f(s_bound) * 1.0001f + 1e-2f;
+            for (int k = tid; k < n; k += P_THREADS) {
+                const float2 c = cyx[k];
+                const float dy = fmaxf(fmaxf(by0 - c.x, c.x - by1), 0.f), dx = fmaxf(fmaxf(bx0 - c.y, c.y - bx1), 0.f);
+                if (!(sqrtf(dy * dy + dx * dx) > bound)) atomicOr(&cand[k >> 5], 1u << (k & 31));
+            }
+        }
+        __syncthreads();
+    } else if (n == 1) {
+        if (tid == 0) cand[0] = 1u;
+        __syncthreads();
+    }
+    if (inb) {
+        if (fgm && n == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (fgm >> j & 1) id[j] = INS_STUFF;
+        } else if (fgm) {
+            float bd2[8];
+            int best[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { bd2[j] = INFINITY; best[j] = 0; }
+            // Thread-level pruning (exact): the eight voted positions of a thread lie in a small box (midpoint m, half
+            // diagonal r).  A centre at distance D from m is at least D - r from each of them, so it cannot beat any current
+            // best when D > max_j best_j + r; the bound carries a relative 2e-5 + absolute 1e-3 slack.
             float mny = ly[0], mxy = ly[0], mnx = lx[0], mxx = lx[0];
 #pragma unroll
             for (int j = 1; j < 8; ++j) {
@@ -423,32 +489,40 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
             }
             const float my = 0.5f * (mny + mxy), mx = 0.5f * (mnx + mxx);
             const float rad = sqrtf((mxy - my) * (mxy - my) + (mxx - mx) * (mxx - mx)) * 1.0001f + 1e-3f;
-            auto prune_bound = [&]() {
-                float b = bd2[0];
+            float cut2 = INFINITY;
+            bool first = true;
+            for (int wd = 0; wd < nwords; ++wd) {
+                uint32_t bits = cand[wd];
+                while (bits) {
+                    const int k = 32 * wd + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    const float2 c = cyx[k];
+                    if (!first) {
+                        const float my_ = c.x - my, mx_ = c.y - mx;
+                        if (my_ * my_ + mx_ * mx_ > cut2) continue;                            // NaN bound: never skips
+                    }
+                    bool changed = false;
 #pragma unroll
-                for (int j = 1; j < 8; ++j) b = fmaxf(b, bd2[j]);
-                const float s_ = sqrtf(b) + rad;
-                return s_ * s_ * 1.00002f + 1e-3f;
-            };
-            float cut2 = prune_bound();
-#pragma unroll 1
-            for (int k = 1; k < n; ++k) {
-                const float2 c = cyx[k];
-                const float my_ = c.x - my, mx_ = c.y - mx;
-                if (my_ * my_ + mx_ * mx_ > cut2) continue;                                    // NaN bound: never skips
-                bool changed = false;
+                    for (int j = 0; j < 8; ++j) {
+                        const float dy = __fsub_rn(c.x, ly[j]), dx = __fsub_rn(c.y, lx[j]);
+                        const float d2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+                        if (first) { bd2[j] = d2; best[j] = k; changed = true; }
+                        else if (d2 < bd2[j]) {
+                            bool better = true;
+                            if (!(d2 < bd2[j] * 0.99999952316284179688f))                      // 1 - 2^-21: the 4-ulp band,
+                                better = __fsqrt_rn(d2) < __fsqrt_rn(bd2[j]);                  // compare the roots
+                            if (better) { bd2[j] = d2; best[j] = k; changed = true; }
+                        }
+                    }
+                    first = false;
+                    if (changed) {
+                        float bb = bd2[0];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const float dy = __fsub_rn(c.x, ly[j]), dx = __fsub_rn(c.y, lx[j]);
-                    const float d2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
-                    if (d2 < bd2[j]) {
-                        bool better = true;
-                        if (!(d2 < bd2[j] * 0.99999952316284179688f))                          // 1 - 2^-21: the 4-ulp band,
-                            better = __fsqrt_rn(d2) < __fsqrt_rn(bd2[j]);                      // compare the roots
-                        if (better) { bd2[j] = d2; best[j] = k; changed = true; }
+                        for (int j = 1; j < 8; ++j) bb = fmaxf(bb, bd2[j]);
+                        const float s_ = sqrtf(bb) + rad;
+                        cut2 = s_ * s_ * 1.00002f + 1e-3f;
                     }
                 }
-                if (changed) cut2 = prune_bound();
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) if (fgm >> j & 1) id[j] = best[j] + 1;
@@ -463,78 +537,153 @@ group_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ 
             st_stream_u4(o, make_uint4(v[0], v[1], v[2], v[3]));
             st_stream_u4(o + 4, make_uint4(v[4], v[5], v[6], v[7]));
         }
-        // area histogram, run-length compressed per thread
-        unsigned cur = id[0], cnt = 0;
+    }
+    // ---- statistics per grouped id (slot 0 = stuff).  A thread whose eight pixels share one id (all but the threads on an
+    // instance border) joins the other such lanes of its warp: match.any groups the lanes by id and redux.sync adds /
+    // maximises inside the group, so one lane issues the shared-memory atomics.  All sums are integers (the sigmoid in 32.32
+    // fixed point), so the result does not depend on the grouping or the order.
+    {
+        int slot[8];
+        bool uni = true, anyfg = false;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            if (id[j] != cur) {
-                if (cur) atomicAdd(&hist[cur == INS_STUFF ? 0 : cur], cnt);
-                cur = id[j]; cnt = 0;
-            }
-            ++cnt;
+            slot[j] = id[j] == 0 ? -1 : (id[j] == INS_STUFF ? 0 : (int)id[j]);
+            uni &= slot[j] == (id[0] == 0 ? -1 : (id[0] == INS_STUFF ? 0 : (int)id[0]));
+            anyfg |= slot[j] >= 0;
         }
-        if (cur) atomicAdd(&hist[cur == INS_STUFF ? 0 : cur], cnt);
-        // error maps
-        const int C = p.eee_channels;
-        if (C > 0 && io.eee && (io.eee_full || io.eee_onehot)) {
-            float bestv[8];
-            int bestc[8];
-            int x0e = x0;
-            asm volatile("" : "+r"(x0e));               // opaque: rebuild the row set-up here instead of keeping it live over the centre loop
-            const Row8 rowe(up, y, x0e);
-            for (int c = 0; c < C; ++c) {
-                const float *ep = io.eee + ((size_t)b * C + c) * hw;
-                float v[8];
-                sample8<S4>(up, rowe, ep, y, x0, v);
+        unsigned long long q[8];
+        if (anyfg) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    if (c == 0 || v[j] > bestv[j]) { bestv[j] = v[j]; bestc[j] = c; }   // first maximum wins
-                if (io.eee_full) {
-                    float *o = io.eee_full + ((size_t)b * C + c) * HW + pix;
-                    st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
-                    st_stream_f4(o + 4, make_float4(v[4], v[5], v[6], v[7]));
-                }
+            for (int j = 0; j < 8; ++j) {
+                const float sg = __fdividef(1.0f, 1.0f + __expf(-sem[j]));     // model.py:319 sigmoid
+                q[j] = __float2ull_rn(sg * 4294967296.0f);
             }
-            if (io.eee_onehot)
-                for (int c = 0; c < C; ++c) {
-                    uint32_t lo = 0, hi = 0;
+        }
+        const bool fast = uni && slot[0] >= 0;
+        const unsigned act = __ballot_sync(0xffffffffu, fast);
+        if (fast) {
+            unsigned long long sig = 0;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        lo |= (uint32_t)(bestc[j] == c) << (8 * j);
-                        hi |= (uint32_t)(bestc[4 + j] == c) << (8 * j);
-                    }
-                    st_stream_u2(io.eee_onehot + ((size_t)b * C + c) * HW + pix, make_uint2(lo, hi));
-                }
+            for (int j = 0; j < 8; ++j) sig += q[j];
+            const unsigned grp = __match_any_sync(act, slot[0]);
+            const unsigned shi = __reduce_add_sync(grp, (unsigned)(sig >> 16)), slo = __reduce_add_sync(grp, (unsigned)(sig & 0xffffu));
+            const unsigned cn = __reduce_add_sync(grp, 8u), sys = __reduce_add_sync(grp, 8u * (unsigned)y);
+            const unsigned sxs = __reduce_add_sync(grp, 8u * (unsigned)x0 + 28u);
+            const unsigned mx = __reduce_max_sync(grp, (unsigned)(x0 + 7)), mnx = __reduce_max_sync(grp, (unsigned)(W - 1 - x0));
+            const unsigned my = __reduce_max_sync(grp, (unsigned)y), mny = __reduce_max_sync(grp, (unsigned)(H - 1 - y));
+            if ((tid & 31) == __ffs(grp) - 1) {
+                InstStat *s = sst + slot[0];
+                atomicAdd(&s->sig, ((unsigned long long)shi << 16) + slo);
+                atomicAdd(&s->sy, (unsigned long long)sys);
+                atomicAdd(&s->sx, (unsigned long long)sxs);
+                atomicAdd(&s->cnt, cn);
+                atomicMax(&s->maxx, mx);
+                atomicMax(&s->maxnx, mnx);
+                atomicMax(&s->maxy, my);
+                atomicMax(&s->maxny, mny);
+            }
+        } else if (anyfg) {                                                    // instance border: run-length compressed per thread
+            int cur = -1;
+            unsigned cnt = 0, sx = 0, mnx = 0, mxx = 0;
+            unsigned long long sig = 0;
+            auto flush = [&]() {
+                if (cur < 0 || cnt == 0) return;
+                InstStat *s = sst + cur;
+                atomicAdd(&s->sig, sig);
+                atomicAdd(&s->sy, (unsigned long long)cnt * (unsigned)y);
+                atomicAdd(&s->sx, (unsigned long long)sx);
+                atomicAdd(&s->cnt, cnt);
+                atomicMax(&s->maxx, mxx);
+                atomicMax(&s->maxnx, (unsigned)(W - 1) - mnx);
+                atomicMax(&s->maxy, (unsigned)y);
+                atomicMax(&s->maxny, (unsigned)(H - 1 - y));
+            };
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (slot[j] != cur) { flush(); cur = slot[j]; cnt = 0; sx = 0; sig = 0; mnx = x0 + j; }
+                if (cur >= 0) { sig += q[j]; ++cnt; sx += x0 + j; mxx = x0 + j; }
+            }
+            flush();
         }
     }
     __syncthreads();
-    for (int i = tid; i <= n; i += P_THREADS)
-        if (hist[i]) atomicAdd(&area[(size_t)b * (p.top_k + 1) + i], hist[i]);
+    for (int i = tid; i <= n; i += P_THREADS) {
+        const InstStat s = sst[i];
+        if (!s.cnt) continue;
+        InstStat *g = stats + (size_t)b * (p.top_k + 1) + i;
+        atomicAdd(&g->sig, s.sig); atomicAdd(&g->sy, s.sy); atomicAdd(&g->sx, s.sx);
+        atomicAdd(&g->cnt, s.cnt);
+        atomicMax(&g->maxx, s.maxx); atomicMax(&g->maxnx, s.maxnx);
+        atomicMax(&g->maxy, s.maxy); atomicMax(&g->maxny, s.maxny);
+    }
+}
+
+// Error maps on their own: x4 up-sample of the C error-head planes (model.py:704-708), argmax -> one-hot
+// (eval/eval_utils.py:311-313).  A pure streaming pass (16 + 4 bytes written per pixel and channel, 0.6 MB read per frame),
+// kept out of the grouping kernel so that both run at their own occupancy.
+template <bool S4>
+__global__ void __launch_bounds__(P_THREADS, 4)
+eee_kernel(quber_post_params p, quber_post_io io) {
+    const int b = blockIdx.z, tid = threadIdx.x, H = p.H, W = p.W, C = p.eee_channels;
+    const UpSampler up = up_of(p);
+    const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
+    const int y = blockIdx.y * P_TH + (tid >> 4), x0 = blockIdx.x * P_TW + (tid & 15) * 8;
+    if (y >= H || x0 >= W) return;
+    const size_t pix = (size_t)y * W + x0;
+    float bestv[8];
+    int bestc[8];
+    const Row8 rowe(up, y, x0);
+    for (int c = 0; c < C; ++c) {
+        const float *ep = io.eee + ((size_t)b * C + c) * hw;
+        float v[8];
+        sample8<S4>(up, rowe, ep, y, x0, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (c == 0 || v[j] > bestv[j]) { bestv[j] = v[j]; bestc[j] = c; }   // first maximum wins
+        if (io.eee_full) {
+            float *o = io.eee_full + ((size_t)b * C + c) * HW + pix;
+            st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
+            st_stream_f4(o + 4, make_float4(v[4], v[5], v[6], v[7]));
+        }
+    }
+    if (io.eee_onehot)
+        for (int c = 0; c < C; ++c) {
+            uint32_t lo = 0, hi = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                lo |= (uint32_t)(bestc[j] == c) << (8 * j);
+                hi |= (uint32_t)(bestc[4 + j] == c) << (8 * j);
+            }
+            st_stream_u2(io.eee_onehot + ((size_t)b * C + c) * HW + pix, make_uint2(lo, hi));
+        }
 }
 
 // merge_semantic_and_instance's id loop (post_processing.py:137-150): ids ascending, drop area < min_area,
 // running new id; stuff paste (:152-160) reachable only for a centre-less image.  One CTA per image.
 __global__ void __launch_bounds__(SEL_THREADS)
-relabel_kernel(quber_post_params p, const int32_t *__restrict__ n_centers, const uint32_t *__restrict__ area,
-               uint32_t *__restrict__ newid, int32_t *__restrict__ n_inst, int32_t *__restrict__ has_stuff) {
+relabel_kernel(quber_post_params p, const int32_t *__restrict__ n_centers, const InstStat *__restrict__ stats,
+               uint32_t *__restrict__ newid, uint32_t *__restrict__ oldid, int32_t *__restrict__ n_inst,
+               int32_t *__restrict__ has_stuff) {
     __shared__ int warp_tot[32];
     const int b = blockIdx.x, tid = threadIdx.x, n = n_centers[b];
-    const uint32_t *a = area + (size_t)b * (p.top_k + 1);
-    uint32_t *nid = newid + (size_t)b * (p.top_k + 1);
+    const InstStat *a = stats + (size_t)b * (p.top_k + 1);       // .cnt = area of the grouped id
+    uint32_t *nid = newid + (size_t)b * (p.top_k + 1), *oid = oldid + (size_t)b * (p.top_k + 1);
     int base = 0;
     for (int i0 = 0; i0 < n; i0 += SEL_THREADS) {
         const int id = i0 + tid + 1;
-        const int flag = (id <= n) && a[id] > 0 && (int)a[id] >= p.min_area;
+        const int flag = (id <= n) && a[id].cnt > 0 && (int)a[id].cnt >= p.min_area;
         int total;
         const int ex = block_excl_scan(flag, warp_tot, total);
         if (id <= n) nid[id] = flag ? base + ex + 1 : 0;
+        if (flag) oid[base + ex] = (uint32_t)id;
         base += total;
     }
     if (tid == 0) {
         nid[0] = 0;
         int hs = 0;
         if (n == 0) {
-            const uint32_t s = a[0];
+            oid[0] = 0;                                          // the stuff paste's statistics live in slot 0
+            const uint32_t s = a[0].cnt;
             hs = s > 0 && (long long)s >= (long long)p.stuff_area;
         }
         has_stuff[b] = hs;
@@ -565,19 +714,16 @@ offsets_kernel(int B, int max_instances, const int32_t *__restrict__ n_inst, int
 // statistics the scores / boxes are made of.  post_processing.py:129,150,160; model.py:318-353.
 __global__ void __launch_bounds__(P_THREADS)
 emit_kernel(quber_post_params p, quber_post_io io, const uint16_t *__restrict__ ins, const uint32_t *__restrict__ newid,
-            const int32_t *__restrict__ n_inst, const int32_t *__restrict__ has_stuff, InstStat *__restrict__ stats) {
+            const int32_t *__restrict__ n_inst, const int32_t *__restrict__ has_stuff) {
     extern __shared__ __align__(16) unsigned char esm[];
     const int b = blockIdx.z, tid = threadIdx.x, H = p.H, W = p.W;
     const int ninst = n_inst[b], hs = has_stuff[b], nc = io.n_centers[b];
-    InstStat *sst = reinterpret_cast<InstStat *>(esm);                         // [max(ninst,1)]
-    uint32_t *nid = reinterpret_cast<uint32_t *>(sst + (ninst > 0 ? ninst : 1)); // [nc+1]
-    for (int i = tid; i < ninst * (int)(sizeof(InstStat) / 4); i += P_THREADS) reinterpret_cast<uint32_t *>(sst)[i] = 0;
+    uint32_t *nid = reinterpret_cast<uint32_t *>(esm);                         // [nc+1]
     for (int i = tid; i <= nc; i += P_THREADS) nid[i] = newid[(size_t)b * (p.top_k + 1) + i];
     __syncthreads();
-    const UpSampler up = up_of(p);
-    const size_t hw = (size_t)up.h * up.w, HW = (size_t)H * W;
+    const size_t HW = (size_t)H * W;
     const int y = blockIdx.y * P_TH + (tid >> 4), x0 = blockIdx.x * P_TW + (tid & 15) * 8;
-    const bool inb = y < H && x0 < W;                       // every lane stays alive: the statistics use warp collectives
+    const bool inb = y < H && x0 < W;
     int idx[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) idx[j] = -1;
@@ -644,92 +790,12 @@ emit_kernel(quber_post_params p, quber_post_io io, const uint16_t *__restrict__ 
             }
         }
     }
-    // Statistics.  A thread whose eight pixels belong to one instance (all but the threads on an instance border) joins
-    // the other such lanes of its warp: match.any groups the lanes by instance and redux.sync adds / maximises inside
-    // the group, so that one lane issues the eight shared-memory atomics instead of up to 32 lanes colliding on the same
-    // slot.  All sums are integers (the sigmoid in 32.32 fixed point), so the result does not depend on the grouping.
-    {
-        const float *fgp = io.foreground + (size_t)b * hw;
-        bool uni = true, anyfg = false;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { uni &= idx[j] == idx[0]; anyfg |= idx[j] >= 0; }
-        unsigned long long q[8];
-        if (anyfg) {
-            float fgv[8];
-            if (p.scale == 4) { const Row8 row(up, y, x0); row.sample(fgp, fgv); }
-            else {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) fgv[j] = up.at(fgp, y, x0 + j);
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float sg = __fdividef(1.0f, 1.0f + __expf(-fgv[j]));     // model.py:319 sigmoid
-                q[j] = __float2ull_rn(sg * 4294967296.0f);
-            }
-        }
-        const bool fast = uni && idx[0] >= 0;
-        const unsigned act = __ballot_sync(0xffffffffu, fast);
-        if (fast) {
-            unsigned long long sig = 0;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) sig += q[j];
-            const unsigned grp = __match_any_sync(act, idx[0]);
-            const unsigned shi = __reduce_add_sync(grp, (unsigned)(sig >> 16)), slo = __reduce_add_sync(grp, (unsigned)(sig & 0xffffu));
-            const unsigned cn = __reduce_add_sync(grp, 8u), sys = __reduce_add_sync(grp, 8u * (unsigned)y);
-            const unsigned sxs = __reduce_add_sync(grp, 8u * (unsigned)x0 + 28u);
-            const unsigned mx = __reduce_max_sync(grp, (unsigned)(x0 + 7)), mnx = __reduce_max_sync(grp, (unsigned)(W - 1 - x0));
-            const unsigned my = __reduce_max_sync(grp, (unsigned)y), mny = __reduce_max_sync(grp, (unsigned)(H - 1 - y));
-            if ((tid & 31) == __ffs(grp) - 1) {
-                InstStat *s = sst + idx[0];
-                atomicAdd(&s->sig, ((unsigned long long)shi << 16) + slo);
-                atomicAdd(&s->sy, (unsigned long long)sys);
-                atomicAdd(&s->sx, (unsigned long long)sxs);
-                atomicAdd(&s->cnt, cn);
-                atomicMax(&s->maxx, mx);
-                atomicMax(&s->maxnx, mnx);
-                atomicMax(&s->maxy, my);
-                atomicMax(&s->maxny, mny);
-            }
-        } else if (anyfg) {                                                    // instance border: run-length compressed per thread
-            int cur = -1;
-            unsigned cnt = 0, sx = 0, mnx = 0, mxx = 0;
-            unsigned long long sig = 0;
-            auto flush = [&]() {
-                if (cur < 0 || cnt == 0) return;
-                InstStat *s = sst + cur;
-                atomicAdd(&s->sig, sig);
-                atomicAdd(&s->sy, (unsigned long long)cnt * (unsigned)y);
-                atomicAdd(&s->sx, (unsigned long long)sx);
-                atomicAdd(&s->cnt, cnt);
-                atomicMax(&s->maxx, mxx);
-                atomicMax(&s->maxnx, (unsigned)(W - 1) - mnx);
-                atomicMax(&s->maxy, (unsigned)y);
-                atomicMax(&s->maxny, (unsigned)(H - 1 - y));
-            };
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                if (idx[j] != cur) { flush(); cur = idx[j]; cnt = 0; sx = 0; sig = 0; mnx = x0 + j; }
-                if (cur >= 0) { sig += q[j]; ++cnt; sx += x0 + j; mxx = x0 + j; }
-            }
-            flush();
-        }
-    }
-    __syncthreads();
-    for (int i = tid; i < ninst; i += P_THREADS) {
-        const InstStat s = sst[i];
-        if (!s.cnt) continue;
-        InstStat *g = stats + (size_t)b * p.top_k + i;
-        atomicAdd(&g->sig, s.sig); atomicAdd(&g->sy, s.sy); atomicAdd(&g->sx, s.sx);
-        atomicAdd(&g->cnt, s.cnt);
-        atomicMax(&g->maxx, s.maxx); atomicMax(&g->maxnx, s.maxnx);
-        atomicMax(&g->maxy, s.maxy); atomicMax(&g->maxny, s.maxny);
-    }
 }
 
 // model.py:322-353: label, score = mean(sigmoid(fg)[mask]) * centre[int(cy), int(cx)], box.
 __global__ void __launch_bounds__(P_THREADS)
 finalize_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict__ n_inst,
-                const int32_t *__restrict__ has_stuff, const InstStat *__restrict__ stats) {
+                const int32_t *__restrict__ has_stuff, const InstStat *__restrict__ stats, const uint32_t *__restrict__ oldid) {
     const int b = blockIdx.x;
     const int ninst = n_inst[b], hs = has_stuff[b], off = io.inst_offsets[b];
     const UpSampler up = up_of(p);
@@ -737,7 +803,7 @@ finalize_kernel(quber_post_params p, quber_post_io io, const int32_t *__restrict
     for (int i = threadIdx.x; i < ninst; i += blockDim.x) {
         const int row = off + i;
         if (row >= p.max_instances) break;
-        const InstStat s = stats[(size_t)b * p.top_k + i];
+        const InstStat s = stats[(size_t)b * (p.top_k + 1) + oldid[(size_t)b * (p.top_k + 1) + i]];
         io.labels[row] = p.label_divisor + (hs ? 0 : i + 1);
         const double cnt = (double)s.cnt;
         const float sem = (float)((double)s.sig * (1.0 / 4294967296.0) / cnt);
@@ -873,23 +939,33 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
         if (int rc = check_launch("center_select_kernel")) return rc;
     }
     dim3 pgrid(cdiv(p.W, P_TW), cdiv(p.H, P_TH), p.B);
-    if (p.scale == 4)
-        group_kernel<true><<<pgrid, P_THREADS, (3 * (size_t)p.top_k + 1) * 4, st>>>(p, io, io.n_centers, ws.ins, ws.area);
-    else
-        group_kernel<false><<<pgrid, P_THREADS, (3 * (size_t)p.top_k + 1) * 4, st>>>(p, io, io.n_centers, ws.ins, ws.area);
-    if (int rc = check_launch("group_kernel")) return rc;
-    relabel_kernel<<<p.B, SEL_THREADS, 0, st>>>(p, io.n_centers, ws.area, ws.newid, ws.n_inst, ws.has_stuff);
+    {
+        const size_t gsmem = ((size_t)p.top_k + 1) * sizeof(InstStat) + (size_t)p.top_k * sizeof(float2) + (((size_t)p.top_k + 31) / 32) * 4;
+        const bool has_eee = p.eee_channels > 0 && io.eee && (io.eee_full || io.eee_onehot);
+        if (gsmem > 48 * 1024) {
+            QUBER_CUDA_TRY(cudaFuncSetAttribute(group_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem));
+            QUBER_CUDA_TRY(cudaFuncSetAttribute(group_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem));
+        }
+        if (p.scale == 4) group_kernel<true><<<pgrid, P_THREADS, gsmem, st>>>(p, io, io.n_centers, ws.ins, ws.stats);
+        else group_kernel<false><<<pgrid, P_THREADS, gsmem, st>>>(p, io, io.n_centers, ws.ins, ws.stats);
+        if (int rc = check_launch("group_kernel")) return rc;
+        // the error maps are a pure streaming pass of their own (measured, C2: fused 172 us; 99 + 66 us split)
+        if (has_eee) {
+            if (p.scale == 4) eee_kernel<true><<<pgrid, P_THREADS, 0, st>>>(p, io);
+            else eee_kernel<false><<<pgrid, P_THREADS, 0, st>>>(p, io);
+            if (int rc = check_launch("eee_kernel")) return rc;
+        }
+    }
+    relabel_kernel<<<p.B, SEL_THREADS, 0, st>>>(p, io.n_centers, ws.stats, ws.newid, ws.oldid, ws.n_inst, ws.has_stuff);
     if (int rc = check_launch("relabel_kernel")) return rc;
     offsets_kernel<<<1, SEL_THREADS, 0, st>>>(p.B, p.max_instances, ws.n_inst, io.inst_offsets, io.status);
     if (int rc = check_launch("offsets_kernel")) return rc;
     {
-        const size_t smem = (size_t)p.top_k * sizeof(InstStat) + ((size_t)p.top_k + 1) * 4 + sizeof(InstStat);
-        if (smem > 48 * 1024)
-            QUBER_CUDA_TRY(cudaFuncSetAttribute(emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        emit_kernel<<<pgrid, P_THREADS, smem, st>>>(p, io, ws.ins, ws.newid, ws.n_inst, ws.has_stuff, ws.stats);
+        const size_t smem = ((size_t)p.top_k + 1) * 4;
+        emit_kernel<<<pgrid, P_THREADS, smem, st>>>(p, io, ws.ins, ws.newid, ws.n_inst, ws.has_stuff);
         if (int rc = check_launch("emit_kernel")) return rc;
     }
-    finalize_kernel<<<p.B, P_THREADS, 0, st>>>(p, io, ws.n_inst, ws.has_stuff, ws.stats);
+    finalize_kernel<<<p.B, P_THREADS, 0, st>>>(p, io, ws.n_inst, ws.has_stuff, ws.stats, ws.oldid);
     return check_launch("finalize_kernel");
 }
 

@@ -117,7 +117,7 @@ class HotPath:
         return out
 
     # kernels launched per call (for bench.py's gpu_launches; memsets are not kernels)
-    LAUNCHES = dict(encode=2, boundary=1, post=7, msda_layer=1)
+    LAUNCHES = dict(encode=2, boundary=1, post=8, msda_layer=1)
 
     # --- end to end: host buffers in, host results out ------------------------------------------
     def _staging(self, masks_host, head_host):
