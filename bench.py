@@ -346,6 +346,7 @@ def run_ours(args):
         # under the host-side packing / host->device copies of refine_batch_host's chunk pipeline
         hp.msda_layers(d["msda"], N_LAYERS)
         o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL, kernel_frames=E2E_KERNEL)
+        hp.last_route_dense = dict(hp.last_route)
         gather_host_call(keep)
         return o
 
@@ -384,7 +385,9 @@ def run_ours(args):
     rle_val, rle_ms, _, _ = time_e2e(e2e_rle)
     packed = bool(hp.pack_masks)
     head_bytes = sum(v.numel() * 4 for v in sets[0]["h_head"].values())
-    h2d = sets[0]["h_masks"].numel() // (8 if packed else 1) + head_bytes
+    route = getattr(hp, "last_route_dense", dict(byte_frames=B, packed_frames=0))
+    fb = sets[0]["h_masks"][0].numel()
+    h2d = route["byte_frames"] * fb + route["packed_frames"] * fb // 8 + head_bytes
     h2d_rle = sets[0]["h_rle_counts"].numel() * 4 + sets[0]["h_rle_offsets"].numel() * 8 + head_bytes
     # what this box's host link gives a plain pinned copy of the same mask bytes (the floor under the dense call; it differs
     # between boxes of the pool by NUMA placement of the pinned pages)
@@ -452,9 +455,10 @@ def run_ours(args):
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms, "steps": e2e_steps, "host_link": pcie,
                 "input": "dense uint8 masks [B,K,H,W] in pinned host memory (MaskRefinerPredictor.predict's contract)",
-                "mask_transfer": ("one bit per pixel, packed on %d host threads inside the timed region" % hp.pack_threads) if packed
+                "mask_transfer": ("%d frames as bytes through the copy engine while %d host threads bit-pack the other %d (one bit per pixel), "
+                                  "inside the timed region" % (route["byte_frames"], hp.pack_threads, route["packed_frames"])) if packed
                                  else "bytes",
-                "route_rule": hp.pack_rule, "graphs": bool(hp.use_graphs),
+                "route_rule": hp.pack_rule, "route": getattr(hp, "last_route_dense", None), "graphs": bool(hp.use_graphs),
                 # the dense call has to read every mask byte on the host once (packing) or push it over the link (bytes)
                 "bound": "host (reading the dense mask bytes: DRAM rate of the packing threads / host link)"
                          if pcie and e2e_ms < 2.0 * max(pcie.get("h2d_floor_ms_per_step", 0.0),

@@ -7,16 +7,16 @@
 // maskrefiner/modeling/backbone/resnet.py:473-485).  PyTorch stores a Linear weight as [N,K] row-major,
 // i.e. BOTH operands are K-major — exactly what tcgen05.mma wants from shared memory.
 //
-// Structure (one 128 x BN output tile per CTA, 192 threads, 2-3 CTAs per SM so that one CTA's epilogue
-// overlaps another's main loop — with K = 256 the main loop is only four k-blocks and the GEMM is bound by
-// the HBM traffic of A and C, not by the tensor pipe):
-//   warp 0   one lane: TMA producer — A and W tiles (128B-swizzled, K-major) into a 3-stage ring, mbarrier
-//            complete_tx; rows / columns / k past the matrix edge arrive as zeros (TMA out-of-bounds fill)
-//   warp 1   allocates TMEM (BN fp32 columns x 128 lanes); one lane issues tcgen05.mma (cta_group::1,
+// Structure (persistent: one CTA per SM walks 128 x BN output tiles, BN in {64, 128, 256}; the accumulator is
+// double-buffered in TMEM so that the epilogue of one tile overlaps the MMAs of the next — with K = 256 a tile's main loop
+// is only four k-blocks and the GEMM is bound by the HBM traffic of A and C, not by the tensor pipe):
+//   warp 0   one lane: TMA producer — A and W tiles (128B-swizzled, K-major) into a 3-4-stage ring that keeps running
+//            across tiles, mbarrier complete_tx; rows / columns / k past the matrix edge arrive as zeros (TMA fill)
+//   warp 1   allocates TMEM (2 x BN fp32 columns x 128 lanes); one lane issues tcgen05.mma (cta_group::1,
 //            kind::f16 for bf16 or kind::tf32 for fp32 inputs, M = 128, N = BN, K = 32 bytes per instruction),
 //            tcgen05.commit frees the smem stage / signals the epilogue
 //   warps 2-5  epilogue: tcgen05.ld (32 lanes x 32 columns per instruction) -> + bias -> activation ->
-//            128B-swizzled staging in the (now dead) pipeline stages -> TMA store of 32-row x 128-byte boxes
+//            128B-swizzled staging -> TMA store of 32-row x 128-byte boxes; hand the TMEM buffer back
 //
 // fp32-accurate mode (SPLIT, "3xTF32"): the reference runs these layers in fp32 (`autocast(enabled=False)`,
 // msdeformattn.py:314) and a single TF32 product only carries 10 mantissa bits.  Every fp32 operand is split into
@@ -34,7 +34,6 @@
 namespace quber {
 
 constexpr int G_BM = 128;
-constexpr int G_STAGES = 3;
 constexpr int G_THREADS = 192;
 constexpr int G_KBYTES = 128;          // bytes of K per stage row = one 128B swizzle atom
 
@@ -85,36 +84,46 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
     return d;
 }
 
+// Persistent kernel: one CTA per SM walks the output tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... (N tiles fastest, so
+// the CTAs working on one row panel at the same time share its A tile in L2).  The accumulator is double-buffered in
+// TMEM (2 x BN fp32 columns), so the MMAs of tile t + 1 run while the epilogue warps drain tile t — with K = 256 a tile is
+// only four k-blocks of MMA and a one-tile-per-CTA kernel spends most of its life in the prologue / epilogue.
+//   warp 0       TMA producer (A, W [, W_lo] into an NST-stage ring; the ring runs on across tile boundaries)
+//   warp 1       TMEM allocation, MMA issue: waits tmem_empty[buf], issues the tile's MMAs, commits tmem_full[buf]
+//   warps 2-5    epilogue: tcgen05.ld -> + bias -> activation -> swizzled staging -> TMA store; arrive on tmem_empty[buf]
+//   warps 6-9    (SPLIT only) operand split of the A stage in shared memory, between the TMA's arrival and the MMA issue
 template <int BN, bool TF32, typename OT, bool SPLIT = false>
-__global__ void __launch_bounds__(G_THREADS)
+__global__ void __launch_bounds__(SPLIT ? G_THREADS + 128 : G_THREADS)
 gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                      const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_c,
                      const float *__restrict__ bias, int M, int N, int K, int act) {
     static_assert(!SPLIT || TF32, "the split mode is an fp32 mode");
-    constexpr int NST = SPLIT ? 2 : G_STAGES;           // SPLIT stages hold A_hi | A_lo | W_hi | W_lo: twice the bytes
+    static_assert(BN == 64 || BN == 128 || BN == 256, "tile width");
+    constexpr int NST = SPLIT ? 2 : (BN == 256 ? 3 : 4);     // SPLIT stages hold A_hi | A_lo | W_hi | W_lo: twice the bytes
     extern __shared__ __align__(1024) unsigned char gsm_raw[];
     // SWIZZLE_128B tiles must sit on 1024-byte boundaries of the SHARED address space
     unsigned char *gsm = gsm_raw + ((1024u - (g_smem_u32(gsm_raw) & 1023u)) & 1023u);
-    __shared__ __align__(8) uint64_t full[G_STAGES], empty[G_STAGES], conv[G_STAGES], tmem_full;
+    __shared__ __align__(8) uint64_t full[4], empty[4], conv[4], tmem_full[2], tmem_empty[2];
     __shared__ uint32_t tmem_base_s;
     __shared__ float bias_s[BN];
     __shared__ int abort_s;
     constexpr int A_BYTES = G_BM * G_KBYTES, W_BYTES = BN * G_KBYTES, STAGE = (SPLIT ? 2 : 1) * (A_BYTES + W_BYTES);
     constexpr int W_OFF = (SPLIT ? 2 : 1) * A_BYTES;    // stage layout: A [| A_lo] | W [| W_lo]
     constexpr int KELEMS = TF32 ? 32 : 64;              // elements of K per stage
+    unsigned char *stg_base = gsm + (size_t)NST * STAGE;      // epilogue staging: 4 warps x 2 buffers x 4 KB, after the ring
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.y * G_BM, n0 = blockIdx.x * BN;   // N tiles fastest: neighbours share the A tile in L2
     const int nkb = (K + KELEMS - 1) / KELEMS;
+    const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + G_BM - 1) / G_BM;
+    const int ntiles = tiles_n * tiles_m;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < G_STAGES; ++s) { g_mbar_init(&full[s], 1); g_mbar_init(&empty[s], 1); g_mbar_init(&conv[s], G_THREADS - 64); }
-        g_mbar_init(&tmem_full, 1);
+        for (int s = 0; s < 4; ++s) { g_mbar_init(&full[s], 1); g_mbar_init(&empty[s], 1); g_mbar_init(&conv[s], 128); }
+        for (int s = 0; s < 2; ++s) { g_mbar_init(&tmem_full[s], 1); g_mbar_init(&tmem_empty[s], 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         abort_s = 0;
     }
-    for (int i = threadIdx.x; i < BN; i += G_THREADS) bias_s[i] = (bias && n0 + i < N) ? __ldg(bias + n0 + i) : 0.f;
-    if (warp == 1) {                                     // TMEM: BN fp32 accumulator columns
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(g_smem_u32(&tmem_base_s)), "n"(BN) : "memory");
+    if (warp == 1) {                                     // TMEM: two accumulators of BN fp32 columns
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(g_smem_u32(&tmem_base_s)), "n"(2 * BN) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -125,14 +134,18 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     if (warp == 0) {
         if (lane == 0) {
             // ===== TMA producer =====
-            for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb % NST;
-                if (kb >= NST && !g_mbar_wait(&empty[s], ((kb / NST) - 1) & 1)) { abort_s = 1; break; }
-                unsigned char *sa = gsm + (size_t)s * STAGE, *sw = sa + W_OFF;
-                g_mbar_expect_tx(&full[s], A_BYTES + (SPLIT ? 2 : 1) * W_BYTES);
-                g_tma_load_2d(sa, &map_a, &full[s], kb * KELEMS, m0);
-                g_tma_load_2d(sw, &map_w, &full[s], kb * KELEMS, n0);
-                if (SPLIT) g_tma_load_2d(sw + W_BYTES, &map_wlo, &full[s], kb * KELEMS, n0);
+            int it = 0;
+            for (int t = blockIdx.x; t < ntiles && !abort_s; t += gridDim.x) {
+                const int m0 = (t / tiles_n) * G_BM, n0 = (t % tiles_n) * BN;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % NST;
+                    if (it >= NST && !g_mbar_wait(&empty[s], ((it / NST) - 1) & 1)) { abort_s = 1; break; }
+                    unsigned char *sa = gsm + (size_t)s * STAGE, *sw = sa + W_OFF;
+                    g_mbar_expect_tx(&full[s], A_BYTES + (SPLIT ? 2 : 1) * W_BYTES);
+                    g_tma_load_2d(sa, &map_a, &full[s], kb * KELEMS, m0);
+                    g_tma_load_2d(sw, &map_w, &full[s], kb * KELEMS, n0);
+                    if (SPLIT) g_tma_load_2d(sw + W_BYTES, &map_wlo, &full[s], kb * KELEMS, n0);
+                }
             }
         }
     } else if (warp == 1) {
@@ -142,79 +155,72 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             // both K-major, N >> 3 at bit 17, M >> 4 at bit 24
             const uint32_t fmt = TF32 ? 2u : 1u;
             const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(G_BM >> 4) << 24);
+            int it = 0, tc = 0;
             bool ok = true;
-            for (int kb = 0; kb < nkb && ok; ++kb) {
-                const int s = kb % NST;
-                ok = g_mbar_wait(SPLIT ? &conv[s] : &full[s], (kb / NST) & 1);      // SPLIT: the converter warps have written A_hi / A_lo
-                if (!ok) { abort_s = 1; break; }
+            for (int t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++tc) {
+                const int buf = tc & 1;
+                if (tc >= 2 && !g_mbar_wait(&tmem_empty[buf], ((tc >> 1) - 1) & 1)) { abort_s = 1; break; }   // the epilogue has drained it
                 tc_fence_after();
-                const uint32_t sa = g_smem_u32(gsm + (size_t)s * STAGE), sw = sa + W_OFF;
-                const uint64_t ad = umma_desc_k128(sa), wd = umma_desc_k128(sw);
+                const uint32_t acc = tmem_d + (uint32_t)(buf * BN);
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % NST;
+                    ok = g_mbar_wait(SPLIT ? &conv[s] : &full[s], (it / NST) & 1);      // SPLIT: the converter warps have written A_hi / A_lo
+                    if (!ok) { abort_s = 1; break; }
+                    tc_fence_after();
+                    const uint32_t sa = g_smem_u32(gsm + (size_t)s * STAGE), sw = sa + W_OFF;
+                    const uint64_t ad = umma_desc_k128(sa), wd = umma_desc_k128(sw);
 #pragma unroll
-                for (int k = 0; k < G_KBYTES / 32; ++k) {        // 32 bytes of K per instruction: +2 in the 16-byte address field
-                    if (SPLIT) {                                 // small terms first, then hi * hi
-                        const uint64_t ald = umma_desc_k128(sa + A_BYTES), wld = umma_desc_k128(sw + W_BYTES);
-                        tc_mma(tmem_d, ald + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, 1);
-                        tc_mma(tmem_d, ad + 2 * k, wld + 2 * k, idesc, 1, 1);
-                        tc_mma(tmem_d, ad + 2 * k, wd + 2 * k, idesc, 1, 1);
-                    } else {
-                        tc_mma(tmem_d, ad + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, TF32);
+                    for (int k = 0; k < G_KBYTES / 32; ++k) {    // 32 bytes of K per instruction: +2 in the 16-byte address field
+                        if (SPLIT) {                             // small terms first, then hi * hi
+                            const uint64_t ald = umma_desc_k128(sa + A_BYTES), wld = umma_desc_k128(sw + W_BYTES);
+                            tc_mma(acc, ald + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, 1);
+                            tc_mma(acc, ad + 2 * k, wld + 2 * k, idesc, 1, 1);
+                            tc_mma(acc, ad + 2 * k, wd + 2 * k, idesc, 1, 1);
+                        } else {
+                            tc_mma(acc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, TF32);
+                        }
                     }
+                    tc_commit(&empty[s]);                        // frees the stage when these MMAs have read it
                 }
-                tc_commit(&empty[s]);                            // frees the stage when these MMAs have read it
+                tc_commit(&tmem_full[buf]);                      // accumulator complete (or abort: release the epilogue)
             }
-            tc_commit(&tmem_full);                               // accumulator complete (or abort: release the epilogue)
         }
-    } else {
+    } else if (warp < 6) {
         // ===== epilogue: warps 2..5 own TMEM lanes 32 * (warp % 4) .. +31 =====
-        // Each warp stages its 32 rows x 128 bytes of output per chunk in shared memory (the pipeline stages are
-        // dead once tmem_full has fired), 128B-swizzled so that the 32 row-owning lanes hit distinct banks, and
-        // hands it to a TMA store: full 128-byte row segments leave the SM, rows / columns past the matrix
-        // edge are clipped by the hardware.  Two staging buffers per warp: the store of chunk c overlaps the
-        // TMEM read of chunk c + 1.
+        // Each warp stages its 32 rows x 128 bytes of output per chunk in its own shared-memory buffers, 128B-swizzled so
+        // that the 32 row-owning lanes hit distinct banks, and hands it to a TMA store: full 128-byte row segments leave
+        // the SM, rows / columns past the matrix edge are clipped by the hardware.  Two staging buffers per warp: the store
+        // of chunk c overlaps the TMEM read of chunk c + 1.
         const int q = warp & 3;
-        if (SPLIT) {
-            // ===== operand split (warps 2..5 = 128 threads): A -> A_hi (in place), A_lo, 16 KB per stage, elementwise =====
-            const int t = threadIdx.x - 64;
-            for (int kb = 0; kb < nkb; ++kb) {
-                const int s = kb % NST;
-                if (!g_mbar_wait(&full[s], (kb / NST) & 1)) { abort_s = 1; break; }
-                uint4 *pa = reinterpret_cast<uint4 *>(gsm + (size_t)s * STAGE), *pl = pa + A_BYTES / 16;
-#pragma unroll
-                for (int i = 0; i < A_BYTES / 16 / (G_THREADS - 64); ++i) {
-                    const uint4 v = pa[i * (G_THREADS - 64) + t];
-                    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-                    uint32_t hi[4], lo[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        hi[j] = w[j] & 0xffffe000u;                                       // the 19 bits kind::tf32 reads
-                        lo[j] = __float_as_uint(__fsub_rn(__uint_as_float(w[j]), __uint_as_float(hi[j])));   // exact
-                    }
-                    pa[i * (G_THREADS - 64) + t] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                    pl[i * (G_THREADS - 64) + t] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                }
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");             // generic-proxy writes -> tensor-core reads
-                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(g_smem_u32(&conv[s])) : "memory");
+        constexpr int CW = 128 / (int)sizeof(OT);            // output columns per 128-byte chunk: 32 fp32 / 64 bf16
+        unsigned char *stg = stg_base + (size_t)(warp - 2) * 2 * 4096;
+        const uint32_t sw = (uint32_t)(lane & 7);            // swizzle phase of this lane's staging row
+        int tc = 0, ci = 0, last_n0 = -1;
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tc) {
+            const int buf = tc & 1;
+            const int m0 = (t / tiles_n) * G_BM, n0 = (t % tiles_n) * BN;
+            if (n0 != last_n0) {                             // the tile's bias slice (changes only when tiles_n > 1)
+                asm volatile("bar.sync 1, 128;" ::: "memory");              // nobody still reads the previous slice
+                for (int i = threadIdx.x - 64; i < BN; i += 128) bias_s[i] = (bias && n0 + i < N) ? __ldg(bias + n0 + i) : 0.f;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                last_n0 = n0;
             }
-        }
-        const bool ok = g_mbar_wait(&tmem_full, 0);
-        tc_fence_after();
-        if (ok && !abort_s) {
-            constexpr int CW = 128 / (int)sizeof(OT);            // output columns per 128-byte chunk: 32 fp32 / 64 bf16
-            unsigned char *stg = gsm + (size_t)(warp - 2) * 2 * 4096;
-            const uint32_t sw = (uint32_t)(lane & 7);            // swizzle phase of this lane's staging row
+            const bool ok = g_mbar_wait(&tmem_full[buf], (tc >> 1) & 1);
+            tc_fence_after();
+            if (!ok || abort_s) break;
+            const uint32_t acc = tmem_d + (uint32_t)(buf * BN);
 #pragma unroll 1
-            for (int c0 = 0, ci = 0; c0 < BN; c0 += CW, ++ci) {
-                unsigned char *buf = stg + (ci & 1) * 4096;
+            for (int c0 = 0; c0 < BN; c0 += CW, ++ci) {
+                unsigned char *bufp = stg + (ci & 1) * 4096;
                 if (ci >= 2) {
                     if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
                     __syncwarp();
                 }
-                unsigned char *myrow = buf + lane * 128;
+                unsigned char *myrow = bufp + lane * 128;
 #pragma unroll
                 for (int h = 0; h < CW / 32; ++h) {
                     uint32_t r[32];
-                    const uint32_t taddr = tmem_d + ((uint32_t)(32 * q) << 16) + (uint32_t)(c0 + 32 * h);
+                    const uint32_t taddr = acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(c0 + 32 * h);
                     asm volatile(
                         "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
                         "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
@@ -240,28 +246,62 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                         for (int j = 0; j < 4; ++j) {
                             uint32_t w[4];
 #pragma unroll
-                            for (int t = 0; t < 4; ++t) {
-                                const __nv_bfloat162 hh = __floats2bfloat162_rn(v[8 * j + 2 * t], v[8 * j + 2 * t + 1]);
-                                w[t] = *reinterpret_cast<const uint32_t *>(&hh);
+                            for (int t2 = 0; t2 < 4; ++t2) {
+                                const __nv_bfloat162 hh = __floats2bfloat162_rn(v[8 * j + 2 * t2], v[8 * j + 2 * t2 + 1]);
+                                w[t2] = *reinterpret_cast<const uint32_t *>(&hh);
                             }
                             *reinterpret_cast<uint4 *>(myrow + ((((uint32_t)(4 * h + j)) ^ sw) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
                         }
                     }
                 }
+                if (c0 + CW >= BN) {                         // last TMEM read of this tile: hand the accumulator back to the MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(g_smem_u32(&tmem_empty[buf])) : "memory");
+                }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
                 if (lane == 0 && n0 + c0 < N) {
                     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
-                                 ::"l"(&map_c), "r"(g_smem_u32(buf)), "r"(n0 + c0), "r"(m0 + 32 * q) : "memory");
+                                 ::"l"(&map_c), "r"(g_smem_u32(bufp)), "r"(n0 + c0), "r"(m0 + 32 * q) : "memory");
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                } else if (lane == 0) {
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");      // keep the group count in step with `ci`
                 }
             }
-            if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // smem must outlive the stores that read it
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // smem must outlive the stores that read it
+    } else if (SPLIT) {
+        // ===== operand split (warps 6..9 = 128 threads): A -> A_hi (in place), A_lo, 16 KB per stage, elementwise =====
+        const int tdx = threadIdx.x - G_THREADS;
+        int it = 0;
+        bool ok = true;
+        for (int t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+                const int s = it % NST;
+                if (!g_mbar_wait(&full[s], (it / NST) & 1)) { abort_s = 1; ok = false; break; }
+                uint4 *pa = reinterpret_cast<uint4 *>(gsm + (size_t)s * STAGE), *pl = pa + A_BYTES / 16;
+#pragma unroll
+                for (int i = 0; i < A_BYTES / 16 / 128; ++i) {
+                    const uint4 v = pa[i * 128 + tdx];
+                    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        hi[j] = w[j] & 0xffffe000u;                                       // the 19 bits kind::tf32 reads
+                        lo[j] = __float_as_uint(__fsub_rn(__uint_as_float(w[j]), __uint_as_float(hi[j])));   // exact
+                    }
+                    pa[i * 128 + tdx] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                    pl[i * 128 + tdx] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");             // generic-proxy writes -> tensor-core reads
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(g_smem_u32(&conv[s])) : "memory");
+            }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(BN) : "memory");
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(2 * BN) : "memory");
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -290,14 +330,24 @@ static bool gemm_map(CUtensorMap *m, const void *base, int rows, int K, int ld, 
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+static int gemm_sm_count() {
+    static int n = [] {
+        int dev = 0, sms = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        return sms > 0 ? sms : 148;
+    }();
+    return n;
+}
+
 template <int BN, bool TF32, typename OT, bool SPLIT = false>
 static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUtensorMap &mwlo, const CUtensorMap &mc, const float *bias,
                        int M, int N, int K, int act, cudaStream_t st) {
-    const size_t smem = (SPLIT ? (size_t)2 * 2 : (size_t)G_STAGES) * (G_BM + BN) * G_KBYTES + 1024;
+    constexpr int NST = SPLIT ? 2 : (BN == 256 ? 3 : 4);
+    const size_t smem = (size_t)NST * (SPLIT ? 2 : 1) * (G_BM + BN) * G_KBYTES + 4 * 2 * 4096 + 1024;
     QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_bias_act_kernel<BN, TF32, OT, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (cdiv(M, G_BM) > 65535) return QUBER_E_UNSUPPORTED;
-    dim3 grid(cdiv(N, BN), cdiv(M, G_BM));
-    gemm_bias_act_kernel<BN, TF32, OT, SPLIT><<<grid, G_THREADS, smem, st>>>(ma, mw, mwlo, mc, bias, M, N, K, act);
+    const long long ntiles = (long long)cdiv(M, G_BM) * cdiv(N, BN);
+    const int grid = (int)(ntiles < gemm_sm_count() ? ntiles : gemm_sm_count());       // persistent: one CTA per SM
+    gemm_bias_act_kernel<BN, TF32, OT, SPLIT><<<grid, SPLIT ? G_THREADS + 128 : G_THREADS, smem, st>>>(ma, mw, mwlo, mc, bias, M, N, K, act);
     return check_launch("gemm_bias_act_kernel");
 }
 
@@ -330,7 +380,7 @@ extern "C" int quber_gemm_bias_act(const void *A, const void *W, const float *bi
     if (lda < K || ldw < K || ldc < N) return QUBER_E_INVALID;
     if (!aligned16(A) || !aligned16(W) || !aligned16(C) || ((size_t)lda * es) % 16 || ((size_t)ldw * es) % 16 || ((size_t)ldc * os) % 16)
         return QUBER_E_ALIGN;
-    const int BN = (N % 128 == 0 || N > 192) ? 128 : 64;
+    const int BN = (N % 256 == 0) ? 256 : ((N % 128 == 0 || N > 192) ? 128 : 64);    // 256: the whole row panel, A read once
     CUtensorMap ma, mw, mc;                 // C: 128-byte x 32-row boxes, one per epilogue warp and chunk
     if (!gemm_map(&ma, A, M, K, lda, G_BM, es) || !gemm_map(&mw, W, N, K, ldw, BN, es) || !gemm_map(&mc, C, M, N, ldc, 32, os)) {
         set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
@@ -338,7 +388,10 @@ extern "C" int quber_gemm_bias_act(const void *A, const void *W, const float *bi
     }
     cudaStream_t st = (cudaStream_t)stream;
 #define QG(BN_, TF_, OT_) return gemm_launch<BN_, TF_, OT_>(ma, mw, mw, mc, bias, M, N, K, act, st)
-    if (BN == 128) {
+    if (BN == 256) {
+        if (tf32) { if (out_dtype == 0) QG(256, true, float); else QG(256, true, __nv_bfloat16); }
+        else      { if (out_dtype == 0) QG(256, false, float); else QG(256, false, __nv_bfloat16); }
+    } else if (BN == 128) {
         if (tf32) { if (out_dtype == 0) QG(128, true, float); else QG(128, true, __nv_bfloat16); }
         else      { if (out_dtype == 0) QG(128, false, float); else QG(128, false, __nv_bfloat16); }
     } else {
@@ -366,7 +419,7 @@ extern "C" int quber_gemm_bias_act_x3(const float *A, const float *W_hi, const f
     if (!aligned16(A) || !aligned16(W_hi) || !aligned16(W_lo) || !aligned16(C) || ((size_t)lda * 4) % 16 || ((size_t)ldw * 4) % 16 ||
         ((size_t)ldc * os) % 16)
         return QUBER_E_ALIGN;
-    const int BN = (N % 128 == 0 || N > 192) ? 128 : 64;
+    const int BN = (N % 256 == 0) ? 256 : ((N % 128 == 0 || N > 192) ? 128 : 64);    // 256: A is read AND split once per row panel
     CUtensorMap ma, mw, mwl, mc;
     if (!gemm_map(&ma, A, M, K, lda, G_BM, 4) || !gemm_map(&mw, W_hi, N, K, ldw, BN, 4) || !gemm_map(&mwl, W_lo, N, K, ldw, BN, 4) ||
         !gemm_map(&mc, C, M, N, ldc, 32, os)) {
@@ -374,6 +427,10 @@ extern "C" int quber_gemm_bias_act_x3(const float *A, const float *W_hi, const f
         return QUBER_E_CUDA;
     }
     cudaStream_t st = (cudaStream_t)stream;
+    if (BN == 256) {
+        if (out_dtype == 0) return gemm_launch<256, true, float, true>(ma, mw, mwl, mc, bias, M, N, K, act, st);
+        return gemm_launch<256, true, __nv_bfloat16, true>(ma, mw, mwl, mc, bias, M, N, K, act, st);
+    }
     if (BN == 128) {
         if (out_dtype == 0) return gemm_launch<128, true, float, true>(ma, mw, mwl, mc, bias, M, N, K, act, st);
         return gemm_launch<128, true, __nv_bfloat16, true>(ma, mw, mwl, mc, bias, M, N, K, act, st);

@@ -137,7 +137,7 @@ class HotPath:
             pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
             st = dict(key=key, masks=torch.empty(shape, dtype=torch.uint8, device=dev),
                       head={k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in head_host.items()},
-                      h2d=torch.cuda.Stream(device=dev), d2h=torch.cuda.Stream(device=dev), free=None,
+                      h2d=torch.cuda.Stream(device=dev), h2d_bytes=torch.cuda.Stream(device=dev), d2h=torch.cuda.Stream(device=dev), free=None,
                       packed_host=pin((numel + 31) // 32, torch.int32),
                       packed_dev=torch.empty((numel + 31) // 32, dtype=torch.int32, device=dev), copied={},
                       graphs={}, bstatus=torch.zeros(B + 1, dtype=torch.int32, device=dev),
@@ -223,7 +223,19 @@ class HotPath:
                 c0 += n
         return out
 
-    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2, kernel_frames=0):
+    def byte_frames_rule(self, B):
+        """How many of the B frames travel as bytes through the copy engine WHILE the host threads bit-pack the others:
+        the dense masks have to be read from host DRAM once either way, so the two readers (DMA at ~55 GB/s, packing at
+        ~5 GB/s per thread up to ~60 GB/s) are run side by side and the frames are split in proportion to their rates.
+        Deterministic (a function of the thread count), nominal rates from profiles/r01_hostpack_v12.txt and the bench's
+        host_link figures."""
+        if not self.pack_masks:
+            return B
+        copy_gbs, pack_gbs = 55.0, min(5.0 * self.pack_threads, 60.0)
+        nb = int(round(B * copy_gbs / (copy_gbs + pack_gbs)))
+        return max(0, min(B, nb))
+
+    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2, kernel_frames=0, byte_frames=None):
         """The end-to-end call: host buffers in, host results out.
 
         masks_host: pinned uint8 [B,K,H,W]; head_host: dict of pinned float32 head outputs (what the
@@ -241,6 +253,8 @@ class HotPath:
         boundary kernels are launched once per group of consecutive chunks holding at least `kernel_frames` frames — full
         grids and one graph launch instead of one small launch sequence per chunk.  `keep` = per kernel group (encoding, per-instance boundaries,
         the batch's post-processing result, inst_start slice, inst_counts slice).
+        `byte_frames` (default: byte_frames_rule): the first that many frames go over the link as bytes on a second copy
+        stream while the host threads pack the rest — two readers of host DRAM instead of one.
         The host tensors are pinned and reused between calls; they are valid once the caller has synchronised
         the current stream (which this call makes wait for both copy streams).
         """
@@ -256,19 +270,24 @@ class HotPath:
         d2h.wait_stream(cur)                      # ... and whoever consumed the pinned results was ordered on `cur`
         keep = []
         frame_bytes = masks_host[0].numel()
-        sched = self.chunk_schedule(B, chunk_frames, min_tail)
         if self.pack_masks is None:
             if st["free"] is not None:
                 st["free"].synchronize()
-            self.pack_masks = self._calibrate_pack(masks_host, st, sched)
-        pack = self.pack_masks and frame_bytes % 32 == 0 and masks_host.is_contiguous()
+            self.pack_masks = self._calibrate_pack(masks_host, st, self.chunk_schedule(B, chunk_frames, min_tail))
+        pack = bool(self.pack_masks) and frame_bytes % 32 == 0 and masks_host.is_contiguous()
+        nb = B if not pack else (self.byte_frames_rule(B) if byte_frames is None else max(0, min(B, int(byte_frames))))
+        pack = pack and nb < B
+        byte_sched = self.chunk_schedule(nb, chunk_frames, chunk_frames) if nb else []
+        sched = [(nb + a, nb + b) for a, b in self.chunk_schedule(B - nb, chunk_frames, min_tail)] if nb < B else []
+        self.last_route = dict(byte_frames=nb, packed_frames=B - nb if pack else 0)
         if pack:
             # One bit per pixel over the host link (csrc/hostpack.cpp): the pool threads pack the chunks in order while
             # this thread enqueues copies and kernels of the chunks already packed.  The pinned words may still be read
             # by the previous call's copies: wait for those first.
             for ev in st["copied"].values():
                 ev.synchronize()
-            ops.host_pack_begin(masks_host, st["packed_host"], self.pack_threads, [c1 * frame_bytes for _, c1 in sched])
+            ops.host_pack_begin(masks_host[nb:], st["packed_host"][nb * frame_bytes // 32:], self.pack_threads,
+                                [(c1 - nb) * frame_bytes for _, c1 in sched])
         try:
             # Post-processing needs the head outputs only (20 MB): they go first and the whole batch is post-processed in
             # one launch sequence (full grids, one set of the small serial kernels) while the masks are packed / copied.
@@ -277,6 +296,19 @@ class HotPath:
                     st["head"][k].copy_(v, non_blocking=True)
                 heads_ready = h2d.record_event()
             st["copied"]["heads"] = heads_ready
+            bytes_ready = None
+            if byte_sched:
+                # the byte share of the masks: queued on its own copy stream at once, the copy engine reads host DRAM
+                # while the pool threads read (and pack) the other frames
+                h2b = st["h2d_bytes"]
+                if st["free"] is not None:
+                    h2b.wait_event(st["free"])
+                bytes_ready = []
+                with torch.cuda.stream(h2b):
+                    for (c0, c1) in byte_sched:
+                        st["masks"][c0:c1].copy_(masks_host[c0:c1], non_blocking=True)
+                        bytes_ready.append((c1, h2b.record_event()))
+                st["copied"]["bytes"] = bytes_ready[-1][1]
             cur.wait_event(heads_ready)
             r = self._run_graphed(st, "post", lambda: self.post(st["head"]))
             off = r["inst_offsets"]
@@ -291,6 +323,23 @@ class HotPath:
                 out["labels"].copy_(r["labels"][:B * slab], non_blocking=True)
                 out["scores"].copy_(r["scores"][:B * slab], non_blocking=True)
                 out["boxes"].copy_(r["boxes"][:B * slab], non_blocking=True)
+
+            def byte_groups():
+                """encode / boundary kernels of the byte share, in groups of `kernel_frames` frames (one group if 0)."""
+                step = kernel_frames if kernel_frames else chunk_frames
+                for g0 in range(0, nb, step):
+                    g1 = min(nb, g0 + step)
+                    cur.wait_event(next(ev for c1, ev in bytes_ready if c1 >= g1))   # copies are in stream order
+                    bs = st["bstatus"][g0:g0 + 1]
+                    enc, per, uni, fg = self._run_graphed(st, (g0, g1), lambda: self.encode_and_boundary(st["masks"][g0:g1], bs))
+                    done = cur.record_event()
+                    with torch.cuda.stream(d2h):
+                        d2h.wait_event(done)
+                        out["boundary"][g0:g1].copy_(uni, non_blocking=True)
+                    keep.append((enc, per, r, start[g0:g1], counts[g0:g1], g0))
+
+            if byte_sched and not sched:
+                byte_groups()
             pend = []                                 # chunks copied but not yet processed: (c0, c1, packed, value)
             for ci, (c0, c1) in enumerate(sched):
                 packed, value = False, -1
@@ -326,8 +375,11 @@ class HotPath:
                     with torch.cuda.stream(d2h):
                         d2h.wait_event(done)
                         out["boundary"][g0:g1].copy_(uni, non_blocking=True)
-                    keep.append((enc, per, r, start[g0:g1], counts[g0:g1]))
+                    keep.append((enc, per, r, start[g0:g1], counts[g0:g1], g0))
                 pend = []
+            if byte_sched and sched:
+                byte_groups()
+            keep.sort(key=lambda k: k[5])             # frame order, whatever order the groups were launched in
         except BaseException:
             if pack:
                 for c in range(len(sched)):           # the pool must not go on reading the caller's buffers
@@ -414,7 +466,7 @@ class HotPath:
             with torch.cuda.stream(d2h):
                 d2h.wait_event(done)
                 out["boundary"][g0:g1].copy_(uni, non_blocking=True)
-            keep.append((enc, per, r, start[g0:g1], counts[g0:g1]))
+            keep.append((enc, per, r, start[g0:g1], counts[g0:g1], g0))
         with torch.cuda.stream(d2h):
             d2h.wait_event(cur.record_event())
             out["rle_status"].copy_(rle_status, non_blocking=True)

@@ -77,8 +77,8 @@ def test_refine_batch_host_packed_mask_transfer_is_identical():
             s0, n = int(o0["inst_start"][b]), int(o0["inst_counts"][b])
             for key in ("labels", "scores", "boxes"):
                 assert torch.equal(o0[key][s0:s0 + n], o1[key][s0:s0 + n]), (key, b)
-        for a, b in zip(k0, k1):
-            assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])      # encoding and per-instance boundaries
+        for i in (0, 1):                                    # encoding and per-instance boundaries (group cuts differ by route)
+            assert torch.equal(torch.cat([k[i] for k in k0]), torch.cat([k[i] for k in k1]))
     hm = sets[0][0].clone().pin_memory()
     hm[3][hm[3] != 0] = 7                                   # frame 3 (chunk 2..3) carries a second value: byte copy
     hm[5, 2][hm[5, 2] != 0] = 9                             # two values inside one frame
@@ -86,8 +86,7 @@ def test_refine_batch_host_packed_mask_transfer_is_identical():
     o1, k1 = packed.refine_batch_host(hm, sets[0][1], chunk_frames=2)
     torch.cuda.current_stream().synchronize()
     assert torch.equal(packed._stage["masks"], hm.cuda())
-    for a, b in zip(k0, k1):
-        assert torch.equal(a[1], b[1])                      # boundary values follow the mask's own value (util.py:72-90)
+    assert torch.equal(torch.cat([k[1] for k in k0]), torch.cat([k[1] for k in k1]))   # boundary values follow the mask's own value (util.py:72-90)
     for src in (sets[1][0], (sets[1][0] != 0).to(torch.uint8)):            # 0/255 as the reference's eval makes them, and 0/1
         words, value = ops.host_pack_masks(src)
         assert value == int(src.max())
@@ -267,7 +266,7 @@ def test_refine_batch_host_kernel_groups_and_uint8_label_map(B, chunk, tail, kf,
         hp = HotPath(RefinerConfig(compact_label_map=True), "cuda")
         hp.pack_masks = pack
         for rep in range(3):
-            o1, k1 = hp.refine_batch_host(hm, hh, chunk_frames=chunk, min_tail=tail, kernel_frames=kf)
+            o1, k1 = hp.refine_batch_host(hm, hh, chunk_frames=chunk, min_tail=tail, kernel_frames=kf, byte_frames=0 if pack else None)
             torch.cuda.current_stream().synchronize()
         o0, k0 = ref.refine_batch_host(hm, hh, chunk_frames=chunk, min_tail=tail)
         torch.cuda.current_stream().synchronize()
@@ -284,7 +283,7 @@ def test_refine_batch_host_kernel_groups_and_uint8_label_map(B, chunk, tail, kf,
         hm2[1][hm2[1] != 0] = 7                              # chunk (0, 2) now carries two values: byte route for it
         hp = HotPath(RefinerConfig(compact_label_map=True), "cuda")
         hp.pack_masks = True
-        o1, k1 = hp.refine_batch_host(hm2, hh, chunk_frames=chunk, min_tail=tail, kernel_frames=kf)
+        o1, k1 = hp.refine_batch_host(hm2, hh, chunk_frames=chunk, min_tail=tail, kernel_frames=kf, byte_frames=0)
         o0, k0 = ref.refine_batch_host(hm2, hh, chunk_frames=chunk, min_tail=tail)
         torch.cuda.current_stream().synchronize()
         assert sum(k[0].shape[0] for k in k1) == B and len(k1) > len(sizes)
@@ -352,3 +351,34 @@ def test_custom_ops_compile_fullgraph_and_opcheck():
     w = torch.randn(192, 256, device="cuda")
     hi, lo = torch.ops.quber.split_tf32(w)
     torch.library.opcheck(torch.ops.quber.gemm_bias_act_x3.default, (a, hi, lo, None, True, False), test_utils=("test_schema", "test_faketensor"))
+
+
+@pytest.mark.parametrize("B,nb,kf", [(7, 3, 0), (7, 5, 4), (8, 8, 4), (6, 0, 2), (9, None, 4)])
+def test_refine_batch_host_hybrid_route_bytes_and_packed_side_by_side(B, nb, kf):
+    """The dense call reads the host masks with two readers at once: the first `byte_frames` frames go through the copy
+    engine as bytes while the pool threads bit-pack the others (HotPath.byte_frames_rule by default).  Same results as the
+    all-bytes call for every split, groups returned in frame order."""
+    K, H, W = 6, 240, 320
+    masks, head = _inputs(B, K, H, W, seed=810)
+    hm = torch.from_numpy(masks).pin_memory()
+    hh = {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}
+    ref = HotPath(RefinerConfig(compact_label_map=True), "cuda")
+    ref.pack_masks = False
+    o0, k0 = ref.refine_batch_host(hm, hh, chunk_frames=2)
+    torch.cuda.current_stream().synchronize()
+    o0 = {k: v.clone() for k, v in o0.items()}
+    e0, p0 = torch.cat([k[0] for k in k0]).clone(), torch.cat([k[1] for k in k0]).clone()
+    hp = HotPath(RefinerConfig(compact_label_map=True), "cuda")
+    hp.pack_masks = True
+    for rep in range(3):
+        o1, k1 = hp.refine_batch_host(hm, hh, chunk_frames=2, min_tail=1, kernel_frames=kf, byte_frames=nb)
+        torch.cuda.current_stream().synchronize()
+        HotPath.check_status(o1)
+        want_nb = hp.byte_frames_rule(B) if nb is None else nb
+        assert hp.last_route == dict(byte_frames=want_nb, packed_frames=B - want_nb if want_nb < B else 0)
+        assert [k[5] for k in k1] == sorted(k[5] for k in k1) and sum(k[0].shape[0] for k in k1) == B
+        for key in ("label_map", "boundary", "inst_start", "inst_counts"):
+            assert torch.equal(o0[key], o1[key]), key
+        assert torch.equal(torch.cat([k[0] for k in k1]), e0) and torch.equal(torch.cat([k[1] for k in k1]), p0)
+        assert torch.equal(hp._stage["masks"], hm.cuda())
+    assert 0 <= hp.byte_frames_rule(32) <= 32
