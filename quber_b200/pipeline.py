@@ -232,8 +232,8 @@ class HotPath:
         if not self.pack_masks:
             return B
         copy_gbs, pack_gbs = 55.0, min(5.0 * self.pack_threads, 60.0)
-        nb = int(round(B * copy_gbs / (copy_gbs + pack_gbs)))
-        return max(0, min(B, nb))
+        nb = int(round(B * copy_gbs / (copy_gbs + pack_gbs) / 4.0)) * 4 if B >= 8 else int(round(B * copy_gbs / (copy_gbs + pack_gbs)))
+        return max(0, min(B, nb))                 # multiples of 4 frames: even chunk sizes on both routes
 
     def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2, kernel_frames=0, byte_frames=None):
         """The end-to-end call: host buffers in, host results out.

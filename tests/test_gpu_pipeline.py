@@ -127,7 +127,7 @@ def test_refine_batch_host_full_size_c2_packed_graphs_equal_resident():
     r = ref.post({k: v.cuda() for k, v in hh.items()})
     offs = r["inst_offsets"].cpu().numpy()
     for rep in range(3):
-        out, keep = hp.refine_batch_host(hm, hh, chunk_frames=16, min_tail=8)
+        out, keep = hp.refine_batch_host(hm, hh, chunk_frames=16, min_tail=8, byte_frames=0)     # every frame bit-packed
         torch.cuda.current_stream().synchronize()
         assert [k[0].shape[0] for k in keep] == [16, 8, 8]
         assert torch.equal(hp._stage["masks"], hm.cuda())
