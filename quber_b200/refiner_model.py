@@ -1,11 +1,15 @@
 """Drop-in for the caller of the path, `eval/refiner_model.py::MaskRefiner` (:213-297): same constructor and the same
-`predict(...) -> (refined_masks [N,H,W] bool ndarray, output dict, seconds, fg_mask)` contract, with arrays instead of
-file paths (reading the PNG / NPY files stays with the caller, as does the optional LMFFNet foreground model).
+`predict(rgb_path, depth_path, initial_masks, fg_mask) -> (refined_masks [N,H,W] bool ndarray, output dict, seconds,
+fg_mask)` contract.  `rgb_path` / `depth_path` may be file paths (as in the reference: cv2.imread, np.load for '.npy',
+16-bit PNG otherwise) or the arrays themselves.
 
 What runs where:
+  * file reading, cv2.resize of the frame (:247-262) — host, OpenCV, exactly the reference's calls;
   * depth normalisation (`eval/preprocess_utils.py:12-28`) — `normalize_depth` below, numpy, as the reference;
-  * depth in-painting (`preprocess_utils.py:44-64`, cv2.inpaint TELEA) — NOT rebuilt: pass an in-painted depth image or a
-    callable `inpaint=`; it is CPU OpenCV code on the caller's side of the boundary in the reference as well;
+  * depth in-painting (`preprocess_utils.py:44-64`, cv2.inpaint TELEA) — `inpaint_depth` below: the reference's own
+    sequence of OpenCV calls on the host (fast-marching in-painting is a serial priority-queue algorithm on the caller's
+    side of the boundary; not rebuilt as a kernel).  `inpaint=` replaces it, `inpaint=False` skips it;
+  * the armbench mask resize, cv2.INTER_NEAREST per mask (:231) — `ops.resize_nearest` (GPU, bit-exact with OpenCV);
   * armbench resize rule `ResizeShortestEdge.get_output_shape(h, w, 800, 1333)` (:228) — `resize_shortest_edge_shape`;
   * the network + post-processing — `MaskRefinerPredictor.predict` (GPU);
   * the foreground-overlap filter `> 0.3` and the OCID zero-depth clear (:271-288) — `ops.filter_instances` (GPU,
@@ -42,31 +46,76 @@ def resize_shortest_edge_shape(h, w, short=800, max_size=1333):
     return int(newh + 0.5), int(neww + 0.5)
 
 
+def inpaint_depth(depth, factor=1, kernel_size=3, dilate=True):
+    """eval/preprocess_utils.py:44-64: fill the zero pixels of a normalised [H,W,3] uint8 depth image with OpenCV's TELEA
+    in-painting (host side, the reference's own call sequence)."""
+    import cv2
+    Hd, Wd, _ = depth.shape
+    small = cv2.resize(depth, (Wd // factor, Hd // factor))
+    mask = np.all(small == 0, axis=2).astype(np.uint8)
+    if dilate:
+        mask = cv2.dilate(mask, np.ones((kernel_size, kernel_size), np.uint8), iterations=1)
+    filled = cv2.resize(cv2.inpaint(small, mask, kernel_size, cv2.INPAINT_TELEA), (Wd, Hd))
+    return np.where(depth == 0, filled, depth)
+
+
+def _read_depth(path):
+    """:249-252: np.load for '.npy' (metres), imageio.imread otherwise (16-bit PNG, millimetres); OpenCV reads the same
+    PNG samples with IMREAD_UNCHANGED."""
+    if "npy" in path:
+        return np.load(path), True
+    import cv2
+    d = cv2.imread(path, cv2.IMREAD_UNCHANGED)
+    if d is None:
+        raise FileNotFoundError(path)
+    return d, False
+
+
 class MaskRefiner:
     def __init__(self, config_file, weights_file=None, dataset="OSD", precision="fp32", fg_model=None, inpaint=None):
-        """`fg_model(rgb, depth) -> [H,W] bool` replaces the reference's LMFFNet (:219, :269); `inpaint(depth_u8x3)`
-        replaces preprocess_utils.inpaint_depth (:264)."""
+        """`fg_model(rgb, depth) -> [H,W] bool` replaces the reference's LMFFNet (:219, :269; a separate foreground
+        network, out of this path's scope); `inpaint(depth_u8x3)` replaces `inpaint_depth` (:264), False skips it."""
         self.refiner_predictor = MaskRefinerPredictor(config_file, weights_file=weights_file, precision=precision)
         self.dataset = dataset
         self.fg_model = fg_model
-        self.inpaint = inpaint
+        self.inpaint = inpaint_depth if inpaint is None else (inpaint or None)
 
-    def predict(self, rgb_img, depth_img, initial_masks, fg_mask=None, depth_is_metres=False):
-        """rgb_img [H,W,3] uint8 (BGR as cv2.imread gives it); depth_img raw depth [H,W] (mm, or metres with
-        `depth_is_metres`, the reference's '.npy' branch :258-259) or None (armbench, RGB only);
-        initial_masks [N,H,W] bool | uint8.  Frames are expected at the working resolution (640x480, or the armbench
-        shape from `resize_shortest_edge_shape`) — resizing image files is the caller's job, as in the reference."""
+    def predict(self, rgb_path, depth_path, initial_masks, fg_mask=None, depth_is_metres=False):
+        """eval/refiner_model.py:224-297.  rgb_path: file path or [H,W,3] uint8 BGR array; depth_path: file path, raw
+        depth array [H,W] (mm; metres with `depth_is_metres` or a '.npy' path, :258-259) or None (armbench, RGB only);
+        initial_masks [N,h,w] bool | uint8.  Files are read and the frame resized as the reference does (:226-236,
+        :247-262); arrays are taken as they come (already at the working resolution)."""
+        rgb_img, depth_img = rgb_path, depth_path
+        from_files = isinstance(rgb_path, str)
         initial_masks = np.asarray(initial_masks)
         if initial_masks.dtype == bool:
-            initial_masks = np.uint8(initial_masks) * 255                                    # :236, :267
+            initial_masks = np.uint8(initial_masks) * 255                                    # :229-230, :266-267
+        if from_files:
+            import cv2
+            rgb_img = cv2.imread(rgb_path)
+            if rgb_img is None:
+                raise FileNotFoundError(rgb_path)
+            if self.dataset == "armbench":
+                h, w = resize_shortest_edge_shape(rgb_img.shape[0], rgb_img.shape[1], 800, 1333)          # :228
+                rgb_img = cv2.resize(rgb_img, (w, h))
+                if len(initial_masks) and initial_masks.shape[1:] != (h, w):                  # :231, cv2.INTER_NEAREST per mask
+                    initial_masks = ops.resize_nearest(torch.from_numpy(np.ascontiguousarray(initial_masks)).cuda(), (h, w))
+                depth_img = None
+            else:
+                rgb_img = cv2.resize(rgb_img, (W, H))                                        # :253
+                if isinstance(depth_path, str):
+                    depth_img, depth_is_metres = _read_depth(depth_path)
         zero_depth = None
         depth_u8 = None
         if depth_img is not None and self.dataset != "armbench":
             raw = np.asarray(depth_img)
             zero_depth = raw == 0                                                            # :255
             depth_u8 = normalize_depth(raw.astype(np.float32), 0.25, 1.5) if depth_is_metres else normalize_depth(raw.astype(np.float32))
+            if from_files:
+                import cv2
+                depth_u8 = cv2.resize(depth_u8, (W, H), interpolation=cv2.INTER_NEAREST)     # :262
             if self.inpaint is not None:
-                depth_u8 = self.inpaint(depth_u8)
+                depth_u8 = self.inpaint(depth_u8)                                            # :264
         start = time.time()
         output = self.refiner_predictor.predict(rgb_img, depth_u8, initial_masks)[0]
         if "instances" not in output:
@@ -75,7 +124,7 @@ class MaskRefiner:
         if self.dataset == "armbench":
             return masks.cpu().numpy(), output, time.time() - start, None                    # :239-246
         if self.fg_model is not None:
-            fg_mask = self.fg_model(rgb_img, depth_img)                                      # :269
+            fg_mask = self.fg_model(rgb_path, depth_path)                                    # :269 (lmffnet.predict takes the paths)
         if fg_mask is None and self.dataset != "OCID":
             return masks.cpu().numpy(), output, time.time() - start, fg_mask
         n = masks.shape[0]

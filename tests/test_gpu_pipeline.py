@@ -382,3 +382,48 @@ def test_refine_batch_host_hybrid_route_bytes_and_packed_side_by_side(B, nb, kf)
         assert torch.equal(torch.cat([k[0] for k in k1]), e0) and torch.equal(torch.cat([k[1] for k in k1]), p0)
         assert torch.equal(hp._stage["masks"], hm.cuda())
     assert 0 <= hp.byte_frames_rule(32) <= 32
+
+
+def test_refiner_adapter_takes_file_paths_like_the_reference(tmp_path):
+    """eval/refiner_model.py:224-297 takes PATHS: frames are read with OpenCV, resized to 640x480 (depth: nearest), the
+    depth normalised and in-painted (cv2 TELEA, the reference's own calls); armbench frames go to 750x1333 and the masks
+    through the nearest-neighbour resize kernel."""
+    import cv2
+    from quber_b200.meta_arch import Instances
+    from quber_b200.refiner_model import MaskRefiner, inpaint_depth, normalize_depth
+    rng = np.random.default_rng(5)
+    rgb = rng.integers(0, 255, (240, 320, 3), dtype=np.uint8)
+    depth = rng.integers(300, 1400, (240, 320)).astype(np.uint16)
+    depth[rng.random((240, 320)) < 0.05] = 0
+    cv2.imwrite(str(tmp_path / "rgb.png"), rgb)
+    cv2.imwrite(str(tmp_path / "depth.png"), depth)
+    np.save(str(tmp_path / "depth_m.npy"), depth.astype(np.float32) / 1000.0)
+    seen = {}
+
+    class Stub:
+        def predict(self, rgb_img, dep, init):
+            seen.update(rgb=rgb_img, dep=dep, init=init)
+            H_, W_ = rgb_img.shape[:2]
+            return [{"instances": Instances((H_, W_), pred_masks=torch.zeros((1, H_, W_), dtype=torch.bool, device="cuda"))}]
+
+    masks = np.zeros((2, 480, 640), bool); masks[0, 100:200, 100:200] = True
+    r = MaskRefiner.__new__(MaskRefiner)
+    r.refiner_predictor, r.dataset, r.fg_model, r.inpaint = Stub(), "OSD", None, inpaint_depth
+    r.predict(str(tmp_path / "rgb.png"), str(tmp_path / "depth.png"), masks, fg_mask=None)
+    assert seen["rgb"].shape == (480, 640, 3) and np.array_equal(seen["rgb"], cv2.resize(rgb, (640, 480)))
+    want = cv2.resize(normalize_depth(depth.astype(np.float32)), (640, 480), interpolation=cv2.INTER_NEAREST)
+    mask = cv2.dilate(np.all(want == 0, axis=2).astype(np.uint8), np.ones((3, 3), np.uint8), iterations=1)
+    want = np.where(want == 0, cv2.inpaint(want, mask, 3, cv2.INPAINT_TELEA), want)
+    assert np.array_equal(seen["dep"], want) and (seen["dep"] > 0).mean() > 0.99
+    assert seen["init"].dtype == np.uint8 and seen["init"].max() == 255
+    r.predict(str(tmp_path / "rgb.png"), str(tmp_path / "depth_m.npy"), masks, fg_mask=None)         # metres branch (:258-259)
+    assert seen["dep"].shape == (480, 640, 3) and abs(int(seen["dep"][100, 100, 0]) - int(want[100, 100, 0])) <= 1
+    # armbench: 1080 x 1920 -> 750 x 1333, masks by cv2.INTER_NEAREST on the GPU
+    big = rng.integers(0, 255, (1080, 1920, 3), dtype=np.uint8)
+    cv2.imwrite(str(tmp_path / "big.png"), big)
+    bm = np.zeros((3, 1080, 1920), bool); bm[0, 200:700, 300:900] = True; bm[1, ::7, ::5] = True
+    r.dataset = "armbench"
+    r.predict(str(tmp_path / "big.png"), None, bm, None)
+    assert seen["rgb"].shape == (750, 1333, 3) and seen["dep"] is None
+    ref_m = np.array([cv2.resize(m, (1333, 750), interpolation=cv2.INTER_NEAREST) for m in np.uint8(bm) * 255])
+    assert np.array_equal(seen["init"].cpu().numpy(), ref_m)

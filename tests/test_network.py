@@ -273,3 +273,23 @@ MODEL:
     cfg2.MODEL.DEVICE = "cpu"
     m2 = build_model(cfg2)
     assert m2.ins_embed_head.pixel_decoder is None and any(k.startswith("ins_embed_head.decoder.") for k in m2.state_dict())
+
+
+def test_inpaint_depth_equals_the_reference_function():
+    """eval/preprocess_utils.py:44-64 executed from /root/reference (build container) against refiner_model.inpaint_depth."""
+    import os
+    import importlib.util
+    path = "/root/reference/eval/preprocess_utils.py"
+    if not os.path.exists(path):
+        pytest.skip("reference checkout not present (GPU box)")
+    import numpy as np
+    from quber_b200.refiner_model import inpaint_depth, normalize_depth
+    spec = importlib.util.spec_from_file_location("ref_preprocess_utils", path)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    rng = np.random.default_rng(2)
+    d = rng.uniform(200, 1600, (120, 160)).astype(np.float32)
+    d[rng.random((120, 160)) < 0.06] = 0
+    a = normalize_depth(d)
+    assert np.array_equal(a, ref.normalize_depth(d.copy()))
+    assert np.array_equal(inpaint_depth(a), ref.inpaint_depth(a.copy()))
