@@ -227,14 +227,20 @@ class MSDeformAttnTransformerEncoderOnly(nn.Module):
 
     def forward(self, srcs, pos_embeds):
         # masks are all-False in the reference (msdeformattn.py:62), so every valid ratio is exactly 1
-        src_flatten, lvl_pos, host_shapes = [], [], []
-        for lvl, (src, pos_embed) in enumerate(zip(srcs, pos_embeds)):
+        src_flatten, host_shapes = [], []
+        for lvl, src in enumerate(srcs):
             bs, c, h, w = src.shape
             host_shapes.append((h, w))
-            src_flatten.append(src.flatten(2).transpose(1, 2))
-            lvl_pos.append(pos_embed.flatten(2).transpose(1, 2) + self.level_embed[lvl].view(1, 1, -1))
+            src_flatten.append(src.flatten(2).transpose(1, 2))       # a view for channels-last sources: the cat is one copy
         src_flatten = torch.cat(src_flatten, 1)
-        lvl_pos = torch.cat(lvl_pos, 1)
+        # position + level embedding (msdeformattn.py:70-72) depends only on the level shapes and the level_embed
+        # parameter: built once per (sources' identity, parameter version), not per forward
+        key = tuple((p.data_ptr(), p._version, tuple(p.shape)) for p in pos_embeds) + ((self.level_embed.data_ptr(), self.level_embed._version),)
+        cache = self.__dict__.get("_lvl_pos")
+        if cache is None or cache[0] != key:
+            lvl_pos = torch.cat([p.flatten(2).transpose(1, 2) + self.level_embed[l].view(1, 1, -1) for l, p in enumerate(pos_embeds)], 1)
+            cache = self.__dict__["_lvl_pos"] = (key, lvl_pos.contiguous())
+        lvl_pos = cache[1]
         spatial_shapes = torch.as_tensor(host_shapes, dtype=torch.long, device=src_flatten.device)
         level_start_index = torch.cat((spatial_shapes.new_zeros((1,)), spatial_shapes.prod(1).cumsum(0)[:-1]))
         valid_ratios = torch.ones((src_flatten.shape[0], len(srcs), 2), dtype=torch.float32, device=src_flatten.device)
