@@ -54,7 +54,7 @@ class HotPath:
         self.device = torch.device(device)
         self.launches_per_step = 0
         # host-buffer path: send the 0/1 masks as one bit per pixel (csrc/hostpack.cpp).  QUBER_PACK_MASKS=0|1 overrides.
-        # None = decide on the first call by timing both routes on this host (_calibrate_pack).
+        # None ("auto") = decide on the first call by timing both routes on this host (_calibrate_pack).
         self.use_graphs = os.environ.get("QUBER_E2E_GRAPHS", "1") == "1"   # host-buffer path: one CUDA graph per chunk
         # this rank's share of the box's cores (torchrun exports LOCAL_WORLD_SIZE), two left for the launching threads
         cores = len(os.sched_getaffinity(0)) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
