@@ -334,44 +334,85 @@ def run_ours(args):
     E2E_TAIL = int(os.environ.get("QUBER_E2E_TAIL", "2"))
     E2E_KERNEL = int(os.environ.get("QUBER_E2E_KERNEL_FRAMES", "16"))
 
-    def gather_host_call(keep):
-        if world > 1:                                          # the call's label maps are the graph pool's: one D2D copy into the payload
-            payload.maps.copy_(keep[0][2]["label_map"])
-            payload.counts.copy_(torch.cat([k[4] for k in keep]))
-            payload.gather()
+    # host calls: one payload per slot, the collective on the side stream (ranks are not made to meet on the main stream;
+    # a slot's payload is rewritten two calls later, after its gather has read it)
+    payloads_e2e = [sharding.Payload(B, g["Ho"], g["Wo"], dev, world) for _ in range(2)] if world > 1 else []
+    gathered = [None, None]
 
-    def e2e_dense(i):
+    def gather_host_call(keep, slot):
+        if world > 1:
+            p = payloads_e2e[slot]
+            cur = torch.cuda.current_stream()
+            if gathered[slot] is not None:
+                cur.wait_event(gathered[slot])
+            p.maps.copy_(keep[0][2]["label_map"])              # the call's label maps are the graph pool's: one D2D copy
+            p.counts.copy_(torch.cat([k[4] for k in keep]))
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                p.gather()
+                gathered[slot] = side.record_event()
+
+    def e2e_dense(i, slot=0, async_result=False):
         d = sets[i % NSETS]
         # decoder activations never live on the host (resident inputs); launched first so the sampling kernels run
         # under the host-side packing / host->device copies of refine_batch_host's chunk pipeline
         hp.msda_layers(d["msda"], N_LAYERS)
-        o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL, kernel_frames=E2E_KERNEL)
+        o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL, kernel_frames=E2E_KERNEL,
+                                       slot=slot, async_result=async_result)
         hp.last_route_dense = dict(hp.last_route)
-        gather_host_call(keep)
+        gather_host_call(keep, slot)
         return o
 
-    def e2e_rle(i):
+    def e2e_rle(i, slot=0, async_result=False):
         d = sets[i % NSETS]
         hp.msda_layers(d["msda"], N_LAYERS)
         o, keep = hp.refine_batch_rle(d["h_rle_counts"], d["h_rle_offsets"], (B, K, H, Wp), d["h_head"], value=255,
-                                      kernel_frames=E2E_KERNEL)
-        gather_host_call(keep)
+                                      kernel_frames=E2E_KERNEL, slot=slot, async_result=async_result)
+        gather_host_call(keep, slot)
         return o
 
-    def time_e2e(fn):
-        for i in range(max(1, min(args.warmup, 3))):
-            o = fn(i)
+    E2E_DEPTH = 2 if os.environ.get("QUBER_E2E_DEPTH", "2") != "1" else 1
+
+    def time_e2e(fn, depth=E2E_DEPTH):
+        """K host calls, every one with its host->device copies and the device->host read of its results inside the timed
+        region.  depth 1: the host reads call i's results before it issues call i+1.  depth 2 (default): the caller keeps
+        two calls in flight on alternating slots — call i+1 is issued (its packing, copies and kernels queued) before the
+        results of call i are read, so the copies of one call run under the kernels of the other; every call's results
+        are still read and checked on the host inside the timed region."""
+        for i in range(max(2, min(args.warmup, 3))):
+            fn(i, i % depth, depth > 1)
+            o = hp.wait_result(i % depth)
+        torch.cuda.synchronize()
         barrier()
         n_steps = max(2, min(steps, 10))
         e0 = _ev()
         inst = 0
-        for i in range(n_steps):
-            o = fn(i)
-            torch.cuda.current_stream().synchronize()          # the caller reads the host result of every step
+        pending = []
+        host = dict(issue=0.0, wait=0.0)
+
+        def collect():
+            nonlocal inst
+            t = time.perf_counter()
+            o = hp.wait_result(pending.pop(0))                 # the caller reads the host result of every step
+            host["wait"] += time.perf_counter() - t
             HotPath.check_status(o)
             inst += int(o["inst_counts"].sum())
+            return o
+        for i in range(n_steps):
+            t = time.perf_counter()
+            fn(i, i % depth, depth > 1)
+            host["issue"] += time.perf_counter() - t
+            pending.append(i % depth)
+            if len(pending) >= depth:
+                o = collect()
+        while pending:
+            o = collect()
+        if world > 1:
+            torch.cuda.current_stream().wait_stream(side)      # the last gather is inside the timed region
+        torch.cuda.current_stream().synchronize()
         e1 = _ev()
         barrier()
+        time_e2e.host_ms = {k: v * 1e3 / n_steps for k, v in host.items()}
         t_ms = e0.elapsed_time(e1)
         if world > 1:
             t = torch.tensor([t_ms, float(inst)], device=dev, dtype=torch.float64)
@@ -382,7 +423,11 @@ def run_ours(args):
         return inst / (t_ms * 1e-3), t_ms / n_steps, n_steps, d2h
 
     e2e_val, e2e_ms, e2e_steps, d2h = time_e2e(e2e_dense)
+    e2e_host = dict(time_e2e.host_ms)
     rle_val, rle_ms, _, _ = time_e2e(e2e_rle)
+    rle_host = dict(time_e2e.host_ms)
+    _, e2e_ms_sync, _, _ = time_e2e(e2e_dense, 1) if E2E_DEPTH > 1 else (0, e2e_ms, 0, 0)
+    _, rle_ms_sync, _, _ = time_e2e(e2e_rle, 1) if E2E_DEPTH > 1 else (0, rle_ms, 0, 0)
     packed = bool(hp.pack_masks)
     head_bytes = sum(v.numel() * 4 for v in sets[0]["h_head"].values())
     route = getattr(hp, "last_route_dense", dict(byte_frames=B, packed_frames=0))
@@ -454,6 +499,8 @@ def run_ours(args):
         "data": "synthetic", "config": workload_config(name, world), "clocks": clocks,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms, "steps": e2e_steps, "host_link": pcie,
+                "calls_in_flight": E2E_DEPTH, "ms_per_step_one_call_in_flight": e2e_ms_sync,
+                "host_ms_per_step": e2e_host,
                 "input": "dense uint8 masks [B,K,H,W] in pinned host memory (MaskRefinerPredictor.predict's contract)",
                 "mask_transfer": ("%d frames as bytes through the copy engine while %d host threads bit-pack the other %d (one bit per pixel), "
                                   "inside the timed region" % (route["byte_frames"], hp.pack_threads, route["packed_frames"])) if packed
@@ -465,7 +512,8 @@ def run_ours(args):
                                                         sets[0]["h_masks"].numel() / (pcie.get("host_pack_gbs", 1e9) * 1e9) * 1e3)
                          else "kernels",
                 "schedule": {"chunk_frames": E2E_CHUNK, "min_tail": E2E_TAIL, "kernel_frames": E2E_KERNEL, "label_map": "uint8"}},
-        "e2e_rle": {"value": rle_val, "unit": UNIT, "ms_per_step": rle_ms, "h2d_bytes_per_step": int(h2d_rle),
+        "e2e_rle": {"value": rle_val, "unit": UNIT, "ms_per_step": rle_ms, "calls_in_flight": E2E_DEPTH,
+                    "ms_per_step_one_call_in_flight": rle_ms_sync, "host_ms_per_step": rle_host, "h2d_bytes_per_step": int(h2d_rle),
                     "d2h_bytes_per_step": int(d2h), "graphs": bool(hp.use_graphs),
                     "input": "the same masks as COCO RLE counts (register_uoais_sim_panoptic.py:121-144) in pinned host memory, "
                              "decoded on the device by quber_rle_decode",

@@ -120,14 +120,16 @@ class HotPath:
     LAUNCHES = dict(encode=2, boundary=1, post=8, msda_layer=1)
 
     # --- end to end: host buffers in, host results out ------------------------------------------
-    def _staging(self, masks_host, head_host):
-        return self._staging_shape(tuple(masks_host.shape), head_host)
+    def _staging(self, masks_host, head_host, slot=0):
+        return self._staging_shape(tuple(masks_host.shape), head_host, slot)
 
-    def _staging_shape(self, shape, head_host):
-        """Persistent device staging buffers, pinned result buffers, copy streams and events, keyed by shape."""
+    def _staging_shape(self, shape, head_host, slot=0):
+        """Persistent device staging buffers, pinned result buffers, copy streams and events, keyed by shape; one set per
+        `slot` (a caller that keeps two calls in flight alternates between two slots)."""
         ldt = torch.uint8 if self.cfg.compact_label_map and self.cfg.top_k <= 255 else torch.int32
         key = (tuple(shape), ldt) + tuple((k, tuple(v.shape)) for k, v in sorted(head_host.items()))
-        st = getattr(self, "_stage", None)
+        stages = self.__dict__.setdefault("_stages", {})
+        st = stages.get(slot)
         if st is None or st["key"] != key:
             dev = self.device
             B, K, H, W = shape
@@ -148,8 +150,21 @@ class HotPath:
                                boxes=pin((B * slab, 4), torch.float32)))
             for k in ("status", "rle_status", "boundary_status"):
                 st["out"][k].zero_()
-            self._stage = st
+            st["ready"] = None
+            stages[slot] = st
         return st
+
+    @property
+    def _stage(self):
+        return self._stages[0]
+
+    def wait_result(self, slot=0):
+        """Block until the host results of the last call on `slot` are complete (all its device->host copies done) and
+        return them — the counterpart of `async_result=True`."""
+        st = self._stages[slot]
+        if st["ready"] is not None:
+            st["ready"].synchronize()
+        return st["out"]
 
     def _run_graphed(self, st, key, body):
         """`body()` (kernel launches on the current stream, inputs = the persistent staging buffers) eagerly, or with
@@ -235,7 +250,8 @@ class HotPath:
         nb = int(round(B * copy_gbs / (copy_gbs + pack_gbs) / 4.0)) * 4 if B >= 8 else int(round(B * copy_gbs / (copy_gbs + pack_gbs)))
         return max(0, min(B, nb))                 # multiples of 4 frames: even chunk sizes on both routes
 
-    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2, kernel_frames=0, byte_frames=None):
+    def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2, kernel_frames=0, byte_frames=None,
+                          slot=0, async_result=False):
         """The end-to-end call: host buffers in, host results out.
 
         masks_host: pinned uint8 [B,K,H,W]; head_host: dict of pinned float32 head outputs (what the
@@ -257,9 +273,14 @@ class HotPath:
         stream while the host threads pack the rest — two readers of host DRAM instead of one.
         The host tensors are pinned and reused between calls; they are valid once the caller has synchronised
         the current stream (which this call makes wait for both copy streams).
+        Two calls in flight: with `async_result=True` the current stream is NOT made to wait for the device->host copies
+        (the next call's kernels start right behind this call's); the results are complete after `wait_result(slot)`.
+        A caller that alternates `slot` between 0 and 1 has the copies and the host-side packing of call i+1 running under
+        the kernels of call i; each slot has its own staging buffers, pinned results and graphs, and call i+2 on a slot
+        must not be issued before the results of call i on it have been read.
         """
         dev = self.device
-        st = self._staging(masks_host, head_host)
+        st = self._staging(masks_host, head_host, slot)
         out = st["out"] if out_host is None else out_host
         cur = torch.cuda.current_stream(dev)
         h2d, d2h = st["h2d"], st["d2h"]
@@ -388,9 +409,11 @@ class HotPath:
         with torch.cuda.stream(d2h):
             d2h.wait_event(cur.record_event())
             out["boundary_status"].copy_(st["bstatus"], non_blocking=True)     # non-zero: a TMA load was lost, see check_status
+            st["ready"] = d2h.record_event()
         st["free"] = cur.record_event()
-        cur.wait_stream(d2h)
-        self._keep = keep                         # device results stay alive until the next call replaces them
+        if not async_result:
+            cur.wait_stream(d2h)
+        self.__dict__.setdefault("_keeps", {})[slot] = keep    # device results stay alive until the slot's next call replaces them
         return out, keep
 
     @staticmethod
@@ -404,18 +427,20 @@ class HotPath:
         if "rle_status" in out and int(out["rle_status"][0]) & 1:
             raise ValueError("quber_rle_decode: RLE counts do not sum to H*W")
 
-    def refine_batch_rle(self, counts_host, offsets_host, shape, head_host, value=255, out_host=None, kernel_frames=16):
+    def refine_batch_rle(self, counts_host, offsets_host, shape, head_host, value=255, out_host=None, kernel_frames=16,
+                         slot=0, async_result=False):
         """The end-to-end call with the initial masks in the form the reference's datasets hold them: COCO run-length
         encodings (register_uoais_sim_panoptic.py:121-144 -> mask_util.decode at
         perturbed_panoptic_dataset_mapper.py:195-214).  counts_host: pinned int32 [total] (uint32 run lengths of the
         B*K masks back to back, `rle.pack_rles`), offsets_host: pinned int64 [B*K+1], shape = (B, K, H, W); head_host as
         refine_batch_host.  ~0.6 MB cross the host link instead of 295 MB (C2): quber_rle_decode writes the bit-packed
-        planes that the encode pass reads anyway.  Same results and result layout as refine_batch_host."""
+        planes that the encode pass reads anyway.  Same results and result layout as refine_batch_host; `slot` /
+        `async_result` as there."""
         dev = self.device
         B, K, H, W = shape
         if W % 32:
             raise ValueError("refine_batch_rle needs W % 32 == 0 (decode the RLEs with ops.rle_decode and use the dense call)")
-        st = self._staging_shape((B, K, H, W), head_host)
+        st = self._staging_shape((B, K, H, W), head_host, slot)
         out = st["out"] if out_host is None else out_host
         cur = torch.cuda.current_stream(dev)
         h2d, d2h = st["h2d"], st["d2h"]
@@ -471,7 +496,9 @@ class HotPath:
             d2h.wait_event(cur.record_event())
             out["rle_status"].copy_(rle_status, non_blocking=True)
             out["boundary_status"].copy_(st["bstatus"], non_blocking=True)
+            st["ready"] = d2h.record_event()
         st["free"] = cur.record_event()
-        cur.wait_stream(d2h)
-        self._keep = keep
+        if not async_result:
+            cur.wait_stream(d2h)
+        self.__dict__.setdefault("_keeps", {})[slot] = keep
         return out, keep

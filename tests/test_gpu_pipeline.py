@@ -427,3 +427,44 @@ def test_refiner_adapter_takes_file_paths_like_the_reference(tmp_path):
     assert seen["rgb"].shape == (750, 1333, 3) and seen["dep"] is None
     ref_m = np.array([cv2.resize(m, (1333, 750), interpolation=cv2.INTER_NEAREST) for m in np.uint8(bm) * 255])
     assert np.array_equal(seen["init"].cpu().numpy(), ref_m)
+
+
+@pytest.mark.parametrize("route", ["dense", "rle"])
+def test_two_host_calls_in_flight_on_alternating_slots(route):
+    """slot / async_result: call i+1 is issued before the results of call i are read (its copies and packing run under
+    call i's kernels).  Six calls on two different input sets, alternating slots; every call's host results equal the
+    one-call-at-a-time results of the same input bit for bit."""
+    from quber_b200 import rle
+    B, K, H, W = 6, 9, 240, 320
+    data = []
+    for seed in (810, 811):
+        masks, head = _inputs(B, K, H, W, seed=seed)
+        hm = torch.from_numpy(masks).pin_memory()
+        hh = {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}
+        rles = [{"size": [H, W], "counts": oracle.rle_to_string(oracle.rle_encode(m))} for m in masks.reshape(-1, H, W)]
+        counts, offsets, _ = rle.pack_rles(rles)
+        data.append((hm, hh, torch.from_numpy(counts).pin_memory(), torch.from_numpy(offsets).pin_memory()))
+    keys = ("label_map", "boundary", "inst_start", "inst_counts", "status", "boundary_status")
+    one = HotPath(RefinerConfig(), "cuda")
+    want = []
+    for hm, hh, hc, ho in data:
+        o, _ = one.refine_batch_host(hm, hh, chunk_frames=2, kernel_frames=4)
+        torch.cuda.current_stream().synchronize()
+        want.append({k: o[k].clone() for k in keys})
+    two = HotPath(RefinerConfig(), "cuda")
+
+    def submit(i):
+        hm, hh, hc, ho = data[i % 2]
+        if route == "dense":
+            two.refine_batch_host(hm, hh, chunk_frames=2, kernel_frames=4, slot=i % 2, async_result=True)
+        else:
+            two.refine_batch_rle(hc, ho, (B, K, H, W), hh, value=255, kernel_frames=4, slot=i % 2, async_result=True)
+    submit(0)
+    for i in range(1, 7):
+        if i < 6:
+            submit(i)                                       # call i in flight before call i-1's results are read
+        o = two.wait_result((i - 1) % 2)
+        HotPath.check_status(o)
+        for k in keys:
+            assert torch.equal(o[k], want[(i - 1) % 2][k]), (i - 1, k)
+    assert two._stages[0]["masks"].data_ptr() != two._stages[1]["masks"].data_ptr()
