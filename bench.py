@@ -260,9 +260,9 @@ def run_ours(args):
         d = sets[i % NSETS]
         mark = (lambda: None) if evs is None else (lambda: evs.append(_ev()))
         mark()
-        enc = ops.encode_initial_masks(d["masks"], hp.cfg.sigma, hp.cfg.valid_w)
+        enc, occ = ops.encode_initial_masks(d["masks"], hp.cfg.sigma, hp.cfg.valid_w, with_occupancy=True)
         mark()
-        per, uni, fg = ops.mask_boundary(d["masks"], d_bnd)
+        per, uni, fg = ops.mask_boundary(d["masks"], d_bnd, occupancy=occ)
         mark()
         hp.msda_layers(d["msda"], N_LAYERS)
         mark()

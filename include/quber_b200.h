@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define QUBER_ABI_VERSION 2
+#define QUBER_ABI_VERSION 3
 
 enum {
     QUBER_OK = 0,
@@ -65,15 +65,21 @@ const char *quber_last_cuda_error(void);
  * ------------------------------------------------------------------------------------------- */
 void quber_gaussian_table(int sigma, float *host_table);
 size_t quber_encode_workspace_bytes(int B, int K, int H, int W);
+/* occupancy (optional, NULL = not wanted): dev uint8 [B][K][ceil(H/16)][ceil(W/128)], quber_occupancy_bytes() bytes —
+ * 1 where the 128 x 16 pixel tile holds a set pixel of mask k.  A by-product of the pass that reads every mask byte;
+ * quber_mask_boundary takes it to skip the (tile, plane) pairs that have no mask pixel nearby (87 % of them at C2). */
+#define QUBER_OCC_TILE_W 128
+#define QUBER_OCC_TILE_H 16
+size_t quber_occupancy_bytes(int B, int K, int H, int W);
 int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int valid_w, int sigma,
-                               const float *gauss, float *out, void *workspace, size_t workspace_bytes,
+                               const float *gauss, float *out, uint8_t *occupancy, void *workspace, size_t workspace_bytes,
                                void *stream);
 /* The same from bit-packed masks (quber_host_pack_masks): packed dev uint32 [B*K*H*W / 32], set pixels carry `value`
  * (1..255).  Also writes the byte planes masks_out dev [B,K,H,W] uint8 (0 / value) — what quber_unpack_masks would give —
  * for quber_mask_boundary, so the expansion costs no pass of its own. */
 int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t *masks_out, int B, int K, int H, int W,
-                                      int valid_w, int sigma, const float *gauss, float *out, void *workspace,
-                                      size_t workspace_bytes, void *stream);
+                                      int valid_w, int sigma, const float *gauss, float *out, uint8_t *occupancy,
+                                      void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K2  boundary extraction by erosion — replaces mask_to_boundary / masks_to_boundary /
@@ -84,6 +90,9 @@ int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t
  *   per_instance  dev [B,K,H,W] uint8 or NULL: mask - erode_d(mask)      (util.py:72-90)
  *   boundary      dev [B,H,W] uint8 or NULL: (uint8 sum over k of per-instance) > 0   (util.py:92-99)
  *   fg            dev [B,H,W] uint8 or NULL: (uint8 sum over k of masks) > 0          (util.py:62-68)
+ *   occupancy     dev uint8 or NULL: the tile occupancy written by quber_encode_initial_masks[_packed] for the SAME masks
+ *                 (layout there).  Planes without a set pixel within d of a tile are not loaded for that tile and get the
+ *                 zero tile; results are identical with and without it.  Ignored when K > 512.
  *   status        dev int32 [1] or NULL: cleared by the call; bit 0 is set if a TMA tile load never arrived (the kernel
  *                 gives up instead of hanging the GPU) — the outputs of THIS call are then invalid.  Always 0 on a
  *                 healthy device; the Python shim copies it out with the results and raises.
@@ -94,7 +103,7 @@ int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t
  * ------------------------------------------------------------------------------------------- */
 int quber_boundary_dilation(int H, int W, double ratio);
 int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
-                        uint8_t *boundary, uint8_t *fg, int32_t *status, void *stream);
+                        uint8_t *boundary, uint8_t *fg, const uint8_t *occupancy, int32_t *status, void *stream);
 int quber_quadruple_maps(const uint8_t *gt, const uint8_t *pred, int B, size_t n, uint8_t *out, void *stream);
 /* Diagnostic, NOT on the hot path (synchronises the device): number of TMA tile loads that
  * quber_mask_boundary gave up waiting for since the library was loaded (process-wide counter; the per-call signal is

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libquber_b200.so")
 
-ABI_VERSION = 2      # QUBER_ABI_VERSION of include/quber_b200.h
+ABI_VERSION = 3      # QUBER_ABI_VERSION of include/quber_b200.h
 QUBER_OK, E_INVALID, E_WORKSPACE, E_CUDA, E_ALIGN, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 POST_GIVEN_CENTERS, POST_NO_TOPK, POST_LABEL_U8 = 1, 2, 4
 
@@ -40,10 +40,11 @@ SYMBOLS = {
     "quber_last_cuda_error": (ctypes.c_char_p, []),
     "quber_gaussian_table": (None, [c_i, c_vp]),
     "quber_encode_workspace_bytes": (c_sz, [c_i, c_i, c_i, c_i]),
-    "quber_encode_initial_masks": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp]),
-    "quber_encode_initial_masks_packed": (c_i, [c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "quber_occupancy_bytes": (c_sz, [c_i, c_i, c_i, c_i]),
+    "quber_encode_initial_masks": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "quber_encode_initial_masks_packed": (c_i, [c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "quber_boundary_dilation": (c_i, [c_i, c_i, c_d]),
-    "quber_mask_boundary": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "quber_mask_boundary": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "quber_quadruple_maps": (c_i, [c_vp, c_vp, c_i, c_sz, c_vp, c_vp]),
     "quber_tma_timeouts": (c_i, []),
     "quber_gemm_bias_act": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp]),

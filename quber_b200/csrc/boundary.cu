@@ -22,6 +22,7 @@ constexpr int B_TWW = B_TW / 4;     // 32
 constexpr int B_TH = 64;            // tile height
 constexpr int B_THREADS = 256;
 constexpr int B_RPT = B_TH * B_TWW / B_THREADS;  // central words per thread (8)
+constexpr int B_MAXK_OCC = 512;     // the occupancy short-cut handles up to this many planes per image
 
 __device__ __forceinline__ uint32_t shift_bytes(uint32_t lo, uint32_t hi, int s) {
     // bytes [s, s+4) of the little-endian 8-byte string lo:hi, s in 0..3
@@ -118,11 +119,14 @@ __device__ unsigned int g_tma_timeouts = 0;     // diagnostic: mbarrier waits th
 
 __global__ void __launch_bounds__(B_THREADS)
 boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map, int K, int H, int W,
-                    int d, int has_per, uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg, int32_t *__restrict__ status) {
+                    int d, int has_per, uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg, int32_t *__restrict__ status,
+                    const uint8_t *__restrict__ occ, int occ_ty, int occ_tx) {
     extern __shared__ __align__(128) unsigned char sm_raw[];
     __shared__ __align__(8) uint64_t full[2];
     __shared__ uint32_t red[6];                 // 3 rotating (OR, AND) slots of the per-plane byte census
     __shared__ int s_abort;
+    __shared__ uint16_t s_live[B_MAXK_OCC];     // planes with a set pixel near this tile, in plane order
+    __shared__ int s_nlive;
     const BGeom g(d);
     const int hx = g.hx, WS = g.WS, WS16 = g.WS16, R = g.R, RW32 = g.RW32, hw = hx >> 2;
     auto S = [&](int i) { return reinterpret_cast<uint32_t *>(sm_raw + (size_t)(i & 1) * g.stage_stride); };
@@ -150,16 +154,52 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
         red[1] = red[3] = red[5] = 0xffffffffu;
         s_abort = 0;
     }
+    // Occupancy short-cut.  `occ` (written by the encode pass that read every mask byte anyway, csrc/encode.cu) says for
+    // every plane and every 128 x 16 pixel tile whether the tile holds a set pixel.  A plane with no set pixel within d of
+    // this tile has neither boundary nor foreground here: it is never loaded, its per-instance tile is the zero tile.
+    // Conservative (tile granularity), so the census below still sees some empty boxes.  Warp 0 builds the list of live
+    // planes in plane order.
+    const bool use_occ = occ != nullptr && K <= B_MAXK_OCC;
+    if (warp == 0) {
+        int n = 0;
+        if (use_occ) {
+            const int r0 = max(ty0 - d, 0) / QUBER_OCC_TILE_H, r1 = min((ty0 + B_TH - 1 + d) / QUBER_OCC_TILE_H, occ_ty - 1);
+            const int c0 = max(tx0 - d, 0) / QUBER_OCC_TILE_W, c1 = min((tx0 + B_TW - 1 + d) / QUBER_OCC_TILE_W, occ_tx - 1);
+            for (int k0 = 0; k0 < K; k0 += 32) {
+                const int k = k0 + lane;
+                int any = 0;
+                if (k < K) {
+                    const uint8_t *o = occ + ((size_t)b * K + k) * occ_ty * occ_tx;
+                    for (int r = r0; r <= r1; ++r)
+                        for (int c = c0; c <= c1; ++c) any |= __ldg(o + r * occ_tx + c);
+                }
+                const uint32_t m = __ballot_sync(0xffffffffu, any != 0);
+                if (any) s_live[n + __popc(m & ((1u << lane) - 1u))] = (uint16_t)k;
+                n += __popc(m);
+            }
+        }
+        if (lane == 0) s_nlive = use_occ ? n : K;
+    }
     fence_proxy_async();         // Z was written by the generic proxy, TMA stores read it
     __syncthreads();
-    auto issue = [&](int k) {    // thread 0 only: fetch plane k into stage k & 1
+    const int n_live = s_nlive;
+    auto plane_of = [&](int j) { return use_occ ? (int)s_live[j] : j; };
+    auto issue = [&](int j) {    // thread 0 only: fetch the j-th live plane into stage j & 1
         fence_proxy_async();
-        mbar_expect_tx(&full[k & 1], g.stage_bytes);
-        tma_load_3d(S(k), &in_map, &full[k & 1], tx0 - hx, ty0 - d, b * K + k);
+        mbar_expect_tx(&full[j & 1], g.stage_bytes);
+        tma_load_3d(S(j), &in_map, &full[j & 1], tx0 - hx, ty0 - d, b * K + plane_of(j));
     };
     if (tid == 0) {
-        issue(0);
-        if (K > 1) issue(1);
+        if (n_live > 0) issue(0);
+        if (n_live > 1) issue(1);
+    }
+    if (use_occ && has_per && tid == 32) {       // the zero tiles of the planes that are not live: one thread, its own bulk group
+        int j = 0;
+        for (int k = 0; k < K; ++k) {
+            if (j < n_live && (int)s_live[j] == k) { ++j; continue; }
+            tma_store_3d(&out_map, Z, tx0, ty0, b * K + k);
+        }
+        tma_commit();
     }
 
     const int row = tid >> 2, jw = tid & 3;     // this thread's 32 output pixels: tile row, 32-pixel column group
@@ -168,7 +208,7 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
     for (int q = 0; q < 8; ++q) uni_acc[q] = fg_acc[q] = 0;
     int o_slot = 0;
 
-    for (int k = 0; k < K; ++k) {
+    for (int k = 0; k < n_live; ++k) {          // k counts LIVE planes from here on; the plane itself is plane_of(k)
         uint32_t *cur = S(k);
         if (!mbar_wait(&full[k & 1], (k >> 1) & 1)) {            // a lost TMA: this CTA's outputs are invalid — say so per call
             s_abort = 1;
@@ -197,10 +237,10 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
             const int s2 = ((k + 2) % 3) * 2;               // next written two iterations from now, last read one ago
             red[s2] = 0u;
             red[s2 + 1] = 0xffffffffu;
-            if (empty && k + 2 < K) issue(k + 2);           // every read of the stage is done
+            if (empty && k + 2 < n_live) issue(k + 2);      // every read of the stage is done
         }
         if (empty) {
-            if (has_per && tid == 0) { tma_store_3d(&out_map, Z, tx0, ty0, b * K + k); tma_commit(); }
+            if (has_per && tid == 0) { tma_store_3d(&out_map, Z, tx0, ty0, b * K + plane_of(k)); tma_commit(); }
             continue;
         }
         // ---- pass B: AND census of the non-zero bytes (binary plane?) + bit packing, 16 pixels per shared load ----
@@ -223,7 +263,7 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
         const uint32_t ac = red[slot + 1];
         const uint32_t va = (ac & (ac >> 8) & (ac >> 16) & (ac >> 24)) & 0xffu;         // AND of the non-zero bytes
         const bool binary = v == va;
-        if (tid == 0 && binary && k + 2 < K) issue(k + 2);
+        if (tid == 0 && binary && k + 2 < n_live) issue(k + 2);
         uint32_t bdw[8], mw[8];
         if (binary) {
             // ---- horizontal erosion on bit rows: window [x-d, x+d] for the four central 32-pixel words ----
@@ -315,10 +355,10 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
         __syncthreads();                                     // S3: O tile complete; bits / Hb / V1 / cur are free again
         if (tid == 0) {
             if (has_per) {
-                tma_store_3d(&out_map, O0 + (size_t)o_slot * B_TH * B_TWW, tx0, ty0, b * K + k);
+                tma_store_3d(&out_map, O0 + (size_t)o_slot * B_TH * B_TWW, tx0, ty0, b * K + plane_of(k));
                 tma_commit();
             }
-            if (!binary && k + 2 < K) issue(k + 2);
+            if (!binary && k + 2 < n_live) issue(k + 2);
         }
         o_slot ^= 1;
     }
@@ -338,7 +378,7 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
             }
         }
     }
-    if (tid == 0) tma_wait_all();     // shared memory must outlive the bulk stores that read it
+    if (tid == 0 || tid == 32) tma_wait_all();     // shared memory must outlive the bulk stores that read it
 }
 
 __global__ void __launch_bounds__(256)
@@ -409,7 +449,7 @@ static bool make_map(CUtensorMap *m, const void *base, int planes, int H, int W,
 }  // namespace quber
 
 extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
-                                   uint8_t *boundary, uint8_t *fg, int32_t *status, void *stream) {
+                                   uint8_t *boundary, uint8_t *fg, const uint8_t *occupancy, int32_t *status, void *stream) {
     using namespace quber;
     if (!masks || B <= 0 || K <= 0 || H <= 0 || W <= 0 || d < 1 || d > 64) return QUBER_E_INVALID;
     if (!per_instance && !boundary && !fg) return QUBER_E_INVALID;
@@ -428,7 +468,8 @@ extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, in
     QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
     if (status) QUBER_CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(int32_t), (cudaStream_t)stream));
     boundary_tma_kernel<<<grid, B_THREADS, g.smem, (cudaStream_t)stream>>>(in_map, out_map, K, H, W, d, per_instance != nullptr,
-                                                                          boundary, fg, status);
+                                                                          boundary, fg, status, occupancy,
+                                                                          cdiv(H, QUBER_OCC_TILE_H), cdiv(W, QUBER_OCC_TILE_W));
     return check_launch("boundary_tma_kernel");
 }
 

@@ -32,7 +32,16 @@ inline int check_launch(const char *where) {
 
 inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
-inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+__host__ __device__ inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+// SMs of the current device (asked once per process: every device of a box is the same part)
+inline int sm_count() {
+    static int n = [] {
+        int dev = 0, sms = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        return sms > 0 ? sms : 148;
+    }();
+    return n;
+}
 
 // Streaming 128-bit accesses: inputs that are read once bypass L1 allocation, outputs
 // that are never re-read by the kernel are written with the same hint.

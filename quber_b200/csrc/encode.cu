@@ -18,7 +18,7 @@
 
 namespace quber {
 
-constexpr int E_TW = 128, E_TH = 16, E_THREADS = 256;   // 8 px per thread
+constexpr int E_TW = QUBER_OCC_TILE_W, E_TH = QUBER_OCC_TILE_H, E_THREADS = 256;   // 128 x 16 pixel tiles, 8 px per thread
 constexpr uint8_t E_NONE = 0xff;
 
 struct EncSums { unsigned long long n, sy, sx; };
@@ -35,7 +35,8 @@ struct EncSums { unsigned long long n, sy, sx; };
 template <bool PACKED, bool DB>
 __global__ void __launch_bounds__(E_THREADS)
 encode_reduce_unrolled_kernel(const uint8_t *__restrict__ masks, int K, int H, int W, EncSums *__restrict__ sums,
-                              uint8_t *__restrict__ lastk, uint8_t *__restrict__ unpacked, uint32_t value) {
+                              uint8_t *__restrict__ lastk, uint8_t *__restrict__ unpacked, uint32_t value,
+                              uint8_t *__restrict__ occ) {
     extern __shared__ unsigned int acc[];   // [K][3]
     const int tid = threadIdx.x, b = blockIdx.z;
     for (int i = tid; i < 3 * K; i += E_THREADS) acc[i] = 0;
@@ -104,13 +105,17 @@ encode_reduce_unrolled_kernel(const uint8_t *__restrict__ masks, int K, int H, i
     }
     if (inb) st_stream_u2(lastk + (size_t)b * HW + pix, make_uint2(last_lo, last_hi));
     __syncthreads();
-    for (int k = tid; k < K; k += E_THREADS)
+    for (int k = tid; k < K; k += E_THREADS) {
+        // occupancy [B][K][tile rows][tile columns]: does this tile hold a set pixel of mask k — the boundary pass skips
+        // the planes that have none near its tile (csrc/boundary.cu)
+        if (occ) occ[(((size_t)b * K + k) * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = acc[3 * k] != 0;
         if (acc[3 * k]) {
             EncSums *s = sums + (size_t)b * K + k;
             atomicAdd(&s->n, (unsigned long long)acc[3 * k]);
             atomicAdd(&s->sy, (unsigned long long)acc[3 * k + 1]);
             atomicAdd(&s->sx, (unsigned long long)acc[3 * k + 2]);
         }
+    }
 }
 
 struct EncCentre { double cy, cx; int uly, ulx; };
@@ -199,13 +204,18 @@ extern "C" void quber_gaussian_table(int sigma, float *host_table) {
         }
 }
 
+extern "C" size_t quber_occupancy_bytes(int B, int K, int H, int W) {
+    if (B <= 0 || K <= 0 || H <= 0 || W <= 0) return 0;
+    return (size_t)B * K * quber::cdiv(H, QUBER_OCC_TILE_H) * quber::cdiv(W, QUBER_OCC_TILE_W);
+}
+
 extern "C" size_t quber_encode_workspace_bytes(int B, int K, int H, int W) {
     if (B <= 0 || K <= 0 || H <= 0 || W <= 0) return 0;
     return quber::align_up((size_t)B * K * sizeof(quber::EncSums), 256) + quber::align_up((size_t)B * H * W, 256);
 }
 
 static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *unpacked, int B, int K, int H, int W, int valid_w, int sigma,
-                         const float *gauss, float *out, void *workspace, size_t workspace_bytes, void *stream) {
+                         const float *gauss, float *out, uint8_t *occupancy, void *workspace, size_t workspace_bytes, void *stream) {
     using namespace quber;
     if (!masks || !gauss || !out || B <= 0 || K <= 0 || K > 254 || H <= 0 || W <= 0 || sigma < 1) return QUBER_E_INVALID;
     if (valid_w < 0 || valid_w > W) return QUBER_E_INVALID;
@@ -222,7 +232,7 @@ static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *
     const size_t rsm = 3 * K * sizeof(unsigned);
     const uint32_t val = packed ? (uint32_t)value : 0u;
     uint8_t *unp = packed ? unpacked : nullptr;
-#define QUBER_REDUCE_LAUNCH(KERNEL) KERNEL<<<grid, E_THREADS, rsm, st>>>(masks, K, H, W, sums, lastk, unp, val)
+#define QUBER_REDUCE_LAUNCH(KERNEL) KERNEL<<<grid, E_THREADS, rsm, st>>>(masks, K, H, W, sums, lastk, unp, val, occupancy)
     if (packed) QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<true, false>));
     else QUBER_REDUCE_LAUNCH((encode_reduce_unrolled_kernel<false, false>));
 #undef QUBER_REDUCE_LAUNCH
@@ -233,13 +243,13 @@ static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *
 }
 
 extern "C" int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int valid_w, int sigma, const float *gauss,
-                                          float *out, void *workspace, size_t workspace_bytes, void *stream) {
-    return encode_launch(masks, false, 0, nullptr, B, K, H, W, valid_w, sigma, gauss, out, workspace, workspace_bytes, stream);
+                                          float *out, uint8_t *occupancy, void *workspace, size_t workspace_bytes, void *stream) {
+    return encode_launch(masks, false, 0, nullptr, B, K, H, W, valid_w, sigma, gauss, out, occupancy, workspace, workspace_bytes, stream);
 }
 
 extern "C" int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t *masks_out, int B, int K, int H, int W,
-                                                 int valid_w, int sigma, const float *gauss, float *out, void *workspace,
-                                                 size_t workspace_bytes, void *stream) {
+                                                 int valid_w, int sigma, const float *gauss, float *out, uint8_t *occupancy,
+                                                 void *workspace, size_t workspace_bytes, void *stream) {
     return encode_launch(reinterpret_cast<const uint8_t *>(packed), true, value, masks_out, B, K, H, W, valid_w, sigma, gauss, out,
-                         workspace, workspace_bytes, stream);
+                         occupancy, workspace, workspace_bytes, stream);
 }

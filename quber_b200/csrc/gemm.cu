@@ -330,15 +330,6 @@ static bool gemm_map(CUtensorMap *m, const void *base, int rows, int K, int ld, 
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-static int gemm_sm_count() {
-    static int n = [] {
-        int dev = 0, sms = 148;
-        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        return sms > 0 ? sms : 148;
-    }();
-    return n;
-}
-
 template <int BN, bool TF32, typename OT, bool SPLIT = false>
 static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUtensorMap &mwlo, const CUtensorMap &mc, const float *bias,
                        int M, int N, int K, int act, cudaStream_t st) {
@@ -346,7 +337,7 @@ static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUten
     const size_t smem = (size_t)NST * (SPLIT ? 2 : 1) * (G_BM + BN) * G_KBYTES + 4 * 2 * 4096 + 1024;
     QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_bias_act_kernel<BN, TF32, OT, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long ntiles = (long long)cdiv(M, G_BM) * cdiv(N, BN);
-    const int grid = (int)(ntiles < gemm_sm_count() ? ntiles : gemm_sm_count());       // persistent: one CTA per SM
+    const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());       // persistent: one CTA per SM
     gemm_bias_act_kernel<BN, TF32, OT, SPLIT><<<grid, SPLIT ? G_THREADS + 128 : G_THREADS, smem, st>>>(ma, mw, mwlo, mc, bias, M, N, K, act);
     return check_launch("gemm_bias_act_kernel");
 }

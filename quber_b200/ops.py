@@ -51,25 +51,37 @@ def boundary_dilation(H, W, ratio):
     return int(_lib.lib().quber_boundary_dilation(int(H), int(W), float(ratio)))
 
 
-def encode_initial_masks(masks, sigma=10, valid_w=0):
+OCC_TILE = (16, 128)     # QUBER_OCC_TILE_H, QUBER_OCC_TILE_W
+
+
+def _occupancy(B, K, H, W, device):
+    th, tw = OCC_TILE
+    return torch.empty((B, K, (H + th - 1) // th, (W + tw - 1) // tw), dtype=torch.uint8, device=device)
+
+
+def encode_initial_masks(masks, sigma=10, valid_w=0, with_occupancy=False):
     """maskrefiner/predictor.py:304-357 for a batch: masks [B,K,H,W] uint8 -> [B,3,H,W] float32.
-    valid_w (0 = W): the frames' own width when W is a zero-padded row pitch (see encode_initial_masks_any_width)."""
+    valid_w (0 = W): the frames' own width when W is a zero-padded row pitch (see encode_initial_masks_any_width).
+    with_occupancy: also return the tile occupancy [B,K,ceil(H/16),ceil(W/128)] uint8 (1 = the tile holds a set pixel of
+    the mask), a by-product of the pass over the mask bytes that mask_boundary(occupancy=) uses to skip empty tiles."""
     _need_cuda(masks, "masks", torch.uint8)
     B, K, H, W = masks.shape
     L = _lib.lib()
     out = torch.empty((B, 3, H, W), dtype=torch.float32, device=masks.device)
+    occ = _occupancy(B, K, H, W, masks.device) if with_occupancy else None
     nbytes = L.quber_encode_workspace_bytes(B, K, H, W)
     ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=masks.device)
     g = gaussian_table(sigma, masks.device)
     with torch.cuda.device(masks.device):
-        _lib.check(L.quber_encode_initial_masks(_ptr(masks), B, K, H, W, int(valid_w), sigma, _ptr(g), _ptr(out), _ptr(ws), nbytes,
-                                                _stream()), "quber_encode_initial_masks")
-    return out
+        _lib.check(L.quber_encode_initial_masks(_ptr(masks), B, K, H, W, int(valid_w), sigma, _ptr(g), _ptr(out), _ptr(occ), _ptr(ws),
+                                                nbytes, _stream()), "quber_encode_initial_masks")
+    return (out, occ) if with_occupancy else out
 
 
-def encode_initial_masks_packed(packed, value, masks_out, sigma=10, valid_w=0):
+def encode_initial_masks_packed(packed, value, masks_out, sigma=10, valid_w=0, with_occupancy=False):
     """encode_initial_masks from bit-packed masks (host_pack_masks): packed int32 CUDA [B*K*H*W / 32], set pixels carry
-    `value`; masks_out uint8 CUDA [B,K,H,W] receives the byte planes (0 / value) on the way -> [B,3,H,W] float32."""
+    `value`; masks_out uint8 CUDA [B,K,H,W] receives the byte planes (0 / value) on the way -> [B,3,H,W] float32
+    (and the tile occupancy with with_occupancy, see encode_initial_masks)."""
     _need_cuda(packed, "packed", torch.int32)
     _need_cuda(masks_out, "masks_out", torch.uint8)
     B, K, H, W = masks_out.shape
@@ -77,13 +89,14 @@ def encode_initial_masks_packed(packed, value, masks_out, sigma=10, valid_w=0):
         raise ValueError("packed words do not match masks_out")
     L = _lib.lib()
     out = torch.empty((B, 3, H, W), dtype=torch.float32, device=packed.device)
+    occ = _occupancy(B, K, H, W, packed.device) if with_occupancy else None
     nbytes = L.quber_encode_workspace_bytes(B, K, H, W)
     ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=packed.device)
     g = gaussian_table(sigma, packed.device)
     with torch.cuda.device(packed.device):
         _lib.check(L.quber_encode_initial_masks_packed(_ptr(packed), int(value), _ptr(masks_out), B, K, H, W, int(valid_w), sigma, _ptr(g), _ptr(out),
-                                                       _ptr(ws), nbytes, _stream()), "quber_encode_initial_masks_packed")
-    return out
+                                                       _ptr(occ), _ptr(ws), nbytes, _stream()), "quber_encode_initial_masks_packed")
+    return (out, occ) if with_occupancy else out
 
 
 def encode_initial_masks_any_width(masks, sigma=10):
@@ -112,9 +125,11 @@ def boundary_status(device=None, check=False):
     return st
 
 
-def mask_boundary(masks, d, per_instance=True, union=True, fg=True, status=None):
+def mask_boundary(masks, d, per_instance=True, union=True, fg=True, status=None, occupancy=None):
     """explicit_error_estimation/util.py:62-99 for a batch: masks [B,K,H,W] uint8 ->
     (per-instance boundary [B,K,H,W] | None, union boundary [B,H,W] | None, fg [B,H,W] | None).
+    occupancy: the tile occupancy encode_initial_masks(with_occupancy=True) returned for the SAME masks — planes with no
+    pixel near a tile are then skipped there (same results, less to read).
     The call's device status word (see boundary_status) is written to `status` (int32 CUDA [1]) or to a per-device
     word that boundary_status() returns; nothing is synchronised here."""
     _need_cuda(masks, "masks", torch.uint8)
@@ -128,9 +143,13 @@ def mask_boundary(masks, d, per_instance=True, union=True, fg=True, status=None)
             status = _BOUNDARY_STATUS[masks.device] = torch.zeros(1, dtype=torch.int32, device=masks.device)
     else:
         _need_cuda(status, "status", torch.int32)
+    if occupancy is not None:
+        _need_cuda(occupancy, "occupancy", torch.uint8)
+        if tuple(occupancy.shape) != tuple(_occupancy(B, K, H, W, "meta").shape) or not occupancy.is_contiguous():
+            raise ValueError("occupancy does not belong to masks of this shape")
     with torch.cuda.device(masks.device):
         _lib.check(_lib.lib().quber_mask_boundary(_ptr(masks), B, K, H, W, int(d), _ptr(per), _ptr(uni), _ptr(fgm),
-                                                  _ptr(status), _stream()), "quber_mask_boundary")
+                                                  _ptr(occupancy), _ptr(status), _stream()), "quber_mask_boundary")
     return per, uni, fgm
 
 

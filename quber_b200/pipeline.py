@@ -71,9 +71,10 @@ class HotPath:
     def encode_and_boundary(self, masks, status=None):
         c = self.cfg
         B, K, H, W = masks.shape
-        enc = ops.encode_initial_masks(masks, c.sigma, c.valid_w)
+        # the encode pass reads every mask byte: its tile occupancy lets the boundary pass skip the empty (tile, plane) pairs
+        enc, occ = ops.encode_initial_masks(masks, c.sigma, c.valid_w, with_occupancy=True)
         d = ops.boundary_dilation(H, c.valid_w or W, c.boundary_ratio)
-        per, uni, fg = ops.mask_boundary(masks, d, status=status)
+        per, uni, fg = ops.mask_boundary(masks, d, status=status, occupancy=occ)
         return enc, per, uni, fg
 
     def encode_and_boundary_packed(self, st, c0, c1, w0, w1, value, status=None):
@@ -84,8 +85,9 @@ class HotPath:
         if W % 16:                                # the packed encode shares the byte kernel's width rule
             ops.unpack_masks(st["packed_dev"][w0:w1], masks.shape, value=value, out=masks)
             return self.encode_and_boundary(masks, status)
-        enc = ops.encode_initial_masks_packed(st["packed_dev"][w0:w1], value, masks, c.sigma, c.valid_w)
-        per, uni, fg = ops.mask_boundary(masks, ops.boundary_dilation(H, c.valid_w or W, c.boundary_ratio), status=status)
+        enc, occ = ops.encode_initial_masks_packed(st["packed_dev"][w0:w1], value, masks, c.sigma, c.valid_w, with_occupancy=True)
+        per, uni, fg = ops.mask_boundary(masks, ops.boundary_dilation(H, c.valid_w or W, c.boundary_ratio), status=status,
+                                         occupancy=occ)
         return enc, per, uni, fg
 
     def post(self, head, label_map_out=None):

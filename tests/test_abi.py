@@ -19,7 +19,7 @@ def _header():
 
 def test_library_present_and_versioned():
     assert os.path.exists(_lib.SO_PATH), "build it: python -c 'import __graft_entry__ as g; g.build()'"
-    assert _lib.lib().quber_version() == _lib.ABI_VERSION == 2
+    assert _lib.lib().quber_version() == _lib.ABI_VERSION == 3
 
 
 def test_every_declared_symbol_is_exported_and_bound():
@@ -64,10 +64,10 @@ def test_error_strings_and_exception_mapping():
 def test_argument_validation_without_gpu():
     """Argument checks run before any CUDA call, so they are testable on a CPU-only host."""
     L = _lib.lib()
-    assert L.quber_encode_initial_masks(None, 1, 1, 16, 16, 0, 10, None, None, None, 0, None) == _lib.E_INVALID
-    assert L.quber_mask_boundary(None, 1, 1, 16, 16, 8, None, None, None, None, None) == _lib.E_INVALID
-    assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 24, 8, ctypes.c_void_p(16), None, None, None, None) == _lib.E_ALIGN
-    assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 16, 0, ctypes.c_void_p(16), None, None, None, None) == _lib.E_INVALID
+    assert L.quber_encode_initial_masks(None, 1, 1, 16, 16, 0, 10, None, None, None, None, 0, None) == _lib.E_INVALID
+    assert L.quber_mask_boundary(None, 1, 1, 16, 16, 8, None, None, None, None, None, None) == _lib.E_INVALID
+    assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 24, 8, ctypes.c_void_p(16), None, None, None, None, None) == _lib.E_ALIGN
+    assert L.quber_mask_boundary(ctypes.c_void_p(16), 1, 1, 16, 16, 0, ctypes.c_void_p(16), None, None, None, None, None) == _lib.E_INVALID
     assert L.quber_msda_forward(None, None, None, None, None, 1, 1, 1, 1, 1, 1, 1, 0, None, None) == _lib.E_INVALID
     v16 = ctypes.c_void_p(16)
     assert L.quber_gemm_bias_act(None, v16, None, v16, 128, 128, 64, 64, 64, 128, 1, 0, 0, None) == _lib.E_INVALID

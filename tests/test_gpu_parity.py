@@ -102,6 +102,45 @@ def test_boundary_binary_route_values_and_mixed_planes(d):
     assert _lib.lib().quber_tma_timeouts() == 0
 
 
+@pytest.mark.parametrize("d,H,W", [(1, 200, 272), (8, 480, 640), (17, 136, 400), (64, 200, 272)])
+def test_boundary_with_encode_occupancy_is_identical(d, H, W):
+    """The tile occupancy written by the encode pass (which reads every mask byte anyway) lets quber_mask_boundary skip
+    the (tile, plane) pairs that have no mask pixel within d of the tile: same per-instance / union / foreground maps as
+    without it and as the oracle; occupancy itself = any() over the 128 x 16 tiles.  Small masks far apart, a mask that
+    touches only a tile corner, an empty plane, a noise plane (byte route) and a full plane."""
+    rng = np.random.default_rng(900 + d)
+    K = 9
+    m = np.zeros((2, K, H, W), np.uint8)
+    el = synth.ellipse_masks(5, H, W, seed=d, axes=(6, 30), margin=8, value=255)
+    m[0, :5] = el
+    m[1, 1:6] = el[::-1]
+    m[0, 5, 63:65, 127:129] = 255                                    # four pixels around a tile corner
+    m[0, 6] = (rng.random((H, W)) < 0.001) * np.uint8(255)           # sparse specks everywhere
+    m[1, 6] = rng.integers(0, 256, (H, W), dtype=np.uint8)           # noise: the exact min-filter route
+    m[1, 7] = 255                                                    # full plane; plane 8 (and 0 of frame 1) stay empty
+    dm = cu(m)
+    enc, occ = ops.encode_initial_masks(dm, 10, with_occupancy=True)
+    assert torch.equal(enc, ops.encode_initial_masks(dm, 10))
+    th, tw = ops.OCC_TILE
+    want = np.zeros(tuple(occ.shape), np.uint8)
+    for r in range(occ.shape[2]):
+        for c in range(occ.shape[3]):
+            want[:, :, r, c] = m[:, :, r * th:(r + 1) * th, c * tw:(c + 1) * tw].reshape(2, K, -1).any(-1)
+    np.testing.assert_array_equal(occ.cpu().numpy(), want)
+    per0, uni0, fg0 = ops.mask_boundary(dm, d)
+    per1, uni1, fg1 = ops.mask_boundary(dm, d, occupancy=occ)
+    assert torch.equal(per0, per1) and torch.equal(uni0, uni1) and torch.equal(fg0, fg1)
+    _, uni2, fg2 = ops.mask_boundary(dm, d, per_instance=False, occupancy=occ)
+    assert torch.equal(uni0, uni2) and torch.equal(fg0, fg2)
+    for b in range(2):
+        p = np.stack([_oracle_boundary_d(x, d) for x in m[b]])
+        np.testing.assert_array_equal(per1[b].cpu().numpy(), p)
+        np.testing.assert_array_equal(fg1[b].cpu().numpy(), oracle.masks_to_fg_mask(m[b]))
+    assert int(ops.boundary_status(dm.device)[0]) == 0
+    with pytest.raises(ValueError):
+        ops.mask_boundary(dm, d, occupancy=occ[:, :-1].contiguous())
+
+
 def _oracle_boundary_d(mask, d):
     import ctypes
     out = np.empty_like(mask)
