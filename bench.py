@@ -241,6 +241,7 @@ def run_ours(args):
         md = {k: torch.from_numpy(v).to(dev) for k, v in msda.items() if k in ("value", "shapes", "starts", "oa", "ref")}
         if c["value"] == "bf16":
             md["value"] = md["value"].bfloat16()
+        md["levels"] = tuple(tuple(int(v) for v in hw) for hw in c["levels"])   # the host copy of the level table
         d = dict(h_masks=hm, h_head=hh, masks=hm.to(dev), head={k: v.to(dev) for k, v in hh.items()}, msda=md)
         # the same masks as COCO RLE (the form the reference's datasets hold), encoded once by the product's own encoder
         cnt, off, st_ = ops.rle_encode(d["masks"].view(B * K, H, Wp))

@@ -207,10 +207,14 @@ int quber_msda_forward(const void *value, const int64_t *shapes, const int64_t *
  *   reference_points  dev [B*Q, L, 2] float32 (x, y) in [0,1]
  *   loc = reference_points + offsets / (W_l, H_l) (:106-109), attention = softmax over L*P (:104-105), then as
  *   quber_msda_forward.  P == 4, L <= 4 and D*sizeof(value) a multiple of 64 bytes; QUBER_E_UNSUPPORTED otherwise
- *   (callers then use quber_msda_prepare + quber_msda_forward). */
+ *   (callers then use quber_msda_prepare + quber_msda_forward).
+ *   levels_host       HOST int32 [L][3] = (H_l, W_l, start_l) or NULL — the same level table as shapes / starts, for
+ *                     callers that built it on the host (the pixel decoder does): the kernel then takes it from its
+ *                     parameter bank instead of shared memory (fewer wavefronts on the L1 data pipe that bounds it).
+ *                     Results are identical either way; it must agree with shapes / starts. */
 int quber_msda_forward_fused(const void *value, const int64_t *shapes, const int64_t *starts, const float *oa, int ld,
                              const float *reference_points, int B, int S, int M, int D, int L, int Q, int P, int dtype,
-                             void *out, void *stream);
+                             void *out, const int32_t *levels_host, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Network glue that is pure bandwidth (csrc/fusion.cu).

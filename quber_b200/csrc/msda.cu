@@ -343,11 +343,13 @@ msda_forward_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__
 // pass (quber_msda_prepare: 464 MB of traffic and 110 us per layer at C2) and the loc / attn tensors disappear; the
 // bytes this kernel reads are the same (288 floats per row either way).
 // ------------------------------------------------------------------------------------------------
-template <int D, typename VT, int MINB, int L>
+struct LevelTab { int h[4], w[4], start[4]; };
+
+template <int D, typename VT, int MINB, int L, bool CLV>
 __global__ void __launch_bounds__(256, MINB)
 msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
                      const float *__restrict__ oa, int ld, const float *__restrict__ ref, int S, int M, int Q,
-                     VT *__restrict__ out) {
+                     VT *__restrict__ out, const __grid_constant__ LevelTab lv) {
     constexpr int P = 4, VB = 16;
     constexpr int NW = VB / 4;
     constexpr int CPL = VB / (int)sizeof(VT);
@@ -364,12 +366,20 @@ msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ s
     const int lane = tid % LPG, grp = tid / LPG;
     const int m = blockIdx.y, b = blockIdx.z;
     const int MD = M * D;
-    if (tid < L) {
-        s_h[tid] = (int)__ldg(shapes + 2 * tid);
-        s_w[tid] = (int)__ldg(shapes + 2 * tid + 1);
-        s_start[tid] = (int)__ldg(starts + tid);
+    // CLV: the caller knows the level table on the host (it built spatial_shapes itself) and passes it by value: it then
+    // sits in the constant bank and the per-round look-ups cost no shared-memory wavefront (2.5 of the 20 set-up
+    // wavefronts per (query, head) that share the L1 data pipe with the 48 gathered lines).
+    if (!CLV) {
+        if (tid < L) {
+            s_h[tid] = (int)__ldg(shapes + 2 * tid);
+            s_w[tid] = (int)__ldg(shapes + 2 * tid + 1);
+            s_start[tid] = (int)__ldg(starts + tid);
+        }
+        __syncthreads();
     }
-    __syncthreads();
+    auto lv_h = [&](int l) { return CLV ? lv.h[l] : s_h[l]; };
+    auto lv_w = [&](int l) { return CLV ? lv.w[l] : s_w[l]; };
+    auto lv_start = [&](int l) { return CLV ? lv.start[l] : s_start[l]; };
     const int qreal = blockIdx.x * GPB + grp;
     const int q = min(qreal, Q - 1);
     const size_t row = (size_t)b * Q + q;
@@ -415,7 +425,7 @@ msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ s
         float A = 0.f, Bw = 0.f, f = 0.f;
         if (tap < LP) {
             const int l = tap / P;
-            const int h = s_h[l], w = s_w[l];
+            const int h = lv_h(l), w = lv_w(l);
             const float lx = __fadd_rn(__uint_as_float(raw_ref.x), __fdiv_rn(__uint_as_float(raw_off.x), (float)w));   // :106-109
             const float ly = __fadd_rn(__uint_as_float(raw_ref.y), __fdiv_rn(__uint_as_float(raw_off.y), (float)h));
             const float him = ly * h - 0.5f, wim = lx * w - 0.5f;                              // cuh:290-291
@@ -430,7 +440,7 @@ msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ s
                 f = xb ? lw : 0.f;
                 A = y0 ? hh * ag : 0.f;
                 Bw = y1 ? lh * ag : 0.f;
-                o1 = ((uint32_t)(s_start[l] + ry0 * w + cx0) * MDu) | (xb ? 0x80000000u : 0u) | (yb ? 0x40000000u : 0u);
+                o1 = ((uint32_t)(lv_start(l) + ry0 * w + cx0) * MDu) | (xb ? 0x80000000u : 0u) | (yb ? 0x40000000u : 0u);
             }
         }
         if (r + 1 < NR && tap + LPG < LP) {
@@ -440,7 +450,7 @@ msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ s
         const int nt = min(LPG, LP - s0);
         uint32_t pitch[NLR];
 #pragma unroll
-        for (int k = 0; k < NLR; ++k) pitch[k] = (uint32_t)s_w[min(s0 / P + k, L - 1)] * MDu;
+        for (int k = 0; k < NLR; ++k) pitch[k] = (uint32_t)lv_w(min(s0 / P + k, L - 1)) * MDu;
         rec[lane] = make_uint4(o1, __float_as_uint(A), __float_as_uint(Bw), __float_as_uint(f));
         __syncwarp();
 #pragma unroll
@@ -480,18 +490,24 @@ msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ s
 
 template <int D, typename VT>
 static int launch_fused(const void *value, const int64_t *shapes, const int64_t *starts, const float *oa, int ld, const float *ref,
-                        int B, int S, int M, int L, int Q, void *out, cudaStream_t st) {
+                        int B, int S, int M, int L, int Q, void *out, const int32_t *levels_host, cudaStream_t st) {
     constexpr int GPB = 256 / (D * (int)sizeof(VT) / 16);
     const dim3 grid(cdiv(Q, GPB), M, B);
     const VT *v = static_cast<const VT *>(value);
     VT *o = static_cast<VT *>(out);
+    LevelTab lv = {};
+    if (levels_host)
+        for (int l = 0; l < L; ++l) { lv.h[l] = levels_host[3 * l]; lv.w[l] = levels_host[3 * l + 1]; lv.start[l] = levels_host[3 * l + 2]; }
+#define QUBER_FUSED(LL)                                                                                                         \
+    case LL:                                                                                                                    \
+        if (levels_host) msda_fused_p4_kernel<D, VT, 5, LL, true><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o, lv);  \
+        else msda_fused_p4_kernel<D, VT, 5, LL, false><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o, lv);          \
+        break;
     switch (L) {
-        case 1: msda_fused_p4_kernel<D, VT, 5, 1><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o); break;
-        case 2: msda_fused_p4_kernel<D, VT, 5, 2><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o); break;
-        case 3: msda_fused_p4_kernel<D, VT, 5, 3><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o); break;
-        case 4: msda_fused_p4_kernel<D, VT, 5, 4><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o); break;
+        QUBER_FUSED(1) QUBER_FUSED(2) QUBER_FUSED(3) QUBER_FUSED(4)
         default: return QUBER_E_UNSUPPORTED;
     }
+#undef QUBER_FUSED
     return check_launch("msda_fused_p4_kernel");
 }
 
@@ -599,7 +615,7 @@ extern "C" int quber_msda_forward(const void *value, const int64_t *shapes, cons
 
 extern "C" int quber_msda_forward_fused(const void *value, const int64_t *shapes, const int64_t *starts, const float *oa, int ld,
                                         const float *reference_points, int B, int S, int M, int D, int L, int Q, int P,
-                                        int dtype, void *out, void *stream) {
+                                        int dtype, void *out, const int32_t *levels_host, void *stream) {
     using namespace quber;
     if (!value || !shapes || !starts || !oa || !reference_points || !out) return QUBER_E_INVALID;
     if (B <= 0 || S <= 0 || M <= 0 || D <= 0 || L <= 0 || Q <= 0 || P <= 0 || ld < M * L * P * 3) return QUBER_E_INVALID;
@@ -612,15 +628,15 @@ extern "C" int quber_msda_forward_fused(const void *value, const int64_t *shapes
     cudaStream_t st = (cudaStream_t)stream;
     if (dtype == 1) {
         switch (D) {
-            case 32: return launch_fused<32, __nv_bfloat16>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
-            case 64: return launch_fused<64, __nv_bfloat16>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
+            case 32: return launch_fused<32, __nv_bfloat16>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, levels_host, st);
+            case 64: return launch_fused<64, __nv_bfloat16>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, levels_host, st);
             default: return QUBER_E_UNSUPPORTED;
         }
     }
     switch (D) {
-        case 16: return launch_fused<16, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
-        case 32: return launch_fused<32, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
-        case 64: return launch_fused<64, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, st);
+        case 16: return launch_fused<16, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, levels_host, st);
+        case 32: return launch_fused<32, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, levels_host, st);
+        case 64: return launch_fused<64, float>(value, shapes, starts, oa, ld, reference_points, B, S, M, L, Q, out, levels_host, st);
         default: return QUBER_E_UNSUPPORTED;
     }
 }

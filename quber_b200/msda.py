@@ -126,14 +126,15 @@ class MSDeformAttn(nn.Module):
             self.__dict__["_packed"] = p
         return p
 
-    def sample(self, value, oa, reference_points, spatial_shapes, level_start_index):
+    def sample(self, value, oa, reference_points, spatial_shapes, level_start_index, levels=None):
         """value [N,S,M,D], oa [N,Q,M*L*P*3] (offsets | logits, the qk GEMM's rows), reference_points [N,Q,L,2|4]
         -> [N,Q,M*D]: ms_deform_attn.py:102-117 + the sampling op."""
         N, Q, _ = oa.shape
         M, L, P = self.n_heads, self.n_levels, self.n_points
         rp = reference_points
         if rp.shape[-1] == 2 and rp.dtype == torch.float32 and ops.msda_fused_supported(value, L, P):
-            return ops.msda_forward_fused(value, spatial_shapes, level_start_index, oa, rp.contiguous(), L, P)
+            # levels: the host copy of spatial_shapes when the caller has one (the pixel decoder builds the tensor from it)
+            return ops.msda_forward_fused(value, spatial_shapes, level_start_index, oa, rp.contiguous(), L, P, levels=levels)
         if rp.shape[-1] == 2 and rp.dtype == torch.float32:
             loc, aw = ops.msda_prepare(oa, rp.contiguous(), spatial_shapes, M, L, P)
         elif rp.shape[-1] in (2, 4):

@@ -305,11 +305,14 @@ def msda_fused_supported(value, n_levels, n_points):
             and (D * value.element_size()) % 64 == 0 and D in (16, 32, 64))
 
 
-def msda_forward_fused(value, spatial_shapes, level_start_index, oa, reference_points, n_levels, n_points):
+def msda_forward_fused(value, spatial_shapes, level_start_index, oa, reference_points, n_levels, n_points, levels=None):
     """MSDeformAttn.forward between its Linear layers and the output projection in one kernel
     (OPS/modules/ms_deform_attn.py:102-117 + ms_deform_attn_forward): value [N,S,M,D] float32 | bfloat16, oa [N,Q,ld]
     float32 = the fused sampling_offsets | attention_weights GEMM output, reference_points [N,Q,L,2] float32
-    -> [N,Q,M*D] in value's dtype.  The softmax and `ref + off / (W_l, H_l)` happen in the kernel's set-up phase."""
+    -> [N,Q,M*D] in value's dtype.  The softmax and `ref + off / (W_l, H_l)` happen in the kernel's set-up phase.
+    levels: the HOST copy of the level table, ((H_0, W_0), (H_1, W_1), ...) as the caller built spatial_shapes from (level
+    starts are the cumulative H*W) — optional; with it the kernel reads the table from its parameter bank (faster, same
+    results).  It must describe the same levels as spatial_shapes / level_start_index."""
     _need_cuda(value, "value")
     _need_cuda(spatial_shapes, "spatial_shapes", torch.int64)
     _need_cuda(level_start_index, "level_start_index", torch.int64)
@@ -322,12 +325,34 @@ def msda_forward_fused(value, spatial_shapes, level_start_index, oa, reference_p
     if oa.shape[0] != N or ld < M * n_levels * n_points * 3 or tuple(reference_points.shape) != (N, Q, n_levels, 2):
         raise ValueError("msda_forward_fused: oa must be [N,Q,>=M*L*P*3] and reference_points [N,Q,L,2]")
     out = torch.empty((N, Q, M * D), dtype=value.dtype, device=value.device)
+    tab = None
+    if levels is not None:
+        tab = _level_table(levels)
+        if len(levels) != n_levels or tab[1] != S:
+            raise ValueError("msda_forward_fused: `levels` does not describe value's S positions in n_levels levels")
     with torch.cuda.device(value.device):
         _lib.check(_lib.lib().quber_msda_forward_fused(_ptr(value), _ptr(spatial_shapes), _ptr(level_start_index), _ptr(oa), ld,
                                                        _ptr(reference_points), N, S, M, D, n_levels, Q, n_points,
-                                                       0 if value.dtype == torch.float32 else 1, _ptr(out), _stream()),
+                                                       0 if value.dtype == torch.float32 else 1, _ptr(out),
+                                                       None if tab is None else tab[0], _stream()),
                    "quber_msda_forward_fused")
     return out
+
+
+_LEVEL_TABLES = {}
+
+
+def _level_table(levels):
+    """((H, W), ...) -> (ctypes int32 [L][3] = (H, W, start), total positions); cached per level tuple."""
+    key = tuple((int(h), int(w)) for h, w in levels)
+    ent = _LEVEL_TABLES.get(key)
+    if ent is None:
+        flat, start = [], 0
+        for h, w in key:
+            flat += [h, w, start]
+            start += h * w
+        ent = _LEVEL_TABLES[key] = ((ctypes.c_int32 * len(flat))(*flat), start)
+    return ent
 
 
 def gemm_bias_act(a, weight, bias=None, act="none", out_dtype=None):

@@ -113,7 +113,8 @@ class HotPath:
         for _ in range(n_layers):
             if "oa" in msda:
                 L = msda["ref"].shape[2]
-                out = ops.msda_forward_fused(msda["value"], msda["shapes"], msda["starts"], msda["oa"], msda["ref"], L, 4)
+                out = ops.msda_forward_fused(msda["value"], msda["shapes"], msda["starts"], msda["oa"], msda["ref"], L, 4,
+                                             levels=msda.get("levels"))
             else:
                 out = ops.msda_forward(msda["value"], msda["shapes"], msda["starts"], msda["loc"], msda["attn"])
         return out

@@ -109,7 +109,7 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
         return p
 
     def _forward_kernels(self, src, pos, reference_points, spatial_shapes, level_start_index, padding_mask, pre=None,
-                         emit_next=False):
+                         emit_next=False, host_shapes=None):
         """msdeformattn.py:122-131 on this repo's kernels.  `pre` = (x, q) already in the GEMM dtype, written by the
         previous layer's last LayerNorm pass; `emit_next` asks this layer's last LayerNorm for the same pair (returned
         as the second value)."""
@@ -131,7 +131,8 @@ class MSDeformAttnTransformerEncoderLayer(nn.Module):
             value = value.masked_fill(padding_mask[..., None], float(0))
         oa = pk["qk"](q, prec, out_dtype=torch.float32)                                       # :102-103, one GEMM
         # softmax over L*P, ref + off / (W_l, H_l) and the sampling in ONE kernel (:104-117)
-        samp = a.sample(value.view(N, S, M, C // M), oa.view(N, S, -1), reference_points, spatial_shapes, level_start_index)
+        samp = a.sample(value.view(N, S, M, C // M), oa.view(N, S, -1), reference_points, spatial_shapes, level_start_index,
+                        levels=host_shapes)
         src2 = pk["o"](samp, prec, out_dtype=torch.float32)                                   # :124
         fused_ln = C % 128 == 0 and C <= 1024 and C // 128 not in (5, 7)
         if fused_ln:                                                                          # norm1(src + src2), one pass
@@ -192,7 +193,7 @@ class MSDeformAttnTransformerEncoder(nn.Module):
             if output.is_cuda:
                 nxt = i + 1 < len(self.layers) and self.layers[i + 1].precision == layer.precision
                 r = layer._forward_kernels(output, pos, reference_points, spatial_shapes, level_start_index, padding_mask,
-                                           pre=pre, emit_next=nxt)
+                                           pre=pre, emit_next=nxt, host_shapes=shapes)
                 output, pre = r if nxt else (r, None)
             else:
                 output, pre = layer(output, pos, reference_points, spatial_shapes, level_start_index, padding_mask), None

@@ -666,6 +666,10 @@ def test_msda_fused_equals_prepare_plus_forward_and_oracle(D, dt, L):
     ref_pts = torch.rand(N, Q, L, 2, device=DEV, generator=g) * 1.1 - 0.05
     vt = value.bfloat16() if dt == "bf16" else value
     fused = ops.msda_forward_fused(vt, shapes, starts, oa, ref_pts, L, P)
+    # the level table handed over on the host as well (parameter bank instead of shared memory): the same bits
+    assert torch.equal(fused, ops.msda_forward_fused(vt, shapes, starts, oa, ref_pts, L, P, levels=shapes_l))
+    with pytest.raises(ValueError):
+        ops.msda_forward_fused(vt, shapes, starts, oa, ref_pts, L, P, levels=shapes_l[:-1] + [(7, 7)])
     loc, aw = ops.msda_prepare(oa, ref_pts, shapes, M, L, P)
     two = ops.msda_forward(vt, shapes, starts, loc, aw)
     assert fused.dtype == vt.dtype and fused.shape == (N, Q, M * D)
