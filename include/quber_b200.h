@@ -74,9 +74,9 @@ size_t quber_occupancy_bytes(int B, int K, int H, int W);
 int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int valid_w, int sigma,
                                const float *gauss, float *out, uint8_t *occupancy, void *workspace, size_t workspace_bytes,
                                void *stream);
-/* The same from bit-packed masks (quber_host_pack_masks): packed dev uint32 [B*K*H*W / 32], set pixels carry `value`
- * (1..255).  Also writes the byte planes masks_out dev [B,K,H,W] uint8 (0 / value) — what quber_unpack_masks would give —
- * for quber_mask_boundary, so the expansion costs no pass of its own. */
+/* The same from bit-packed masks (quber_host_pack_masks / quber_rle_decode): packed dev uint32 [B*K*H*W / 32], set pixels
+ * carry `value` (1..255).  masks_out (optional, NULL = not wanted): dev [B,K,H,W] uint8 receives the byte planes
+ * (0 / value) — what quber_unpack_masks would give — on the way; quber_mask_boundary_bits works from the bits. */
 int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t *masks_out, int B, int K, int H, int W,
                                       int valid_w, int sigma, const float *gauss, float *out, uint8_t *occupancy,
                                       void *workspace, size_t workspace_bytes, void *stream);
@@ -104,6 +104,11 @@ int quber_encode_initial_masks_packed(const uint32_t *packed, int value, uint8_t
 int quber_boundary_dilation(int H, int W, double ratio);
 int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, int W, int d, uint8_t *per_instance,
                         uint8_t *boundary, uint8_t *fg, const uint8_t *occupancy, int32_t *status, void *stream);
+/* quber_mask_boundary from bit planes (packed dev uint32 [B*K*H*W / 32], bit i of word w = pixel 32 w + i; set pixels
+ * carry `value` in the outputs): same three outputs, no byte planes read or needed, no TMA load (nothing to time out).
+ * W % 32 == 0.  occupancy as above (from quber_encode_initial_masks_packed on the same planes) or NULL. */
+int quber_mask_boundary_bits(const uint32_t *packed, int value, int B, int K, int H, int W, int d, uint8_t *per_instance,
+                             uint8_t *boundary, uint8_t *fg, const uint8_t *occupancy, void *stream);
 int quber_quadruple_maps(const uint8_t *gt, const uint8_t *pred, int B, size_t n, uint8_t *out, void *stream);
 /* Diagnostic, NOT on the hot path (synchronises the device): number of TMA tile loads that
  * quber_mask_boundary gave up waiting for since the library was loaded (process-wide counter; the per-call signal is

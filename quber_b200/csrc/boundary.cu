@@ -381,6 +381,163 @@ boundary_tma_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_con
     if (tid == 0 || tid == 32) tma_wait_all();     // shared memory must outlive the bulk stores that read it
 }
 
+// ------------------------------------------------------------------------------------------------
+// The same per-instance boundaries from BIT planes (one bit per pixel: quber_host_pack_masks / quber_rle_decode — what the
+// host-buffer routes hold anyway).  No byte planes are ever materialised: a plane's (tile + halo) box is R x 5..6 words
+// fetched with plain loads one live plane ahead, so there is no byte census, no packing pass and no TMA load (hence
+// nothing to time out); the erosion on bit rows and the byte expansion of the 128 x 64 result are those of the binary
+// route above.  Set pixels carry `v` in the outputs (the byte value the planes were packed from).  W % 32 == 0.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(B_THREADS)
+boundary_bits_kernel(const uint32_t *__restrict__ planes, uint32_t v, const __grid_constant__ CUtensorMap out_map, int K, int H, int W,
+                     int d, int has_per, uint8_t *__restrict__ boundary, uint8_t *__restrict__ fg,
+                     const uint8_t *__restrict__ occ, int occ_ty, int occ_tx) {
+    extern __shared__ __align__(128) unsigned char sm_raw[];
+    __shared__ uint16_t s_live[B_MAXK_OCC];
+    __shared__ int s_nlive;
+    const BGeom g(d);
+    const int hx = g.hx, R = g.R, RW32 = g.RW32, BW = g.SW >> 5;     // BW: box words per row (RW32 = BW + the zero pad word)
+    uint32_t *O0 = reinterpret_cast<uint32_t *>(sm_raw);                                    // [2][64][32]
+    uint32_t *Z = O0 + 2 * B_TH * B_TWW;                                                   // zero tile
+    uint32_t *bits = Z + B_TH * B_TWW;                                                     // [R][RW32]
+    uint32_t *Hb = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(bits) + g.bits_bytes);   // [R][4]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.z;
+    const int ty0 = blockIdx.y * B_TH, tx0 = blockIdx.x * B_TW;
+    const size_t HW = (size_t)H * W;
+    const int WB = W >> 5;
+    const int w = 2 * d + 1;
+    for (int i = tid; i < B_TH * B_TWW; i += B_THREADS) Z[i] = 0u;
+    for (int i = tid; i < R * RW32; i += B_THREADS) bits[i] = 0u;      // the pad word of every bit row stays 0
+    const bool use_occ = occ != nullptr && K <= B_MAXK_OCC;
+    if (warp == 0) {
+        int n = 0;
+        if (use_occ) {
+            const int r0 = max(ty0 - d, 0) / QUBER_OCC_TILE_H, r1 = min((ty0 + B_TH - 1 + d) / QUBER_OCC_TILE_H, occ_ty - 1);
+            const int c0 = max(tx0 - d, 0) / QUBER_OCC_TILE_W, c1 = min((tx0 + B_TW - 1 + d) / QUBER_OCC_TILE_W, occ_tx - 1);
+            for (int k0 = 0; k0 < K; k0 += 32) {
+                const int k = k0 + lane;
+                int any = 0;
+                if (k < K) {
+                    const uint8_t *o = occ + ((size_t)b * K + k) * occ_ty * occ_tx;
+                    for (int r = r0; r <= r1; ++r)
+                        for (int c = c0; c <= c1; ++c) any |= __ldg(o + r * occ_tx + c);
+                }
+                const uint32_t m = __ballot_sync(0xffffffffu, any != 0);
+                if (any) s_live[n + __popc(m & ((1u << lane) - 1u))] = (uint16_t)k;
+                n += __popc(m);
+            }
+        }
+        if (lane == 0) s_nlive = use_occ ? n : K;
+    }
+    fence_proxy_async();         // Z was written by the generic proxy, TMA stores read it
+    __syncthreads();
+    const int n_live = s_nlive;
+    auto plane_of = [&](int j) { return use_occ ? (int)s_live[j] : j; };
+    if (use_occ && has_per && tid == 32) {       // zero tiles of the planes that are not live
+        int j = 0;
+        for (int k = 0; k < K; ++k) {
+            if (j < n_live && (int)s_live[j] == k) { ++j; continue; }
+            tma_store_3d(&out_map, Z, tx0, ty0, b * K + k);
+        }
+        tma_commit();
+    }
+    // box word `it` (row r, word c) of a plane: pixels tx0 - hx + 32 c ... + 31 of image row ty0 - d + r, zero outside
+    const int n_box = R * BW;
+    auto fetch = [&](int j, int it) -> uint32_t {
+        if (j >= n_live || it >= n_box) return 0u;
+        const int r = it / BW, c = it - r * BW;
+        const int gy = ty0 - d + r;
+        if (gy < 0 || gy >= H) return 0u;
+        const int x0 = tx0 - hx + 32 * c;
+        const int wq = x0 >> 5, sh = x0 & 31;                          // arithmetic shift: floor for negative x0
+        const uint32_t *row = planes + ((size_t)(b * K + plane_of(j)) * H + gy) * WB;
+        const uint32_t lo = (wq >= 0 && wq < WB) ? __ldg(row + wq) : 0u;
+        const uint32_t hi = (sh && wq + 1 >= 0 && wq + 1 < WB) ? __ldg(row + wq + 1) : 0u;
+        return __funnelshift_r(lo, hi, sh);
+    };
+    constexpr int NF = 3;                       // box words per thread: R * BW <= (64 + 128) * 6 ... covered in NF passes for d <= 16
+    const int passes = (n_box + B_THREADS - 1) / B_THREADS;
+    uint32_t nxt[NF];
+#pragma unroll
+    for (int q = 0; q < NF; ++q) nxt[q] = fetch(0, tid + q * B_THREADS);
+    const int row = tid >> 2, jw = tid & 3;     // this thread's 32 output pixels: tile row, 32-pixel column group
+    uint32_t uni_acc[8], fg_acc[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) uni_acc[q] = fg_acc[q] = 0;
+    int o_slot = 0;
+    for (int k = 0; k < n_live; ++k) {
+        uint32_t any = 0u;
+#pragma unroll
+        for (int q = 0; q < NF; ++q) {
+            const int it = tid + q * B_THREADS;
+            if (it < n_box) { bits[(it / BW) * RW32 + (it % BW)] = nxt[q]; any |= nxt[q]; }
+        }
+        for (int q = NF; q < passes; ++q) {      // large radii: the rest of the box, not prefetched
+            const int it = tid + q * B_THREADS;
+            if (it < n_box) { const uint32_t x = fetch(k, it); bits[(it / BW) * RW32 + (it % BW)] = x; any |= x; }
+        }
+#pragma unroll
+        for (int q = 0; q < NF; ++q) nxt[q] = fetch(k + 1, tid + q * B_THREADS);
+        if (!__syncthreads_or(any != 0u)) {       // S1: the box is empty after all (occupancy is per 128 x 16 tile)
+            if (has_per && tid == 0) { tma_store_3d(&out_map, Z, tx0, ty0, b * K + plane_of(k)); tma_commit(); }
+            continue;
+        }
+        // ---- horizontal erosion on bit rows: window [x-d, x+d] for the four central 32-pixel words ----
+        for (int it = tid; it < R * 4; it += B_THREADS) {
+            const uint32_t *row32 = bits + (it >> 2) * RW32;
+            const int s0 = hx + 32 * (it & 3) - d;
+            uint32_t e = 0xffffffffu;
+            for (int t = 0; t < w; ++t) {
+                const int s = s0 + t;
+                e &= __funnelshift_r(row32[s >> 5], row32[(s >> 5) + 1], s & 31);
+            }
+            Hb[it] = e;
+        }
+        if (has_per && tid == 0) tma_wait_read<1>();     // the store that last used this O slot has read it
+        __syncthreads();                                 // S2
+        uint32_t e = 0xffffffffu;
+        for (int t = 0; t < w; ++t) e &= Hb[(row + t) * 4 + jw];
+        const uint32_t *mrow = bits + (row + d) * RW32 + (hx >> 5) + jw;
+        const uint32_t m = __funnelshift_r(mrow[0], mrow[1], hx & 31);
+        const uint32_t bd = m & ~e;                      // mask - eroded, one bit per pixel
+        uint32_t bdw[8], mw[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            bdw[q] = nibble_to_bytes01((bd >> (4 * q)) & 15u) * v;
+            mw[q] = nibble_to_bytes01((m >> (4 * q)) & 15u) * v;
+            uni_acc[q] = add_bytes(uni_acc[q], bdw[q]);
+            fg_acc[q] = add_bytes(fg_acc[q], mw[q]);
+        }
+        if (has_per) {
+            uint4 *o4 = reinterpret_cast<uint4 *>(O0 + (size_t)o_slot * B_TH * B_TWW + row * B_TWW + 8 * jw);
+            o4[0] = make_uint4(bdw[0], bdw[1], bdw[2], bdw[3]);
+            o4[1] = make_uint4(bdw[4], bdw[5], bdw[6], bdw[7]);
+            fence_proxy_async();
+        }
+        __syncthreads();                                 // S3: O tile complete; bits / Hb are free again
+        if (has_per && tid == 0) {
+            tma_store_3d(&out_map, O0 + (size_t)o_slot * B_TH * B_TWW, tx0, ty0, b * K + plane_of(k));
+            tma_commit();
+        }
+        o_slot ^= 1;
+    }
+    const int gy = ty0 + row, gx = tx0 + 32 * jw;
+    if (gy < H && gx < W) {
+        const size_t o = (size_t)b * HW + (size_t)gy * W + gx;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (boundary)
+                st_stream_u4(boundary + o + 16 * h, make_uint4(nonzero_bytes01(uni_acc[4 * h]), nonzero_bytes01(uni_acc[4 * h + 1]),
+                                                               nonzero_bytes01(uni_acc[4 * h + 2]), nonzero_bytes01(uni_acc[4 * h + 3])));
+            if (fg)
+                st_stream_u4(fg + o + 16 * h, make_uint4(nonzero_bytes01(fg_acc[4 * h]), nonzero_bytes01(fg_acc[4 * h + 1]),
+                                                         nonzero_bytes01(fg_acc[4 * h + 2]), nonzero_bytes01(fg_acc[4 * h + 3])));
+        }
+    }
+    if (tid == 0 || tid == 32) tma_wait_all();     // shared memory must outlive the bulk stores that read it
+}
+
 __global__ void __launch_bounds__(256)
 quadruple_kernel(const uint8_t *__restrict__ gt, const uint8_t *__restrict__ pred, size_t n, uint8_t *__restrict__ out) {
     const int b = blockIdx.y;
@@ -471,6 +628,30 @@ extern "C" int quber_mask_boundary(const uint8_t *masks, int B, int K, int H, in
                                                                           boundary, fg, status, occupancy,
                                                                           cdiv(H, QUBER_OCC_TILE_H), cdiv(W, QUBER_OCC_TILE_W));
     return check_launch("boundary_tma_kernel");
+}
+
+extern "C" int quber_mask_boundary_bits(const uint32_t *packed, int value, int B, int K, int H, int W, int d, uint8_t *per_instance,
+                                        uint8_t *boundary, uint8_t *fg, const uint8_t *occupancy, void *stream) {
+    using namespace quber;
+    if (!packed || B <= 0 || K <= 0 || H <= 0 || W <= 0 || d < 1 || d > 64 || value < 1 || value > 255) return QUBER_E_INVALID;
+    if (!per_instance && !boundary && !fg) return QUBER_E_INVALID;
+    if (W % 32 != 0 || (reinterpret_cast<uintptr_t>(packed) & 3u) || (per_instance && !aligned16(per_instance)) ||
+        (boundary && !aligned16(boundary)) || (fg && !aligned16(fg)))
+        return QUBER_E_ALIGN;
+    if (B > 65535) return QUBER_E_UNSUPPORTED;
+    dim3 grid(cdiv(W, B_TW), cdiv(H, B_TH), B);
+    const BGeom g(d);
+    CUtensorMap out_map;
+    if (!make_map(&out_map, per_instance ? (const void *)per_instance : (const void *)packed, B * K, H, W, B_TW, B_TH)) {
+        set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
+        return QUBER_E_CUDA;
+    }
+    const size_t smem = 3 * (size_t)B_TH * B_TWW * 4 + g.bits_bytes + g.hb_bytes + 128;
+    QUBER_CUDA_TRY(cudaFuncSetAttribute(boundary_bits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    boundary_bits_kernel<<<grid, B_THREADS, smem, (cudaStream_t)stream>>>(packed, (uint32_t)value, out_map, K, H, W, d,
+                                                                         per_instance != nullptr, boundary, fg, occupancy,
+                                                                         cdiv(H, QUBER_OCC_TILE_H), cdiv(W, QUBER_OCC_TILE_W));
+    return check_launch("boundary_bits_kernel");
 }
 
 extern "C" int quber_tma_timeouts(void) {

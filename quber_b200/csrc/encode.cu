@@ -28,8 +28,8 @@ struct EncSums { unsigned long long n, sy, sx; };
 // redux.sync, shared-memory atomics per CTA, one global atomic per CTA and mask — and records per pixel the LAST mask
 // covering it (the reference's overwrite order, predictor.py:337-356).
 // PACKED: `masks` holds one bit per pixel (quber_host_pack_masks / quber_rle_decode: bit i of word w = pixel 32 w + i of
-// the flattened [B,K,H,W] array) and the kernel also writes the byte planes (0 / value) to `unpacked` for the boundary
-// kernel — the expansion rides on the pass that reads every plane anyway instead of costing a kernel of its own.
+// the flattened [B,K,H,W] array); with `unpacked` the kernel also writes the byte planes (0 / value) — the expansion
+// rides on the pass that reads every plane anyway.  quber_mask_boundary_bits does not need them.
 // DB (not instantiated in the shipped library: measured equal, 12 more registers): the next group's loads issued before
 // the current group is processed.
 template <bool PACKED, bool DB>
@@ -56,7 +56,7 @@ encode_reduce_unrolled_kernel(const uint8_t *__restrict__ masks, int K, int H, i
                 const uint32_t bits = __ldg(base + (size_t)k * (HW / 8));
                 v = make_uint2((((bits & 0xfu) * 0x00204081u) & 0x01010101u) * value,
                                (((bits >> 4) * 0x00204081u) & 0x01010101u) * value);
-                st_stream_u2(unpacked + plane0 + (size_t)k * HW, v);
+                if (unpacked) st_stream_u2(unpacked + plane0 + (size_t)k * HW, v);
             } else {
                 v = ld_stream_u2(base + (size_t)k * HW);
             }
@@ -220,8 +220,8 @@ static int encode_launch(const uint8_t *masks, bool packed, int value, uint8_t *
     if (!masks || !gauss || !out || B <= 0 || K <= 0 || K > 254 || H <= 0 || W <= 0 || sigma < 1) return QUBER_E_INVALID;
     if (valid_w < 0 || valid_w > W) return QUBER_E_INVALID;
     if (W % 16 != 0 || !aligned16(out) || (reinterpret_cast<uintptr_t>(masks) & (packed ? 3u : 15u))) return QUBER_E_ALIGN;
-    if (packed && (!unpacked || value < 1 || value > 255)) return QUBER_E_INVALID;
-    if (packed && !aligned16(unpacked)) return QUBER_E_ALIGN;
+    if (packed && (value < 1 || value > 255)) return QUBER_E_INVALID;
+    if (packed && unpacked && !aligned16(unpacked)) return QUBER_E_ALIGN;
     if (!workspace || workspace_bytes < quber_encode_workspace_bytes(B, K, H, W) || !aligned16(workspace)) return QUBER_E_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     EncSums *sums = reinterpret_cast<EncSums *>(workspace);

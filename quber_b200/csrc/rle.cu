@@ -13,9 +13,9 @@
 // are ~20 KB of counts instead of 9.2 MB of bytes, which is what takes the host link out of the end-to-end call.
 //
 // decode:  rle_scan_kernel (inclusive prefix sums of the counts, one CTA per mask)
-//          rle_fill_kernel (lane = column, binary search for the run holding the first row of the chunk, then a walk down
-//                           the column; a warp's 32 column bits of one row are one ballot = one packed word, staged through
-//                           shared memory so that rows leave as 32-byte segments; or bytes 0 / value)
+//          rle_fill_runs_kernel (bit planes: cleared, then every run of ones ORs its own bits in)
+//          rle_fill_kernel (byte planes: lane = column, binary search for the run holding the first row of the chunk,
+//                           then a walk down the column)
 // encode:  rle_count_kernel -> rle_colscan_kernel -> rle_offsets_kernel -> rle_positions_kernel -> rle_diff_kernel
 #include "common.cuh"
 
@@ -61,19 +61,18 @@ rle_scan_kernel(const uint32_t *__restrict__ counts, const int64_t *__restrict__
     if (tid == 0 && s_carry != area) atomicOr(status, 1);
 }
 
-template <bool PACKED>
+// Byte output: lane = column, binary search for the run holding the first row of the chunk, then a walk down the column.
 __global__ void __launch_bounds__(RLE_THREADS)
 rle_fill_kernel(const uint32_t *__restrict__ ends, const int64_t *__restrict__ offsets, int H, int W, int value,
-                uint32_t *__restrict__ packed, uint8_t *__restrict__ bytes) {
-    __shared__ uint32_t tile[RLE_ROWS][RLE_THREADS / 32];
-    const int i = blockIdx.z, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+                uint8_t *__restrict__ bytes) {
+    const int i = blockIdx.z, tid = threadIdx.x;
     const int x = blockIdx.x * RLE_THREADS + tid, y0 = blockIdx.y * RLE_ROWS;
     const int rows = min(RLE_ROWS, H - y0);
     const uint32_t *e = ends + offsets[i];
     const int m = (int)(offsets[i + 1] - offsets[i]);
-    const bool live = x < W;
+    if (x >= W) return;
     // j = index of the run holding column-major index idx = x*H + y0: the first run whose inclusive end exceeds idx
-    unsigned idx = live ? (unsigned)x * (unsigned)H + (unsigned)y0 : 0u;
+    unsigned idx = (unsigned)x * (unsigned)H + (unsigned)y0;
     int lo = 0, hi = m;
     while (lo < hi) {
         const int mid = (lo + hi) >> 1;
@@ -87,21 +86,38 @@ rle_fill_kernel(const uint32_t *__restrict__ ends, const int64_t *__restrict__ o
             ++j;
             end = j < m ? __ldg(e + j) : 0xffffffffu;
         }
-        const bool bit = live && j < m && (j & 1);
-        if (PACKED) {
-            const uint32_t word = __ballot_sync(0xffffffffu, bit);
-            if (lane == 0) tile[r][warp] = word;
-        } else if (live) {
-            bytes[(plane + y0 + r) * (size_t)W + x] = bit ? (uint8_t)value : (uint8_t)0;
-        }
+        bytes[(plane + y0 + r) * (size_t)W + x] = (j < m && (j & 1)) ? (uint8_t)value : (uint8_t)0;
     }
-    if (PACKED) {
-        __syncthreads();
-        const int WB = W / 32, wb0 = blockIdx.x * (RLE_THREADS / 32);
-        for (int t = tid; t < rows * (RLE_THREADS / 32); t += RLE_THREADS) {
-            const int r = t / (RLE_THREADS / 32), c = t % (RLE_THREADS / 32);
-            if (wb0 + c < WB) packed[(plane + y0 + r) * (size_t)WB + wb0 + c] = tile[r][c];
-        }
+}
+
+// Packed output, run-major: the planes are cleared by one memset and every run of ones sets its own bits (column-major
+// index idx -> pixel (idx % H, idx / H) -> bit x % 32 of word (y, x / 32)) with atomicOr.  Work is proportional to the set
+// pixels (~4 000 per mask at C2) instead of to H*W, and there is no per-chunk binary search over the runs.  Thread =
+// one count of the flat counts array; its mask is found by bisection of the n + 1 offsets; even runs (zeros) leave.
+__global__ void __launch_bounds__(256)
+rle_fill_runs_kernel(const uint32_t *__restrict__ ends, const int64_t *__restrict__ offsets, int n, size_t total, int H, int W,
+                     uint32_t *__restrict__ packed) {
+    const size_t g = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (g >= total) return;
+    int lo = 0, hi = n;                                 // the mask i with offsets[i] <= g < offsets[i + 1]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if ((size_t)__ldg(offsets + mid) <= g) lo = mid; else hi = mid;
+    }
+    const int i = lo;
+    const size_t o0 = (size_t)__ldg(offsets + i);
+    if (g >= (size_t)__ldg(offsets + i + 1)) return;    // counts past the last mask / empty masks in between
+    const size_t j = g - o0;
+    if (!(j & 1)) return;                               // odd runs are the ones
+    const unsigned area = (unsigned)H * (unsigned)W;
+    const unsigned a = min(__ldg(ends + g - 1), area), b = min(__ldg(ends + g), area);   // runs past H*W are cut
+    if (a >= b) return;
+    const int WB = W / 32;
+    uint32_t *plane = packed + (size_t)i * H * WB;
+    unsigned x = a / (unsigned)H, y = a - x * (unsigned)H;
+    for (unsigned idx = a; idx < b; ++idx) {
+        atomicOr(plane + (size_t)y * WB + (x >> 5), 1u << (x & 31));
+        if (++y == (unsigned)H) { y = 0; ++x; }
     }
 }
 
@@ -242,11 +258,13 @@ extern "C" int quber_rle_decode(const uint32_t *counts, const int64_t *offsets, 
     if (int rc = check_launch("rle_scan_kernel")) return rc;
     const dim3 grid(cdiv(W, RLE_THREADS), cdiv(H, RLE_ROWS), n);
     if (packed_out) {
-        rle_fill_kernel<true><<<grid, RLE_THREADS, 0, st>>>(ends, offsets, H, W, value, packed_out, nullptr);
-        if (int rc = check_launch("rle_fill_kernel<packed>")) return rc;
+        QUBER_CUDA_TRY(cudaMemsetAsync(packed_out, 0, (size_t)n * H * (W / 32) * sizeof(uint32_t), st));
+        if (total_counts > 0)
+            rle_fill_runs_kernel<<<(unsigned)((total_counts + 255) / 256), 256, 0, st>>>(ends, offsets, n, total_counts, H, W, packed_out);
+        if (int rc = check_launch("rle_fill_runs_kernel")) return rc;
     }
     if (masks_out) {
-        rle_fill_kernel<false><<<grid, RLE_THREADS, 0, st>>>(ends, offsets, H, W, value, nullptr, masks_out);
+        rle_fill_kernel<<<grid, RLE_THREADS, 0, st>>>(ends, offsets, H, W, value, masks_out);
         if (int rc = check_launch("rle_fill_kernel<bytes>")) return rc;
     }
     return QUBER_OK;

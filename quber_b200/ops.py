@@ -78,15 +78,20 @@ def encode_initial_masks(masks, sigma=10, valid_w=0, with_occupancy=False):
     return (out, occ) if with_occupancy else out
 
 
-def encode_initial_masks_packed(packed, value, masks_out, sigma=10, valid_w=0, with_occupancy=False):
-    """encode_initial_masks from bit-packed masks (host_pack_masks): packed int32 CUDA [B*K*H*W / 32], set pixels carry
-    `value`; masks_out uint8 CUDA [B,K,H,W] receives the byte planes (0 / value) on the way -> [B,3,H,W] float32
+def encode_initial_masks_packed(packed, value, masks_out, sigma=10, valid_w=0, with_occupancy=False, shape=None):
+    """encode_initial_masks from bit-packed masks (host_pack_masks / rle_decode): packed int32 CUDA [B*K*H*W / 32], set
+    pixels carry `value`; masks_out uint8 CUDA [B,K,H,W] receives the byte planes (0 / value) on the way, or None with
+    shape=(B,K,H,W) when nobody needs them (mask_boundary_bits works from the bits) -> [B,3,H,W] float32
     (and the tile occupancy with with_occupancy, see encode_initial_masks)."""
     _need_cuda(packed, "packed", torch.int32)
-    _need_cuda(masks_out, "masks_out", torch.uint8)
-    B, K, H, W = masks_out.shape
-    if packed.numel() * 32 != masks_out.numel():
-        raise ValueError("packed words do not match masks_out")
+    if masks_out is not None:
+        _need_cuda(masks_out, "masks_out", torch.uint8)
+        shape = tuple(masks_out.shape)
+    elif shape is None:
+        raise ValueError("encode_initial_masks_packed: give masks_out or shape")
+    B, K, H, W = shape
+    if packed.numel() * 32 != B * K * H * W:
+        raise ValueError("packed words do not match the mask shape")
     L = _lib.lib()
     out = torch.empty((B, 3, H, W), dtype=torch.float32, device=packed.device)
     occ = _occupancy(B, K, H, W, packed.device) if with_occupancy else None
@@ -150,6 +155,27 @@ def mask_boundary(masks, d, per_instance=True, union=True, fg=True, status=None,
     with torch.cuda.device(masks.device):
         _lib.check(_lib.lib().quber_mask_boundary(_ptr(masks), B, K, H, W, int(d), _ptr(per), _ptr(uni), _ptr(fgm),
                                                   _ptr(occupancy), _ptr(status), _stream()), "quber_mask_boundary")
+    return per, uni, fgm
+
+
+def mask_boundary_bits(packed, value, shape, d, per_instance=True, union=True, fg=True, occupancy=None):
+    """mask_boundary from bit planes (packed int32 CUDA [B*K*H*W / 32], set pixels carry `value` in the outputs; W % 32
+    == 0): the same three outputs without byte planes ever existing on the device."""
+    _need_cuda(packed, "packed", torch.int32)
+    B, K, H, W = shape
+    if packed.numel() * 32 != B * K * H * W:
+        raise ValueError("packed words do not match the mask shape")
+    dev = packed.device
+    per = torch.empty((B, K, H, W), dtype=torch.uint8, device=dev) if per_instance else None
+    uni = torch.empty((B, H, W), dtype=torch.uint8, device=dev) if union else None
+    fgm = torch.empty((B, H, W), dtype=torch.uint8, device=dev) if fg else None
+    if occupancy is not None:
+        _need_cuda(occupancy, "occupancy", torch.uint8)
+        if tuple(occupancy.shape) != tuple(_occupancy(B, K, H, W, "meta").shape) or not occupancy.is_contiguous():
+            raise ValueError("occupancy does not belong to masks of this shape")
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().quber_mask_boundary_bits(_ptr(packed), int(value), B, K, H, W, int(d), _ptr(per), _ptr(uni), _ptr(fgm),
+                                                       _ptr(occupancy), _stream()), "quber_mask_boundary_bits")
     return per, uni, fgm
 
 

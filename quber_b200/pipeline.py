@@ -78,16 +78,19 @@ class HotPath:
         return enc, per, uni, fg
 
     def encode_and_boundary_packed(self, st, c0, c1, w0, w1, value, status=None):
-        """encode_and_boundary for a chunk whose masks arrived bit-packed (refine_batch_host)."""
+        """encode_and_boundary for a chunk whose masks arrived bit-packed (refine_batch_host / refine_batch_rle): both kernels
+        work from the bit planes, no byte planes are written on the device (W % 32 == 0; other widths expand the bits and
+        take the byte kernels)."""
         c = self.cfg
         masks = st["masks"][c0:c1]
         B, K, H, W = masks.shape
-        if W % 16:                                # the packed encode shares the byte kernel's width rule
+        if W % 32:
             ops.unpack_masks(st["packed_dev"][w0:w1], masks.shape, value=value, out=masks)
             return self.encode_and_boundary(masks, status)
-        enc, occ = ops.encode_initial_masks_packed(st["packed_dev"][w0:w1], value, masks, c.sigma, c.valid_w, with_occupancy=True)
-        per, uni, fg = ops.mask_boundary(masks, ops.boundary_dilation(H, c.valid_w or W, c.boundary_ratio), status=status,
-                                         occupancy=occ)
+        words = st["packed_dev"][w0:w1]
+        enc, occ = ops.encode_initial_masks_packed(words, value, None, c.sigma, c.valid_w, with_occupancy=True, shape=(B, K, H, W))
+        per, uni, fg = ops.mask_boundary_bits(words, value, (B, K, H, W), ops.boundary_dilation(H, c.valid_w or W, c.boundary_ratio),
+                                              occupancy=occ)
         return enc, per, uni, fg
 
     def post(self, head, label_map_out=None):

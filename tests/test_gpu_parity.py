@@ -141,6 +141,45 @@ def test_boundary_with_encode_occupancy_is_identical(d, H, W):
         ops.mask_boundary(dm, d, occupancy=occ[:, :-1].contiguous())
 
 
+@pytest.mark.parametrize("d,H,W,value", [(1, 200, 288, 255), (8, 480, 640, 255), (16, 136, 416, 1), (17, 136, 416, 7), (40, 200, 288, 255),
+                                         (64, 100, 160, 128)])
+def test_boundary_from_bit_planes_equals_byte_kernel_and_oracle(d, H, W, value):
+    """quber_mask_boundary_bits (the planes as one bit per pixel, what the host-buffer routes hold) against the byte kernel
+    and the oracle: per-instance, union and foreground maps, with and without the encode pass' occupancy; overlapping
+    planes so that the uint8 wrap-around of the union sums matters (value 128: two planes sum to 0), masks touching the
+    image border and tile corners, an empty and a full plane; W a multiple of 32 but not of the 128-pixel tile."""
+    rng = np.random.default_rng(950 + d)
+    K = 8
+    m = np.zeros((2, K, H, W), np.uint8)
+    el = synth.ellipse_masks(5, H, W, seed=d, axes=(8, 60), margin=0, value=1)
+    m[0, :5] = el
+    m[1, 1:6] = el[::-1]
+    m[0, 5] = m[0, 4]                                                # identical planes: value 128 wraps to 0 in the sums
+    m[0, 6, 63:65, 127:129] = 1
+    m[0, 6, :3, :] = 1                                               # along the top border
+    m[1, 6] = rng.random((H, W)) < 0.3                               # speckle: every tile live, thin structures
+    m[1, 7] = 1                                                      # full plane: only the image border erodes
+    m *= np.uint8(value)
+    dm = cu(m)
+    words, v = ops.host_pack_masks(torch.from_numpy(m).pin_memory())
+    assert v == value
+    dw = words.cuda()
+    enc_p, occ = ops.encode_initial_masks_packed(dw, value, None, 10, with_occupancy=True, shape=m.shape)
+    enc_b, occ_b = ops.encode_initial_masks(dm, 10, with_occupancy=True)
+    assert torch.equal(enc_p, enc_b) and torch.equal(occ, occ_b)
+    per0, uni0, fg0 = ops.mask_boundary(dm, d)
+    for oc in (None, occ):
+        per1, uni1, fg1 = ops.mask_boundary_bits(dw, value, m.shape, d, occupancy=oc)
+        assert torch.equal(per0, per1) and torch.equal(uni0, uni1) and torch.equal(fg0, fg1)
+    _, uni2, fg2 = ops.mask_boundary_bits(dw, value, m.shape, d, per_instance=False, occupancy=occ)
+    assert torch.equal(uni0, uni2) and torch.equal(fg0, fg2)
+    for b in range(2):
+        p = np.stack([_oracle_boundary_d(x, d) for x in m[b]])
+        np.testing.assert_array_equal(per1[b].cpu().numpy(), p)
+    with pytest.raises(ValueError):
+        ops.mask_boundary_bits(dw[:-1], value, m.shape, d)
+
+
 def _oracle_boundary_d(mask, d):
     import ctypes
     out = np.empty_like(mask)

@@ -11,6 +11,20 @@ from quber_b200.pipeline import HotPath, RefinerConfig
 pytestmark = pytest.mark.gpu
 
 
+def _assert_staged(hp, hm):
+    """Every frame of the last host call reached the device by one of the two routes: its bytes in the byte staging
+    buffer, or its bits in the packed words (the packed route no longer expands them into bytes)."""
+    st = hp._stage
+    dm = hm.cuda()
+    ok_bytes = (st["masks"] == dm).flatten(1).all(1)
+    if dm[0].numel() % 32 == 0:
+        bits = ops.unpack_masks(st["packed_dev"], tuple(dm.shape), value=1)
+        ok_bits = ((bits != 0) == (dm != 0)).flatten(1).all(1)
+    else:
+        ok_bits = torch.zeros_like(ok_bytes)
+    assert bool((ok_bytes | ok_bits).all())
+
+
 def _inputs(B, K, H, W, seed):
     masks = np.stack([synth.ellipse_masks(K, H, W, seed=seed + b, axes=(14, 40), margin=30) for b in range(B)])
     heads = [synth.head_outputs(masks[b], seed=seed + b) for b in range(B)]
@@ -70,7 +84,7 @@ def test_refine_batch_host_packed_mask_transfer_is_identical():
         o0, k0 = plain.refine_batch_host(hm, hh, chunk_frames=2)
         o1, k1 = packed.refine_batch_host(hm, hh, chunk_frames=2)
         torch.cuda.current_stream().synchronize()
-        assert torch.equal(packed._stage["masks"], hm.cuda())
+        _assert_staged(packed, hm)
         for key in ("label_map", "boundary", "inst_start", "inst_counts"):
             assert torch.equal(o0[key], o1[key]), key
         for b in range(B):                                  # rows past inst_counts[b] are never written
@@ -85,7 +99,7 @@ def test_refine_batch_host_packed_mask_transfer_is_identical():
     o0, k0 = plain.refine_batch_host(hm, sets[0][1], chunk_frames=2)
     o1, k1 = packed.refine_batch_host(hm, sets[0][1], chunk_frames=2)
     torch.cuda.current_stream().synchronize()
-    assert torch.equal(packed._stage["masks"], hm.cuda())
+    _assert_staged(packed, hm)
     assert torch.equal(torch.cat([k[1] for k in k0]), torch.cat([k[1] for k in k1]))   # boundary values follow the mask's own value (util.py:72-90)
     for src in (sets[1][0], (sets[1][0] != 0).to(torch.uint8)):            # 0/255 as the reference's eval makes them, and 0/1
         words, value = ops.host_pack_masks(src)
@@ -130,7 +144,7 @@ def test_refine_batch_host_full_size_c2_packed_graphs_equal_resident():
         out, keep = hp.refine_batch_host(hm, hh, chunk_frames=16, min_tail=8, byte_frames=0)     # every frame bit-packed
         torch.cuda.current_stream().synchronize()
         assert [k[0].shape[0] for k in keep] == [16, 8, 8]
-        assert torch.equal(hp._stage["masks"], hm.cuda())
+        _assert_staged(hp, hm)
         assert np.array_equal(out["label_map"].numpy(), r["label_map"].cpu().numpy())
         assert np.array_equal(out["boundary"].numpy(), uni.cpu().numpy())
         assert np.array_equal(out["inst_counts"].numpy(), offs[1:] - offs[:-1])
@@ -277,7 +291,7 @@ def test_refine_batch_host_kernel_groups_and_uint8_label_map(B, chunk, tail, kf,
             assert torch.equal(o0[key], o1[key]), key
         assert torch.equal(torch.cat([k[0] for k in k1]), torch.cat([k[0] for k in k0]))
         assert torch.equal(torch.cat([k[1] for k in k1]), torch.cat([k[1] for k in k0]))
-        assert torch.equal(hp._stage["masks"], hm.cuda())
+        _assert_staged(hp, hm)
     if kf:
         hm2 = hm.clone().pin_memory()
         hm2[1][hm2[1] != 0] = 7                              # chunk (0, 2) now carries two values: byte route for it
@@ -289,7 +303,7 @@ def test_refine_batch_host_kernel_groups_and_uint8_label_map(B, chunk, tail, kf,
         assert sum(k[0].shape[0] for k in k1) == B and len(k1) > len(sizes)
         assert torch.equal(o0["boundary"], o1["boundary"])
         assert torch.equal(torch.cat([k[1] for k in k1]), torch.cat([k[1] for k in k0]))
-        assert torch.equal(hp._stage["masks"], hm2.cuda())
+        _assert_staged(hp, hm2)
 
 
 @pytest.mark.parametrize("B,K,H,W,kf", [(5, 7, 240, 320, 2), (8, 30, 480, 640, 0)])
@@ -312,7 +326,7 @@ def test_refine_batch_rle_equals_dense_host_call(B, K, H, W, kf):
         o1, k1 = sparse.refine_batch_rle(hc, ho, (B, K, H, W), hh, value=255, kernel_frames=kf)
         torch.cuda.current_stream().synchronize()
         assert int(o1["rle_status"][0]) == 0 and int(o1["status"][0]) == 0
-        assert torch.equal(sparse._stage["masks"], hm.cuda())
+        _assert_staged(sparse, hm)
         for key in ("label_map", "boundary", "inst_start", "inst_counts"):
             assert torch.equal(o0[key], o1[key]), key
         for b in range(B):
@@ -380,7 +394,7 @@ def test_refine_batch_host_hybrid_route_bytes_and_packed_side_by_side(B, nb, kf)
         for key in ("label_map", "boundary", "inst_start", "inst_counts"):
             assert torch.equal(o0[key], o1[key]), key
         assert torch.equal(torch.cat([k[0] for k in k1]), e0) and torch.equal(torch.cat([k[1] for k in k1]), p0)
-        assert torch.equal(hp._stage["masks"], hm.cuda())
+        _assert_staged(hp, hm)
     assert 0 <= hp.byte_frames_rule(32) <= 32
 
 
