@@ -74,6 +74,18 @@ size_t quber_occupancy_bytes(int B, int K, int H, int W);
 int quber_encode_initial_masks(const uint8_t *masks, int B, int K, int H, int W, int valid_w, int sigma,
                                const float *gauss, float *out, uint8_t *occupancy, void *workspace, size_t workspace_bytes,
                                void *stream);
+/* quber_encode_initial_masks for callers that cannot allocate and have no workspace to pass (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The scratch (quber_encode_workspace_bytes(B, K, H, W) bytes) lives in a static device array of
+ * QUBER_ENCODE_STATIC_SCRATCH_BYTES inside the library — every GPU that loads the library holds it until the process
+ * exits; larger problems are refused with QUBER_E_WORKSPACE (quber_last_cuda_error() names the sizes; C2's 32 frames of
+ * 640 x 480 with 30 masks need 9.9 MB).  The call allocates nothing.  All calls on a device share the array: calls that
+ * overlap on the GPU race, so keep them on one stream or order them with events.  Arguments and results as
+ * quber_encode_initial_masks. */
+#define QUBER_ENCODE_STATIC_SCRATCH_BYTES (16u << 20)
+size_t quber_encode_static_scratch_bytes(void);
+int quber_encode_initial_masks_static(const uint8_t *masks, int B, int K, int H, int W, int valid_w, int sigma,
+                                      const float *gauss, float *out, uint8_t *occupancy, void *stream);
 /* The same from bit-packed masks (quber_host_pack_masks / quber_rle_decode): packed dev uint32 [B*K*H*W / 32], set pixels
  * carry `value` (1..255).  masks_out (optional, NULL = not wanted): dev [B,K,H,W] uint8 receives the byte planes
  * (0 / value) — what quber_unpack_masks would give — on the way; quber_mask_boundary_bits works from the bits. */

@@ -42,6 +42,8 @@ SYMBOLS = {
     "quber_encode_workspace_bytes": (c_sz, [c_i, c_i, c_i, c_i]),
     "quber_occupancy_bytes": (c_sz, [c_i, c_i, c_i, c_i]),
     "quber_encode_initial_masks": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "quber_encode_static_scratch_bytes": (c_sz, []),
+    "quber_encode_initial_masks_static": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp]),
     "quber_encode_initial_masks_packed": (c_i, [c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "quber_boundary_dilation": (c_i, [c_i, c_i, c_d]),
     "quber_mask_boundary": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

@@ -253,3 +253,54 @@ extern "C" int quber_encode_initial_masks_packed(const uint32_t *packed, int val
     return encode_launch(reinterpret_cast<const uint8_t *>(packed), true, value, masks_out, B, K, H, W, valid_w, sigma, gauss, out,
                          occupancy, workspace, workspace_bytes, stream);
 }
+
+// ------------------------------------------------------------------------------------------------
+// quber_encode_initial_masks without any allocation anywhere: the scratch (per-mask sums + the last-mask map) lives in a
+// file-scope device array instead of a caller-provided workspace.  No counterpart in the reference; added
+// for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  Every GPU that loads the library holds QUBER_ENCODE_STATIC_SCRATCH_BYTES until the process exits.  All
+// calls on a device share the array: calls that overlap on the GPU (different streams) race — serialise them.  The array
+// keeps the previous call's contents; the sums, the only part that must start at zero, are cleared by every call (the
+// same cudaMemsetAsync as the workspace path), the last-mask map is fully rewritten for the tiles the call covers.
+// ------------------------------------------------------------------------------------------------
+namespace quber {
+static __device__ __align__(256) unsigned char g_encode_scratch[QUBER_ENCODE_STATIC_SCRATCH_BYTES];
+
+// In host code `g_encode_scratch` is only a handle for the symbol, not a device address: the address is asked of the
+// runtime once per device, with that device current.
+static int encode_scratch_address(void **ptr) {
+    constexpr int MAX_DEV = 64;
+    static void *addr[MAX_DEV] = {};
+    int dev = -1;
+    QUBER_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) return QUBER_E_UNSUPPORTED;
+    void *p = __atomic_load_n(&addr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        QUBER_CUDA_TRY(cudaGetSymbolAddress(&p, g_encode_scratch));     // the same answer from every thread: a benign race
+        if (!p) return QUBER_E_CUDA;
+        __atomic_store_n(&addr[dev], p, __ATOMIC_RELEASE);
+    }
+    *ptr = p;
+    return QUBER_OK;
+}
+}  // namespace quber
+
+extern "C" size_t quber_encode_static_scratch_bytes(void) { return QUBER_ENCODE_STATIC_SCRATCH_BYTES; }
+
+extern "C" int quber_encode_initial_masks_static(const uint8_t *masks, int B, int K, int H, int W, int valid_w, int sigma,
+                                                 const float *gauss, float *out, uint8_t *occupancy, void *stream) {
+    using namespace quber;
+    if (B <= 0 || K <= 0 || H <= 0 || W <= 0) return QUBER_E_INVALID;
+    const size_t need = quber_encode_workspace_bytes(B, K, H, W);
+    if (need > (size_t)QUBER_ENCODE_STATIC_SCRATCH_BYTES) {             // checked before any CUDA call
+        char msg[200];
+        snprintf(msg, sizeof(msg), "quber_encode_initial_masks_static: B=%d K=%d H=%d W=%d needs %zu bytes of scratch, the static array holds %zu",
+                 B, K, H, W, need, (size_t)QUBER_ENCODE_STATIC_SCRATCH_BYTES);
+        set_last_cuda_error(cudaErrorMemoryAllocation, msg);
+        return QUBER_E_WORKSPACE;
+    }
+    void *scratch = nullptr;
+    if (int rc = encode_scratch_address(&scratch)) return rc;
+    return encode_launch(masks, false, 0, nullptr, B, K, H, W, valid_w, sigma, gauss, out, occupancy, scratch,
+                         QUBER_ENCODE_STATIC_SCRATCH_BYTES, stream);
+}
