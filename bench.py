@@ -84,7 +84,7 @@ def workload_config(name, n_gpus, extra=None):
         "excluded": "cuDNN backbone/decoder/heads (SURVEY 8a A3-A5) and the decoder's GEMMs (asides `network`, `encoder`); "
                     "head outputs are synthetic",
         "l2": f"inputs larger than L2 ({NSETS} input sets alternated)",
-        "sharding": f"{n_gpus} x independent image batches" + (", ONE all_gather_into_tensor (label maps + counts) per step" if n_gpus > 1 else ""),
+        "sharding": f"{n_gpus} x independent image batches" + (", ONE all-gather (label maps + counts in one buffer) per step" if n_gpus > 1 else ""),
     }
     if extra:
         cfg.update(extra)
@@ -423,6 +423,21 @@ def run_ours(args):
         d2h = sum(v.numel() * v.element_size() for v in o.values())
         return inst / (t_ms * 1e-3), t_ms / n_steps, n_steps, d2h
 
+    # the collective's transport, and (outside every timed region) its result checked against a plain NCCL all-gather
+    gather_info = None
+    if world > 1:
+        torch.cuda.synchronize()
+        want = torch.empty((world, payload.nbytes), dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(want.view(-1), payload.buf)
+        payload.gather()
+        torch.cuda.synchronize()
+        same = bool(torch.equal(payload.all, want))
+        gather_info = {"gather_transport": payload.transport, "gather_verified_against_nccl": same,
+                       "gather_bytes_per_rank": int(payload.nbytes)}
+        if getattr(payload, "peer_copy_error", None):
+            gather_info["peer_copy_unavailable"] = payload.peer_copy_error[:200]
+        if not same:
+            raise RuntimeError("the gathered payload differs from an NCCL all-gather of the same buffers")
     e2e_val, e2e_ms, e2e_steps, d2h = time_e2e(e2e_dense)
     e2e_host = dict(time_e2e.host_ms)
     rle_val, rle_ms, _, _ = time_e2e(e2e_rle)
@@ -497,7 +512,7 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": args.warmup,
         "ms_per_step": ms / max_steps, "higher_is_better": True, "scaling": "strong" if "total_frames" in c else "weak",
         "vs_baseline": None, "dtype": "f32" if c["value"] == "f32" else "f32 (bf16 value tensor)",
-        "data": "synthetic", "config": workload_config(name, world), "clocks": clocks,
+        "data": "synthetic", "config": workload_config(name, world, gather_info), "clocks": clocks,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms, "steps": e2e_steps, "host_link": pcie,
                 "calls_in_flight": E2E_DEPTH, "ms_per_step_one_call_in_flight": e2e_ms_sync,

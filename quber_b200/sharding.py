@@ -50,21 +50,65 @@ class Payload:
     """The ONE buffer a rank contributes to the step's collective: the uint8 label maps [B,H,W] followed (16-byte
     aligned) by the int32 instance counts [B].  quber_post_process writes the maps straight into `maps`
     (ops.post_process(label_map_out=...)), the counts are a B-element copy; `gather()` is then a single
-    all_gather_into_tensor — north_star: "results are collected with a single NCCL all-gather"."""
+    all-gather — north_star: "results are collected with a single NCCL all-gather".
 
-    def __init__(self, B, H, W, device, world=1):
+    Transport of that all-gather (`self.transport`):
+      "peer_copy"  one process per GPU on an NVLink / NVSwitch box: the gathered buffer of every rank is symmetric memory
+                   (torch.distributed._symmetric_memory), each rank PUSHES its payload into row `rank` of every peer's
+                   buffer with plain device-to-device copies — copy engines over NVLink, no SM and no NCCL kernel under
+                   the memory-bound kernels of the next step — between two device-side barriers (nobody still reads the
+                   previous contents / everybody's rows have landed).
+      "nccl"       all_gather_into_tensor, when symmetric memory cannot be set up on every rank.
+      "gloo"       all_gather (CPU tests).
+    """
+
+    def __init__(self, B, H, W, device, world=1, group=None, peer_copy=True):
         self.B, self.H, self.W, self.world = B, H, W, world
         self.map_bytes = (B * H * W + 15) // 16 * 16
         self.nbytes = self.map_bytes + 4 * B
         self.buf = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
         self.maps = self.buf[: B * H * W].view(B, H, W)
         self.counts = self.buf[self.map_bytes:].view(torch.int32)
-        self.all = torch.empty((world, self.nbytes), dtype=torch.uint8, device=device) if world > 1 else self.buf[None]
+        self.transport = "local"
+        self._peer_rows = None
+        if world > 1:
+            self.transport = "nccl" if dist.get_backend(group) == "nccl" else "gloo"
+            if self.transport == "nccl" and peer_copy:
+                self._setup_peer_copy(device, group)
+            if self._peer_rows is None:
+                self.all = torch.empty((world, self.nbytes), dtype=torch.uint8, device=device)
+        else:
+            self.all = self.buf[None]
+
+    def _setup_peer_copy(self, device, group):
+        """Symmetric `all` buffer + this rank's row in every peer's copy of it.  Every rank must end up on the same
+        transport: the outcome is agreed with one all-reduce."""
+        ok, rows, all_, hdl = 1, None, None, None
+        try:
+            import torch.distributed._symmetric_memory as symm
+            g = group if group is not None else dist.group.WORLD
+            rank = dist.get_rank(g)
+            all_ = symm.empty((self.world, self.nbytes), dtype=torch.uint8, device=device)
+            hdl = symm.rendezvous(all_, g)
+            rows = [hdl.get_buffer(r, (self.world, self.nbytes), torch.uint8)[rank] for r in range(self.world)]
+            order = [(rank + 1 + i) % self.world for i in range(self.world)]       # start at the neighbour: no hot peer
+            rows = [rows[r] for r in order]
+        except Exception as e:                                   # noqa: BLE001 — any failure means "use NCCL"
+            ok, self.peer_copy_error = 0, f"{type(e).__name__}: {e}"
+        flag = torch.tensor([ok], dtype=torch.int32, device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag[0]) == 1:
+            self.all, self._peer_rows, self._hdl, self.transport = all_, rows, hdl, "peer_copy"
 
     def gather(self, group=None):
-        """-> (maps [G,B,H,W] uint8, counts [G,B] int32) on every rank; one collective."""
-        if self.world > 1:
-            if dist.get_backend(group) == "nccl":
+        """-> (maps [G,B,H,W] uint8, counts [G,B] int32) on every rank; one collective, on the current stream."""
+        if self._peer_rows is not None:
+            self._hdl.barrier(channel=0)                          # every rank is done with the previous contents of its `all`
+            for row in self._peer_rows:
+                row.copy_(self.buf, non_blocking=True)
+            self._hdl.barrier(channel=1)                          # every rank's pushes (stream-ordered before its arrival) have landed
+        elif self.world > 1:
+            if self.transport == "nccl":
                 dist.all_gather_into_tensor(self.all.view(-1), self.buf, group=group)
             else:
                 dist.all_gather(list(self.all.unbind(0)), self.buf, group=group)

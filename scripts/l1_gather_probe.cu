@@ -13,8 +13,8 @@
 constexpr int M = 8, D = 32, L = 3, P = 4;
 __constant__ int c_h[L], c_w[L], c_start[L];
 
-template <int VARIANT>
-__global__ void __launch_bounds__(256, 5) probe(const float *__restrict__ value, int S, int Q, float *__restrict__ out) {
+template <int VARIANT, int MINB>
+__global__ void __launch_bounds__(256, MINB) probe(const float *__restrict__ value, int S, int Q, float *__restrict__ out) {
     const int tid = threadIdx.x, lane = tid & 7, grp = tid >> 3;
     const int m = blockIdx.y, b = blockIdx.z;
     const int q = min(blockIdx.x * 32 + grp, Q - 1);
@@ -65,21 +65,33 @@ int main() {
     dim3 grid((Q + 31) / 32, M, B);
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
-    for (int variant = 0; variant < 2; ++variant) {
-        for (int i = 0; i < 4; ++i) {
-            if (variant == 0) probe<0><<<grid, 256>>>(val[i & 1], S, Q, out); else probe<1><<<grid, 256>>>(val[i & 1], S, Q, out);
+    auto run = [&](int variant, int minb, int smem, int i) {
+#define P_(V, MB) probe<V, MB><<<grid, 256, smem>>>(val[i & 1], S, Q, out)
+        if (variant == 0) { if (minb == 5) P_(0, 5); else if (minb == 6) P_(0, 6); else P_(0, 8); }
+        else { if (minb == 5) P_(1, 5); else if (minb == 6) P_(1, 6); else P_(1, 8); }
+#undef P_
+    };
+    // resident CTAs per SM: asked of the compiler (registers) and limited from above by dynamic shared memory
+    const int cfg[][2] = {{5, 72 * 1024}, {5, 44 * 1024}, {5, 0}, {6, 0}, {8, 0}};       // -> 3, 5, 5 (by registers: up to 8), 6.., 8
+    for (auto &c : cfg) {
+        cudaFuncSetAttribute(probe<0, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+        cudaFuncSetAttribute(probe<1, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+        for (int variant = 0; variant < 2; ++variant) {
+            for (int i = 0; i < 4; ++i) run(variant, c[0], c[1], i);
+            cudaDeviceSynchronize();
+            const int N = 20;
+            cudaEventRecord(e0);
+            for (int i = 0; i < N; ++i) run(variant, c[0], c[1], i);
+            cudaEventRecord(e1); cudaEventSynchronize(e1);
+            float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+            int nb = 0;
+            if (c[0] == 5) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, probe<0, 5>, 256, c[1]);
+            else if (c[0] == 6) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, probe<0, 6>, 256, c[1]);
+            else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, probe<0, 8>, 256, c[1]);
+            const double lines = (double)B * Q * M * (variant == 0 ? 48 : 24);
+            printf("minb %d smem %d KB (%d CTAs/SM) variant %d (%d corner lines per (query, head)): %.1f us/launch, %.2f TB/s through L1, err=%d\n",
+                   c[0], c[1] / 1024, nb, variant, variant == 0 ? 48 : 24, ms / N * 1e3, lines * 128 / (ms / N * 1e-3) / 1e12, (int)cudaGetLastError());
         }
-        cudaDeviceSynchronize();
-        const int N = 20;
-        cudaEventRecord(e0);
-        for (int i = 0; i < N; ++i) {
-            if (variant == 0) probe<0><<<grid, 256>>>(val[i & 1], S, Q, out); else probe<1><<<grid, 256>>>(val[i & 1], S, Q, out);
-        }
-        cudaEventRecord(e1); cudaEventSynchronize(e1);
-        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
-        const double lines = (double)B * Q * M * (variant == 0 ? 48 : 24);
-        printf("variant %d (%d corner lines per (query, head)): %.1f us/launch, %.2f TB/s through L1 (128 B per line), err=%d\n", variant,
-               variant == 0 ? 48 : 24, ms / N * 1e3, lines * 128 / (ms / N * 1e-3) / 1e12, (int)cudaGetLastError());
     }
     return 0;
 }
