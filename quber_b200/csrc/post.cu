@@ -903,6 +903,40 @@ static int post_validate(const quber_post_params *p) {
     return QUBER_OK;
 }
 
+namespace quber {
+// The error-map pass (eee_kernel) depends on nothing but the call's inputs, and it is a pure store stream, while the centre
+// chain beside it (NMS -> select -> grouping -> relabel -> offsets) is compute- and latency-bound with several one-CTA-per-
+// image steps that leave the GPU almost idle.  It is therefore forked onto a low-priority side stream at the start of the
+// call and joined at its end (event fork / join: legal under CUDA graph capture, the side stream joins the capture).
+// One side stream and two events per host thread and device, created on first use.
+struct PostFork { cudaStream_t side = nullptr; cudaEvent_t fork = nullptr, join = nullptr; };
+static int post_fork(cudaStream_t st, PostFork **out) {
+    constexpr int MAX_DEV = 64;
+    static thread_local PostFork pf[MAX_DEV];
+    int dev = -1;
+    *out = nullptr;                                                          // no fork: everything on the caller's stream
+    QUBER_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) return QUBER_OK;
+    PostFork &f = pf[dev];
+    if (!f.side) {
+        // streams and events must not be created while the caller's stream is being captured: the first call of a thread
+        // under capture stays on one stream
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        QUBER_CUDA_TRY(cudaStreamIsCapturing(st, &cs));
+        if (cs != cudaStreamCaptureStatusNone) return QUBER_OK;
+        int lo = 0, hi = 0;
+        QUBER_CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        cudaStream_t s = nullptr;
+        QUBER_CUDA_TRY(cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, lo));
+        QUBER_CUDA_TRY(cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming));
+        QUBER_CUDA_TRY(cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming));
+        f.side = s;
+    }
+    *out = &f;
+    return QUBER_OK;
+}
+}  // namespace quber
+
 extern "C" size_t quber_post_workspace_bytes(const quber_post_params *p) {
     if (post_validate(p) != QUBER_OK) return 0;
     return quber::carve(*p, reinterpret_cast<void *>(4096)).total;
@@ -928,6 +962,24 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
     QUBER_CUDA_TRY(cudaMemsetAsync(workspace, 0, ws.zero_bytes, st));
     QUBER_CUDA_TRY(cudaMemsetAsync(io.status, 0, sizeof(int32_t), st));
 
+    dim3 pgrid(cdiv(p.W, P_TW), cdiv(p.H, P_TH), p.B);
+    const bool has_eee = p.eee_channels > 0 && io.eee && (io.eee_full || io.eee_onehot);
+    PostFork *fk = nullptr;
+    if (has_eee) {
+        // the error maps: a pure streaming pass of their own (measured, C2: fused with grouping 172 us; 99 + 66 us split),
+        // forked beside the centre chain
+        if (int rc = post_fork(st, &fk)) return rc;
+        cudaStream_t es = st;
+        if (fk) {
+            QUBER_CUDA_TRY(cudaEventRecord(fk->fork, st));
+            QUBER_CUDA_TRY(cudaStreamWaitEvent(fk->side, fk->fork, 0));
+            es = fk->side;
+        }
+        if (p.scale == 4) eee_kernel<true><<<pgrid, P_THREADS, 0, es>>>(p, io);
+        else eee_kernel<false><<<pgrid, P_THREADS, 0, es>>>(p, io);
+        if (int rc = check_launch("eee_kernel")) return rc;
+        if (fk) QUBER_CUDA_TRY(cudaEventRecord(fk->join, fk->side));
+    }
     if (!(p.flags & QUBER_POST_GIVEN_CENTERS)) {
         const int TWp = N_TW + p.nms_kernel - 1, THp = N_TH + p.nms_kernel - 1;
         const size_t smem = ((size_t)THp * TWp + (size_t)THp * N_TW) * sizeof(float);
@@ -938,10 +990,8 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
                                                          ws.bitmask, io.centers_yx, io.n_centers, io.status);
         if (int rc = check_launch("center_select_kernel")) return rc;
     }
-    dim3 pgrid(cdiv(p.W, P_TW), cdiv(p.H, P_TH), p.B);
     {
         const size_t gsmem = ((size_t)p.top_k + 1) * sizeof(InstStat) + (size_t)p.top_k * sizeof(float2) + (((size_t)p.top_k + 31) / 32) * 4;
-        const bool has_eee = p.eee_channels > 0 && io.eee && (io.eee_full || io.eee_onehot);
         if (gsmem > 48 * 1024) {
             QUBER_CUDA_TRY(cudaFuncSetAttribute(group_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem));
             QUBER_CUDA_TRY(cudaFuncSetAttribute(group_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem));
@@ -949,12 +999,6 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
         if (p.scale == 4) group_kernel<true><<<pgrid, P_THREADS, gsmem, st>>>(p, io, io.n_centers, ws.ins, ws.stats);
         else group_kernel<false><<<pgrid, P_THREADS, gsmem, st>>>(p, io, io.n_centers, ws.ins, ws.stats);
         if (int rc = check_launch("group_kernel")) return rc;
-        // the error maps are a pure streaming pass of their own (measured, C2: fused 172 us; 99 + 66 us split)
-        if (has_eee) {
-            if (p.scale == 4) eee_kernel<true><<<pgrid, P_THREADS, 0, st>>>(p, io);
-            else eee_kernel<false><<<pgrid, P_THREADS, 0, st>>>(p, io);
-            if (int rc = check_launch("eee_kernel")) return rc;
-        }
     }
     relabel_kernel<<<p.B, SEL_THREADS, 0, st>>>(p, io.n_centers, ws.stats, ws.newid, ws.oldid, ws.n_inst, ws.has_stuff);
     if (int rc = check_launch("relabel_kernel")) return rc;
@@ -966,7 +1010,9 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
         if (int rc = check_launch("emit_kernel")) return rc;
     }
     finalize_kernel<<<p.B, P_THREADS, 0, st>>>(p, io, ws.n_inst, ws.has_stuff, ws.stats, ws.oldid);
-    return check_launch("finalize_kernel");
+    if (int rc = check_launch("finalize_kernel")) return rc;
+    if (fk) QUBER_CUDA_TRY(cudaStreamWaitEvent(st, fk->join, 0));        // join: the error maps belong to this call's results
+    return QUBER_OK;
 }
 
 extern "C" size_t quber_filter_workspace_bytes(int B, int max_per) {

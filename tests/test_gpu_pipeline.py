@@ -482,3 +482,33 @@ def test_two_host_calls_in_flight_on_alternating_slots(route):
         for k in keys:
             assert torch.equal(o[k], want[(i - 1) % 2][k]), (i - 1, k)
     assert two._stages[0]["masks"].data_ptr() != two._stages[1]["masks"].data_ptr()
+
+
+def test_post_process_graph_capture_with_and_without_forked_error_maps():
+    """quber_post_process forks its error-map pass onto a side stream (event fork / join).  Captured into a CUDA graph it
+    must replay to the eager results both when the side stream already exists (this thread has called it before) and on
+    a host thread's very first call, which happens under capture and therefore stays on one stream."""
+    import threading
+    B, K, H, W = 3, 6, 240, 320
+    _, head = _inputs(B, K, H, W, seed=1234)
+    dh = {k: torch.from_numpy(v).cuda() for k, v in head.items()}
+    hp = HotPath(RefinerConfig(), "cuda")
+    want = hp.post(dh)
+    torch.cuda.synchronize()
+    keys = ("label_map", "eee_onehot", "eee_full", "masks", "inst_offsets")
+    result = {}
+
+    def capture_and_replay(tag):
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=s):
+                r = hp.post(dh)
+            for _ in range(2):
+                g.replay()
+            s.synchronize()
+            result[tag] = all(torch.equal(r[k], want[k]) for k in keys if k in want and want[k] is not None)
+    capture_and_replay("forked")                            # this thread's side stream exists since the eager call above
+    t = threading.Thread(target=capture_and_replay, args=("first_call_under_capture",))
+    t.start(); t.join()
+    assert result == {"forked": True, "first_call_under_capture": True}
