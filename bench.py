@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — refined instances/s of the maskrefiner hot path on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c2|c3|c4|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c1|c2|c3|c4|c5]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 One "step" = one pass of the hot path over one batch of synthetic input per GPU.  Default workload = C2 of
@@ -47,6 +47,9 @@ M_HEADS, D_HEAD, N_POINTS = 8, 32, 4
 # BASELINE.json configs (SURVEY §8-d "Config -> concrete run").  H x W = the frames; Wp = zero-padded row pitch of the
 # mask planes (W % 16 == 0 for the kernels); head = the 1/4-resolution head outputs' size.
 CONFIGS = {
+    "c1": dict(B=1, K=20, H=480, W=640, axes=(20, 60), margin=60, levels=((60, 80), (30, 40), (15, 20)), value="f32",
+               name="C1: ONE 640x480 RGB-D frame per step, 20 initial masks, fp32 — the reference's own CPU-runnable case on "
+                    "the GPU at batch 1 (BASELINE.json configs[0])"),
     "c2": dict(B=32, K=30, H=480, W=640, axes=(20, 60), margin=60, levels=((60, 80), (30, 40), (15, 20)), value="f32",
                name="C2: 32 frames 640x480 RGB-D per GPU per step, 30 initial masks each, fp32 (BASELINE.json configs[1])"),
     "c3": dict(B=32, K=60, H=480, W=640, axes=(10, 40), margin=40, levels=((60, 80), (30, 40), (15, 20)), value="bf16",

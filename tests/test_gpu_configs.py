@@ -28,6 +28,31 @@ def _post_vs_oracle(masks, seed, max_instances):
     return len(ref["labels"])
 
 
+# ------------------------------------------------------------------ C1: the reference's own CPU case (one frame, K = 20)
+def test_c1_single_frame_20_masks_whole_path():
+    """BASELINE.json configs[0]: ONE 640x480 frame with 20 initial masks — the shape the reference runs on a CPU.  Encode,
+    boundaries (with and without the encode pass' occupancy), the six sampling layers' operands and post-processing
+    against the oracle at batch 1."""
+    K, H, W = 20, 480, 640
+    masks = synth.ellipse_masks(K, H, W, seed=100, axes=(20, 60), margin=60)
+    dm = cu(masks)[None]
+    enc, occ = ops.encode_initial_masks(dm, with_occupancy=True)
+    np.testing.assert_array_equal(enc[0].cpu().numpy(), oracle.encode_initial_masks(masks))
+    d = ops.boundary_dilation(H, W, 0.01)
+    u, p = oracle.masks_to_boundary(masks, 0.01, return_per_instance=True)
+    for oc in (None, occ):
+        per, uni, fg = ops.mask_boundary(dm, d, occupancy=oc)
+        np.testing.assert_array_equal(per[0].cpu().numpy(), p)
+        np.testing.assert_array_equal(uni[0].cpu().numpy(), u)
+    inp = synth.msda_inputs(B=1, mode="module", seed=100, operands=True)
+    got = ops.msda_forward_fused(cu(inp["value"]), cu(inp["shapes"]), cu(inp["starts"]), cu(inp["oa"]), cu(inp["ref"]), 3, 4,
+                                 levels=((60, 80), (30, 40), (15, 20)))
+    sel = np.r_[0:200, 4700:4900, 6200:6300]
+    want = oracle.msda_forward(inp["value"], inp["shapes"], inp["starts"], inp["loc"][:, sel], inp["attn"][:, sel])
+    np.testing.assert_allclose(got[0, sel].cpu().numpy(), want[0], rtol=0, atol=1e-6)
+    assert _post_vs_oracle(masks, 100, max_instances=200) >= 5
+
+
 # ------------------------------------------------------------------ C3: dense clutter, K = 60
 @pytest.mark.parametrize("seed", [300, 301])
 def test_c3_clutter_encode_boundary_post(seed):
