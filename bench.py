@@ -718,9 +718,21 @@ def cpu_baseline(name, budget_s=20.0):
     for _ in range(min(reps, 3)):
         a, b_ = _run_cpu(frames, cores)
         n += a; t += b_
-    return {"value": n / t, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{len(frames)} frames of the same workload ({name}: K={c['K']}, {c['W']}x{c['H']}, msda x{N_LAYERS}), one frame per "
-                      f"thread, {min(reps, 3)} repetition(s), oracle/quber_oracle.c; single-core: {n1 / t1:.2f} instances/s"}
+    out = {"value": n / t, "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": f"{len(frames)} frames of the same workload ({name}: K={c['K']}, {c['W']}x{c['H']}, msda x{N_LAYERS}), one frame per "
+                     f"thread, {min(reps, 3)} repetition(s), oracle/quber_oracle.c; single-core: {n1 / t1:.2f} instances/s"}
+    # the reference's OWN Python cannot run on the GPU box (no /root/reference there): quote the line recorded where it can
+    rec = os.path.join(ROOT, "profiles", "r02_bench_ref_reference_python_build_container.json")
+    if name == "c2" and os.path.exists(rec):
+        try:
+            txt = open(rec).read()
+            r = json.loads(txt[txt.index("{"):])
+            out["reference_python_recorded"] = {"value": r["value"], "unit": r["unit"], "cores": r["cpu_baseline"]["cores"],
+                                                "where": "build container (bench.py --impl reference with /root/reference readable)",
+                                                "source": os.path.basename(rec)}
+        except Exception:
+            pass
+    return out
 
 
 def _reference_python_available():
