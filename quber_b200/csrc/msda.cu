@@ -345,7 +345,7 @@ msda_forward_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__
 // ------------------------------------------------------------------------------------------------
 struct LevelTab { int h[4], w[4], start[4]; };
 
-template <int D, typename VT, int MINB, int L, bool CLV>
+template <int D, typename VT, int MINB, int L, bool CLV, bool ALLREC = false>
 __global__ void __launch_bounds__(256, MINB)
 msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ shapes, const int64_t *__restrict__ starts,
                      const float *__restrict__ oa, int ld, const float *__restrict__ ref, int S, int M, int Q,
@@ -361,7 +361,8 @@ msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ s
     constexpr int GPB = 256 / LPG;
     constexpr int GPW = 32 / LPG;
     __shared__ int s_h[MSDA_MAX_L], s_w[MSDA_MAX_L], s_start[MSDA_MAX_L];
-    __shared__ __align__(16) uint4 s_rec[8 * GPW * (LPG + 1)];
+    constexpr int RPG = ALLREC ? LP + 1 : LPG + 1;      // record slots per group (+1: bank spread)
+    __shared__ __align__(16) uint4 s_rec[8 * GPW * RPG];
     const int tid = threadIdx.x;
     const int lane = tid % LPG, grp = tid / LPG;
     const int m = blockIdx.y, b = blockIdx.z;
@@ -416,7 +417,7 @@ msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ s
     float acc[CPL];
 #pragma unroll
     for (int c = 0; c < CPL; ++c) acc[c] = 0.f;
-    uint4 *rec = s_rec + (tid >> 5) * (GPW * (LPG + 1)) + ((tid & 31) / LPG) * (LPG + 1);
+    uint4 *rec = s_rec + (tid >> 5) * (GPW * RPG) + ((tid & 31) / LPG) * RPG;
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
         const int s0 = r * LPG;
@@ -451,6 +452,31 @@ msda_fused_p4_kernel(const VT *__restrict__ value, const int64_t *__restrict__ s
         uint32_t pitch[NLR];
 #pragma unroll
         for (int k = 0; k < NLR; ++k) pitch[k] = (uint32_t)lv_w(min(s0 / P + k, L - 1)) * MDu;
+        if (ALLREC) {                                    // all rounds' records first, then one uninterrupted gather phase
+            if (tap < LP) rec[tap] = make_uint4(o1, __float_as_uint(A), __float_as_uint(Bw), __float_as_uint(f));
+            if (r + 1 < NR) continue;
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < LP; ++j) {
+                const uint4 ra = rec[j];
+                const uint32_t dx = (uint32_t)((int32_t)ra.x >> 31) & MDu;
+                const uint32_t dy = (uint32_t)((int32_t)(ra.x << 1) >> 31) & ((uint32_t)lv_w(j / P) * MDu);
+                uint32_t a1 = ra.x & 0x3fffffffu;
+                asm volatile("" : "+r"(a1));
+                const uint32_t a3 = a1 + dy;
+                const float bf = __uint_as_float(ra.w), bg = 1.f - bf;
+                const float b1 = __uint_as_float(ra.y) * bg, b2 = __uint_as_float(ra.y) * bf;
+                const float b3 = __uint_as_float(ra.z) * bg, b4 = __uint_as_float(ra.z) * bf;
+                uint32_t r1[NW], r2[NW], r3[NW], r4[NW];
+                ld_corner<VB>(vlane + (size_t)a1 * VB, r1);
+                ld_corner<VB>(vlane + (size_t)(a1 + dx) * VB, r2);
+                ld_corner<VB>(vlane + (size_t)a3 * VB, r3);
+                ld_corner<VB>(vlane + (size_t)(a3 + dx) * VB, r4);
+                fma_corner<VT, NW>(b1, r1, acc); fma_corner<VT, NW>(b2, r2, acc);
+                fma_corner<VT, NW>(b3, r3, acc); fma_corner<VT, NW>(b4, r4, acc);
+            }
+            continue;
+        }
         rec[lane] = make_uint4(o1, __float_as_uint(A), __float_as_uint(Bw), __float_as_uint(f));
         __syncwarp();
 #pragma unroll
@@ -498,9 +524,13 @@ static int launch_fused(const void *value, const int64_t *shapes, const int64_t 
     LevelTab lv = {};
     if (levels_host)
         for (int l = 0; l < L; ++l) { lv.h[l] = levels_host[3 * l]; lv.w[l] = levels_host[3 * l + 1]; lv.start[l] = levels_host[3 * l + 2]; }
+    // Parameter-bank variant: all L*P tap records are prepared first and the gathers run as one uninterrupted phase
+    // (ALLREC); without the shared-memory level table the fp32 kernel fits 40 registers = 6 CTAs per SM.  Measured at C2,
+    // us per launch: fp32 474 -> 463 (6 CTAs; 5 CTAs with ALLREC 491, 6 without 487), bf16 350 -> 343 (5 CTAs; 6: 352).
+    constexpr int CLV_MINB = sizeof(VT) == 4 ? 6 : 5;
 #define QUBER_FUSED(LL)                                                                                                         \
     case LL:                                                                                                                    \
-        if (levels_host) msda_fused_p4_kernel<D, VT, 5, LL, true><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o, lv);  \
+        if (levels_host) msda_fused_p4_kernel<D, VT, CLV_MINB, LL, true, true><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o, lv);  \
         else msda_fused_p4_kernel<D, VT, 5, LL, false><<<grid, 256, 0, st>>>(v, shapes, starts, oa, ld, ref, S, M, Q, o, lv);          \
         break;
     switch (L) {
