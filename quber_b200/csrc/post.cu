@@ -76,6 +76,58 @@ static PostWs carve(const quber_post_params &p, void *base) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Eight consecutive full-resolution pixels (x0 .. x0+7, x0 % 8 == 0) of row y, sampled from a 1/4-resolution plane
+// with EXACTLY UpSampler::at's arithmetic (same products, same sums, same rounding), but with the per-row and
+// per-column set-up shared by every plane and 8 loads per plane instead of 32: at scale 4 the eight pixels only
+// touch source columns 2m-1 .. 2m+2 (m = x0 / 8).  Column c[i] is clamped into the plane, which reproduces the
+// reference's `+ (x1 < w - 1)` step at the right edge; at the left edge (m == 0) the clamped source coordinate
+// makes pixels 0 and 1 read columns (0, 1) instead of (-1, 0).
+// ------------------------------------------------------------------------------------------------
+struct Row8 {
+    int top, bot;            // element offsets of the two source rows
+    int c0, c1, c2, c3;      // the four source columns
+    float ly, hy;
+    float lx[8];
+    bool left;
+    __device__ __forceinline__ Row8(const UpSampler &up, int y, int x0) {
+        float sy = __fsub_rn(__fmul_rn(up.r, __fadd_rn((float)y, 0.5f)), 0.5f);
+        sy = sy < 0.f ? 0.f : sy;
+        const int y1 = (int)sy;
+        top = y1 * up.w;
+        bot = top + ((y1 < up.h - 1) ? up.w : 0);
+        ly = __fsub_rn(sy, (float)y1);
+        hy = __fsub_rn(1.f, ly);
+        const int m2 = x0 >> 2;                          // 2m
+        left = m2 == 0;
+        c0 = max(m2 - 1, 0); c1 = m2; c2 = min(m2 + 1, up.w - 1); c3 = min(m2 + 2, up.w - 1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float sx = __fsub_rn(__fmul_rn(up.r, __fadd_rn((float)(x0 + j), 0.5f)), 0.5f);
+            sx = sx < 0.f ? 0.f : sx;
+            const int x1 = (int)sx;
+            lx[j] = __fsub_rn(sx, (float)x1);
+        }
+    }
+    __device__ __forceinline__ void sample(const float *__restrict__ plane, float *out) const {
+        const float *t = plane + top, *b = plane + bot;
+        const float t0 = __ldg(t + c0), t1 = __ldg(t + c1), t2 = __ldg(t + c2), t3 = __ldg(t + c3);
+        const float b0 = __ldg(b + c0), b1 = __ldg(b + c1), b2 = __ldg(b + c2), b3 = __ldg(b + c3);
+        // pixel j reads source columns (x1, x1 + 1): j = 0,1 -> (2m-1, 2m); 2..5 -> (2m, 2m+1); 6,7 -> (2m+1, 2m+2)
+        const float ta[8] = {left ? t1 : t0, left ? t1 : t0, t1, t1, t1, t1, t2, t2};
+        const float tb[8] = {left ? t2 : t1, left ? t2 : t1, t2, t2, t2, t2, t3, t3};
+        const float ba[8] = {left ? b1 : b0, left ? b1 : b0, b1, b1, b1, b1, b2, b2};
+        const float bb[8] = {left ? b2 : b1, left ? b2 : b1, b2, b2, b2, b2, b3, b3};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float hx = __fsub_rn(1.f, lx[j]);
+            const float tp = __fadd_rn(__fmul_rn(hx, ta[j]), __fmul_rn(lx[j], tb[j]));
+            const float bt = __fadd_rn(__fmul_rn(hx, ba[j]), __fmul_rn(lx[j], bb[j]));
+            out[j] = __fadd_rn(__fmul_rn(hy, tp), __fmul_rn(ly, bt));
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
 // find_instance_center, part 1: threshold + kxk max-pool NMS -> candidate bit mask.
 // post_processing.py:22-29.  Candidate <=> thresholded value equals its window maximum and is > 0
 // (only positive survivors can pass the final `> max(kth, 0)` test at :37/:41).
@@ -87,7 +139,7 @@ center_nms_kernel(const float *__restrict__ center, quber_post_params pp, uint32
     const float threshold = pp.threshold;
     const int p = (nms_kernel - 1) / 2;
     const int TWp = N_TW + nms_kernel - 1, THp = N_TH + nms_kernel - 1;
-    float *T = nsm, *RM = nsm + THp * TWp;        // RM: [THp][N_TW]
+    float *T = nsm, *RM = nsm + THp * TWp;        // RM: [THp][N_TW] (moved behind the wider T on the fast path)
     const UpSampler up = up_of(pp);
     const int b = blockIdx.z, ty0 = blockIdx.y * N_TH, tx0 = blockIdx.x * N_TW;
     const float *plane = center + (size_t)b * up.h * up.w;
@@ -114,21 +166,44 @@ center_nms_kernel(const float *__restrict__ center, quber_post_params pp, uint32
             return;
         }
     }
-    for (int idx = tid; idx < THp * TWp; idx += P_THREADS) {
-        const int r = idx / TWp, c = idx - r * TWp;
-        const int gy = ty0 - p + r, gx = tx0 - p + c;
-        float t = -INFINITY;                         // max_pool2d pads with -inf (columns past the cropped width too)
-        if (gy >= 0 && gy < H && gx >= 0 && gx < Wv) {
-            const float v = up.at(plane, gy, gx);
-            t = v > threshold ? v : -1.0f;          // F.threshold(x, thr, -1)
+    // x4 maps with a halo of at most 8: the staged rows start 8 columns left of the tile, so that every thread up-samples
+    // 8 consecutive, 8-aligned pixels of one row with the shared set-up of Row8 (the same arithmetic, operation for
+    // operation, as UpSampler::at) instead of one pixel at a time
+    const bool fast = scale == 4 && p <= 8;
+    const int TWs = fast ? N_TW + 16 : TWp, xoff = fast ? 8 - p : 0;      // row pitch of T, column of the window's first tap
+    if (fast) {
+        RM = nsm + THp * TWs;
+        constexpr int UPR = (N_TW + 16) / 8;
+        for (int u = tid; u < THp * UPR; u += P_THREADS) {
+            const int r = u / UPR, cu = u - r * UPR;
+            const int gy = ty0 - p + r, gx0 = tx0 - 8 + 8 * cu;
+            float v[8];
+            const bool rowin = gy >= 0 && gy < H && gx0 >= 0 && gx0 < Wv;
+            if (rowin) {
+                const Row8 row(up, gy, gx0);
+                row.sample(plane, v);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                T[r * TWs + 8 * cu + j] = (rowin && gx0 + j < Wv) ? (v[j] > threshold ? v[j] : -1.0f) : -INFINITY;
         }
-        T[idx] = t;
+    } else {
+        for (int idx = tid; idx < THp * TWp; idx += P_THREADS) {
+            const int r = idx / TWp, c = idx - r * TWp;
+            const int gy = ty0 - p + r, gx = tx0 - p + c;
+            float t = -INFINITY;                         // max_pool2d pads with -inf (columns past the cropped width too)
+            if (gy >= 0 && gy < H && gx >= 0 && gx < Wv) {
+                const float v = up.at(plane, gy, gx);
+                t = v > threshold ? v : -1.0f;          // F.threshold(x, thr, -1)
+            }
+            T[idx] = t;
+        }
     }
     __syncthreads();
     for (int idx = tid; idx < THp * N_TW; idx += P_THREADS) {
         const int r = idx / N_TW, c = idx - r * N_TW;
-        float m = T[r * TWp + c];
-        for (int j = 1; j < nms_kernel; ++j) m = fmaxf(m, T[r * TWp + c + j]);
+        float m = T[r * TWs + xoff + c];
+        for (int j = 1; j < nms_kernel; ++j) m = fmaxf(m, T[r * TWs + xoff + c + j]);
         RM[idx] = m;
     }
     __syncthreads();
@@ -138,7 +213,7 @@ center_nms_kernel(const float *__restrict__ center, quber_post_params pp, uint32
         const int gy = ty0 + row, gx = tx0 + xx;
         float m = RM[row * N_TW + xx];
         for (int j = 1; j < nms_kernel; ++j) m = fmaxf(m, RM[(row + j) * N_TW + xx]);
-        const float v = T[(row + p) * TWp + xx + p];
+        const float v = T[(row + p) * TWs + xoff + xx + p];
         const bool cand = gy < H && gx < Wv && v == m && v > 0.f;
         const uint32_t word = __ballot_sync(0xffffffffu, cand);
         const int wx = (tx0 >> 5) + half;
@@ -281,58 +356,6 @@ center_select_kernel(const float *__restrict__ center, quber_post_params pp, int
         if (base > top_k) atomicOr(overflow, 2);
     }
 }
-
-// ------------------------------------------------------------------------------------------------
-// Eight consecutive full-resolution pixels (x0 .. x0+7, x0 % 8 == 0) of row y, sampled from a 1/4-resolution plane
-// with EXACTLY UpSampler::at's arithmetic (same products, same sums, same rounding), but with the per-row and
-// per-column set-up shared by every plane and 8 loads per plane instead of 32: at scale 4 the eight pixels only
-// touch source columns 2m-1 .. 2m+2 (m = x0 / 8).  Column c[i] is clamped into the plane, which reproduces the
-// reference's `+ (x1 < w - 1)` step at the right edge; at the left edge (m == 0) the clamped source coordinate
-// makes pixels 0 and 1 read columns (0, 1) instead of (-1, 0).
-// ------------------------------------------------------------------------------------------------
-struct Row8 {
-    int top, bot;            // element offsets of the two source rows
-    int c0, c1, c2, c3;      // the four source columns
-    float ly, hy;
-    float lx[8];
-    bool left;
-    __device__ __forceinline__ Row8(const UpSampler &up, int y, int x0) {
-        float sy = __fsub_rn(__fmul_rn(up.r, __fadd_rn((float)y, 0.5f)), 0.5f);
-        sy = sy < 0.f ? 0.f : sy;
-        const int y1 = (int)sy;
-        top = y1 * up.w;
-        bot = top + ((y1 < up.h - 1) ? up.w : 0);
-        ly = __fsub_rn(sy, (float)y1);
-        hy = __fsub_rn(1.f, ly);
-        const int m2 = x0 >> 2;                          // 2m
-        left = m2 == 0;
-        c0 = max(m2 - 1, 0); c1 = m2; c2 = min(m2 + 1, up.w - 1); c3 = min(m2 + 2, up.w - 1);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            float sx = __fsub_rn(__fmul_rn(up.r, __fadd_rn((float)(x0 + j), 0.5f)), 0.5f);
-            sx = sx < 0.f ? 0.f : sx;
-            const int x1 = (int)sx;
-            lx[j] = __fsub_rn(sx, (float)x1);
-        }
-    }
-    __device__ __forceinline__ void sample(const float *__restrict__ plane, float *out) const {
-        const float *t = plane + top, *b = plane + bot;
-        const float t0 = __ldg(t + c0), t1 = __ldg(t + c1), t2 = __ldg(t + c2), t3 = __ldg(t + c3);
-        const float b0 = __ldg(b + c0), b1 = __ldg(b + c1), b2 = __ldg(b + c2), b3 = __ldg(b + c3);
-        // pixel j reads source columns (x1, x1 + 1): j = 0,1 -> (2m-1, 2m); 2..5 -> (2m, 2m+1); 6,7 -> (2m+1, 2m+2)
-        const float ta[8] = {left ? t1 : t0, left ? t1 : t0, t1, t1, t1, t1, t2, t2};
-        const float tb[8] = {left ? t2 : t1, left ? t2 : t1, t2, t2, t2, t2, t3, t3};
-        const float ba[8] = {left ? b1 : b0, left ? b1 : b0, b1, b1, b1, b1, b2, b2};
-        const float bb[8] = {left ? b2 : b1, left ? b2 : b1, b2, b2, b2, b2, b3, b3};
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float hx = __fsub_rn(1.f, lx[j]);
-            const float tp = __fadd_rn(__fmul_rn(hx, ta[j]), __fmul_rn(lx[j], tb[j]));
-            const float bt = __fadd_rn(__fmul_rn(hx, ba[j]), __fmul_rn(lx[j], bb[j]));
-            out[j] = __fadd_rn(__fmul_rn(hy, tp), __fmul_rn(ly, bt));
-        }
-    }
-};
 
 // Samples 8 pixels of one plane: the shared-set-up route at scale 4, UpSampler::at otherwise.
 template <bool S4>
@@ -982,7 +1005,7 @@ extern "C" int quber_post_process(const quber_post_params *pp, const quber_post_
     }
     if (!(p.flags & QUBER_POST_GIVEN_CENTERS)) {
         const int TWp = N_TW + p.nms_kernel - 1, THp = N_TH + p.nms_kernel - 1;
-        const size_t smem = ((size_t)THp * TWp + (size_t)THp * N_TW) * sizeof(float);
+        const size_t smem = ((size_t)THp * (TWp > N_TW + 16 ? TWp : N_TW + 16) + (size_t)THp * N_TW) * sizeof(float);
         dim3 grid(cdiv(p.W, N_TW), cdiv(p.H, N_TH), p.B);
         center_nms_kernel<<<grid, P_THREADS, smem, st>>>(io.center, p, ws.bitmask);
         if (int rc = check_launch("center_nms_kernel")) return rc;
