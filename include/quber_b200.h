@@ -286,6 +286,12 @@ int quber_gemm_timeouts(void);
  * quber_split_tf32: w dev [n] float32 -> hi, lo dev [n] float32 (once per weight).
  * quber_gemm_bias_act_x3: as quber_gemm_bias_act with float32 A [M,K] (split inside the kernel, in shared memory) and
  *   the pre-split weight W_hi / W_lo dev [N,K] (pitch ldw). */
+/* quber_gemm_bias_act over the K-concatenation A = [A1 | A2] (A1 dev [M,K1], A2 dev [M,K2], W dev [N, K1+K2]) without
+ * materialising it — the 1x1 convolution behind the RGB-D "concat" fusion (torch.cat([rgb, depth], 1) -> Conv2d(2c, c, 1),
+ * maskrefiner/modeling/backbone/resnet.py:466-479,497-501) on channels-last rows.  K1 must be a multiple of 64 (bf16) /
+ * 32 (fp32) elements; everything else as quber_gemm_bias_act. */
+int quber_gemm_bias_act_cat2(const void *A1, const void *A2, const void *W, const float *bias, void *C, int M, int N, int K1,
+                             int K2, int lda1, int lda2, int ldw, int ldc, int in_dtype, int out_dtype, int act, void *stream);
 int quber_split_tf32(const float *w, size_t n, float *hi, float *lo, void *stream);
 int quber_gemm_bias_act_x3(const float *A, const float *W_hi, const float *W_lo, const float *bias, void *C, int M, int N, int K,
                            int lda, int ldw, int ldc, int out_dtype, int act, void *stream);

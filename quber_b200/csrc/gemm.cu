@@ -96,7 +96,8 @@ template <int BN, bool TF32, typename OT, bool SPLIT = false>
 __global__ void __launch_bounds__(SPLIT ? G_THREADS + 128 : G_THREADS)
 gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                      const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_c,
-                     const float *__restrict__ bias, int M, int N, int K, int act) {
+                     const float *__restrict__ bias, int M, int N, int K, int act,
+                     const __grid_constant__ CUtensorMap map_a2, int kb_split) {
     static_assert(!SPLIT || TF32, "the split mode is an fp32 mode");
     static_assert(BN == 64 || BN == 128 || BN == 256, "tile width");
     constexpr int NST = SPLIT ? 2 : (BN == 256 ? 3 : 4);     // SPLIT stages hold A_hi | A_lo | W_hi | W_lo: twice the bytes
@@ -142,7 +143,10 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                     if (it >= NST && !g_mbar_wait(&empty[s], ((it / NST) - 1) & 1)) { abort_s = 1; break; }
                     unsigned char *sa = gsm + (size_t)s * STAGE, *sw = sa + W_OFF;
                     g_mbar_expect_tx(&full[s], A_BYTES + (SPLIT ? 2 : 1) * W_BYTES);
-                    g_tma_load_2d(sa, &map_a, &full[s], kb * KELEMS, m0);
+                    // kb_split > 0: A is the K-concatenation [A1 | A2] of two matrices that is never materialised
+                    // (quber_gemm_bias_act_cat2): k-blocks below the split come from map_a, the others from map_a2
+                    if (kb_split > 0 && kb >= kb_split) g_tma_load_2d(sa, &map_a2, &full[s], (kb - kb_split) * KELEMS, m0);
+                    else g_tma_load_2d(sa, &map_a, &full[s], kb * KELEMS, m0);
                     g_tma_load_2d(sw, &map_w, &full[s], kb * KELEMS, n0);
                     if (SPLIT) g_tma_load_2d(sw + W_BYTES, &map_wlo, &full[s], kb * KELEMS, n0);
                 }
@@ -332,13 +336,14 @@ static bool gemm_map(CUtensorMap *m, const void *base, int rows, int K, int ld, 
 
 template <int BN, bool TF32, typename OT, bool SPLIT = false>
 static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUtensorMap &mwlo, const CUtensorMap &mc, const float *bias,
-                       int M, int N, int K, int act, cudaStream_t st) {
+                       int M, int N, int K, int act, cudaStream_t st, const CUtensorMap *ma2 = nullptr, int kb_split = 0) {
     constexpr int NST = SPLIT ? 2 : (BN == 256 ? 3 : 4);
     const size_t smem = (size_t)NST * (SPLIT ? 2 : 1) * (G_BM + BN) * G_KBYTES + 4 * 2 * 4096 + 1024;
     QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_bias_act_kernel<BN, TF32, OT, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long ntiles = (long long)cdiv(M, G_BM) * cdiv(N, BN);
     const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());       // persistent: one CTA per SM
-    gemm_bias_act_kernel<BN, TF32, OT, SPLIT><<<grid, SPLIT ? G_THREADS + 128 : G_THREADS, smem, st>>>(ma, mw, mwlo, mc, bias, M, N, K, act);
+    gemm_bias_act_kernel<BN, TF32, OT, SPLIT><<<grid, SPLIT ? G_THREADS + 128 : G_THREADS, smem, st>>>(ma, mw, mwlo, mc, bias, M, N, K, act,
+                                                                                                     ma2 ? *ma2 : ma, kb_split);
     return check_launch("gemm_bias_act_kernel");
 }
 
@@ -390,6 +395,45 @@ extern "C" int quber_gemm_bias_act(const void *A, const void *W, const float *bi
         else      { if (out_dtype == 0) QG(64, false, float); else QG(64, false, __nv_bfloat16); }
     }
 #undef QG
+}
+
+// C = act([A1 | A2] W^T + bias): the 1x1 convolution that follows a channel concatenation (RGB-D "concat" fusion,
+// maskrefiner/modeling/backbone/resnet.py:466-479,497-501: torch.cat([rgb, depth], 1) -> Conv2d(2c, c, 1)) on channels-last
+// rows, without materialising the concatenation: the TMA producer takes the k-blocks below K1 from A1 and the rest from A2.
+extern "C" int quber_gemm_bias_act_cat2(const void *A1, const void *A2, const void *W, const float *bias, void *C, int M, int N,
+                                        int K1, int K2, int lda1, int lda2, int ldw, int ldc, int in_dtype, int out_dtype, int act,
+                                        void *stream) {
+    using namespace quber;
+    if (!A1 || !A2 || !W || !C || M <= 0 || N <= 0 || K1 <= 0 || K2 <= 0) return QUBER_E_INVALID;
+    if ((in_dtype != 1 && in_dtype != 2) || (out_dtype != 0 && out_dtype != 1) || (act != 0 && act != 1)) return QUBER_E_INVALID;
+    const bool tf32 = in_dtype == 2;
+    const int es = tf32 ? 4 : 2, os = out_dtype == 0 ? 4 : 2, kelems = tf32 ? 32 : 64, K = K1 + K2;
+    if (lda1 < K1 || lda2 < K2 || ldw < K || ldc < N) return QUBER_E_INVALID;
+    if (K1 % kelems != 0) return QUBER_E_UNSUPPORTED;                 // the split must fall on a k-block boundary
+    if (!aligned16(A1) || !aligned16(A2) || !aligned16(W) || !aligned16(C) || ((size_t)lda1 * es) % 16 || ((size_t)lda2 * es) % 16 ||
+        ((size_t)ldw * es) % 16 || ((size_t)ldc * os) % 16)
+        return QUBER_E_ALIGN;
+    const int BN = (N % 256 == 0) ? 256 : ((N % 128 == 0 || N > 192) ? 128 : 64);
+    CUtensorMap ma, ma2, mw, mc;
+    if (!gemm_map(&ma, A1, M, K1, lda1, G_BM, es) || !gemm_map(&ma2, A2, M, K2, lda2, G_BM, es) || !gemm_map(&mw, W, N, K, ldw, BN, es) ||
+        !gemm_map(&mc, C, M, N, ldc, 32, os)) {
+        set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled");
+        return QUBER_E_CUDA;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ks = K1 / kelems;
+#define QG2(BN_, TF_, OT_) return gemm_launch<BN_, TF_, OT_>(ma, mw, mw, mc, bias, M, N, K, act, st, &ma2, ks)
+    if (BN == 256) {
+        if (tf32) { if (out_dtype == 0) QG2(256, true, float); else QG2(256, true, __nv_bfloat16); }
+        else      { if (out_dtype == 0) QG2(256, false, float); else QG2(256, false, __nv_bfloat16); }
+    } else if (BN == 128) {
+        if (tf32) { if (out_dtype == 0) QG2(128, true, float); else QG2(128, true, __nv_bfloat16); }
+        else      { if (out_dtype == 0) QG2(128, false, float); else QG2(128, false, __nv_bfloat16); }
+    } else {
+        if (tf32) { if (out_dtype == 0) QG2(64, true, float); else QG2(64, true, __nv_bfloat16); }
+        else      { if (out_dtype == 0) QG2(64, false, float); else QG2(64, false, __nv_bfloat16); }
+    }
+#undef QG2
 }
 
 extern "C" int quber_split_tf32(const float *w, size_t n, float *hi, float *lo, void *stream) {

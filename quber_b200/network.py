@@ -90,9 +90,10 @@ def _maxpool(conv, x):
     return F.max_pool2d(x, kernel_size=3, stride=2, padding=1)
 
 
-def run_conv_gn_relu(seq, x, fast):
+def run_conv_gn_relu(seq, x, fast, skip_conv=False):
     """An nn.Sequential of nn.Conv2d / nn.GroupNorm / nn.ReLU (resnet.py:466-479); with `fast`, GroupNorm + ReLU pairs
-    go through the fused kernel."""
+    go through the fused kernel.  skip_conv: `x` already is the first convolution's output WITHOUT its bias (the K-split
+    GEMM of the concat fusion); the bias still rides in the GroupNorm kernel."""
     if not fast:
         return seq(x)
     from . import ops
@@ -102,7 +103,7 @@ def run_conv_gn_relu(seq, x, fast):
         m = mods[i]
         if type(m) is nn.Conv2d and m.bias is not None and i + 1 < len(mods) and isinstance(mods[i + 1], nn.GroupNorm) and x.is_cuda:
             # conv bias rides in the GroupNorm kernel's loads instead of a separate pass over the activation
-            y = F.conv2d(x, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
+            y = x if (skip_conv and i == 0) else F.conv2d(x, m.weight, None, m.stride, m.padding, m.dilation, m.groups)
             relu = i + 2 < len(mods) and isinstance(mods[i + 2], nn.ReLU)
             z = _gn_relu(mods[i + 1], y, relu, pre_bias=m.bias) if ops.group_norm_supported(y, mods[i + 1].num_groups) else None
             if z is not None:
@@ -398,13 +399,42 @@ class RGBDFusionBackbone(nn.Module):
         rgb_x, depth_x, offset_x = x[:, :3], x[:, 3:6], x[:, 6:]
         rgb_out = self.rgb_backbone(torch.cat([rgb_x, offset_x], dim=1))
         depth_out = self.depth_backbone(torch.cat([depth_x, offset_x], dim=1))
+        fast = self.__dict__.get("_fast", False)
         for k in rgb_out.keys():
             if self.fusion_strategy == "concat":
+                y = self._concat_1x1(self.fusion_layers[k], rgb_out[k], depth_out["depth_" + k]) if fast else None
+                if y is not None:                               # the concatenation never exists: K-split GEMM over both streams
+                    rgb_out[k] = run_conv_gn_relu(self.fusion_layers[k], y, True, skip_conv=True)
+                    continue
                 rgb_out[k] = torch.cat([rgb_out[k], depth_out["depth_" + k]], dim=1)
             elif self.fusion_strategy == "add":
                 rgb_out[k] = rgb_out[k] + depth_out["depth_" + k]
-            rgb_out[k] = run_conv_gn_relu(self.fusion_layers[k], rgb_out[k], self.__dict__.get("_fast", False))
+            rgb_out[k] = run_conv_gn_relu(self.fusion_layers[k], rgb_out[k], fast)
         return rgb_out
+
+    @staticmethod
+    def _concat_1x1(seq, a, b):
+        """Conv2d(2c, c, 1) of torch.cat([a, b], 1) (resnet.py:466-468, 497-501) as ONE quber_gemm_bias_act_cat2 call on the
+        channels-last rows of both streams, bias left to the GroupNorm kernel behind it (`pre_bias`); None when the
+        tensors do not qualify (CPU, fp32 plan, NCHW-contiguous memory): the caller then concatenates."""
+        conv = seq[0]
+        if len(seq) < 2 or conv.bias is None or not isinstance(seq[1], nn.GroupNorm):
+            return None
+        if not (type(conv) is nn.Conv2d and conv.kernel_size == (1, 1) and a.is_cuda and a.dtype == b.dtype == torch.bfloat16
+                and a.shape == b.shape and conv.in_channels == 2 * a.shape[1] and a.shape[1] % 64 == 0):
+            return None
+        if not (a.is_contiguous(memory_format=torch.channels_last) and b.is_contiguous(memory_format=torch.channels_last)):
+            return None
+        from . import ops
+        B, C, h, w = a.shape
+        wkey = (conv.weight.data_ptr(), conv.weight._version)
+        cache = conv.__dict__.get("_w_rows")
+        if cache is None or cache[0] != wkey:
+            cache = (wkey, conv.weight.detach().reshape(conv.out_channels, 2 * C).to(torch.bfloat16).contiguous())
+            conv.__dict__["_w_rows"] = cache
+        y = ops.gemm_bias_act_cat2(a.permute(0, 2, 3, 1).reshape(-1, C), b.permute(0, 2, 3, 1).reshape(-1, C), cache[1], None,
+                                   out_dtype=torch.bfloat16)
+        return y.view(B, h, w, conv.out_channels).permute(0, 3, 1, 2)             # NCHW view of channels-last memory
 
 
 def build_resnet_deeplab_rgbd_fusion_backbone(cfg, input_shape=None):

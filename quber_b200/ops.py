@@ -421,6 +421,44 @@ def gemm_bias_act(a, weight, bias=None, act="none", out_dtype=None):
     return out.reshape(tuple(a.shape[:-1]) + (N,))
 
 
+def gemm_bias_act_cat2(a1, a2, weight, bias=None, act="none", out_dtype=None):
+    """act(cat([a1, a2], -1) @ weight.T + bias) without the concatenation (quber_gemm_bias_act_cat2): a1 [..., K1],
+    a2 [..., K2] with equal leading shapes, weight [N, K1 + K2]; dtypes / act / out_dtype as gemm_bias_act.  K1 must be a
+    multiple of 64 (bfloat16) or 32 (float32).  The 1x1 convolution behind the RGB-D concat fusion on channels-last rows."""
+    _need_cuda(weight, "weight")
+    for t, nm in ((a1, "a1"), (a2, "a2")):
+        if not isinstance(t, torch.Tensor) or not t.is_cuda:
+            raise ValueError(f"{nm} must be a CUDA tensor")
+    if not (a1.dtype == a2.dtype == weight.dtype) or a1.dtype not in (torch.bfloat16, torch.float32):
+        raise ValueError("a1, a2 and weight must all be bfloat16 or all float32")
+    K1, K2, N = a1.shape[-1], a2.shape[-1], weight.shape[0]
+    if weight.dim() != 2 or weight.shape[1] != K1 + K2 or tuple(a1.shape[:-1]) != tuple(a2.shape[:-1]):
+        raise ValueError("weight must be [N, K1 + K2] and a1 / a2 must share their leading shape")
+    if K1 % (64 if a1.dtype == torch.bfloat16 else 32):
+        raise ValueError("K1 must fall on a k-block boundary (64 bfloat16 / 32 float32 elements)")
+    r1, r2 = a1.reshape(-1, K1), a2.reshape(-1, K2)
+    r1 = r1 if r1.stride(1) == 1 else r1.contiguous()
+    r2 = r2 if r2.stride(1) == 1 else r2.contiguous()
+    M = r1.shape[0]
+    out_dtype = a1.dtype if out_dtype is None else out_dtype
+    if out_dtype not in (torch.float32, torch.bfloat16):
+        raise ValueError("out_dtype must be float32 or bfloat16")
+    if bias is not None:
+        _need_cuda(bias, "bias", torch.float32)
+        if bias.numel() != N:
+            raise ValueError("bias must have N elements")
+    if act not in ("none", "relu"):
+        raise ValueError("act must be 'none' or 'relu'")
+    out = torch.empty((M, N), dtype=out_dtype, device=a1.device)
+    if M > 0:
+        with torch.cuda.device(a1.device):
+            _lib.check(_lib.lib().quber_gemm_bias_act_cat2(_ptr(r1), _ptr(r2), _ptr(weight), _ptr(bias), _ptr(out), M, N, K1, K2,
+                                                           r1.stride(0), r2.stride(0), weight.stride(0), N,
+                                                           1 if a1.dtype == torch.bfloat16 else 2, 0 if out_dtype == torch.float32 else 1,
+                                                           1 if act == "relu" else 0, _stream()), "quber_gemm_bias_act_cat2")
+    return out.reshape(tuple(a1.shape[:-1]) + (N,))
+
+
 def split_tf32(w):
     """fp32 CUDA tensor -> (hi, lo): hi = w with the 13 low mantissa bits cleared (what a TF32 tensor-core product
     reads), lo = w - hi (exact).  The pre-split weight of gemm_bias_act_x3."""
@@ -1040,6 +1078,15 @@ def _register():
     @_gemm.register_fake
     def _(a, weight, bias, relu, out_bf16):
         return a.new_empty(tuple(a.shape[:-1]) + (weight.shape[0],), dtype=torch.bfloat16 if out_bf16 else torch.float32)
+
+    @custom_op("quber::gemm_bias_act_cat2", mutates_args=(), device_types="cuda")
+    def _gemm_cat2(a1: T, a2: T, weight: T, bias: Optional[T], relu: bool, out_bf16: bool) -> T:
+        return gemm_bias_act_cat2(a1, a2, weight, bias, act="relu" if relu else "none",
+                                  out_dtype=torch.bfloat16 if out_bf16 else torch.float32)
+
+    @_gemm_cat2.register_fake
+    def _(a1, a2, weight, bias, relu, out_bf16):
+        return a1.new_empty(tuple(a1.shape[:-1]) + (weight.shape[0],), dtype=torch.bfloat16 if out_bf16 else torch.float32)
 
     @custom_op("quber::gemm_bias_act_x3", mutates_args=(), device_types="cuda")
     def _gemm3(a: T, w_hi: T, w_lo: T, bias: Optional[T], relu: bool, out_bf16: bool) -> T:

@@ -725,6 +725,34 @@ def test_msda_fused_equals_prepare_plus_forward_and_oracle(D, dt, L):
         np.testing.assert_allclose(fused.cpu().numpy(), want, rtol=0, atol=1e-7)
 
 
+@pytest.mark.parametrize("rows,N,K1,K2,dt", [(1000, 256, 256, 256, "bf16"), (6300, 512, 512, 512, "bf16"), (333, 256, 64, 192, "bf16"),
+                                              (515, 128, 128, 96, "bf16"), (700, 256, 96, 160, "f32")])
+def test_gemm_cat2_equals_gemm_of_the_concatenation(rows, N, K1, K2, dt):
+    """quber_gemm_bias_act_cat2: the K-concatenation [A1 | A2] is never materialised; the k-blocks are issued in the same
+    order as for the concatenated matrix, so the result equals quber_gemm_bias_act(cat) bit for bit; and float64 within
+    the GEMM tests' tolerance."""
+    g = torch.Generator(device=DEV).manual_seed(rows + K1)
+    tdt = torch.bfloat16 if dt == "bf16" else torch.float32
+    a1 = (torch.randn(rows, K1, device=DEV, generator=g) * 0.5).to(tdt)
+    a2 = (torch.randn(rows, K2, device=DEV, generator=g) * 0.5).to(tdt)
+    w = (torch.randn(N, K1 + K2, device=DEV, generator=g) * 0.1).to(tdt)
+    b = torch.randn(N, device=DEV, generator=g)
+    for out_dtype in (torch.float32, torch.bfloat16):
+        got = ops.gemm_bias_act_cat2(a1, a2, w, b, act="relu", out_dtype=out_dtype)
+        want = ops.gemm_bias_act(torch.cat([a1, a2], 1), w, b, act="relu", out_dtype=out_dtype)
+        assert got.dtype == out_dtype and torch.equal(got, want)
+    ref = torch.relu(torch.cat([a1, a2], 1).double() @ w.double().T + b.double())
+    got = ops.gemm_bias_act_cat2(a1, a2, w, b, act="relu", out_dtype=torch.float32)
+    tol = 1e-4 if dt == "bf16" else 2e-2                    # bf16 inputs are exact products; fp32 inputs multiply as TF32
+    assert float((got.double() - ref).abs().max()) <= tol * max(1.0, float(ref.abs().max()))
+    # strided views of channels-last activations: row pitch larger than K
+    big = (torch.randn(rows, K1 + K2 + 64, device=DEV, generator=g) * 0.5).to(tdt)
+    v1, v2 = big[:, :K1], big[:, K1 + 64:]
+    assert torch.equal(ops.gemm_bias_act_cat2(v1, v2, w, b), ops.gemm_bias_act(torch.cat([v1, v2], 1).contiguous(), w, b))
+    with pytest.raises(ValueError):
+        ops.gemm_bias_act_cat2(a1[:, :-8], a2, w[:, :-8].contiguous(), b)                     # K1 off a k-block boundary
+
+
 @pytest.mark.parametrize("case", list(MSDA_CASES))
 def test_msda_float64_is_real_float64(case):
     """The reference dispatches fp64 (ms_deform_attn_cuda.cu:69, OPS/test.py:24-44 checks it with allclose at fp64
