@@ -337,6 +337,7 @@ def run_ours(args):
     E2E_CHUNK = int(os.environ.get("QUBER_E2E_CHUNK", "8"))
     E2E_TAIL = int(os.environ.get("QUBER_E2E_TAIL", "2"))
     E2E_KERNEL = int(os.environ.get("QUBER_E2E_KERNEL_FRAMES", "16"))
+    E2E_BYTE_FRAMES = int(os.environ["QUBER_E2E_BYTE_FRAMES"]) if "QUBER_E2E_BYTE_FRAMES" in os.environ else None   # None: the rule
 
     # host calls: one payload per slot, the collective on the side stream (ranks are not made to meet on the main stream;
     # a slot's payload is rewritten two calls later, after its gather has read it)
@@ -362,7 +363,7 @@ def run_ours(args):
         # under the host-side packing / host->device copies of refine_batch_host's chunk pipeline
         hp.msda_layers(d["msda"], N_LAYERS)
         o, keep = hp.refine_batch_host(d["h_masks"], d["h_head"], chunk_frames=E2E_CHUNK, min_tail=E2E_TAIL, kernel_frames=E2E_KERNEL,
-                                       slot=slot, async_result=async_result)
+                                       slot=slot, async_result=async_result, byte_frames=E2E_BYTE_FRAMES)
         hp.last_route_dense = dict(hp.last_route)
         gather_host_call(keep, slot)
         return o

@@ -244,17 +244,29 @@ class HotPath:
                 c0 += n
         return out
 
-    def byte_frames_rule(self, B):
+    def byte_frames_rule(self, B, frame_bytes=0, head_bytes=0):
         """How many of the B frames travel as bytes through the copy engine WHILE the host threads bit-pack the others:
         the dense masks have to be read from host DRAM once either way, so the two readers (DMA at ~55 GB/s, packing at
-        ~5 GB/s per thread up to ~60 GB/s) are run side by side and the frames are split in proportion to their rates.
-        Deterministic (a function of the thread count), nominal rates from profiles/r01_hostpack_v12.txt and the bench's
-        host_link figures."""
+        ~5 GB/s per thread up to ~60 GB/s) are run side by side.  The split (a multiple of 4 frames) minimises the longer
+        of the two: the link carries the byte frames AND an eighth of the packed ones AND the head outputs, the threads
+        read the packed frames.  Deterministic (a function of the thread count and the sizes), nominal rates from
+        profiles/r01_hostpack_v12.txt and the bench's host_link figures; measured at C2 with 14 threads: 12 byte frames
+        3.73 ms per call, 16: 3.90, 8: 4.44."""
         if not self.pack_masks:
             return B
         copy_gbs, pack_gbs = 55.0, min(5.0 * self.pack_threads, 60.0)
-        nb = int(round(B * copy_gbs / (copy_gbs + pack_gbs) / 4.0)) * 4 if B >= 8 else int(round(B * copy_gbs / (copy_gbs + pack_gbs)))
-        return max(0, min(B, nb))                 # multiples of 4 frames: even chunk sizes on both routes
+        if frame_bytes <= 0:                      # sizes unknown: proportional to the rates
+            nb = int(round(B * copy_gbs / (copy_gbs + pack_gbs) / 4.0)) * 4 if B >= 8 else int(round(B * copy_gbs / (copy_gbs + pack_gbs)))
+            return max(0, min(B, nb))
+        step = 4 if B >= 8 else 1
+        best, best_t = B, None
+        for nb in range(0, B + 1, step):
+            t_copy = (nb * frame_bytes + (B - nb) * frame_bytes / 8.0 + head_bytes) / copy_gbs
+            t_pack = (B - nb) * frame_bytes / pack_gbs
+            t = max(t_copy, t_pack)
+            if best_t is None or t < best_t - 1e-9:
+                best, best_t = nb, t
+        return best
 
     def refine_batch_host(self, masks_host, head_host, out_host=None, chunk_frames=8, min_tail=2, kernel_frames=0, byte_frames=None,
                           slot=0, async_result=False):
@@ -302,7 +314,8 @@ class HotPath:
                 st["free"].synchronize()
             self.pack_masks = self._calibrate_pack(masks_host, st, self.chunk_schedule(B, chunk_frames, min_tail))
         pack = bool(self.pack_masks) and frame_bytes % 32 == 0 and masks_host.is_contiguous()
-        nb = B if not pack else (self.byte_frames_rule(B) if byte_frames is None else max(0, min(B, int(byte_frames))))
+        head_bytes = sum(v.numel() * v.element_size() for v in head_host.values())
+        nb = B if not pack else (self.byte_frames_rule(B, frame_bytes, head_bytes) if byte_frames is None else max(0, min(B, int(byte_frames))))
         pack = pack and nb < B
         byte_sched = self.chunk_schedule(nb, chunk_frames, chunk_frames) if nb else []
         sched = [(nb + a, nb + b) for a, b in self.chunk_schedule(B - nb, chunk_frames, min_tail)] if nb < B else []

@@ -388,14 +388,14 @@ def test_refine_batch_host_hybrid_route_bytes_and_packed_side_by_side(B, nb, kf)
         o1, k1 = hp.refine_batch_host(hm, hh, chunk_frames=2, min_tail=1, kernel_frames=kf, byte_frames=nb)
         torch.cuda.current_stream().synchronize()
         HotPath.check_status(o1)
-        want_nb = hp.byte_frames_rule(B) if nb is None else nb
+        want_nb = hp.byte_frames_rule(B, hm[0].numel(), sum(v.numel() * v.element_size() for v in hh.values())) if nb is None else nb
         assert hp.last_route == dict(byte_frames=want_nb, packed_frames=B - want_nb if want_nb < B else 0)
         assert [k[5] for k in k1] == sorted(k[5] for k in k1) and sum(k[0].shape[0] for k in k1) == B
         for key in ("label_map", "boundary", "inst_start", "inst_counts"):
             assert torch.equal(o0[key], o1[key]), key
         assert torch.equal(torch.cat([k[0] for k in k1]), e0) and torch.equal(torch.cat([k[1] for k in k1]), p0)
         _assert_staged(hp, hm)
-    assert 0 <= hp.byte_frames_rule(32) <= 32
+    assert 0 <= hp.byte_frames_rule(32) <= 32 and hp.byte_frames_rule(32, 30 * 480 * 640, 20 << 20) % 4 == 0
 
 
 def test_refiner_adapter_takes_file_paths_like_the_reference(tmp_path):
