@@ -185,7 +185,9 @@ class MaskRefiner(nn.Module):
     def _network_logits(self, x):
         if self.precision == "bf16" and x.is_cuda:
             with torch.autocast("cuda", dtype=torch.bfloat16):
-                feats = self.backbone(x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
+                # the RGB-D backbone splits / casts / re-lays-out the packed fp32 input itself in one pass (ops.split_rgbd_input)
+                own_split = getattr(self.backbone, "splits_packed_input", False) and x.dtype == torch.float32 and x.is_contiguous()
+                feats = self.backbone(x if own_split else x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
                 out = self.ins_embed_head.layers({k: v for k, v in feats.items()})
         else:
             if x.is_cuda and self.use_inference_plan and not self.training:

@@ -394,12 +394,24 @@ class RGBDFusionBackbone(nn.Module):
         self._out_feature_channels = rgb_backbone._out_feature_channels
         self._out_feature_strides = rgb_backbone._out_feature_strides
         self.size_divisibility = 0
+        self.splits_packed_input = True              # forward takes the packed fp32 [B,9,H,W] input as it is (bf16 plan)
 
     def forward(self, x):
-        rgb_x, depth_x, offset_x = x[:, :3], x[:, 3:6], x[:, 6:]
-        rgb_out = self.rgb_backbone(torch.cat([rgb_x, offset_x], dim=1))
-        depth_out = self.depth_backbone(torch.cat([depth_x, offset_x], dim=1))
         fast = self.__dict__.get("_fast", False)
+        stem = self.rgb_backbone.stem
+        first = getattr(stem, "conv_1", None) if hasattr(stem, "conv_1") else getattr(stem, "conv1", None)     # BasicStem / DeepLabStem
+        stem_plan = first.__dict__.get("_plan") if first is not None else None
+        if (fast and x.is_cuda and x.dtype == torch.float32 and x.shape[1] == 9 and x.is_contiguous() and (x.shape[2] * x.shape[3]) % 4 == 0
+                and stem_plan is not None and stem_plan[0].dtype == torch.bfloat16):
+            from . import ops
+            rgb_in, depth_in = ops.split_rgbd_input(x)       # both cats, the channels-last layout and the bf16 cast in one pass
+        else:
+            if fast and x.is_cuda and stem_plan is not None and x.dtype != stem_plan[0].dtype:
+                x = x.to(stem_plan[0].dtype).contiguous(memory_format=torch.channels_last)     # what the caller used to do
+            rgb_x, depth_x, offset_x = x[:, :3], x[:, 3:6], x[:, 6:]
+            rgb_in, depth_in = torch.cat([rgb_x, offset_x], dim=1), torch.cat([depth_x, offset_x], dim=1)
+        rgb_out = self.rgb_backbone(rgb_in)
+        depth_out = self.depth_backbone(depth_in)
         for k in rgb_out.keys():
             if self.fusion_strategy == "concat":
                 y = self._concat_1x1(self.fusion_layers[k], rgb_out[k], depth_out["depth_" + k]) if fast else None

@@ -538,3 +538,20 @@ MODEL:
             "height": 256, "width": 320} for _ in range(2)]
     res = model(inp)
     assert len(res) == 2 and tuple(res[0]["sem_seg"].shape) == (1, 256, 320) and "panoptic_seg" in res[0]
+
+
+def test_split_rgbd_input_equals_the_two_cats():
+    """quber_split_rgbd_input: cat([rgb, offsets], 1) / cat([depth, offsets], 1) of RGBDFusionBackbone.forward
+    (resnet.py:489-493) as channels-last bfloat16 in one pass — the same bytes as cat + cast + layout change."""
+    from quber_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(77)
+    for B, H, W in ((2, 48, 64), (3, 30, 44), (1, 480, 640)):
+        x = torch.randn(B, 9, H, W, device="cuda", generator=g) * 3
+        a, b = ops.split_rgbd_input(x)
+        for got, img in ((a, x[:, :3]), (b, x[:, 3:6])):
+            want = torch.cat([img, x[:, 6:]], 1).to(torch.bfloat16)
+            assert got.shape == want.shape and got.dtype == torch.bfloat16
+            assert got.is_contiguous(memory_format=torch.channels_last)
+            assert torch.equal(got, want)
+    with pytest.raises(ValueError):
+        ops.split_rgbd_input(torch.zeros(1, 8, 4, 4, device="cuda"))
