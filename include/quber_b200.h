@@ -253,9 +253,11 @@ int quber_pack_input(const uint8_t *image, const float *offsets, const float *me
                      int CO, int H, int W, float *out, void *stream);
 /* RGBDFusionBackbone.forward's input stage for the bf16 inference plan (maskrefiner/modeling/backbone/resnet.py:489-493):
  *   x dev [B,9,H,W] float32 = (rgb 3 | depth 3 | encoded offsets 3), the output of quber_pack_input
- *   out_rgb / out_depth dev [B,H,W,6] bfloat16 (channels-last): cat([rgb, offsets], 1) / cat([depth, offsets], 1)
+ *   out_rgb / out_depth dev [B,H,W,pitch] bfloat16 (channels-last): cat([rgb, offsets], 1) / cat([depth, offsets], 1);
+ *   pitch = 6, or 8 with two zero channels behind them (16-byte pixels: the stem convolution then runs with a weight
+ *   zero-padded to 8 input channels — same sums — on cuDNN's tensor-core kernels instead of its 6-channel fall-backs)
  * — the two torch.cat, layout changes and casts in one pass.  H*W must be a multiple of 4. */
-int quber_split_rgbd_input(const float *x, int B, int H, int W, void *out_rgb, void *out_depth, void *stream);
+int quber_split_rgbd_input(const float *x, int B, int H, int W, int pitch, void *out_rgb, void *out_depth, void *stream);
 int quber_fuse_concat(const float *const *sources, const int *channels, const int *ops, int n_sources, int B, int h,
                       int w, int layout, int pitch, void *out, void *stream);
 /* quber_fuse_concat_rows — the same chain (model.py:745-759) for sources that are already channels-last rows:

@@ -83,7 +83,7 @@ SYMBOLS = {
     "quber_upsample_crop_resize": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_f, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_resize_nearest_u8": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
     "quber_gemm_bias_act_cat2": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp]),
-    "quber_split_rgbd_input": (c_i, [c_vp, c_i, c_i, c_i, c_vp, c_vp, c_vp]),
+    "quber_split_rgbd_input": (c_i, [c_vp, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp]),
     "quber_msda_forward_fused": (c_i, [c_vp, c_vp, c_vp, c_vp, c_i, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp, c_vp]),
     "quber_msda_forward": (c_i, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_vp, c_vp]),
 }

@@ -53,6 +53,7 @@ pack_input_kernel(const uint8_t *__restrict__ image, const float *__restrict__ o
 // x[:, 6:] -> cat([rgb, offsets], 1) for the RGB stream and cat([depth, offsets], 1) for the depth stream.  On the bf16
 // inference plan both stems want channels-last bf16: the two cats, two layout changes and two casts are one pass here
 // (nine fp32 planes read once, two [B,H,W,6] bf16 tensors written once).  Four pixels per thread: 48-byte stores.
+template <int PITCH>     // channels per pixel in the outputs: 6, or 8 with two zero channels (16-byte pixels, what cuDNN's tensor-core kernels want)
 __global__ void __launch_bounds__(256)
 split_rgbd_input_kernel(const float *__restrict__ x, size_t HW, __nv_bfloat16 *__restrict__ out_rgb, __nv_bfloat16 *__restrict__ out_depth) {
     const int b = blockIdx.y;
@@ -66,20 +67,23 @@ split_rgbd_input_kernel(const float *__restrict__ x, size_t HW, __nv_bfloat16 *_
     }
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
-        uint32_t w[12];                                  // 4 pixels x 6 channels, two bf16 per word
+        uint32_t w[4 * PITCH / 2];                       // 4 pixels x PITCH channels, two bf16 per word
 #pragma unroll
         for (int px = 0; px < 4; ++px)
 #pragma unroll
-            for (int cp = 0; cp < 3; ++cp) {
-                const int c0 = 2 * cp, c1 = 2 * cp + 1;  // output channels; 0-2 = the stream's image, 3-5 = the offsets
-                const float f0 = v[c0 < 3 ? 3 * s + c0 : 3 + c0][px], f1 = v[c1 < 3 ? 3 * s + c1 : 3 + c1][px];
-                const __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
-                w[px * 3 + cp] = *reinterpret_cast<const uint32_t *>(&h);
+            for (int cp = 0; cp < PITCH / 2; ++cp) {
+                const int c0 = 2 * cp, c1 = 2 * cp + 1;  // output channels; 0-2 = the stream's image, 3-5 = the offsets, 6-7 = 0
+                uint32_t word = 0u;
+                if (cp < 3) {
+                    const float f0 = v[c0 < 3 ? 3 * s + c0 : 3 + c0][px], f1 = v[c1 < 3 ? 3 * s + c1 : 3 + c1][px];
+                    const __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
+                    word = *reinterpret_cast<const uint32_t *>(&h);
+                }
+                w[px * (PITCH / 2) + cp] = word;
             }
-        __nv_bfloat16 *o = (s == 0 ? out_rgb : out_depth) + ((size_t)b * HW + i) * 6;
-        st_stream_u4(o, make_uint4(w[0], w[1], w[2], w[3]));
-        st_stream_u4(o + 8, make_uint4(w[4], w[5], w[6], w[7]));
-        st_stream_u4(o + 16, make_uint4(w[8], w[9], w[10], w[11]));
+        __nv_bfloat16 *o = (s == 0 ? out_rgb : out_depth) + ((size_t)b * HW + i) * PITCH;
+#pragma unroll
+        for (int q = 0; q < PITCH / 2; ++q) st_stream_u4(o + 8 * q, make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]));
     }
 }
 
@@ -251,15 +255,17 @@ extern "C" int quber_pack_input(const uint8_t *image, const float *offsets, cons
     return check_launch("pack_input_kernel");
 }
 
-extern "C" int quber_split_rgbd_input(const float *x, int B, int H, int W, void *out_rgb, void *out_depth, void *stream) {
+extern "C" int quber_split_rgbd_input(const float *x, int B, int H, int W, int pitch, void *out_rgb, void *out_depth, void *stream) {
     using namespace quber;
     if (!x || !out_rgb || !out_depth || B <= 0 || H <= 0 || W <= 0) return QUBER_E_INVALID;
     const size_t HW = (size_t)H * W;
+    if (pitch != 6 && pitch != 8) return QUBER_E_INVALID;
     if (HW % 4 != 0 || B > 65535) return QUBER_E_UNSUPPORTED;
     if (!aligned16(x) || !aligned16(out_rgb) || !aligned16(out_depth)) return QUBER_E_ALIGN;
     dim3 grid((unsigned)((HW / 4 + 255) / 256), B);
-    split_rgbd_input_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, HW, static_cast<__nv_bfloat16 *>(out_rgb),
-                                                                  static_cast<__nv_bfloat16 *>(out_depth));
+    __nv_bfloat16 *o1 = static_cast<__nv_bfloat16 *>(out_rgb), *o2 = static_cast<__nv_bfloat16 *>(out_depth);
+    if (pitch == 6) split_rgbd_input_kernel<6><<<grid, 256, 0, (cudaStream_t)stream>>>(x, HW, o1, o2);
+    else split_rgbd_input_kernel<8><<<grid, 256, 0, (cudaStream_t)stream>>>(x, HW, o1, o2);
     return check_launch("split_rgbd_input_kernel");
 }
 

@@ -164,8 +164,20 @@ class Conv2d(nn.Conv2d):
         self.__dict__["_plan"] = (w.contiguous() if not channels_last else w, None if b is None else b.to(dtype).contiguous(), folded,
                                   self._sig())
 
+    def _padded_weight(self, p, cin):
+        """The plan's weight with zero input channels appended up to `cin` (same sums), cached per plan."""
+        c = self.__dict__.get("_w_pad")
+        if c is None or c[0] is not p[0] or c[1] != cin:
+            w = F.pad(p[0], (0, 0, 0, 0, 0, cin - p[0].shape[1]))
+            if p[0].is_contiguous(memory_format=torch.channels_last):
+                w = w.contiguous(memory_format=torch.channels_last)
+            c = (p[0], cin, w)
+            self.__dict__["_w_pad"] = c
+        return c[2]
+
     def drop_plan(self):
         self.__dict__.pop("_plan", None)
+        self.__dict__.pop("_w_pad", None)
 
     def forward(self, x, relu=False, add=None):
         """`relu` / `add`: the caller's trailing F.relu_ / residual add, handed over so that they can be fused."""
@@ -183,6 +195,8 @@ class Conv2d(nn.Conv2d):
             self.plan(*self.__dict__["_plan_args"])
             p = self.__dict__["_plan"]
         w, b, folded = p[:3]
+        if x.shape[1] > w.shape[1] and self.groups == 1:          # input with zero channels appended (ops.split_rgbd_input(pad8))
+            w = self._padded_weight(p, x.shape[1])
         wn = self.__dict__.get("_w_nchw")
         if wn is not None and 2 * max(self.dilation) > min(x.shape[-2:]):
             w, x = wn, x.contiguous()
@@ -404,7 +418,7 @@ class RGBDFusionBackbone(nn.Module):
         if (fast and x.is_cuda and x.dtype == torch.float32 and x.shape[1] == 9 and x.is_contiguous() and (x.shape[2] * x.shape[3]) % 4 == 0
                 and stem_plan is not None and stem_plan[0].dtype == torch.bfloat16):
             from . import ops
-            rgb_in, depth_in = ops.split_rgbd_input(x)       # both cats, the channels-last layout and the bf16 cast in one pass
+            rgb_in, depth_in = ops.split_rgbd_input(x, pad8=True)    # both cats, the channels-last layout and the bf16 cast in one pass
         else:
             if fast and x.is_cuda and stem_plan is not None and x.dtype != stem_plan[0].dtype:
                 x = x.to(stem_plan[0].dtype).contiguous(memory_format=torch.channels_last)     # what the caller used to do

@@ -459,18 +459,19 @@ def gemm_bias_act_cat2(a1, a2, weight, bias=None, act="none", out_dtype=None):
     return out.reshape(tuple(a1.shape[:-1]) + (N,))
 
 
-def split_rgbd_input(x):
+def split_rgbd_input(x, pad8=False):
     """x [B,9,H,W] float32 (rgb | depth | encoded offsets, ops.pack_input) -> (rgb6, depth6): NCHW-shaped [B,6,H,W]
     bfloat16 tensors in channels-last memory, cat([rgb, offsets], 1) and cat([depth, offsets], 1) of
-    RGBDFusionBackbone.forward (resnet.py:489-493) in one pass."""
+    RGBDFusionBackbone.forward (resnet.py:489-493) in one pass.  pad8: [B,8,H,W] with two zero channels behind them."""
     _need_cuda(x, "x", torch.float32)
     if x.dim() != 4 or x.shape[1] != 9 or not x.is_contiguous() or (x.shape[2] * x.shape[3]) % 4:
         raise ValueError("split_rgbd_input: x must be a contiguous [B,9,H,W] tensor with H*W a multiple of 4")
     B, _, H, W = x.shape
-    a = torch.empty((B, H, W, 6), dtype=torch.bfloat16, device=x.device)
-    b = torch.empty((B, H, W, 6), dtype=torch.bfloat16, device=x.device)
+    C = 8 if pad8 else 6
+    a = torch.empty((B, H, W, C), dtype=torch.bfloat16, device=x.device)
+    b = torch.empty((B, H, W, C), dtype=torch.bfloat16, device=x.device)
     with torch.cuda.device(x.device):
-        _lib.check(_lib.lib().quber_split_rgbd_input(_ptr(x), B, H, W, _ptr(a), _ptr(b), _stream()), "quber_split_rgbd_input")
+        _lib.check(_lib.lib().quber_split_rgbd_input(_ptr(x), B, H, W, C, _ptr(a), _ptr(b), _stream()), "quber_split_rgbd_input")
     return a.permute(0, 3, 1, 2), b.permute(0, 3, 1, 2)
 
 
@@ -1095,13 +1096,13 @@ def _register():
         return a.new_empty(tuple(a.shape[:-1]) + (weight.shape[0],), dtype=torch.bfloat16 if out_bf16 else torch.float32)
 
     @custom_op("quber::split_rgbd_input", mutates_args=(), device_types="cuda")
-    def _split_rgbd(x: T) -> tuple[T, T]:
-        return split_rgbd_input(x)
+    def _split_rgbd(x: T, pad8: bool) -> tuple[T, T]:
+        return split_rgbd_input(x, pad8)
 
     @_split_rgbd.register_fake
-    def _(x):
+    def _(x, pad8):
         B, _, H, W = x.shape
-        e = lambda: torch.empty((B, H, W, 6), dtype=torch.bfloat16, device=x.device).permute(0, 3, 1, 2)
+        e = lambda: torch.empty((B, H, W, 8 if pad8 else 6), dtype=torch.bfloat16, device=x.device).permute(0, 3, 1, 2)
         return e(), e()
 
     @custom_op("quber::gemm_bias_act_cat2", mutates_args=(), device_types="cuda")

@@ -553,5 +553,8 @@ def test_split_rgbd_input_equals_the_two_cats():
             assert got.shape == want.shape and got.dtype == torch.bfloat16
             assert got.is_contiguous(memory_format=torch.channels_last)
             assert torch.equal(got, want)
+        a8, b8 = ops.split_rgbd_input(x, pad8=True)
+        assert a8.shape == (B, 8, H, W) and torch.equal(a8[:, :6], a) and torch.equal(b8[:, :6], b)
+        assert float(a8[:, 6:].abs().max()) == 0.0 and float(b8[:, 6:].abs().max()) == 0.0
     with pytest.raises(ValueError):
         ops.split_rgbd_input(torch.zeros(1, 8, 4, 4, device="cuda"))
