@@ -455,10 +455,45 @@ class HotPath:
         refine_batch_host.  ~0.6 MB cross the host link instead of 295 MB (C2): quber_rle_decode writes the bit-packed
         planes that the encode pass reads anyway.  Same results and result layout as refine_batch_host; `slot` /
         `async_result` as there."""
+        B, K, H, W = shape
+        n = B * K
+        total = int(counts_host.numel())
+
+        def copy_in(st):                          # on the copy stream
+            if st.get("rle_cap", 0) < total:
+                st["rle_counts"] = torch.empty(max(total * 2, 1 << 16), dtype=torch.int32, device=self.device)
+                st["rle_offsets"] = torch.empty(n + 1, dtype=torch.int64, device=self.device)
+                st["rle_cap"] = st["rle_counts"].numel()
+            st["rle_counts"][:total].copy_(counts_host, non_blocking=True)
+            st["rle_offsets"].copy_(offsets_host, non_blocking=True)
+
+        def make_planes(st):                      # on the caller's stream, after the copies: -> status word or None
+            return ops.rle_decode(st["rle_counts"][:total], st["rle_offsets"], n, H, W, value=value, packed=True,
+                                  out=st["packed_dev"])[1]
+        return self._refine_planes("refine_batch_rle", shape, head_host, value, out_host, kernel_frames, slot, async_result,
+                                   copy_in, make_planes)
+
+    def refine_batch_bits(self, packed_host, shape, head_host, value=255, out_host=None, kernel_frames=16, slot=0,
+                          async_result=False):
+        """The end-to-end call for a caller that already holds the initial masks as bit planes: packed_host pinned int32
+        [B*K*H*W / 32] (bit i of word w = pixel 32 w + i of the flattened [B,K,H,W] array — what ops.host_pack_masks
+        writes), set pixels carry `value`.  An eighth of the dense call's bytes cross the link and no host thread packs.
+        Same results and result layout as refine_batch_host."""
+        B, K, H, W = shape
+        if packed_host.dtype != torch.int32 or packed_host.numel() * 32 != B * K * H * W:
+            raise ValueError("packed_host must hold B*K*H*W / 32 int32 words")
+
+        def copy_in(st):
+            st["packed_dev"].copy_(packed_host, non_blocking=True)
+        return self._refine_planes("refine_batch_bits", shape, head_host, value, out_host, kernel_frames, slot, async_result,
+                                   copy_in, lambda st: None)
+
+    def _refine_planes(self, what, shape, head_host, value, out_host, kernel_frames, slot, async_result, copy_in, make_planes):
+        """Shared body of the routes whose masks reach the device as bit planes (st["packed_dev"])."""
         dev = self.device
         B, K, H, W = shape
         if W % 32:
-            raise ValueError("refine_batch_rle needs W % 32 == 0 (decode the RLEs with ops.rle_decode and use the dense call)")
+            raise ValueError(f"{what} needs W % 32 == 0 (use the dense call)")
         st = self._staging_shape((B, K, H, W), head_host, slot)
         out = st["out"] if out_host is None else out_host
         cur = torch.cuda.current_stream(dev)
@@ -467,19 +502,12 @@ class HotPath:
         if st["free"] is not None:
             h2d.wait_event(st["free"])
         d2h.wait_stream(cur)
-        n = B * K
-        total = int(counts_host.numel())
-        if st.get("rle_cap", 0) < total:
-            st["rle_counts"] = torch.empty(max(total * 2, 1 << 16), dtype=torch.int32, device=dev)
-            st["rle_offsets"] = torch.empty(n + 1, dtype=torch.int64, device=dev)
-            st["rle_cap"] = st["rle_counts"].numel()
         with torch.cuda.stream(h2d):
             for k, v in head_host.items():
                 st["head"][k].copy_(v, non_blocking=True)
             heads_ready = h2d.record_event()
-            st["rle_counts"][:total].copy_(counts_host, non_blocking=True)
-            st["rle_offsets"].copy_(offsets_host, non_blocking=True)
-            rle_ready = h2d.record_event()
+            copy_in(st)
+            planes_ready = h2d.record_event()
         st["copied"]["heads"] = heads_ready
         cur.wait_event(heads_ready)
         r = self._run_graphed(st, "post", lambda: self.post(st["head"]))
@@ -495,9 +523,8 @@ class HotPath:
             out["labels"].copy_(r["labels"][:B * slab], non_blocking=True)
             out["scores"].copy_(r["scores"][:B * slab], non_blocking=True)
             out["boxes"].copy_(r["boxes"][:B * slab], non_blocking=True)
-        cur.wait_event(rle_ready)
-        _, rle_status = ops.rle_decode(st["rle_counts"][:total], st["rle_offsets"], n, H, W, value=value, packed=True,
-                                       out=st["packed_dev"])
+        cur.wait_event(planes_ready)
+        plane_status = make_planes(st)
         keep = []
         fw = K * H * W // 32
         step = kernel_frames if kernel_frames and kernel_frames < B else B
@@ -513,7 +540,10 @@ class HotPath:
             keep.append((enc, per, r, start[g0:g1], counts[g0:g1], g0))
         with torch.cuda.stream(d2h):
             d2h.wait_event(cur.record_event())
-            out["rle_status"].copy_(rle_status, non_blocking=True)
+            if plane_status is not None:
+                out["rle_status"].copy_(plane_status, non_blocking=True)
+            else:
+                out["rle_status"].zero_()
             out["boundary_status"].copy_(st["bstatus"], non_blocking=True)
             st["ready"] = d2h.record_event()
         st["free"] = cur.record_event()

@@ -512,3 +512,29 @@ def test_post_process_graph_capture_with_and_without_forked_error_maps():
     t = threading.Thread(target=capture_and_replay, args=("first_call_under_capture",))
     t.start(); t.join()
     assert result == {"forked": True, "first_call_under_capture": True}
+
+
+def test_refine_batch_bits_equals_dense_host_call():
+    """The bit-plane route (the caller holds one bit per pixel: an eighth of the bytes over the link, no host packing)
+    gives the dense call's results bit for bit, on repeated calls (graph replays, staging reuse)."""
+    B, K, H, W = 5, 7, 240, 320
+    masks, head = _inputs(B, K, H, W, seed=910)
+    hm = torch.from_numpy(masks).pin_memory()
+    hh = {k: torch.from_numpy(v).pin_memory() for k, v in head.items()}
+    words, value = ops.host_pack_masks(hm)
+    assert value == 255
+    hw = words.pin_memory()
+    dense, bits = HotPath(RefinerConfig(), "cuda"), HotPath(RefinerConfig(), "cuda")
+    o0, k0 = dense.refine_batch_host(hm, hh, chunk_frames=2)
+    torch.cuda.current_stream().synchronize()
+    o0 = {k: v.clone() for k, v in o0.items()}
+    for rep in range(3):
+        o1, k1 = bits.refine_batch_bits(hw, (B, K, H, W), hh, value=value, kernel_frames=2)
+        torch.cuda.current_stream().synchronize()
+        HotPath.check_status(o1)
+        for key in ("label_map", "boundary", "inst_start", "inst_counts"):
+            assert torch.equal(o0[key], o1[key]), key
+        assert torch.equal(torch.cat([k[0] for k in k0]), torch.cat([k[0] for k in k1]))
+        assert torch.equal(torch.cat([k[1] for k in k0]), torch.cat([k[1] for k in k1]))
+    with pytest.raises(ValueError):
+        bits.refine_batch_bits(hw[:-1], (B, K, H, W), hh)
