@@ -80,11 +80,9 @@ class MaskRefiner:
         self.fg_model = fg_model
         self.inpaint = inpaint_depth if inpaint is None else (inpaint or None)
 
-    def predict(self, rgb_path, depth_path, initial_masks, fg_mask=None, depth_is_metres=False):
-        """eval/refiner_model.py:224-297.  rgb_path: file path or [H,W,3] uint8 BGR array; depth_path: file path, raw
-        depth array [H,W] (mm; metres with `depth_is_metres` or a '.npy' path, :258-259) or None (armbench, RGB only);
-        initial_masks [N,h,w] bool | uint8.  Files are read and the frame resized as the reference does (:226-236,
-        :247-262); arrays are taken as they come (already at the working resolution)."""
+    def _prepare(self, rgb_path, depth_path, initial_masks, depth_is_metres=False):
+        """The host side in front of the predictor (eval/refiner_model.py:226-236, :247-267): read, resize, normalise and
+        in-paint with the reference's own OpenCV calls.  -> (rgb_img, depth_u8 | None, initial_masks, zero_depth | None)."""
         rgb_img, depth_img = rgb_path, depth_path
         from_files = isinstance(rgb_path, str)
         initial_masks = np.asarray(initial_masks)
@@ -116,8 +114,11 @@ class MaskRefiner:
                 depth_u8 = cv2.resize(depth_u8, (W, H), interpolation=cv2.INTER_NEAREST)     # :262
             if self.inpaint is not None:
                 depth_u8 = self.inpaint(depth_u8)                                            # :264
-        start = time.time()
-        output = self.refiner_predictor.predict(rgb_img, depth_u8, initial_masks)[0]
+        return rgb_img, depth_u8, initial_masks, zero_depth
+
+    def _finish(self, output, start, rgb_path, depth_path, fg_mask, zero_depth):
+        """The host side behind the predictor (:239-246, :269-297): foreground-overlap filter and OCID zero-depth clear on
+        the device."""
         if "instances" not in output:
             return [], output, time.time() - start, fg_mask
         masks = output["instances"].pred_masks                                               # [N,H,W] bool, device
@@ -140,6 +141,41 @@ class MaskRefiner:
         m = int(new_counts[0])
         refined = ops_masks_from_label_map(out_map[0], m).cpu().numpy()
         return refined, output, time.time() - start, fg_mask
+
+    def predict(self, rgb_path, depth_path, initial_masks, fg_mask=None, depth_is_metres=False):
+        """eval/refiner_model.py:224-297.  rgb_path: file path or [H,W,3] uint8 BGR array; depth_path: file path, raw
+        depth array [H,W] (mm; metres with `depth_is_metres` or a '.npy' path, :258-259) or None (armbench, RGB only);
+        initial_masks [N,h,w] bool | uint8.  Files are read and the frame resized as the reference does (:226-236,
+        :247-262); arrays are taken as they come (already at the working resolution)."""
+        rgb_img, depth_u8, initial_masks, zero_depth = self._prepare(rgb_path, depth_path, initial_masks, depth_is_metres)
+        start = time.time()
+        output = self.refiner_predictor.predict(rgb_img, depth_u8, initial_masks)[0]
+        return self._finish(output, start, rgb_path, depth_path, fg_mask, zero_depth)
+
+    def predict_many(self, rgb_paths, depth_paths, initial_masks_list, fg_masks=None, depth_is_metres=False, workers=8):
+        """`predict` for a list of frames — what the reference's evaluation loop does one frame at a time
+        (eval/eval_utils.py:360-392).  The host work in front of the network (file reads, resizes, depth normalisation and
+        TELEA in-painting: OpenCV releases the GIL) runs on `workers` threads, frames of one size go through the network and
+        the hot path as ONE batch (`MaskRefinerPredictor.predict_batch`), the caller-side filter runs per frame.  Returns
+        the list of `predict`'s tuples, in order; the results are the per-frame call's."""
+        n = len(rgb_paths)
+        depth_paths = [None] * n if depth_paths is None else depth_paths
+        fg_masks = [None] * n if fg_masks is None else fg_masks
+        if self.dataset == "armbench":                          # masks come back as device tensors of per-frame size: frame by frame
+            return [self.predict(r, d, m, f, depth_is_metres) for r, d, m, f in zip(rgb_paths, depth_paths, initial_masks_list, fg_masks)]
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max(1, int(workers))) as ex:
+            prep = list(ex.map(lambda a: self._prepare(a[0], a[1], a[2], depth_is_metres), zip(rgb_paths, depth_paths, initial_masks_list)))
+        results = [None] * n
+        groups = {}
+        for i, (rgb, dep, _, _) in enumerate(prep):
+            groups.setdefault((rgb.shape[:2], dep is None), []).append(i)
+        for idx in groups.values():
+            start = time.time()
+            outs = self.refiner_predictor.predict_batch([prep[i][0] for i in idx], [prep[i][1] for i in idx], [prep[i][2] for i in idx])
+            for i, out in zip(idx, outs):
+                results[i] = self._finish(out, start, rgb_paths[i], depth_paths[i], fg_masks[i], prep[i][3])
+        return results
 
 
 def ops_masks_from_label_map(label_map, n):

@@ -538,3 +538,67 @@ def test_refine_batch_bits_equals_dense_host_call():
         assert torch.equal(torch.cat([k[1] for k in k0]), torch.cat([k[1] for k in k1]))
     with pytest.raises(ValueError):
         bits.refine_batch_bits(hw[:-1], (B, K, H, W), hh)
+
+
+def test_predict_many_equals_frame_by_frame_predict(tmp_path):
+    """MaskRefiner.predict_many: host preparation on worker threads, frames of one size through the predictor as ONE batch,
+    the caller-side filter per frame — the results are those of `predict` called frame by frame, in order, for files and
+    for arrays, with frames of two sizes in one call."""
+    import cv2
+    from quber_b200.meta_arch import Instances
+    from quber_b200.refiner_model import MaskRefiner, inpaint_depth
+    rng = np.random.default_rng(11)
+    n = 5
+    rgb_paths, depth_paths, masks, fgs = [], [], [], []
+    for i in range(n):
+        rgb = rng.integers(0, 255, (480, 640, 3), dtype=np.uint8)          # OCID frames are 640 x 480 on disk
+        depth = rng.integers(300, 1400, (480, 640)).astype(np.uint16)
+        depth[rng.random((480, 640)) < 0.05] = 0
+        cv2.imwrite(str(tmp_path / f"rgb{i}.png"), rgb)
+        cv2.imwrite(str(tmp_path / f"depth{i}.png"), depth)
+        rgb_paths.append(str(tmp_path / f"rgb{i}.png")); depth_paths.append(str(tmp_path / f"depth{i}.png"))
+        m = synth.ellipse_masks(3 + i, 480, 640, seed=20 + i, axes=(15, 50), margin=40) != 0
+        masks.append(m)
+        fgs.append(m[: 2].any(0))
+    calls = []
+
+    class Stub:                                   # "refined" instances = the initial masks made disjoint, scaled by the mean depth sign
+        def _one(self, rgb_img, dep, init):
+            init = np.asarray(init) != 0
+            taken = np.zeros(init.shape[1:], bool)
+            out = []
+            for m in init:
+                m = m & ~taken
+                taken |= m
+                out.append(m)
+            return {"instances": Instances(init.shape[1:], pred_masks=torch.from_numpy(np.stack(out)).cuda()),
+                    "probe": (int(rgb_img.sum()) % 9973, None if dep is None else int(dep.sum()) % 9973)}
+
+        def predict(self, rgb_img, dep, init):
+            calls.append(1)
+            return [self._one(rgb_img, dep, init)]
+
+        def predict_batch(self, rgbs, deps, inits):
+            calls.append(len(rgbs))
+            return [self._one(r, d, m) for r, d, m in zip(rgbs, deps, inits)]
+
+    r = MaskRefiner.__new__(MaskRefiner)
+    r.refiner_predictor, r.dataset, r.fg_model, r.inpaint = Stub(), "OCID", None, inpaint_depth
+    want = [r.predict(a, b, m, fg_mask=f) for a, b, m, f in zip(rgb_paths, depth_paths, masks, fgs)]
+    calls.clear()
+    got = r.predict_many(rgb_paths, depth_paths, masks, fgs, workers=4)
+    assert calls == [n]                                                   # one batch
+    assert len(got) == n
+    for g, w in zip(got, want):
+        assert np.array_equal(g[0], w[0]) and g[1]["probe"] == w[1]["probe"] and np.array_equal(g[3], w[3])
+    # arrays of two sizes: two batches, results in the caller's order
+    arrs = [rng.integers(0, 255, (120 if i % 2 else 96, 160, 3), dtype=np.uint8) for i in range(4)]
+    deps = [rng.integers(300, 1400, a.shape[:2]).astype(np.uint16) for a in arrs]
+    ms = [synth.ellipse_masks(2, a.shape[0], 160, seed=40 + i, axes=(6, 20), margin=10) != 0 for i, a in enumerate(arrs)]
+    r.dataset, r.inpaint = "OSD", None
+    calls.clear()
+    got = r.predict_many(arrs, deps, ms, [m.any(0) for m in ms], workers=2)
+    assert sorted(calls) == [2, 2]
+    for i, g in enumerate(got):
+        w = r.predict(arrs[i], deps[i], ms[i], fg_mask=ms[i].any(0))
+        assert np.array_equal(g[0], w[0]) and g[1]["probe"] == w[1]["probe"]
