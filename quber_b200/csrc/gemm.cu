@@ -34,7 +34,8 @@
 namespace quber {
 
 constexpr int G_BM = 128;
-constexpr int G_THREADS = 192;
+constexpr int G_THREADS = 192;          // producer, MMA issuer, 4 epilogue warps (SPLIT kernels; + 4 converter warps)
+constexpr int G_THREADS8 = 320;         // ... 8 epilogue warps (all other kernels)
 constexpr int G_KBYTES = 128;          // bytes of K per stage row = one 128B swizzle atom
 
 __device__ __forceinline__ uint32_t g_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -93,7 +94,7 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
 //   warps 2-5    epilogue: tcgen05.ld -> + bias -> activation -> swizzled staging -> TMA store; arrive on tmem_empty[buf]
 //   warps 6-9    (SPLIT only) operand split of the A stage in shared memory, between the TMA's arrival and the MMA issue
 template <int BN, bool TF32, typename OT, bool SPLIT = false>
-__global__ void __launch_bounds__(SPLIT ? G_THREADS + 128 : G_THREADS)
+__global__ void __launch_bounds__(SPLIT ? G_THREADS + 128 : G_THREADS8)
 gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                      const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_c,
                      const float *__restrict__ bias, int M, int N, int K, int act,
@@ -111,7 +112,11 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     constexpr int A_BYTES = G_BM * G_KBYTES, W_BYTES = BN * G_KBYTES, STAGE = (SPLIT ? 2 : 1) * (A_BYTES + W_BYTES);
     constexpr int W_OFF = (SPLIT ? 2 : 1) * A_BYTES;    // stage layout: A [| A_lo] | W [| W_lo]
     constexpr int KELEMS = TF32 ? 32 : 64;              // elements of K per stage
-    unsigned char *stg_base = gsm + (size_t)NST * STAGE;      // epilogue staging: 4 warps x 2 buffers x 4 KB, after the ring
+    // Epilogue warps: a warp reads the TMEM lanes 32 * (warp % 4) .. + 31 only, so four warps cover a tile's rows.  With
+    // K = 256 a tile's MMAs take ~1.8 us while four warps need ~3.5 us to drain, convert and stage 128 x 256 outputs: the
+    // kernels that are not tensor-bound run EIGHT epilogue warps, two per lane quarter, each taking half of the columns.
+    constexpr int NEPI = SPLIT ? 4 : 8;
+    unsigned char *stg_base = gsm + (size_t)NST * STAGE;      // epilogue staging: NEPI warps x 2 buffers x 4 KB, after the ring
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nkb = (K + KELEMS - 1) / KELEMS;
     const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + G_BM - 1) / G_BM;
@@ -119,7 +124,7 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < 4; ++s) { g_mbar_init(&full[s], 1); g_mbar_init(&empty[s], 1); g_mbar_init(&conv[s], 128); }
-        for (int s = 0; s < 2; ++s) { g_mbar_init(&tmem_full[s], 1); g_mbar_init(&tmem_empty[s], 4); }
+        for (int s = 0; s < 2; ++s) { g_mbar_init(&tmem_full[s], 1); g_mbar_init(&tmem_empty[s], NEPI); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         abort_s = 0;
     }
@@ -189,14 +194,17 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                 tc_commit(&tmem_full[buf]);                      // accumulator complete (or abort: release the epilogue)
             }
         }
-    } else if (warp < 6) {
-        // ===== epilogue: warps 2..5 own TMEM lanes 32 * (warp % 4) .. +31 =====
+    } else if (warp < 2 + NEPI) {
+        // ===== epilogue: warps 2 .. 1 + NEPI own TMEM lanes 32 * (warp % 4) .. +31 =====
         // Each warp stages its 32 rows x 128 bytes of output per chunk in its own shared-memory buffers, 128B-swizzled so
         // that the 32 row-owning lanes hit distinct banks, and hands it to a TMA store: full 128-byte row segments leave
         // the SM, rows / columns past the matrix edge are clipped by the hardware.  Two staging buffers per warp: the store
         // of chunk c overlaps the TMEM read of chunk c + 1.
         const int q = warp & 3;
         constexpr int CW = 128 / (int)sizeof(OT);            // output columns per 128-byte chunk: 32 fp32 / 64 bf16
+        constexpr int NCH = BN / CW;                         // chunks per tile; this warp's share: [ch0, ch1)
+        const int part = (warp - 2) >> 2;                    // 0, or 1 for the second set of four warps
+        const int ch0 = NEPI == 8 ? (part == 0 ? 0 : (NCH + 1) / 2) : 0, ch1 = NEPI == 8 ? (part == 0 ? (NCH + 1) / 2 : NCH) : NCH;
         unsigned char *stg = stg_base + (size_t)(warp - 2) * 2 * 4096;
         const uint32_t sw = (uint32_t)(lane & 7);            // swizzle phase of this lane's staging row
         int tc = 0, ci = 0, last_n0 = -1;
@@ -204,17 +212,22 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             const int buf = tc & 1;
             const int m0 = (t / tiles_n) * G_BM, n0 = (t % tiles_n) * BN;
             if (n0 != last_n0) {                             // the tile's bias slice (changes only when tiles_n > 1)
-                asm volatile("bar.sync 1, 128;" ::: "memory");              // nobody still reads the previous slice
-                for (int i = threadIdx.x - 64; i < BN; i += 128) bias_s[i] = (bias && n0 + i < N) ? __ldg(bias + n0 + i) : 0.f;
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(NEPI * 32) : "memory");              // nobody still reads the previous slice
+                for (int i = threadIdx.x - 64; i < BN; i += NEPI * 32) bias_s[i] = (bias && n0 + i < N) ? __ldg(bias + n0 + i) : 0.f;
+                asm volatile("bar.sync 1, %0;" ::"n"(NEPI * 32) : "memory");
                 last_n0 = n0;
             }
             const bool ok = g_mbar_wait(&tmem_full[buf], (tc >> 1) & 1);
             tc_fence_after();
             if (!ok || abort_s) break;
             const uint32_t acc = tmem_d + (uint32_t)(buf * BN);
+            if (ch0 >= ch1) {                                // nothing to drain (one-chunk tiles): hand the accumulator back at once
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(g_smem_u32(&tmem_empty[buf])) : "memory");
+            }
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += CW, ++ci) {
+            for (int c0 = ch0 * CW; c0 < ch1 * CW; c0 += CW, ++ci) {
                 unsigned char *bufp = stg + (ci & 1) * 4096;
                 if (ci >= 2) {
                     if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
@@ -258,7 +271,7 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                         }
                     }
                 }
-                if (c0 + CW >= BN) {                         // last TMEM read of this tile: hand the accumulator back to the MMA warp
+                if (c0 + CW >= ch1 * CW) {                   // this warp's last TMEM read of the tile: hand the accumulator back to the MMA warp
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(g_smem_u32(&tmem_empty[buf])) : "memory");
@@ -276,7 +289,7 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         }
         if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // smem must outlive the stores that read it
     } else if (SPLIT) {
-        // ===== operand split (warps 6..9 = 128 threads): A -> A_hi (in place), A_lo, 16 KB per stage, elementwise =====
+        // ===== operand split (SPLIT kernels have 4 epilogue warps: warps 6..9 = 128 threads): A -> A_hi (in place), A_lo =====
         const int tdx = threadIdx.x - G_THREADS;
         int it = 0;
         bool ok = true;
@@ -338,11 +351,11 @@ template <int BN, bool TF32, typename OT, bool SPLIT = false>
 static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUtensorMap &mwlo, const CUtensorMap &mc, const float *bias,
                        int M, int N, int K, int act, cudaStream_t st, const CUtensorMap *ma2 = nullptr, int kb_split = 0) {
     constexpr int NST = SPLIT ? 2 : (BN == 256 ? 3 : 4);
-    const size_t smem = (size_t)NST * (SPLIT ? 2 : 1) * (G_BM + BN) * G_KBYTES + 4 * 2 * 4096 + 1024;
+    const size_t smem = (size_t)NST * (SPLIT ? 2 : 1) * (G_BM + BN) * G_KBYTES + (SPLIT ? 4 : 8) * 2 * 4096 + 1024;
     QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_bias_act_kernel<BN, TF32, OT, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long ntiles = (long long)cdiv(M, G_BM) * cdiv(N, BN);
     const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());       // persistent: one CTA per SM
-    gemm_bias_act_kernel<BN, TF32, OT, SPLIT><<<grid, SPLIT ? G_THREADS + 128 : G_THREADS, smem, st>>>(ma, mw, mwlo, mc, bias, M, N, K, act,
+    gemm_bias_act_kernel<BN, TF32, OT, SPLIT><<<grid, SPLIT ? G_THREADS + 128 : G_THREADS8, smem, st>>>(ma, mw, mwlo, mc, bias, M, N, K, act,
                                                                                                      ma2 ? *ma2 : ma, kb_split);
     return check_launch("gemm_bias_act_kernel");
 }
