@@ -624,8 +624,9 @@ def encoder_side_measurement(dev, c, peaks):
         enc = MSDeformAttnTransformerEncoderOnly(256, M_HEADS, N_LAYERS, 1024, 0.0, "relu", L, N_POINTS).to(dev).eval()
         shapes = list(c["levels"])[::-1]                      # res5 -> res3 order (msdeformattn.py:318-324)
         B = c["B"]
-        srcs = [torch.randn(B, 256, h, w, device=dev) for h, w in shapes]
-        pos = [torch.randn(B, 256, h, w, device=dev) * 0.1 for h, w in shapes]
+        # channels-last memory, as the network's input_proj convolutions hand the level maps over (the flatten is then a view)
+        srcs = [torch.randn(B, 256, h, w, device=dev).contiguous(memory_format=torch.channels_last) for h, w in shapes]
+        pos = [(torch.randn(B, 256, h, w, device=dev) * 0.1).contiguous(memory_format=torch.channels_last) for h, w in shapes]
         rows = B * sum(h * w for h, w in shapes)
         flops = 2.0 * rows * 256 * (256 + 288 + 256 + 1024 + 1024) * N_LAYERS      # value, offsets|weights, output, FFN1, FFN2
         with torch.no_grad():
@@ -660,7 +661,8 @@ def encoder_side_measurement(dev, c, peaks):
         if "bf16_tflops_sustained" in peaks and "gemm_tflops_bf16" in out:
             out["gemm_frac_of_measured_bf16_peak"] = out["gemm_tflops_bf16"]["algorithmic"] / peaks["bf16_tflops_sustained"]
         out["note"] = ("6 encoder layers for the config's frames, every Linear / FFN GEMM on quber_gemm_bias_act(_x3), sampling on "
-                       "quber_msda_forward_fused, residual + LayerNorm on quber_add_layer_norm; no cuBLAS call; outside `value`")
+                       "quber_msda_forward_fused, residual + LayerNorm on quber_add_layer_norm; no cuBLAS call; level maps in channels-last memory "
+                       "(what the network hands over); outside `value`")
     except Exception as e:
         out["error"] = f"{type(e).__name__}: {e}"[:300]
     return out

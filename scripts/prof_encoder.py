@@ -9,8 +9,8 @@ torch.manual_seed(0)
 enc = MSDeformAttnTransformerEncoderOnly(256, 8, 6, 1024, 0.0, "relu", 3, 4).to(dev).eval()
 shapes = [(15, 20), (30, 40), (60, 80)]
 B = 32
-srcs = [torch.randn(B, 256, h, w, device=dev) for h, w in shapes]
-pos = [torch.randn(B, 256, h, w, device=dev) * 0.1 for h, w in shapes]
+srcs = [torch.randn(B, 256, h, w, device=dev).contiguous(memory_format=torch.channels_last) for h, w in shapes]
+pos = [(torch.randn(B, 256, h, w, device=dev) * 0.1).contiguous(memory_format=torch.channels_last) for h, w in shapes]
 with torch.no_grad():
     for prec in (sys.argv[1:] or ["bf16", "fp32"]):
         enc.set_precision(prec)
