@@ -446,8 +446,16 @@ def run_ours(args):
     e2e_host = dict(time_e2e.host_ms)
     rle_val, rle_ms, _, _ = time_e2e(e2e_rle)
     rle_host = dict(time_e2e.host_ms)
-    _, e2e_ms_sync, _, _ = time_e2e(e2e_dense, 1) if E2E_DEPTH > 1 else (0, e2e_ms, 0, 0)
-    _, rle_ms_sync, _, _ = time_e2e(e2e_rle, 1) if E2E_DEPTH > 1 else (0, rle_ms, 0, 0)
+    e2e_val1, e2e_ms_sync, _, _ = time_e2e(e2e_dense, 1) if E2E_DEPTH > 1 else (e2e_val, e2e_ms, 0, 0)
+    rle_val1, rle_ms_sync, _, _ = time_e2e(e2e_rle, 1) if E2E_DEPTH > 1 else (rle_val, rle_ms, 0, 0)
+    # Both ways of driving the same public call are measured (two calls in flight on alternating slots / one at a time);
+    # the line's `e2e` is the faster one on this host and says which (`calls_in_flight`), the other figure stays beside it.
+    e2e_ms2, rle_ms2 = e2e_ms, rle_ms
+    e2e_depth = rle_depth = E2E_DEPTH
+    if e2e_val1 > e2e_val:
+        e2e_val, e2e_ms, e2e_depth = e2e_val1, e2e_ms_sync, 1
+    if rle_val1 > rle_val:
+        rle_val, rle_ms, rle_depth = rle_val1, rle_ms_sync, 1
     packed = bool(hp.pack_masks)
     head_bytes = sum(v.numel() * 4 for v in sets[0]["h_head"].values())
     route = getattr(hp, "last_route_dense", dict(byte_frames=B, packed_frames=0))
@@ -519,7 +527,7 @@ def run_ours(args):
         "data": "synthetic", "config": workload_config(name, world, gather_info), "clocks": clocks,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms, "steps": e2e_steps, "host_link": pcie,
-                "calls_in_flight": E2E_DEPTH, "ms_per_step_one_call_in_flight": e2e_ms_sync,
+                "calls_in_flight": e2e_depth, "ms_per_step_one_call_in_flight": e2e_ms_sync, "ms_per_step_two_calls_in_flight": e2e_ms2,
                 "host_ms_per_step": e2e_host,
                 "input": "dense uint8 masks [B,K,H,W] in pinned host memory (MaskRefinerPredictor.predict's contract)",
                 "mask_transfer": ("%d frames as bytes through the copy engine while %d host threads bit-pack the other %d (one bit per pixel), "
@@ -532,8 +540,8 @@ def run_ours(args):
                                                         sets[0]["h_masks"].numel() / (pcie.get("host_pack_gbs", 1e9) * 1e9) * 1e3)
                          else "kernels",
                 "schedule": {"chunk_frames": E2E_CHUNK, "min_tail": E2E_TAIL, "kernel_frames": E2E_KERNEL, "label_map": "uint8"}},
-        "e2e_rle": {"value": rle_val, "unit": UNIT, "ms_per_step": rle_ms, "calls_in_flight": E2E_DEPTH,
-                    "ms_per_step_one_call_in_flight": rle_ms_sync, "host_ms_per_step": rle_host, "h2d_bytes_per_step": int(h2d_rle),
+        "e2e_rle": {"value": rle_val, "unit": UNIT, "ms_per_step": rle_ms, "calls_in_flight": rle_depth,
+                    "ms_per_step_one_call_in_flight": rle_ms_sync, "ms_per_step_two_calls_in_flight": rle_ms2, "host_ms_per_step": rle_host, "h2d_bytes_per_step": int(h2d_rle),
                     "d2h_bytes_per_step": int(d2h), "graphs": bool(hp.use_graphs),
                     "input": "the same masks as COCO RLE counts (register_uoais_sim_panoptic.py:121-144) in pinned host memory, "
                              "decoded on the device by quber_rle_decode",
