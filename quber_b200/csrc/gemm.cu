@@ -107,7 +107,7 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     unsigned char *gsm = gsm_raw + ((1024u - (g_smem_u32(gsm_raw) & 1023u)) & 1023u);
     __shared__ __align__(8) uint64_t full[4], empty[4], conv[4], tmem_full[2], tmem_empty[2];
     __shared__ uint32_t tmem_base_s;
-    __shared__ float bias_s[BN];
+    __shared__ __align__(16) float bias_s[BN];
     __shared__ int abort_s;
     constexpr int A_BYTES = G_BM * G_KBYTES, W_BYTES = BN * G_KBYTES, STAGE = (SPLIT ? 2 : 1) * (A_BYTES + W_BYTES);
     constexpr int W_OFF = (SPLIT ? 2 : 1) * A_BYTES;    // stage layout: A [| A_lo] | W [| W_lo]
@@ -248,11 +248,17 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                         : "r"(taddr));
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     float v[32];
+                    const float4 *b4 = reinterpret_cast<const float4 *>(bias_s + c0 + 32 * h);   // 8 broadcast LDS.128, not 32 LDS.32
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        float x = __uint_as_float(r[j]) + bias_s[c0 + 32 * h + j];
-                        if (act == 1) x = fmaxf(x, 0.f);
-                        v[j] = x;
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 bb = b4[j4];
+                        const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+                        for (int t2 = 0; t2 < 4; ++t2) {
+                            float x = __uint_as_float(r[4 * j4 + t2]) + bv[t2];
+                            if (act == 1) x = fmaxf(x, 0.f);
+                            v[4 * j4 + t2] = x;
+                        }
                     }
                     if constexpr (sizeof(OT) == 4) {
 #pragma unroll
@@ -321,6 +327,177 @@ gemm_bias_act_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(2 * BN) : "memory");
 }
 
+// ------------------------------------------------------------------------------------------------
+// W-resident variant for bf16 operands, BN = 256 and K <= 256 (the MSDeformAttn projections and FFN1: K = d_model).
+// ncu on the kernel above: after the epilogue was widened, 35 % of all warp samples are epilogue warps waiting for
+// tmem_full — the MMAs wait for their operands, and two thirds of the operand bytes are the W tile (256 x 256 bf16 =
+// 128 KB) that every output tile fetches again from L2: 148 SMs x 192 KB per 3.2 us = 8.9 TB/s, ~70 % of what the L2
+// delivers chip-wide.  Here a CTA keeps ONE W tile in shared memory for its whole life (CTA c owns the n-tile c mod
+// tiles_n and walks m-tiles), so a tile costs 64 KB of A from L2 instead of 192 KB.
+//   shared memory: W 4 x 32 KB | A ring 4 x 16 KB | staging 8 warps x 4 KB (single buffers: the ring took their twins)
+// Roles as above: warp 0 producer, warp 1 MMA issuer, warps 2-9 epilogue.
+template <typename OT>
+__global__ void __launch_bounds__(G_THREADS8)
+gemm_wres_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                 const __grid_constant__ CUtensorMap map_c, const float *__restrict__ bias, int M, int N, int K, int act) {
+    constexpr int BN = 256, NSTA = 4, KELEMS = 64;
+    constexpr int A_BYTES = G_BM * G_KBYTES, WKB_BYTES = BN * G_KBYTES;      // 16 KB, 32 KB per k-block
+    extern __shared__ __align__(1024) unsigned char gsm_raw[];
+    unsigned char *gsm = gsm_raw + ((1024u - (g_smem_u32(gsm_raw) & 1023u)) & 1023u);
+    __shared__ __align__(8) uint64_t full[NSTA], empty[NSTA], w_full, tmem_full[2], tmem_empty[2];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ __align__(16) float bias_s[BN];
+    __shared__ int abort_s;
+    unsigned char *w_res = gsm, *a_ring = gsm + 4 * WKB_BYTES, *stg_base = a_ring + NSTA * A_BYTES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nkb = (K + KELEMS - 1) / KELEMS;                               // <= 4
+    const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + G_BM - 1) / G_BM;
+    const int nt = blockIdx.x % tiles_n, g = blockIdx.x / tiles_n, G = gridDim.x / tiles_n;   // host: gridDim.x % tiles_n == 0
+    const int n0 = nt * BN;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NSTA; ++s) { g_mbar_init(&full[s], 1); g_mbar_init(&empty[s], 1); }
+        g_mbar_init(&w_full, 1);
+        for (int s = 0; s < 2; ++s) { g_mbar_init(&tmem_full[s], 1); g_mbar_init(&tmem_empty[s], 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        abort_s = 0;
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(g_smem_u32(&tmem_base_s)), "n"(2 * BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_d = tmem_base_s;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer: the W tile once, then the A tiles of this CTA's m-tiles =====
+            g_mbar_expect_tx(&w_full, (uint32_t)nkb * WKB_BYTES);
+            for (int kb = 0; kb < nkb; ++kb) g_tma_load_2d(w_res + (size_t)kb * WKB_BYTES, &map_w, &w_full, kb * KELEMS, n0);
+            int it = 0;
+            for (int mt = g; mt < tiles_m && !abort_s; mt += G) {
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % NSTA;
+                    if (it >= NSTA && !g_mbar_wait(&empty[s], ((it / NSTA) - 1) & 1)) { abort_s = 1; break; }
+                    g_mbar_expect_tx(&full[s], A_BYTES);
+                    g_tma_load_2d(a_ring + (size_t)s * A_BYTES, &map_a, &full[s], kb * KELEMS, mt * G_BM);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(G_BM >> 4) << 24);
+            int it = 0, tc = 0;
+            bool ok = g_mbar_wait(&w_full, 0);
+            if (!ok) abort_s = 1;
+            tc_fence_after();
+            for (int mt = g; mt < tiles_m && ok; mt += G, ++tc) {
+                const int buf = tc & 1;
+                if (tc >= 2 && !g_mbar_wait(&tmem_empty[buf], ((tc >> 1) - 1) & 1)) { abort_s = 1; break; }
+                tc_fence_after();
+                const uint32_t acc = tmem_d + (uint32_t)(buf * BN);
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % NSTA;
+                    ok = g_mbar_wait(&full[s], (it / NSTA) & 1);
+                    if (!ok) { abort_s = 1; break; }
+                    tc_fence_after();
+                    const uint64_t ad = umma_desc_k128(g_smem_u32(a_ring + (size_t)s * A_BYTES));
+                    const uint64_t wd = umma_desc_k128(g_smem_u32(w_res + (size_t)kb * WKB_BYTES));
+#pragma unroll
+                    for (int k = 0; k < G_KBYTES / 32; ++k) tc_mma(acc, ad + 2 * k, wd + 2 * k, idesc, (kb | k) != 0, 0);
+                    tc_commit(&empty[s]);
+                }
+                tc_commit(&tmem_full[buf]);
+            }
+        }
+    } else {
+        // ===== epilogue: warps 2..9, two per TMEM lane quarter, half of the columns each =====
+        const int q = warp & 3, part = (warp - 2) >> 2;
+        constexpr int CW = 128 / (int)sizeof(OT), NCH = BN / CW;
+        const int ch0 = part == 0 ? 0 : NCH / 2, ch1 = part == 0 ? NCH / 2 : NCH;
+        unsigned char *bufp = stg_base + (size_t)(warp - 2) * 4096;
+        const uint32_t sw = (uint32_t)(lane & 7);
+        for (int i = threadIdx.x - 64; i < BN; i += 256) bias_s[i] = (bias && n0 + i < N) ? __ldg(bias + n0 + i) : 0.f;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        unsigned char *myrow = bufp + lane * 128;
+        int tc = 0, ci = 0;
+        for (int mt = g; mt < tiles_m; mt += G, ++tc) {
+            const int buf = tc & 1, m0 = mt * G_BM;
+            const bool ok = g_mbar_wait(&tmem_full[buf], (tc >> 1) & 1);
+            tc_fence_after();
+            if (!ok || abort_s) break;
+            const uint32_t acc = tmem_d + (uint32_t)(buf * BN) + ((uint32_t)(32 * q) << 16);
+#pragma unroll 1
+            for (int c0 = ch0 * CW; c0 < ch1 * CW; c0 += CW, ++ci) {
+                uint32_t outw[32];                                   // the chunk's 128 bytes of this lane's row
+#pragma unroll
+                for (int h = 0; h < CW / 32; ++h) {
+                    uint32_t r[32];
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+                          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+                          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                        : "r"(acc + (uint32_t)(c0 + 32 * h)));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const float4 *b4 = reinterpret_cast<const float4 *>(bias_s + c0 + 32 * h);   // 8 broadcast LDS.128, not 32 LDS.32
+#pragma unroll
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 bb = b4[j4];
+                        const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+                        for (int t2 = 0; t2 < 4; ++t2) {
+                            float x = __uint_as_float(r[4 * j4 + t2]) + bv[t2];
+                            if (act == 1) x = fmaxf(x, 0.f);
+                            r[4 * j4 + t2] = __float_as_uint(x);
+                        }
+                    }
+                    if constexpr (sizeof(OT) == 4) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) outw[j] = r[j];
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const __nv_bfloat162 hh = __floats2bfloat162_rn(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+                            outw[16 * h + j] = *reinterpret_cast<const uint32_t *>(&hh);
+                        }
+                    }
+                }
+                if (c0 + CW >= ch1 * CW) {                           // last TMEM read of the tile by this warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(g_smem_u32(&tmem_empty[buf])) : "memory");
+                }
+                if (ci >= 1) {                                       // single staging buffer: the previous store has read it
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    __syncwarp();
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j)                          // 16-byte chunk j of the row lands at chunk j ^ (row & 7)
+                    *reinterpret_cast<uint4 *>(myrow + ((((uint32_t)j) ^ sw) << 4)) =
+                        make_uint4(outw[4 * j], outw[4 * j + 1], outw[4 * j + 2], outw[4 * j + 3]);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) {
+                    if (n0 + c0 < N)
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+                                     ::"l"(&map_c), "r"(g_smem_u32(bufp)), "r"(n0 + c0), "r"(m0 + 32 * q) : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+            }
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(2 * BN) : "memory");
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -360,6 +537,18 @@ static int gemm_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUten
     return check_launch("gemm_bias_act_kernel");
 }
 
+template <typename OT>
+static int gemm_wres_launch(const CUtensorMap &ma, const CUtensorMap &mw, const CUtensorMap &mc, const float *bias, int M, int N, int K,
+                            int act, cudaStream_t st) {
+    const size_t smem = 4 * (size_t)256 * G_KBYTES + 4 * (size_t)G_BM * G_KBYTES + 8 * 4096 + 1024;
+    QUBER_CUDA_TRY(cudaFuncSetAttribute(gemm_wres_kernel<OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int tiles_n = cdiv(N, 256), tiles_m = cdiv(M, G_BM);
+    int per = sm_count() / tiles_n;                               // CTAs per n-tile
+    if (per > tiles_m) per = tiles_m;
+    gemm_wres_kernel<OT><<<per * tiles_n, G_THREADS8, smem, st>>>(ma, mw, mc, bias, M, N, K, act);
+    return check_launch("gemm_wres_kernel");
+}
+
 // w -> hi = w with the 13 low mantissa bits cleared (what kind::tf32 reads), lo = w - hi (exact)
 __global__ void __launch_bounds__(256)
 split_tf32_kernel(const float *__restrict__ w, size_t n, float *__restrict__ hi, float *__restrict__ lo) {
@@ -396,6 +585,10 @@ extern "C" int quber_gemm_bias_act(const void *A, const void *W, const float *bi
         return QUBER_E_CUDA;
     }
     cudaStream_t st = (cudaStream_t)stream;
+    // W tile resident in shared memory: measured for bf16 output (FFN1 138 -> 121 us, value projection 46 -> 42 us); with
+    // fp32 output its single staging buffers cost what the saved L2 traffic returns (59 -> 62 us), so those stay above
+    if (!tf32 && out_dtype == 1 && BN == 256 && K <= 256 && cdiv(N, 256) <= sm_count())
+        return gemm_wres_launch<__nv_bfloat16>(ma, mw, mc, bias, M, N, K, act, st);
 #define QG(BN_, TF_, OT_) return gemm_launch<BN_, TF_, OT_>(ma, mw, mw, mc, bias, M, N, K, act, st)
     if (BN == 256) {
         if (tf32) { if (out_dtype == 0) QG(256, true, float); else QG(256, true, __nv_bfloat16); }
