@@ -658,8 +658,9 @@ def encoder_side_measurement(dev, c, peaks):
                     t_us = getattr(ev, "device_time_total", None)
                     if t_us is None:
                         t_us = getattr(ev, "cuda_time_total", 0.0)
-                    for key in ("gemm_bias_act", "msda_fused", "add_layer_norm"):
-                        if key in ev.key:
+                    for key, names in (("gemm_bias_act", ("gemm_bias_act", "gemm_wres")), ("msda_fused", ("msda_fused",)),
+                                       ("add_layer_norm", ("add_layer_norm",))):
+                        if any(nm in ev.key for nm in names):            # both GEMM kernels (csrc/gemm.cu) under one key
                             by[key] = by.get(key, 0.0) + t_us * 1e-3
                 gemm_ms = by.get("gemm_bias_act", 0.0)
                 issued = flops * (3 if prec == "fp32" else 1)
