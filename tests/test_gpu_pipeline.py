@@ -507,7 +507,9 @@ def test_post_process_graph_capture_with_and_without_forked_error_maps():
             for _ in range(2):
                 g.replay()
             s.synchronize()
-            result[tag] = all(torch.equal(r[k], want[k]) for k in keys if k in want and want[k] is not None)
+            n_valid = int(want["inst_offsets"][-1])                  # rows of the instance pool past it are never written
+            same = all(torch.equal(r[k], want[k]) for k in keys if k != "masks" and k in want and want[k] is not None)
+            result[tag] = same and torch.equal(r["masks"][:n_valid], want["masks"][:n_valid])
     capture_and_replay("forked")                            # this thread's side stream exists since the eager call above
     t = threading.Thread(target=capture_and_replay, args=("first_call_under_capture",))
     t.start(); t.join()
