@@ -563,7 +563,10 @@ def _tf32(x):
 
 
 @pytest.mark.parametrize("shape", [(128, 128, 64), (300, 256, 256), (1000, 192, 256), (1000, 96, 256), (515, 1024, 256),
-                                   (515, 256, 1024), (77, 40, 168), (1000, 4, 32), (333, 100, 72), (6300, 256, 256)])
+                                   (515, 256, 1024), (77, 40, 168), (1000, 4, 32), (333, 100, 72), (6300, 256, 256),
+                                   # the W-resident bf16 kernel's edges: K off the 64-element k-block, one k-block only, several
+                                   # n-tiles with fewer m-tiles than CTAs per n-tile, many m-tiles per CTA
+                                   (130, 256, 72), (1, 512, 64), (40000, 768, 200), (257, 256, 8)])
 @pytest.mark.parametrize("dt", ["bf16", "tf32"])
 def test_gemm_bias_act_matches_fp64_reference(shape, dt):
     """C = relu(A W^T + b) against a float64 torch reference on inputs that are exactly representable in the
